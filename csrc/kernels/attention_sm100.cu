@@ -1,0 +1,423 @@
+// attention_sm100.cu — fused multi-head self-attention forward and backward for sequences of up to
+// 128 tokens with head_dim 64 (BERT-base GLUE shape: seq 128, 12 heads), one CTA per (batch, head).
+//
+// All five matrix products run on tcgen05 tensor cores with TMEM accumulators; Q/K/V/dO tiles are
+// fetched by TMA straight out of the packed [tokens, 3*hidden] QKV activation (no head split /
+// transpose kernels), and the probability tile never leaves the SM:
+//
+//   fwd:  S = Q K^T  ->  P = dropout(softmax(S*scale + mask))  ->  O = P V
+//   bwd:  S, dP' = dO V^T  ->  P, dS (registers)  ->  dV = P'^T dO, dQ = dS K, dK = dS^T Q
+//
+// The transposed products use MN-major shared-memory descriptors over the SAME swizzled smem tile
+// that the row-major products read, so P and dS are written once.
+//
+// Replaces HF BertSelfAttention's matmul/softmax/dropout/matmul chain used by the reference's BERT
+// example (reference: examples/nlp/bert_glue_pytorch/model_def.py:60-68).
+#include "host_utils.h"
+#include "sm100_ptx.cuh"
+
+namespace det {
+
+struct AttnParams {
+  int B, S, H;          // batch, sequence length (<=128), heads
+  int hidden;           // H * 64
+  float scale;          // 1/sqrt(64)
+  const float* mask;    // additive key mask [B, S] fp32, or null
+  float* lse;           // [B, H, S] fp32 (fwd writes, bwd reads)
+  __nv_bfloat16* out;   // fwd: ctx [T, hidden]; bwd: dqkv [T, 3*hidden]
+  uint32_t drop_threshold;
+  float drop_scale;
+  uint32_t drop_seed;
+};
+
+constexpr int ATT_S = 128;
+constexpr int ATT_D = 64;
+constexpr uint32_t ATT_TILE = ATT_S * ATT_D * 2;  // 16 KB
+constexpr float LOG2E = 1.4426950408889634f;
+
+// ------------------------------------------------------------------------------------------------
+// Forward
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t ATT_FWD_SMEM = 3 * ATT_TILE + 2 * ATT_TILE + 1024 + 64;
+
+__global__ void __launch_bounds__(128, 2)
+attention_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + ATT_TILE;
+  uint8_t* sV = smem + 2 * ATT_TILE;
+  uint8_t* sP = smem + 3 * ATT_TILE;  // 2 chunks of [128 q][64 keys]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 5 * ATT_TILE);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.x / p.H, h = blockIdx.x % p.H;
+  const uint32_t tma_bar = ptx::smem_u32(&bars[0]);
+  const uint32_t mma_bar = ptx::smem_u32(&bars[1]);
+
+  if (tid == 0) {
+    ptx::tma_prefetch_desc(&tma_qkv);
+    ptx::mbar_init(tma_bar, 1);
+    ptx::mbar_init(mma_bar, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 0) ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 256);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem;        // 128 columns
+  const uint32_t tO = tmem + 128;  // 64 columns
+
+  if (tid == 0) {
+    ptx::mbar_expect_tx(tma_bar, 3 * ATT_TILE);
+    const int row0 = b * p.S;
+    ptx::tma_load_2d(ptx::smem_u32(sQ), &tma_qkv, tma_bar, h * ATT_D, row0);
+    ptx::tma_load_2d(ptx::smem_u32(sK), &tma_qkv, tma_bar, p.hidden + h * ATT_D, row0);
+    ptx::tma_load_2d(ptx::smem_u32(sV), &tma_qkv, tma_bar, 2 * p.hidden + h * ATT_D, row0);
+    ptx::mbar_wait(tma_bar, 0);
+    ptx::tc_fence_after();
+    constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(128, 128, 0, 0);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint64_t ad = ptx::make_smem_desc_sw128(ptx::smem_u32(sQ) + k * 32, 16, 1024);
+      const uint64_t bd = ptx::make_smem_desc_sw128(ptx::smem_u32(sK) + k * 32, 16, 1024);
+      ptx::umma_bf16_ss(tS, ad, bd, idesc, k > 0);
+    }
+    ptx::umma_commit(mma_bar);
+  }
+  ptx::mbar_wait(mma_bar, 0);
+  ptx::tc_fence_after();
+
+  // ---- softmax on this thread's query row ----
+  const int q = tid;  // query row == TMEM lane
+  const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+  float s[128];
+#pragma unroll
+  for (int c = 0; c < 4; ++c) ptx::tmem_ld_32x32b_x32(tS + lane_base + c * 32, s + c * 32);
+  ptx::tmem_ld_wait();
+  const float sc = p.scale * LOG2E;
+  float mx = -INFINITY;
+#pragma unroll
+  for (int j = 0; j < 128; ++j) {
+    float m = 0.0f;
+    if (p.mask != nullptr && j < p.S) m = __ldg(p.mask + b * p.S + j) * LOG2E;
+    s[j] = (j < p.S) ? (s[j] * sc + m) : -INFINITY;
+    mx = fmaxf(mx, s[j]);
+  }
+  float sum = 0.0f;
+#pragma unroll
+  for (int j = 0; j < 128; ++j) {
+    s[j] = exp2f(s[j] - mx);
+    sum += s[j];
+  }
+  const float inv = 1.0f / sum;
+  if (q < p.S) p.lse[(static_cast<long long>(b) * p.H + h) * p.S + q] = (mx + log2f(sum)) * (1.0f / LOG2E);
+  const uint32_t didx0 = ((static_cast<uint32_t>(b) * p.H + h) * p.S + q) * p.S;
+#pragma unroll
+  for (int u = 0; u < 16; ++u) {  // 16-byte units of 8 keys
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int j = u * 8 + e;
+      float pv = s[j] * inv;
+      if (p.drop_threshold != 0u) pv = dropout_keep(p.drop_seed, didx0 + j, p.drop_threshold) ? pv * p.drop_scale : 0.0f;
+      v[e] = pv;
+    }
+    uint4 pk;
+    pk.x = ptx::pack_bf16x2(v[0], v[1]); pk.y = ptx::pack_bf16x2(v[2], v[3]);
+    pk.z = ptx::pack_bf16x2(v[4], v[5]); pk.w = ptx::pack_bf16x2(v[6], v[7]);
+    const uint32_t chunk = u >> 3, unit = u & 7;
+    *reinterpret_cast<uint4*>(sP + chunk * ATT_TILE + ptx::sw128_offset(q, unit)) = pk;
+  }
+  ptx::fence_proxy_async_smem();
+  ptx::tc_fence_before();
+  __syncthreads();
+
+  if (tid == 0) {
+    ptx::tc_fence_after();
+    constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(128, 64, 0, 1);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const uint64_t ad = ptx::make_smem_desc_sw128(ptx::smem_u32(sP) + (k >> 2) * ATT_TILE + (k & 3) * 32, 16, 1024);
+      const uint64_t bd = ptx::make_smem_desc_sw128(ptx::smem_u32(sV) + k * 2048, 8192, 1024);
+      ptx::umma_bf16_ss(tO, ad, bd, idesc, k > 0);
+    }
+    ptx::umma_commit(mma_bar);
+  }
+  ptx::mbar_wait(mma_bar, 1);
+  ptx::tc_fence_after();
+  float o[64];
+  ptx::tmem_ld_32x32b_x32(tO + lane_base, o);
+  ptx::tmem_ld_32x32b_x32(tO + lane_base + 32, o + 32);
+  ptx::tmem_ld_wait();
+  if (q < p.S) {
+    uint4* dst = reinterpret_cast<uint4*>(p.out + (static_cast<long long>(b) * p.S + q) * p.hidden + h * ATT_D);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      uint4 pk;
+      pk.x = ptx::pack_bf16x2(o[8 * u + 0], o[8 * u + 1]); pk.y = ptx::pack_bf16x2(o[8 * u + 2], o[8 * u + 3]);
+      pk.z = ptx::pack_bf16x2(o[8 * u + 4], o[8 * u + 5]); pk.w = ptx::pack_bf16x2(o[8 * u + 6], o[8 * u + 7]);
+      dst[u] = pk;
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem, 256);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Backward
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t ATT_BWD_SMEM = 4 * ATT_TILE + 4 * ATT_TILE + 1024 + 64;
+
+__global__ void __launch_bounds__(128, 1)
+attention_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
+                     const __grid_constant__ CUtensorMap tma_do, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + ATT_TILE;
+  uint8_t* sV = smem + 2 * ATT_TILE;
+  uint8_t* sdO = smem + 3 * ATT_TILE;
+  uint8_t* sP = smem + 4 * ATT_TILE;   // 2 chunks
+  uint8_t* sdS = smem + 6 * ATT_TILE;  // 2 chunks
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 8 * ATT_TILE);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int b = blockIdx.x / p.H, h = blockIdx.x % p.H;
+  const uint32_t tma_bar = ptx::smem_u32(&bars[0]);
+  const uint32_t mma_bar = ptx::smem_u32(&bars[1]);
+
+  if (tid == 0) {
+    ptx::tma_prefetch_desc(&tma_qkv);
+    ptx::tma_prefetch_desc(&tma_do);
+    ptx::mbar_init(tma_bar, 1);
+    ptx::mbar_init(mma_bar, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 0) ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 512);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem, tdP = tmem + 128, tdV = tmem + 256, tdQ = tmem + 320, tdK = tmem + 384;
+
+  if (tid == 0) {
+    ptx::mbar_expect_tx(tma_bar, 4 * ATT_TILE);
+    const int row0 = b * p.S;
+    ptx::tma_load_2d(ptx::smem_u32(sQ), &tma_qkv, tma_bar, h * ATT_D, row0);
+    ptx::tma_load_2d(ptx::smem_u32(sK), &tma_qkv, tma_bar, p.hidden + h * ATT_D, row0);
+    ptx::tma_load_2d(ptx::smem_u32(sV), &tma_qkv, tma_bar, 2 * p.hidden + h * ATT_D, row0);
+    ptx::tma_load_2d(ptx::smem_u32(sdO), &tma_do, tma_bar, h * ATT_D, row0);
+    ptx::mbar_wait(tma_bar, 0);
+    ptx::tc_fence_after();
+    constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(128, 128, 0, 0);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {  // S = Q K^T
+      const uint64_t ad = ptx::make_smem_desc_sw128(ptx::smem_u32(sQ) + k * 32, 16, 1024);
+      const uint64_t bd = ptx::make_smem_desc_sw128(ptx::smem_u32(sK) + k * 32, 16, 1024);
+      ptx::umma_bf16_ss(tS, ad, bd, idesc, k > 0);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {  // dP' = dO V^T
+      const uint64_t ad = ptx::make_smem_desc_sw128(ptx::smem_u32(sdO) + k * 32, 16, 1024);
+      const uint64_t bd = ptx::make_smem_desc_sw128(ptx::smem_u32(sV) + k * 32, 16, 1024);
+      ptx::umma_bf16_ss(tdP, ad, bd, idesc, k > 0);
+    }
+    ptx::umma_commit(mma_bar);
+  }
+  ptx::mbar_wait(mma_bar, 0);
+  ptx::tc_fence_after();
+
+  const int q = tid;
+  const bool q_ok = q < p.S;
+  const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+  const float sc = p.scale * LOG2E;
+  const float lse2 = q_ok ? p.lse[(static_cast<long long>(b) * p.H + h) * p.S + q] * LOG2E : 0.0f;
+  const uint32_t didx0 = ((static_cast<uint32_t>(b) * p.H + h) * p.S + q) * p.S;
+
+  // Pass A: P' = dropout(P) -> smem, delta = sum_j P'_ij dP'_ij
+  float delta = 0.0f;
+#pragma unroll 1
+  for (int c = 0; c < 4; ++c) {
+    float s[32], dp[32];
+    ptx::tmem_ld_32x32b_x32(tS + lane_base + c * 32, s);
+    ptx::tmem_ld_32x32b_x32(tdP + lane_base + c * 32, dp);
+    ptx::tmem_ld_wait();
+#pragma unroll
+    for (int e = 0; e < 32; ++e) {
+      const int j = c * 32 + e;
+      float m = 0.0f;
+      if (p.mask != nullptr && j < p.S) m = __ldg(p.mask + b * p.S + j) * LOG2E;
+      float pv = (q_ok && j < p.S) ? exp2f(s[e] * sc + m - lse2) : 0.0f;
+      if (p.drop_threshold != 0u) pv = dropout_keep(p.drop_seed, didx0 + j, p.drop_threshold) ? pv * p.drop_scale : 0.0f;
+      s[e] = pv;
+      delta += pv * dp[e];
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      uint4 pk;
+      pk.x = ptx::pack_bf16x2(s[8 * u + 0], s[8 * u + 1]); pk.y = ptx::pack_bf16x2(s[8 * u + 2], s[8 * u + 3]);
+      pk.z = ptx::pack_bf16x2(s[8 * u + 4], s[8 * u + 5]); pk.w = ptx::pack_bf16x2(s[8 * u + 6], s[8 * u + 7]);
+      const uint32_t gu = c * 4 + u;  // global 16-byte unit index 0..15
+      *reinterpret_cast<uint4*>(sP + (gu >> 3) * ATT_TILE + ptx::sw128_offset(q, gu & 7)) = pk;
+    }
+  }
+  // Pass B: dS = P * (dP - delta) * scale -> smem
+#pragma unroll 1
+  for (int c = 0; c < 4; ++c) {
+    float s[32], dp[32];
+    ptx::tmem_ld_32x32b_x32(tS + lane_base + c * 32, s);
+    ptx::tmem_ld_32x32b_x32(tdP + lane_base + c * 32, dp);
+    ptx::tmem_ld_wait();
+#pragma unroll
+    for (int e = 0; e < 32; ++e) {
+      const int j = c * 32 + e;
+      float m = 0.0f;
+      if (p.mask != nullptr && j < p.S) m = __ldg(p.mask + b * p.S + j) * LOG2E;
+      const float pv = (q_ok && j < p.S) ? exp2f(s[e] * sc + m - lse2) : 0.0f;
+      float dpv = dp[e];
+      if (p.drop_threshold != 0u) dpv = dropout_keep(p.drop_seed, didx0 + j, p.drop_threshold) ? dpv * p.drop_scale : 0.0f;
+      s[e] = pv * (dpv - delta) * p.scale;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      uint4 pk;
+      pk.x = ptx::pack_bf16x2(s[8 * u + 0], s[8 * u + 1]); pk.y = ptx::pack_bf16x2(s[8 * u + 2], s[8 * u + 3]);
+      pk.z = ptx::pack_bf16x2(s[8 * u + 4], s[8 * u + 5]); pk.w = ptx::pack_bf16x2(s[8 * u + 6], s[8 * u + 7]);
+      const uint32_t gu = c * 4 + u;
+      *reinterpret_cast<uint4*>(sdS + (gu >> 3) * ATT_TILE + ptx::sw128_offset(q, gu & 7)) = pk;
+    }
+  }
+  ptx::fence_proxy_async_smem();
+  ptx::tc_fence_before();
+  __syncthreads();
+
+  if (tid == 0) {
+    ptx::tc_fence_after();
+    constexpr uint32_t idesc_tn = ptx::make_idesc_bf16_f32(128, 64, 1, 1);  // A^T (MN-major), B MN-major
+    constexpr uint32_t idesc_nn = ptx::make_idesc_bf16_f32(128, 64, 0, 1);  // A K-major,     B MN-major
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {  // dV[key, d] = sum_q P'[q, key] dO[q, d]
+      const uint64_t ad = ptx::make_smem_desc_sw128(ptx::smem_u32(sP) + k * 2048, ATT_TILE, 1024);
+      const uint64_t bd = ptx::make_smem_desc_sw128(ptx::smem_u32(sdO) + k * 2048, 8192, 1024);
+      ptx::umma_bf16_ss(tdV, ad, bd, idesc_tn, k > 0);
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {  // dQ[q, d] = sum_key dS[q, key] K[key, d]
+      const uint64_t ad = ptx::make_smem_desc_sw128(ptx::smem_u32(sdS) + (k >> 2) * ATT_TILE + (k & 3) * 32, 16, 1024);
+      const uint64_t bd = ptx::make_smem_desc_sw128(ptx::smem_u32(sK) + k * 2048, 8192, 1024);
+      ptx::umma_bf16_ss(tdQ, ad, bd, idesc_nn, k > 0);
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {  // dK[key, d] = sum_q dS[q, key] Q[q, d]
+      const uint64_t ad = ptx::make_smem_desc_sw128(ptx::smem_u32(sdS) + k * 2048, ATT_TILE, 1024);
+      const uint64_t bd = ptx::make_smem_desc_sw128(ptx::smem_u32(sQ) + k * 2048, 8192, 1024);
+      ptx::umma_bf16_ss(tdK, ad, bd, idesc_tn, k > 0);
+    }
+    ptx::umma_commit(mma_bar);
+  }
+  ptx::mbar_wait(mma_bar, 1);
+  ptx::tc_fence_after();
+
+  const long long out_row = (static_cast<long long>(b) * p.S + q) * (3LL * p.hidden) + h * ATT_D;
+#pragma unroll 1
+  for (int which = 0; which < 3; ++which) {
+    const uint32_t src = (which == 0) ? tdQ : (which == 1 ? tdK : tdV);
+    float o[64];
+    ptx::tmem_ld_32x32b_x32(src + lane_base, o);
+    ptx::tmem_ld_32x32b_x32(src + lane_base + 32, o + 32);
+    ptx::tmem_ld_wait();
+    if (q_ok) {
+      uint4* dst = reinterpret_cast<uint4*>(p.out + out_row + static_cast<long long>(which) * p.hidden);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        uint4 pk;
+        pk.x = ptx::pack_bf16x2(o[8 * u + 0], o[8 * u + 1]); pk.y = ptx::pack_bf16x2(o[8 * u + 2], o[8 * u + 3]);
+        pk.z = ptx::pack_bf16x2(o[8 * u + 4], o[8 * u + 5]); pk.w = ptx::pack_bf16x2(o[8 * u + 6], o[8 * u + 7]);
+        dst[u] = pk;
+      }
+    }
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem, 512);
+  }
+}
+
+static int fill_params(AttnParams& p, int B, int S, int H, const float* mask, float* lse, void* out,
+                       float dropout_p, unsigned seed) {
+  DET_REQUIRE(S >= 1 && S <= ATT_S, "fused attention supports sequence length <= 128");
+  DET_REQUIRE(B >= 1 && H >= 1, "bad attention shape");
+  p.B = B; p.S = S; p.H = H; p.hidden = H * ATT_D;
+  p.scale = 0.125f;
+  p.mask = mask; p.lse = lse; p.out = reinterpret_cast<__nv_bfloat16*>(out);
+  if (dropout_p > 0.0f) {
+    DET_REQUIRE(dropout_p < 1.0f, "dropout p must be < 1");
+    p.drop_threshold = static_cast<uint32_t>(static_cast<double>(dropout_p) * 4294967296.0);
+    p.drop_scale = 1.0f / (1.0f - dropout_p);
+  } else {
+    p.drop_threshold = 0; p.drop_scale = 1.0f;
+  }
+  p.drop_seed = seed;
+  return 0;
+}
+
+}  // namespace det
+
+// qkv: [B*S, 3*H*64] bf16 packed (Q | K | V, each head-major);  ctx: [B*S, H*64] bf16;
+// mask: additive fp32 [B, S] or null;  lse: [B, H, S] fp32.
+extern "C" int det_attention_fwd(const void* qkv, const float* mask, void* ctx, float* lse, int B,
+                                 int S, int H, float dropout_p, unsigned int seed,
+                                 cudaStream_t stream) {
+  using namespace det;
+  AttnParams p;
+  int rc = fill_params(p, B, S, H, mask, lse, ctx, dropout_p, seed);
+  if (rc) return rc;
+  CUtensorMap tq;
+  rc = make_tma_2d_bf16(&tq, qkv, 3ull * p.hidden, (uint64_t)B * S, 3ull * p.hidden, 64, ATT_S);
+  if (rc) return rc;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  DET_CHECK_CUDA(cudaGetDevice(&dev));
+  if (dev < 64 && !attr_set[dev]) {
+    DET_CHECK_CUDA(cudaFuncSetAttribute(attention_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_FWD_SMEM));
+    attr_set[dev] = true;
+  }
+  attention_fwd_kernel<<<B * H, 128, ATT_FWD_SMEM, stream>>>(tq, p);
+  DET_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// dctx: [B*S, H*64] bf16;  dqkv (out): [B*S, 3*H*64] bf16.
+extern "C" int det_attention_bwd(const void* qkv, const void* dctx, const float* mask,
+                                 const float* lse, void* dqkv, int B, int S, int H, float dropout_p,
+                                 unsigned int seed, cudaStream_t stream) {
+  using namespace det;
+  AttnParams p;
+  int rc = fill_params(p, B, S, H, mask, const_cast<float*>(lse), dqkv, dropout_p, seed);
+  if (rc) return rc;
+  CUtensorMap tq, td;
+  rc = make_tma_2d_bf16(&tq, qkv, 3ull * p.hidden, (uint64_t)B * S, 3ull * p.hidden, 64, ATT_S);
+  if (rc) return rc;
+  rc = make_tma_2d_bf16(&td, dctx, (uint64_t)p.hidden, (uint64_t)B * S, (uint64_t)p.hidden, 64, ATT_S);
+  if (rc) return rc;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  DET_CHECK_CUDA(cudaGetDevice(&dev));
+  if (dev < 64 && !attr_set[dev]) {
+    DET_CHECK_CUDA(cudaFuncSetAttribute(attention_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_BWD_SMEM));
+    attr_set[dev] = true;
+  }
+  attention_bwd_kernel<<<B * H, 128, ATT_BWD_SMEM, stream>>>(tq, td, p);
+  DET_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
