@@ -1,0 +1,312 @@
+// fused_allreduce.cu — in-kernel collectives over NVLink peer memory for one 8xB200 NVSwitch box.
+//
+// Every rank owns a "symmetric arena": the same allocation on each GPU, mapped into every peer's
+// address space (CUDA IPC or torch symmetric memory; see determined_b200/parallel/arena.py). The
+// kernels below take the table of peer pointers and do the whole collective themselves:
+//
+//   det_fused_allreduce  — bucketed gradient all-reduce fused with averaging (÷world, ÷agg_freq),
+//                          loss-scale unscale, non-finite detection and the grad-norm partial sum.
+//                          One pass: rank r pulls slice r of every peer's bucket with 16-byte P2P
+//                          loads, reduces in fp32 registers, and pushes the finished slice into every
+//                          peer's bucket with P2P stores (reduce-scatter and all-gather in one sweep).
+//                          Optional NVLS path: multimem.ld_reduce / multimem.st through a multicast
+//                          address so the switch does the arithmetic.
+//                          Replaces Horovod's NCCL ring allreduce + the per-parameter
+//                          `_average_gradients` kernels + apex unscale
+//                          (reference: harness/determined/pytorch/_pytorch_context.py:192-198, :462,
+//                          :470-477, :522).
+//   det_p2p_broadcast    — parameter / optimizer-state broadcast from rank 0 (reference:
+//                          hvd.broadcast_parameters, _pytorch_trial.py:71-73): every rank pulls the
+//                          root's bucket.
+//   det_metric_allreduce — AVG/SUM/MIN/MAX of a small metric vector across ranks (reference: ZMQ +
+//                          pickle gather, _pytorch_trial.py:292-335, :542-616): one-shot, every rank
+//                          reads all peers.
+//
+// Cross-rank synchronisation is a flag barrier in peer memory: block b of rank r writes an epoch
+// number into slot [b][r] of every peer's flag table and spins until its own row holds that epoch
+// from everyone. Grids are identical on all ranks and never larger than the SM count, so every
+// block is resident while it waits. Spins are bounded (trap after ~10 s) so a lost rank cannot
+// wedge the GPU.
+#include <cuda_bf16.h>
+
+#include <algorithm>
+
+#include "host_utils.h"
+
+namespace det {
+
+constexpr int COMM_MAX_RANKS = 8;
+constexpr int COMM_MAX_BLOCKS = 256;
+
+struct PeerTable {
+  void* buf[COMM_MAX_RANKS];        // bucket base on each rank (peer-mapped addresses)
+  uint32_t* flags[COMM_MAX_RANKS];  // flag table on each rank: [COMM_MAX_BLOCKS][COMM_MAX_RANKS]
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// All threads of the block call this. `epoch` must be the same on every rank for this barrier.
+__device__ __forceinline__ void rank_barrier(const PeerTable& t, int rank, int world, uint32_t epoch) {
+  __syncthreads();
+  if (threadIdx.x < world) {
+    __threadfence_system();
+    st_release_sys(t.flags[threadIdx.x] + blockIdx.x * COMM_MAX_RANKS + rank, epoch);
+    const uint32_t* mine = t.flags[rank] + blockIdx.x * COMM_MAX_RANKS + threadIdx.x;
+    const long long t0 = clock64();
+    while (static_cast<int32_t>(ld_acquire_sys(mine) - epoch) < 0) {
+      if (clock64() - t0 > 20000000000LL) __trap();
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ float4 ld_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.global.relaxed.sys.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_f4(float* p, const float4& v) {
+  asm volatile("st.global.relaxed.sys.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w) : "memory");
+}
+
+struct AllreduceArgs {
+  PeerTable t;
+  float* mc_ptr;          // multicast (NVLS) address of the bucket, or null
+  uint32_t* epoch;        // local device counter [COMM_MAX_BLOCKS]
+  long long n;            // fp32 elements in the bucket (multiple of 4)
+  int rank, world;
+  const float* scale_dev; // optional device scalar multiplied into `scale`
+  float scale;
+  float* sumsq;           // optional: += sum of squares of the reduced, scaled slice owned by this rank
+  int* found_inf;         // optional: set to 1 when a non-finite value is seen
+};
+
+template <bool USE_MC>
+__global__ void __launch_bounds__(512)
+fused_allreduce_kernel(const AllreduceArgs a) {
+  const int rank = a.rank, world = a.world;
+  uint32_t ep = a.epoch[blockIdx.x];
+  rank_barrier(a.t, rank, world, ep + 1);  // every rank's gradients for this bucket are complete
+
+  const float scale = a.scale * (a.scale_dev ? *a.scale_dev : 1.0f);
+  // slice owned by this rank, in float4 units
+  const long long n4 = a.n >> 2;
+  const long long per = (n4 + world - 1) / world;
+  const long long lo = std::min<long long>(per * rank, n4), hi = std::min<long long>(lo + per, n4);
+  float acc = 0.0f;
+  bool bad = false;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+  for (long long i = lo + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < hi; i += stride) {
+    float4 s;
+    if (USE_MC) {
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                   : "=f"(s.x), "=f"(s.y), "=f"(s.z), "=f"(s.w) : "l"(a.mc_ptr + i * 4) : "memory");
+    } else {
+      float4 v[COMM_MAX_RANKS];
+#pragma unroll
+      for (int r = 0; r < COMM_MAX_RANKS; ++r)
+        if (r < world) v[r] = ld_f4(reinterpret_cast<const float*>(a.t.buf[(rank + r) % world]) + i * 4);
+      s = v[0];
+#pragma unroll
+      for (int r = 1; r < COMM_MAX_RANKS; ++r)
+        if (r < world) { s.x += v[r].x; s.y += v[r].y; s.z += v[r].z; s.w += v[r].w; }
+    }
+    s.x *= scale; s.y *= scale; s.z *= scale; s.w *= scale;
+    acc += s.x * s.x + s.y * s.y + s.z * s.z + s.w * s.w;
+    bad |= !(isfinite(s.x) && isfinite(s.y) && isfinite(s.z) && isfinite(s.w));
+    if (USE_MC) {
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(a.mc_ptr + i * 4),
+                   "f"(s.x), "f"(s.y), "f"(s.z), "f"(s.w) : "memory");
+    } else {
+#pragma unroll
+      for (int r = 0; r < COMM_MAX_RANKS; ++r)
+        if (r < world) st_f4(reinterpret_cast<float*>(a.t.buf[(rank + r) % world]) + i * 4, s);
+    }
+  }
+  if (a.sumsq != nullptr || a.found_inf != nullptr) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    __shared__ float red[16];
+    __shared__ int sbad;
+    if (threadIdx.x == 0) sbad = 0;
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    if (bad) sbad = 1;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float s = 0.0f;
+      for (int w = 0; w < (blockDim.x >> 5); ++w) s += red[w];
+      if (a.sumsq) atomicAdd(a.sumsq, s);
+      if (sbad && a.found_inf) atomicExch(a.found_inf, 1);
+    }
+  }
+  rank_barrier(a.t, rank, world, ep + 2);  // every slice has landed everywhere
+  if (threadIdx.x == 0) a.epoch[blockIdx.x] = ep + 2;
+}
+
+struct BcastArgs {
+  PeerTable t;
+  uint32_t* epoch;
+  long long nbytes;  // multiple of 16
+  int rank, world, root;
+};
+
+__global__ void __launch_bounds__(512)
+p2p_broadcast_kernel(const BcastArgs a) {
+  uint32_t ep = a.epoch[blockIdx.x];
+  rank_barrier(a.t, a.rank, a.world, ep + 1);  // root's data is final, receivers' buffers are idle
+  if (a.rank != a.root) {
+    const uint4* src = reinterpret_cast<const uint4*>(a.t.buf[a.root]);
+    uint4* dst = reinterpret_cast<uint4*>(a.t.buf[a.rank]);
+    const long long n16 = a.nbytes >> 4;
+    const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
+    for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n16; i += stride) {
+      uint4 v;
+      asm volatile("ld.global.relaxed.sys.v4.u32 {%0, %1, %2, %3}, [%4];"
+                   : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(src + i) : "memory");
+      dst[i] = v;
+    }
+  }
+  rank_barrier(a.t, a.rank, a.world, ep + 2);  // root may overwrite its buffer again
+  if (threadIdx.x == 0) a.epoch[blockIdx.x] = ep + 2;
+}
+
+struct MetricArgs {
+  PeerTable t;
+  uint32_t* epoch;
+  float* out;            // local result [n]
+  const float* weights;  // optional per-rank weights [world] for weighted AVG (batches per process)
+  int n, rank, world, op;  // op: 0 AVG, 1 SUM, 2 MAX, 3 MIN
+};
+
+__global__ void __launch_bounds__(256)
+metric_allreduce_kernel(const MetricArgs a) {
+  uint32_t ep = a.epoch[blockIdx.x];
+  rank_barrier(a.t, a.rank, a.world, ep + 1);
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < a.n; i += gridDim.x * blockDim.x) {
+    float acc = (a.op == 2) ? -INFINITY : (a.op == 3 ? INFINITY : 0.0f);
+    float wsum = 0.0f;
+    for (int r = 0; r < a.world; ++r) {
+      float v;
+      asm volatile("ld.global.relaxed.sys.f32 %0, [%1];" : "=f"(v) : "l"(reinterpret_cast<const float*>(a.t.buf[r]) + i) : "memory");
+      const float w = a.weights ? a.weights[r] : 1.0f;
+      if (a.op == 0) { acc += v * w; wsum += w; }
+      else if (a.op == 1) acc += v;
+      else if (a.op == 2) acc = fmaxf(acc, v);
+      else acc = fminf(acc, v);
+    }
+    a.out[i] = (a.op == 0) ? acc / wsum : acc;
+  }
+  rank_barrier(a.t, a.rank, a.world, ep + 2);
+  if (threadIdx.x == 0) a.epoch[blockIdx.x] = ep + 2;
+}
+
+static int fill_table(PeerTable& t, void* const* bufs, void* const* flags, int world) {
+  DET_REQUIRE(world >= 1 && world <= COMM_MAX_RANKS, "world size must be in [1, 8]");
+  for (int r = 0; r < COMM_MAX_RANKS; ++r) {
+    t.buf[r] = r < world ? bufs[r] : nullptr;
+    t.flags[r] = r < world ? reinterpret_cast<uint32_t*>(flags[r]) : nullptr;
+  }
+  return 0;
+}
+
+}  // namespace det
+
+// Bytes a flag table needs on each rank (zero-initialised once), and the epoch counter array.
+extern "C" long long det_comm_flag_bytes() { return 1LL * det::COMM_MAX_BLOCKS * det::COMM_MAX_RANKS * 4; }
+extern "C" long long det_comm_epoch_bytes() { return 1LL * det::COMM_MAX_BLOCKS * 4; }
+
+// peer_bufs / peer_flags: host arrays of `world` device pointers (this rank's view of every rank).
+extern "C" int det_fused_allreduce(void* const* peer_bufs, void* const* peer_flags, void* mc_ptr,
+                                   void* epoch_dev, long long n_f32, int rank, int world, float scale,
+                                   const float* scale_dev, float* sumsq_dev, int* found_inf_dev,
+                                   int max_blocks, cudaStream_t stream) {
+  using namespace det;
+  if (n_f32 <= 0) return 0;
+  DET_REQUIRE(n_f32 % 4 == 0, "bucket length must be a multiple of 4 floats");
+  AllreduceArgs a;
+  int rc = fill_table(a.t, peer_bufs, peer_flags, world);
+  if (rc) return rc;
+  a.mc_ptr = reinterpret_cast<float*>(mc_ptr);
+  a.epoch = reinterpret_cast<uint32_t*>(epoch_dev);
+  a.n = n_f32; a.rank = rank; a.world = world; a.scale = scale; a.scale_dev = scale_dev;
+  a.sumsq = sumsq_dev; a.found_inf = found_inf_dev;
+  const long long per4 = ((n_f32 >> 2) + world - 1) / world;
+  int blocks = static_cast<int>(std::min<long long>((per4 + 511) / 512, std::min(sm_count(), COMM_MAX_BLOCKS)));
+  if (max_blocks > 0) blocks = std::min(blocks, max_blocks);
+  blocks = std::max(blocks, 1);
+  // Every rank must launch the same grid: blocks depends only on (n, world, SM count, max_blocks).
+  if (mc_ptr != nullptr && world > 1) fused_allreduce_kernel<true><<<blocks, 512, 0, stream>>>(a);
+  else fused_allreduce_kernel<false><<<blocks, 512, 0, stream>>>(a);
+  DET_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int det_p2p_broadcast(void* const* peer_bufs, void* const* peer_flags, void* epoch_dev,
+                                 long long nbytes, int rank, int world, int root, cudaStream_t stream) {
+  using namespace det;
+  if (nbytes <= 0 || world <= 1) return 0;
+  DET_REQUIRE(nbytes % 16 == 0, "broadcast size must be a multiple of 16 bytes");
+  BcastArgs a;
+  int rc = fill_table(a.t, peer_bufs, peer_flags, world);
+  if (rc) return rc;
+  a.epoch = reinterpret_cast<uint32_t*>(epoch_dev);
+  a.nbytes = nbytes; a.rank = rank; a.world = world; a.root = root;
+  const int blocks = static_cast<int>(std::max<long long>(1, std::min<long long>((nbytes / 16 + 511) / 512, std::min(sm_count(), COMM_MAX_BLOCKS))));
+  p2p_broadcast_kernel<<<blocks, 512, 0, stream>>>(a);
+  DET_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+extern "C" int det_metric_allreduce(void* const* peer_bufs, void* const* peer_flags, void* epoch_dev,
+                                    float* out_dev, const float* weights_dev, int n, int rank, int world,
+                                    int op, cudaStream_t stream) {
+  using namespace det;
+  if (n <= 0) return 0;
+  MetricArgs a;
+  int rc = fill_table(a.t, peer_bufs, peer_flags, world);
+  if (rc) return rc;
+  a.epoch = reinterpret_cast<uint32_t*>(epoch_dev);
+  a.out = out_dev; a.weights = weights_dev; a.n = n; a.rank = rank; a.world = world; a.op = op;
+  const int blocks = std::max(1, std::min((n + 255) / 256, 8));
+  metric_allreduce_kernel<<<blocks, 256, 0, stream>>>(a);
+  DET_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// ---- CUDA IPC plumbing for the symmetric arena (cudaMalloc'd, exported to the other local ranks) ----
+extern "C" int det_arena_alloc(long long bytes, void** out) {
+  DET_CHECK_CUDA(cudaMalloc(out, static_cast<size_t>(bytes)));
+  DET_CHECK_CUDA(cudaMemset(*out, 0, static_cast<size_t>(bytes)));
+  return 0;
+}
+extern "C" int det_arena_free(void* p) {
+  DET_CHECK_CUDA(cudaFree(p));
+  return 0;
+}
+extern "C" int det_ipc_export(void* p, unsigned char* handle64) {
+  cudaIpcMemHandle_t h;
+  DET_CHECK_CUDA(cudaIpcGetMemHandle(&h, p));
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(handle64, &h, 64);
+  return 0;
+}
+extern "C" int det_ipc_import(const unsigned char* handle64, void** out) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  DET_CHECK_CUDA(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+extern "C" int det_ipc_close(void* p) {
+  DET_CHECK_CUDA(cudaIpcCloseMemHandle(p));
+  return 0;
+}

@@ -28,6 +28,7 @@ struct AttnParams {
   uint32_t drop_threshold;
   float drop_scale;
   uint32_t drop_seed;
+  const uint32_t* drop_seed_dev;
 };
 
 constexpr int ATT_S = 128;
@@ -115,6 +116,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnPara
   const float inv = 1.0f / sum;
   if (q < p.S) p.lse[(static_cast<long long>(b) * p.H + h) * p.S + q] = (mx + log2f(sum)) * (1.0f / LOG2E);
   const uint32_t didx0 = ((static_cast<uint32_t>(b) * p.H + h) * p.S + q) * p.S;
+  const uint32_t dseed = p.drop_seed + (p.drop_seed_dev ? __ldg(p.drop_seed_dev) * 0x9E3779B9u : 0u);
 #pragma unroll
   for (int u = 0; u < 16; ++u) {  // 16-byte units of 8 keys
     float v[8];
@@ -122,7 +124,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnPara
     for (int e = 0; e < 8; ++e) {
       const int j = u * 8 + e;
       float pv = s[j] * inv;
-      if (p.drop_threshold != 0u) pv = dropout_keep(p.drop_seed, didx0 + j, p.drop_threshold) ? pv * p.drop_scale : 0.0f;
+      if (p.drop_threshold != 0u) pv = dropout_keep(dseed, didx0 + j, p.drop_threshold) ? pv * p.drop_scale : 0.0f;
       v[e] = pv;
     }
     uint4 pk;
@@ -241,6 +243,7 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
   const float sc = p.scale * LOG2E;
   const float lse2 = q_ok ? p.lse[(static_cast<long long>(b) * p.H + h) * p.S + q] * LOG2E : 0.0f;
   const uint32_t didx0 = ((static_cast<uint32_t>(b) * p.H + h) * p.S + q) * p.S;
+  const uint32_t dseed = p.drop_seed + (p.drop_seed_dev ? __ldg(p.drop_seed_dev) * 0x9E3779B9u : 0u);
 
   // Pass A: P' = dropout(P) -> smem, delta = sum_j P'_ij dP'_ij
   float delta = 0.0f;
@@ -256,7 +259,7 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
       float m = 0.0f;
       if (p.mask != nullptr && j < p.S) m = __ldg(p.mask + b * p.S + j) * LOG2E;
       float pv = (q_ok && j < p.S) ? exp2f(s[e] * sc + m - lse2) : 0.0f;
-      if (p.drop_threshold != 0u) pv = dropout_keep(p.drop_seed, didx0 + j, p.drop_threshold) ? pv * p.drop_scale : 0.0f;
+      if (p.drop_threshold != 0u) pv = dropout_keep(dseed, didx0 + j, p.drop_threshold) ? pv * p.drop_scale : 0.0f;
       s[e] = pv;
       delta += pv * dp[e];
     }
@@ -283,7 +286,7 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
       if (p.mask != nullptr && j < p.S) m = __ldg(p.mask + b * p.S + j) * LOG2E;
       const float pv = (q_ok && j < p.S) ? exp2f(s[e] * sc + m - lse2) : 0.0f;
       float dpv = dp[e];
-      if (p.drop_threshold != 0u) dpv = dropout_keep(p.drop_seed, didx0 + j, p.drop_threshold) ? dpv * p.drop_scale : 0.0f;
+      if (p.drop_threshold != 0u) dpv = dropout_keep(dseed, didx0 + j, p.drop_threshold) ? dpv * p.drop_scale : 0.0f;
       s[e] = pv * (dpv - delta) * p.scale;
     }
 #pragma unroll
@@ -354,7 +357,7 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
 }
 
 static int fill_params(AttnParams& p, int B, int S, int H, const float* mask, float* lse, void* out,
-                       float dropout_p, unsigned seed) {
+                       float dropout_p, unsigned seed, const unsigned* seed_dev) {
   DET_REQUIRE(S >= 1 && S <= ATT_S, "fused attention supports sequence length <= 128");
   DET_REQUIRE(B >= 1 && H >= 1, "bad attention shape");
   p.B = B; p.S = S; p.H = H; p.hidden = H * ATT_D;
@@ -368,6 +371,7 @@ static int fill_params(AttnParams& p, int B, int S, int H, const float* mask, fl
     p.drop_threshold = 0; p.drop_scale = 1.0f;
   }
   p.drop_seed = seed;
+  p.drop_seed_dev = seed_dev;
   return 0;
 }
 
@@ -377,10 +381,10 @@ static int fill_params(AttnParams& p, int B, int S, int H, const float* mask, fl
 // mask: additive fp32 [B, S] or null;  lse: [B, H, S] fp32.
 extern "C" int det_attention_fwd(const void* qkv, const float* mask, void* ctx, float* lse, int B,
                                  int S, int H, float dropout_p, unsigned int seed,
-                                 cudaStream_t stream) {
+                                 const unsigned int* seed_dev, cudaStream_t stream) {
   using namespace det;
   AttnParams p;
-  int rc = fill_params(p, B, S, H, mask, lse, ctx, dropout_p, seed);
+  int rc = fill_params(p, B, S, H, mask, lse, ctx, dropout_p, seed, seed_dev);
   if (rc) return rc;
   CUtensorMap tq;
   rc = make_tma_2d_bf16(&tq, qkv, 3ull * p.hidden, (uint64_t)B * S, 3ull * p.hidden, 64, ATT_S);
@@ -400,10 +404,10 @@ extern "C" int det_attention_fwd(const void* qkv, const float* mask, void* ctx, 
 // dctx: [B*S, H*64] bf16;  dqkv (out): [B*S, 3*H*64] bf16.
 extern "C" int det_attention_bwd(const void* qkv, const void* dctx, const float* mask,
                                  const float* lse, void* dqkv, int B, int S, int H, float dropout_p,
-                                 unsigned int seed, cudaStream_t stream) {
+                                 unsigned int seed, const unsigned int* seed_dev, cudaStream_t stream) {
   using namespace det;
   AttnParams p;
-  int rc = fill_params(p, B, S, H, mask, const_cast<float*>(lse), dqkv, dropout_p, seed);
+  int rc = fill_params(p, B, S, H, mask, const_cast<float*>(lse), dqkv, dropout_p, seed, seed_dev);
   if (rc) return rc;
   CUtensorMap tq, td;
   rc = make_tma_2d_bf16(&tq, qkv, 3ull * p.hidden, (uint64_t)B * S, 3ull * p.hidden, 64, ATT_S);

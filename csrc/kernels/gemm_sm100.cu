@@ -44,6 +44,7 @@ struct GemmParams {
   uint32_t drop_threshold;  // 0 = no dropout
   float drop_scale;
   uint32_t drop_seed;
+  const uint32_t* drop_seed_dev;  // optional per-step seed in device memory (CUDA-graph friendly)
 };
 
 __device__ __forceinline__ float gelu_erf(float x) {
@@ -268,9 +269,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           } else if (p.epi == EPI_BIAS_RESID) {
             if (p.drop_threshold != 0u) {
               const uint32_t base = static_cast<uint32_t>(row) * static_cast<uint32_t>(p.N) + static_cast<uint32_t>(col0);
+              const uint32_t dseed = p.drop_seed + (p.drop_seed_dev ? __ldg(p.drop_seed_dev) * 0x9E3779B9u : 0u);
 #pragma unroll
               for (int j = 0; j < 32; ++j)
-                v[j] = dropout_keep(p.drop_seed, base + j, p.drop_threshold) ? v[j] * p.drop_scale : 0.0f;
+                v[j] = dropout_keep(dseed, base + j, p.drop_threshold) ? v[j] * p.drop_scale : 0.0f;
             }
             if (full_cols) {
               const uint4* ri = reinterpret_cast<const uint4*>(p.aux_in + aux_off);
@@ -394,7 +396,8 @@ extern "C" int det_gemm_bf16(const void* A, const void* B, void* C, int M, int N
                              int b_mn, long long lda, long long ldb, long long ldc, int out_mode,
                              int epi, float alpha, const float* bias, const void* aux_in,
                              void* aux_out, long long ld_aux, float dropout_p,
-                             unsigned int dropout_seed, int splitk, int force_bn,
+                             unsigned int dropout_seed, const unsigned int* dropout_seed_dev, int splitk,
+                             int force_bn,
                              cudaStream_t stream) {
   using namespace det;
   DET_REQUIRE(M > 0 && N > 0 && K > 0, "empty GEMM");
@@ -431,6 +434,7 @@ extern "C" int det_gemm_bf16(const void* A, const void* B, void* C, int M, int N
     p.drop_threshold = 0; p.drop_scale = 1.0f;
   }
   p.drop_seed = dropout_seed;
+  p.drop_seed_dev = dropout_seed_dev;
 
   CUtensorMap ta, tb;
   int rc;

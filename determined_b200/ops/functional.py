@@ -1,0 +1,212 @@
+"""Tensor-level wrappers over the sm_100a kernel library.
+
+Each function takes ``torch`` CUDA tensors, launches on the CURRENT stream (so it composes with
+side streams and CUDA-graph capture), and returns/fills torch tensors. No function here
+synchronises the device or touches host memory.
+
+Operand conventions for :func:`gemm` mirror the C ABI: an operand is "K-major" when the contraction
+dimension is contiguous, "MN-major" when the M/N dimension is. With those two flags forward
+(``x @ W.T``), dgrad (``dy @ W``) and wgrad (``dy.T @ x``) need no transposed copies.
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Tuple
+
+import torch
+
+from . import _native
+
+EPI_NONE, EPI_BIAS, EPI_BIAS_GELU, EPI_DGELU, EPI_BIAS_RESID = 0, 1, 2, 3, 4
+OUT_BF16, OUT_F32, OUT_F32_ATOMIC_ADD = 0, 1, 2
+OPT_ADAM, OPT_ADAMW, OPT_SGD, OPT_RMSPROP, OPT_ADADELTA = 0, 1, 2, 3, 4
+RED_AVG, RED_SUM, RED_MAX, RED_MIN = 0, 1, 2, 3
+
+
+def _p(t: Optional[torch.Tensor]):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def native_available() -> bool:
+    return torch.cuda.is_available() and _native.available()
+
+
+# ------------------------------------------------------------------------------------------------
+# Per-step dropout seed (device resident so CUDA-graph replays draw fresh masks)
+# ------------------------------------------------------------------------------------------------
+_seed_state = {}
+
+
+def step_seed_tensor(device=None) -> torch.Tensor:
+    dev = torch.device(device if device is not None else torch.cuda.current_device())
+    if dev.type == "cuda" and dev.index is None:
+        dev = torch.device("cuda", torch.cuda.current_device())
+    t = _seed_state.get(dev)
+    if t is None:
+        t = torch.zeros(1, dtype=torch.int32, device=dev)
+        _seed_state[dev] = t
+    return t
+
+
+def advance_step_seed(device=None) -> None:
+    """Bump the device-side dropout seed (captured as one tiny kernel inside a step graph)."""
+    step_seed_tensor(device).add_(1)
+
+
+def set_step_seed(value: int, device=None) -> None:
+    step_seed_tensor(device).fill_(int(value) & 0x7FFFFFFF)
+
+
+# ------------------------------------------------------------------------------------------------
+# GEMM
+# ------------------------------------------------------------------------------------------------
+def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K: int, *, a_mn: bool = False,
+         b_mn: bool = False, out_mode: int = OUT_BF16, epi: int = EPI_NONE, alpha: float = 1.0,
+         bias: Optional[torch.Tensor] = None, aux_in: Optional[torch.Tensor] = None,
+         aux_out: Optional[torch.Tensor] = None, dropout_p: float = 0.0, seed: int = 0,
+         splitk: int = 0, force_bn: int = 0) -> torch.Tensor:
+    """``out[M,N] = epilogue(a[M,K] @ b[N,K].T)`` on tcgen05 tensor cores (bf16 in, fp32 accumulate).
+
+    ``a``: [M,K] (K-major) or, with ``a_mn``, stored [K,M].  ``b``: [N,K] or, with ``b_mn``, stored [K,N].
+    """
+    aux = aux_in if aux_in is not None else aux_out
+    _native.call(
+        "det_gemm_bf16", _p(a), _p(b), _p(out), M, N, K, int(a_mn), int(b_mn), a.stride(0), b.stride(0),
+        out.stride(0), out_mode, epi, float(alpha), _p(bias), _p(aux_in), _p(aux_out),
+        aux.stride(0) if aux is not None else 0, float(dropout_p), int(seed) & 0xFFFFFFFF,
+        _p(step_seed_tensor(a.device)) if dropout_p > 0 else None, splitk, force_bn, _stream())
+    return out
+
+
+def tma_compatible(t: torch.Tensor) -> bool:
+    return (t.dtype == torch.bfloat16 and t.dim() == 2 and t.stride(1) == 1 and t.stride(0) % 8 == 0
+            and t.data_ptr() % 16 == 0)
+
+
+def gemm_small(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K: int,
+               sa: Tuple[int, int], sb: Tuple[int, int], sc: Tuple[int, int], *, bias: Optional[torch.Tensor] = None,
+               act_tanh: bool = False, alpha: float = 1.0, accumulate: bool = False) -> torch.Tensor:
+    """Strided CUDA-core GEMM for tiny heads: ``out[m,n] (+)= act(alpha * sum_k a[m,k] b[n,k] + bias[n])``.
+    ``sa=(stride_m, stride_k)``, ``sb=(stride_n, stride_k)``, ``sc=(stride_m, stride_n)`` in elements."""
+    def f32(t):
+        if t.dtype == torch.float32:
+            return 1
+        if t.dtype == torch.bfloat16:
+            return 0
+        raise TypeError(f"gemm_small supports bf16/fp32, got {t.dtype}")
+    _native.call("det_gemm_small", _p(a), _p(b), _p(out), M, N, K, sa[0], sa[1], sb[0], sb[1], sc[0], sc[1],
+                 f32(a), f32(b), f32(out), _p(bias), int(act_tanh), float(alpha), int(accumulate), _stream())
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+# Attention / LayerNorm / misc
+# ------------------------------------------------------------------------------------------------
+def attention_fwd(qkv: torch.Tensor, mask: Optional[torch.Tensor], B: int, S: int, H: int, dropout_p: float,
+                  seed: int) -> Tuple[torch.Tensor, torch.Tensor]:
+    ctx = torch.empty(B * S, H * 64, dtype=torch.bfloat16, device=qkv.device)
+    lse = torch.empty(B, H, S, dtype=torch.float32, device=qkv.device)
+    _native.call("det_attention_fwd", _p(qkv), _p(mask), _p(ctx), _p(lse), B, S, H, float(dropout_p),
+                 int(seed) & 0xFFFFFFFF, _p(step_seed_tensor(qkv.device)) if dropout_p > 0 else None, _stream())
+    return ctx, lse
+
+
+def attention_bwd(qkv: torch.Tensor, dctx: torch.Tensor, mask: Optional[torch.Tensor], lse: torch.Tensor, B: int,
+                  S: int, H: int, dropout_p: float, seed: int) -> torch.Tensor:
+    dqkv = torch.empty_like(qkv)
+    _native.call("det_attention_bwd", _p(qkv), _p(dctx), _p(mask), _p(lse), _p(dqkv), B, S, H, float(dropout_p),
+                 int(seed) & 0xFFFFFFFF, _p(step_seed_tensor(qkv.device)) if dropout_p > 0 else None, _stream())
+    return dqkv
+
+
+def layernorm_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float, dropout_p: float = 0.0,
+                  seed: int = 0) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    T, H = x.shape
+    y = torch.empty_like(x)
+    mean = torch.empty(T, dtype=torch.float32, device=x.device)
+    rstd = torch.empty(T, dtype=torch.float32, device=x.device)
+    _native.call("det_layernorm_fwd", _p(x), _p(gamma), _p(beta), _p(y), _p(mean), _p(rstd), T, H, float(eps),
+                 float(dropout_p), int(seed) & 0xFFFFFFFF,
+                 _p(step_seed_tensor(x.device)) if dropout_p > 0 else None, _stream())
+    return y, mean, rstd
+
+
+def layernorm_bwd(dy: torch.Tensor, x: torch.Tensor, gamma: torch.Tensor, mean: torch.Tensor, rstd: torch.Tensor,
+                  dgamma: Optional[torch.Tensor], dbeta: Optional[torch.Tensor], *, want_masked: bool = False,
+                  in_dropout_p: float = 0.0, in_seed: int = 0, out_dropout_p: float = 0.0,
+                  out_seed: int = 0) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """Returns (dx, dx_masked). dgamma/dbeta (fp32) are ACCUMULATED into."""
+    T, H = x.shape
+    dx = torch.empty_like(x)
+    dxm = torch.empty_like(x) if want_masked else None
+    any_drop = in_dropout_p > 0 or out_dropout_p > 0
+    _native.call("det_layernorm_bwd", _p(dy), _p(x), _p(gamma), _p(mean), _p(rstd), _p(dx), _p(dxm), _p(dgamma),
+                 _p(dbeta), T, H, float(in_dropout_p), int(in_seed) & 0xFFFFFFFF, float(out_dropout_p),
+                 int(out_seed) & 0xFFFFFFFF, _p(step_seed_tensor(x.device)) if any_drop else None, _stream())
+    return dx, dxm
+
+
+def colsum_accum(x: torch.Tensor, out_f32: torch.Tensor) -> None:
+    """out[n] += sum_t x[t, n] (bf16 in, fp32 accumulate) — bias gradients."""
+    T, N = x.shape
+    _native.call("det_colsum_bf16", _p(x), _p(out_f32), T, N, x.stride(0), _stream())
+
+
+def embed_gather(ids: torch.Tensor, type_ids: Optional[torch.Tensor], word: torch.Tensor, pos: torch.Tensor,
+                 typ: torch.Tensor, S: int) -> torch.Tensor:
+    T = ids.numel()
+    H = word.shape[1]
+    out = torch.empty(T, H, dtype=torch.bfloat16, device=word.device)
+    _native.call("det_embed_gather", _p(ids), _p(type_ids), _p(word), _p(pos), _p(typ), _p(out), T, S, H, _stream())
+    return out
+
+
+def embed_scatter(ids: torch.Tensor, type_ids: Optional[torch.Tensor], de: torch.Tensor, dword: torch.Tensor,
+                  dpos: torch.Tensor, dtyp: torch.Tensor, S: int) -> None:
+    T, H = de.shape
+    _native.call("det_embed_scatter", _p(ids), _p(type_ids), _p(de), _p(dword), _p(dpos), _p(dtyp), T, S, H, _stream())
+
+
+def softmax_ce(logits_f32: torch.Tensor, labels: torch.Tensor, gscale: float) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Per-row loss and dlogits = (softmax - onehot) * gscale in one pass."""
+    B, C = logits_f32.shape
+    loss = torch.empty(B, dtype=torch.float32, device=logits_f32.device)
+    dlogits = torch.empty_like(logits_f32)
+    _native.call("det_softmax_ce", _p(logits_f32), _p(labels), _p(loss), _p(dlogits), B, C, float(gscale), _stream())
+    return loss, dlogits
+
+
+def cast_to_bf16(src_f32: torch.Tensor, dst_bf16: torch.Tensor) -> None:
+    _native.call("det_cast_f32_bf16", _p(src_f32), _p(dst_bf16), src_f32.numel(), _stream())
+
+
+# ------------------------------------------------------------------------------------------------
+# Optimizer / gradient bucket kernels
+# ------------------------------------------------------------------------------------------------
+def fused_optimizer_step(variant: int, param: torch.Tensor, grad: torch.Tensor, state1: torch.Tensor,
+                         state2: Optional[torch.Tensor], shadow: Optional[torch.Tensor], hyper_dev: torch.Tensor,
+                         grad_scale_dev: Optional[torch.Tensor], found_inf_dev: Optional[torch.Tensor],
+                         zero_grad: bool) -> None:
+    _native.call("det_fused_optimizer_step", variant, _p(param), _p(grad), _p(state1), _p(state2), _p(shadow),
+                 param.numel(), _p(hyper_dev), _p(grad_scale_dev), _p(found_inf_dev), int(zero_grad), _stream())
+
+
+def grad_sumsq_finite(grad: torch.Tensor, grad_scale_dev: Optional[torch.Tensor], sumsq_dev: torch.Tensor,
+                      found_inf_dev: Optional[torch.Tensor]) -> None:
+    _native.call("det_grad_sumsq_finite", _p(grad), grad.numel(), _p(grad_scale_dev), _p(sumsq_dev),
+                 _p(found_inf_dev), _stream())
+
+
+def clip_coef(sumsq_dev: torch.Tensor, max_norm: float, base_scale_dev: Optional[torch.Tensor],
+              out2_dev: torch.Tensor) -> None:
+    _native.call("det_clip_coef", _p(sumsq_dev), float(max_norm), _p(base_scale_dev), _p(out2_dev), _stream())
+
+
+def loss_scale_update(state3_dev: torch.Tensor, found_inf_dev: torch.Tensor, growth: float, backoff: float,
+                      growth_interval: int, divisor: float) -> None:
+    _native.call("det_loss_scale_update", _p(state3_dev), _p(found_inf_dev), float(growth), float(backoff),
+                 int(growth_interval), float(divisor), _stream())
