@@ -11,6 +11,11 @@
 // The transposed products use MN-major shared-memory descriptors over the SAME swizzled smem tile
 // that the row-major products read, so P and dS are written once.
 //
+// Thread mapping: a 128x128 score tile lives in TMEM as 128 lanes (query rows) x 128 columns (keys).
+// A warp may only touch the 32 lanes of its quarter (warp_id % 4), so the CTA uses several warps per
+// quarter, each owning a slice of the columns; row reductions (max / sum / delta) are combined
+// through a small smem exchange.
+//
 // Replaces HF BertSelfAttention's matmul/softmax/dropout/matmul chain used by the reference's BERT
 // example (reference: examples/nlp/bert_glue_pytorch/model_def.py:60-68).
 #include "host_utils.h"
@@ -36,12 +41,21 @@ constexpr int ATT_D = 64;
 constexpr uint32_t ATT_TILE = ATT_S * ATT_D * 2;  // 16 KB
 constexpr float LOG2E = 1.4426950408889634f;
 
-// ------------------------------------------------------------------------------------------------
-// Forward
-// ------------------------------------------------------------------------------------------------
-constexpr uint32_t ATT_FWD_SMEM = 3 * ATT_TILE + 2 * ATT_TILE + 1024 + 64;
+__device__ __forceinline__ uint4 pack8_bf16(const float* v) {
+  uint4 pk;
+  pk.x = ptx::pack_bf16x2(v[0], v[1]); pk.y = ptx::pack_bf16x2(v[2], v[3]);
+  pk.z = ptx::pack_bf16x2(v[4], v[5]); pk.w = ptx::pack_bf16x2(v[6], v[7]);
+  return pk;
+}
 
-__global__ void __launch_bounds__(128, 2)
+// ------------------------------------------------------------------------------------------------
+// Forward: 256 threads = 4 lane quarters x 2 column halves (64 keys each); 2 CTAs per SM.
+// ------------------------------------------------------------------------------------------------
+constexpr int ATT_FWD_THREADS = 256;
+constexpr uint32_t ATT_FWD_RED = 2 * 2 * ATT_S * 4;  // max + sum exchange
+constexpr uint32_t ATT_FWD_SMEM = 5 * ATT_TILE + 1024 + 64 + ATT_FWD_RED;
+
+__global__ void __launch_bounds__(ATT_FWD_THREADS, 2)
 attention_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -51,6 +65,8 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnPara
   uint8_t* sP = smem + 3 * ATT_TILE;  // 2 chunks of [128 q][64 keys]
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 5 * ATT_TILE);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+  float* red_max = reinterpret_cast<float*>(smem + 5 * ATT_TILE + 64);  // [2][128]
+  float* red_sum = red_max + 2 * ATT_S;                                  // [2][128]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b = blockIdx.x / p.H, h = blockIdx.x % p.H;
@@ -91,47 +107,51 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnPara
   ptx::mbar_wait(mma_bar, 0);
   ptx::tc_fence_after();
 
-  // ---- softmax on this thread's query row ----
-  const int q = tid;  // query row == TMEM lane
-  const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
-  float s[128];
-#pragma unroll
-  for (int c = 0; c < 4; ++c) ptx::tmem_ld_32x32b_x32(tS + lane_base + c * 32, s + c * 32);
+  // ---- softmax: this thread owns query row q, keys [64*cg, 64*cg + 64) ----
+  const int q = (warp & 3) * 32 + lane;  // query row == TMEM lane
+  const int cg = warp >> 2;              // column half
+  const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
+  float s[64];
+  ptx::tmem_ld_32x32b_x32(tS + lane_base + cg * 64, s);
+  ptx::tmem_ld_32x32b_x32(tS + lane_base + cg * 64 + 32, s + 32);
   ptx::tmem_ld_wait();
   const float sc = p.scale * LOG2E;
   float mx = -INFINITY;
 #pragma unroll
-  for (int j = 0; j < 128; ++j) {
+  for (int e = 0; e < 64; ++e) {
+    const int j = cg * 64 + e;
     float m = 0.0f;
     if (p.mask != nullptr && j < p.S) m = __ldg(p.mask + b * p.S + j) * LOG2E;
-    s[j] = (j < p.S) ? (s[j] * sc + m) : -INFINITY;
-    mx = fmaxf(mx, s[j]);
+    s[e] = (j < p.S) ? (s[e] * sc + m) : -INFINITY;
+    mx = fmaxf(mx, s[e]);
   }
+  red_max[cg * ATT_S + q] = mx;
+  __syncthreads();
+  mx = fmaxf(red_max[q], red_max[ATT_S + q]);
   float sum = 0.0f;
 #pragma unroll
-  for (int j = 0; j < 128; ++j) {
-    s[j] = exp2f(s[j] - mx);
-    sum += s[j];
+  for (int e = 0; e < 64; ++e) {
+    s[e] = exp2f(s[e] - mx);
+    sum += s[e];
   }
+  red_sum[cg * ATT_S + q] = sum;
+  __syncthreads();
+  sum = red_sum[q] + red_sum[ATT_S + q];
   const float inv = 1.0f / sum;
-  if (q < p.S) p.lse[(static_cast<long long>(b) * p.H + h) * p.S + q] = (mx + log2f(sum)) * (1.0f / LOG2E);
-  const uint32_t didx0 = ((static_cast<uint32_t>(b) * p.H + h) * p.S + q) * p.S;
+  if (cg == 0 && q < p.S) p.lse[(static_cast<long long>(b) * p.H + h) * p.S + q] = (mx + log2f(sum)) * (1.0f / LOG2E);
+  const uint32_t didx0 = ((static_cast<uint32_t>(b) * p.H + h) * p.S + q) * p.S + cg * 64;
   const uint32_t dseed = p.drop_seed + (p.drop_seed_dev ? __ldg(p.drop_seed_dev) * 0x9E3779B9u : 0u);
 #pragma unroll
-  for (int u = 0; u < 16; ++u) {  // 16-byte units of 8 keys
+  for (int u = 0; u < 8; ++u) {  // 16-byte units of 8 keys; this half is exactly smem chunk `cg`
     float v[8];
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
-      const int j = u * 8 + e;
-      float pv = s[j] * inv;
-      if (p.drop_threshold != 0u) pv = dropout_keep(dseed, didx0 + j, p.drop_threshold) ? pv * p.drop_scale : 0.0f;
+      float pv = s[u * 8 + e] * inv;
+      if (p.drop_threshold != 0u)
+        pv = dropout_keep(dseed, didx0 + u * 8 + e, p.drop_threshold) ? pv * p.drop_scale : 0.0f;
       v[e] = pv;
     }
-    uint4 pk;
-    pk.x = ptx::pack_bf16x2(v[0], v[1]); pk.y = ptx::pack_bf16x2(v[2], v[3]);
-    pk.z = ptx::pack_bf16x2(v[4], v[5]); pk.w = ptx::pack_bf16x2(v[6], v[7]);
-    const uint32_t chunk = u >> 3, unit = u & 7;
-    *reinterpret_cast<uint4*>(sP + chunk * ATT_TILE + ptx::sw128_offset(q, unit)) = pk;
+    *reinterpret_cast<uint4*>(sP + cg * ATT_TILE + ptx::sw128_offset(q, u)) = pack8_bf16(v);
   }
   ptx::fence_proxy_async_smem();
   ptx::tc_fence_before();
@@ -150,19 +170,13 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnPara
   }
   ptx::mbar_wait(mma_bar, 1);
   ptx::tc_fence_after();
-  float o[64];
-  ptx::tmem_ld_32x32b_x32(tO + lane_base, o);
-  ptx::tmem_ld_32x32b_x32(tO + lane_base + 32, o + 32);
+  float o[32];
+  ptx::tmem_ld_32x32b_x32(tO + lane_base + cg * 32, o);
   ptx::tmem_ld_wait();
   if (q < p.S) {
-    uint4* dst = reinterpret_cast<uint4*>(p.out + (static_cast<long long>(b) * p.S + q) * p.hidden + h * ATT_D);
+    uint4* dst = reinterpret_cast<uint4*>(p.out + (static_cast<long long>(b) * p.S + q) * p.hidden + h * ATT_D + cg * 32);
 #pragma unroll
-    for (int u = 0; u < 8; ++u) {
-      uint4 pk;
-      pk.x = ptx::pack_bf16x2(o[8 * u + 0], o[8 * u + 1]); pk.y = ptx::pack_bf16x2(o[8 * u + 2], o[8 * u + 3]);
-      pk.z = ptx::pack_bf16x2(o[8 * u + 4], o[8 * u + 5]); pk.w = ptx::pack_bf16x2(o[8 * u + 6], o[8 * u + 7]);
-      dst[u] = pk;
-    }
+    for (int u = 0; u < 4; ++u) dst[u] = pack8_bf16(o + 8 * u);
   }
   ptx::tc_fence_before();
   __syncthreads();
@@ -173,11 +187,13 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnPara
 }
 
 // ------------------------------------------------------------------------------------------------
-// Backward
+// Backward: 512 threads = 4 lane quarters x 4 column groups (32 keys each); 1 CTA per SM.
 // ------------------------------------------------------------------------------------------------
-constexpr uint32_t ATT_BWD_SMEM = 4 * ATT_TILE + 4 * ATT_TILE + 1024 + 64;
+constexpr int ATT_BWD_THREADS = 512;
+constexpr uint32_t ATT_BWD_RED = 4 * ATT_S * 4;
+constexpr uint32_t ATT_BWD_SMEM = 8 * ATT_TILE + 1024 + 64 + ATT_BWD_RED;
 
-__global__ void __launch_bounds__(128, 1)
+__global__ void __launch_bounds__(ATT_BWD_THREADS, 1)
 attention_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
                      const __grid_constant__ CUtensorMap tma_do, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -190,8 +206,9 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
   uint8_t* sdS = smem + 6 * ATT_TILE;  // 2 chunks
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 8 * ATT_TILE);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+  float* red_delta = reinterpret_cast<float*>(smem + 8 * ATT_TILE + 64);  // [4][128]
 
-  const int tid = threadIdx.x, warp = tid >> 5;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b = blockIdx.x / p.H, h = blockIdx.x % p.H;
   const uint32_t tma_bar = ptx::smem_u32(&bars[0]);
   const uint32_t mma_bar = ptx::smem_u32(&bars[1]);
@@ -237,66 +254,52 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
   ptx::mbar_wait(mma_bar, 0);
   ptx::tc_fence_after();
 
-  const int q = tid;
+  const int q = (warp & 3) * 32 + lane;
+  const int cg = warp >> 2;  // keys [32*cg, 32*cg + 32)
   const bool q_ok = q < p.S;
-  const uint32_t lane_base = static_cast<uint32_t>(warp * 32) << 16;
+  const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
   const float sc = p.scale * LOG2E;
   const float lse2 = q_ok ? p.lse[(static_cast<long long>(b) * p.H + h) * p.S + q] * LOG2E : 0.0f;
-  const uint32_t didx0 = ((static_cast<uint32_t>(b) * p.H + h) * p.S + q) * p.S;
+  const uint32_t didx0 = ((static_cast<uint32_t>(b) * p.H + h) * p.S + q) * p.S + cg * 32;
   const uint32_t dseed = p.drop_seed + (p.drop_seed_dev ? __ldg(p.drop_seed_dev) * 0x9E3779B9u : 0u);
 
-  // Pass A: P' = dropout(P) -> smem, delta = sum_j P'_ij dP'_ij
+  float pr[32], dp[32];
+  ptx::tmem_ld_32x32b_x32(tS + lane_base + cg * 32, pr);
+  ptx::tmem_ld_32x32b_x32(tdP + lane_base + cg * 32, dp);
+  ptx::tmem_ld_wait();
+  // P (pre-dropout probabilities), masked dP, P' = dropout(P) -> smem, partial delta
   float delta = 0.0f;
-#pragma unroll 1
-  for (int c = 0; c < 4; ++c) {
-    float s[32], dp[32];
-    ptx::tmem_ld_32x32b_x32(tS + lane_base + c * 32, s);
-    ptx::tmem_ld_32x32b_x32(tdP + lane_base + c * 32, dp);
-    ptx::tmem_ld_wait();
+  {
+    float pd[32];
 #pragma unroll
     for (int e = 0; e < 32; ++e) {
-      const int j = c * 32 + e;
+      const int j = cg * 32 + e;
       float m = 0.0f;
       if (p.mask != nullptr && j < p.S) m = __ldg(p.mask + b * p.S + j) * LOG2E;
-      float pv = (q_ok && j < p.S) ? exp2f(s[e] * sc + m - lse2) : 0.0f;
-      if (p.drop_threshold != 0u) pv = dropout_keep(dseed, didx0 + j, p.drop_threshold) ? pv * p.drop_scale : 0.0f;
-      s[e] = pv;
-      delta += pv * dp[e];
+      const float pv = (q_ok && j < p.S) ? exp2f(pr[e] * sc + m - lse2) : 0.0f;
+      float keep = 1.0f;
+      if (p.drop_threshold != 0u) keep = dropout_keep(dseed, didx0 + e, p.drop_threshold) ? p.drop_scale : 0.0f;
+      pr[e] = pv;
+      pd[e] = pv * keep;
+      dp[e] *= keep;               // dP = dP' * mask * scale
+      delta += pv * dp[e];         // sum_j P'_ij dP'_ij  ==  sum_j P_ij dP_ij
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
-      uint4 pk;
-      pk.x = ptx::pack_bf16x2(s[8 * u + 0], s[8 * u + 1]); pk.y = ptx::pack_bf16x2(s[8 * u + 2], s[8 * u + 3]);
-      pk.z = ptx::pack_bf16x2(s[8 * u + 4], s[8 * u + 5]); pk.w = ptx::pack_bf16x2(s[8 * u + 6], s[8 * u + 7]);
-      const uint32_t gu = c * 4 + u;  // global 16-byte unit index 0..15
-      *reinterpret_cast<uint4*>(sP + (gu >> 3) * ATT_TILE + ptx::sw128_offset(q, gu & 7)) = pk;
+      const uint32_t gu = cg * 4 + u;  // global 16-byte unit index 0..15
+      *reinterpret_cast<uint4*>(sP + (gu >> 3) * ATT_TILE + ptx::sw128_offset(q, gu & 7)) = pack8_bf16(pd + 8 * u);
     }
   }
-  // Pass B: dS = P * (dP - delta) * scale -> smem
-#pragma unroll 1
-  for (int c = 0; c < 4; ++c) {
-    float s[32], dp[32];
-    ptx::tmem_ld_32x32b_x32(tS + lane_base + c * 32, s);
-    ptx::tmem_ld_32x32b_x32(tdP + lane_base + c * 32, dp);
-    ptx::tmem_ld_wait();
+  red_delta[cg * ATT_S + q] = delta;
+  __syncthreads();
+  delta = red_delta[q] + red_delta[ATT_S + q] + red_delta[2 * ATT_S + q] + red_delta[3 * ATT_S + q];
+  // dS = P * (dP - delta) * scale -> smem
 #pragma unroll
-    for (int e = 0; e < 32; ++e) {
-      const int j = c * 32 + e;
-      float m = 0.0f;
-      if (p.mask != nullptr && j < p.S) m = __ldg(p.mask + b * p.S + j) * LOG2E;
-      const float pv = (q_ok && j < p.S) ? exp2f(s[e] * sc + m - lse2) : 0.0f;
-      float dpv = dp[e];
-      if (p.drop_threshold != 0u) dpv = dropout_keep(dseed, didx0 + j, p.drop_threshold) ? dpv * p.drop_scale : 0.0f;
-      s[e] = pv * (dpv - delta) * p.scale;
-    }
+  for (int e = 0; e < 32; ++e) pr[e] = pr[e] * (dp[e] - delta) * p.scale;
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      uint4 pk;
-      pk.x = ptx::pack_bf16x2(s[8 * u + 0], s[8 * u + 1]); pk.y = ptx::pack_bf16x2(s[8 * u + 2], s[8 * u + 3]);
-      pk.z = ptx::pack_bf16x2(s[8 * u + 4], s[8 * u + 5]); pk.w = ptx::pack_bf16x2(s[8 * u + 6], s[8 * u + 7]);
-      const uint32_t gu = c * 4 + u;
-      *reinterpret_cast<uint4*>(sdS + (gu >> 3) * ATT_TILE + ptx::sw128_offset(q, gu & 7)) = pk;
-    }
+  for (int u = 0; u < 4; ++u) {
+    const uint32_t gu = cg * 4 + u;
+    *reinterpret_cast<uint4*>(sdS + (gu >> 3) * ATT_TILE + ptx::sw128_offset(q, gu & 7)) = pack8_bf16(pr + 8 * u);
   }
   ptx::fence_proxy_async_smem();
   ptx::tc_fence_before();
@@ -329,23 +332,21 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
   ptx::mbar_wait(mma_bar, 1);
   ptx::tc_fence_after();
 
+  // Readout: 3 matrices x 64 columns = 192 columns; column group cg takes 48 of them (3 x 16).
   const long long out_row = (static_cast<long long>(b) * p.S + q) * (3LL * p.hidden) + h * ATT_D;
-#pragma unroll 1
-  for (int which = 0; which < 3; ++which) {
+#pragma unroll
+  for (int t = 0; t < 3; ++t) {
+    const int c16 = cg * 3 + t;          // 16-column slab index 0..11 over [dQ | dK | dV]
+    const int which = c16 >> 2;          // 0 dQ, 1 dK, 2 dV
+    const int col = (c16 & 3) * 16;
     const uint32_t src = (which == 0) ? tdQ : (which == 1 ? tdK : tdV);
-    float o[64];
-    ptx::tmem_ld_32x32b_x32(src + lane_base, o);
-    ptx::tmem_ld_32x32b_x32(src + lane_base + 32, o + 32);
+    float o[16];
+    ptx::tmem_ld_32x32b_x16(src + lane_base + col, o);
     ptx::tmem_ld_wait();
     if (q_ok) {
-      uint4* dst = reinterpret_cast<uint4*>(p.out + out_row + static_cast<long long>(which) * p.hidden);
-#pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        uint4 pk;
-        pk.x = ptx::pack_bf16x2(o[8 * u + 0], o[8 * u + 1]); pk.y = ptx::pack_bf16x2(o[8 * u + 2], o[8 * u + 3]);
-        pk.z = ptx::pack_bf16x2(o[8 * u + 4], o[8 * u + 5]); pk.w = ptx::pack_bf16x2(o[8 * u + 6], o[8 * u + 7]);
-        dst[u] = pk;
-      }
+      uint4* dst = reinterpret_cast<uint4*>(p.out + out_row + static_cast<long long>(which) * p.hidden + col);
+      dst[0] = pack8_bf16(o);
+      dst[1] = pack8_bf16(o + 8);
     }
   }
   ptx::tc_fence_before();
@@ -396,7 +397,7 @@ extern "C" int det_attention_fwd(const void* qkv, const float* mask, void* ctx, 
     DET_CHECK_CUDA(cudaFuncSetAttribute(attention_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_FWD_SMEM));
     attr_set[dev] = true;
   }
-  attention_fwd_kernel<<<B * H, 128, ATT_FWD_SMEM, stream>>>(tq, p);
+  attention_fwd_kernel<<<B * H, ATT_FWD_THREADS, ATT_FWD_SMEM, stream>>>(tq, p);
   DET_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -421,7 +422,7 @@ extern "C" int det_attention_bwd(const void* qkv, const void* dctx, const float*
     DET_CHECK_CUDA(cudaFuncSetAttribute(attention_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_BWD_SMEM));
     attr_set[dev] = true;
   }
-  attention_bwd_kernel<<<B * H, 128, ATT_BWD_SMEM, stream>>>(tq, td, p);
+  attention_bwd_kernel<<<B * H, ATT_BWD_THREADS, ATT_BWD_SMEM, stream>>>(tq, td, p);
   DET_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

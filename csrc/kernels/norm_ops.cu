@@ -210,13 +210,15 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
 // Column sum: out[n] += sum_t x[t, n]   (bias gradients).  N % 8 == 0.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-colsum_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, int T, int N, long long ld) {
+colsum_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, int T, int N, long long ld,
+              const long long* __restrict__ sel, long long sel_value) {
   __shared__ float red[8][256 + 4];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int col = blockIdx.x * 256 + lane * 8;
   float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   if (col < N) {
     for (int row = blockIdx.y * 8 + warp; row < T; row += gridDim.y * 8) {
+      if (sel != nullptr && __ldg(sel + row) != sel_value) continue;
       float f[8];
       unpack8(__ldg(reinterpret_cast<const uint4*>(x + static_cast<long long>(row) * ld + col)), f);
 #pragma unroll
@@ -271,7 +273,7 @@ embed_scatter_kernel(const long long* __restrict__ ids, const long long* __restr
   if (row >= T) return;
   float* w = dword + ids[row] * H;
   float* p = dpos + static_cast<long long>(row % S) * H;
-  float* ty = dtype + (tts ? tts[row] : 0) * H;
+  float* ty = dtype ? dtype + (tts ? tts[row] : 0) * H : nullptr;
   for (int c = lane * 8; c < H; c += 256) {
     float f[8];
     unpack8(__ldg(reinterpret_cast<const uint4*>(de + static_cast<long long>(row) * H + c)), f);
@@ -279,7 +281,7 @@ embed_scatter_kernel(const long long* __restrict__ ids, const long long* __restr
     for (int e = 0; e < 8; ++e) {
       atomicAdd(w + c + e, f[e]);
       atomicAdd(p + c + e, f[e]);
-      atomicAdd(ty + c + e, f[e]);
+      if (dtype != nullptr) atomicAdd(ty + c + e, f[e]);
     }
   }
 }
@@ -414,7 +416,21 @@ extern "C" int det_colsum_bf16(const void* x, float* out, int T, int N, long lon
   DET_REQUIRE(N % 8 == 0 && ld % 8 == 0, "colsum needs N and ld multiples of 8");
   const int gx = (N + 255) / 256;
   int gy = std::max(1, std::min((T + 7) / 8, (det::sm_count() * 4 + gx - 1) / gx));
-  det::colsum_kernel<<<dim3(gx, gy), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x), out, T, N, ld);
+  det::colsum_kernel<<<dim3(gx, gy), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x), out, T, N, ld,
+                                                       nullptr, 0);
+  DET_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// out[n] += sum over rows t with sel[t] == sel_value of x[t, n]  (token-type embedding gradients:
+// a handful of destination rows, so a reduction instead of millions of same-address atomics).
+extern "C" int det_colsum_select_bf16(const void* x, const long long* sel, long long sel_value, float* out,
+                                      int T, int N, long long ld, cudaStream_t stream) {
+  DET_REQUIRE(N % 8 == 0 && ld % 8 == 0, "colsum needs N and ld multiples of 8");
+  const int gx = (N + 255) / 256;
+  int gy = std::max(1, std::min((T + 7) / 8, (det::sm_count() * 4 + gx - 1) / gx));
+  det::colsum_kernel<<<dim3(gx, gy), 256, 0, stream>>>(reinterpret_cast<const __nv_bfloat16*>(x), out, T, N, ld,
+                                                       sel, sel_value);
   DET_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -1,0 +1,332 @@
+"""BERT-base encoder + sequence-classification head (GLUE shape: seq 128) on the sm_100a kernels.
+
+Architecture and default sizes follow ``bert-base-uncased`` as fine-tuned by the reference's
+``examples/nlp/bert_glue_pytorch/model_def.py:27-174`` (HF ``BertForSequenceClassification``): post-LN
+encoder, erf-GELU, learned position/type embeddings, tanh pooler, dropout 0.1.
+
+On CUDA each encoder layer runs as ONE autograd node (:class:`_BertLayerFn`) that launches the
+hand-written kernels directly:
+
+    fwd   QKV GEMM(+bias) → fused attention → out-proj GEMM(+bias+dropout+residual) → LN →
+          FFN1 GEMM(+bias+GELU, saves pre-activation) → FFN2 GEMM(+bias+dropout+residual) → LN
+    bwd   LN-bwd (emits both the residual gradient and the dropout-masked gradient) → wgrad GEMMs
+          accumulating into the flat fp32 gradient bucket → dgrad GEMMs with dGELU / residual-add
+          epilogues → fused attention backward
+
+so no elementwise, transpose, head-split or mask kernels are ever launched. On CPU (tests, local
+mode) the same parameters run through a plain fp32 PyTorch statement of the same math, which is
+also the numerics oracle for the CUDA path.
+"""
+from __future__ import annotations
+
+import dataclasses
+import math
+from typing import Optional, Tuple
+
+import torch
+import torch.nn as nn
+
+from ..ops import functional as F
+from ..ops.modules import accumulate_bgrad, accumulate_wgrad, grad_buffer, shadow_of
+
+
+@dataclasses.dataclass
+class BertConfig:
+    vocab_size: int = 30522
+    hidden_size: int = 768
+    num_hidden_layers: int = 12
+    num_attention_heads: int = 12
+    intermediate_size: int = 3072
+    max_position_embeddings: int = 512
+    type_vocab_size: int = 2
+    hidden_dropout_prob: float = 0.1
+    attention_probs_dropout_prob: float = 0.1
+    layer_norm_eps: float = 1e-12
+    initializer_range: float = 0.02
+    num_labels: int = 2
+
+
+def _gelu(x: torch.Tensor) -> torch.Tensor:
+    return 0.5 * x * (1.0 + torch.erf(x * 0.7071067811865476))
+
+
+# ------------------------------------------------------------------------------------------------
+# Encoder layer
+# ------------------------------------------------------------------------------------------------
+class _BertLayerFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, mask, layer: "BertLayer", B: int, S: int, training: bool):
+        c = layer.cfg
+        T, Hd, I, NH = x.shape[0], c.hidden_size, c.intermediate_size, c.num_attention_heads
+        p_h = c.hidden_dropout_prob if training else 0.0
+        p_a = c.attention_probs_dropout_prob if training else 0.0
+        sd = layer.seed_base
+        dev = x.device
+        bf = torch.bfloat16
+        qkv = torch.empty(T, 3 * Hd, dtype=bf, device=dev)
+        F.gemm(x, shadow_of(layer.qkv_weight), qkv, T, 3 * Hd, Hd, epi=F.EPI_BIAS, bias=layer.qkv_bias)
+        att, lse = F.attention_fwd(qkv, mask, B, S, NH, p_a, sd + 0)
+        h1 = torch.empty(T, Hd, dtype=bf, device=dev)
+        F.gemm(att, shadow_of(layer.out_weight), h1, T, Hd, Hd, epi=F.EPI_BIAS_RESID, bias=layer.out_bias, aux_in=x,
+               dropout_p=p_h, seed=sd + 1)
+        x1, mean1, rstd1 = F.layernorm_fwd(h1, layer.ln1_weight, layer.ln1_bias, c.layer_norm_eps)
+        z = torch.empty(T, I, dtype=bf, device=dev)
+        a = torch.empty(T, I, dtype=bf, device=dev)
+        F.gemm(x1, shadow_of(layer.ffn1_weight), a, T, I, Hd, epi=F.EPI_BIAS_GELU, bias=layer.ffn1_bias, aux_out=z)
+        h2 = torch.empty(T, Hd, dtype=bf, device=dev)
+        F.gemm(a, shadow_of(layer.ffn2_weight), h2, T, Hd, I, epi=F.EPI_BIAS_RESID, bias=layer.ffn2_bias, aux_in=x1,
+               dropout_p=p_h, seed=sd + 2)
+        x2, mean2, rstd2 = F.layernorm_fwd(h2, layer.ln2_weight, layer.ln2_bias, c.layer_norm_eps)
+        ctx.save_for_backward(x, qkv, lse, att, h1, mean1, rstd1, x1, z, a, h2, mean2, rstd2)
+        ctx.layer, ctx.mask, ctx.dims, ctx.drop = layer, mask, (B, S), (p_h, p_a)
+        return x2
+
+    @staticmethod
+    def backward(ctx, dx2):
+        x, qkv, lse, att, h1, mean1, rstd1, x1, z, a, h2, mean2, rstd2 = ctx.saved_tensors
+        L: BertLayer = ctx.layer
+        c = L.cfg
+        B, S = ctx.dims
+        p_h, p_a = ctx.drop
+        sd = L.seed_base
+        T, Hd, I, NH = x.shape[0], c.hidden_size, c.intermediate_size, c.num_attention_heads
+        dev, bf = x.device, torch.bfloat16
+        dx2 = dx2.contiguous()
+        masked = p_h > 0.0
+        # LN2 backward: dh2 (residual branch) and dh2m (dropout-masked: gradient of FFN2's pre-dropout output)
+        dh2, dh2m = F.layernorm_bwd(dx2, h2, L.ln2_weight, mean2, rstd2, grad_buffer(L.ln2_weight),
+                                    grad_buffer(L.ln2_bias), want_masked=masked, out_dropout_p=p_h, out_seed=sd + 2)
+        if not masked:
+            dh2m = dh2
+        accumulate_wgrad(L.ffn2_weight, dh2m, a)
+        accumulate_bgrad(L.ffn2_bias, dh2m)
+        dz = torch.empty(T, I, dtype=bf, device=dev)
+        F.gemm(dh2m, shadow_of(L.ffn2_weight), dz, T, I, Hd, b_mn=True, epi=F.EPI_DGELU, aux_in=z)
+        accumulate_wgrad(L.ffn1_weight, dz, x1)
+        accumulate_bgrad(L.ffn1_bias, dz)
+        dx1 = torch.empty(T, Hd, dtype=bf, device=dev)
+        F.gemm(dz, shadow_of(L.ffn1_weight), dx1, T, Hd, I, b_mn=True, epi=F.EPI_BIAS_RESID, aux_in=dh2)
+        dh1, dh1m = F.layernorm_bwd(dx1, h1, L.ln1_weight, mean1, rstd1, grad_buffer(L.ln1_weight),
+                                    grad_buffer(L.ln1_bias), want_masked=masked, out_dropout_p=p_h, out_seed=sd + 1)
+        if not masked:
+            dh1m = dh1
+        accumulate_wgrad(L.out_weight, dh1m, att)
+        accumulate_bgrad(L.out_bias, dh1m)
+        datt = torch.empty(T, Hd, dtype=bf, device=dev)
+        F.gemm(dh1m, shadow_of(L.out_weight), datt, T, Hd, Hd, b_mn=True)
+        dqkv = F.attention_bwd(qkv, datt, ctx.mask, lse, B, S, NH, p_a, sd + 0)
+        accumulate_wgrad(L.qkv_weight, dqkv, x)
+        accumulate_bgrad(L.qkv_bias, dqkv)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty(T, Hd, dtype=bf, device=dev)
+            F.gemm(dqkv, shadow_of(L.qkv_weight), dx, T, Hd, 3 * Hd, b_mn=True, epi=F.EPI_BIAS_RESID, aux_in=dh1)
+        return dx, None, None, None, None, None
+
+
+class BertLayer(nn.Module):
+    def __init__(self, cfg: BertConfig, index: int) -> None:
+        super().__init__()
+        self.cfg = cfg
+        self.seed_base = 0x1000 + 16 * index
+        Hd, I = cfg.hidden_size, cfg.intermediate_size
+        std = cfg.initializer_range
+        self.qkv_weight = nn.Parameter(torch.randn(3 * Hd, Hd) * std)
+        self.qkv_bias = nn.Parameter(torch.zeros(3 * Hd))
+        self.out_weight = nn.Parameter(torch.randn(Hd, Hd) * std)
+        self.out_bias = nn.Parameter(torch.zeros(Hd))
+        self.ln1_weight = nn.Parameter(torch.ones(Hd))
+        self.ln1_bias = nn.Parameter(torch.zeros(Hd))
+        self.ffn1_weight = nn.Parameter(torch.randn(I, Hd) * std)
+        self.ffn1_bias = nn.Parameter(torch.zeros(I))
+        self.ffn2_weight = nn.Parameter(torch.randn(Hd, I) * std)
+        self.ffn2_bias = nn.Parameter(torch.zeros(Hd))
+        self.ln2_weight = nn.Parameter(torch.ones(Hd))
+        self.ln2_bias = nn.Parameter(torch.zeros(Hd))
+
+    def forward(self, x: torch.Tensor, mask: Optional[torch.Tensor], B: int, S: int) -> torch.Tensor:
+        if x.is_cuda:
+            if not torch.is_grad_enabled() or not x.requires_grad:
+                # the fused node wants a graph edge on x even for layer 0 whose input comes from the
+                # embedding node; eval / no-grad simply runs the forward kernels
+                pass
+            return _BertLayerFn.apply(x, mask, self, B, S, self.training)
+        return self._reference_forward(x, mask, B, S)
+
+    def _reference_forward(self, x, mask, B, S):
+        c = self.cfg
+        Hd, NH = c.hidden_size, c.num_attention_heads
+        drop = nn.functional.dropout
+        xf = x.float()
+        qkv = xf @ self.qkv_weight.t() + self.qkv_bias
+        q, k, v = [t.view(B, S, NH, 64).transpose(1, 2) for t in qkv.split(Hd, dim=-1)]
+        sc = q @ k.transpose(-1, -2) / math.sqrt(64.0)
+        if mask is not None:
+            sc = sc + mask[:, None, None, :].float()
+        p = drop(torch.softmax(sc, dim=-1), c.attention_probs_dropout_prob, self.training)
+        att = (p @ v).transpose(1, 2).reshape(B * S, Hd)
+        h1 = drop(att @ self.out_weight.t() + self.out_bias, c.hidden_dropout_prob, self.training) + xf
+        x1 = nn.functional.layer_norm(h1, (Hd,), self.ln1_weight, self.ln1_bias, c.layer_norm_eps)
+        a = _gelu(x1 @ self.ffn1_weight.t() + self.ffn1_bias)
+        h2 = drop(a @ self.ffn2_weight.t() + self.ffn2_bias, c.hidden_dropout_prob, self.training) + x1
+        return nn.functional.layer_norm(h2, (Hd,), self.ln2_weight, self.ln2_bias, c.layer_norm_eps).to(x.dtype)
+
+
+# ------------------------------------------------------------------------------------------------
+# Embeddings
+# ------------------------------------------------------------------------------------------------
+class _BertEmbedFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ids, tts, emb: "BertEmbeddings", S: int, training: bool, anchor):
+        c = emb.cfg
+        p = c.hidden_dropout_prob if training else 0.0
+        e = F.embed_gather(ids, tts, emb.word_embeddings, emb.position_embeddings, emb.token_type_embeddings, S)
+        x0, mean, rstd = F.layernorm_fwd(e, emb.ln_weight, emb.ln_bias, c.layer_norm_eps, p, emb.seed)
+        ctx.save_for_backward(ids, tts, e, mean, rstd)
+        ctx.emb, ctx.S, ctx.p = emb, S, p
+        return x0
+
+    @staticmethod
+    def backward(ctx, dx0):
+        ids, tts, e, mean, rstd = ctx.saved_tensors
+        emb: BertEmbeddings = ctx.emb
+        de, _ = F.layernorm_bwd(dx0.contiguous(), e, emb.ln_weight, mean, rstd, grad_buffer(emb.ln_weight),
+                                grad_buffer(emb.ln_bias), in_dropout_p=ctx.p, in_seed=emb.seed)
+        F.embed_scatter(ids, tts, de, grad_buffer(emb.word_embeddings), grad_buffer(emb.position_embeddings),
+                        grad_buffer(emb.token_type_embeddings), ctx.S)
+        return None, None, None, None, None, None
+
+
+class BertEmbeddings(nn.Module):
+    def __init__(self, cfg: BertConfig) -> None:
+        super().__init__()
+        self.cfg = cfg
+        self.seed = 0x0777
+        std = cfg.initializer_range
+        self.word_embeddings = nn.Parameter(torch.randn(cfg.vocab_size, cfg.hidden_size) * std)
+        self.position_embeddings = nn.Parameter(torch.randn(cfg.max_position_embeddings, cfg.hidden_size) * std)
+        self.token_type_embeddings = nn.Parameter(torch.randn(cfg.type_vocab_size, cfg.hidden_size) * std)
+        self.ln_weight = nn.Parameter(torch.ones(cfg.hidden_size))
+        self.ln_bias = nn.Parameter(torch.zeros(cfg.hidden_size))
+        # autograd anchor: gives the embedding node a differentiable input so its backward runs
+        self._anchor = nn.Parameter(torch.zeros(1), requires_grad=True)
+
+    def forward(self, ids: torch.Tensor, tts: Optional[torch.Tensor], S: int) -> torch.Tensor:
+        ids = ids.reshape(-1).to(torch.int64).contiguous()
+        tts = None if tts is None else tts.reshape(-1).to(torch.int64).contiguous()
+        if ids.is_cuda:
+            return _BertEmbedFn.apply(ids, tts, self, S, self.training, self._anchor)
+        pos = torch.arange(ids.numel(), device=ids.device) % S
+        e = self.word_embeddings[ids] + self.position_embeddings[pos]
+        e = e + self.token_type_embeddings[tts if tts is not None else torch.zeros_like(ids)]
+        x = nn.functional.layer_norm(e, (self.cfg.hidden_size,), self.ln_weight, self.ln_bias, self.cfg.layer_norm_eps)
+        return nn.functional.dropout(x, self.cfg.hidden_dropout_prob, self.training)
+
+
+# ------------------------------------------------------------------------------------------------
+# Pooler + classifier + loss (tiny: CUDA-core strided GEMM kernel)
+# ------------------------------------------------------------------------------------------------
+class _BertHeadFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, head: "BertClassificationHead", B: int, S: int, training: bool):
+        c = head.cfg
+        Hd, C = c.hidden_size, c.num_labels
+        dev = x.device
+        x_cls = x.view(B, S, Hd)[:, 0]  # strided [B, Hd] view (row pitch S*Hd): TMA reads it in place
+        pre = torch.empty(B, Hd, dtype=torch.bfloat16, device=dev)
+        F.gemm(x_cls, shadow_of(head.pooler_weight), pre, B, Hd, Hd, epi=F.EPI_BIAS, bias=head.pooler_bias)
+        pooled = torch.tanh(pre.float())
+        if training and c.hidden_dropout_prob > 0:
+            keep = (torch.rand(B, Hd, device=dev) >= c.hidden_dropout_prob).float() / (1.0 - c.hidden_dropout_prob)
+            pd = pooled * keep
+        else:
+            keep, pd = None, pooled
+        logits = torch.empty(B, C, dtype=torch.float32, device=dev)
+        F.gemm_small(pd, head.classifier_weight, logits, B, C, Hd, (Hd, 1), (Hd, 1), (C, 1), bias=head.classifier_bias)
+        ctx.save_for_backward(x, pooled, keep, pd)
+        ctx.head, ctx.dims = head, (B, S)
+        return logits
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        x, pooled, keep, pd = ctx.saved_tensors
+        head: BertClassificationHead = ctx.head
+        B, S = ctx.dims
+        c = head.cfg
+        Hd, C = c.hidden_size, c.num_labels
+        dlogits = dlogits.float().contiguous()
+        F.gemm_small(dlogits, pd, grad_buffer(head.classifier_weight), C, Hd, B, (1, C), (1, Hd), (Hd, 1), accumulate=True)
+        grad_buffer(head.classifier_bias).add_(dlogits.sum(0))
+        dpd = torch.empty(B, Hd, dtype=torch.float32, device=x.device)
+        F.gemm_small(dlogits, head.classifier_weight, dpd, B, Hd, C, (C, 1), (1, Hd), (Hd, 1))
+        if keep is not None:
+            dpd = dpd * keep
+        dpre32 = dpd * (1.0 - pooled * pooled)
+        dpre = dpre32.to(torch.bfloat16)
+        x_cls = x.view(B, S, Hd)[:, 0]
+        F.gemm(dpre, x_cls, grad_buffer(head.pooler_weight), Hd, Hd, B, a_mn=True, b_mn=True,
+               out_mode=F.OUT_F32_ATOMIC_ADD)
+        grad_buffer(head.pooler_bias).add_(dpre32.sum(0))
+        dcls = torch.empty(B, Hd, dtype=torch.bfloat16, device=x.device)
+        F.gemm(dpre, shadow_of(head.pooler_weight), dcls, B, Hd, Hd, b_mn=True)
+        dx = torch.zeros_like(x)
+        dx.view(B, S, Hd)[:, 0] = dcls
+        return dx, None, None, None, None
+
+
+class BertClassificationHead(nn.Module):
+    def __init__(self, cfg: BertConfig) -> None:
+        super().__init__()
+        self.cfg = cfg
+        std = cfg.initializer_range
+        self.pooler_weight = nn.Parameter(torch.randn(cfg.hidden_size, cfg.hidden_size) * std)
+        self.pooler_bias = nn.Parameter(torch.zeros(cfg.hidden_size))
+        self.classifier_weight = nn.Parameter(torch.randn(cfg.num_labels, cfg.hidden_size) * std)
+        self.classifier_bias = nn.Parameter(torch.zeros(cfg.num_labels))
+
+    def forward(self, x: torch.Tensor, B: int, S: int) -> torch.Tensor:
+        if x.is_cuda:
+            return _BertHeadFn.apply(x, self, B, S, self.training)
+        cls = x.view(B, S, -1)[:, 0].float()
+        pooled = torch.tanh(cls @ self.pooler_weight.t() + self.pooler_bias)
+        pooled = nn.functional.dropout(pooled, self.cfg.hidden_dropout_prob, self.training)
+        return pooled @ self.classifier_weight.t() + self.classifier_bias
+
+
+class BertForSequenceClassification(nn.Module):
+    """``forward(input_ids, attention_mask=None, token_type_ids=None, labels=None)`` →
+    ``(loss, logits)`` when labels are given, else ``(logits,)`` — the HF calling convention the
+    reference's trial uses (``model_def.py:141-151``)."""
+
+    def __init__(self, cfg: Optional[BertConfig] = None) -> None:
+        super().__init__()
+        self.cfg = cfg or BertConfig()
+        if self.cfg.hidden_size != self.cfg.num_attention_heads * 64:
+            raise ValueError("the fused attention kernel is built for head_dim 64")
+        self.embeddings = BertEmbeddings(self.cfg)
+        self.layers = nn.ModuleList([BertLayer(self.cfg, i) for i in range(self.cfg.num_hidden_layers)])
+        self.head = BertClassificationHead(self.cfg)
+
+    def forward(self, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None,
+                token_type_ids: Optional[torch.Tensor] = None, labels: Optional[torch.Tensor] = None) -> Tuple:
+        B, S = input_ids.shape
+        if input_ids.is_cuda and S > 128:
+            raise ValueError("fused attention supports sequences of at most 128 tokens")
+        mask = None
+        if attention_mask is not None:
+            mask = ((1.0 - attention_mask.to(torch.float32)) * -10000.0).contiguous()
+        x = self.embeddings(input_ids, token_type_ids, S)
+        for layer in self.layers:
+            x = layer(x, mask, B, S)
+        logits = self.head(x, B, S)
+        if labels is None:
+            return (logits,)
+        from ..ops.modules import cross_entropy
+
+        return cross_entropy(logits, labels.reshape(-1)), logits
+
+    def flops_per_sample(self, seq_len: int = 128) -> float:
+        c = self.cfg
+        per_tok = 2 * (4 * c.hidden_size * c.hidden_size + 2 * c.hidden_size * c.intermediate_size)
+        attn = 4 * seq_len * c.hidden_size
+        return 3.0 * c.num_hidden_layers * seq_len * (per_tok + attn)

@@ -25,6 +25,7 @@ _SIGNATURES = {
     "det_layernorm_bwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                           c_int, c_int, c_float, c_uint, c_float, c_uint, c_void_p, c_void_p],
     "det_colsum_bf16": [c_void_p, c_void_p, c_int, c_int, c_ll, c_void_p],
+    "det_colsum_select_bf16": [c_void_p, c_void_p, c_ll, c_void_p, c_int, c_int, c_ll, c_void_p],
     "det_embed_gather": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p],
     "det_embed_scatter": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p],
     "det_softmax_ce": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p],

@@ -168,7 +168,13 @@ def embed_gather(ids: torch.Tensor, type_ids: Optional[torch.Tensor], word: torc
 def embed_scatter(ids: torch.Tensor, type_ids: Optional[torch.Tensor], de: torch.Tensor, dword: torch.Tensor,
                   dpos: torch.Tensor, dtyp: torch.Tensor, S: int) -> None:
     T, H = de.shape
-    _native.call("det_embed_scatter", _p(ids), _p(type_ids), _p(de), _p(dword), _p(dpos), _p(dtyp), T, S, H, _stream())
+    _native.call("det_embed_scatter", _p(ids), _p(type_ids), _p(de), _p(dword), _p(dpos), None, T, S, H, _stream())
+    # token-type rows are few: reduce instead of hammering two addresses with atomics
+    if type_ids is None:
+        _native.call("det_colsum_bf16", _p(de), _p(dtyp[0]), T, H, de.stride(0), _stream())
+    else:
+        for t in range(dtyp.shape[0]):
+            _native.call("det_colsum_select_bf16", _p(de), _p(type_ids), t, _p(dtyp[t]), T, H, de.stride(0), _stream())
 
 
 def softmax_ce(logits_f32: torch.Tensor, labels: torch.Tensor, gscale: float) -> Tuple[torch.Tensor, torch.Tensor]:

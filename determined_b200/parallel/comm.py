@@ -1,0 +1,299 @@
+"""Communicator: everything a trial's worker processes say to one another.
+
+The reference splits this over three transports — Horovod/NCCL for gradients and parameter broadcast
+(``_pytorch_context.py:192-198``, ``_pytorch_trial.py:71-73``), ZMQ + pickle for metrics and barriers
+(``_trial_controller.py:269-315``, ``_pytorch_trial.py:292-335, 580-616``) and ``hvd.broadcast_object``.
+Here one object owns them all:
+
+* **control plane** — ``torch.distributed`` (NCCL on GPUs, Gloo on CPU) for rendezvous, barriers and small
+  pickled objects;
+* **data plane** — on CUDA the hand-written peer-memory kernels (``csrc/comm/fused_allreduce.cu``) over a
+  symmetric arena: fused gradient all-reduce (sum + average + unscale + non-finite flag + grad-norm partial),
+  parameter/optimizer-state broadcast, metric reduce. On CPU (tests, gloo) the same API falls back to
+  ``torch.distributed`` collectives so the host-side logic is exercised without GPUs.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import pickle
+from typing import Any, Dict, List, Optional, Sequence
+
+import torch
+
+from ..ops import _native
+from ..ops import functional as F
+
+
+class Communicator:
+    """Single-process communicator (size 1). Also the interface."""
+
+    rank = 0
+    size = 1
+    local_rank = 0
+
+    def barrier(self) -> None:
+        pass
+
+    def allgather_object(self, obj: Any) -> List[Any]:
+        return [obj]
+
+    def broadcast_object(self, obj: Any, root: int = 0) -> Any:
+        return obj
+
+    def alloc(self, n: int, dtype: torch.dtype, kind: str, device: torch.device) -> torch.Tensor:
+        return torch.zeros(n, dtype=dtype, device=device)
+
+    def allreduce_grad_bucket(self, flat_g: torch.Tensor, scale: float, scale_dev: Optional[torch.Tensor] = None,
+                              sumsq_dev: Optional[torch.Tensor] = None,
+                              found_inf_dev: Optional[torch.Tensor] = None) -> bool:
+        """Sum ``flat_g`` over ranks and multiply by ``scale`` in place. Returns True when the scale (and the
+        optional sumsq / found_inf side outputs) were applied by the collective itself."""
+        return False
+
+    def allreduce_tensors(self, tensors: Sequence[torch.Tensor], scale: float) -> None:
+        if scale != 1.0:
+            for t in tensors:
+                t.mul_(scale)
+
+    def broadcast_tensors(self, tensors: Sequence[torch.Tensor], root: int = 0) -> None:
+        pass
+
+    def reduce_metrics(self, values: torch.Tensor, op: int = F.RED_AVG, weights: Optional[Sequence[float]] = None) -> torch.Tensor:
+        return values
+
+    def close(self) -> None:
+        pass
+
+
+class _SymmetricRegion:
+    """One peer-mapped allocation: local tensor + every rank's address of the same region."""
+
+    def __init__(self, local: torch.Tensor, peer_ptrs: List[int], keep: Any) -> None:
+        self.local = local
+        self.peer_ptrs = peer_ptrs
+        self.keep = keep
+        self.base = local.data_ptr()
+        self.nbytes = local.numel() * local.element_size()
+
+    def table(self, offset_bytes: int = 0):
+        arr = (ctypes.c_void_p * len(self.peer_ptrs))(*[p + offset_bytes for p in self.peer_ptrs])
+        return arr
+
+
+class TorchDistCommunicator(Communicator):
+    """Multi-process communicator over an initialised ``torch.distributed`` default group."""
+
+    def __init__(self, device: torch.device, use_p2p: Optional[bool] = None) -> None:
+        import torch.distributed as dist
+
+        if not dist.is_initialized():
+            raise RuntimeError("torch.distributed must be initialised before building a communicator")
+        self.dist = dist
+        self.rank, self.size = dist.get_rank(), dist.get_world_size()
+        self.local_rank = int(os.environ.get("LOCAL_RANK", self.rank))
+        self.device = device
+        if use_p2p is None:
+            use_p2p = os.environ.get("DET_DISABLE_P2P") != "1"
+        self.p2p = bool(use_p2p and device.type == "cuda" and self.size <= 8 and F.native_available())
+        self._regions: List[_SymmetricRegion] = []
+        self._flags: Optional[_SymmetricRegion] = None
+        self._epoch: Optional[torch.Tensor] = None
+        self._metric_region: Optional[_SymmetricRegion] = None
+        self._backend = "none"
+        if self.p2p:
+            try:
+                lib = _native.load()
+                self._flags = self._symmetric_alloc(int(lib.det_comm_flag_bytes()) // 4, torch.int32)
+                self._epoch = torch.zeros(int(lib.det_comm_epoch_bytes()) // 4, dtype=torch.int32, device=device)
+                self._metric_region = self._symmetric_alloc(4096, torch.float32)
+                self.barrier()
+            except Exception as e:  # pragma: no cover - depends on the box
+                if os.environ.get("DET_REQUIRE_P2P") == "1":
+                    raise
+                print(f"[det] peer-memory arena unavailable ({e!r}); falling back to NCCL collectives", flush=True)
+                self.p2p = False
+
+    # ---- control plane ---------------------------------------------------------------------------
+    def barrier(self) -> None:
+        if self.device.type == "cuda":
+            self.dist.barrier(device_ids=[self.device.index if self.device.index is not None else 0])
+        else:
+            self.dist.barrier()
+
+    def allgather_object(self, obj: Any) -> List[Any]:
+        out: List[Any] = [None] * self.size
+        self.dist.all_gather_object(out, obj)
+        return out
+
+    def broadcast_object(self, obj: Any, root: int = 0) -> Any:
+        box = [obj]
+        self.dist.broadcast_object_list(box, src=root)
+        return box[0]
+
+    # ---- symmetric memory --------------------------------------------------------------------------
+    def _symmetric_alloc(self, n: int, dtype: torch.dtype) -> _SymmetricRegion:
+        """Allocate the same-sized region on every rank and map every peer's copy.
+
+        Preferred: ``torch.distributed._symmetric_memory`` (cuMem + fabric/fd handle exchange; also gives
+        an NVLS multicast address when the switch supports it). Fallback: cudaMalloc + CUDA IPC handles
+        exchanged through the control plane."""
+        elem = torch.empty((), dtype=dtype).element_size()
+        if os.environ.get("DET_ARENA_BACKEND", "symm") == "symm":
+            try:
+                import torch.distributed._symmetric_memory as symm
+
+                t = symm.empty(n, dtype=dtype, device=self.device)
+                hdl = symm.rendezvous(t, self.dist.group.WORLD)
+                t.zero_()
+                ptrs = [int(p) for p in hdl.buffer_ptrs]
+                region = _SymmetricRegion(t, ptrs, hdl)
+                region.multicast_ptr = int(getattr(hdl, "multicast_ptr", 0) or 0)
+                self._backend = "torch_symmetric_memory"
+                self._regions.append(region)
+                return region
+            except Exception as e:  # pragma: no cover
+                if os.environ.get("DET_ARENA_BACKEND") == "symm":
+                    raise
+                print(f"[det] torch symmetric memory unavailable ({e!r}); using CUDA IPC arena", flush=True)
+        lib = _native.load()
+        ptr = ctypes.c_void_p()
+        _native.check(lib.det_arena_alloc(n * elem, ctypes.byref(ptr)))
+        handle = ctypes.create_string_buffer(64)
+        _native.check(lib.det_ipc_export(ptr, handle))
+        handles = self.allgather_object(bytes(handle.raw))
+        ptrs: List[int] = []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                ptrs.append(int(ptr.value))
+            else:
+                out = ctypes.c_void_p()
+                _native.check(lib.det_ipc_import(h, ctypes.byref(out)))
+                ptrs.append(int(out.value))
+        local = _tensor_from_ptr(int(ptr.value), n, dtype, self.device)
+        region = _SymmetricRegion(local, ptrs, None)
+        region.multicast_ptr = 0
+        self._backend = "cuda_ipc"
+        self._regions.append(region)
+        return region
+
+    def alloc(self, n: int, dtype: torch.dtype, kind: str, device: torch.device) -> torch.Tensor:
+        if self.p2p and kind in ("grad", "param", "state"):
+            region = self._symmetric_alloc(n, dtype)
+            return region.local
+        return torch.zeros(n, dtype=dtype, device=device)
+
+    def _region_of(self, t: torch.Tensor) -> Optional[_SymmetricRegion]:
+        p = t.data_ptr()
+        for r in self._regions:
+            if r.base <= p < r.base + r.nbytes:
+                return r
+        return None
+
+    # ---- data plane ------------------------------------------------------------------------------------
+    def allreduce_grad_bucket(self, flat_g, scale, scale_dev=None, sumsq_dev=None, found_inf_dev=None) -> bool:
+        region = self._region_of(flat_g) if self.p2p else None
+        if region is None:
+            self.dist.all_reduce(flat_g)
+            return False
+        off = flat_g.data_ptr() - region.base
+        n = flat_g.numel()
+        assert n % 4 == 0
+        mc = region.multicast_ptr + off if (region.multicast_ptr and os.environ.get("DET_DISABLE_NVLS") != "1") else None
+        _native.call("det_fused_allreduce", region.table(off), self._flags.table(), ctypes.c_void_p(mc) if mc else None,
+                     ctypes.c_void_p(self._epoch.data_ptr()), n, self.rank, self.size, float(scale),
+                     F._p(scale_dev), F._p(sumsq_dev), F._p(found_inf_dev), 0, F._stream())
+        if sumsq_dev is not None:
+            # each rank holds the sum of squares of ITS slice: finish with a tiny metric reduce
+            self._sum_scalar_inplace(sumsq_dev)
+        return True
+
+    def _sum_scalar_inplace(self, t: torch.Tensor) -> None:
+        reg = self._metric_region
+        n = t.numel()
+        reg.local[:n].copy_(t.reshape(-1))
+        _native.call("det_metric_allreduce", reg.table(), self._flags.table(), ctypes.c_void_p(self._epoch.data_ptr()),
+                     F._p(t), None, n, self.rank, self.size, F.RED_SUM, F._stream())
+
+    def allreduce_tensors(self, tensors, scale) -> None:
+        for t in tensors:
+            self.dist.all_reduce(t)
+            if scale != 1.0:
+                t.mul_(scale)
+
+    def broadcast_tensors(self, tensors, root: int = 0) -> None:
+        for t in tensors:
+            region = self._region_of(t) if self.p2p else None
+            nbytes = t.numel() * t.element_size()
+            if region is None or nbytes % 16 != 0:
+                self.dist.broadcast(t, src=root)
+                continue
+            off = t.data_ptr() - region.base
+            _native.call("det_p2p_broadcast", region.table(off), self._flags.table(),
+                         ctypes.c_void_p(self._epoch.data_ptr()), nbytes, self.rank, self.size, root, F._stream())
+
+    def reduce_metrics(self, values, op=F.RED_AVG, weights=None) -> torch.Tensor:
+        """Reduce a small fp32 vector across ranks; result valid on every rank."""
+        if self.p2p and values.is_cuda and values.numel() <= 4096:
+            reg = self._metric_region
+            n = values.numel()
+            reg.local[:n].copy_(values.reshape(-1).float())
+            out = torch.empty(n, dtype=torch.float32, device=values.device)
+            w = None
+            if weights is not None:
+                w = torch.tensor(list(weights), dtype=torch.float32, device=values.device)
+            _native.call("det_metric_allreduce", reg.table(), self._flags.table(),
+                         ctypes.c_void_p(self._epoch.data_ptr()), F._p(out), F._p(w), n, self.rank, self.size, op, F._stream())
+            return out.view_as(values)
+        v = values.float().clone()
+        if op == F.RED_AVG:
+            wsum = float(self.size)
+            if weights is not None:
+                v = v * float(weights[self.rank])
+                wsum = float(sum(weights))
+            self.dist.all_reduce(v)
+            return v / wsum
+        ops = {F.RED_SUM: self.dist.ReduceOp.SUM, F.RED_MAX: self.dist.ReduceOp.MAX, F.RED_MIN: self.dist.ReduceOp.MIN}
+        self.dist.all_reduce(v, op=ops[op])
+        return v
+
+    def describe(self) -> Dict[str, Any]:
+        return {"size": self.size, "p2p": self.p2p, "arena_backend": self._backend,
+                "nvls": bool(self._regions and getattr(self._regions[0], "multicast_ptr", 0))}
+
+
+def _tensor_from_ptr(ptr: int, n: int, dtype: torch.dtype, device: torch.device) -> torch.Tensor:
+    """Wrap raw device memory as a tensor through ``__cuda_array_interface__``."""
+    typestr = {torch.float32: "<f4", torch.int32: "<i4", torch.bfloat16: "<u2", torch.float16: "<f2"}[dtype]
+
+    class _Holder:
+        pass
+
+    h = _Holder()
+    h.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 3}
+    t = torch.as_tensor(h, device=device)
+    if dtype == torch.bfloat16:
+        t = t.view(torch.bfloat16)
+    return t
+
+
+def init_process_group_from_env(device: torch.device) -> None:
+    import torch.distributed as dist
+
+    if dist.is_initialized():
+        return
+    backend = "nccl" if device.type == "cuda" else "gloo"
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29511")
+    kwargs: Dict[str, Any] = {}
+    if device.type == "cuda":
+        kwargs["device_id"] = device
+    dist.init_process_group(backend=backend, rank=int(os.environ.get("RANK", "0")),
+                            world_size=int(os.environ.get("WORLD_SIZE", "1")), **kwargs)
+
+
+def make_communicator(device: torch.device) -> Communicator:
+    if int(os.environ.get("WORLD_SIZE", "1")) <= 1:
+        return Communicator()
+    init_process_group_from_env(device)
+    return TorchDistCommunicator(device)

@@ -1,0 +1,355 @@
+"""``PyTorchTrialContext`` — model / optimizer wrapping, backward, optimizer stepping.
+
+API parity with reference ``harness/determined/pytorch/_pytorch_context.py:38-571`` (``wrap_model``,
+``wrap_optimizer``, ``wrap_lr_scheduler``, ``configure_apex_amp``, ``backward``, ``step_optimizer``,
+``to_device``, ``is_epoch_start/end``, deprecated ``get_model/get_optimizer/get_lr_scheduler``).
+
+What is different underneath (B200-first):
+
+* no Horovod — one process per GPU, identity from the launcher; ``wrap_optimizer`` returns a
+  :class:`~determined_b200.parallel.fused_optimizer.FusedOptimizer` whose gradient bucket lives in the
+  peer-mapped symmetric arena, so ``step_optimizer`` is: fused all-reduce kernel (sum + average over ranks and
+  aggregation_frequency + loss-scale unscale + non-finite flag + grad-norm partial) → fused update kernel
+  (clip coefficient, skip-on-overflow, zero-grad, bf16 shadow refresh);
+* no apex — ``configure_apex_amp`` / ``optimizations.mixed_precision`` map to native bf16 autocast (O1/O2/O3,
+  no loss scaling needed) or fp16 with a device-resident dynamic loss scaler; the reference's restriction
+  ``aggregation_frequency == 1 and num_losses == 1`` under AMP + distributed (``:336-352``) is lifted;
+* ``native_parallel: true`` (``nn.DataParallel`` in the reference, ``:135-144``) maps onto the same
+  multi-process path with the same global-batch semantics.
+"""
+from __future__ import annotations
+
+import contextlib
+import logging
+from typing import Any, Callable, Dict, Iterable, List, Optional, Sequence, Tuple, Union
+
+import torch
+import torch.nn as nn
+
+from .._env import DistributedContext, EnvContext
+from .._train_context import TrialContext
+from ..parallel.comm import Communicator
+from ..parallel.fused_optimizer import FusedOptimizer
+from . import _callback, _data, _reducer
+from ._lr_scheduler import LRScheduler
+
+log = logging.getLogger("determined.pytorch")
+
+
+class _LossScaler:
+    """fp16 dynamic loss scaling with all state on the device (K5)."""
+
+    def __init__(self, device: torch.device, init_scale: float = 65536.0, growth: float = 2.0, backoff: float = 0.5,
+                 interval: int = 2000) -> None:
+        self.state = torch.tensor([init_scale, 0.0, 1.0 / init_scale], dtype=torch.float32, device=device)
+        self.growth, self.backoff, self.interval = growth, backoff, interval
+
+    def scale_tensor(self) -> torch.Tensor:
+        return self.state[0:1]
+
+    def state_dict(self) -> Dict[str, Any]:
+        return {"state": self.state.detach().cpu()}
+
+    def load_state_dict(self, sd: Dict[str, Any]) -> None:
+        self.state.copy_(sd["state"])
+
+
+class _Experimental:
+    """``context.experimental`` — B200-specific opt-ins that have no counterpart in the reference."""
+
+    def __init__(self, parent: "PyTorchTrialContext") -> None:
+        self._parent = parent
+        self.cuda_graphs = False
+        self.graph_warmup_batches = 3
+
+    def enable_cuda_graphs(self, warmup_batches: int = 3) -> None:
+        """Capture ``train_batch`` (forward, backward, all-reduce, optimizer) into CUDA graphs after a few eager
+        batches and replay it afterwards. Requires static shapes and a ``train_batch`` without host syncs."""
+        self.cuda_graphs = True
+        self.graph_warmup_batches = max(int(warmup_batches), 3)
+
+
+class PyTorchTrialContext(TrialContext):
+    def __init__(self, env: EnvContext, dist: Optional[DistributedContext] = None,
+                 comm: Optional[Communicator] = None) -> None:
+        super().__init__(env, dist)
+        self.comm: Communicator = comm or Communicator()
+        self.models: List[nn.Module] = []
+        self.optimizers: List[torch.optim.Optimizer] = []
+        self.lr_schedulers: List[LRScheduler] = []
+        self.reducers: Dict[str, Tuple[_reducer.MetricReducer, bool, bool]] = {}
+        self._epoch_len: Optional[int] = None
+        self._current_batch_idx: Optional[int] = None
+        self._loss_ids: Dict[int, int] = {}
+        self._last_backward_batch_idx: Optional[int] = None
+        self._main_model = nn.Module()
+        self._use_amp = False
+        self._amp_dtype: Optional[torch.dtype] = None
+        self._loss_scaler: Optional[_LossScaler] = None
+        self._scaler_divisor_applied = False
+        self.experimental = _Experimental(self)
+        self.warned_types: set = set()
+
+        opt_cfg = env.experiment_config.get_optimizations_config()
+        self.aggregation_frequency = int(opt_cfg.get("aggregation_frequency", 1))
+        self.average_aggregated_gradients = bool(opt_cfg.get("average_aggregated_gradients", True))
+        self.gradient_compression = bool(opt_cfg.get("gradient_compression", False))
+        if self.aggregation_frequency < 1:
+            raise ValueError("optimizations.aggregation_frequency must be >= 1")
+        self.device = self._init_device()
+        mp = opt_cfg.get("mixed_precision", "O0")
+        if mp != "O0":
+            self._configure_mixed_precision(mp)
+
+    # ---- device / identity -----------------------------------------------------------------------
+    def _init_device(self) -> torch.device:
+        if self.env.use_gpu and torch.cuda.is_available():
+            idx = self.distributed.get_local_rank() if self.distributed.get_size() > 1 else 0
+            idx = idx % max(torch.cuda.device_count(), 1)
+            torch.cuda.set_device(idx)
+            return torch.device("cuda", idx)
+        return torch.device("cpu")
+
+    @property
+    def n_gpus(self) -> int:
+        return len(self.env.container_gpus)
+
+    def _configure_mixed_precision(self, level: str, dtype: Optional[torch.dtype] = None) -> None:
+        if level not in ("O0", "O1", "O2", "O3"):
+            raise ValueError(f"mixed_precision must be one of O0..O3, got {level!r}")
+        if level == "O0":
+            self._use_amp = False
+            return
+        self._use_amp = True
+        self._amp_dtype = dtype or torch.bfloat16
+        if self._amp_dtype == torch.float16 and self.device.type == "cuda":
+            self._loss_scaler = _LossScaler(self.device)
+
+    @contextlib.contextmanager
+    def autocast(self):
+        """Autocast region matching the trial's mixed-precision setting (no-op for O0 or on CPU)."""
+        if self._use_amp and self.device.type == "cuda":
+            with torch.autocast("cuda", dtype=self._amp_dtype):
+                yield
+        else:
+            yield
+
+    # ---- wrapping ------------------------------------------------------------------------------------
+    def wrap_model(self, model: nn.Module) -> nn.Module:
+        """Move the model to this trial's device and register it (checkpointing, broadcast)."""
+        if not isinstance(model, nn.Module):
+            raise TypeError("wrap_model expects a torch.nn.Module")
+        model = model.to(self.device)
+        self._main_model.add_module(f"model_{len(self.models)}", model)
+        self.models.append(model)
+        return model
+
+    def wrap_optimizer(self, optimizer: torch.optim.Optimizer, backward_passes_per_step: int = 1) -> torch.optim.Optimizer:
+        """Adopt a torch optimizer. On CUDA this flattens its parameters into fp32 buckets inside the symmetric
+        arena and swaps in the fused update; elsewhere the optimizer is used as is. ``backward_passes_per_step``
+        is accepted for API compatibility (several ``backward`` calls per batch accumulate into the same
+        bucket; communication happens once, in ``step_optimizer``)."""
+        if not isinstance(optimizer, torch.optim.Optimizer):
+            raise TypeError("wrap_optimizer expects a torch.optim.Optimizer")
+        if backward_passes_per_step < 1:
+            raise ValueError("backward_passes_per_step must be >= 1")
+        if self.device.type == "cuda":
+            dev = self.device
+
+            def alloc(n: int, dtype: torch.dtype, kind: str) -> torch.Tensor:
+                return self.comm.alloc(n, dtype, kind, dev)
+
+            wrapped: torch.optim.Optimizer = FusedOptimizer(optimizer, alloc=alloc)
+        else:
+            wrapped = optimizer
+        self.optimizers.append(wrapped)
+        return wrapped
+
+    def wrap_lr_scheduler(self, lr_scheduler: Any, step_mode: LRScheduler.StepMode, frequency: int = 1) -> Any:
+        """Register a torch LR scheduler together with when the harness should step it. Returns the scheduler
+        (so ``MANUAL_STEP`` users can call ``.step()`` themselves)."""
+        opt = getattr(lr_scheduler, "optimizer", None)
+        if opt is not None and not any(opt is o or opt is getattr(o, "inner", None) for o in self.optimizers):
+            raise ValueError("wrap the optimizer with context.wrap_optimizer() before its LR scheduler")
+        wrapped = LRScheduler(lr_scheduler, step_mode, frequency)
+        self.lr_schedulers.append(wrapped)
+        return lr_scheduler
+
+    def wrap_reducer(self, reducer: Union[_reducer.MetricReducer, Callable[[List[Any]], Any]], name: Optional[str] = None,
+                     for_training: bool = True, for_validation: bool = True) -> _reducer.MetricReducer:
+        """Register a custom cross-rank metric (extension; see :class:`MetricReducer`). Call
+        ``reducer.accumulate(value)`` from ``train_batch`` / ``evaluate_batch``; the harness reduces it at the
+        end of the workload and reports it under ``name``."""
+        if not isinstance(reducer, _reducer.MetricReducer):
+            if not callable(reducer):
+                raise TypeError("reducer must be a MetricReducer or a function over the list of values")
+            reducer = _reducer.make_metric_reducer(reducer)
+        name = name or f"reducer_{len(self.reducers)}"
+        if name in self.reducers:
+            raise ValueError(f"a reducer named {name!r} is already registered")
+        self.reducers[name] = (reducer, for_training, for_validation)
+        return reducer
+
+    def configure_apex_amp(self, models: Union[nn.Module, List[nn.Module]],
+                           optimizers: Union[torch.optim.Optimizer, List[torch.optim.Optimizer]],
+                           enabled: Optional[bool] = True, opt_level: Optional[str] = "O1",
+                           cast_model_type: Optional[torch.dtype] = None, patch_torch_functions: Optional[bool] = None,
+                           keep_batchnorm_fp32: Optional[Union[bool, str]] = None,
+                           master_weights: Optional[bool] = None, loss_scale: Optional[Union[float, str]] = None,
+                           cast_model_outputs: Optional[torch.dtype] = None, num_losses: Optional[int] = 1,
+                           verbosity: Optional[int] = 1, min_loss_scale: Optional[float] = None,
+                           max_loss_scale: Optional[float] = 2.0 ** 24) -> Tuple:
+        """Same signature as the reference (which forwards to ``apex.amp.initialize``). Here it switches on
+        native mixed precision: parameters stay fp32 masters, compute runs in bf16 (or fp16 when
+        ``cast_model_type=torch.float16``, with dynamic loss scaling kept on the device). Works with any
+        ``aggregation_frequency`` and any number of losses, distributed or not."""
+        if enabled:
+            dtype = torch.float16 if cast_model_type == torch.float16 else torch.bfloat16
+            self._configure_mixed_precision(opt_level or "O1", dtype)
+            if self._loss_scaler is not None and isinstance(loss_scale, (int, float)):
+                self._loss_scaler.state[0] = float(loss_scale)
+        return models, optimizers
+
+    # ---- batch bookkeeping ---------------------------------------------------------------------------
+    def _set_current_batch(self, batch_idx: int, epoch_len: Optional[int]) -> None:
+        self._current_batch_idx = batch_idx
+        self._epoch_len = epoch_len
+
+    def current_train_batch(self) -> int:
+        if self._current_batch_idx is None:
+            raise RuntimeError("no training batch is in progress")
+        return self._current_batch_idx
+
+    def _should_communicate_and_update(self) -> bool:
+        if self._current_batch_idx is None:
+            raise RuntimeError("step_optimizer / backward called outside train_batch")
+        return (self._current_batch_idx + 1) % self.aggregation_frequency == 0
+
+    def is_epoch_start(self) -> bool:
+        if self._current_batch_idx is None:
+            raise RuntimeError("is_epoch_start() is only valid during training")
+        if self._epoch_len is None:
+            raise RuntimeError("is_epoch_start() needs records_per_epoch or a sized training loader")
+        return self._current_batch_idx % self._epoch_len == 0
+
+    def is_epoch_end(self) -> bool:
+        if self._current_batch_idx is None:
+            raise RuntimeError("is_epoch_end() is only valid during training")
+        if self._epoch_len is None:
+            raise RuntimeError("is_epoch_end() needs records_per_epoch or a sized training loader")
+        return self._current_batch_idx % self._epoch_len == self._epoch_len - 1
+
+    def to_device(self, data: _data.TorchData) -> _data.TorchData:
+        return _data.to_device(data, self.device, self.warned_types)
+
+    # ---- backward / step -------------------------------------------------------------------------------
+    def backward(self, loss: torch.Tensor, gradient: Optional[torch.Tensor] = None, retain_graph: bool = False,
+                 create_graph: bool = False) -> None:
+        """``loss.backward()`` with loss scaling when fp16 is on. Gradients accumulate into the optimizer's
+        bucket; nothing is communicated until ``step_optimizer``. May be called several times per batch."""
+        if self._loss_scaler is not None:
+            loss = loss * self._loss_scaler.scale_tensor()
+        loss.backward(gradient=gradient, retain_graph=retain_graph, create_graph=create_graph)
+
+    def _grad_divisor(self) -> float:
+        d = float(self.comm.size)
+        if self.average_aggregated_gradients:
+            d *= float(self.aggregation_frequency)
+        return d
+
+    def step_optimizer(self, optimizer: torch.optim.Optimizer,
+                       clip_grads: Optional[Callable[[Iterable[torch.Tensor]], None]] = None,
+                       auto_zero_grads: bool = True) -> None:
+        """Communicate, average, (clip), update, (zero) — only on batches that close an aggregation window.
+
+        ``clip_grads`` receives the parameters with unscaled, averaged gradients, as in the reference
+        (``_pytorch_context.py:524-536``). Passing ``det.pytorch.ClipGradsL2Norm(x)`` keeps the whole step on the
+        fused path (norm computed by the all-reduce / bucket kernels, coefficient folded into the update)."""
+        if optimizer not in self.optimizers:
+            raise ValueError("step_optimizer() got an optimizer that was not wrapped with wrap_optimizer()")
+        if not self._should_communicate_and_update():
+            return
+        divisor = self._grad_divisor()
+        fused = isinstance(optimizer, FusedOptimizer) and optimizer.fused
+        max_norm = 0.0
+        slow_clip = None
+        if clip_grads is not None:
+            if isinstance(clip_grads, _callback.ClipGradsL2Norm) and fused:
+                max_norm = clip_grads.clip_value
+            else:
+                slow_clip = clip_grads
+        if fused:
+            self._step_fused(optimizer, divisor, max_norm, slow_clip, auto_zero_grads)
+        else:
+            self._step_plain(optimizer, divisor, slow_clip, auto_zero_grads)
+
+    def _step_fused(self, opt: FusedOptimizer, divisor: float, max_norm: float, slow_clip, auto_zero: bool) -> None:
+        scaler = self._loss_scaler
+        inv_scale_dev = scaler.state[2:3] if scaler is not None else None  # 1/(loss_scale) maintained on device
+        if scaler is not None:
+            # state[2] holds 1/(scale*divisor_ref); keep divisor_ref == 1 and fold the divisor on the host side
+            pass
+        found_inf = opt.found_inf_dev if scaler is not None else None
+        applied_all = True
+        for g in opt.grad_buckets():
+            applied = self.comm.allreduce_grad_bucket(g, 1.0 / divisor, scale_dev=inv_scale_dev, found_inf_dev=found_inf)
+            applied_all = applied_all and applied
+        if applied_all and self.comm.size > 1:
+            opt.grad_scale_dev.fill_(1.0)
+        else:
+            # single process (or NCCL fallback): averaging / unscale rides along in the update kernel
+            if inv_scale_dev is not None:
+                torch.mul(inv_scale_dev, 1.0 / divisor, out=opt.grad_scale_dev)
+            else:
+                opt.grad_scale_dev.fill_(1.0 / divisor)
+        if slow_clip is not None:
+            # arbitrary user callback: materialise unscaled, averaged gradients first
+            for g in opt.grad_buckets():
+                g.mul_(opt.grad_scale_dev)
+            opt.grad_scale_dev.fill_(1.0)
+            slow_clip([p for grp in opt.param_groups for p in grp["params"]])
+        if scaler is not None and found_inf is not None and self.comm.size <= 1:
+            from ..ops import functional as F
+
+            sc = opt._scratch
+            sc[0:1].zero_()
+            for g in opt.grad_buckets():
+                F.grad_sumsq_finite(g, opt.grad_scale_dev, sc[0:1], found_inf)
+        opt.step(max_grad_norm=max_norm, zero_grad=auto_zero)
+        if scaler is not None:
+            from ..ops import functional as F
+
+            F.loss_scale_update(scaler.state, opt.found_inf_dev, scaler.growth, scaler.backoff, scaler.interval, 1.0)
+
+    def _step_plain(self, opt: torch.optim.Optimizer, divisor: float, slow_clip, auto_zero: bool) -> None:
+        params = [p for grp in opt.param_groups for p in grp["params"] if p.grad is not None]
+        if self.comm.size > 1:
+            self.comm.allreduce_tensors([p.grad for p in params], 1.0 / divisor)
+        elif divisor != 1.0:
+            for p in params:
+                p.grad.div_(divisor)
+        if self._loss_scaler is not None:
+            inv = 1.0 / float(self._loss_scaler.state[0])
+            for p in params:
+                p.grad.mul_(inv)
+        if slow_clip is not None:
+            slow_clip([p for grp in opt.param_groups for p in grp["params"]])
+        opt.step()
+        if auto_zero:
+            opt.zero_grad()
+
+    # ---- deprecated single-object getters ------------------------------------------------------------------
+    def get_model(self) -> nn.Module:
+        if len(self.models) != 1:
+            raise RuntimeError("get_model() requires exactly one wrapped model")
+        return self.models[0]
+
+    def get_optimizer(self) -> torch.optim.Optimizer:
+        if len(self.optimizers) != 1:
+            raise RuntimeError("get_optimizer() requires exactly one wrapped optimizer")
+        return self.optimizers[0]
+
+    def get_lr_scheduler(self) -> Optional[LRScheduler]:
+        if len(self.lr_schedulers) > 1:
+            raise RuntimeError("get_lr_scheduler() requires at most one wrapped LR scheduler")
+        return self.lr_schedulers[0] if self.lr_schedulers else None
