@@ -28,6 +28,10 @@ from ..ops import functional as F
 
 _ALIGN = 64  # elements; keeps every parameter 256-byte (fp32) / 128-byte (bf16) aligned
 
+# Callables notified with the optimizer after every fused ``step()`` — the CUDA-graph runner uses this to learn
+# which optimizers a captured batch stepped, so it can refresh their host-side hyper-parameters on replay.
+STEP_OBSERVERS: List[Callable[["FusedOptimizer"], None]] = []
+
 
 def _variant_of(opt: torch.optim.Optimizer) -> Optional[int]:
     name = type(opt).__name__
@@ -190,6 +194,8 @@ class FusedOptimizer(torch.optim.Optimizer):
             return loss
         self.host_prepare()
         self.device_step(max_grad_norm=max_grad_norm, zero_grad=zero_grad)
+        for observer in STEP_OBSERVERS:
+            observer(self)
         return loss
 
     # ---- state dict in stock torch format -----------------------------------------------------------

@@ -1,0 +1,265 @@
+"""GPU numerics tests: every sm_100a kernel against a plain PyTorch fp32 statement of the same op."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _F():
+    from determined_b200.ops import _native
+    from determined_b200.ops import functional as F
+
+    _native.load(build_if_missing=False)  # fail loudly if the extension is missing on a GPU box
+    return F
+
+
+def rel(out, ref):
+    return ((out.float() - ref.float()).abs().max() / ref.float().abs().max().clamp_min(1e-6)).item()
+
+
+@pytest.mark.parametrize("a_mn", [False, True])
+@pytest.mark.parametrize("b_mn", [False, True])
+@pytest.mark.parametrize("bn", [64, 128, 256])
+def test_gemm_layouts(a_mn, b_mn, bn):
+    F = _F()
+    torch.manual_seed(1)
+    M, N, K = 1000, 776, 200
+    A = torch.randn(M, K, device="cuda").bfloat16()
+    B = torch.randn(N, K, device="cuda").bfloat16()
+    ref = A.float() @ B.float().t()
+    As = A.t().contiguous() if a_mn else A
+    Bs = B.t().contiguous() if b_mn else B
+    C = torch.zeros(M, N, device="cuda", dtype=torch.bfloat16)
+    F.gemm(As, Bs, C, M, N, K, a_mn=a_mn, b_mn=b_mn, force_bn=bn)
+    assert rel(C, ref) < 1.5e-2
+
+
+def test_gemm_epilogues_and_splitk():
+    F = _F()
+    torch.manual_seed(2)
+    M, N, K = 512, 768, 256
+    A = torch.randn(M, K, device="cuda").bfloat16()
+    B = (torch.randn(N, K, device="cuda") * 0.05).bfloat16()
+    bias = torch.randn(N, device="cuda")
+    acc = A.float() @ B.float().t()
+    C = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    Z = torch.empty_like(C)
+    F.gemm(A, B, C, M, N, K, epi=F.EPI_BIAS_GELU, bias=bias, aux_out=Z)
+    assert rel(C, torch.nn.functional.gelu(acc + bias)) < 1.5e-2 and rel(Z, acc + bias) < 1.5e-2
+    zf = Z.float().requires_grad_(True)
+    torch.nn.functional.gelu(zf).sum().backward()
+    F.gemm(A, B, C, M, N, K, epi=F.EPI_DGELU, aux_in=Z)
+    assert rel(C, acc * zf.grad) < 2e-2
+    R = torch.randn(M, N, device="cuda").bfloat16()
+    F.gemm(A, B, C, M, N, K, epi=F.EPI_BIAS_RESID, bias=bias, aux_in=R)
+    assert rel(C, acc + bias + R.float()) < 1.5e-2
+    K2 = 4096
+    dY = torch.randn(K2, 768, device="cuda").bfloat16()
+    X = torch.randn(K2, 512, device="cuda").bfloat16()
+    G = torch.ones(768, 512, device="cuda")
+    F.gemm(dY, X, G, 768, 512, K2, a_mn=True, b_mn=True, out_mode=F.OUT_F32_ATOMIC_ADD)
+    assert rel(G - 1.0, dY.float().t() @ X.float()) < 1e-3
+
+
+@pytest.mark.parametrize("B,S,H,use_mask", [(2, 128, 2, False), (3, 128, 12, True), (2, 77, 3, True)])
+def test_attention_fwd_bwd(B, S, H, use_mask):
+    F = _F()
+    torch.manual_seed(3)
+    hid = H * 64
+    qkv = (torch.randn(B * S, 3 * hid, device="cuda") * 0.5).bfloat16()
+    mask = None
+    if use_mask:
+        mask = torch.zeros(B, S, device="cuda")
+        mask[:, S - S // 4:] = -10000.0
+    ctx, lse = F.attention_fwd(qkv, mask, B, S, H, 0.0, 0)
+    q, k, v = [t.float().view(B, S, H, 64).transpose(1, 2).requires_grad_(True) for t in qkv.split(hid, dim=1)]
+    sc = q @ k.transpose(-1, -2) * 0.125
+    if mask is not None:
+        sc = sc + mask[:, None, None, :]
+    o = torch.softmax(sc, dim=-1) @ v
+    ref = o.transpose(1, 2).reshape(B * S, hid)
+    assert rel(ctx, ref) < 2e-2
+    assert rel(lse, torch.logsumexp(sc, dim=-1)) < 1e-2
+    dctx = (torch.randn(B * S, hid, device="cuda") * 0.5).bfloat16()
+    dqkv = F.attention_bwd(qkv, dctx, mask, lse, B, S, H, 0.0, 0)
+    ref.backward(dctx.float())
+    ref_d = torch.cat([t.grad.transpose(1, 2).reshape(B * S, hid) for t in (q, k, v)], dim=1)
+    for a, b in zip(dqkv.split(hid, dim=1), ref_d.split(hid, dim=1)):
+        assert rel(a, b) < 3e-2
+
+
+def test_attention_dropout_adjoint():
+    F = _F()
+    torch.manual_seed(4)
+    B, S, H = 2, 128, 2
+    hid = H * 64
+    qkv = (torch.randn(B * S, 3 * hid, device="cuda") * 0.5).bfloat16()
+    F.set_step_seed(11)
+    c1, lse = F.attention_fwd(qkv, None, B, S, H, 0.1, 55)
+    dctx = torch.randn_like(c1)
+    dV = F.attention_bwd(qkv, dctx, None, lse, B, S, H, 0.1, 55)[:, 2 * hid:].float()
+    qkv2 = qkv.clone()
+    pert = (torch.randn(B * S, hid, device="cuda") * 0.25).bfloat16()
+    qkv2[:, 2 * hid:] = pert
+    c2, _ = F.attention_fwd(qkv2, None, B, S, H, 0.1, 55)
+    lhs = (c2.float() * dctx.float()).sum().item()
+    rhs = (dV * pert.float()).sum().item()
+    assert abs(lhs - rhs) / max(abs(lhs), 1e-3) < 3e-2
+
+
+@pytest.mark.parametrize("H", [256, 768, 1024])
+def test_layernorm(H):
+    F = _F()
+    torch.manual_seed(5)
+    T = 1000
+    x = torch.randn(T, H, device="cuda").bfloat16()
+    g = torch.randn(H, device="cuda") * 0.1 + 1.0
+    b = torch.randn(H, device="cuda") * 0.1
+    y, mean, rstd = F.layernorm_fwd(x, g, b, 1e-12)
+    xf, gf, bf = x.float().requires_grad_(True), g.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    ref = torch.nn.functional.layer_norm(xf, (H,), gf, bf, 1e-12)
+    assert rel(y, ref) < 1e-2
+    dy = torch.randn(T, H, device="cuda").bfloat16()
+    dg, db = torch.zeros(H, device="cuda"), torch.zeros(H, device="cuda")
+    dx, _ = F.layernorm_bwd(dy, x, g, mean, rstd, dg, db)
+    ref.backward(dy.float())
+    assert rel(dx, xf.grad) < 1.5e-2 and rel(dg, gf.grad) < 1e-2 and rel(db, bf.grad) < 1e-2
+
+
+def test_dropout_mask_consistency_gemm_vs_layernorm_bwd():
+    F = _F()
+    T, H = 512, 768
+    F.set_step_seed(3)
+    A = torch.randn(T, 64, device="cuda").bfloat16()
+    W = torch.randn(H, 64, device="cuda").bfloat16()
+    R = torch.zeros(T, H, device="cuda").bfloat16()
+    C = torch.empty(T, H, device="cuda", dtype=torch.bfloat16)
+    F.gemm(A, W, C, T, H, 64, epi=F.EPI_BIAS_RESID, aux_in=R, dropout_p=0.25, seed=99)
+    x = torch.randn(T, H, device="cuda").bfloat16()
+    g, b = torch.ones(H, device="cuda"), torch.zeros(H, device="cuda")
+    _, mean, rstd = F.layernorm_fwd(x, g, b, 1e-12)
+    dy = torch.randn(T, H, device="cuda").bfloat16()
+    dx, dxm = F.layernorm_bwd(dy, x, g, mean, rstd, None, None, want_masked=True, out_dropout_p=0.25, out_seed=99)
+    assert ((C.float() != 0) != (dxm.float() != 0)).float().mean().item() < 2e-3
+
+
+def test_embedding_softmax_colsum_smallgemm():
+    F = _F()
+    torch.manual_seed(6)
+    V, S, Bn, H = 1000, 128, 4, 768
+    word, pos, typ = torch.randn(V, H, device="cuda"), torch.randn(512, H, device="cuda"), torch.randn(2, H, device="cuda")
+    ids = torch.randint(0, V, (Bn * S,), device="cuda")
+    tts = torch.randint(0, 2, (Bn * S,), device="cuda")
+    posidx = torch.arange(Bn * S, device="cuda") % S
+    assert rel(F.embed_gather(ids, tts, word, pos, typ, S), word[ids] + pos[posidx] + typ[tts]) < 1e-2
+    de = torch.randn(Bn * S, H, device="cuda").bfloat16()
+    dw, dp, dt = torch.zeros_like(word), torch.zeros_like(pos), torch.zeros_like(typ)
+    F.embed_scatter(ids, tts, de, dw, dp, dt, S)
+    assert rel(dw, torch.zeros_like(word).index_add_(0, ids, de.float())) < 1e-4
+    assert rel(dp, torch.zeros_like(pos).index_add_(0, posidx, de.float())) < 1e-4
+    assert rel(dt, torch.zeros_like(typ).index_add_(0, tts, de.float())) < 1e-3
+    logits = torch.randn(48, 10, device="cuda")
+    labels = torch.randint(0, 10, (48,), device="cuda")
+    loss, dl = F.softmax_ce(logits, labels, 1.0 / 48)
+    lf = logits.clone().requires_grad_(True)
+    rl = torch.nn.functional.cross_entropy(lf, labels, reduction="none")
+    rl.mean().backward()
+    assert rel(loss, rl) < 1e-5 and rel(dl, lf.grad) < 1e-4
+    x = torch.randn(3000, 2304, device="cuda").bfloat16()
+    out = torch.ones(2304, device="cuda")
+    F.colsum_accum(x, out)
+    assert rel(out - 1.0, x.float().sum(0)) < 1e-3
+    G = torch.ones(2, 768, device="cuda")
+    dlog, pooled = torch.randn(48, 2, device="cuda"), torch.randn(48, 768, device="cuda").bfloat16()
+    F.gemm_small(dlog, pooled, G, 2, 768, 48, (1, 2), (1, 768), (768, 1), accumulate=True)
+    assert rel(G - 1.0, dlog.t() @ pooled.float()) < 1e-4
+
+
+@pytest.mark.parametrize("name", ["adam", "adamw", "sgd", "rmsprop", "adadelta"])
+def test_fused_optimizers_match_torch(name):
+    F = _F()
+    torch.manual_seed(7)
+    n = 100003 * 4
+    variant = {"adam": F.OPT_ADAM, "adamw": F.OPT_ADAMW, "sgd": F.OPT_SGD, "rmsprop": F.OPT_RMSPROP, "adadelta": F.OPT_ADADELTA}[name]
+    p0 = torch.randn(n, device="cuda")
+    ref_p = p0.clone().requires_grad_(True)
+    opt = {"adam": lambda: torch.optim.Adam([ref_p], lr=1e-2, weight_decay=0.01),
+           "adamw": lambda: torch.optim.AdamW([ref_p], lr=1e-2, weight_decay=0.01),
+           "sgd": lambda: torch.optim.SGD([ref_p], lr=1e-2, momentum=0.9, weight_decay=0.01),
+           "rmsprop": lambda: torch.optim.RMSprop([ref_p], lr=1e-2, alpha=0.9, eps=1e-8),
+           "adadelta": lambda: torch.optim.Adadelta([ref_p], lr=1.0, rho=0.9, eps=1e-6)}[name]()
+    p = p0.clone()
+    s1, s2 = torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    shadow = torch.empty(n, device="cuda", dtype=torch.bfloat16)
+    gs = torch.full((1,), 0.5, device="cuda")
+    for step in range(1, 4):
+        g = torch.randn(n, device="cuda")
+        ref_p.grad = (g * 0.5).clone()
+        opt.step()
+        hp = torch.zeros(12)
+        if name in ("adam", "adamw"):
+            hp[:7] = torch.tensor([1e-2, 0.9, 0.999, 1e-8, 0.01, 1 - 0.9 ** step, 1 - 0.999 ** step])
+        elif name == "sgd":
+            hp[:9] = torch.tensor([1e-2, 0.9, 0.0, 0.0, 0.01, 0, 0, 0.0, 1.0 if step == 1 else 0.0])
+        elif name == "rmsprop":
+            hp[:5] = torch.tensor([1e-2, 0.9, 0.0, 1e-8, 0.0])
+        else:
+            hp[:5] = torch.tensor([1.0, 0.9, 0.0, 1e-6, 0.0])
+        grad = g.clone()
+        F.fused_optimizer_step(variant, p, grad, s1, s2, shadow, hp.cuda(), gs, None, True)
+        assert grad.abs().max().item() == 0.0
+    assert rel(p, ref_p.detach()) < 2e-5 and rel(shadow, p) < 5e-3
+
+
+def test_grad_norm_clip_and_loss_scale_state_machine():
+    F = _F()
+    g = torch.randn(1 << 20, device="cuda")
+    ss = torch.zeros(1, device="cuda")
+    fi = torch.zeros(1, dtype=torch.int32, device="cuda")
+    F.grad_sumsq_finite(g, None, ss, fi)
+    assert abs(ss.item() - g.double().pow(2).sum().item()) / g.double().pow(2).sum().item() < 1e-4 and fi.item() == 0
+    out2 = torch.zeros(2, device="cuda")
+    F.clip_coef(ss, 1.0, None, out2)
+    assert out2[0].item() == pytest.approx(1.0 / g.norm().item(), rel=1e-3)
+    g[5] = float("inf")
+    F.grad_sumsq_finite(g, None, ss, fi)
+    assert fi.item() == 1
+    st = torch.tensor([65536.0, 0.0, 0.0], device="cuda")
+    F.loss_scale_update(st, fi, 2.0, 0.5, 2000, 1.0)
+    assert st[0].item() == 32768.0 and fi.item() == 0
+
+
+def test_bert_fused_matches_cpu_reference():
+    from determined_b200.models.bert import BertConfig, BertForSequenceClassification
+
+    _F()
+    torch.manual_seed(0)
+    cfg = BertConfig(num_hidden_layers=2, hidden_dropout_prob=0.0, attention_probs_dropout_prob=0.0, vocab_size=1000)
+    ref = BertForSequenceClassification(cfg)
+    gpu = BertForSequenceClassification(cfg)
+    gpu.load_state_dict(ref.state_dict())
+    gpu.cuda()
+    B, S = 4, 128
+    ids = torch.randint(0, 1000, (B, S))
+    am = torch.ones(B, S, dtype=torch.long)
+    am[:, 100:] = 0
+    tt = torch.randint(0, 2, (B, S))
+    y = torch.randint(0, 2, (B,))
+    loss_r, _ = ref(ids, am, tt, y)
+    loss_r.backward()
+    loss_g, _ = gpu(ids.cuda(), am.cuda(), tt.cuda(), y.cuda())
+    loss_g.backward()
+    assert abs(loss_r.item() - loss_g.item()) < 2e-2
+    for (n, pr), (_, pg) in zip(ref.named_parameters(), gpu.named_parameters()):
+        if n.endswith("_anchor"):
+            continue
+        cos = torch.nn.functional.cosine_similarity(pr.grad.flatten(), pg.grad.cpu().flatten(), dim=0).item()
+        assert cos > 0.995, (n, cos)
+
+
+def test_graft_smoke():
+    import __graft_entry__ as ge
+
+    ge.smoke()
