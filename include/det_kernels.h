@@ -1,0 +1,97 @@
+/* det_kernels.h — C ABI of libdet_kernels.so (hand-written sm_100a kernels).
+ *
+ * Every function returns 0 on success; on failure det_last_error() holds a message (thread-local).
+ * Pointers are device pointers unless a parameter is documented as a host array. Kernels are enqueued on
+ * `stream` and never synchronise. bf16 tensors are row-major with the given leading dimension (elements).
+ * Reference citations say which library call of the reference's stack (PyTorch 1.4 + Horovod/NCCL + apex;
+ * the reference repository itself contains no GPU code) each entry point replaces.
+ */
+#ifndef DET_KERNELS_H_
+#define DET_KERNELS_H_
+
+#include <cuda_runtime_api.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* det_last_error(void);
+int det_kernels_abi_version(void);
+
+/* ---- tensor-core GEMM (tcgen05 + TMEM + TMA) -------------------------------------------------------------
+ * C[M,N] = epilogue(alpha * A[M,K] B[N,K]^T). a_mn/b_mn: 0 = K-major ([M,K] / [N,K] storage), 1 = MN-major
+ * ([K,M] / [K,N] storage). out_mode: 0 bf16, 1 fp32, 2 fp32 atomic accumulate (split-K allowed).
+ * epi: 0 none, 1 +bias, 2 +bias then GELU (pre-activation to aux_out), 3 *gelu'(aux_in), 4 dropout(+bias)+aux_in.
+ * Replaces torch.addmm / cuBLAS behind nn.Linear (reference: examples/nlp/bert_glue_pytorch/model_def.py:60-68). */
+int det_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int a_mn, int b_mn, long long lda,
+                  long long ldb, long long ldc, int out_mode, int epi, float alpha, const float* bias,
+                  const void* aux_in, void* aux_out, long long ld_aux, float dropout_p, unsigned int dropout_seed,
+                  const unsigned int* dropout_seed_dev, int splitk, int force_bn, cudaStream_t stream);
+
+/* Strided CUDA-core GEMM for tiny heads (pooler / classifier): C[m,n] (+)= act(alpha*sum_k A[m,k]B[n,k]+bias[n]). */
+int det_gemm_small(const void* A, const void* B, void* C, int M, int N, int K, long long sam, long long sak,
+                   long long sbn, long long sbk, long long scm, long long scn, int a_f32, int b_f32, int c_f32,
+                   const float* bias, int act, float alpha, int accumulate, cudaStream_t stream);
+
+/* ---- fused self-attention, seq <= 128, head_dim 64 (reference: HF BertSelfAttention via model_def.py:60) --- */
+int det_attention_fwd(const void* qkv, const float* mask, void* ctx, float* lse, int B, int S, int H,
+                      float dropout_p, unsigned int seed, const unsigned int* seed_dev, cudaStream_t stream);
+int det_attention_bwd(const void* qkv, const void* dctx, const float* mask, const float* lse, void* dqkv, int B,
+                      int S, int H, float dropout_p, unsigned int seed, const unsigned int* seed_dev,
+                      cudaStream_t stream);
+
+/* ---- LayerNorm / reductions / embeddings / loss (reference: torch.nn.LayerNorm, Embedding, CrossEntropyLoss) */
+int det_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
+                      int T, int H, float eps, float dropout_p, unsigned int seed, const unsigned int* seed_dev,
+                      cudaStream_t stream);
+int det_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
+                      void* dx, void* dx_masked, float* dgamma, float* dbeta, int T, int H, float in_dropout_p,
+                      unsigned int in_seed, float out_dropout_p, unsigned int out_seed,
+                      const unsigned int* seed_dev, cudaStream_t stream);
+int det_colsum_bf16(const void* x, float* out, int T, int N, long long ld, cudaStream_t stream);
+int det_colsum_select_bf16(const void* x, const long long* sel, long long sel_value, float* out, int T, int N,
+                           long long ld, cudaStream_t stream);
+int det_embed_gather(const long long* ids, const long long* type_ids, const float* word, const float* pos,
+                     const float* type, void* out, int T, int S, int H, cudaStream_t stream);
+int det_embed_scatter(const long long* ids, const long long* type_ids, const void* de, float* dword, float* dpos,
+                      float* dtype, int T, int S, int H, cudaStream_t stream);
+int det_softmax_ce(const float* logits, const long long* labels, float* loss, float* dlogits, int B, int C,
+                   float gscale, cudaStream_t stream);
+int det_cast_f32_bf16(const float* in, void* out, long long n, cudaStream_t stream);
+
+/* ---- fused optimizers on flat buckets (reference: optimizer.step()/zero_grad()/_average_gradients/clip_grads,
+ *      harness/determined/pytorch/_pytorch_context.py:470-545; apex.amp loss scaling :444-462) -------------
+ * variant: 0 Adam, 1 AdamW, 2 SGD(momentum), 3 RMSprop, 4 Adadelta. hyper_dev: 12 fp32 (see fused_optim.cu). */
+int det_fused_optimizer_step(int variant, float* param, float* grad, float* state1, float* state2,
+                             void* shadow_bf16, long long n, const float* hyper_dev, const float* grad_scale_dev,
+                             const int* found_inf_dev, int zero_grad, cudaStream_t stream);
+/* sumsq_dev (+=) and found_inf_dev (set) are accumulators the CALLER allocates and clears. */
+int det_grad_sumsq_finite(const float* grad, long long n, const float* grad_scale_dev, float* sumsq_dev,
+                          int* found_inf_dev, cudaStream_t stream);
+int det_clip_coef(const float* sumsq_dev, float max_norm, const float* base_scale_dev, float* out2_dev,
+                  cudaStream_t stream);
+int det_loss_scale_update(float* state3_dev, int* found_inf_dev, float growth, float backoff, int growth_interval,
+                          float divisor, cudaStream_t stream);
+
+/* ---- in-kernel collectives over NVLink peer memory (reference: Horovod/NCCL allreduce + broadcast,
+ *      _pytorch_context.py:192-198, _pytorch_trial.py:71-73; ZMQ metric gather _pytorch_trial.py:292-335) -----
+ * peer_bufs / peer_flags are HOST arrays of `world` device pointers (this rank's mapping of every rank). */
+long long det_comm_flag_bytes(void);
+long long det_comm_epoch_bytes(void);
+int det_fused_allreduce(void* const* peer_bufs, void* const* peer_flags, void* mc_ptr, void* epoch_dev,
+                        long long n_f32, int rank, int world, float scale, const float* scale_dev,
+                        float* sumsq_dev, int* found_inf_dev, int max_blocks, cudaStream_t stream);
+int det_p2p_broadcast(void* const* peer_bufs, void* const* peer_flags, void* epoch_dev, long long nbytes, int rank,
+                      int world, int root, cudaStream_t stream);
+int det_metric_allreduce(void* const* peer_bufs, void* const* peer_flags, void* epoch_dev, float* out_dev,
+                         const float* weights_dev, int n, int rank, int world, int op, cudaStream_t stream);
+int det_arena_alloc(long long bytes, void** out);
+int det_arena_free(void* p);
+int det_ipc_export(void* p, unsigned char* handle64);
+int det_ipc_import(const unsigned char* handle64, void** out);
+int det_ipc_close(void* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DET_KERNELS_H_ */
