@@ -70,6 +70,16 @@ int det_grad_sumsq_finite(const float* grad, long long n, const float* grad_scal
                           int* found_inf_dev, cudaStream_t stream);
 int det_clip_coef(const float* sumsq_dev, float max_norm, const float* base_scale_dev, float* out2_dev,
                   cudaStream_t stream);
+/* Gradient L2 norm + non-finite flag for callers that cannot allocate device memory (a hook inside a trainer
+ * whose memory is all held by the framework's allocator; a C plugin called inside the step loop). Same math as
+ * det_grad_sumsq_finite, but the scratch is a fixed ~256 KB array inside the library (held by every GPU that
+ * loads it), so n is limited to det_grad_norm_noalloc_max_elems() = 2^30 and larger inputs are refused.
+ * out2_dev[0] = norm, out2_dev[1] = norm^2; found_inf_out_dev (nullable) = 0/1. The first call on a device
+ * resolves the array's address: make it before any stream capture. Calls on one device share the array and
+ * must not overlap on the GPU. Allocates nothing. No counterpart in the reference. */
+long long det_grad_norm_noalloc_max_elems(void);
+int det_grad_norm_noalloc(const float* grad, long long n, const float* grad_scale_dev, float* out2_dev,
+                          int* found_inf_out_dev, cudaStream_t stream);
 int det_loss_scale_update(float* state3_dev, int* found_inf_dev, float growth, float backoff, int growth_interval,
                           float divisor, cudaStream_t stream);
 
