@@ -1,0 +1,128 @@
+"""Multi-GPU check of the peer-memory collectives (run under torch.distributed.run, one rank per GPU):
+fused all-reduce (scale + sumsq + found_inf) vs NCCL, broadcast, metric reduce, and bandwidth timing."""
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from determined_b200.ops import functional as F  # noqa: E402
+from determined_b200.parallel.comm import make_communicator  # noqa: E402
+
+
+def main():
+    rank, local = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    comm = make_communicator(dev)
+    world = comm.size
+    ok = True
+    if rank == 0:
+        print("comm:", comm.describe(), flush=True)
+    results = {}
+    for n in (4096, 1 << 20, 25 * (1 << 20) + 64):
+        torch.manual_seed(100 + rank)
+        g = comm.alloc(n, torch.float32, "grad", dev)
+        g.copy_(torch.randn(n, device=dev))
+        ref = g.clone()
+        dist.all_reduce(ref)
+        ref *= 0.125
+        sumsq = torch.zeros(1, device=dev)
+        finf = torch.zeros(1, dtype=torch.int32, device=dev)
+        applied = comm.allreduce_grad_bucket(g, 0.125, sumsq_dev=sumsq, found_inf_dev=finf)
+        torch.cuda.synchronize()
+        err = ((g - ref).abs().max() / ref.abs().max()).item()
+        ss_ref = ref.double().pow(2).sum().item()
+        ss_err = abs(sumsq.item() - ss_ref) / ss_ref
+        good = applied and err < 1e-5 and ss_err < 1e-3 and finf.item() == 0
+        ok &= good
+        if rank == 0:
+            print(f"{'PASS' if good else 'FAIL'} allreduce n={n} applied={applied} err={err:.2e} sumsq_err={ss_err:.2e}", flush=True)
+        # non-finite propagation
+        g.copy_(torch.randn(n, device=dev))
+        if rank == world - 1:
+            g[n // 2] = float("nan")
+        finf.zero_()
+        comm.allreduce_grad_bucket(g, 1.0, found_inf_dev=finf)
+        torch.cuda.synchronize()
+        flags = comm.allgather_object(int(finf.item()))
+        # the owner of the slice containing n//2 must have seen it
+        good = sum(flags) >= 1
+        ok &= good
+        if rank == 0:
+            print(f"{'PASS' if good else 'FAIL'} allreduce found_inf flags={flags}", flush=True)
+    # broadcast
+    p = comm.alloc(1 << 20, torch.float32, "param", dev)
+    p.fill_(float(rank + 1))
+    comm.broadcast_tensors([p], root=0)
+    torch.cuda.synchronize()
+    good = bool((p == 1.0).all().item())
+    ok &= good
+    if rank == 0:
+        print(f"{'PASS' if good else 'FAIL'} broadcast", flush=True)
+    # metric reduce
+    v = torch.tensor([float(rank), float(rank) * 2 + 1, -float(rank)], device=dev)
+    avg = comm.reduce_metrics(v, F.RED_AVG)
+    mx = comm.reduce_metrics(v, F.RED_MAX)
+    wavg = comm.reduce_metrics(v, F.RED_AVG, weights=[float(r + 1) for r in range(world)])
+    torch.cuda.synchronize()
+    exp_avg = sum(range(world)) / world
+    wsum = sum(r + 1 for r in range(world))
+    exp_w = sum(r * (r + 1) for r in range(world)) / wsum
+    good = abs(avg[0].item() - exp_avg) < 1e-5 and abs(mx[0].item() - (world - 1)) < 1e-6 and abs(wavg[0].item() - exp_w) < 1e-5
+    ok &= good
+    if rank == 0:
+        print(f"{'PASS' if good else 'FAIL'} metric reduce avg={avg.tolist()} max={mx.tolist()} wavg={wavg.tolist()}", flush=True)
+
+    # timing: BERT-base sized bucket (110M fp32 = 440 MB) fused vs NCCL
+    n = 110 * (1 << 20)
+    g = comm.alloc(n, torch.float32, "grad", dev)
+    g.normal_()
+    nccl_buf = torch.randn(n, device=dev)
+
+    def timeit(fn, iters=10):
+        for _ in range(3):
+            fn()
+        dist.barrier(device_ids=[local])
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / iters], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item()
+
+    sumsq = torch.zeros(1, device=dev)
+    finf = torch.zeros(1, dtype=torch.int32, device=dev)
+    t_fused = timeit(lambda: comm.allreduce_grad_bucket(g, 1.0 / world, sumsq_dev=sumsq, found_inf_dev=finf))
+
+    def nccl_path():
+        dist.all_reduce(nccl_buf)
+        nccl_buf.mul_(1.0 / world)
+        torch.isfinite(nccl_buf).all()
+        nccl_buf.pow(2).sum()
+
+    t_nccl = timeit(nccl_path)
+    t_nccl_only = timeit(lambda: dist.all_reduce(nccl_buf))
+    bytes_moved = 2 * (world - 1) / world * n * 4
+    results = {"world": world, "bucket_mb": n * 4 / 1e6, "fused_ms": round(t_fused, 3), "nccl_allreduce_only_ms": round(t_nccl_only, 3),
+               "nccl_plus_scale_finite_norm_ms": round(t_nccl, 3), "fused_busbw_gbs": round(bytes_moved / t_fused / 1e6, 1),
+               "nccl_busbw_gbs": round(bytes_moved / t_nccl_only / 1e6, 1), "comm": comm.describe()}
+    if rank == 0:
+        print(json.dumps(results), flush=True)
+        os.makedirs("gpurun_out", exist_ok=True)
+        with open(f"gpurun_out/comm_timing_w{world}.json", "w") as f:
+            json.dump(results, f, indent=1)
+        print("SUMMARY", "PASS" if ok else "FAIL", flush=True)
+    dist.barrier(device_ids=[local])
+    dist.destroy_process_group()
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()
