@@ -1,0 +1,218 @@
+// agent.hpp — node-agent machinery: device detection (nvidia-smi, CPU fallback, artificial slots for tests), a
+// process-based "container" manager (fork/exec per task with injected DET_* environment and GPU pinning through
+// CUDA_VISIBLE_DEVICES, stdout/stderr capture with [rank=N] parsing, signal / kill, state reporting
+// Assigned→Pulling→Starting→Running→Terminated), and an HTTP readiness checker.
+// Parity: reference agent/internal/{detect.go:20-115, nvidia.go:17-41, containers.go:145-213, container.go:29-238,
+// docker.go:28-314, fluent.go (log shipping), check.go:20-112}. Docker is replaced by plain processes: on one
+// 8-GPU box the isolation unit is the process + its GPU mask, which removes image pulls and container start-up from
+// the trial launch path.
+#pragma once
+#include <fcntl.h>
+#include <signal.h>
+#include <sys/types.h>
+#include <sys/wait.h>
+#include <unistd.h>
+
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <functional>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <regex>
+#include <sstream>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "json.hpp"
+
+namespace det {
+
+struct Device {
+  int id = 0;
+  std::string brand, uuid, type;  // type: "gpu" | "cpu"
+  Json to_json() const {
+    Json j = Json::object();
+    j["id"] = id; j["brand"] = brand; j["uuid"] = uuid; j["type"] = type;
+    return j;
+  }
+};
+
+inline std::string run_capture(const std::string& cmd) {
+  std::string out;
+  FILE* p = popen((cmd + " 2>/dev/null").c_str(), "r");
+  if (!p) return out;
+  char buf[4096];
+  size_t n;
+  while ((n = fread(buf, 1, sizeof buf, p)) > 0) out.append(buf, n);
+  pclose(p);
+  return out;
+}
+
+inline std::string nvidia_driver_version() {
+  std::string v = run_capture("nvidia-smi --query-gpu=driver_version --format=csv,noheader");
+  auto nl = v.find('\n');
+  return nl == std::string::npos ? v : v.substr(0, nl);
+}
+
+// slot_type: "auto" | "gpu" | "cpu" | "none"; visible_gpus: comma list of indices/UUIDs ("" = all);
+// artificial_slots > 0 fabricates that many slots (scheduling tests without hardware).
+inline std::vector<Device> detect_devices(const std::string& slot_type = "auto", const std::string& visible_gpus = "", int artificial_slots = 0) {
+  std::vector<Device> out;
+  if (artificial_slots > 0) {
+    for (int i = 0; i < artificial_slots; ++i) out.push_back(Device{i, "Artificial", "artificial-" + std::to_string(i), "gpu"});
+    return out;
+  }
+  if (slot_type == "none") return out;
+  if (slot_type == "auto" || slot_type == "gpu") {
+    std::string cmd = "nvidia-smi --query-gpu=index,name,uuid --format=csv,noheader";
+    if (!visible_gpus.empty()) cmd += " --id=" + visible_gpus;
+    std::istringstream ss(run_capture(cmd));
+    std::string line;
+    while (std::getline(ss, line)) {
+      std::vector<std::string> f;
+      std::stringstream ls(line);
+      std::string item;
+      while (std::getline(ls, item, ',')) {
+        while (!item.empty() && item.front() == ' ') item.erase(item.begin());
+        while (!item.empty() && (item.back() == ' ' || item.back() == '\r')) item.pop_back();
+        f.push_back(item);
+      }
+      if (f.size() == 3) out.push_back(Device{atoi(f[0].c_str()), f[1], f[2], "gpu"});
+    }
+    if (!out.empty() || slot_type == "gpu") return out;
+  }
+  // CPU fallback: one slot standing for the host's cores
+  std::string model = "cpu";
+  std::istringstream ci(run_capture("grep -m1 'model name' /proc/cpuinfo"));
+  std::string l;
+  if (std::getline(ci, l)) { auto c = l.find(':'); if (c != std::string::npos) model = l.substr(c + 2); }
+  out.push_back(Device{0, model, "cpu-0", "cpu"});
+  return out;
+}
+
+struct ContainerSpec {
+  std::string container_id, task_id, description;
+  std::vector<std::string> argv;
+  std::map<std::string, std::string> env;
+  std::string cwd;
+  std::vector<Device> devices;
+};
+
+struct ContainerEvent {
+  std::string container_id, state;  // ASSIGNED | PULLING | STARTING | RUNNING | TERMINATED
+  int exit_code = 0;
+  std::string failure;  // "" on clean exit
+};
+
+struct LogLine {
+  std::string container_id, stdtype, message;
+  int rank = -1;
+};
+
+class ContainerManager {
+ public:
+  using EventFn = std::function<void(const ContainerEvent&)>;
+  using LogFn = std::function<void(const LogLine&)>;
+  ContainerManager(EventFn on_event, LogFn on_log) : on_event_(std::move(on_event)), on_log_(std::move(on_log)) {}
+  ~ContainerManager() { kill_all(); }
+
+  bool start(const ContainerSpec& spec) {
+    on_event_({spec.container_id, "ASSIGNED", 0, ""});
+    on_event_({spec.container_id, "PULLING", 0, ""});   // no image to pull: state kept for protocol parity
+    on_event_({spec.container_id, "STARTING", 0, ""});
+    int out_pipe[2], err_pipe[2];
+    if (pipe(out_pipe) != 0 || pipe(err_pipe) != 0) { on_event_({spec.container_id, "TERMINATED", 127, "pipe() failed"}); return false; }
+    std::map<std::string, std::string> env = spec.env;
+    env["DET_CONTAINER_ID"] = spec.container_id;
+    std::string slot_ids = "[", gpu_mask;
+    bool use_gpu = false;
+    for (size_t i = 0; i < spec.devices.size(); ++i) {
+      slot_ids += (i ? "," : "") + std::to_string(spec.devices[i].id);
+      if (spec.devices[i].type == "gpu" && spec.devices[i].brand != "Artificial") { use_gpu = true; gpu_mask += (gpu_mask.empty() ? "" : ",") + std::to_string(spec.devices[i].id); }
+    }
+    env["DET_SLOT_IDS"] = slot_ids + "]";
+    env["DET_USE_GPU"] = use_gpu ? "true" : "false";
+    if (use_gpu) env["CUDA_VISIBLE_DEVICES"] = gpu_mask;
+    else if (!spec.devices.empty() || env.count("DET_FORCE_CPU")) env["CUDA_VISIBLE_DEVICES"] = "";
+    pid_t pid = fork();
+    if (pid < 0) { on_event_({spec.container_id, "TERMINATED", 127, "fork() failed"}); return false; }
+    if (pid == 0) {
+      setpgid(0, 0);
+      dup2(out_pipe[1], 1);
+      dup2(err_pipe[1], 2);
+      close(out_pipe[0]); close(out_pipe[1]); close(err_pipe[0]); close(err_pipe[1]);
+      if (!spec.cwd.empty() && chdir(spec.cwd.c_str()) != 0) { perror("chdir"); _exit(126); }
+      for (auto& kv : env) setenv(kv.first.c_str(), kv.second.c_str(), 1);
+      std::vector<char*> argv;
+      for (auto& a : spec.argv) argv.push_back(const_cast<char*>(a.c_str()));
+      argv.push_back(nullptr);
+      execvp(argv[0], argv.data());
+      perror("execvp");
+      _exit(127);
+    }
+    close(out_pipe[1]);
+    close(err_pipe[1]);
+    {
+      std::lock_guard<std::mutex> g(mu_);
+      pids_[spec.container_id] = pid;
+    }
+    on_event_({spec.container_id, "RUNNING", 0, ""});
+    const std::string cid = spec.container_id;
+    std::thread([this, cid, fd = out_pipe[0]] { pump(cid, fd, "stdout"); }).detach();
+    std::thread([this, cid, fd = err_pipe[0]] { pump(cid, fd, "stderr"); }).detach();
+    std::thread([this, cid, pid] {
+      int status = 0;
+      waitpid(pid, &status, 0);
+      ContainerEvent ev{cid, "TERMINATED", 0, ""};
+      if (WIFEXITED(status)) { ev.exit_code = WEXITSTATUS(status); if (ev.exit_code) ev.failure = "container failed with non-zero exit code: " + std::to_string(ev.exit_code); }
+      else if (WIFSIGNALED(status)) { ev.exit_code = 128 + WTERMSIG(status); ev.failure = std::string("container killed by signal ") + strsignal(WTERMSIG(status)); }
+      { std::lock_guard<std::mutex> g(mu_); pids_.erase(cid); }
+      on_event_(ev);
+    }).detach();
+    return true;
+  }
+  void signal(const std::string& container_id, int sig) {
+    std::lock_guard<std::mutex> g(mu_);
+    auto it = pids_.find(container_id);
+    if (it != pids_.end()) ::kill(-it->second, sig);  // whole process group (the launcher's worker ranks too)
+  }
+  void kill_all() {
+    std::lock_guard<std::mutex> g(mu_);
+    for (auto& kv : pids_) ::kill(-kv.second, SIGKILL);
+  }
+  size_t running() {
+    std::lock_guard<std::mutex> g(mu_);
+    return pids_.size();
+  }
+
+ private:
+  void pump(const std::string& cid, int fd, const std::string& stdtype) {
+    static const std::regex rank_re("^\\[rank=(\\d+)\\] ?(.*)$");
+    std::string pending;
+    char buf[4096];
+    ssize_t n;
+    while ((n = read(fd, buf, sizeof buf)) > 0) {
+      pending.append(buf, static_cast<size_t>(n));
+      size_t nl;
+      while ((nl = pending.find('\n')) != std::string::npos) {
+        std::string line = pending.substr(0, nl);
+        pending.erase(0, nl + 1);
+        LogLine l{cid, stdtype, line, -1};
+        std::smatch m;
+        if (std::regex_match(line, m, rank_re)) { l.rank = atoi(m[1].str().c_str()); l.message = m[2].str(); }
+        on_log_(l);
+      }
+    }
+    if (!pending.empty()) on_log_(LogLine{cid, stdtype, pending, -1});
+    close(fd);
+  }
+  EventFn on_event_;
+  LogFn on_log_;
+  std::mutex mu_;
+  std::map<std::string, pid_t> pids_;
+};
+
+}  // namespace det

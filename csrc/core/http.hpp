@@ -1,0 +1,250 @@
+// http.hpp — minimal HTTP/1.1 server (thread per connection, route patterns with :params, JSON helpers) and a
+// blocking client. Serves the master's REST API; long-poll endpoints replace the reference's WebSockets
+// (master/internal/api/*.go, core.go:313-606 register the reference's echo routes).
+#pragma once
+#include <arpa/inet.h>
+#include <netinet/in.h>
+#include <netinet/tcp.h>
+#include <sys/socket.h>
+#include <unistd.h>
+
+#include <atomic>
+#include <cstring>
+#include <functional>
+#include <map>
+#include <sstream>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "json.hpp"
+
+namespace det {
+
+struct HttpRequest {
+  std::string method, path, query_string, body;
+  std::map<std::string, std::string> headers, query, params;
+  Json json() const { return body.empty() ? Json::object() : Json::parse(body); }
+  std::string q(const std::string& k, const std::string& def = "") const {
+    auto it = query.find(k);
+    return it == query.end() ? def : it->second;
+  }
+  long long qi(const std::string& k, long long def = 0) const {
+    auto it = query.find(k);
+    return it == query.end() || it->second.empty() ? def : atoll(it->second.c_str());
+  }
+};
+
+struct HttpResponse {
+  int status = 200;
+  std::string content_type = "application/json";
+  std::string body;
+  static HttpResponse json(const Json& j, int status = 200) { HttpResponse r; r.status = status; r.body = j.dump(); return r; }
+  static HttpResponse error(int status, const std::string& msg) {
+    Json j = Json::object();
+    j["error"] = msg;
+    j["code"] = status;
+    return json(j, status);
+  }
+  static HttpResponse text(const std::string& s, int status = 200, const std::string& ct = "text/plain") {
+    HttpResponse r; r.status = status; r.content_type = ct; r.body = s; return r;
+  }
+};
+
+inline std::string url_decode(const std::string& s) {
+  std::string o;
+  for (size_t i = 0; i < s.size(); ++i) {
+    if (s[i] == '%' && i + 2 < s.size()) { o.push_back(static_cast<char>(strtol(s.substr(i + 1, 2).c_str(), nullptr, 16))); i += 2; }
+    else if (s[i] == '+') o.push_back(' ');
+    else o.push_back(s[i]);
+  }
+  return o;
+}
+
+class HttpServer {
+ public:
+  using Handler = std::function<HttpResponse(const HttpRequest&)>;
+  void route(const std::string& method, const std::string& pattern, Handler h) { routes_.push_back(Route{method, split(pattern), std::move(h)}); }
+  void set_middleware(std::function<bool(const HttpRequest&, HttpResponse&)> mw) { middleware_ = std::move(mw); }
+
+  // Binds and listens; returns the bound port (useful with port 0) or -1.
+  int listen(const std::string& host, int port) {
+    fd_ = ::socket(AF_INET, SOCK_STREAM, 0);
+    if (fd_ < 0) return -1;
+    int one = 1;
+    setsockopt(fd_, SOL_SOCKET, SO_REUSEADDR, &one, sizeof one);
+    sockaddr_in addr{};
+    addr.sin_family = AF_INET;
+    addr.sin_port = htons(static_cast<uint16_t>(port));
+    addr.sin_addr.s_addr = host.empty() || host == "0.0.0.0" ? INADDR_ANY : inet_addr(host.c_str());
+    if (::bind(fd_, reinterpret_cast<sockaddr*>(&addr), sizeof addr) < 0) { ::close(fd_); fd_ = -1; return -1; }
+    if (::listen(fd_, 256) < 0) { ::close(fd_); fd_ = -1; return -1; }
+    socklen_t len = sizeof addr;
+    getsockname(fd_, reinterpret_cast<sockaddr*>(&addr), &len);
+    port_ = ntohs(addr.sin_port);
+    return port_;
+  }
+  void serve_forever() {
+    while (!stop_) {
+      int c = ::accept(fd_, nullptr, nullptr);
+      if (c < 0) { if (stop_) break; continue; }
+      int one = 1;
+      setsockopt(c, IPPROTO_TCP, TCP_NODELAY, &one, sizeof one);
+      std::thread([this, c] { handle(c); }).detach();
+    }
+  }
+  void start() { thread_ = std::thread([this] { serve_forever(); }); }
+  void stop() {
+    stop_ = true;
+    if (fd_ >= 0) { ::shutdown(fd_, SHUT_RDWR); ::close(fd_); fd_ = -1; }
+    if (thread_.joinable()) thread_.join();
+  }
+  int port() const { return port_; }
+
+ private:
+  struct Route { std::string method; std::vector<std::string> parts; Handler h; };
+  static std::vector<std::string> split(const std::string& p) {
+    std::vector<std::string> out;
+    std::stringstream ss(p);
+    std::string item;
+    while (std::getline(ss, item, '/')) if (!item.empty()) out.push_back(item);
+    return out;
+  }
+  static bool read_request(int c, HttpRequest& req) {
+    std::string buf;
+    char tmp[8192];
+    size_t header_end = std::string::npos;
+    while (header_end == std::string::npos) {
+      ssize_t n = ::recv(c, tmp, sizeof tmp, 0);
+      if (n <= 0) return false;
+      buf.append(tmp, static_cast<size_t>(n));
+      header_end = buf.find("\r\n\r\n");
+      if (buf.size() > (1u << 20) && header_end == std::string::npos) return false;
+    }
+    std::istringstream hs(buf.substr(0, header_end));
+    std::string line;
+    std::getline(hs, line);
+    if (!line.empty() && line.back() == '\r') line.pop_back();
+    std::istringstream rl(line);
+    std::string target, ver;
+    rl >> req.method >> target >> ver;
+    auto qpos = target.find('?');
+    req.path = url_decode(target.substr(0, qpos));
+    if (qpos != std::string::npos) {
+      req.query_string = target.substr(qpos + 1);
+      std::stringstream qs(req.query_string);
+      std::string kv;
+      while (std::getline(qs, kv, '&')) {
+        auto eq = kv.find('=');
+        req.query[url_decode(kv.substr(0, eq))] = eq == std::string::npos ? "" : url_decode(kv.substr(eq + 1));
+      }
+    }
+    while (std::getline(hs, line)) {
+      if (!line.empty() && line.back() == '\r') line.pop_back();
+      auto colon = line.find(':');
+      if (colon == std::string::npos) continue;
+      std::string k = line.substr(0, colon), v = line.substr(colon + 1);
+      for (auto& ch : k) ch = static_cast<char>(tolower(ch));
+      while (!v.empty() && v.front() == ' ') v.erase(v.begin());
+      req.headers[k] = v;
+    }
+    size_t content_len = 0;
+    auto it = req.headers.find("content-length");
+    if (it != req.headers.end()) content_len = static_cast<size_t>(atoll(it->second.c_str()));
+    req.body = buf.substr(header_end + 4);
+    while (req.body.size() < content_len) {
+      ssize_t n = ::recv(c, tmp, sizeof tmp, 0);
+      if (n <= 0) return false;
+      req.body.append(tmp, static_cast<size_t>(n));
+    }
+    return true;
+  }
+  void handle(int c) {
+    HttpRequest req;
+    if (read_request(c, req)) {
+      HttpResponse resp = dispatch(req);
+      static const std::map<int, const char*> reason = {{200, "OK"}, {201, "Created"}, {204, "No Content"}, {400, "Bad Request"},
+                                                        {401, "Unauthorized"}, {403, "Forbidden"}, {404, "Not Found"},
+                                                        {409, "Conflict"}, {500, "Internal Server Error"}};
+      auto rit = reason.find(resp.status);
+      std::ostringstream os;
+      os << "HTTP/1.1 " << resp.status << " " << (rit == reason.end() ? "Status" : rit->second) << "\r\n"
+         << "Content-Type: " << resp.content_type << "\r\nContent-Length: " << resp.body.size()
+         << "\r\nAccess-Control-Allow-Origin: *\r\nConnection: close\r\n\r\n" << resp.body;
+      const std::string out = os.str();
+      size_t sent = 0;
+      while (sent < out.size()) {
+        ssize_t n = ::send(c, out.data() + sent, out.size() - sent, MSG_NOSIGNAL);
+        if (n <= 0) break;
+        sent += static_cast<size_t>(n);
+      }
+    }
+    ::close(c);
+  }
+  HttpResponse dispatch(HttpRequest& req) {
+    try {
+      if (req.method == "OPTIONS") return HttpResponse::text("", 204);
+      auto parts = split(req.path);
+      bool path_matched = false;
+      for (auto& r : routes_) {
+        if (r.parts.size() != parts.size() && !(r.parts.size() <= parts.size() && !r.parts.empty() && r.parts.back() == "*")) continue;
+        std::map<std::string, std::string> params;
+        bool ok = true;
+        for (size_t i = 0; i < r.parts.size() && ok; ++i) {
+          if (r.parts[i] == "*") { std::string rest; for (size_t j = i; j < parts.size(); ++j) rest += (j > i ? "/" : "") + parts[j]; params["*"] = rest; break; }
+          if (r.parts[i][0] == ':') params[r.parts[i].substr(1)] = parts[i];
+          else if (r.parts[i] != parts[i]) ok = false;
+        }
+        if (!ok) continue;
+        path_matched = true;
+        if (r.method != req.method) continue;
+        req.params = params;
+        HttpResponse resp;
+        if (middleware_ && !middleware_(req, resp)) return resp;
+        return r.h(req);
+      }
+      return HttpResponse::error(path_matched ? 405 : 404, path_matched ? "method not allowed" : "no route for " + req.path);
+    } catch (const std::exception& e) {
+      return HttpResponse::error(400, e.what());
+    }
+  }
+  std::vector<Route> routes_;
+  std::function<bool(const HttpRequest&, HttpResponse&)> middleware_;
+  int fd_ = -1, port_ = 0;
+  std::atomic<bool> stop_{false};
+  std::thread thread_;
+};
+
+// Blocking one-shot client: returns status (or -1) and fills body.
+inline int http_request(const std::string& host, int port, const std::string& method, const std::string& path,
+                        const std::string& body, std::string* out, int timeout_s = 60, const std::string& auth = "") {
+  int fd = ::socket(AF_INET, SOCK_STREAM, 0);
+  if (fd < 0) return -1;
+  timeval tv{timeout_s, 0};
+  setsockopt(fd, SOL_SOCKET, SO_RCVTIMEO, &tv, sizeof tv);
+  sockaddr_in addr{};
+  addr.sin_family = AF_INET;
+  addr.sin_port = htons(static_cast<uint16_t>(port));
+  addr.sin_addr.s_addr = inet_addr(host == "localhost" ? "127.0.0.1" : host.c_str());
+  if (::connect(fd, reinterpret_cast<sockaddr*>(&addr), sizeof addr) < 0) { ::close(fd); return -1; }
+  std::ostringstream os;
+  os << method << " " << path << " HTTP/1.1\r\nHost: " << host << "\r\nContent-Type: application/json\r\nContent-Length: " << body.size()
+     << "\r\nConnection: close\r\n";
+  if (!auth.empty()) os << "Authorization: Bearer " << auth << "\r\n";
+  os << "\r\n" << body;
+  const std::string req = os.str();
+  if (::send(fd, req.data(), req.size(), MSG_NOSIGNAL) < 0) { ::close(fd); return -1; }
+  std::string buf;
+  char tmp[8192];
+  ssize_t n;
+  while ((n = ::recv(fd, tmp, sizeof tmp, 0)) > 0) buf.append(tmp, static_cast<size_t>(n));
+  ::close(fd);
+  auto he = buf.find("\r\n\r\n");
+  if (he == std::string::npos) return -1;
+  int status = -1;
+  sscanf(buf.c_str(), "HTTP/%*s %d", &status);
+  if (out) *out = buf.substr(he + 4);
+  return status;
+}
+
+}  // namespace det

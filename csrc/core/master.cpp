@@ -1,0 +1,329 @@
+// master.cpp — Master bootstrap, configuration, container routing, command tasks, checkpoint GC, restore.
+#include "master.hpp"
+
+#include <sys/stat.h>
+
+#include <algorithm>
+#include <chrono>
+#include <ctime>
+#include <fstream>
+#include <set>
+
+namespace det {
+
+static Json obj(std::initializer_list<std::pair<const char*, Json>> kv) {
+  Json j = Json::object();
+  for (auto& p : kv) j[p.first] = p.second;
+  return j;
+}
+
+std::string now_rfc3339() {
+  using namespace std::chrono;
+  auto now = system_clock::now();
+  std::time_t t = system_clock::to_time_t(now);
+  char buf[40];
+  std::tm tm{};
+  gmtime_r(&t, &tm);
+  strftime(buf, sizeof buf, "%Y-%m-%dT%H:%M:%S", &tm);
+  char out[64];
+  snprintf(out, sizeof out, "%s.%06ldZ", buf, static_cast<long>(duration_cast<microseconds>(now.time_since_epoch()).count() % 1000000));
+  return out;
+}
+std::string random_hex(int bytes) {
+  static thread_local std::mt19937_64 rng(std::random_device{}());
+  static const char* hex = "0123456789abcdef";
+  std::string s;
+  for (int i = 0; i < bytes; ++i) { unsigned v = static_cast<unsigned>(rng() & 0xff); s.push_back(hex[v >> 4]); s.push_back(hex[v & 15]); }
+  return s;
+}
+std::string md5_hex(const std::string& s) {
+  // two 64-bit halves out of the md5 helper (low half of md5(s), low half of md5(s + "#")) — used only for
+  // salted password digests inside this store, not for interchange
+  char buf[40];
+  snprintf(buf, sizeof buf, "%016llx%016llx", static_cast<unsigned long long>(md5_low64(s)), static_cast<unsigned long long>(md5_low64(s + "#")));
+  return buf;
+}
+
+MasterConfig MasterConfig::from_json(const Json& j) {
+  static const std::set<std::string> known = {"host", "port", "data_dir", "scheduler", "fitting_policy", "preemption", "checkpoint_storage",
+                                              "python", "repo_root", "slot_type", "visible_gpus", "artificial_slots", "auth_required",
+                                              "cluster_name", "scheduler_tick_ms", "terminate_timeout_ms", "resource_pools", "db", "telemetry",
+                                              "security", "task_container_defaults"};
+  MasterConfig c;
+  for (auto& kv : j.obj())
+    if (!known.count(kv.first)) throw ConfigError("unknown field in master config: '" + kv.first + "'");
+  c.host = j["host"].str_or(c.host);
+  c.port = static_cast<int>(j["port"].as_int(c.port));
+  c.data_dir = j["data_dir"].str_or(c.data_dir);
+  if (j["scheduler"].is_object()) {  // reference shape: scheduler: {type, fit, preemption}
+    c.scheduler = j["scheduler"]["type"].str_or(c.scheduler);
+    c.fitting_policy = j["scheduler"]["fit"].str_or(c.fitting_policy);
+    c.preemption = j["scheduler"]["preemption"].as_bool(false);
+  } else {
+    c.scheduler = j["scheduler"].str_or(c.scheduler);
+  }
+  c.fitting_policy = j["fitting_policy"].str_or(c.fitting_policy);
+  if (j.contains("preemption")) c.preemption = j["preemption"].as_bool(false);
+  c.checkpoint_storage = j["checkpoint_storage"];
+  c.python = j["python"].str_or(c.python);
+  c.repo_root = j["repo_root"].str_or(c.repo_root);
+  c.slot_type = j["slot_type"].str_or(c.slot_type);
+  c.visible_gpus = j["visible_gpus"].str_or("");
+  c.artificial_slots = static_cast<int>(j["artificial_slots"].as_int(0));
+  c.auth_required = j["auth_required"].as_bool(false) || j["security"]["auth_required"].as_bool(false);
+  c.cluster_name = j["cluster_name"].str_or(c.cluster_name);
+  c.scheduler_tick_ms = static_cast<int>(j["scheduler_tick_ms"].as_int(c.scheduler_tick_ms));
+  c.terminate_timeout_ms = static_cast<int>(j["terminate_timeout_ms"].as_int(c.terminate_timeout_ms));
+  if (c.scheduler != "fair_share" && c.scheduler != "priority" && c.scheduler != "round_robin") throw ConfigError("scheduler must be fair_share, priority or round_robin");
+  if (c.fitting_policy != "best" && c.fitting_policy != "worst") throw ConfigError("fitting_policy must be best or worst");
+  return c;
+}
+Json MasterConfig::to_json() const {
+  return obj({{"host", host}, {"port", port}, {"data_dir", data_dir}, {"scheduler", scheduler}, {"fitting_policy", fitting_policy},
+              {"preemption", preemption}, {"checkpoint_storage", checkpoint_storage}, {"python", python}, {"repo_root", repo_root},
+              {"slot_type", slot_type}, {"artificial_slots", artificial_slots}, {"auth_required", auth_required},
+              {"cluster_name", cluster_name}, {"scheduler_tick_ms", scheduler_tick_ms}});
+}
+
+// ---- command tasks (generic commands, notebooks, shells, tensorboards) ---------------------------------------------
+namespace {
+class CommandActor : public Actor {
+ public:
+  CommandActor(Master* m, long long id, const Json& spec) : m_(m), id_(id), spec_(spec) { task_id_ = "command-" + std::to_string(id); }
+  void pre_start(Context& ctx) override {
+    set_state("PENDING");
+    m_->system.tell(m_->rm, "allocate", obj({{"task_id", task_id_}, {"name", spec_["description"].str_or(task_id_)}, {"group", task_id_},
+                                             {"slots_needed", spec_["slots"].as_int(0)}, {"non_preemptible", true}, {"single_agent", true}}), ctx.self());
+  }
+  void receive(Context& ctx, const Message& msg) override {
+    if (msg.type == "resources_allocated") {
+      const Json& a = msg.body["allocations"].at(0);
+      ContainerSpec spec;
+      spec.container_id = a["container_id"].as_string();
+      spec.task_id = task_id_;
+      for (auto& v : spec_["argv"].arr()) spec.argv.push_back(v.as_string());
+      spec.cwd = spec_["cwd"].str_or("");
+      for (auto& kv : spec_["env"].obj()) spec.env[kv.first] = kv.second.as_string();
+      for (auto& d : a["devices"].arr()) spec.devices.push_back(Device{static_cast<int>(d["id"].as_int()), d["brand"].as_string(), d["uuid"].as_string(), d["type"].as_string()});
+      container_ = spec.container_id;
+      m_->register_container(container_, ctx.self(), -id_);
+      set_state("RUNNING");
+      m_->containers->start(spec);
+    } else if (msg.type == "container_event") {
+      if (msg.body["state"].as_string() == "TERMINATED") {
+        m_->unregister_container(container_);
+        m_->store.update("commands", id_, obj({{"exit_code", msg.body["exit_code"]}, {"end_time", now_rfc3339()}}));
+        set_state("TERMINATED");
+        ctx.tell(m_->rm, "release", obj({{"task_id", task_id_}}));
+        ctx.stop_self();
+      }
+    } else if (msg.type == "kill" || msg.type == "release_resources") {
+      if (!container_.empty()) m_->containers->signal(container_, SIGKILL);
+      else { set_state("TERMINATED"); ctx.tell(m_->rm, "release", obj({{"task_id", task_id_}})); ctx.stop_self(); }
+      msg.respond(Json(true));
+    } else if (msg.type == "log") {
+      m_->store.append("command_logs", std::to_string(id_), msg.body);
+    }
+  }
+
+ private:
+  void set_state(const std::string& s) { m_->store.update("commands", id_, obj({{"state", s}})); }
+  Master* m_;
+  long long id_;
+  Json spec_;
+  std::string task_id_, container_;
+};
+}  // namespace
+
+std::unique_ptr<Actor> make_command(Master* m, long long id, const Json& spec) { return std::unique_ptr<Actor>(new CommandActor(m, id, spec)); }
+
+// ---- Master ------------------------------------------------------------------------------------------------------------
+Master::Master(const MasterConfig& c) : cfg(c), store(c.data_dir), system(16) {
+  containers.reset(new ContainerManager([this](const ContainerEvent& ev) { route_container_event(ev); }, [this](const LogLine& l) { route_log(l); }));
+}
+Master::~Master() { stop(); }
+
+void Master::log(const std::string& level, const std::string& msg) {
+  Json e = obj({{"time", now_rfc3339()}, {"level", level}, {"message", msg}});
+  {
+    std::lock_guard<std::mutex> g(log_mu_);
+    log_ring_.push_back(e);
+    if (log_ring_.size() > 25000) log_ring_.pop_front();
+  }
+  fprintf(stderr, "[%s] %s: %s\n", e["time"].as_string().c_str(), level.c_str(), msg.c_str());
+}
+std::vector<Json> Master::recent_logs(size_t limit) {
+  std::lock_guard<std::mutex> g(log_mu_);
+  std::vector<Json> out;
+  size_t start = log_ring_.size() > limit ? log_ring_.size() - limit : 0;
+  for (size_t i = start; i < log_ring_.size(); ++i) out.push_back(log_ring_[i]);
+  return out;
+}
+
+ActorRef Master::experiment_actor(long long id) { return system.get("experiments/" + std::to_string(id)); }
+
+void Master::register_container(const std::string& cid, const ActorRef& owner, long long trial_id) {
+  std::lock_guard<std::mutex> g(container_mu_);
+  container_owner_[cid] = {owner, trial_id};
+}
+void Master::unregister_container(const std::string& cid) {
+  std::lock_guard<std::mutex> g(container_mu_);
+  container_owner_.erase(cid);
+}
+void Master::route_container_event(const ContainerEvent& ev) {
+  ActorRef owner;
+  {
+    std::lock_guard<std::mutex> g(container_mu_);
+    auto it = container_owner_.find(ev.container_id);
+    if (it != container_owner_.end()) owner = it->second.first;
+  }
+  if (owner) system.tell(owner, "container_event", obj({{"container_id", ev.container_id}, {"state", ev.state}, {"exit_code", ev.exit_code}, {"failure", ev.failure}}));
+}
+void Master::route_log(const LogLine& l) {
+  ActorRef owner;
+  long long trial_id = 0;
+  {
+    std::lock_guard<std::mutex> g(container_mu_);
+    auto it = container_owner_.find(l.container_id);
+    if (it != container_owner_.end()) { owner = it->second.first; trial_id = it->second.second; }
+  }
+  Json row = obj({{"trial_id", trial_id}, {"container_id", l.container_id}, {"timestamp", now_rfc3339()}, {"stdtype", l.stdtype},
+                  {"rank", l.rank >= 0 ? Json(l.rank) : Json()}, {"message", l.message}, {"source", "agent"}, {"agent_id", "agent-local"},
+                  {"level", l.stdtype == "stderr" ? "INFO" : "INFO"}});
+  if (trial_id > 0) system.tell(logger, "log", row);
+  else if (owner) system.tell(owner, "log", row);
+}
+
+long long Master::create_experiment(const Json& config, const Json& model_definition, long long parent_id, bool activate, const std::string& owner) {
+  const long long id = store.next_id("experiments");
+  const std::string dir = model_def_dir(id);
+  mkdirs(dir);
+  // model_definition: [{"path": "...", "content": "<text>", "mode": 0644}]; directories are implied by paths
+  for (auto& f : model_definition.arr()) {
+    const std::string rel = f["path"].as_string();
+    if (rel.empty() || rel.find("..") != std::string::npos || rel[0] == '/') continue;
+    const std::string full = dir + "/" + rel;
+    auto slash = full.rfind('/');
+    if (slash != std::string::npos) mkdirs(full.substr(0, slash));
+    if (f["type"].str_or("file") == "dir") { mkdirs(full); continue; }
+    std::ofstream out(full, std::ios::binary);
+    out << f["content"].as_string();
+    out.close();
+    if (f["mode"].is_number()) chmod(full.c_str(), static_cast<mode_t>(f["mode"].as_int()));
+  }
+  store.put("experiments", id, obj({{"id", id}, {"state", activate ? "ACTIVE" : "PAUSED"}, {"config", config}, {"parent_id", parent_id > 0 ? Json(parent_id) : Json()},
+                                    {"start_time", now_rfc3339()}, {"end_time", Json()}, {"archived", false}, {"progress", 0.0}, {"owner", owner},
+                                    {"description", config["description"]}, {"labels", config["labels"]}, {"best_validation", Json()}}));
+  system.actor_of("experiments/" + std::to_string(id), make_experiment(this, id, false), experiments_root);
+  log("info", "created experiment " + std::to_string(id));
+  return id;
+}
+
+// Pick checkpoints outside save_experiment_best / save_trial_best / save_trial_latest (never ones used for warm
+// starts), mark them DELETED and run the GC task that removes their files. (reference checkpoint_gc.go:15-88,
+// postgres.go:1043-1156)
+void Master::spawn_checkpoint_gc(long long experiment_id) {
+  Json exp = store.get("experiments", experiment_id);
+  if (exp.is_null()) return;
+  const Json& cs = exp["config"]["checkpoint_storage"];
+  const int keep_exp = static_cast<int>(cs["save_experiment_best"].as_int(0)), keep_best = static_cast<int>(cs["save_trial_best"].as_int(1)),
+            keep_latest = static_cast<int>(cs["save_trial_latest"].as_int(1));
+  const std::string metric = exp["config"]["searcher"]["metric"].str_or("");
+  const bool smaller = exp["config"]["searcher"]["smaller_is_better"].is_null() ? true : exp["config"]["searcher"]["smaller_is_better"].as_bool(true);
+  auto ckpts = store.list("checkpoints", [&](const Json& r) { return r["experiment_id"].as_int() == experiment_id && r["state"].as_string() == "COMPLETED"; });
+  std::set<std::string> warm;
+  for (auto& t : store.list("trials")) if (t["warm_start_checkpoint"].is_object()) warm.insert(t["warm_start_checkpoint"]["uuid"].str_or(""));
+  auto metric_of = [&](const Json& c, double* out) {
+    for (auto& v : store.series("validations", std::to_string(c["trial_id"].as_int())))
+      if (v["total_batches"].as_int() == c["total_batches"].as_int()) {
+        const Json& m = v["metrics"]["validation_metrics"][metric];
+        if (m.is_number()) { *out = smaller ? m.as_double() : -m.as_double(); return true; }
+      }
+    return false;
+  };
+  std::set<std::string> keep;
+  std::map<long long, std::vector<Json>> by_trial;
+  for (auto& c : ckpts) by_trial[c["trial_id"].as_int()].push_back(c);
+  std::vector<std::pair<double, std::string>> exp_ranked;
+  for (auto& kv : by_trial) {
+    auto& v = kv.second;
+    std::sort(v.begin(), v.end(), [](const Json& a, const Json& b) { return a["total_batches"].as_int() > b["total_batches"].as_int(); });
+    for (int i = 0; i < keep_latest && i < static_cast<int>(v.size()); ++i) keep.insert(v[static_cast<size_t>(i)]["uuid"].as_string());
+    std::vector<std::pair<double, std::string>> ranked;
+    for (auto& c : v) { double m; if (metric_of(c, &m)) { ranked.push_back({m, c["uuid"].as_string()}); exp_ranked.push_back({m, c["uuid"].as_string()}); } }
+    std::sort(ranked.begin(), ranked.end());
+    for (int i = 0; i < keep_best && i < static_cast<int>(ranked.size()); ++i) keep.insert(ranked[static_cast<size_t>(i)].second);
+  }
+  std::sort(exp_ranked.begin(), exp_ranked.end());
+  for (int i = 0; i < keep_exp && i < static_cast<int>(exp_ranked.size()); ++i) keep.insert(exp_ranked[static_cast<size_t>(i)].second);
+  Json to_delete = Json::array();
+  for (auto& c : ckpts) {
+    const std::string uuid = c["uuid"].as_string();
+    if (keep.count(uuid) || warm.count(uuid)) continue;
+    store.update("checkpoints", uuid, obj({{"state", "DELETED"}}));
+    to_delete.push_back(obj({{"uuid", uuid}, {"resources", c["resources"]}}));
+  }
+  if (to_delete.size() == 0) return;
+  const long long cmd_id = store.next_id("commands");
+  Json spec = obj({{"type", "gc"}, {"description", "checkpoint GC (experiment " + std::to_string(experiment_id) + ")"}, {"slots", 0},
+                   {"argv", Json(Json::array_t{Json(cfg.python), Json("-m"), Json("determined_b200.exec.gc_checkpoints")})},
+                   {"env", obj({{"DET_EXPERIMENT_ID", std::to_string(experiment_id)}, {"DET_EXPERIMENT_CONFIG", exp["config"].dump()},
+                                {"DET_DELETE", to_delete.dump()}, {"PYTHONPATH", cfg.repo_root}})}});
+  store.put("commands", cmd_id, obj({{"id", cmd_id}, {"type", "gc"}, {"state", "PENDING"}, {"spec", spec}, {"start_time", now_rfc3339()}}));
+  system.actor_of("commands/" + std::to_string(cmd_id), make_command(this, cmd_id, spec), commands_root);
+  log("info", "checkpoint GC for experiment " + std::to_string(experiment_id) + ": deleting " + std::to_string(to_delete.size()) + " checkpoints");
+}
+
+bool Master::check_auth(const HttpRequest& req, std::string* user) {
+  auto it = req.headers.find("authorization");
+  std::string token;
+  if (it != req.headers.end() && it->second.rfind("Bearer ", 0) == 0) token = it->second.substr(7);
+  if (!token.empty()) {
+    Json s = store.get("sessions", token);
+    if (!s.is_null()) { if (user) *user = s["username"].as_string(); return true; }
+  }
+  if (user) *user = "determined";
+  return !cfg.auth_required;
+}
+
+void Master::restore_experiments() {
+  // non-terminal experiments come back through searcher-event replay (reference core.go:453-466)
+  for (auto& e : store.list("experiments", [](const Json& r) { return !is_terminal_state(r["state"].as_string()); })) {
+    const long long id = e["id"].as_int();
+    system.actor_of("experiments/" + std::to_string(id), make_experiment(this, id, true), experiments_root);
+  }
+  for (auto& c : store.list("commands", [](const Json& r) { return r["state"].as_string() != "TERMINATED"; }))
+    store.update("commands", c["id"].as_int(), obj({{"state", "TERMINATED"}, {"exit_code", -1}}));  // processes did not survive the master
+}
+
+int Master::start() {
+  started_at = static_cast<long long>(std::time(nullptr));
+  Json cl = store.get("cluster", "id");
+  if (cl.is_null()) { cluster_id = random_hex(16); store.put("cluster", "id", obj({{"cluster_id", cluster_id}})); }
+  else cluster_id = cl["cluster_id"].as_string();
+  for (const char* u : {"determined", "admin"})
+    if (!store.exists("users", u)) store.put("users", u, obj({{"username", u}, {"admin", std::string(u) == "admin"}, {"active", true}, {"password_hash", ""}, {"salt", ""}}));
+  experiments_root = system.actor_of("experiments", make_root());
+  commands_root = system.actor_of("commands", make_root());
+  rm = system.actor_of("rm", make_resource_pool(this));
+  logger = system.actor_of("trial_logger", make_trial_logger(this));
+  devices = detect_devices(cfg.slot_type, cfg.visible_gpus, cfg.artificial_slots);
+  Json devs = Json::array();
+  for (auto& d : devices) devs.push_back(d.to_json());
+  system.ask(rm, "add_agent", obj({{"id", "agent-local"}, {"label", ""}, {"devices", devs}, {"registered_time", now_rfc3339()},
+                                   {"addresses", Json(Json::array_t{Json("127.0.0.1")})}, {"driver_version", nvidia_driver_version()}}));
+  register_routes();
+  const int port = http.listen(cfg.host, cfg.port);
+  if (port < 0) throw std::runtime_error("cannot bind " + cfg.host + ":" + std::to_string(cfg.port));
+  log("info", "master listening on " + cfg.host + ":" + std::to_string(port) + " with " + std::to_string(devices.size()) + " local slots (" + cfg.scheduler + ")");
+  restore_experiments();
+  return port;
+}
+void Master::run_forever() { http.serve_forever(); }
+void Master::stop() {
+  http.stop();
+  if (containers) containers->kill_all();
+  system.shutdown();
+}
+
+}  // namespace det

@@ -1,0 +1,102 @@
+// master.hpp — the single-box master: configuration, shared services, actor declarations.
+// Parity map (reference → here): master/internal/core.go Master.Run → Master::run; config.go → MasterConfig;
+// resourcemanagers/resource_pool.go → ResourcePoolActor; experiment.go → ExperimentActor; trial.go → TrialActor;
+// trial_logger.go → TrialLoggerActor; command/*.go → CommandActor; checkpoint_gc.go → Master::spawn_checkpoint_gc;
+// agent/internal/agent.go → the embedded local agent (ContainerManager) plus det-agent for extra nodes.
+#pragma once
+#include <atomic>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <random>
+#include <string>
+#include <vector>
+
+#include "actor.hpp"
+#include "agent.hpp"
+#include "http.hpp"
+#include "json.hpp"
+#include "model.hpp"
+#include "scheduler.hpp"
+#include "searcher.hpp"
+#include "sequencer.hpp"
+#include "store.hpp"
+
+namespace det {
+
+struct MasterConfig {
+  std::string host = "127.0.0.1";
+  int port = 8080;
+  std::string data_dir = "/tmp/determined-master";
+  std::string scheduler = "fair_share";  // fair_share | priority | round_robin
+  std::string fitting_policy = "best";
+  bool preemption = false;
+  Json checkpoint_storage;               // master-level default
+  std::string python = "python";
+  std::string repo_root;                 // added to PYTHONPATH of launched harness processes
+  std::string slot_type = "auto";
+  std::string visible_gpus;
+  int artificial_slots = 0;
+  bool auth_required = false;
+  std::string cluster_name = "b200-box";
+  int scheduler_tick_ms = 500;
+  int terminate_timeout_ms = 60000;
+
+  static MasterConfig from_json(const Json& j);  // strict: unknown keys are rejected
+  Json to_json() const;
+};
+
+std::string now_rfc3339();
+std::string random_hex(int bytes);
+std::string md5_hex(const std::string& s);
+
+class Master {
+ public:
+  explicit Master(const MasterConfig& cfg);
+  ~Master();
+  int start();         // binds the API port, starts actors, restores experiments; returns the bound port
+  void run_forever();  // blocks in the HTTP accept loop
+  void stop();
+
+  MasterConfig cfg;
+  Store store;
+  ActorSystem system;
+  HttpServer http;
+  std::unique_ptr<ContainerManager> containers;
+  std::vector<Device> devices;
+  ActorRef rm, logger, experiments_root, commands_root;
+  std::string cluster_id;
+  std::atomic<long long> started_at{0};
+
+  // log ring served at /logs (reference: master/pkg/logger LogBuffer)
+  void log(const std::string& level, const std::string& msg);
+  std::vector<Json> recent_logs(size_t limit);
+
+  // services used by actors
+  long long create_experiment(const Json& resolved_config, const Json& model_definition, long long parent_id, bool activate,
+                              const std::string& owner);
+  ActorRef experiment_actor(long long id);
+  void route_container_event(const ContainerEvent& ev);
+  void route_log(const LogLine& l);
+  void register_container(const std::string& container_id, const ActorRef& owner, long long trial_id);
+  void unregister_container(const std::string& container_id);
+  void spawn_checkpoint_gc(long long experiment_id);
+  std::string model_def_dir(long long experiment_id) const { return cfg.data_dir + "/experiments/" + std::to_string(experiment_id) + "/model_def"; }
+  bool check_auth(const HttpRequest& req, std::string* user);
+
+ private:
+  void register_routes();
+  void restore_experiments();
+  std::mutex log_mu_;
+  std::deque<Json> log_ring_;
+  std::mutex container_mu_;
+  std::map<std::string, std::pair<ActorRef, long long>> container_owner_;
+};
+
+std::unique_ptr<Actor> make_resource_pool(Master* m);
+std::unique_ptr<Actor> make_trial_logger(Master* m);
+std::unique_ptr<Actor> make_experiment(Master* m, long long id, bool restoring);
+std::unique_ptr<Actor> make_command(Master* m, long long id, const Json& spec);
+std::unique_ptr<Actor> make_root();
+
+}  // namespace det

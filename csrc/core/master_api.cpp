@@ -1,0 +1,440 @@
+// master_api.cpp — REST API of the master (JSON over HTTP/1.1). Long-poll endpoints serve the harness where the
+// reference uses WebSockets (/ws/trial/:exp/:trial/:container). Route groups follow the reference's
+// master/internal/core.go:313-606 and api_*.go: experiments, trials, checkpoints, tasks, searcher preview, agents/slots,
+// users/auth, templates, models, commands/notebooks/shells/tensorboards, master info/logs/config.
+#include <algorithm>
+#include <fstream>
+#include <sstream>
+
+#include "lttb.hpp"
+#include "master.hpp"
+
+namespace det {
+
+namespace {
+Json obj(std::initializer_list<std::pair<const char*, Json>> kv) {
+  Json j = Json::object();
+  for (auto& p : kv) j[p.first] = p.second;
+  return j;
+}
+Json arr(const std::vector<Json>& v) {
+  Json a = Json::array();
+  for (auto& x : v) a.push_back(x);
+  return a;
+}
+HttpResponse ok(const Json& j) { return HttpResponse::json(j); }
+HttpResponse not_found(const std::string& what) { return HttpResponse::error(404, what + " not found"); }
+
+Json experiment_summary(Store& store, const Json& e) {
+  Json out = e.deep_copy();
+  const long long id = e["id"].as_int();
+  long long n = 0;
+  for (auto& t : store.list("trials", [&](const Json& r) { return r["experiment_id"].as_int() == id; })) { (void)t; ++n; }
+  out["num_trials"] = n;
+  return out;
+}
+Json trial_detail(Store& store, const Json& t, bool with_metrics) {
+  Json out = t.deep_copy();
+  const std::string key = std::to_string(t["id"].as_int());
+  auto steps = store.series("steps", key);
+  auto vals = store.series("validations", key);
+  out["total_batches_processed"] = steps.empty() ? 0 : steps.back()["total_batches"].as_int();
+  out["num_steps"] = static_cast<long long>(steps.size());
+  if (with_metrics) { out["steps"] = arr(steps); out["validations"] = arr(vals); }
+  Json ck = Json::array();
+  for (auto& c : store.list("checkpoints", [&](const Json& r) { return r["trial_id"].as_int() == t["id"].as_int(); })) ck.push_back(c);
+  out["checkpoints"] = ck;
+  if (!vals.empty()) out["latest_validation"] = vals.back();
+  return out;
+}
+}  // namespace
+
+void Master::register_routes() {
+  Master* m = this;
+  http.set_middleware([m](const HttpRequest& req, HttpResponse& resp) {
+    // harness / agent callbacks and login are exempt; everything else needs a session when auth is required
+    static const char* open[] = {"/api/v1/auth/login", "/api/v1/trials/", "/api/v1/trial_logs", "/api/v1/master", "/info", "/api/v1/agents/"};
+    for (auto* p : open) if (req.path.rfind(p, 0) == 0) return true;
+    if (m->check_auth(req, nullptr)) return true;
+    resp = HttpResponse::error(401, "authentication required: POST /api/v1/auth/login");
+    return false;
+  });
+
+  // ---- master ----
+  auto info = [m](const HttpRequest&) {
+    return ok(obj({{"version", "0.13.10.dev0+b200.1"}, {"master_id", m->cluster_id}, {"cluster_id", m->cluster_id}, {"cluster_name", m->cfg.cluster_name},
+                   {"uptime_s", static_cast<long long>(std::time(nullptr)) - m->started_at.load()}, {"scheduler", m->cfg.scheduler}}));
+  };
+  http.route("GET", "/info", info);
+  http.route("GET", "/api/v1/master", info);
+  http.route("GET", "/api/v1/master/config", [m](const HttpRequest&) { return ok(m->cfg.to_json()); });
+  http.route("GET", "/logs", [m](const HttpRequest& r) { return ok(arr(m->recent_logs(static_cast<size_t>(r.qi("limit", 1000))))); });
+  http.route("GET", "/api/v1/master/logs", [m](const HttpRequest& r) { return ok(arr(m->recent_logs(static_cast<size_t>(r.qi("limit", 1000))))); });
+
+  // ---- auth / users ----
+  http.route("POST", "/api/v1/auth/login", [m](const HttpRequest& r) {
+    Json b = r.json();
+    Json u = m->store.get("users", b["username"].as_string());
+    if (u.is_null() || !u["active"].as_bool(true)) return HttpResponse::error(403, "invalid credentials");
+    const std::string want = u["password_hash"].as_string();
+    const std::string got = b["password"].as_string().empty() ? "" : md5_hex(u["salt"].as_string() + b["password"].as_string());
+    if (want != got) return HttpResponse::error(403, "invalid credentials");
+    const std::string token = random_hex(24);
+    m->store.put("sessions", token, obj({{"username", u["username"]}, {"created", now_rfc3339()}}));
+    return ok(obj({{"token", token}, {"user", obj({{"username", u["username"]}, {"admin", u["admin"]}})}}));
+  });
+  http.route("POST", "/api/v1/auth/logout", [m](const HttpRequest& r) {
+    auto it = r.headers.find("authorization");
+    if (it != r.headers.end() && it->second.rfind("Bearer ", 0) == 0) m->store.del("sessions", it->second.substr(7));
+    return ok(Json::object());
+  });
+  http.route("GET", "/api/v1/auth/user", [m](const HttpRequest& r) { std::string u; m->check_auth(r, &u); return ok(obj({{"username", u}})); });
+  http.route("GET", "/api/v1/users", [m](const HttpRequest&) {
+    Json a = Json::array();
+    for (auto& u : m->store.list("users")) a.push_back(obj({{"username", u["username"]}, {"admin", u["admin"]}, {"active", u["active"]}, {"agent_user_group", u["agent_user_group"]}}));
+    return ok(a);
+  });
+  http.route("POST", "/api/v1/users", [m](const HttpRequest& r) {
+    Json b = r.json();
+    const std::string name = b["username"].as_string();
+    if (name.empty()) return HttpResponse::error(400, "username required");
+    if (m->store.exists("users", name)) return HttpResponse::error(409, "user exists");
+    m->store.put("users", name, obj({{"username", name}, {"admin", b["admin"].as_bool(false)}, {"active", true}, {"password_hash", ""}, {"salt", ""}}));
+    return ok(obj({{"username", name}}));
+  });
+  http.route("PATCH", "/api/v1/users/:name", [m](const HttpRequest& r) {
+    Json u = m->store.get("users", r.params.at("name"));
+    if (u.is_null()) return not_found("user");
+    Json b = r.json(), upd = Json::object();
+    if (b.contains("password")) {
+      const std::string salt = random_hex(8);
+      upd["salt"] = salt;
+      upd["password_hash"] = b["password"].as_string().empty() ? "" : md5_hex(salt + b["password"].as_string());
+    }
+    for (const char* k : {"active", "admin", "agent_user_group"}) if (b.contains(k)) upd[k] = b[k];
+    m->store.update("users", r.params.at("name"), upd);
+    return ok(obj({{"username", r.params.at("name")}}));
+  });
+
+  // ---- experiments ----
+  http.route("POST", "/api/v1/experiments", [m](const HttpRequest& r) {
+    Json b = r.json();
+    Json tmpl;
+    if (b["template"].is_string()) {
+      tmpl = m->store.get("templates", b["template"].as_string())["config"];
+      if (tmpl.is_null()) return HttpResponse::error(404, "template " + b["template"].as_string() + " not found");
+    }
+    Json cfg;
+    try {
+      cfg = resolve_experiment_config(b["config"], m->cfg.checkpoint_storage.is_object() ? &m->cfg.checkpoint_storage : nullptr,
+                                      tmpl.is_object() ? &tmpl : nullptr, static_cast<unsigned>(std::time(nullptr)));
+    } catch (const std::exception& e) {
+      return HttpResponse::error(400, std::string("invalid experiment configuration: ") + e.what());
+    }
+    auto errs = validate_experiment_config(cfg);
+    if (!errs.empty()) {
+      std::string all;
+      for (auto& e : errs) all += (all.empty() ? "" : "; ") + e;
+      return HttpResponse::error(400, "invalid experiment configuration: " + all);
+    }
+    if (b["validate_only"].as_bool(false)) return ok(obj({{"config", cfg}}));
+    std::string user;
+    m->check_auth(r, &user);
+    const long long id = m->create_experiment(cfg, b["model_definition"], b["parent_id"].as_int(0), b["activate"].is_null() ? true : b["activate"].as_bool(true), user);
+    return HttpResponse::json(obj({{"id", id}, {"config", cfg}}), 201);
+  });
+  http.route("GET", "/api/v1/experiments", [m](const HttpRequest& r) {
+    const bool all = r.q("all") == "true" || r.q("archived") == "true";
+    const std::string state = r.q("state");
+    Json a = Json::array();
+    for (auto& e : m->store.list("experiments", [&](const Json& row) {
+           if (!all && row["archived"].as_bool(false)) return false;
+           return state.empty() || row["state"].as_string() == state;
+         }))
+      a.push_back(experiment_summary(m->store, e));
+    return ok(a);
+  });
+  http.route("GET", "/api/v1/experiments/:id", [m](const HttpRequest& r) {
+    Json e = m->store.get("experiments", r.params.at("id"));
+    if (e.is_null()) return not_found("experiment");
+    Json out = experiment_summary(m->store, e);
+    Json trials = Json::array();
+    const long long id = e["id"].as_int();
+    for (auto& t : m->store.list("trials", [&](const Json& row) { return row["experiment_id"].as_int() == id; })) trials.push_back(trial_detail(m->store, t, r.q("metrics") == "true"));
+    out["trials"] = trials;
+    return ok(out);
+  });
+  http.route("PATCH", "/api/v1/experiments/:id", [m](const HttpRequest& r) {
+    const std::string id = r.params.at("id");
+    Json e = m->store.get("experiments", id);
+    if (e.is_null()) return not_found("experiment");
+    Json b = r.json(), upd = Json::object();
+    for (const char* k : {"description", "labels", "archived"}) if (b.contains(k)) upd[k] = b[k];
+    if (b.contains("archived") && b["archived"].as_bool(false) && !is_terminal_state(e["state"].as_string()))
+      return HttpResponse::error(400, "only experiments in a terminal state can be archived");
+    if (upd.size()) m->store.update("experiments", id, upd);
+    auto actor = m->experiment_actor(atoll(id.c_str()));
+    if (b.contains("state")) {
+      if (!actor) return HttpResponse::error(400, "experiment is in terminal state " + e["state"].as_string());
+      m->system.ask(actor, "set_state", b["state"]);
+    }
+    if (b.contains("resources") && actor) m->system.ask(actor, "set_resources", b["resources"]);
+    return ok(m->store.get("experiments", id));
+  });
+  auto state_route = [m, this](const char* verb, const char* state, bool kill) {
+    http.route("POST", std::string("/api/v1/experiments/:id/") + verb, [m, state, kill](const HttpRequest& r) {
+      const std::string id = r.params.at("id");
+      Json e = m->store.get("experiments", id);
+      if (e.is_null()) return not_found("experiment");
+      auto actor = m->experiment_actor(atoll(id.c_str()));
+      if (!actor) return is_terminal_state(e["state"].as_string()) ? ok(e) : HttpResponse::error(409, "experiment actor is gone");
+      Json resp = kill ? m->system.ask(actor, "kill") : m->system.ask(actor, "set_state", Json(std::string(state)));
+      return ok(obj({{"id", e["id"]}, {"state", resp["state"]}}));
+    });
+  };
+  state_route("activate", "ACTIVE", false);
+  state_route("pause", "PAUSED", false);
+  state_route("cancel", "STOPPING_CANCELED", false);
+  state_route("kill", "STOPPING_CANCELED", true);
+  for (const char* verb : {"archive", "unarchive"}) {
+    const bool val = std::string(verb) == "archive";
+    http.route("POST", std::string("/api/v1/experiments/:id/") + verb, [m, val](const HttpRequest& r) {
+      Json e = m->store.get("experiments", r.params.at("id"));
+      if (e.is_null()) return not_found("experiment");
+      if (val && !is_terminal_state(e["state"].as_string())) return HttpResponse::error(400, "only experiments in a terminal state can be archived");
+      return ok(m->store.update("experiments", r.params.at("id"), obj({{"archived", val}})));
+    });
+  }
+  http.route("DELETE", "/api/v1/experiments/:id", [m](const HttpRequest& r) {
+    Json e = m->store.get("experiments", r.params.at("id"));
+    if (e.is_null()) return not_found("experiment");
+    if (!is_terminal_state(e["state"].as_string())) return HttpResponse::error(400, "only experiments in a terminal state can be deleted");
+    const long long id = e["id"].as_int();
+    for (auto& t : m->store.list("trials", [&](const Json& row) { return row["experiment_id"].as_int() == id; })) m->store.del("trials", std::to_string(t["id"].as_int()));
+    m->store.del("experiments", r.params.at("id"));
+    return ok(Json::object());
+  });
+  http.route("GET", "/api/v1/experiments/:id/checkpoints", [m](const HttpRequest& r) {
+    const long long id = atoll(r.params.at("id").c_str());
+    return ok(arr(m->store.list("checkpoints", [&](const Json& row) { return row["experiment_id"].as_int() == id; })));
+  });
+  http.route("GET", "/api/v1/experiments/:id/model_def", [m](const HttpRequest& r) {
+    // returns the stored files as the same [{path, content}] list that was uploaded
+    const std::string dir = m->model_def_dir(atoll(r.params.at("id").c_str()));
+    Json files = Json::array();
+    std::istringstream ls(run_capture("cd '" + dir + "' && find . -type f | sort"));
+    std::string rel;
+    while (std::getline(ls, rel)) {
+      if (rel.size() < 3) continue;
+      std::ifstream f(dir + "/" + rel.substr(2), std::ios::binary);
+      std::stringstream ss;
+      ss << f.rdbuf();
+      files.push_back(obj({{"path", rel.substr(2)}, {"content", ss.str()}}));
+    }
+    return ok(files);
+  });
+  http.route("GET", "/api/v1/experiments/:id/metrics", [m](const HttpRequest& r) {
+    // metric series per trial, optionally LTTB-downsampled: ?name=loss&type=training|validation&max_points=N
+    const long long id = atoll(r.params.at("id").c_str());
+    const std::string name = r.q("name", "loss"), type = r.q("type", "training");
+    const int max_points = static_cast<int>(r.qi("max_points", 0));
+    Json out = Json::object();
+    for (auto& t : m->store.list("trials", [&](const Json& row) { return row["experiment_id"].as_int() == id; })) {
+      std::vector<std::pair<double, double>> pts;
+      const std::string key = std::to_string(t["id"].as_int());
+      if (type == "training") {
+        for (auto& s : m->store.series("steps", key)) { const Json& v = s["metrics"]["avg_metrics"][name]; if (v.is_number()) pts.emplace_back(s["total_batches"].as_double(), v.as_double()); }
+      } else {
+        for (auto& s : m->store.series("validations", key)) { const Json& v = s["metrics"]["validation_metrics"][name]; if (v.is_number()) pts.emplace_back(s["total_batches"].as_double(), v.as_double()); }
+      }
+      if (max_points > 2) pts = lttb_downsample(pts, max_points);
+      Json a = Json::array();
+      for (auto& p : pts) { Json q = Json::array(); q.push_back(p.first); q.push_back(p.second); a.push_back(q); }
+      out[key] = a;
+    }
+    return ok(out);
+  });
+
+  // ---- trials ----
+  http.route("GET", "/api/v1/trials/:id", [m](const HttpRequest& r) {
+    Json t = m->store.get("trials", r.params.at("id"));
+    if (t.is_null()) return not_found("trial");
+    return ok(trial_detail(m->store, t, r.q("metrics") != "false"));
+  });
+  http.route("GET", "/api/v1/trials/:id/logs", [m](const HttpRequest& r) {
+    m->system.ask(m->logger, "flush");
+    auto lines = m->store.read_logs(atoll(r.params.at("id").c_str()), static_cast<size_t>(r.qi("offset", 0)), static_cast<size_t>(r.qi("limit", 5000)));
+    // filters as in the reference log API: rank, stdtype, level, agent, container, search
+    std::vector<Json> out;
+    for (auto& l : lines) {
+      if (!r.q("rank").empty() && l["rank"].as_int(-1) != r.qi("rank")) continue;
+      if (!r.q("stdtype").empty() && l["stdtype"].as_string() != r.q("stdtype")) continue;
+      if (!r.q("container_id").empty() && l["container_id"].as_string() != r.q("container_id")) continue;
+      if (!r.q("search").empty() && l["message"].as_string().find(r.q("search")) == std::string::npos) continue;
+      out.push_back(l);
+    }
+    return ok(arr(out));
+  });
+  http.route("POST", "/api/v1/trials/:id/kill", [m](const HttpRequest& r) {
+    Json t = m->store.get("trials", r.params.at("id"));
+    if (t.is_null()) return not_found("trial");
+    auto actor = m->system.get("experiments/" + std::to_string(t["experiment_id"].as_int()) + "/" + t["request_id"].as_string());
+    if (actor) m->system.ask(actor, "kill");
+    return ok(Json::object());
+  });
+  // harness side: long-poll for the next workload, report completion
+  http.route("GET", "/api/v1/trials/:id/next_workload", [m](const HttpRequest& r) {
+    Json t = m->store.get("trials", r.params.at("id"));
+    if (t.is_null()) return not_found("trial");
+    auto actor = m->system.get("experiments/" + std::to_string(t["experiment_id"].as_int()) + "/" + t["request_id"].as_string());
+    if (!actor) return ok(obj({{"type", "TERMINATE"}}));
+    Json resp = m->system.ask(actor, "next_workload", Json(), 30000);
+    return ok(resp.is_null() ? obj({{"type", "WAIT"}}) : resp);
+  });
+  http.route("POST", "/api/v1/trials/:id/workload_completed", [m](const HttpRequest& r) {
+    Json t = m->store.get("trials", r.params.at("id"));
+    if (t.is_null()) return not_found("trial");
+    auto actor = m->system.get("experiments/" + std::to_string(t["experiment_id"].as_int()) + "/" + t["request_id"].as_string());
+    if (!actor) return HttpResponse::error(409, "trial is not running");
+    m->system.ask(actor, "workload_completed", r.json(), 30000);
+    return ok(Json::object());
+  });
+  http.route("POST", "/api/v1/trial_logs", [m](const HttpRequest& r) {
+    Json b = r.json();
+    for (auto& l : (b.is_array() ? b : b["logs"]).arr()) m->system.tell(m->logger, "log", l);
+    return ok(Json::object());
+  });
+
+  // ---- checkpoints ----
+  http.route("GET", "/api/v1/checkpoints/:uuid", [m](const HttpRequest& r) {
+    Json c = m->store.get("checkpoints", r.params.at("uuid"));
+    if (c.is_null()) return not_found("checkpoint");
+    Json t = m->store.get("trials", c["trial_id"].as_int());
+    Json e = m->store.get("experiments", c["experiment_id"].as_int());
+    c["hparams"] = t["hparams"];
+    c["experiment_config"] = e["config"];
+    for (auto& v : m->store.series("validations", std::to_string(c["trial_id"].as_int())))
+      if (v["total_batches"].as_int() == c["total_batches"].as_int()) c["validation"] = v;
+    return ok(c);
+  });
+  http.route("POST", "/api/v1/checkpoints/:uuid/metadata", [m](const HttpRequest& r) {
+    Json c = m->store.get("checkpoints", r.params.at("uuid"));
+    if (c.is_null()) return not_found("checkpoint");
+    Json md = c["metadata"].is_object() ? c["metadata"] : Json::object();
+    Json b = r.json();
+    for (auto& kv : b["metadata"].obj()) md[kv.first] = kv.second;
+    for (auto& k : b["remove"].arr()) md.obj().erase(k.as_string());
+    return ok(m->store.update("checkpoints", r.params.at("uuid"), obj({{"metadata", md}})));
+  });
+
+  // ---- cluster ----
+  http.route("GET", "/api/v1/agents", [m](const HttpRequest&) { return ok(m->system.ask(m->rm, "summary")["agents"]); });
+  http.route("GET", "/api/v1/slots", [m](const HttpRequest&) {
+    Json out = Json::array();
+    Json agents = m->system.ask(m->rm, "summary")["agents"];
+    for (auto& a : agents.arr()) for (auto& s : a["slots"].arr()) { Json x = s.deep_copy(); x["agent_id"] = a["id"]; out.push_back(x); }
+    return ok(out);
+  });
+  http.route("GET", "/api/v1/tasks", [m](const HttpRequest&) { return ok(m->system.ask(m->rm, "summary")["tasks"]); });
+  http.route("POST", "/api/v1/agents/:agent/slots/:slot/:verb", [m](const HttpRequest& r) {
+    const std::string verb = r.params.at("verb");
+    if (verb != "enable" && verb != "disable") return HttpResponse::error(400, "verb must be enable or disable");
+    Json ok_ = m->system.ask(m->rm, verb + "_slot", obj({{"agent", r.params.at("agent")}, {"slot", atoll(r.params.at("slot").c_str())}}));
+    return ok_.as_bool(false) ? ok(Json::object()) : not_found("agent");
+  });
+  http.route("POST", "/api/v1/agents/:agent/:verb", [m](const HttpRequest& r) {
+    const std::string verb = r.params.at("verb");
+    if (verb == "register") {  // det-agent on another node announces its devices
+      Json b = r.json();
+      b["id"] = r.params.at("agent");
+      b["registered_time"] = now_rfc3339();
+      m->system.ask(m->rm, "add_agent", b);
+      return ok(obj({{"master_set_agent_options", obj({{"master_info", obj({{"cluster_id", m->cluster_id}})}})}}));
+    }
+    if (verb == "unregister") { m->system.ask(m->rm, "remove_agent", obj({{"id", r.params.at("agent")}})); return ok(Json::object()); }
+    if (verb != "enable" && verb != "disable") return HttpResponse::error(400, "unknown agent verb");
+    m->system.ask(m->rm, verb + "_slot", obj({{"agent", r.params.at("agent")}, {"slot", -1}}));
+    return ok(Json::object());
+  });
+  http.route("POST", "/api/v1/searcher/preview", [](const HttpRequest& r) {
+    Json b = r.json();
+    SearcherConfig cfg = SearcherConfig::from_json(b["searcher"]);
+    std::vector<std::string> errs;
+    cfg.validate(errs);
+    if (!errs.empty()) return HttpResponse::error(400, errs[0]);
+    Searcher s(static_cast<uint32_t>(b["seed"].as_int(0)), new_search_method(cfg), hyperparameters_from_json(b["hyperparameters"]));
+    ValidationFunction vf = [](std::mt19937_64& rng, int, int) { return std::uniform_real_distribution<double>(0, 1)(rng); };
+    SimulationResult sim = simulate(s, b["seed"].as_int(0), vf, true, cfg.metric);
+    return ok(obj({{"results", sim.summary()}, {"trials", static_cast<long long>(sim.results.size())}}));
+  });
+
+  // ---- templates / model registry ----
+  http.route("GET", "/api/v1/templates", [m](const HttpRequest&) { return ok(arr(m->store.list("templates"))); });
+  http.route("GET", "/api/v1/templates/:name", [m](const HttpRequest& r) { Json t = m->store.get("templates", r.params.at("name")); return t.is_null() ? not_found("template") : ok(t); });
+  http.route("PUT", "/api/v1/templates/:name", [m](const HttpRequest& r) {
+    m->store.put("templates", r.params.at("name"), obj({{"name", r.params.at("name")}, {"config", r.json()["config"]}}));
+    return ok(obj({{"name", r.params.at("name")}}));
+  });
+  http.route("DELETE", "/api/v1/templates/:name", [m](const HttpRequest& r) { m->store.del("templates", r.params.at("name")); return ok(Json::object()); });
+  http.route("GET", "/api/v1/models", [m](const HttpRequest&) { return ok(arr(m->store.list("models"))); });
+  http.route("POST", "/api/v1/models", [m](const HttpRequest& r) {
+    Json b = r.json();
+    const std::string name = b["name"].as_string();
+    if (name.empty()) return HttpResponse::error(400, "model name required");
+    if (m->store.exists("models", name)) return HttpResponse::error(409, "model exists");
+    m->store.put("models", name, obj({{"name", name}, {"description", b["description"]}, {"metadata", b["metadata"].is_object() ? b["metadata"] : Json::object()},
+                                      {"creation_time", now_rfc3339()}, {"last_updated_time", now_rfc3339()}, {"num_versions", 0}}));
+    return HttpResponse::json(m->store.get("models", name), 201);
+  });
+  http.route("GET", "/api/v1/models/:name", [m](const HttpRequest& r) { Json t = m->store.get("models", r.params.at("name")); return t.is_null() ? not_found("model") : ok(t); });
+  http.route("PATCH", "/api/v1/models/:name", [m](const HttpRequest& r) {
+    if (!m->store.exists("models", r.params.at("name"))) return not_found("model");
+    Json b = r.json(), upd = obj({{"last_updated_time", now_rfc3339()}});
+    for (const char* k : {"description", "metadata"}) if (b.contains(k)) upd[k] = b[k];
+    return ok(m->store.update("models", r.params.at("name"), upd));
+  });
+  http.route("GET", "/api/v1/models/:name/versions", [m](const HttpRequest& r) { return ok(arr(m->store.series("model_versions", r.params.at("name")))); });
+  http.route("POST", "/api/v1/models/:name/versions", [m](const HttpRequest& r) {
+    Json model = m->store.get("models", r.params.at("name"));
+    if (model.is_null()) return not_found("model");
+    Json b = r.json();
+    Json c = m->store.get("checkpoints", b["checkpoint_uuid"].as_string());
+    if (c.is_null()) return not_found("checkpoint");
+    const long long v = model["num_versions"].as_int() + 1;
+    Json ver = obj({{"version", v}, {"checkpoint", c}, {"creation_time", now_rfc3339()}, {"model", r.params.at("name")}});
+    m->store.append("model_versions", r.params.at("name"), ver);
+    m->store.update("models", r.params.at("name"), obj({{"num_versions", v}, {"last_updated_time", now_rfc3339()}}));
+    return HttpResponse::json(ver, 201);
+  });
+
+  // ---- commands / notebooks / shells / tensorboards: all are command tasks with a type tag ----
+  for (const char* kind : {"commands", "notebooks", "shells", "tensorboards"}) {
+    const std::string type = std::string(kind).substr(0, strlen(kind) - 1);
+    http.route("POST", std::string("/api/v1/") + kind, [m, type](const HttpRequest& r) {
+      Json b = r.json();
+      if (!b["argv"].is_array() || b["argv"].size() == 0) return HttpResponse::error(400, "argv (list of strings) is required");
+      const long long id = m->store.next_id("commands");
+      Json spec = obj({{"type", type}, {"description", b["description"].str_or(type)}, {"slots", b["slots"].as_int(0)}, {"argv", b["argv"]},
+                       {"env", b["env"].is_object() ? b["env"] : Json::object()}, {"cwd", b["cwd"].str_or("")}});
+      m->store.put("commands", id, obj({{"id", id}, {"type", type}, {"state", "PENDING"}, {"spec", spec}, {"start_time", now_rfc3339()}}));
+      m->system.actor_of("commands/" + std::to_string(id), make_command(m, id, spec), m->commands_root);
+      return HttpResponse::json(m->store.get("commands", id), 201);
+    });
+    http.route("GET", std::string("/api/v1/") + kind, [m, type](const HttpRequest&) {
+      return ok(arr(m->store.list("commands", [&](const Json& row) { return row["type"].as_string() == type; })));
+    });
+    http.route("GET", std::string("/api/v1/") + kind + "/:id", [m](const HttpRequest& r) {
+      Json c = m->store.get("commands", r.params.at("id"));
+      if (c.is_null()) return not_found("task");
+      c["logs"] = arr(m->store.series("command_logs", r.params.at("id")));
+      return ok(c);
+    });
+    http.route("POST", std::string("/api/v1/") + kind + "/:id/kill", [m](const HttpRequest& r) {
+      auto actor = m->system.get("commands/" + r.params.at("id"));
+      if (actor) m->system.ask(actor, "kill");
+      return ok(Json::object());
+    });
+  }
+}
+
+}  // namespace det
