@@ -1,0 +1,186 @@
+"""Trial runner entrypoint (``python -m determined_b200.exec.harness``), launched by the master per allocation.
+
+Reads the ``DET_*`` environment contract, validates checkpoint storage by a write/read/delete round trip, restores
+the latest checkpoint, builds the layer pipeline (master channel → workload manager → rank broadcast → controller)
+and runs it. With more than one slot it first re-executes itself once per GPU (``RANK`` / ``LOCAL_RANK`` /
+``WORLD_SIZE`` set, output prefixed ``[rank=N]``) — no ssh, no horovodrun.
+Parity: reference ``harness/determined/exec/harness.py:43-223``, ``exec/worker_process.py:19-59``,
+``exec/worker_process_wrapper.py:15-54``, ``layers/_worker_process.py:75-339``.
+"""
+from __future__ import annotations
+
+import contextlib
+import faulthandler
+import json
+import logging
+import os
+import pathlib
+import socket
+import subprocess
+import sys
+import threading
+from typing import Any, Dict, Iterator, List, Optional
+
+ENVIRONMENT_VARIABLE_KEYS = {
+    "DET_MASTER_ADDR", "DET_MASTER_PORT", "DET_CONTAINER_ID", "DET_SLOT_IDS", "DET_USE_GPU", "DET_EXPERIMENT_ID",
+    "DET_TRIAL_ID", "DET_TRIAL_SEED", "DET_EXPERIMENT_CONFIG", "DET_HPARAMS", "DET_INITIAL_WORKLOAD",
+    "DET_LATEST_CHECKPOINT", "DET_WORKLOAD_MANAGER_TYPE", "DET_RENDEZVOUS_PORTS", "DET_TRIAL_RUNNER_NETWORK_INTERFACE",
+    "DET_CLUSTER_ID",
+}
+
+
+def _free_port() -> int:
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def build_env():
+    from determined_b200 import workload as wl
+    from determined_b200._env import EnvContext
+
+    missing = sorted(k for k in ENVIRONMENT_VARIABLE_KEYS if k not in os.environ)
+    if missing:
+        raise RuntimeError(f"harness environment is missing: {missing}")
+    e = os.environ
+    slot_ids = json.loads(e["DET_SLOT_IDS"])
+    latest = json.loads(e["DET_LATEST_CHECKPOINT"])
+    use_gpu = e["DET_USE_GPU"].lower() == "true"
+    return EnvContext(
+        master_addr=e["DET_MASTER_ADDR"], master_port=int(e["DET_MASTER_PORT"]), container_id=e["DET_CONTAINER_ID"],
+        experiment_config=json.loads(e["DET_EXPERIMENT_CONFIG"]), hparams=json.loads(e["DET_HPARAMS"]),
+        initial_workload=wl.Workload.from_json(json.loads(e["DET_INITIAL_WORKLOAD"])), latest_checkpoint=latest or None,
+        use_gpu=use_gpu, container_gpus=[f"slot-{i}" for i in slot_ids] if use_gpu else [], slot_ids=slot_ids,
+        debug=e.get("DET_DEBUG", "false").lower() == "true", workload_manager_type=e["DET_WORKLOAD_MANAGER_TYPE"],
+        det_rendezvous_ports=e["DET_RENDEZVOUS_PORTS"],
+        det_trial_runner_network_interface=e["DET_TRIAL_RUNNER_NETWORK_INTERFACE"], det_trial_id=e["DET_TRIAL_ID"],
+        det_experiment_id=e["DET_EXPERIMENT_ID"], det_cluster_id=e["DET_CLUSTER_ID"], trial_seed=int(e["DET_TRIAL_SEED"]))
+
+
+def _pump(stream, rank: int, out) -> None:
+    for line in iter(stream.readline, b""):
+        out.write(f"[rank={rank}] ".encode() + line)
+        out.flush()
+
+
+def launch_workers(n: int) -> int:
+    """One worker process per slot on this machine; any worker failing takes the gang down."""
+    port = _free_port()
+    procs: List[subprocess.Popen] = []
+    threads = []
+    for rank in range(n):
+        env = dict(os.environ, RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(n), LOCAL_WORLD_SIZE=str(n),
+                   MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), DET_WORKER_PROCESS="1")
+        p = subprocess.Popen([sys.executable, "-m", "determined_b200.exec.harness"], env=env, stdout=subprocess.PIPE,
+                             stderr=subprocess.STDOUT)
+        procs.append(p)
+        t = threading.Thread(target=_pump, args=(p.stdout, rank, sys.stdout.buffer), daemon=True)
+        t.start()
+        threads.append(t)
+    rc = 0
+    import time
+
+    while procs:
+        alive = []
+        for p in procs:
+            code = p.poll()
+            if code is None:
+                alive.append(p)
+            elif code != 0 and rc == 0:
+                rc = code
+        if rc != 0:
+            for p in alive:
+                p.kill()
+            break
+        procs = alive
+        time.sleep(0.2)
+    for t in threads:
+        t.join(timeout=2)
+    return rc
+
+
+def run_worker() -> int:
+    import torch
+
+    from determined_b200 import load, storage
+    from determined_b200 import workload as wl
+    from determined_b200._env import DistributedContext
+    from determined_b200._execution import InvalidHP
+    from determined_b200.layers import BroadcastWorkloads, HarnessProfiler, MasterWorkloadSource, build_workload_manager
+    from determined_b200.parallel.comm import Communicator, make_communicator
+
+    env = build_env()
+    if env.debug:
+        faulthandler.dump_traceback_later(30, repeat=True)
+    logging.basicConfig(level=logging.DEBUG if env.debug else logging.INFO, format="%(levelname)s: %(message)s")
+    dist = DistributedContext.from_environ()
+    is_chief = dist.get_rank() == 0
+    n_slots = max(len(env.slot_ids), 1)
+    env.experiment_config.setdefault("resources", {})["slots_per_trial"] = max(dist.get_size(), 1) if dist.get_size() > 1 else env.experiment_config.get("resources", {}).get("slots_per_trial", 1)
+    env._per_slot_batch_size, env._global_batch_size = env._calculate_batch_sizes()
+    device = torch.device("cuda", dist.get_local_rank()) if (env.use_gpu and torch.cuda.is_available()) else torch.device("cpu")
+    if device.type == "cuda":
+        torch.cuda.set_device(device)
+    comm = make_communicator(device) if dist.get_size() > 1 else Communicator()
+
+    storage_cfg = env.experiment_config.get("checkpoint_storage") or {"type": "shared_fs", "host_path": "/tmp/determined-checkpoints"}
+    if is_chief:
+        storage.validate_config(storage_cfg)
+    storage_mgr = storage.build(storage_cfg)
+
+    source = MasterWorkloadSource(env) if is_chief else None
+    profiler = HarnessProfiler(use_gpu=env.use_gpu) if (env.debug and is_chief) else None
+
+    def profiled(stream: wl.Stream) -> wl.Stream:
+        for w, a, r in stream:
+            if profiler:
+                profiler.start()
+            yield w, a, r
+            if profiler:
+                profiler.stop()
+                profiler.serialize(f"/tmp/step-{w.step_id}-{w.kind.name}")
+
+    chief_stream = iter(build_workload_manager(env, profiled(iter(source)), is_chief=True)) if is_chief else None
+    if not is_chief:
+        # non-chief ranks still need checkpoint args shaped like the chief's; the broadcast layer provides them
+        pass
+    workloads = iter(BroadcastWorkloads(comm, chief_stream))
+
+    with contextlib.ExitStack() as stack:
+        load_path: Optional[pathlib.Path] = None
+        if env.latest_checkpoint:
+            meta = storage.StorageMetadata.from_json(env.latest_checkpoint)
+            load_path = pathlib.Path(stack.enter_context(storage_mgr.restore_path(meta)))
+            logging.info(f"Restoring trial from checkpoint {meta.storage_id}")
+        try:
+            controller = load.prepare_controller_with_comm(env, workloads, load_path, dist, comm)
+            controller.run()
+        except InvalidHP as e:
+            logging.info(f"InvalidHP raised by the trial: {e}")
+            if is_chief and source is not None:
+                source.report_invalid_hp()
+    if dist.get_size() > 1:
+        try:
+            comm.barrier()
+        except Exception:
+            pass
+    return 0
+
+
+def main() -> int:
+    if os.environ.get("DET_WORKER_PROCESS") == "1" or int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        return run_worker()
+    slot_ids = json.loads(os.environ.get("DET_SLOT_IDS", "[]"))
+    cfg = json.loads(os.environ.get("DET_EXPERIMENT_CONFIG", "{}"))
+    native_parallel = cfg.get("resources", {}).get("native_parallel", False)
+    n = len(slot_ids)
+    if n > 1:
+        # `native_parallel: true` (nn.DataParallel in the reference) maps onto the same multi-process path
+        if native_parallel:
+            print("native_parallel requested: using the multi-process data-parallel path", flush=True)
+        return launch_workers(n)
+    return run_worker()
+
+
+if __name__ == "__main__":
+    sys.exit(main())

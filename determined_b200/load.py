@@ -147,6 +147,16 @@ def load_controller_from_trial(trial_class: Type, env: EnvContext, workloads: wl
                                        load_path=load_path, rendezvous_info=rendezvous_info)
 
 
+def prepare_controller_with_comm(env: EnvContext, workloads: wl.Stream, load_path: Optional[pathlib.Path],
+                                 dist: DistributedContext, comm: Any) -> Any:
+    """Worker-process entry: like :func:`prepare_controller` but with the trial's communicator already built (the
+    workload broadcast layer needs it before the controller exists)."""
+    cfg = env.experiment_config
+    native = cfg.get("internal", {}) and cfg["internal"].get("native", {}).get("command")
+    trial_class = load_native_implementation(env, dist, list(native)) if native else trial_class_from_entrypoint(cfg["entrypoint"])
+    return load_controller_from_trial(trial_class, env, workloads, load_path, None, dist, comm=comm)
+
+
 def prepare_controller(env: EnvContext, workloads: wl.Stream, load_path: Optional[pathlib.Path],
                        rendezvous_info: Optional[RendezvousInfo], dist: Optional[DistributedContext] = None) -> Any:
     """Entry used by worker processes: resolve the trial class from the experiment config and build its

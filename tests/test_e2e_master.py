@@ -1,0 +1,138 @@
+"""End-to-end on CPU: the C++ master daemon with artificial slots, experiments submitted through the SDK, real harness
+processes. Mirrors the reference's e2e_cpu tier (create → wait COMPLETED → verify metadata), which needs docker there."""
+import os
+import pathlib
+import subprocess
+import sys
+import time
+
+import pytest
+
+from determined_b200.experimental.client import APIError, Determined
+
+ROOT = pathlib.Path(__file__).resolve().parent.parent
+MASTER = ROOT / "determined_b200" / "_lib" / "det-master"
+MODEL_DIR = str(ROOT / "tests" / "fixtures" / "xor_model_def")
+
+
+def base_config(tmp, searcher, hp=None, **extra):
+    cfg = {"entrypoint": "model_def:XorTrial", "description": "e2e",
+           "hyperparameters": dict({"global_batch_size": 8, "hidden_size": 4, "learning_rate": 0.5}, **(hp or {})),
+           "searcher": searcher, "scheduling_unit": 10,
+           "checkpoint_storage": {"type": "shared_fs", "host_path": str(tmp / "ckpts")}, "max_restarts": 2}
+    cfg.update(extra)
+    return cfg
+
+
+@pytest.fixture(scope="module")
+def master(tmp_path_factory):
+    from determined_b200 import _build
+
+    _build.build_core()
+    tmp = tmp_path_factory.mktemp("master")
+    port_file = tmp / "port"
+    env = dict(os.environ, DET_CONFIG_DIR=str(tmp / "cfg"))
+    proc = subprocess.Popen([str(MASTER), "--port", "0", "--data-dir", str(tmp / "data"), "--artificial-slots", "4", "--repo-root", str(ROOT),
+                             "--python", sys.executable, "--print-port-file", str(port_file)],
+                            stdout=open(tmp / "master.log", "w"), stderr=subprocess.STDOUT, env=env)
+    for _ in range(100):
+        if port_file.exists() and port_file.read_text().strip():
+            break
+        time.sleep(0.05)
+    port = int(port_file.read_text())
+    os.environ["DET_CONFIG_DIR"] = str(tmp / "cfg")
+    yield {"url": f"127.0.0.1:{port}", "tmp": tmp, "proc": proc, "port": port}
+    proc.terminate()
+    try:
+        proc.wait(timeout=5)
+    except Exception:
+        proc.kill()
+
+
+def test_single_experiment_completes_with_checkpoint_and_logs(master):
+    d = Determined(master["url"])
+    exp = d.create_experiment(base_config(master["tmp"], {"name": "single", "metric": "validation_loss", "max_length": {"batches": 30}}), MODEL_DIR)
+    assert exp.wait(timeout=120) == "COMPLETED"
+    desc = exp.describe(metrics=True)
+    assert desc["progress"] == 1.0 and len(desc["trials"]) == 1
+    t = desc["trials"][0]
+    assert t["state"] == "COMPLETED" and t["total_batches_processed"] == 30 and len(t["steps"]) == 3
+    assert len(t["validations"]) >= 1 and "validation_loss" in t["validations"][-1]["metrics"]["validation_metrics"]
+    ck = d.get_trial(t["id"]).select_checkpoint(latest=True)
+    assert ck.batch_number == 30 and "state_dict.pth" in ck.resources and ck.framework.startswith("torch")
+    path = ck.download(str(master["tmp"] / "dl"))
+    assert (pathlib.Path(path) / "state_dict.pth").exists() and (pathlib.Path(path) / "metadata.json").exists()
+    trial = ck.load(str(master["tmp"] / "dl2"))
+    assert hasattr(trial, "model")
+    logs = d.get_trial(t["id"]).logs()
+    assert any("Saved trial to checkpoint" in l["message"] or "checkpoint" in l["message"].lower() for l in logs)
+    ck.add_metadata({"note": "best"})
+    assert d.get_checkpoint(ck.uuid).metadata["note"] == "best"
+
+
+def test_adaptive_asha_packs_trials_and_gc_runs(master):
+    d = Determined(master["url"])
+    cfg = base_config(master["tmp"], {"name": "adaptive_asha", "metric": "validation_loss", "max_length": {"batches": 40}, "max_trials": 6,
+                                      "max_rungs": 2, "divisor": 4, "mode": "aggressive", "max_concurrent_trials": 4},
+                      hp={"learning_rate": {"type": "log", "minval": -2, "maxval": 0, "base": 10}, "hidden_size": {"type": "int", "minval": 2, "maxval": 8}})
+    exp = d.create_experiment(cfg, MODEL_DIR)
+    assert exp.wait(timeout=300) == "COMPLETED"
+    desc = exp.describe()
+    assert len(desc["trials"]) == 6
+    lens = sorted(t["total_batches_processed"] for t in desc["trials"])
+    assert lens[0] == 10 and lens[-1] == 40  # bottom rung 10 batches, promoted trials reach 40
+    best = exp.top_checkpoint()
+    assert best.uuid
+    time.sleep(1.5)  # GC is asynchronous
+    states = [c["state"] for c in d._session.get(f"/api/v1/experiments/{exp.id}/checkpoints")]
+    assert "COMPLETED" in states
+
+
+def test_pause_activate_cancel_and_validation_errors(master):
+    d = Determined(master["url"])
+    exp = d.create_experiment(base_config(master["tmp"], {"name": "single", "metric": "validation_loss", "max_length": {"batches": 4000}}),
+                              MODEL_DIR, activate=False)
+    assert exp.describe()["state"] == "PAUSED"
+    exp.activate()
+    time.sleep(3)
+    exp.pause()
+    time.sleep(2)
+    assert exp.describe()["state"] == "PAUSED"
+    exp.cancel()
+    assert exp.wait(timeout=60) == "CANCELED"
+    with pytest.raises(APIError) as e:
+        d.create_experiment({"entrypoint": "m:T", "hyperparameters": {}, "searcher": {"name": "single", "metric": "x"}}, MODEL_DIR)
+    assert "global_batch_size" in str(e.value)
+
+
+def test_failure_restarts_then_errors(master):
+    d = Determined(master["url"])
+    exp = d.create_experiment(base_config(master["tmp"], {"name": "single", "metric": "validation_loss", "max_length": {"batches": 30}},
+                                          hp={"chaos_probability": 1.0}, max_restarts=1), MODEL_DIR)
+    assert exp.wait(timeout=180) == "ERROR"
+    t = exp.describe()["trials"][0]
+    assert t["restarts"] == 2 and t["state"] == "ERROR"
+
+
+def test_cluster_endpoints_and_registry(master):
+    d = Determined(master["url"])
+    s = d._session
+    agents = s.get("/api/v1/agents")
+    assert agents[0]["id"] == "agent-local" and agents[0]["num_slots"] == 4
+    assert len(s.get("/api/v1/slots")) == 4
+    prev = s.post("/api/v1/searcher/preview", {"searcher": {"name": "random", "metric": "m", "max_trials": 3, "max_length": {"batches": 5}},
+                                               "hyperparameters": {"global_batch_size": 1}})
+    assert prev["results"] == {"5B V": 3}
+    s.request("PUT", "/api/v1/templates/small", {"config": {"scheduling_unit": 7}})
+    assert s.get("/api/v1/templates/small")["config"]["scheduling_unit"] == 7
+    m = d.create_model("xor", "demo")
+    assert [x.name for x in d.get_models()] == ["xor"]
+    assert s.post("/api/v1/auth/login", {"username": "determined", "password": ""})["token"]
+    cmd = s.post("/api/v1/commands", {"argv": ["sh", "-c", "echo hello-from-command"], "description": "echo"})
+    for _ in range(50):
+        c = s.get(f"/api/v1/commands/{cmd['id']}")
+        if c["state"] == "TERMINATED":
+            break
+        time.sleep(0.1)
+    assert c["state"] == "TERMINATED" and any("hello-from-command" in l["message"] for l in c["logs"])
+    del m
