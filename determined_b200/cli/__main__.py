@@ -1,0 +1,558 @@
+"""``det`` command line (``python -m determined_b200.cli`` or the ``det`` script at the repository root).
+
+Verbs follow the reference CLI (``cli/determined_cli/cli.py:40-283``, ``experiment.py:630-924``):
+``experiment {list,describe,config,create,activate,pause,cancel,kill,archive,unarchive,delete,wait,label,set,
+list-trials,list-checkpoints,download-model-def}``, ``trial {describe,logs,kill,download}``,
+``checkpoint {describe,download}``, ``task list``, ``preview-search``, ``slot``/``agent``, ``master {config,logs,info}``,
+``user``, ``template``, ``model``, ``cmd``/``notebook``/``shell``/``tensorboard``, plus ``master up`` / ``agent detect``
+that wrap the native daemons.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import pathlib
+import subprocess
+import sys
+import time
+from typing import Any, Dict, List, Optional
+
+import yaml
+
+from ..experimental.client import APIError, Determined, Session, read_context
+
+LIB = pathlib.Path(__file__).resolve().parent.parent / "_lib"
+ROOT = pathlib.Path(__file__).resolve().parent.parent.parent
+
+
+def _table(rows: List[List[Any]], headers: List[str]) -> str:
+    try:
+        from tabulate import tabulate
+
+        return tabulate(rows, headers, tablefmt="presto")
+    except Exception:
+        widths = [max(len(str(x)) for x in col) for col in zip(headers, *rows)] if rows else [len(h) for h in headers]
+        line = lambda r: " | ".join(str(x).ljust(w) for x, w in zip(r, widths))  # noqa: E731
+        return "\n".join([line(headers), "-+-".join("-" * w for w in widths)] + [line(r) for r in rows])
+
+
+def _load_config(path: str, overrides: Optional[List[str]] = None) -> Dict[str, Any]:
+    cfg = yaml.safe_load(pathlib.Path(path).read_text()) or {}
+    for ov in overrides or []:  # --config key.sub=value
+        key, _, val = ov.partition("=")
+        cur = cfg
+        parts = key.split(".")
+        for p in parts[:-1]:
+            cur = cur.setdefault(p, {})
+        cur[parts[-1]] = yaml.safe_load(val)
+    return cfg
+
+
+def _follow_logs(d: Determined, exp_id: int) -> str:
+    seen: Dict[int, int] = {}
+    while True:
+        desc = d.get_experiment(exp_id).describe()
+        for t in desc["trials"]:
+            off = seen.get(t["id"], 0)
+            for l in d._session.get(f"/api/v1/trials/{t['id']}/logs?offset={off}"):
+                prefix = f"[trial {t['id']}" + (f" rank={l['rank']}]" if l.get("rank") is not None else "]")
+                print(prefix, l["message"], flush=True)
+                off += 1
+            seen[t["id"]] = off
+        if desc["state"] in ("COMPLETED", "CANCELED", "ERROR"):
+            return desc["state"]
+        time.sleep(1.0)
+
+
+# ---- experiment ------------------------------------------------------------------------------------------------------
+def experiment_create(a: argparse.Namespace) -> int:
+    cfg = _load_config(a.config_file, a.config)
+    if a.local:
+        if not a.test_mode:
+            raise SystemExit("local training is only supported in test mode: add --test-mode")
+        from .. import _execution, load
+        from ..experimental import test_one_batch
+
+        with _execution.local_execution_manager(pathlib.Path(a.model_def)):
+            trial_class = load.trial_class_from_entrypoint(cfg["entrypoint"])
+            test_one_batch(trial_class=trial_class, config=cfg)
+        print("Model definition test succeeded! 🎉")
+        return 0
+    d = Determined(a.master, a.user)
+    if a.test_mode:
+        from .._execution import make_test_experiment_config
+
+        cfg = make_test_experiment_config(cfg)
+    exp = d.create_experiment(cfg, a.model_def, activate=not a.paused, template=a.template)
+    print(f"Created experiment {exp.id}")
+    if a.follow or a.test_mode:
+        state = _follow_logs(d, exp.id)
+        print(f"Experiment {exp.id} finished: {state}")
+        return 0 if state == "COMPLETED" else 1
+    return 0
+
+
+def experiment_list(a: argparse.Namespace) -> int:
+    d = Determined(a.master, a.user)
+    exps = d._session.get("/api/v1/experiments" + ("?all=true" if a.all else ""))
+    rows = [[e["id"], e.get("owner"), (e.get("description") or "")[:40], e["state"], f"{100 * (e.get('progress') or 0):.1f}%",
+             e["start_time"][:19], (e.get("end_time") or "")[:19], e.get("num_trials")] for e in exps]
+    print(_table(rows, ["ID", "Owner", "Description", "State", "Progress", "Start Time", "End Time", "Trials"]))
+    return 0
+
+
+def experiment_describe(a: argparse.Namespace) -> int:
+    d = Determined(a.master, a.user)
+    out = [d.get_experiment(int(i)).describe(metrics=a.metrics) for i in a.experiment_ids.split(",")]
+    if a.json:
+        print(json.dumps(out, indent=2))
+        return 0
+    for e in out:
+        print(_table([[e["id"], e["state"], f"{100 * (e.get('progress') or 0):.1f}%", e["start_time"][:19], (e.get("end_time") or "")[:19],
+                       e.get("description"), e.get("archived"), ",".join(e.get("labels") or [])]],
+                     ["Experiment ID", "State", "Progress", "Start", "End", "Description", "Archived", "Labels"]))
+        rows = [[t["id"], t["state"], json.dumps(t["hparams"]), t["total_batches_processed"], t.get("restarts"),
+                 (t.get("latest_validation") or {}).get("metrics", {}).get("validation_metrics")] for t in e["trials"]]
+        print(_table(rows, ["Trial ID", "State", "H-Params", "Batches", "Restarts", "Latest Validation"]))
+    return 0
+
+
+def _simple_exp(verb: str):
+    def run(a: argparse.Namespace) -> int:
+        exp = Determined(a.master, a.user).get_experiment(a.experiment_id)
+        getattr(exp, verb)()
+        print(f"{verb.capitalize()}d experiment {a.experiment_id}".replace("eed", "ed"))
+        return 0
+    return run
+
+
+def experiment_wait(a: argparse.Namespace) -> int:
+    state = Determined(a.master, a.user).get_experiment(a.experiment_id).wait(interval=a.polling_interval)
+    print(f"Experiment {a.experiment_id} is {state}")
+    return 0 if state == "COMPLETED" else 1
+
+
+def experiment_config(a: argparse.Namespace) -> int:
+    print(yaml.safe_dump(Determined(a.master, a.user).get_experiment(a.experiment_id).describe()["config"], default_flow_style=False))
+    return 0
+
+
+def experiment_set(a: argparse.Namespace) -> int:
+    s = Session(a.master, a.user)
+    body: Dict[str, Any] = {}
+    if a.what == "description":
+        body["description"] = a.value
+    elif a.what in ("max-slots", "weight", "priority"):
+        body["resources"] = {a.what.replace("-", "_"): yaml.safe_load(a.value)}
+    elif a.what == "gc-policy":
+        raise SystemExit("set gc-policy: pass --save-experiment-best/--save-trial-best/--save-trial-latest at create time")
+    s.request("PATCH", f"/api/v1/experiments/{a.experiment_id}", body)
+    print(f"Set {a.what} of experiment {a.experiment_id} to {a.value}")
+    return 0
+
+
+def experiment_label(a: argparse.Namespace) -> int:
+    s = Session(a.master, a.user)
+    labels = set(s.get(f"/api/v1/experiments/{a.experiment_id}").get("labels") or [])
+    (labels.add if a.action == "add" else labels.discard)(a.label)
+    s.request("PATCH", f"/api/v1/experiments/{a.experiment_id}", {"labels": sorted(labels)})
+    return 0
+
+
+def experiment_list_trials(a: argparse.Namespace) -> int:
+    e = Determined(a.master, a.user).get_experiment(a.experiment_id).describe()
+    print(_table([[t["id"], t["state"], json.dumps(t["hparams"]), t["start_time"][:19], (t.get("end_time") or "")[:19], t["total_batches_processed"]]
+                  for t in e["trials"]], ["Trial ID", "State", "H-Params", "Start Time", "End Time", "# of Batches"]))
+    return 0
+
+
+def experiment_list_checkpoints(a: argparse.Namespace) -> int:
+    s = Session(a.master, a.user)
+    cks = s.get(f"/api/v1/experiments/{a.experiment_id}/checkpoints")
+    print(_table([[c["trial_id"], c["total_batches"], c["state"], c["uuid"], (c.get("end_time") or "")[:19]] for c in cks],
+                 ["Trial ID", "# of Batches", "State", "UUID", "End Time"]))
+    return 0
+
+
+def experiment_download_model_def(a: argparse.Namespace) -> int:
+    files = Session(a.master, a.user).get(f"/api/v1/experiments/{a.experiment_id}/model_def")
+    out = pathlib.Path(a.output_dir or f"experiment_{a.experiment_id}_model_def")
+    for f in files:
+        p = out / f["path"]
+        p.parent.mkdir(parents=True, exist_ok=True)
+        p.write_text(f["content"])
+    print(f"Wrote {len(files)} files to {out}")
+    return 0
+
+
+# ---- trial / checkpoint -------------------------------------------------------------------------------------------------
+def trial_describe(a: argparse.Namespace) -> int:
+    t = Determined(a.master, a.user).get_trial(a.trial_id).describe()
+    if a.json:
+        print(json.dumps(t, indent=2))
+        return 0
+    print(_table([[t["id"], t["experiment_id"], t["state"], json.dumps(t["hparams"]), t["start_time"][:19], (t.get("end_time") or "")[:19]]],
+                 ["Trial ID", "Exp ID", "State", "H-Params", "Start Time", "End Time"]))
+    rows = []
+    vals = {v["total_batches"]: v for v in t.get("validations", [])}
+    cks = {c["total_batches"]: c for c in t.get("checkpoints", [])}
+    for s in t.get("steps", []):
+        v, c = vals.get(s["total_batches"]), cks.get(s["total_batches"])
+        rows.append([s["step_id"], s["total_batches"], s["state"], json.dumps(s["metrics"].get("avg_metrics")) if a.metrics else "",
+                     json.dumps(v["metrics"]["validation_metrics"]) if v else "", c["uuid"] if c else ""])
+    print(_table(rows, ["Step", "# of Batches", "State", "Avg Metrics", "Validation Metrics", "Checkpoint UUID"]))
+    return 0
+
+
+def trial_logs(a: argparse.Namespace) -> int:
+    s = Session(a.master, a.user)
+    off = 0
+    while True:
+        q = f"?offset={off}" + (f"&rank={a.rank}" if a.rank is not None else "")
+        lines = s.get(f"/api/v1/trials/{a.trial_id}/logs{q}")
+        for l in lines:
+            print(l["message"], flush=True)
+        off += len(lines)
+        if not a.follow:
+            return 0
+        if s.get(f"/api/v1/trials/{a.trial_id}")["state"] != "ACTIVE" and not lines:
+            return 0
+        time.sleep(1.0)
+
+
+def trial_kill(a: argparse.Namespace) -> int:
+    Determined(a.master, a.user).get_trial(a.trial_id).kill()
+    print(f"Killed trial {a.trial_id}")
+    return 0
+
+
+def trial_download(a: argparse.Namespace) -> int:
+    t = Determined(a.master, a.user).get_trial(a.trial_id)
+    ck = t.select_checkpoint(latest=a.latest, best=a.best, uuid=a.uuid) if (a.latest or a.best or a.uuid) else t.select_checkpoint(latest=True)
+    print("Local checkpoint path:", ck.download(a.output_dir))
+    return 0
+
+
+def checkpoint_describe(a: argparse.Namespace) -> int:
+    c = Session(a.master, a.user).get(f"/api/v1/checkpoints/{a.uuid}")
+    c.pop("experiment_config", None)
+    print(json.dumps(c, indent=2))
+    return 0
+
+
+def checkpoint_download(a: argparse.Namespace) -> int:
+    print("Local checkpoint path:", Determined(a.master, a.user).get_checkpoint(a.uuid).download(a.output_dir))
+    return 0
+
+
+# ---- cluster --------------------------------------------------------------------------------------------------------------
+def task_list(a: argparse.Namespace) -> int:
+    tasks = Session(a.master, a.user).get("/api/v1/tasks")
+    print(_table([[t["id"], t["name"], t["slots_needed"], t["state"], ",".join(c["agent"] for c in t["containers"])] for t in tasks],
+                 ["Task ID", "Name", "Slots Needed", "State", "Agents"]))
+    return 0
+
+
+def preview_search(a: argparse.Namespace) -> int:
+    cfg = _load_config(a.config_file)
+    out = Session(a.master, a.user).post("/api/v1/searcher/preview", {"searcher": cfg["searcher"], "hyperparameters": cfg.get("hyperparameters", {}),
+                                                                       "seed": a.seed})
+    print(f"Using search configuration:\n{yaml.safe_dump(cfg['searcher'], default_flow_style=False)}")
+    print(_table([[n, k] for k, n in sorted(out["results"].items(), key=lambda kv: -kv[1])], ["Trials", "Breakdown"]))
+    return 0
+
+
+def preview_search_local(a: argparse.Namespace) -> int:
+    from ..master import _core
+
+    cfg = _load_config(a.config_file)
+    out = _core.simulate(cfg["searcher"], cfg.get("hyperparameters", {}), seed=a.seed, simulation_seed=a.seed, random_order=True)
+    print(_table([[n, k] for k, n in sorted(out["results"].items(), key=lambda kv: -kv[1])], ["Trials", "Breakdown"]))
+    return 0
+
+
+def agent_list(a: argparse.Namespace) -> int:
+    agents = Session(a.master, a.user).get("/api/v1/agents")
+    print(_table([[x["id"], x.get("registered_time", "")[:19], x["num_slots"], x["num_used_slots"], x.get("label"), x.get("enabled")] for x in agents],
+                 ["Agent ID", "Registered Time", "Slots", "Used", "Label", "Enabled"]))
+    return 0
+
+
+def slot_list(a: argparse.Namespace) -> int:
+    slots = Session(a.master, a.user).get("/api/v1/slots")
+    print(_table([[s["agent_id"], s["id"], s.get("enabled"), s.get("container_id") or "FREE", (s.get("device") or {}).get("type"),
+                   (s.get("device") or {}).get("brand")] for s in slots], ["Agent ID", "Slot ID", "Enabled", "Task", "Type", "Device"]))
+    return 0
+
+
+def slot_toggle(verb: str):
+    def run(a: argparse.Namespace) -> int:
+        Session(a.master, a.user).post(f"/api/v1/agents/{a.agent_id}/slots/{a.slot_id}/{verb}")
+        print(f"{verb}d slot {a.slot_id} of agent {a.agent_id}")
+        return 0
+    return run
+
+
+def agent_toggle(verb: str):
+    def run(a: argparse.Namespace) -> int:
+        Session(a.master, a.user).post(f"/api/v1/agents/{a.agent_id}/{verb}")
+        return 0
+    return run
+
+
+def master_info(a: argparse.Namespace) -> int:
+    print(json.dumps(Session(a.master, a.user).get("/api/v1/master"), indent=2))
+    return 0
+
+
+def master_config(a: argparse.Namespace) -> int:
+    print(yaml.safe_dump(Session(a.master, a.user).get("/api/v1/master/config"), default_flow_style=False))
+    return 0
+
+
+def master_logs(a: argparse.Namespace) -> int:
+    for l in Session(a.master, a.user).get(f"/api/v1/master/logs?limit={a.tail or 1000}"):
+        print(l["time"], l["level"].upper(), l["message"])
+    return 0
+
+
+def master_up(a: argparse.Namespace) -> int:
+    from .. import _build
+
+    _build.build_core()
+    cmd = [str(LIB / "det-master"), "--port", str(a.port), "--data-dir", a.data_dir, "--repo-root", str(ROOT), "--python", sys.executable,
+           "--scheduler", a.scheduler]
+    if a.artificial_slots:
+        cmd += ["--artificial-slots", str(a.artificial_slots)]
+    os.execv(cmd[0], cmd)
+
+
+def agent_detect(a: argparse.Namespace) -> int:
+    from .. import _build
+
+    _build.build_core()
+    return subprocess.call([str(LIB / "det-agent"), "--detect-only"])
+
+
+# ---- users / templates / models / commands ----------------------------------------------------------------------------------
+def user_login(a: argparse.Namespace) -> int:
+    import getpass
+
+    s = Session(a.master, a.username)
+    s.login(getpass.getpass(f"Password for user '{a.username}': ") if sys.stdin.isatty() else "")
+    print(f"Logged in as {a.username}")
+    return 0
+
+
+def user_list(a: argparse.Namespace) -> int:
+    print(_table([[u["username"], u.get("active"), u.get("admin")] for u in Session(a.master, a.user).get("/api/v1/users")], ["Username", "Active", "Admin"]))
+    return 0
+
+
+def user_create(a: argparse.Namespace) -> int:
+    Session(a.master, a.user).post("/api/v1/users", {"username": a.username, "admin": a.admin})
+    print(f"Created user {a.username}")
+    return 0
+
+
+def user_change_password(a: argparse.Namespace) -> int:
+    import getpass
+
+    Session(a.master, a.user).request("PATCH", f"/api/v1/users/{a.username}", {"password": getpass.getpass("New password: ")})
+    return 0
+
+
+def user_activate(active: bool):
+    def run(a: argparse.Namespace) -> int:
+        Session(a.master, a.user).request("PATCH", f"/api/v1/users/{a.username}", {"active": active})
+        return 0
+    return run
+
+
+def template_list(a: argparse.Namespace) -> int:
+    print(_table([[t["name"]] for t in Session(a.master, a.user).get("/api/v1/templates")], ["Name"]))
+    return 0
+
+
+def template_describe(a: argparse.Namespace) -> int:
+    print(yaml.safe_dump(Session(a.master, a.user).get(f"/api/v1/templates/{a.name}")["config"], default_flow_style=False))
+    return 0
+
+
+def template_set(a: argparse.Namespace) -> int:
+    Session(a.master, a.user).request("PUT", f"/api/v1/templates/{a.name}", {"config": _load_config(a.template_file)})
+    print(f"Set template {a.name}")
+    return 0
+
+
+def template_remove(a: argparse.Namespace) -> int:
+    Session(a.master, a.user).request("DELETE", f"/api/v1/templates/{a.name}")
+    return 0
+
+
+def model_list(a: argparse.Namespace) -> int:
+    print(_table([[m.name, m.description, m.creation_time, m.last_updated_time] for m in Determined(a.master, a.user).get_models()],
+                 ["Name", "Description", "Created", "Updated"]))
+    return 0
+
+
+def model_create(a: argparse.Namespace) -> int:
+    Determined(a.master, a.user).create_model(a.name, a.description or "")
+    print(f"Created model {a.name}")
+    return 0
+
+
+def model_describe(a: argparse.Namespace) -> int:
+    m = Determined(a.master, a.user).get_model(a.name)
+    print(json.dumps({"name": m.name, "description": m.description, "metadata": m.metadata,
+                      "versions": [c.uuid for c in m.get_versions()]}, indent=2))
+    return 0
+
+
+def model_register_version(a: argparse.Namespace) -> int:
+    Determined(a.master, a.user).get_model(a.name).register_version(a.uuid)
+    return 0
+
+
+def command_run(kind: str):
+    def run(a: argparse.Namespace) -> int:
+        s = Session(a.master, a.user)
+        argv = a.command if getattr(a, "command", None) else {
+            "notebooks": [sys.executable, "-m", "jupyter", "lab", "--ip=127.0.0.1", "--no-browser"],
+            "shells": ["/bin/sh", "-c", "sleep infinity"],
+            "tensorboards": [sys.executable, "-m", "determined_b200.exec.tensorboard"] + [str(x) for x in getattr(a, "experiment_ids", [])],
+        }[kind]
+        out = s.post(f"/api/v1/{kind}", {"argv": argv, "slots": getattr(a, "slots", 0), "description": " ".join(argv)[:60]})
+        print(f"Started {kind[:-1]} {out['id']}")
+        if getattr(a, "detach", False):
+            return 0
+        seen = 0
+        while True:
+            c = s.get(f"/api/v1/{kind}/{out['id']}")
+            for l in c["logs"][seen:]:
+                print(l["message"], flush=True)
+            seen = len(c["logs"])
+            if c["state"] == "TERMINATED":
+                return int(c.get("exit_code") or 0)
+            time.sleep(0.5)
+    return run
+
+
+def command_list(kind: str):
+    def run(a: argparse.Namespace) -> int:
+        rows = Session(a.master, a.user).get(f"/api/v1/{kind}")
+        print(_table([[c["id"], c["state"], c["spec"]["description"], c["start_time"][:19]] for c in rows], ["ID", "State", "Description", "Start Time"]))
+        return 0
+    return run
+
+
+def command_kill(kind: str):
+    def run(a: argparse.Namespace) -> int:
+        Session(a.master, a.user).post(f"/api/v1/{kind}/{a.id}/kill")
+        return 0
+    return run
+
+
+# ---- parser ---------------------------------------------------------------------------------------------------------------
+def build_parser() -> argparse.ArgumentParser:
+    p = argparse.ArgumentParser(prog="det", description="Determined (B200-native) command line")
+    p.add_argument("-m", "--master", default=None, help="master address (default $DET_MASTER or localhost:8080)")
+    p.add_argument("-u", "--user", default=None)
+    sub = p.add_subparsers(dest="group")
+
+    def group(name: str, aliases: List[str] = []) -> Any:
+        g = sub.add_parser(name, aliases=aliases)
+        return g.add_subparsers(dest="verb")
+
+    def cmd(g: Any, name: str, fn: Any, *args: Any, aliases: List[str] = []) -> argparse.ArgumentParser:
+        c = g.add_parser(name, aliases=aliases)
+        for names, kw in args:
+            c.add_argument(*names, **kw)
+        c.set_defaults(func=fn)
+        return c
+
+    A = lambda *n, **k: (n, k)  # noqa: E731
+    e = group("experiment", ["e"])
+    cmd(e, "create", experiment_create, A("config_file"), A("model_def"), A("--local", action="store_true"), A("--test-mode", "--test", action="store_true"),
+        A("--paused", action="store_true"), A("--follow", "-f", action="store_true"), A("--template"), A("--config", action="append"))
+    cmd(e, "list", experiment_list, A("--all", "-a", action="store_true"), aliases=["ls"])
+    cmd(e, "describe", experiment_describe, A("experiment_ids"), A("--metrics", action="store_true"), A("--json", action="store_true"))
+    cmd(e, "config", experiment_config, A("experiment_id", type=int))
+    for verb in ("activate", "pause", "cancel", "kill", "archive", "unarchive", "delete"):
+        cmd(e, verb, _simple_exp(verb), A("experiment_id", type=int))
+    cmd(e, "wait", experiment_wait, A("experiment_id", type=int), A("--polling-interval", type=float, default=1.0))
+    cmd(e, "set", experiment_set, A("what", choices=["description", "max-slots", "weight", "priority", "gc-policy"]), A("experiment_id", type=int), A("value"))
+    cmd(e, "label", experiment_label, A("action", choices=["add", "remove"]), A("experiment_id", type=int), A("label"))
+    cmd(e, "list-trials", experiment_list_trials, A("experiment_id", type=int), aliases=["lt"])
+    cmd(e, "list-checkpoints", experiment_list_checkpoints, A("experiment_id", type=int), aliases=["lc"])
+    cmd(e, "download-model-def", experiment_download_model_def, A("experiment_id", type=int), A("--output-dir", "-o"))
+    t = group("trial", ["t"])
+    cmd(t, "describe", trial_describe, A("trial_id", type=int), A("--metrics", action="store_true"), A("--json", action="store_true"))
+    cmd(t, "logs", trial_logs, A("trial_id", type=int), A("--follow", "-f", action="store_true"), A("--rank", type=int))
+    cmd(t, "kill", trial_kill, A("trial_id", type=int))
+    cmd(t, "download", trial_download, A("trial_id", type=int), A("--latest", action="store_true"), A("--best", action="store_true"), A("--uuid"), A("--output-dir", "-o"))
+    c = group("checkpoint", ["c"])
+    cmd(c, "describe", checkpoint_describe, A("uuid"))
+    cmd(c, "download", checkpoint_download, A("uuid"), A("--output-dir", "-o"))
+    tk = group("task")
+    cmd(tk, "list", task_list, aliases=["ls"])
+    ps = sub.add_parser("preview-search")
+    ps.add_argument("config_file"), ps.add_argument("--seed", type=int, default=0), ps.add_argument("--offline", action="store_true")
+    ps.set_defaults(func=lambda a: preview_search_local(a) if a.offline else preview_search(a))
+    ag = group("agent", ["a"])
+    cmd(ag, "list", agent_list, aliases=["ls"])
+    cmd(ag, "enable", agent_toggle("enable"), A("agent_id"))
+    cmd(ag, "disable", agent_toggle("disable"), A("agent_id"))
+    cmd(ag, "detect", agent_detect)
+    sl = group("slot", ["s"])
+    cmd(sl, "list", slot_list, aliases=["ls"])
+    cmd(sl, "enable", slot_toggle("enable"), A("agent_id"), A("slot_id"))
+    cmd(sl, "disable", slot_toggle("disable"), A("agent_id"), A("slot_id"))
+    ms = group("master")
+    cmd(ms, "info", master_info)
+    cmd(ms, "config", master_config)
+    cmd(ms, "logs", master_logs, A("--tail", type=int))
+    cmd(ms, "up", master_up, A("--port", type=int, default=8080), A("--data-dir", default="/tmp/determined-master"),
+        A("--scheduler", default="fair_share"), A("--artificial-slots", type=int, default=0))
+    us = group("user", ["u"])
+    cmd(us, "login", user_login, A("username"))
+    cmd(us, "list", user_list, aliases=["ls"])
+    cmd(us, "create", user_create, A("username"), A("--admin", action="store_true"))
+    cmd(us, "change-password", user_change_password, A("username"))
+    cmd(us, "activate", user_activate(True), A("username"))
+    cmd(us, "deactivate", user_activate(False), A("username"))
+    tp = group("template", ["tpl"])
+    cmd(tp, "list", template_list, aliases=["ls"])
+    cmd(tp, "describe", template_describe, A("name"))
+    cmd(tp, "set", template_set, A("name"), A("template_file"))
+    cmd(tp, "remove", template_remove, A("name"), aliases=["rm"])
+    mo = group("model")
+    cmd(mo, "list", model_list, aliases=["ls"])
+    cmd(mo, "create", model_create, A("name"), A("--description"))
+    cmd(mo, "describe", model_describe, A("name"))
+    cmd(mo, "register-version", model_register_version, A("name"), A("uuid"))
+    for name, kind in (("cmd", "commands"), ("notebook", "notebooks"), ("shell", "shells"), ("tensorboard", "tensorboards")):
+        g = group(name)
+        extra = [A("command", nargs=argparse.REMAINDER)] if name == "cmd" else ([A("experiment_ids", nargs="*", type=int)] if name == "tensorboard" else [])
+        cmd(g, "run" if name == "cmd" else "start", command_run(kind), *extra, A("--slots", type=int, default=0), A("--detach", "-d", action="store_true"))
+        cmd(g, "list", command_list(kind), aliases=["ls"])
+        cmd(g, "kill", command_kill(kind), A("id"))
+    return p
+
+
+def main(argv: Optional[List[str]] = None) -> int:
+    parser = build_parser()
+    args = parser.parse_args(argv)
+    if not getattr(args, "func", None):
+        parser.print_help()
+        return 2
+    try:
+        return int(args.func(args) or 0)
+    except APIError as e:
+        print(f"det: {e}", file=sys.stderr)
+        return 1
+
+
+if __name__ == "__main__":
+    sys.exit(main())
