@@ -52,7 +52,7 @@ __device__ __forceinline__ uint4 pack8_bf16(const float* v) {
 // Forward: 256 threads = 4 lane quarters x 2 column halves (64 keys each); 2 CTAs per SM.
 // ------------------------------------------------------------------------------------------------
 constexpr int ATT_FWD_THREADS = 256;
-constexpr uint32_t ATT_FWD_RED = 2 * 2 * ATT_S * 4;  // max + sum exchange
+constexpr uint32_t ATT_FWD_RED = 2 * 2 * ATT_S * 4 + ATT_S * 4;  // max + sum exchange + staged key mask
 constexpr uint32_t ATT_FWD_SMEM = 5 * ATT_TILE + 1024 + 64 + ATT_FWD_RED;
 
 __global__ void __launch_bounds__(ATT_FWD_THREADS, 2)
@@ -67,11 +67,14 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnPara
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
   float* red_max = reinterpret_cast<float*>(smem + 5 * ATT_TILE + 64);  // [2][128]
   float* red_sum = red_max + 2 * ATT_S;                                  // [2][128]
+  float* smask = red_sum + 2 * ATT_S;                                    // [128] additive key mask * log2(e), -inf past S
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b = blockIdx.x / p.H, h = blockIdx.x % p.H;
   const uint32_t tma_bar = ptx::smem_u32(&bars[0]);
   const uint32_t mma_bar = ptx::smem_u32(&bars[1]);
+
+  if (tid < ATT_S) smask[tid] = tid < p.S ? (p.mask != nullptr ? __ldg(p.mask + b * p.S + tid) * LOG2E : 0.0f) : -INFINITY;
 
   if (tid == 0) {
     ptx::tma_prefetch_desc(&tma_qkv);
@@ -120,9 +123,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnPara
 #pragma unroll
   for (int e = 0; e < 64; ++e) {
     const int j = cg * 64 + e;
-    float m = 0.0f;
-    if (p.mask != nullptr && j < p.S) m = __ldg(p.mask + b * p.S + j) * LOG2E;
-    s[e] = (j < p.S) ? (s[e] * sc + m) : -INFINITY;
+    s[e] = fmaf(s[e], sc, smask[j]);  // -inf for keys past the sequence end
     mx = fmaxf(mx, s[e]);
   }
   red_max[cg * ATT_S + q] = mx;
@@ -190,7 +191,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnPara
 // Backward: 512 threads = 4 lane quarters x 4 column groups (32 keys each); 1 CTA per SM.
 // ------------------------------------------------------------------------------------------------
 constexpr int ATT_BWD_THREADS = 512;
-constexpr uint32_t ATT_BWD_RED = 4 * ATT_S * 4;
+constexpr uint32_t ATT_BWD_RED = 4 * ATT_S * 4 + ATT_S * 4;
 constexpr uint32_t ATT_BWD_SMEM = 8 * ATT_TILE + 1024 + 64 + ATT_BWD_RED;
 
 __global__ void __launch_bounds__(ATT_BWD_THREADS, 1)
@@ -207,11 +208,14 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 8 * ATT_TILE);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
   float* red_delta = reinterpret_cast<float*>(smem + 8 * ATT_TILE + 64);  // [4][128]
+  float* smask = red_delta + 4 * ATT_S;                                   // [128]
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b = blockIdx.x / p.H, h = blockIdx.x % p.H;
   const uint32_t tma_bar = ptx::smem_u32(&bars[0]);
   const uint32_t mma_bar = ptx::smem_u32(&bars[1]);
+
+  if (tid < ATT_S) smask[tid] = tid < p.S ? (p.mask != nullptr ? __ldg(p.mask + b * p.S + tid) * LOG2E : 0.0f) : -INFINITY;
 
   if (tid == 0) {
     ptx::tma_prefetch_desc(&tma_qkv);
@@ -274,9 +278,7 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
 #pragma unroll
     for (int e = 0; e < 32; ++e) {
       const int j = cg * 32 + e;
-      float m = 0.0f;
-      if (p.mask != nullptr && j < p.S) m = __ldg(p.mask + b * p.S + j) * LOG2E;
-      const float pv = (q_ok && j < p.S) ? exp2f(pr[e] * sc + m - lse2) : 0.0f;
+      const float pv = q_ok ? exp2f(fmaf(pr[e], sc, smask[j]) - lse2) : 0.0f;  // exp2(-inf) = 0 past the sequence end
       float keep = 1.0f;
       if (p.drop_threshold != 0u) keep = dropout_keep(dseed, didx0 + e, p.drop_threshold) ? p.drop_scale : 0.0f;
       pr[e] = pv;

@@ -47,18 +47,34 @@ struct GemmParams {
   const uint32_t* drop_seed_dev;  // optional per-step seed in device memory (CUDA-graph friendly)
 };
 
+// erf GELU through the Abramowitz–Stegun 7.1.26 rational form (|error| < 1.5e-7, far below bf16 resolution): one
+// reciprocal, one exp2 and six FMAs per element instead of libdevice erff's branchy ~40 instructions. The epilogue
+// is instruction-issue bound, so this is what keeps it under the MMA time of a tile.
+__device__ __forceinline__ void phi_terms(float x, float& cdf, float& e) {
+  const float ax = fabsf(x) * 0.70710678118654752f;
+  const float t = __frcp_rn(fmaf(0.3275911f, ax, 1.0f));
+  e = exp2f(-1.4426950408889634f * ax * ax);  // exp(-x^2/2)
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  const float half_erfc = 0.5f * poly * t * e;      // 0.5 * erfc(|x|/sqrt2)
+  cdf = x >= 0.0f ? 1.0f - half_erfc : half_erfc;
+}
 __device__ __forceinline__ float gelu_erf(float x) {
-  return 0.5f * x * (1.0f + erff(x * 0.70710678118654752f));
+  float cdf, e;
+  phi_terms(x, cdf, e);
+  return x * cdf;
 }
 __device__ __forceinline__ float dgelu_erf(float x) {
-  const float cdf = 0.5f * (1.0f + erff(x * 0.70710678118654752f));
-  const float pdf = 0.3989422804014327f * __expf(-0.5f * x * x);
-  return cdf + x * pdf;
+  float cdf, e;
+  phi_terms(x, cdf, e);
+  return fmaf(x * 0.3989422804014327f, e, cdf);
 }
 
 constexpr int GEMM_BM = 128;
 constexpr int GEMM_BK = 64;
-constexpr int GEMM_EPI_WARPS = 8;
+constexpr int GEMM_EPI_WARPS = 16;  // 4 per TMEM lane quarter: the epilogue is issue-bound, so give every SMSP 4 warps
 constexpr int GEMM_THREADS = 64 + 32 * GEMM_EPI_WARPS;
 
 template <int BN>
@@ -187,8 +203,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     // ===================== Epilogue warps =====================
     const int ew = warp - 2;
     const int q = warp & 3;            // TMEM lane quarter this warp may access
-    const int half = ew >> 2;          // which half of the BN columns
-    constexpr int COLS_PER_WARP = BN / 2;
+    const int half = ew >> 2;          // which quarter of the BN columns (0..3)
+    constexpr int COLS_PER_WARP = BN / 4;
+    constexpr int CW = COLS_PER_WARP < 32 ? COLS_PER_WARP : 32;  // columns per tcgen05.ld chunk (16 when BN == 64)
     uint32_t lt = 0;
     for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++lt) {
       const int tile = w / p.splitk;
@@ -202,28 +219,29 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
       const bool row_ok = row < p.M;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * BN;
 #pragma unroll 1
-      for (int c = half * COLS_PER_WARP; c < (half + 1) * COLS_PER_WARP; c += 32) {
-        float v[32];
-        ptx::tmem_ld_32x32b_x32(taddr + c, v);
+      for (int c = half * COLS_PER_WARP; c < (half + 1) * COLS_PER_WARP; c += CW) {
+        float v[CW];
+        if constexpr (CW == 32) ptx::tmem_ld_32x32b_x32(taddr + c, v);
+        else ptx::tmem_ld_32x32b_x16(taddr + c, v);
         ptx::tmem_ld_wait();
         const int col0 = n0 + c;
         if (col0 >= p.N) continue;  // warp-uniform
-        const bool full_cols = (col0 + 32 <= p.N);
+        const bool full_cols = (col0 + CW <= p.N);
         if (p.alpha != 1.0f) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] *= p.alpha;
+          for (int j = 0; j < CW; ++j) v[j] *= p.alpha;
         }
         if (p.bias != nullptr) {
           if (full_cols) {
             const float4* b4 = reinterpret_cast<const float4*>(p.bias + col0);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
+            for (int j = 0; j < CW / 4; ++j) {
               const float4 b = __ldg(b4 + j);
               v[4 * j + 0] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
             }
           } else {
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
+            for (int j = 0; j < CW; ++j)
               if (col0 + j < p.N) v[j] += __ldg(p.bias + col0 + j);
           }
         }
@@ -234,7 +252,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
               if (full_cols) {
                 uint4* zo = reinterpret_cast<uint4*>(p.aux_out + aux_off);
 #pragma unroll
-                for (int j = 0; j < 4; ++j) {
+                for (int j = 0; j < CW / 8; ++j) {
                   uint4 u;
                   u.x = ptx::pack_bf16x2(v[8 * j + 0], v[8 * j + 1]);
                   u.y = ptx::pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
@@ -244,17 +262,17 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
                 }
               } else {
                 #pragma unroll
-                for (int j = 0; j < 32; ++j)
+                for (int j = 0; j < CW; ++j)
                   if (col0 + j < p.N) p.aux_out[aux_off + j] = __float2bfloat16_rn(v[j]);
               }
             }
 #pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
+            for (int j = 0; j < CW; ++j) v[j] = gelu_erf(v[j]);
           } else if (p.epi == EPI_DGELU) {
             if (full_cols) {
               const uint4* zi = reinterpret_cast<const uint4*>(p.aux_in + aux_off);
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
+              for (int j = 0; j < CW / 8; ++j) {
                 const uint4 u = __ldg(zi + j);
                 v[8 * j + 0] *= dgelu_erf(ptx::bf16_lo(u.x)); v[8 * j + 1] *= dgelu_erf(ptx::bf16_hi(u.x));
                 v[8 * j + 2] *= dgelu_erf(ptx::bf16_lo(u.y)); v[8 * j + 3] *= dgelu_erf(ptx::bf16_hi(u.y));
@@ -263,7 +281,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
               }
             } else {
               #pragma unroll
-              for (int j = 0; j < 32; ++j)
+              for (int j = 0; j < CW; ++j)
                 if (col0 + j < p.N) v[j] *= dgelu_erf(__bfloat162float(p.aux_in[aux_off + j]));
             }
           } else if (p.epi == EPI_BIAS_RESID) {
@@ -271,13 +289,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
               const uint32_t base = static_cast<uint32_t>(row) * static_cast<uint32_t>(p.N) + static_cast<uint32_t>(col0);
               const uint32_t dseed = p.drop_seed + (p.drop_seed_dev ? __ldg(p.drop_seed_dev) * 0x9E3779B9u : 0u);
 #pragma unroll
-              for (int j = 0; j < 32; ++j)
+              for (int j = 0; j < CW; ++j)
                 v[j] = dropout_keep(dseed, base + j, p.drop_threshold) ? v[j] * p.drop_scale : 0.0f;
             }
             if (full_cols) {
               const uint4* ri = reinterpret_cast<const uint4*>(p.aux_in + aux_off);
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
+              for (int j = 0; j < CW / 8; ++j) {
                 const uint4 u = __ldg(ri + j);
                 v[8 * j + 0] += ptx::bf16_lo(u.x); v[8 * j + 1] += ptx::bf16_hi(u.x);
                 v[8 * j + 2] += ptx::bf16_lo(u.y); v[8 * j + 3] += ptx::bf16_hi(u.y);
@@ -286,7 +304,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
               }
             } else {
               #pragma unroll
-              for (int j = 0; j < 32; ++j)
+              for (int j = 0; j < CW; ++j)
                 if (col0 + j < p.N) v[j] += __bfloat162float(p.aux_in[aux_off + j]);
             }
           }
@@ -297,7 +315,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
             if (full_cols && ((reinterpret_cast<uintptr_t>(cp) & 15) == 0)) {
               uint4* co = reinterpret_cast<uint4*>(cp);
 #pragma unroll
-              for (int j = 0; j < 4; ++j) {
+              for (int j = 0; j < CW / 8; ++j) {
                 uint4 u;
                 u.x = ptx::pack_bf16x2(v[8 * j + 0], v[8 * j + 1]);
                 u.y = ptx::pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
@@ -307,7 +325,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
               }
             } else {
               #pragma unroll
-              for (int j = 0; j < 32; ++j)
+              for (int j = 0; j < CW; ++j)
                 if (col0 + j < p.N) cp[j] = __float2bfloat16_rn(v[j]);
             }
           } else if (p.out_mode == OUT_F32) {
@@ -315,23 +333,23 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
             if (full_cols && ((reinterpret_cast<uintptr_t>(cp) & 15) == 0)) {
               float4* co = reinterpret_cast<float4*>(cp);
 #pragma unroll
-              for (int j = 0; j < 8; ++j) co[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+              for (int j = 0; j < CW / 4; ++j) co[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
             } else {
               #pragma unroll
-              for (int j = 0; j < 32; ++j)
+              for (int j = 0; j < CW; ++j)
                 if (col0 + j < p.N) cp[j] = v[j];
             }
           } else {
             float* cp = reinterpret_cast<float*>(p.C) + c_off;
             if (full_cols && ((reinterpret_cast<uintptr_t>(cp) & 15) == 0)) {
 #pragma unroll
-              for (int j = 0; j < 8; ++j)
+              for (int j = 0; j < CW / 4; ++j)
                 asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(cp + 4 * j),
                              "f"(v[4 * j]), "f"(v[4 * j + 1]), "f"(v[4 * j + 2]), "f"(v[4 * j + 3])
                              : "memory");
             } else {
               #pragma unroll
-              for (int j = 0; j < 32; ++j)
+              for (int j = 0; j < CW; ++j)
                 if (col0 + j < p.N) atomicAdd(cp + j, v[j]);
             }
           }
@@ -368,7 +386,9 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   return 0;
 }
 
-static int pick_bn(int M, int N, int sms) {
+static int pick_bn(int M, int N, int sms, bool splitk_ok) {
+  // with split-K available the grid is filled along K, so take the tile with the best arithmetic intensity
+  if (splitk_ok && N >= 192) return 256;
   // Choose the N-tile that wastes the fewest SM-rounds (persistent grid of `sms` CTAs).
   const int tiles_m = (M + GEMM_BM - 1) / GEMM_BM;
   int best = 128;
@@ -379,7 +399,7 @@ static int pick_bn(int M, int N, int sms) {
     const int tiles = tiles_m * ((N + bn - 1) / bn);
     const int rounds = (tiles + sms - 1) / sms;
     // cost ~ rounds * per-tile time; smaller tiles have lower MMA efficiency (smem-bound B reuse)
-    const double eff = (bn == 256) ? 1.0 : (bn == 128 ? 0.92 : 0.75);
+    const double eff = (bn == 256) ? 1.0 : (bn == 128 ? 0.8 : 0.55);
     const double cost = rounds * (bn / eff);
     if (cost < best_cost) { best_cost = cost; best = bn; }
   }
@@ -403,7 +423,7 @@ extern "C" int det_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   DET_REQUIRE(M > 0 && N > 0 && K > 0, "empty GEMM");
   DET_REQUIRE(out_mode >= 0 && out_mode <= 2, "bad out_mode");
   const int sms = sm_count();
-  int bn = force_bn > 0 ? force_bn : pick_bn(M, N, sms);
+  int bn = force_bn > 0 ? force_bn : pick_bn(M, N, sms, out_mode == OUT_F32_ATOMIC_ADD);
   DET_REQUIRE(bn == 64 || bn == 128 || bn == 256, "BN must be 64, 128 or 256");
   GemmParams p;
   p.M = M; p.N = N; p.K = K;
@@ -415,7 +435,7 @@ extern "C" int det_gemm_bf16(const void* A, const void* B, void* C, int M, int N
     splitk = 1;
   } else if (splitk <= 0) {
     splitk = 1;
-    if (tiles < sms) splitk = max(1, min(p.num_kb / 4, sms / tiles));
+    if (tiles < sms) splitk = max(1, min(p.num_kb / 4, (sms + tiles / 2) / tiles));
   }
   splitk = max(1, min(splitk, p.num_kb));
   p.kb_per_split = (p.num_kb + splitk - 1) / splitk;

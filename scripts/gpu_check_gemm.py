@@ -1,41 +1,22 @@
 """GPU bring-up check for the tcgen05 GEMM: every operand-major combination, tile width, epilogue and
 split-K mode against an fp32 torch reference, then a timing sweep against torch.matmul (cuBLAS).
 Prints one line per case and never stops at the first failure, so one gpurun call shows everything."""
-import ctypes
 import json
 import math
 import os
 import sys
-import time
 
 import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-lib = ctypes.CDLL(os.path.join(ROOT, "determined_b200", "_lib", "libdet_kernels.so"))
-lib.det_last_error.restype = ctypes.c_char_p
-lib.det_gemm_bf16.restype = ctypes.c_int
-lib.det_gemm_bf16.argtypes = [
-    ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_int,
-    ctypes.c_int, ctypes.c_int, ctypes.c_longlong, ctypes.c_longlong, ctypes.c_longlong,
-    ctypes.c_int, ctypes.c_int, ctypes.c_float, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
-    ctypes.c_longlong, ctypes.c_float, ctypes.c_uint, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
-]
-
-
-def ptr(t):
-    return None if t is None else ctypes.c_void_p(t.data_ptr())
+sys.path.insert(0, ROOT)
+from determined_b200.ops import functional as F  # noqa: E402
 
 
 def gemm(A, B, C, M, N, K, a_mn, b_mn, out_mode=0, epi=0, alpha=1.0, bias=None, aux_in=None,
          aux_out=None, dropout_p=0.0, seed=0, splitk=0, force_bn=0):
-    lda = A.stride(0)
-    ldb = B.stride(0)
-    ld_aux = (aux_in if aux_in is not None else aux_out).stride(0) if (aux_in is not None or aux_out is not None) else 0
-    rc = lib.det_gemm_bf16(ptr(A), ptr(B), ptr(C), M, N, K, a_mn, b_mn, lda, ldb, C.stride(0), out_mode,
-                           epi, alpha, ptr(bias), ptr(aux_in), ptr(aux_out), ld_aux, dropout_p, seed,
-                           splitk, force_bn, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
-    if rc != 0:
-        raise RuntimeError(lib.det_last_error().decode())
+    F.gemm(A, B, C, M, N, K, a_mn=bool(a_mn), b_mn=bool(b_mn), out_mode=out_mode, epi=epi, alpha=alpha, bias=bias,
+           aux_in=aux_in, aux_out=aux_out, dropout_p=dropout_p, seed=seed, splitk=splitk, force_bn=force_bn)
 
 
 results = []
