@@ -83,6 +83,63 @@ int make_tma_2d_bf16(CUtensorMap* out, const void* gptr, uint64_t inner, uint64_
   return 0;
 }
 
+// N-D (rank 2..4) bf16 tensor map, SWIZZLE_128B, innermost box = 64 elements. dims/box are innermost first;
+// strides_bytes has rank-1 entries (dims 1..rank-1). Cached on every argument.
+int make_tma_nd_bf16(CUtensorMap* out, const void* gptr, int rank, const uint64_t* dims,
+                     const uint64_t* strides_bytes, const uint32_t* box) {
+  struct NdKey {
+    const void* p; int rank; uint64_t d[4]; uint64_t s[3]; uint32_t b[4];
+    bool operator==(const NdKey& o) const { return std::memcmp(this, &o, sizeof(NdKey)) == 0; }
+  };
+  struct NdHash {
+    size_t operator()(const NdKey& k) const {
+      const uint64_t* w = reinterpret_cast<const uint64_t*>(&k);
+      uint64_t h = 0xcbf29ce484222325ull;
+      for (size_t i = 0; i < sizeof(NdKey) / 8; ++i) { h ^= w[i]; h *= 0x100000001b3ull; h ^= h >> 31; }
+      return static_cast<size_t>(h);
+    }
+  };
+  static_assert(sizeof(NdKey) % 8 == 0, "key must be a whole number of words");
+  static std::mutex mu;
+  static std::unordered_map<NdKey, CUtensorMap, NdHash> cache;
+  DET_REQUIRE(rank >= 2 && rank <= 4, "tensor map rank must be 2..4");
+  NdKey key;
+  std::memset(&key, 0, sizeof(key));
+  key.p = gptr; key.rank = rank;
+  for (int i = 0; i < rank; ++i) { key.d[i] = dims[i]; key.b[i] = box[i]; }
+  for (int i = 0; i < rank - 1; ++i) key.s[i] = strides_bytes[i];
+  {
+    std::lock_guard<std::mutex> g(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) { *out = it->second; return 0; }
+  }
+  EncodeTiledFn fn = get_encode_fn();
+  DET_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+  DET_REQUIRE((reinterpret_cast<uintptr_t>(gptr) & 15) == 0, "TMA base must be 16-byte aligned");
+  DET_REQUIRE(box[0] == 64, "SWIZZLE_128B box needs 64 bf16 in the inner dimension");
+  cuuint64_t gdim[4]; cuuint64_t gstr[3]; cuuint32_t bx[4]; cuuint32_t estr[4] = {1, 1, 1, 1};
+  for (int i = 0; i < rank; ++i) {
+    gdim[i] = dims[i]; bx[i] = box[i];
+    DET_REQUIRE(box[i] >= 1 && box[i] <= 256, "TMA box extents must be 1..256");
+  }
+  for (int i = 0; i < rank - 1; ++i) {
+    gstr[i] = strides_bytes[i];
+    DET_REQUIRE(strides_bytes[i] % 16 == 0, "TMA strides must be multiples of 16 bytes");
+  }
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(gptr), gdim, gstr,
+                  bx, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_last_error("cuTensorMapEncodeTiled (rank " + std::to_string(rank) + ") failed with CUresult " +
+                   std::to_string((int)r));
+    return 3;
+  }
+  std::lock_guard<std::mutex> g(mu);
+  if (cache.size() > 65536) cache.clear();
+  cache.emplace(key, *out);
+  return 0;
+}
+
 int sm_count() {
   static int counts[64] = {0};
   int dev = 0;

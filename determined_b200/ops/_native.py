@@ -32,6 +32,23 @@ _SIGNATURES = {
     "det_gemm_small": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_ll, c_ll, c_ll, c_ll, c_ll, c_ll,
                        c_int, c_int, c_int, c_void_p, c_int, c_float, c_int, c_void_p],
     "det_cast_f32_bf16": [c_void_p, c_void_p, c_ll, c_void_p],
+    "det_conv2d_implicit": [c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                            c_int, c_int, c_void_p, c_int, c_int, c_int, c_void_p],
+    "det_im2col": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p],
+    "det_col2im": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p],
+    "det_bn_stats": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_int, c_float, c_float, c_void_p],
+    "det_bn_apply": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_int, c_int, c_float,
+                     c_void_p],
+    "det_bn_bwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                   c_void_p, c_ll, c_int, c_int, c_float, c_void_p],
+    "det_maxpool_fwd": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p],
+    "det_maxpool_bwd": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p],
+    "det_avgpool_fwd": [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p],
+    "det_avgpool_bwd": [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p],
+    "det_act_fwd": [c_void_p, c_void_p, c_ll, c_int, c_float, c_void_p],
+    "det_act_bwd": [c_void_p, c_void_p, c_void_p, c_ll, c_int, c_float, c_void_p],
+    "det_dropout": [c_void_p, c_void_p, c_ll, c_float, c_uint, c_void_p, c_void_p],
+    "det_nchw_to_nhwc_bf16": [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p],
     "det_fused_optimizer_step": [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_void_p, c_void_p,
                                  c_void_p, c_int, c_void_p],
     "det_grad_sumsq_finite": [c_void_p, c_ll, c_void_p, c_void_p, c_void_p, c_void_p],

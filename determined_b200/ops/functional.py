@@ -216,3 +216,130 @@ def loss_scale_update(state3_dev: torch.Tensor, found_inf_dev: torch.Tensor, gro
                       growth_interval: int, divisor: float) -> None:
     _native.call("det_loss_scale_update", _p(state3_dev), _p(found_inf_dev), float(growth), float(backoff),
                  int(growth_interval), float(divisor), _stream())
+
+
+# ------------------------------------------------------------------------------------------------
+# Convolutional stack (NHWC bf16 activations; csrc/kernels/conv_sm100.cu + conv_ops.cu)
+# ------------------------------------------------------------------------------------------------
+CONV_FPROP, CONV_DGRAD, CONV_WGRAD = 0, 1, 2
+ACT_NONE, ACT_RELU, ACT_LEAKY, ACT_TANH, ACT_SIGMOID = 0, 1, 2, 3, 4
+
+
+def conv_out_size(size: int, k: int, stride: int, pad: int) -> int:
+    return (size + 2 * pad - k) // stride + 1
+
+
+def conv2d_implicit(mode: int, src: torch.Tensor, other: torch.Tensor, out: torch.Tensor, N: int, H: int, W: int,
+                    Cin: int, Cout: int, R: int, S: int, pad_h: int, pad_w: int, *, bias: Optional[torch.Tensor] = None,
+                    relu: bool = False, splitk: int = 0, force_bn: int = 0) -> torch.Tensor:
+    """Unit-stride implicit-GEMM convolution on tcgen05 (no im2col buffer). ``mode``: CONV_FPROP (src=x,
+    other=weight [Cout,R,S,Cin] → y), CONV_DGRAD (src=dy, other=weight → dx), CONV_WGRAD (src=dy, other=x →
+    fp32 dW accumulated)."""
+    _native.call("det_conv2d_implicit", mode, _p(src), _p(other), _p(out), N, H, W, Cin, Cout, R, S, pad_h, pad_w,
+                 _p(bias), int(relu), splitk, force_bn, _stream())
+    return out
+
+
+def im2col(x: torch.Tensor, N: int, H: int, W: int, C: int, R: int, S: int, stride: int, pad_h: int, pad_w: int,
+           Kp: int) -> torch.Tensor:
+    Ho, Wo = conv_out_size(H, R, stride, pad_h), conv_out_size(W, S, stride, pad_w)
+    col = torch.empty(N * Ho * Wo, Kp, dtype=torch.bfloat16, device=x.device)
+    _native.call("det_im2col", _p(x), _p(col), N, H, W, C, R, S, stride, pad_h, pad_w, Kp, _stream())
+    return col
+
+
+def col2im(col: torch.Tensor, N: int, H: int, W: int, C: int, R: int, S: int, stride: int, pad_h: int, pad_w: int,
+           Kp: int) -> torch.Tensor:
+    dx = torch.empty(N, H, W, C, dtype=torch.bfloat16, device=col.device)
+    _native.call("det_col2im", _p(col), _p(dx), N, H, W, C, R, S, stride, pad_h, pad_w, Kp, _stream())
+    return dx
+
+
+def bn_stats(x: torch.Tensor, C: int, running_mean: Optional[torch.Tensor], running_var: Optional[torch.Tensor],
+             eps: float, momentum: float) -> Tuple[torch.Tensor, torch.Tensor]:
+    M = x.numel() // C
+    scratch = torch.empty(2 * C, dtype=torch.float32, device=x.device)
+    mean = torch.empty(C, dtype=torch.float32, device=x.device)
+    rstd = torch.empty(C, dtype=torch.float32, device=x.device)
+    _native.call("det_bn_stats", _p(x), _p(scratch), _p(mean), _p(rstd), _p(running_mean), _p(running_var), M, C,
+                 float(eps), float(momentum), _stream())
+    return mean, rstd
+
+
+def bn_apply(x: torch.Tensor, resid: Optional[torch.Tensor], mean: torch.Tensor, rstd: torch.Tensor,
+             gamma: Optional[torch.Tensor], beta: Optional[torch.Tensor], C: int, act: int = ACT_NONE,
+             slope: float = 0.0) -> torch.Tensor:
+    y = torch.empty_like(x)
+    _native.call("det_bn_apply", _p(x), _p(resid), _p(y), _p(mean), _p(rstd), _p(gamma), _p(beta), x.numel() // C, C,
+                 act, float(slope), _stream())
+    return y
+
+
+def bn_bwd(dy: torch.Tensor, x: torch.Tensor, a: Optional[torch.Tensor], mean: torch.Tensor, rstd: torch.Tensor,
+           gamma: Optional[torch.Tensor], dgamma: Optional[torch.Tensor], dbeta: Optional[torch.Tensor], C: int,
+           act: int = ACT_NONE, slope: float = 0.0, want_dresid: bool = False):
+    dx = torch.empty_like(x)
+    dresid = torch.empty_like(x) if want_dresid else None
+    scratch = torch.empty(2 * C, dtype=torch.float32, device=x.device)
+    _native.call("det_bn_bwd", _p(dy), _p(x), _p(a), _p(mean), _p(rstd), _p(gamma), _p(scratch), _p(dx), _p(dresid),
+                 _p(dgamma), _p(dbeta), x.numel() // C, C, act, float(slope), _stream())
+    return dx, dresid
+
+
+def maxpool_fwd(x: torch.Tensor, k: int, stride: int, pad: int) -> Tuple[torch.Tensor, torch.Tensor]:
+    N, H, W, C = x.shape
+    Ho, Wo = conv_out_size(H, k, stride, pad), conv_out_size(W, k, stride, pad)
+    y = torch.empty(N, Ho, Wo, C, dtype=torch.bfloat16, device=x.device)
+    idx = torch.empty(N, Ho, Wo, C, dtype=torch.uint8, device=x.device)
+    _native.call("det_maxpool_fwd", _p(x), _p(y), _p(idx), N, H, W, C, k, stride, pad, _stream())
+    return y, idx
+
+
+def maxpool_bwd(dy: torch.Tensor, idx: torch.Tensor, in_shape, k: int, stride: int, pad: int) -> torch.Tensor:
+    N, H, W, C = in_shape
+    dx = torch.empty(N, H, W, C, dtype=torch.bfloat16, device=dy.device)
+    _native.call("det_maxpool_bwd", _p(dy), _p(idx), _p(dx), N, H, W, C, k, stride, pad, _stream())
+    return dx
+
+
+def avgpool_fwd(x: torch.Tensor) -> torch.Tensor:
+    N, H, W, C = x.shape
+    y = torch.empty(N, C, dtype=torch.bfloat16, device=x.device)
+    _native.call("det_avgpool_fwd", _p(x), _p(y), N, H * W, C, _stream())
+    return y
+
+
+def avgpool_bwd(dy: torch.Tensor, in_shape) -> torch.Tensor:
+    N, H, W, C = in_shape
+    dx = torch.empty(N, H, W, C, dtype=torch.bfloat16, device=dy.device)
+    _native.call("det_avgpool_bwd", _p(dy), _p(dx), N, H * W, C, _stream())
+    return dx
+
+
+def act_fwd(x: torch.Tensor, act: int, slope: float = 0.0) -> torch.Tensor:
+    y = torch.empty_like(x)
+    _native.call("det_act_fwd", _p(x), _p(y), x.numel(), act, float(slope), _stream())
+    return y
+
+
+def act_bwd(dy: torch.Tensor, y: torch.Tensor, act: int, slope: float = 0.0) -> torch.Tensor:
+    dx = torch.empty_like(y)
+    _native.call("det_act_bwd", _p(dy), _p(y), _p(dx), y.numel(), act, float(slope), _stream())
+    return dx
+
+
+def dropout(x: torch.Tensor, p: float, seed: int) -> torch.Tensor:
+    """Stateless-hash dropout keyed by (seed, device step seed, element index); calling it again with the same seed
+    on the gradient IS the backward pass."""
+    y = torch.empty_like(x)
+    _native.call("det_dropout", _p(x), _p(y), x.numel(), float(p), int(seed) & 0xFFFFFFFF,
+                 _p(step_seed_tensor(x.device)), _stream())
+    return y
+
+
+def nchw_to_nhwc_bf16(x: torch.Tensor) -> torch.Tensor:
+    """fp32 NCHW image batch → bf16 NHWC (the layout every convolutional kernel here works in)."""
+    N, C, H, W = x.shape
+    out = torch.empty(N, H, W, C, dtype=torch.bfloat16, device=x.device)
+    _native.call("det_nchw_to_nhwc_bf16", _p(x), _p(out), N, C, H * W, _stream())
+    return out
