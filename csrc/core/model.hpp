@@ -234,9 +234,26 @@ struct SearcherConfig {
 // ---- Experiment config: defaults, merge, validation ----------------------------------------------------------------
 inline void json_merge(Json& base, const Json& over) {
   if (!over.is_object() || !base.is_object()) { base = over.deep_copy(); return; }
+  // Tagged unions replace wholesale instead of merging field by field: a length {epochs: 1} must not inherit the
+  // default's {batches: 0}, and a storage/searcher block of another "type"/"name" must not keep the old one's fields.
+  auto is_length = [](const Json& j) {
+    if (!j.is_object() || j.obj().empty()) return false;
+    for (auto& kv : j.obj())
+      if (kv.first != "records" && kv.first != "batches" && kv.first != "epochs") return false;
+    return true;
+  };
+  auto other_variant = [](const Json& a, const Json& b) {
+    for (const char* tag : {"type", "name"})
+      if (a.contains(tag) && b.contains(tag) && a[tag].is_string() && b[tag].is_string() && a[tag].as_string() != b[tag].as_string())
+        return true;
+    return false;
+  };
   for (auto& kv : over.obj()) {
-    if (kv.second.is_object() && base.contains(kv.first) && base[kv.first].is_object()) json_merge(base[kv.first], kv.second);
-    else base[kv.first] = kv.second.deep_copy();
+    if (kv.second.is_object() && base.contains(kv.first) && base[kv.first].is_object() && !is_length(kv.second) &&
+        !other_variant(base[kv.first], kv.second))
+      json_merge(base[kv.first], kv.second);
+    else
+      base[kv.first] = kv.second.deep_copy();
   }
 }
 

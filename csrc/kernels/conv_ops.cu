@@ -1,8 +1,7 @@
 // conv_ops.cu — the bandwidth-bound half of the convolutional models (NHWC bf16 activations):
 //   * gather / scatter-free col2im for the convolutions the implicit-GEMM kernel does not take
 //     (stride > 1, or channel counts that are not a multiple of 8 such as the RGB stem),
-//   * training-mode BatchNorm: one-pass column statistics, fused normalise + residual-add + (leaky)ReLU,
-//     two-kernel backward (column reductions, then dx and the residual-branch gradient in one pass),
+//   * (training-mode BatchNorm lives in bn_ops.cu),
 //   * max / global-average pooling, elementwise activations, stateless-hash dropout, NCHW fp32 -> NHWC bf16.
 // Every kernel moves 16 bytes per thread per access where the channel count allows it.
 //
@@ -114,180 +113,6 @@ col2im_kernel(const __nv_bfloat16* __restrict__ col, __nv_bfloat16* __restrict__
   __nv_bfloat16* dst = dx + pix * g.C + c;
   if (VEC) *reinterpret_cast<uint4*>(dst) = pack8(acc);
   else *dst = __float2bfloat16_rn(acc[0]);
-}
-
-// ------------------------------------------------------------------------------------------------
-// BatchNorm over the rows of x[M, C] (C % 8 == 0). Column partial sums per block, fp32 atomics to finish.
-// ------------------------------------------------------------------------------------------------
-struct ColMap {
-  int vpr;        // 16-byte vectors per row handled by this block column (<= 256)
-  int rpi;        // rows per iteration = 256 / vpr
-  int cbase;      // first channel of the block column
-};
-__device__ __forceinline__ ColMap col_map(int C) {
-  ColMap m;
-  m.cbase = blockIdx.y * 2048;
-  const int cc = min(2048, C - m.cbase);
-  m.vpr = cc / 8;
-  m.rpi = 256 / m.vpr;
-  return m;
-}
-
-__device__ __forceinline__ float act_mask(float a, int act, float slope) {
-  if (act == 0) return 1.0f;
-  return a > 0.0f ? 1.0f : (act == 2 ? slope : 0.0f);
-}
-
-// sums[0:C] += sum_rows x, sums[C:2C] += sum_rows x^2
-__global__ void __launch_bounds__(256)
-bn_stats_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums, long long M, int C) {
-  __shared__ float red[2][256][8];
-  const ColMap m = col_map(C);
-  const int t = threadIdx.x;
-  const int cv = t % m.vpr, ro = t / m.vpr;
-  float s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  if (ro < m.rpi) {
-    for (long long row = static_cast<long long>(blockIdx.x) * m.rpi + ro; row < M; row += static_cast<long long>(gridDim.x) * m.rpi) {
-      float f[8];
-      unpack8(__ldg(reinterpret_cast<const uint4*>(x + row * C + m.cbase + cv * 8)), f);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) { s[j] += f[j]; q[j] = fmaf(f[j], f[j], q[j]); }
-    }
-  }
-#pragma unroll
-  for (int j = 0; j < 8; ++j) { red[0][t][j] = s[j]; red[1][t][j] = q[j]; }
-  __syncthreads();
-  if (t < m.vpr) {
-    for (int r = 1; r < m.rpi; ++r) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) { s[j] += red[0][t + r * m.vpr][j]; q[j] += red[1][t + r * m.vpr][j]; }
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      atomicAdd(sums + m.cbase + t * 8 + j, s[j]);
-      atomicAdd(sums + C + m.cbase + t * 8 + j, q[j]);
-    }
-  }
-}
-
-// mean / rstd from the sums; running statistics updated the way torch.nn.BatchNorm2d does (unbiased variance).
-__global__ void bn_finalize_kernel(const float* __restrict__ sums, float* __restrict__ mean, float* __restrict__ rstd,
-                                   float* running_mean, float* running_var, long long M, int C, float eps, float momentum) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  const float inv = 1.0f / static_cast<float>(M);
-  const float mu = sums[c] * inv;
-  const float var = fmaxf(sums[C + c] * inv - mu * mu, 0.0f);
-  mean[c] = mu;
-  rstd[c] = rsqrtf(var + eps);
-  if (running_mean != nullptr) {
-    const float unb = M > 1 ? var * static_cast<float>(M) / static_cast<float>(M - 1) : var;
-    running_mean[c] = (1.0f - momentum) * running_mean[c] + momentum * mu;
-    running_var[c] = (1.0f - momentum) * running_var[c] + momentum * unb;
-  }
-}
-
-// y = act((x - mean) * rstd * gamma + beta + resid)
-__global__ void __launch_bounds__(256)
-bn_apply_kernel(const __nv_bfloat16* __restrict__ x, const __nv_bfloat16* __restrict__ resid, __nv_bfloat16* __restrict__ y,
-                const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ gamma,
-                const float* __restrict__ beta, long long total_vec, int C, int act, float slope) {
-  const long long t = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x;
-  if (t >= total_vec) return;
-  const int c = static_cast<int>(t % (C / 8)) * 8;
-  float f[8], r[8];
-  unpack8(__ldg(reinterpret_cast<const uint4*>(x) + t), f);
-  if (resid != nullptr) unpack8(__ldg(reinterpret_cast<const uint4*>(resid) + t), r);
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const float sc = __ldg(rstd + c + j) * (gamma ? __ldg(gamma + c + j) : 1.0f);
-    float v = fmaf(f[j] - __ldg(mean + c + j), sc, beta ? __ldg(beta + c + j) : 0.0f);
-    if (resid != nullptr) v += r[j];
-    if (act == 1) v = fmaxf(v, 0.0f);
-    else if (act == 2) v = v > 0.0f ? v : v * slope;
-    f[j] = v;
-  }
-  reinterpret_cast<uint4*>(y)[t] = pack8(f);
-}
-
-// sums[0:C] += sum dyv, sums[C:2C] += sum dyv * xhat   with dyv = dy * act'(a)
-__global__ void __launch_bounds__(256)
-bn_bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
-                     const __nv_bfloat16* __restrict__ a, const float* __restrict__ mean, const float* __restrict__ rstd,
-                     float* __restrict__ sums, long long M, int C, int act, float slope) {
-  __shared__ float red[2][256][8];
-  const ColMap m = col_map(C);
-  const int t = threadIdx.x;
-  const int cv = t % m.vpr, ro = t / m.vpr;
-  float s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  if (ro < m.rpi) {
-    const int c0 = m.cbase + cv * 8;
-    float mu[8], rs[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) { mu[j] = __ldg(mean + c0 + j); rs[j] = __ldg(rstd + c0 + j); }
-    for (long long row = static_cast<long long>(blockIdx.x) * m.rpi + ro; row < M; row += static_cast<long long>(gridDim.x) * m.rpi) {
-      float d[8], xv[8], av[8];
-      const long long off = row * C + c0;
-      unpack8(__ldg(reinterpret_cast<const uint4*>(dy + off)), d);
-      unpack8(__ldg(reinterpret_cast<const uint4*>(x + off)), xv);
-      if (act != 0) unpack8(__ldg(reinterpret_cast<const uint4*>(a + off)), av);
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float dv = act != 0 ? d[j] * act_mask(av[j], act, slope) : d[j];
-        s[j] += dv;
-        q[j] = fmaf(dv, (xv[j] - mu[j]) * rs[j], q[j]);
-      }
-    }
-  }
-#pragma unroll
-  for (int j = 0; j < 8; ++j) { red[0][t][j] = s[j]; red[1][t][j] = q[j]; }
-  __syncthreads();
-  if (t < m.vpr) {
-    for (int r = 1; r < m.rpi; ++r) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) { s[j] += red[0][t + r * m.vpr][j]; q[j] += red[1][t + r * m.vpr][j]; }
-    }
-#pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      atomicAdd(sums + m.cbase + t * 8 + j, s[j]);
-      atomicAdd(sums + C + m.cbase + t * 8 + j, q[j]);
-    }
-  }
-}
-
-// dx = gamma * rstd * (dyv - mean(dyv) - xhat * mean(dyv * xhat)); dresid = dyv (optional)
-__global__ void __launch_bounds__(256)
-bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
-                    const __nv_bfloat16* __restrict__ a, const float* __restrict__ mean, const float* __restrict__ rstd,
-                    const float* __restrict__ gamma, const float* __restrict__ sums, __nv_bfloat16* __restrict__ dx,
-                    __nv_bfloat16* __restrict__ dresid, long long total_vec, long long M, int C, int act, float slope) {
-  const long long t = static_cast<long long>(blockIdx.x) * 256 + threadIdx.x;
-  if (t >= total_vec) return;
-  const int c = static_cast<int>(t % (C / 8)) * 8;
-  const float inv = 1.0f / static_cast<float>(M);
-  float d[8], xv[8], av[8], o[8];
-  unpack8(__ldg(reinterpret_cast<const uint4*>(dy) + t), d);
-  unpack8(__ldg(reinterpret_cast<const uint4*>(x) + t), xv);
-  if (act != 0) unpack8(__ldg(reinterpret_cast<const uint4*>(a) + t), av);
-#pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    const float dv = act != 0 ? d[j] * act_mask(av[j], act, slope) : d[j];
-    d[j] = dv;
-    const float rs = __ldg(rstd + c + j);
-    const float xh = (xv[j] - __ldg(mean + c + j)) * rs;
-    const float gm = gamma ? __ldg(gamma + c + j) : 1.0f;
-    o[j] = gm * rs * (dv - __ldg(sums + c + j) * inv - xh * __ldg(sums + C + c + j) * inv);
-  }
-  reinterpret_cast<uint4*>(dx)[t] = pack8(o);
-  if (dresid != nullptr) reinterpret_cast<uint4*>(dresid)[t] = pack8(d);
-}
-
-// dgamma += sums[C:2C], dbeta += sums[0:C]
-__global__ void bn_param_grad_kernel(const float* __restrict__ sums, float* dgamma, float* dbeta, int C) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  if (dbeta != nullptr) dbeta[c] += sums[c];
-  if (dgamma != nullptr) dgamma[c] += sums[C + c];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -538,57 +363,6 @@ extern "C" int det_col2im(const void* col, void* dx, int N, int H, int W, int C,
     const long long total = static_cast<long long>(N) * H * W * C;
     det::col2im_kernel<false><<<det::blocks_for(total), 256, 0, stream>>>((const bf16*)col, (bf16*)dx, g, total);
   }
-  DET_CHECK_CUDA(cudaGetLastError());
-  return 0;
-}
-
-static dim3 colred_grid(long long M, int C) {
-  const int vpr = (C < 2048 ? C : 2048) / 8;
-  const int rpi = 256 / vpr;
-  long long bx = (M + rpi - 1) / rpi;
-  const long long cap = 148LL * 8;
-  if (bx > cap) bx = cap;
-  if (bx < 1) bx = 1;
-  return dim3(static_cast<unsigned>(bx), static_cast<unsigned>((C + 2047) / 2048), 1);
-}
-
-// Training-mode statistics: sums_scratch [2*C] fp32 is cleared here; mean/rstd [C] are written; running stats updated
-// in place when given.
-extern "C" int det_bn_stats(const void* x, float* sums_scratch, float* mean, float* rstd, float* running_mean,
-                            float* running_var, long long M, int C, float eps, float momentum, cudaStream_t stream) {
-  DET_REQUIRE(M > 0 && C > 0 && C % 8 == 0, "BatchNorm needs C % 8 == 0");
-  DET_REQUIRE(C <= 2048 || C % 2048 == 0, "BatchNorm: C above 2048 must be a multiple of 2048");
-  DET_CHECK_CUDA(cudaMemsetAsync(sums_scratch, 0, sizeof(float) * 2 * C, stream));
-  det::bn_stats_kernel<<<colred_grid(M, C), 256, 0, stream>>>((const bf16*)x, sums_scratch, M, C);
-  det::bn_finalize_kernel<<<(C + 127) / 128, 128, 0, stream>>>(sums_scratch, mean, rstd, running_mean, running_var, M, C, eps, momentum);
-  DET_CHECK_CUDA(cudaGetLastError());
-  return 0;
-}
-
-extern "C" int det_bn_apply(const void* x, const void* resid, void* y, const float* mean, const float* rstd,
-                            const float* gamma, const float* beta, long long M, int C, int act, float slope,
-                            cudaStream_t stream) {
-  DET_REQUIRE(M > 0 && C > 0 && C % 8 == 0, "BatchNorm needs C % 8 == 0");
-  const long long tv = M * (C / 8);
-  det::bn_apply_kernel<<<det::blocks_for(tv), 256, 0, stream>>>((const bf16*)x, (const bf16*)resid, (bf16*)y, mean, rstd, gamma, beta, tv, C, act, slope);
-  DET_CHECK_CUDA(cudaGetLastError());
-  return 0;
-}
-
-// Backward of y = act(bn(x) + resid). `a` is the saved forward output (needed when act != 0). dgamma/dbeta are
-// accumulated (+=). dresid (optional) receives the gradient of the residual branch.
-extern "C" int det_bn_bwd(const void* dy, const void* x, const void* a, const float* mean, const float* rstd,
-                          const float* gamma, float* sums_scratch, void* dx, void* dresid, float* dgamma, float* dbeta,
-                          long long M, int C, int act, float slope, cudaStream_t stream) {
-  DET_REQUIRE(M > 0 && C > 0 && C % 8 == 0, "BatchNorm needs C % 8 == 0");
-  DET_REQUIRE(C <= 2048 || C % 2048 == 0, "BatchNorm: C above 2048 must be a multiple of 2048");
-  DET_REQUIRE(act == 0 || a != nullptr, "BatchNorm backward through an activation needs the saved output");
-  DET_CHECK_CUDA(cudaMemsetAsync(sums_scratch, 0, sizeof(float) * 2 * C, stream));
-  det::bn_bwd_reduce_kernel<<<colred_grid(M, C), 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, (const bf16*)a, mean, rstd, sums_scratch, M, C, act, slope);
-  const long long tv = M * (C / 8);
-  det::bn_bwd_apply_kernel<<<det::blocks_for(tv), 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, (const bf16*)a, mean, rstd, gamma, sums_scratch, (bf16*)dx, (bf16*)dresid, tv, M, C, act, slope);
-  if (dgamma != nullptr || dbeta != nullptr)
-    det::bn_param_grad_kernel<<<(C + 127) / 128, 128, 0, stream>>>(sums_scratch, dgamma, dbeta, C);
   DET_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -101,6 +101,40 @@ int det_ipc_export(void* p, unsigned char* handle64);
 int det_ipc_import(const unsigned char* handle64, void** out);
 int det_ipc_close(void* p);
 
+/* ---- convolutional stack, NHWC bf16 (reference: torch.nn.Conv2d / BatchNorm2d / pooling → cuDNN in user model code,
+ *      e.g. examples/computer_vision/cifar10_pytorch/model_def.py:49-74) -------------------------
+ * det_conv2d_implicit: unit-stride implicit GEMM on tcgen05; mode 0 fprop (src = x, other = weight [Cout,R,S,Cin],
+ * out = y bf16), 1 dgrad (src = dy, other = weight, out = dx bf16), 2 wgrad (src = dy, other = x, out = dW fp32,
+ * accumulated). Cin, Cout multiples of 8. */
+int det_conv2d_implicit(int mode, const void* src, const void* other, void* out, int N, int H, int W, int Cin,
+                        int Cout, int R, int S, int pad_h, int pad_w, const float* bias, int relu, int splitk,
+                        int force_bn, cudaStream_t stream);
+/* gather path for strided / few-channel convolutions: col [N*Ho*Wo, Kp] with column (r, s, c); Kp % 8 == 0 */
+int det_im2col(const void* x, void* col, int N, int H, int W, int C, int R, int S, int stride, int pad_h, int pad_w,
+               int Kp, cudaStream_t stream);
+int det_col2im(const void* col, void* dx, int N, int H, int W, int C, int R, int S, int stride, int pad_h, int pad_w,
+               int Kp, cudaStream_t stream);
+/* BatchNorm over the rows of x [M, C]; sums_scratch is 2*C floats; act: 0 none, 1 relu, 2 leaky relu (slope) */
+int det_bn_stats(const void* x, float* sums_scratch, float* mean, float* rstd, float* running_mean, float* running_var,
+                 long long M, int C, float eps, float momentum, cudaStream_t stream);
+int det_bn_apply(const void* x, const void* resid, void* y, const float* mean, const float* rstd, const float* gamma,
+                 const float* beta, long long M, int C, int act, float slope, cudaStream_t stream);
+int det_bn_bwd(const void* dy, const void* x, const void* a, const float* mean, const float* rstd, const float* gamma,
+               float* sums_scratch, void* dx, void* dresid, float* dgamma, float* dbeta, long long M, int C, int act,
+               float slope, cudaStream_t stream);
+int det_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int stride, int pad,
+                    cudaStream_t stream);
+int det_maxpool_bwd(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, int k, int stride, int pad,
+                    cudaStream_t stream);
+int det_avgpool_fwd(const void* x, void* y, int N, int HW, int C, cudaStream_t stream);
+int det_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, cudaStream_t stream);
+/* act: 1 relu, 2 leaky relu, 3 tanh, 4 sigmoid; backward reads the saved OUTPUT y */
+int det_act_fwd(const void* x, void* y, long long n, int act, float slope, cudaStream_t stream);
+int det_act_bwd(const void* dy, const void* y, void* dx, long long n, int act, float slope, cudaStream_t stream);
+int det_dropout(const void* x, void* y, long long n, float p, unsigned int seed, const unsigned int* seed_dev,
+                cudaStream_t stream);
+int det_nchw_to_nhwc_bf16(const float* in, void* out, int N, int C, int HW, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -236,6 +236,29 @@ def timing():
         row = {"bn_relu": True, "H": H, "C": Cn, "det_ms": round(t, 4), "det_GBps_3pass": round(3 * gb / t * 1e3, 1), "torch_ms": round(t2, 4)}
         rows.append(row)
         print(json.dumps(row), flush=True)
+    # the four BatchNorm kernels one by one (effective GB/s = bytes each must move / time)
+    for (H, Cn) in [(112, 64), (56, 64), (56, 256), (28, 512), (14, 1024), (7, 2048)]:
+        M = N * H * H
+        xx = torch.randn(M, Cn, device=dev, dtype=torch.bfloat16)
+        dy = torch.randn_like(xx)
+        rs_ = torch.randn_like(xx)
+        gamma = torch.ones(Cn, device=dev); beta = torch.zeros(Cn, device=dev)
+        mean, rstd = F.bn_stats(xx, Cn, None, None, 1e-5, 0.1)
+        yy = F.bn_apply(xx, rs_, mean, rstd, gamma, beta, Cn, F.ACT_RELU)
+        dg = torch.zeros(Cn, device=dev); db = torch.zeros(Cn, device=dev)
+        gb = M * Cn * 2 / 1e9
+        t_stats = bench(lambda: F.bn_stats(xx, Cn, None, None, 1e-5, 0.1))
+        t_apply = bench(lambda: F.bn_apply(xx, None, mean, rstd, gamma, beta, Cn, F.ACT_RELU))
+        t_apply_r = bench(lambda: F.bn_apply(xx, rs_, mean, rstd, gamma, beta, Cn, F.ACT_RELU))
+        t_bwd = bench(lambda: F.bn_bwd(dy, xx, yy, mean, rstd, gamma, dg, db, Cn, F.ACT_RELU, 0.0, want_dresid=False))
+        t_bwd_r = bench(lambda: F.bn_bwd(dy, xx, yy, mean, rstd, gamma, dg, db, Cn, F.ACT_RELU, 0.0, want_dresid=True))
+        row = {"bn_kernels": True, "H": H, "C": Cn, "MB": round(gb * 1e3, 1),
+               "stats_GBps": round(gb / t_stats * 1e3), "apply_GBps": round(2 * gb / t_apply * 1e3),
+               "apply_resid_GBps": round(3 * gb / t_apply_r * 1e3), "bwd_GBps": round(7 * gb / t_bwd * 1e3),
+               "bwd_resid_GBps": round(8 * gb / t_bwd_r * 1e3),
+               "ms": [round(t, 4) for t in (t_stats, t_apply, t_apply_r, t_bwd, t_bwd_r)]}
+        rows.append(row)
+        print(json.dumps(row), flush=True)
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     with open(os.path.join(ROOT, "gpurun_out", "conv_timing.json"), "w") as f:
         json.dump(rows, f, indent=1)

@@ -1,0 +1,147 @@
+"""sm_100a convolution stack against fp32 torch references (forward, input / weight / bias gradients)."""
+import pytest
+import torch
+import torch.nn as nn
+
+pytestmark = pytest.mark.gpu
+
+
+def _bf(t):
+    return t.to(torch.bfloat16).float()
+
+
+def _rel(a, b):
+    a, b = a.float(), b.float()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-6)).item()
+
+
+def _compare(mine, ref, x, tol=2e-2):
+    from determined_b200.ops import _native
+
+    before = _native.launch_count
+    ref = ref.cuda().float()
+    mine = mine.cuda()
+    mine.load_state_dict(ref.state_dict())
+    xr = x.clone().requires_grad_(True)
+    xm = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    yr, ym = ref(xr), mine(xm)
+    assert _rel(ym, yr) < tol
+    g = _bf(torch.randn_like(yr))
+    yr.backward(g)
+    ym.backward(g.to(torch.bfloat16))
+    assert _rel(xm.grad, xr.grad) < tol
+    for (k, pm), (_, pr) in zip(mine.named_parameters(), ref.named_parameters()):
+        gm = pm.grad.permute(0, 3, 1, 2) if pm.grad.dim() == 4 else pm.grad
+        assert _rel(gm, pr.grad) < tol, k
+    assert _native.launch_count > before, "the native kernels did not run"
+
+
+@pytest.mark.parametrize("N,H,W,Cin,Cout,k,s,p", [
+    (4, 56, 56, 64, 64, 3, 1, 1),      # implicit GEMM, box 56x2
+    (3, 14, 14, 256, 256, 3, 1, 1),    # implicit GEMM, box 14x7
+    (5, 7, 7, 512, 512, 3, 1, 1),      # implicit GEMM, boxes span images
+    (2, 10, 13, 32, 48, 3, 1, 1),      # channel tails
+    (2, 12, 12, 32, 64, 3, 1, 0),      # no padding
+    (4, 14, 14, 256, 1024, 1, 1, 0),   # 1x1 → plain GEMM
+    (2, 28, 28, 128, 128, 3, 2, 1),    # strided → gather path
+    (2, 64, 64, 3, 64, 7, 2, 3),       # RGB stem
+    (4, 4, 4, 512, 1, 4, 1, 0),        # single output channel (DCGAN discriminator head)
+])
+def test_conv2d(N, H, W, Cin, Cout, k, s, p):
+    from determined_b200.ops import conv as C
+
+    torch.manual_seed(N + H + Cin + Cout)
+    x = _bf(torch.randn(N, Cin, H, W, device="cuda"))
+    ref = nn.Conv2d(Cin, Cout, k, s, p)
+    with torch.no_grad():
+        ref.weight.copy_(_bf(ref.weight))
+    _compare(C.Conv2d(Cin, Cout, k, s, p), ref, x)
+
+
+@pytest.mark.parametrize("N,H,Cin,Cout,k,s,p", [(4, 1, 100, 512, 4, 1, 0), (2, 8, 256, 128, 4, 2, 1), (2, 16, 64, 3, 4, 2, 1)])
+def test_conv_transpose2d(N, H, Cin, Cout, k, s, p):
+    from determined_b200.ops import conv as C
+
+    torch.manual_seed(H + Cin)
+    x = _bf(torch.randn(N, Cin, H, H, device="cuda"))
+    ref = nn.ConvTranspose2d(Cin, Cout, k, s, p)
+    with torch.no_grad():
+        ref.weight.copy_(_bf(ref.weight))
+    _compare(C.ConvTranspose2d(Cin, Cout, k, s, p), ref, x)
+
+
+@pytest.mark.parametrize("C_,act,resid", [(64, "relu", True), (256, None, False), (128, "leaky_relu", False), (2048, "relu", True)])
+def test_batchnorm_fused(C_, act, resid):
+    from determined_b200.ops import conv as C
+
+    torch.manual_seed(C_)
+    x = _bf(torch.randn(4, C_, 7, 9, device="cuda") * 2 + 0.5)
+    r = _bf(torch.randn_like(x)) if resid else None
+    ref = nn.BatchNorm2d(C_).cuda()
+    mine = C.BatchNorm2d(C_, activation=act, negative_slope=0.2).cuda()
+    with torch.no_grad():
+        ref.weight.copy_(torch.rand(C_) + 0.5)
+        ref.bias.copy_(torch.randn(C_) * 0.2)
+    mine.load_state_dict(ref.state_dict())
+    xr = x.clone().requires_grad_(True)
+    xm = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    rr = r.clone().requires_grad_(True) if resid else None
+    rm = r.to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True) if resid else None
+    yr = ref(xr)
+    if resid:
+        yr = yr + rr
+    if act == "relu":
+        yr = torch.relu(yr)
+    elif act == "leaky_relu":
+        yr = nn.functional.leaky_relu(yr, 0.2)
+    ym = mine(xm, rm)
+    assert _rel(ym, yr) < 2e-2
+    assert _rel(mine.running_var, ref.running_var) < 1e-2 and _rel(mine.running_mean, ref.running_mean) < 1e-2
+    g = _bf(torch.randn_like(yr))
+    yr.backward(g)
+    ym.backward(g.to(torch.bfloat16))
+    assert _rel(xm.grad, xr.grad) < 3e-2
+    assert _rel(mine.weight.grad, ref.weight.grad) < 2e-2 and _rel(mine.bias.grad, ref.bias.grad) < 2e-2
+    if resid:
+        assert _rel(rm.grad, rr.grad) < 2e-2
+
+
+def test_pools_activations_dropout():
+    from determined_b200.ops import conv as C
+
+    torch.manual_seed(5)
+    x = _bf(torch.randn(3, 16, 17, 17, device="cuda"))
+    _compare(C.MaxPool2d(3, 2, 1), nn.MaxPool2d(3, 2, 1), x, tol=1e-2)
+    _compare(C.MaxPool2d(2), nn.MaxPool2d(2), x, tol=1e-2)
+
+    class GAP(nn.Module):
+        def forward(self, t):
+            return t.mean(dim=(2, 3))
+    _compare(C.GlobalAvgPool2d(), GAP(), x, tol=1e-2)
+    for kind, refm in [("relu", nn.ReLU()), ("leaky_relu", nn.LeakyReLU(0.2)), ("tanh", nn.Tanh()), ("sigmoid", nn.Sigmoid())]:
+        _compare(C.Activation(kind, 0.2), refm, x, tol=1e-2)
+    d = C.Dropout(0.25).cuda().train()
+    ones = torch.ones(4, 64, 16, 16, device="cuda", dtype=torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    y = d(ones)
+    assert abs((y.float() > 0).float().mean().item() - 0.75) < 0.01
+    y.backward(torch.ones_like(y))
+    assert torch.equal(ones.grad.float() > 0, y.float() > 0)
+
+
+def test_resnet50_step_loss_falls():
+    from determined_b200.models.resnet import resnet50
+    from determined_b200.ops.modules import cross_entropy
+    from determined_b200.parallel.fused_optimizer import FusedOptimizer
+
+    torch.manual_seed(0)
+    model = resnet50(num_classes=16).cuda().train()
+    opt = FusedOptimizer(torch.optim.SGD(model.parameters(), lr=0.02, momentum=0.9))
+    x = torch.randn(16, 3, 64, 64, device="cuda")
+    y = torch.randint(0, 16, (16,), device="cuda")
+    losses = []
+    for _ in range(8):
+        loss = cross_entropy(model(x), y)
+        loss.backward()
+        opt.step(zero_grad=True)
+        losses.append(loss.item())
+    assert all(l == l for l in losses) and losses[-1] < losses[0]
