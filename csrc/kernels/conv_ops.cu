@@ -320,6 +320,35 @@ nchw_to_nhwc_kernel(const float* __restrict__ in, __nv_bfloat16* __restrict__ ou
   }
 }
 
+// uint8 NHWC (decoded image bytes) -> bf16 NHWC with per-channel (x/255 - mean) / std folded into scale/shift.
+// 16 input bytes per thread; C <= 8.
+struct U8Norm { float scale[8], shift[8]; int C; };
+__global__ void __launch_bounds__(256)
+u8_to_bf16_norm_kernel(const uint8_t* __restrict__ in, __nv_bfloat16* __restrict__ out, long long n, const U8Norm p) {
+  const long long i = (static_cast<long long>(blockIdx.x) * 256 + threadIdx.x) * 16;
+  if (i >= n) return;
+  int c = static_cast<int>(i % p.C);
+  if (i + 16 <= n) {
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(in + i));
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    float f[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const float b = static_cast<float>((w[j >> 2] >> (8 * (j & 3))) & 0xFFu);
+      f[j] = fmaf(b, p.scale[c], p.shift[c]);
+      c = (c + 1 == p.C) ? 0 : c + 1;
+    }
+    uint4* o = reinterpret_cast<uint4*>(out + i);
+    o[0] = pack8(f);
+    o[1] = pack8(f + 8);
+  } else {
+    for (long long k = i; k < n; ++k) {
+      out[k] = __float2bfloat16_rn(fmaf(static_cast<float>(in[k]), p.scale[c], p.shift[c]));
+      c = (c + 1 == p.C) ? 0 : c + 1;
+    }
+  }
+}
+
 static inline unsigned blocks_for(long long n) { return static_cast<unsigned>((n + 255) / 256); }
 
 }  // namespace det
@@ -442,6 +471,25 @@ extern "C" int det_nchw_to_nhwc_bf16(const float* in, void* out, int N, int C, i
   DET_REQUIRE(N > 0 && C > 0 && HW > 0 && N <= 65535, "bad tensor shape for the layout conversion");
   dim3 grid((HW + 31) / 32, (C + 31) / 32, N);
   det::nchw_to_nhwc_kernel<<<grid, 256, 0, stream>>>(in, (bf16*)out, C, HW);
+  DET_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// in: uint8 [n] laid out ...HWC with C channels (C <= 8); out: bf16 [n]; y = (x / 255 - mean[c]) / std[c].
+extern "C" int det_u8_to_bf16_norm(const void* in, void* out, long long n, int C, const float* mean_host,
+                                   const float* std_host, cudaStream_t stream) {
+  DET_REQUIRE(n > 0 && C >= 1 && C <= 8, "u8 normalise: 1..8 channels");
+  DET_REQUIRE((reinterpret_cast<uintptr_t>(in) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0,
+              "u8 normalise: pointers must be 16-byte aligned");
+  det::U8Norm p;
+  p.C = C;
+  for (int c = 0; c < 8; ++c) {
+    const float sd = (c < C && std_host) ? std_host[c] : 1.0f;
+    const float mu = (c < C && mean_host) ? mean_host[c] : 0.0f;
+    p.scale[c] = 1.0f / (255.0f * sd);
+    p.shift[c] = -mu / sd;
+  }
+  det::u8_to_bf16_norm_kernel<<<det::blocks_for((n + 15) / 16), 256, 0, stream>>>((const uint8_t*)in, (bf16*)out, n, p);
   DET_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

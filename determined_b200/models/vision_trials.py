@@ -29,11 +29,22 @@ class SyntheticImageDataset(torch.utils.data.Dataset):
     """``size`` random images of ``shape`` with labels in ``[0, num_classes)``; class-dependent mean so that a network
     can actually learn something from it (losses go down, validation error moves)."""
 
-    def __init__(self, size: int, shape: Tuple[int, int, int], num_classes: int, seed: int = 0) -> None:
+    det_batched = True   # __getitems__ returns a collated batch (one gather instead of per-sample indexing + stack)
+
+    def __init__(self, size: int, shape: Tuple[int, int, int], num_classes: int, seed: int = 0, uint8_nhwc: bool = False) -> None:
         g = torch.Generator().manual_seed(seed)
         self.labels = torch.randint(0, num_classes, (size,), generator=g, dtype=torch.int64)
-        proto = torch.randn(num_classes, *shape, generator=torch.Generator().manual_seed(1234)) * 0.5
-        self.images = torch.randn(size, *shape, generator=g) * 0.5 + proto[self.labels]
+        if uint8_nhwc:
+            # decoded-image layout: bytes, height x width x channels (what a JPEG decoder hands over); low-resolution
+            # class prototypes keep construction cheap at ImageNet sizes
+            C, H, W = shape
+            proto = torch.randint(64, 192, (num_classes, 8, 8, C), generator=torch.Generator().manual_seed(1234), dtype=torch.int16)
+            noise = torch.randint(-48, 48, (size, H, W, C), generator=g, dtype=torch.int16)
+            up = proto[self.labels].repeat_interleave((H + 7) // 8, 1).repeat_interleave((W + 7) // 8, 2)[:, :H, :W]
+            self.images = (up + noise).clamp_(0, 255).to(torch.uint8)
+        else:
+            proto = torch.randn(num_classes, *shape, generator=torch.Generator().manual_seed(1234)) * 0.5
+            self.images = torch.randn(size, *shape, generator=g) * 0.5 + proto[self.labels]
 
     def __len__(self) -> int:
         return self.images.shape[0]
@@ -41,43 +52,70 @@ class SyntheticImageDataset(torch.utils.data.Dataset):
     def __getitem__(self, i: int):
         return self.images[i], self.labels[i]
 
+    def __getitems__(self, idxs):
+        idx = torch.as_tensor(idxs, dtype=torch.int64)
+        return self.images.index_select(0, idx), self.labels.index_select(0, idx)
 
-def _dataset(context, split: str, default_size: int, shape, num_classes: int) -> torch.utils.data.Dataset:
+
+IMAGENET_MEAN, IMAGENET_STD = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+
+
+def normalize_uint8_images(data: torch.Tensor, mean=IMAGENET_MEAN, std=IMAGENET_STD) -> torch.Tensor:
+    """uint8 NHWC bytes → normalised logical-NCHW activations: one fused kernel on CUDA (bf16 NHWC, no transpose needed
+    because the convolutions work in NHWC), plain torch on CPU."""
+    if data.is_cuda:
+        from ..ops import functional as F
+        from ..ops.conv import from_nhwc
+
+        return from_nhwc(F.u8_nhwc_to_bf16(data.contiguous(), mean, std))
+    m = torch.tensor(mean).view(1, -1, 1, 1)
+    s_ = torch.tensor(std).view(1, -1, 1, 1)
+    return (data.permute(0, 3, 1, 2).float() / 255.0 - m) / s_
+
+
+def _dataset(context, split: str, default_size: int, shape, num_classes: int, uint8_nhwc: bool = False) -> torch.utils.data.Dataset:
     data_cfg = context.get_data_config() or {}
     d = data_cfg.get("dir")
     if d and os.path.exists(os.path.join(d, f"{split}.pt")):
         images, labels = torch.load(os.path.join(d, f"{split}.pt"))
         return torch.utils.data.TensorDataset(images.float(), labels.long())
     size = int(data_cfg.get(f"{split}_size", default_size))
-    return SyntheticImageDataset(size, shape, num_classes, seed=1 if split == "train" else 2)
+    return SyntheticImageDataset(size, shape, num_classes, seed=1 if split == "train" else 2, uint8_nhwc=uint8_nhwc)
 
 
-def _loader(context, ds, shuffle: bool) -> dp.DataLoader:
+def _loader(context, ds, shuffle: bool, prefetch: int = 0) -> dp.DataLoader:
     return dp.DataLoader(ds, batch_size=context.get_per_slot_batch_size(), shuffle=shuffle, drop_last=True,
-                         pin_memory=torch.cuda.is_available())
+                         pin_memory=torch.cuda.is_available(), prefetch_batches=prefetch)
 
 
 class _ClassifierTrial(dp.PyTorchTrial):
     shape: Tuple[int, int, int] = (1, 28, 28)
     num_classes = 10
     train_size, val_size = 4096, 1024
+    uint8_input = False   # data set serves uint8 NHWC bytes; normalisation runs on the device
+    prefetch = 0
 
     def build_training_data_loader(self) -> dp.DataLoader:
-        return _loader(self.context, _dataset(self.context, "train", self.train_size, self.shape, self.num_classes), True)
+        ds = _dataset(self.context, "train", self.train_size, self.shape, self.num_classes, self.uint8_input)
+        return _loader(self.context, ds, True, self.prefetch)
 
     def build_validation_data_loader(self) -> dp.DataLoader:
-        return _loader(self.context, _dataset(self.context, "validation", self.val_size, self.shape, self.num_classes), False)
+        ds = _dataset(self.context, "validation", self.val_size, self.shape, self.num_classes, self.uint8_input)
+        return _loader(self.context, ds, False)
+
+    def _inputs(self, data: torch.Tensor) -> torch.Tensor:
+        return normalize_uint8_images(data) if data.dtype == torch.uint8 else data
 
     def train_batch(self, batch: Any, epoch_idx: int, batch_idx: int) -> Dict[str, torch.Tensor]:
         data, labels = batch
-        loss = cross_entropy(self.model(data), labels)
+        loss = cross_entropy(self.model(self._inputs(data)), labels)
         self.context.backward(loss)
         self.context.step_optimizer(self.optimizer)
         return {"loss": loss.detach()}
 
     def evaluate_batch(self, batch: Any) -> Dict[str, Any]:
         data, labels = batch
-        logits = self.model(data)
+        logits = self.model(self._inputs(data))
         loss = cross_entropy(logits, labels)
         acc = (logits.argmax(dim=-1) == labels).float().mean()
         return {"validation_loss": loss, "accuracy": acc, "validation_error": 1.0 - acc}
@@ -111,6 +149,7 @@ class CIFARTrial(_ClassifierTrial):
 class ResNet50Trial(_ClassifierTrial):
     shape, num_classes = (3, 224, 224), 1000
     train_size, val_size = 1024, 256
+    uint8_input, prefetch = True, 2
 
     def __init__(self, context: dp.PyTorchTrialContext) -> None:
         self.context = context

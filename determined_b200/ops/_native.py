@@ -49,6 +49,7 @@ _SIGNATURES = {
     "det_act_bwd": [c_void_p, c_void_p, c_void_p, c_ll, c_int, c_float, c_void_p],
     "det_dropout": [c_void_p, c_void_p, c_ll, c_float, c_uint, c_void_p, c_void_p],
     "det_nchw_to_nhwc_bf16": [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p],
+    "det_u8_to_bf16_norm": [c_void_p, c_void_p, c_ll, c_int, c_void_p, c_void_p, c_void_p],
     "det_fused_optimizer_step": [c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_void_p, c_void_p,
                                  c_void_p, c_int, c_void_p],
     "det_grad_sumsq_finite": [c_void_p, c_ll, c_void_p, c_void_p, c_void_p, c_void_p],

@@ -327,17 +327,23 @@ class _FrozenBatchNormFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, resid, gamma, beta, mean, rstd, act, slope):
         y = F.bn_apply(x, resid, mean, rstd, gamma, beta, x.shape[-1], act, slope)
-        ctx.save_for_backward(y if act != F.ACT_NONE else None, rstd)
-        ctx.gamma, ctx.cfg = gamma, (act, slope, resid is not None)
+        ctx.save_for_backward(y if act != F.ACT_NONE else None, rstd, x, mean)
+        ctx.gamma, ctx.beta, ctx.cfg = gamma, beta, (act, slope, resid is not None)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        y, rstd = ctx.saved_tensors
+        y, rstd, x, mean = ctx.saved_tensors
         act, slope, has_resid = ctx.cfg
         dy = dy.contiguous()
         if act != F.ACT_NONE:
             dy = F.act_bwd(dy, y, act, slope)
+        C = dy.shape[-1]
+        if ctx.beta is not None and ctx.beta.requires_grad:      # rare path (fine-tuning with frozen statistics)
+            grad_buffer(ctx.beta).add_(dy.reshape(-1, C).float().sum(0))
+        if ctx.gamma is not None and ctx.gamma.requires_grad:
+            xhat = (x.reshape(-1, C).float() - mean) * rstd
+            grad_buffer(ctx.gamma).add_((dy.reshape(-1, C).float() * xhat).sum(0))
         scale = rstd if ctx.gamma is None else rstd * ctx.gamma.detach()
         dx = (dy.float() * scale).to(torch.bfloat16)
         return dx, (dy if has_resid else None), None, None, None, None, None, None

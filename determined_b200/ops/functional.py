@@ -343,3 +343,13 @@ def nchw_to_nhwc_bf16(x: torch.Tensor) -> torch.Tensor:
     out = torch.empty(N, H, W, C, dtype=torch.bfloat16, device=x.device)
     _native.call("det_nchw_to_nhwc_bf16", _p(x), _p(out), N, C, H * W, _stream())
     return out
+
+
+def u8_nhwc_to_bf16(x: torch.Tensor, mean, std) -> torch.Tensor:
+    """uint8 NHWC image bytes → normalised bf16 NHWC: ``(x / 255 - mean[c]) / std[c]`` in one pass."""
+    C = x.shape[-1]
+    out = torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+    m = (ctypes.c_float * C)(*[float(v) for v in mean])
+    s = (ctypes.c_float * C)(*[float(v) for v in std])
+    _native.call("det_u8_to_bf16_norm", _p(x), _p(out), x.numel(), C, m, s, _stream())
+    return out

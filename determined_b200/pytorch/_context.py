@@ -144,16 +144,18 @@ class PyTorchTrialContext(TrialContext):
         self.models.append(model)
         return model
 
-    def wrap_optimizer(self, optimizer: torch.optim.Optimizer, backward_passes_per_step: int = 1) -> torch.optim.Optimizer:
+    def wrap_optimizer(self, optimizer: torch.optim.Optimizer, backward_passes_per_step: int = 1,
+                       fused: Optional[bool] = None) -> torch.optim.Optimizer:
         """Adopt a torch optimizer. On CUDA this flattens its parameters into fp32 buckets inside the symmetric
         arena and swaps in the fused update; elsewhere the optimizer is used as is. ``backward_passes_per_step``
         is accepted for API compatibility (several ``backward`` calls per batch accumulate into the same
-        bucket; communication happens once, in ``step_optimizer``)."""
+        bucket; communication happens once, in ``step_optimizer``). ``fused=False`` (an extension) keeps the stock
+        torch optimizer and per-tensor collectives — the comparison arm of the benchmarks."""
         if not isinstance(optimizer, torch.optim.Optimizer):
             raise TypeError("wrap_optimizer expects a torch.optim.Optimizer")
         if backward_passes_per_step < 1:
             raise ValueError("backward_passes_per_step must be >= 1")
-        if self.device.type == "cuda":
+        if self.device.type == "cuda" and fused is not False:
             dev = self.device
 
             def alloc(n: int, dtype: torch.dtype, kind: str) -> torch.Tensor:

@@ -79,6 +79,59 @@ def adapt_batch_sampler(batch_sampler: Sampler, repeat: bool = False, skip: int 
     return batch_sampler
 
 
+def _identity(batch: Any) -> Any:
+    return batch
+
+
+class _Prefetcher:
+    """Runs the wrapped loader (batch gather, collation, page-locking) in a background thread, ``depth`` batches ahead
+    of the training loop, preserving order. An extension over the reference (whose loaders rely on worker processes
+    only): with CUDA graphs the training thread has little to do, so host-side batch assembly would otherwise be the
+    serial bottleneck of large-image models."""
+
+    def __init__(self, loader: Any, depth: int) -> None:
+        self.loader, self.depth = loader, depth
+
+    def __len__(self) -> int:
+        return len(self.loader)
+
+    def __iter__(self) -> Iterator:
+        import queue
+        import threading
+
+        q: "queue.Queue" = queue.Queue(maxsize=self.depth)
+        end = object()
+        stop = threading.Event()
+
+        def work() -> None:
+            try:
+                for item in self.loader:
+                    while not stop.is_set():
+                        try:
+                            q.put(item, timeout=0.2)
+                            break
+                        except queue.Full:
+                            continue
+                    if stop.is_set():
+                        return
+                q.put(end)
+            except BaseException as e:  # noqa: BLE001 - forwarded to the consumer
+                q.put(e)
+
+        t = threading.Thread(target=work, daemon=True, name="det-prefetch")
+        t.start()
+        try:
+            while True:
+                item = q.get()
+                if item is end:
+                    return
+                if isinstance(item, BaseException):
+                    raise item
+                yield item
+        finally:
+            stop.set()
+
+
 class DataLoader:
     """Holds the arguments of a ``torch.utils.data.DataLoader`` so the harness can build the real
     loader later with the repeat / shard / skip adapters. Map-style datasets only."""
@@ -87,7 +140,7 @@ class DataLoader:
                  sampler: Optional[Sampler] = None, batch_sampler: Optional[Sampler] = None, num_workers: int = 0,
                  collate_fn: Optional[Callable] = None, pin_memory: bool = False, drop_last: bool = False,
                  timeout: float = 0, worker_init_fn: Optional[Callable] = None, multiprocessing_context: Any = None,
-                 generator: Any = None) -> None:
+                 generator: Any = None, prefetch_batches: int = 0) -> None:
         if isinstance(dataset, torch.utils.data.IterableDataset):
             raise TypeError("det.pytorch.DataLoader supports map-style datasets only")
         if batch_sampler is not None:
@@ -110,17 +163,22 @@ class DataLoader:
         self.timeout = timeout
         self.worker_init_fn = worker_init_fn
         self.multiprocessing_context = multiprocessing_context
+        self.prefetch_batches = int(prefetch_batches)
 
     def get_data_loader(self, repeat: bool = False, skip: int = 0, num_replicas: int = 1,
-                        rank: int = 0) -> _TorchDataLoader:
+                        rank: int = 0) -> Any:
         bs = adapt_batch_sampler(self.batch_sampler, repeat=repeat, skip=skip, num_replicas=num_replicas, rank=rank)
         kwargs: Dict[str, Any] = dict(batch_sampler=bs, num_workers=self.num_workers, pin_memory=self.pin_memory,
                                       timeout=self.timeout, worker_init_fn=self.worker_init_fn)
         if self.collate_fn is not None:
             kwargs["collate_fn"] = self.collate_fn
+        elif getattr(self.dataset, "det_batched", False) and hasattr(self.dataset, "__getitems__"):
+            # the data set gathers a whole batch in one indexing operation and returns it already collated
+            kwargs["collate_fn"] = _identity
         if self.multiprocessing_context is not None and self.num_workers > 0:
             kwargs["multiprocessing_context"] = self.multiprocessing_context
-        return _TorchDataLoader(self.dataset, **kwargs)
+        loader = _TorchDataLoader(self.dataset, **kwargs)
+        return _Prefetcher(loader, self.prefetch_batches) if self.prefetch_batches > 0 else loader
 
     def __iter__(self) -> Iterator:
         return iter(self.get_data_loader())

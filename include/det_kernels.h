@@ -134,6 +134,9 @@ int det_act_bwd(const void* dy, const void* y, void* dx, long long n, int act, f
 int det_dropout(const void* x, void* y, long long n, float p, unsigned int seed, const unsigned int* seed_dev,
                 cudaStream_t stream);
 int det_nchw_to_nhwc_bf16(const float* in, void* out, int N, int C, int HW, cudaStream_t stream);
+/* decoded image bytes (uint8, ...HWC, C <= 8) -> bf16 with (x/255 - mean[c]) / std[c]; mean/std are HOST arrays */
+int det_u8_to_bf16_norm(const void* in, void* out, long long n, int C, const float* mean_host, const float* std_host,
+                        cudaStream_t stream);
 
 #ifdef __cplusplus
 }
