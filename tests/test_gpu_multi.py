@@ -1,0 +1,35 @@
+"""Multi-GPU checks (skipped with fewer than two GPUs): the peer-memory collectives against NCCL, and a two-slot trial
+whose replicas must stay identical while the fused all-reduce kernel carries the gradients."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+from tests.test_distributed import ROOT, _free_port, run_ranks
+
+pytestmark = pytest.mark.gpu
+
+
+def _need_two():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+
+
+def test_peer_memory_collectives_match_nccl():
+    _need_two()
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                          "127.0.0.1", "--master-port", str(_free_port()), os.path.join(ROOT, "scripts", "gpu_check_comm.py")],
+                         cwd=ROOT, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
+
+
+def test_dp2_trial_on_gpus(tmp_path):
+    _need_two()
+    rep = run_ranks(2, "mnist_gpu", tmp_path, timeout=600)
+    a, b = rep["params_by_rank"]
+    assert a == b, "replicas diverged"
+    losses = [m["loss"] for m in rep["training"]]
+    assert losses[-1] < losses[0]
+    assert rep["comm"].get("p2p") is True, rep["comm"]
