@@ -10,6 +10,7 @@
 #include "lttb.hpp"
 #include "model.hpp"
 #include "nprand.hpp"
+#include "provisioner.hpp"
 #include "scheduler.hpp"
 #include "searcher.hpp"
 #include "sequencer.hpp"
@@ -241,6 +242,14 @@ char* det_core_sequencer_state(void* h) {
 // ---- scheduler / misc -----------------------------------------------------------------------------------------------------------
 char* det_core_schedule(const char* in) {
   return guarded([&] { return schedule_json(Json::parse(in)); });
+}
+// in: {"config": {max_instances, slots_per_instance, max_idle_agent_period, max_agent_starting_period},
+//      "snapshot": {instances, agents, demand, now}} -> {"launch": n, "terminate": [...], "reasons": {...}}
+char* det_core_scale_decide(const char* in) {
+  return guarded([&] {
+    Json j = Json::parse(in);
+    return scale_decide(ProvisionerConfig::from_json(j["config"]), j["snapshot"]);
+  });
 }
 // in: {"points": [[x,y],...], "threshold": n} -> [[x,y],...]
 char* det_core_lttb(const char* in) {

@@ -1,6 +1,7 @@
 // det-agent — node agent: detects devices, registers with the master, reports slots; prints the detection result
 // with --detect-only. On the single-box deployment the master embeds the same machinery as "agent-local"; det-agent
-// serves extra nodes and device inspection.
+// serves extra nodes: it long-polls the master for container commands (start / signal), runs them under its own
+// ContainerManager with the slot's CUDA_VISIBLE_DEVICES mask, and posts container state changes and log lines back.
 //   det-agent [--master-host H] [--master-port N] [--agent-id ID] [--label L] [--slot-type auto|gpu|cpu|none]
 //             [--visible-gpus LIST] [--artificial-slots N] [--detect-only]
 // (reference: agent/cmd/determined-agent/run.go, agent/internal/options.go:12-103, agent.go:60-150)
@@ -8,6 +9,8 @@
 
 #include <csignal>
 #include <iostream>
+#include <mutex>
+#include <thread>
 
 #include "agent.hpp"
 #include "http.hpp"
@@ -34,6 +37,7 @@ int main(int argc, char** argv) {
     else if (a == "--visible-gpus") visible = next();
     else if (a == "--artificial-slots") artificial = atoi(next().c_str());
     else if (a == "--detect-only") detect_only = true;
+    else if (a == "--repo-root" || a == "--python") next();   // accepted for symmetry with det-master; specs carry both
     else { std::cerr << "unknown flag " << a << "\n"; return 2; }
   }
   auto devices = detect_devices(slot_type, visible, artificial);
@@ -57,11 +61,70 @@ int main(int argc, char** argv) {
     sleep(2);
   }
   std::cerr << "det-agent " << id << ": registered " << devices.size() << " slots with " << host << ":" << port << "\n";
-  while (!g_stop) {  // heartbeat: re-register if the master restarted
-    sleep(5);
-    if (http_request(host, port, "GET", "/api/v1/master", "", &out, 5) != 200) continue;
-    http_request(host, port, "POST", "/api/v1/agents/" + id + "/register", body.dump(), &out, 10);
+
+  // outbox of container events and log lines, flushed to the master in batches
+  std::mutex out_mu;
+  Json pending_events = Json::array(), pending_logs = Json::array();
+  ContainerManager cm(
+      [&](const ContainerEvent& ev) {
+        std::lock_guard<std::mutex> g(out_mu);
+        Json e = Json::object();
+        e["container_id"] = ev.container_id; e["state"] = ev.state; e["exit_code"] = static_cast<long long>(ev.exit_code); e["failure"] = ev.failure;
+        pending_events.push_back(e);
+      },
+      [&](const LogLine& l) {
+        std::lock_guard<std::mutex> g(out_mu);
+        Json e = Json::object();
+        e["container_id"] = l.container_id; e["stdtype"] = l.stdtype; e["message"] = l.message;
+        e["rank"] = l.rank >= 0 ? Json(static_cast<long long>(l.rank)) : Json();
+        pending_logs.push_back(e);
+      });
+  std::thread flusher([&] {
+    while (!g_stop) {
+      usleep(100 * 1000);
+      Json b = Json::object();
+      {
+        std::lock_guard<std::mutex> g(out_mu);
+        if (pending_events.arr().empty() && pending_logs.arr().empty()) continue;
+        b["events"] = pending_events; b["logs"] = pending_logs;
+        pending_events = Json::array(); pending_logs = Json::array();
+      }
+      std::string o;
+      for (int attempt = 0; attempt < 20 && !g_stop; ++attempt) {
+        if (http_request(host, port, "POST", "/api/v1/agents/" + id + "/events", b.dump(), &o, 10) == 200) break;
+        sleep(1);
+      }
+    }
+  });
+  time_t last_register = time(nullptr);
+  while (!g_stop) {
+    std::string resp;
+    const int st = http_request(host, port, "GET", "/api/v1/agents/" + id + "/commands?wait_ms=5000", "", &resp, 15);
+    if (st != 200) { sleep(2); }
+    else {
+      Json cmds = Json::parse(resp)["commands"];
+      for (auto& c : cmds.arr()) {
+        if (c["type"].as_string() == "start") {
+          ContainerSpec spec;
+          spec.container_id = c["container_id"].as_string(); spec.task_id = c["task_id"].as_string();
+          spec.description = c["description"].as_string(); spec.cwd = c["cwd"].as_string();
+          for (auto& a : c["argv"].arr()) spec.argv.push_back(a.as_string());
+          for (auto& kv : c["env"].obj()) spec.env[kv.first] = kv.second.as_string();
+          for (auto& d : c["devices"].arr())
+            spec.devices.push_back(Device{static_cast<int>(d["id"].as_int()), d["brand"].as_string(), d["uuid"].as_string(), d["type"].as_string()});
+          cm.start(spec);
+        } else if (c["type"].as_string() == "signal") {
+          cm.signal(c["container_id"].as_string(), static_cast<int>(c["signal"].as_int(SIGTERM)));
+        }
+      }
+    }
+    if (time(nullptr) - last_register >= 5) {  // heartbeat: re-register if the master restarted
+      last_register = time(nullptr);
+      http_request(host, port, "POST", "/api/v1/agents/" + id + "/register", body.dump(), &out, 10);
+    }
   }
+  cm.kill_all();
+  flusher.join();
   http_request(host, port, "POST", "/api/v1/agents/" + id + "/unregister", "{}", &out, 5);
   return 0;
 }

@@ -108,7 +108,7 @@ class CommandActor : public Actor {
       container_ = spec.container_id;
       m_->register_container(container_, ctx.self(), -id_);
       set_state("RUNNING");
-      m_->containers->start(spec);
+      m_->start_container(a["agent"].as_string(), spec);
     } else if (msg.type == "container_event") {
       if (msg.body["state"].as_string() == "TERMINATED") {
         m_->unregister_container(container_);
@@ -118,7 +118,7 @@ class CommandActor : public Actor {
         ctx.stop_self();
       }
     } else if (msg.type == "kill" || msg.type == "release_resources") {
-      if (!container_.empty()) m_->containers->signal(container_, SIGKILL);
+      if (!container_.empty()) m_->signal_container(container_, SIGKILL);
       else { set_state("TERMINATED"); ctx.tell(m_->rm, "release", obj({{"task_id", task_id_}})); ctx.stop_self(); }
       msg.respond(Json(true));
     } else if (msg.type == "log") {
@@ -170,7 +170,49 @@ void Master::unregister_container(const std::string& cid) {
   std::lock_guard<std::mutex> g(container_mu_);
   container_owner_.erase(cid);
 }
+void Master::start_container(const std::string& agent_id, const ContainerSpec& spec) {
+  if (agent_id == "agent-local") { containers->start(spec); return; }
+  Json j = obj({{"type", "start"}, {"container_id", spec.container_id}, {"task_id", spec.task_id}, {"description", spec.description},
+                {"cwd", spec.cwd}});
+  Json argv = Json::array();
+  for (auto& a : spec.argv) argv.push_back(Json(a));
+  j["argv"] = argv;
+  Json env = Json::object();
+  for (auto& kv : spec.env) env[kv.first] = kv.second;
+  j["env"] = env;
+  Json devs = Json::array();
+  for (auto& d : spec.devices) devs.push_back(d.to_json());
+  j["devices"] = devs;
+  std::lock_guard<std::mutex> g(agent_cmd_mu_);
+  container_agent_[spec.container_id] = agent_id;
+  agent_cmds_[agent_id].push_back(j);
+  agent_cmd_cv_.notify_all();
+}
+void Master::signal_container(const std::string& container_id, int sig) {
+  {
+    std::lock_guard<std::mutex> g(agent_cmd_mu_);
+    auto it = container_agent_.find(container_id);
+    if (it != container_agent_.end()) {
+      agent_cmds_[it->second].push_back(obj({{"type", "signal"}, {"container_id", container_id}, {"signal", static_cast<long long>(sig)}}));
+      agent_cmd_cv_.notify_all();
+      return;
+    }
+  }
+  if (containers) containers->signal(container_id, sig);
+}
+Json Master::take_agent_commands(const std::string& agent_id, int wait_ms) {
+  std::unique_lock<std::mutex> lk(agent_cmd_mu_);
+  agent_cmd_cv_.wait_for(lk, std::chrono::milliseconds(wait_ms), [&] { return !agent_cmds_[agent_id].empty(); });
+  Json out = Json::array();
+  for (auto& c : agent_cmds_[agent_id]) out.push_back(c);
+  agent_cmds_[agent_id].clear();
+  return out;
+}
 void Master::route_container_event(const ContainerEvent& ev) {
+  if (ev.state == "TERMINATED") {
+    std::lock_guard<std::mutex> g(agent_cmd_mu_);
+    container_agent_.erase(ev.container_id);
+  }
   ActorRef owner;
   {
     std::lock_guard<std::mutex> g(container_mu_);

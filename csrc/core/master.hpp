@@ -5,6 +5,7 @@
 // agent/internal/agent.go → the embedded local agent (ContainerManager) plus det-agent for extra nodes.
 #pragma once
 #include <atomic>
+#include <condition_variable>
 #include <map>
 #include <memory>
 #include <mutex>
@@ -17,6 +18,8 @@
 #include "http.hpp"
 #include "json.hpp"
 #include "model.hpp"
+#include "provisioner.hpp"
+#include "rw_coordinator.hpp"
 #include "scheduler.hpp"
 #include "searcher.hpp"
 #include "sequencer.hpp"
@@ -65,6 +68,11 @@ class Master {
   std::unique_ptr<ContainerManager> containers;
   std::vector<Device> devices;
   ActorRef rm, logger, experiments_root, commands_root;
+  RWCoordinator rw;
+  std::mutex agent_cmd_mu_;
+  std::condition_variable agent_cmd_cv_;
+  std::map<std::string, std::vector<Json>> agent_cmds_;      // agent id -> pending commands
+  std::map<std::string, std::string> container_agent_;       // container id -> agent id (remote ones only)   // data-layer reader/writer leases (reference: master/internal/rw_coordinator.go)
   std::string cluster_id;
   std::atomic<long long> started_at{0};
 
@@ -77,6 +85,11 @@ class Master {
                               const std::string& owner);
   ActorRef experiment_actor(long long id);
   void route_container_event(const ContainerEvent& ev);
+  // Container placement: "agent-local" runs under the master's own ContainerManager; any other agent receives the
+  // spec through its command queue (long-polled by det-agent) and reports events / logs back over REST.
+  void start_container(const std::string& agent_id, const ContainerSpec& spec);
+  void signal_container(const std::string& container_id, int sig);
+  Json take_agent_commands(const std::string& agent_id, int wait_ms);
   void route_log(const LogLine& l);
   void register_container(const std::string& container_id, const ActorRef& owner, long long trial_id);
   void unregister_container(const std::string& container_id);

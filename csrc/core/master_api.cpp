@@ -53,7 +53,8 @@ void Master::register_routes() {
   Master* m = this;
   http.set_middleware([m](const HttpRequest& req, HttpResponse& resp) {
     // harness / agent callbacks and login are exempt; everything else needs a session when auth is required
-    static const char* open[] = {"/api/v1/auth/login", "/api/v1/trials/", "/api/v1/trial_logs", "/api/v1/master", "/info", "/api/v1/agents/"};
+    static const char* open[] = {"/api/v1/auth/login", "/api/v1/trials/", "/api/v1/trial_logs", "/api/v1/master", "/info", "/api/v1/agents/",
+                                 "/api/v1/rw_coordinator/", "/ui"};
     for (auto* p : open) if (req.path.rfind(p, 0) == 0) return true;
     if (m->check_auth(req, nullptr)) return true;
     resp = HttpResponse::error(401, "authentication required: POST /api/v1/auth/login");
@@ -66,6 +67,57 @@ void Master::register_routes() {
                    {"uptime_s", static_cast<long long>(std::time(nullptr)) - m->started_at.load()}, {"scheduler", m->cfg.scheduler}}));
   };
   http.route("GET", "/info", info);
+  // ---- data-layer reader/writer leases (reference: /ws/data-layer/{resource}, master/internal/rw_coordinator.go) ----
+  http.route("POST", "/api/v1/rw_coordinator/:resource/:verb", [m](const HttpRequest& r) {
+    const std::string verb = r.params.at("verb");
+    Json b = r.json();
+    const int ttl = static_cast<int>(b["ttl_ms"].as_int(60000));
+    if (verb == "read_lock" || verb == "write_lock") {
+      auto g = m->rw.acquire(r.params.at("resource"), verb == "read_lock", static_cast<int>(b["wait_ms"].as_int(25000)), ttl);
+      return ok(obj({{"granted", g.granted}, {"lease", g.lease}}));
+    }
+    if (verb == "renew") return ok(obj({{"ok", m->rw.renew(b["lease"].as_string(), ttl)}}));
+    if (verb == "unlock") return ok(obj({{"ok", m->rw.release(b["lease"].as_string())}}));
+    return HttpResponse::error(400, "verb must be read_lock, write_lock, renew or unlock");
+  });
+  http.route("GET", "/api/v1/rw_coordinator/:resource/:verb", [m](const HttpRequest& r) {
+    int readers = 0, writer = 0, waiting = 0;
+    m->rw.stats(r.params.at("resource"), readers, writer, waiting);
+    return ok(obj({{"readers", static_cast<long long>(readers)}, {"writer", static_cast<long long>(writer)}, {"waiting", static_cast<long long>(waiting)}}));
+  });
+  // ---- provisioner decision preview (reference: provisioner scale decider; providers are out of scope offline) ----
+  http.route("POST", "/api/v1/provisioner/decide", [](const HttpRequest& r) {
+    Json b = r.json();
+    return ok(scale_decide(ProvisionerConfig::from_json(b["config"]), b["snapshot"]));
+  });
+  // ---- minimal status page (the reference ships a React SPA; this is one static page over the same REST API) ----
+  http.route("GET", "/ui", [](const HttpRequest&) {
+    HttpResponse resp;
+    resp.status = 200;
+    resp.content_type = "text/html; charset=utf-8";
+    resp.body = R"HTML(<!doctype html><html><head><meta charset="utf-8"><title>determined_b200</title>
+<style>body{font:14px system-ui,sans-serif;margin:2em;color:#222}table{border-collapse:collapse;margin:1em 0}
+td,th{border:1px solid #ccc;padding:4px 10px;text-align:left}th{background:#f3f3f3}h2{margin-top:1.5em}.bar{background:#ddd;width:120px;height:10px}
+.bar div{background:#2a7;height:10px}</style></head><body><h1>determined_b200 master</h1><div id="info"></div>
+<h2>Experiments</h2><table id="exps"><tr><th>id</th><th>description</th><th>state</th><th>searcher</th><th>progress</th><th>trials</th><th>best</th></tr></table>
+<h2>Slots</h2><table id="slots"><tr><th>agent</th><th>slot</th><th>device</th><th>enabled</th><th>container</th></tr></table>
+<h2>Tasks</h2><table id="tasks"><tr><th>id</th><th>name</th><th>slots</th><th>state</th></tr></table>
+<script>
+async function j(u){const r=await fetch(u);return r.json()}
+function row(t,cells){const tr=t.insertRow();cells.forEach(c=>{const td=tr.insertCell();if(c instanceof Node)td.appendChild(c);else td.textContent=c==null?'':c})}
+function clear(t){while(t.rows.length>1)t.deleteRow(1)}
+async function tick(){try{
+ const m=await j('/api/v1/master');document.getElementById('info').textContent='cluster '+(m.cluster_name||'')+' — version '+(m.version||'')+' — scheduler '+(m.scheduler||'');
+ const es=await j('/api/v1/experiments');const te=document.getElementById('exps');clear(te);
+ (es.experiments||es).forEach(e=>{const b=document.createElement('div');b.className='bar';const f=document.createElement('div');f.style.width=Math.round(100*(e.progress||0))+'%';b.appendChild(f);
+  row(te,[e.id,(e.config||{}).description,e.state,((e.config||{}).searcher||{}).name,b,e.num_trials,e.best_validation])});
+ const ss=await j('/api/v1/slots');const ts=document.getElementById('slots');clear(ts);ss.forEach(s=>row(ts,[s.agent_id,s.id,(s.device||{}).brand,s.enabled,s.container_id]));
+ const tk=await j('/api/v1/tasks');const tt=document.getElementById('tasks');clear(tt);tk.forEach(t=>row(tt,[t.id,t.name,t.slots_needed,t.state]));
+}catch(e){}}
+tick();setInterval(tick,2000);
+</script></body></html>)HTML";
+    return resp;
+  });
   http.route("GET", "/api/v1/master", info);
   http.route("GET", "/api/v1/master/config", [m](const HttpRequest&) { return ok(m->cfg.to_json()); });
   http.route("GET", "/logs", [m](const HttpRequest& r) { return ok(arr(m->recent_logs(static_cast<size_t>(r.qi("limit", 1000))))); });
@@ -342,8 +394,25 @@ void Master::register_routes() {
     Json ok_ = m->system.ask(m->rm, verb + "_slot", obj({{"agent", r.params.at("agent")}, {"slot", atoll(r.params.at("slot").c_str())}}));
     return ok_.as_bool(false) ? ok(Json::object()) : not_found("agent");
   });
+  // det-agent's side of the container protocol: long-poll for start / signal commands, report state changes and logs
+  http.route("GET", "/api/v1/agents/:agent/:verb", [m](const HttpRequest& r) {
+    if (r.params.at("verb") != "commands") return HttpResponse::error(404, "unknown agent resource");
+    return ok(obj({{"commands", m->take_agent_commands(r.params.at("agent"), static_cast<int>(r.qi("wait_ms", 20000)))}}));
+  });
   http.route("POST", "/api/v1/agents/:agent/:verb", [m](const HttpRequest& r) {
     const std::string verb = r.params.at("verb");
+    if (verb == "events") {
+      Json b = r.json();
+      for (auto& l : b["logs"].arr()) {
+        LogLine ll;
+        ll.container_id = l["container_id"].as_string(); ll.stdtype = l["stdtype"].str_or("stdout"); ll.message = l["message"].as_string();
+        ll.rank = l["rank"].is_null() ? -1 : static_cast<int>(l["rank"].as_int(-1));
+        m->route_log(ll);
+      }
+      for (auto& e : b["events"].arr())
+        m->route_container_event(ContainerEvent{e["container_id"].as_string(), e["state"].as_string(), static_cast<int>(e["exit_code"].as_int(0)), e["failure"].str_or("")});
+      return ok(Json::object());
+    }
     if (verb == "register") {  // det-agent on another node announces its devices
       Json b = r.json();
       b["id"] = r.params.at("agent");

@@ -76,11 +76,11 @@ class TrialActor : public Actor {
     } else if (t == "terminate_timeout") {
       if (running_ && awaiting_exit_ && msg.body.as_int() == run_id_) {
         m_->log("warn", task_id_ + ": did not exit after TERMINATE; killing");
-        for (auto& c : containers_) m_->containers->signal(c, SIGKILL);
+        for (auto& c : containers_) m_->signal_container(c, SIGKILL);
       }
     } else if (t == "kill") {
       killed_ = true;
-      if (running_) for (auto& c : containers_) m_->containers->signal(c, SIGKILL);
+      if (running_) for (auto& c : containers_) m_->signal_container(c, SIGKILL);
       else finish(ctx, "CANCELED");
       msg.respond(Json(true));
     } else if (t == "agent_lost") {
@@ -96,7 +96,7 @@ class TrialActor : public Actor {
 
   void post_stop(Context&) override {
     if (poll_.reply) poll_.respond(obj({{"type", "TERMINATE"}}));
-    for (auto& c : containers_) { m_->containers->signal(c, SIGKILL); m_->unregister_container(c); }
+    for (auto& c : containers_) { m_->signal_container(c, SIGKILL); m_->unregister_container(c); }
   }
 
  private:
@@ -215,8 +215,7 @@ class TrialActor : public Actor {
       for (auto& kv : config_["environment"]["environment_variables"].obj()) e[kv.first] = kv.second.is_string() ? kv.second.as_string() : kv.second.dump();
       m_->register_container(spec.container_id, ctx.self(), trial_id_);
       containers_.push_back(spec.container_id);
-      if (a["agent"].as_string() != "agent-local") { m_->log("error", "remote agent launch is not wired for " + a["agent"].as_string()); continue; }
-      m_->containers->start(spec);
+      m_->start_container(a["agent"].as_string(), spec);
     }
     running_ = true;
     awaiting_exit_ = false;
@@ -286,7 +285,7 @@ class TrialActor : public Actor {
     if (!ev["failure"].as_string().empty() && exit_failure_.empty()) exit_failure_ = ev["failure"].as_string();
     if (--live_containers_ > 0) {
       // any rank failing takes the whole gang down (reference trial.go:944-949)
-      if (!ev["failure"].as_string().empty()) for (auto& c : containers_) m_->containers->signal(c, SIGKILL);
+      if (!ev["failure"].as_string().empty()) for (auto& c : containers_) m_->signal_container(c, SIGKILL);
       return;
     }
     on_exit(ctx, static_cast<int>(ev["exit_code"].as_int()), exit_failure_);

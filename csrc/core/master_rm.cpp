@@ -24,6 +24,11 @@ class ResourcePoolActor : public Actor {
       schedule(ctx);
       ctx.system().notify_after(ctx.self(), m_->cfg.scheduler_tick_ms, "tick");
     } else if (t == "add_agent") {
+      if (agents_.count(msg.body["id"].as_string())) {   // heartbeat of a known agent: keep its slot assignments
+        agent_info_[msg.body["id"].as_string()]["last_seen"] = msg.body["registered_time"];
+        msg.respond(Json(true));
+        return;
+      }
       AgentState a = AgentState::make(msg.body["id"].as_string(), 0, msg.body["label"].str_or(""),
                                       static_cast<int>(msg.body["max_zero_slot_containers"].as_int(100)));
       Json devs = msg.body["devices"];

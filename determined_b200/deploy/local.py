@@ -1,0 +1,161 @@
+"""``det-deploy local``: run a master (with its in-process agent) and optional extra agents as background processes on
+this box, with pid / log files under a state directory.
+
+Role of the reference's ``deploy/determined_deploy/local`` (docker-compose: Postgres + master + agent containers,
+``cluster-up / cluster-down / master-up / agent-up / logs``). There is no database or container runtime to start here:
+the master keeps its own journal and launches harness processes directly.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import pathlib
+import signal
+import subprocess
+import sys
+import time
+import urllib.request
+from typing import List, Optional
+
+ROOT = pathlib.Path(__file__).resolve().parent.parent.parent
+LIB = ROOT / "determined_b200" / "_lib"
+
+
+def _state_dir(name: str) -> pathlib.Path:
+    d = pathlib.Path(os.environ.get("DET_DEPLOY_DIR", pathlib.Path.home() / ".local" / "share" / "determined_b200")) / name
+    d.mkdir(parents=True, exist_ok=True)
+    return d
+
+
+def _alive(pid: int) -> bool:
+    try:
+        os.kill(pid, 0)
+        return True
+    except OSError:
+        return False
+
+
+def _read_pid(f: pathlib.Path) -> Optional[int]:
+    try:
+        pid = int(f.read_text().strip())
+        return pid if _alive(pid) else None
+    except Exception:
+        return None
+
+
+def master_up(name: str, port: int, slots: int = 0, scheduler: str = "fair_share", extra: Optional[List[str]] = None) -> int:
+    from determined_b200 import _build
+
+    _build.build_core()
+    d = _state_dir(name)
+    if _read_pid(d / "master.pid"):
+        raise SystemExit(f"cluster {name!r} already has a running master (pid {_read_pid(d / 'master.pid')})")
+    port_file = d / "master.port"
+    port_file.unlink(missing_ok=True)
+    cmd = [str(LIB / "det-master"), "--port", str(port), "--data-dir", str(d / "data"), "--repo-root", str(ROOT), "--python", sys.executable,
+           "--scheduler", scheduler, "--print-port-file", str(port_file)]
+    if slots:
+        cmd += ["--artificial-slots", str(slots)]
+    cmd += extra or []
+    proc = subprocess.Popen(cmd, stdout=open(d / "master.log", "a"), stderr=subprocess.STDOUT, start_new_session=True)
+    (d / "master.pid").write_text(str(proc.pid))
+    for _ in range(200):
+        if port_file.exists() and port_file.read_text().strip():
+            break
+        if proc.poll() is not None:
+            raise SystemExit(f"master exited with code {proc.returncode}; see {d / 'master.log'}")
+        time.sleep(0.05)
+    bound = int(port_file.read_text())
+    for _ in range(100):
+        try:
+            urllib.request.urlopen(f"http://127.0.0.1:{bound}/info", timeout=1).read()
+            break
+        except Exception:
+            time.sleep(0.05)
+    return bound
+
+
+def agent_up(name: str, master_port: int, agent_id: str, slots: int = 0) -> int:
+    d = _state_dir(name)
+    cmd = [str(LIB / "det-agent"), "--master-host", "127.0.0.1", "--master-port", str(master_port), "--agent-id", agent_id,
+           "--repo-root", str(ROOT), "--python", sys.executable]
+    if slots:
+        cmd += ["--artificial-slots", str(slots)]
+    proc = subprocess.Popen(cmd, stdout=open(d / f"agent-{agent_id}.log", "a"), stderr=subprocess.STDOUT, start_new_session=True)
+    (d / f"agent-{agent_id}.pid").write_text(str(proc.pid))
+    return proc.pid
+
+
+def cluster_down(name: str) -> List[int]:
+    d = _state_dir(name)
+    stopped = []
+    for f in sorted(d.glob("*.pid"), key=lambda p: p.name.startswith("master")):   # agents first, master last
+        pid = _read_pid(f)
+        if pid:
+            try:
+                os.killpg(pid, signal.SIGTERM)
+            except OSError:
+                try:
+                    os.kill(pid, signal.SIGTERM)
+                except OSError:
+                    pass
+            for _ in range(100):
+                if not _alive(pid):
+                    break
+                time.sleep(0.05)
+            stopped.append(pid)
+        f.unlink(missing_ok=True)
+    return stopped
+
+
+def status(name: str) -> dict:
+    d = _state_dir(name)
+    out = {"name": name, "dir": str(d), "master_pid": _read_pid(d / "master.pid"), "agents": {}}
+    try:
+        out["port"] = int((d / "master.port").read_text())
+    except Exception:
+        out["port"] = None
+    for f in d.glob("agent-*.pid"):
+        out["agents"][f.stem[len("agent-"):]] = _read_pid(f)
+    return out
+
+
+def main(argv: Optional[List[str]] = None) -> None:
+    ap = argparse.ArgumentParser(prog="det-deploy", description="bring a single-box determined_b200 cluster up or down")
+    sub = ap.add_subparsers(dest="flavour", required=True)
+    local = sub.add_parser("local")
+    lsub = local.add_subparsers(dest="verb", required=True)
+    up = lsub.add_parser("cluster-up")
+    up.add_argument("--cluster-name", default="determined")
+    up.add_argument("--master-port", type=int, default=8080)
+    up.add_argument("--agents", type=int, default=0, help="extra det-agent processes besides the master's in-process agent")
+    up.add_argument("--artificial-slots", type=int, default=0, help="CPU slots instead of detected GPUs (testing)")
+    up.add_argument("--scheduler", default="fair_share", choices=["fair_share", "priority", "round_robin"])
+    down = lsub.add_parser("cluster-down")
+    down.add_argument("--cluster-name", default="determined")
+    st = lsub.add_parser("status")
+    st.add_argument("--cluster-name", default="determined")
+    lg = lsub.add_parser("logs")
+    lg.add_argument("--cluster-name", default="determined")
+    for flavour in ("aws", "gcp"):
+        sub.add_parser(flavour)
+    args = ap.parse_args(argv)
+    if args.flavour != "local":
+        raise SystemExit(f"det-deploy {args.flavour}: cloud deployments are not available offline; use `det-deploy local`")
+    if args.verb == "cluster-up":
+        port = master_up(args.cluster_name, args.master_port, args.artificial_slots, args.scheduler)
+        for i in range(args.agents):
+            agent_up(args.cluster_name, port, f"agent-{i + 1}", args.artificial_slots)
+        print(json.dumps({"master": f"127.0.0.1:{port}", "ui": f"http://127.0.0.1:{port}/ui", **status(args.cluster_name)}))
+    elif args.verb == "cluster-down":
+        print(json.dumps({"stopped": cluster_down(args.cluster_name)}))
+    elif args.verb == "status":
+        print(json.dumps(status(args.cluster_name)))
+    elif args.verb == "logs":
+        f = _state_dir(args.cluster_name) / "master.log"
+        print(f.read_text() if f.exists() else "")
+
+
+if __name__ == "__main__":
+    main()

@@ -49,7 +49,7 @@ def load() -> ctypes.CDLL:
         "det_core_sequencer_complete_cached_checkpoints": ([vp], vp), "det_core_sequencer_preclose_checkpoint": ([vp], vp),
         "det_core_sequencer_terminate_workload": ([vp], vp), "det_core_sequencer_roll_back": ([vp], ci),
         "det_core_sequencer_state": ([vp], vp),
-        "det_core_schedule": ([cp], vp), "det_core_lttb": ([cp], vp), "det_core_md5_low64": ([cp], ctypes.c_ulonglong),
+        "det_core_schedule": ([cp], vp), "det_core_lttb": ([cp], vp), "det_core_scale_decide": ([cp], vp), "det_core_md5_low64": ([cp], ctypes.c_ulonglong),
     }
     for name, (args, res) in sigs.items():
         fn = getattr(lib, name)
@@ -229,6 +229,11 @@ class Sequencer:
 
 def schedule(request: Dict[str, Any]) -> Dict[str, Any]:
     return _take_json(load().det_core_schedule(_enc(request)))
+
+
+def scale_decide(config: Dict[str, Any], snapshot: Dict[str, Any]) -> Dict[str, Any]:
+    """Provisioner decision for one snapshot: ``{"launch": n, "terminate": [ids], "reasons": {...}}``."""
+    return _take_json(load().det_core_scale_decide(_enc({"config": config, "snapshot": snapshot})))
 
 
 def lttb(points: List[List[float]], threshold: int) -> List[List[float]]:

@@ -1,0 +1,188 @@
+"""Cluster services around the master: remote agent container protocol, reader/writer leases, provisioner scale
+decisions, det-deploy local, data-layer cache, and the small utility modules."""
+import json
+import os
+import pathlib
+import subprocess
+import sys
+import threading
+import time
+
+import pytest
+import torch
+
+from determined_b200 import check, data_layer, gpu
+from determined_b200.experimental.client import Determined
+from determined_b200.layers._master_client import MasterClient
+from determined_b200.master import _core
+
+ROOT = pathlib.Path(__file__).resolve().parent.parent
+LIB = ROOT / "determined_b200" / "_lib"
+MODEL_DIR = str(ROOT / "tests" / "fixtures" / "xor_model_def")
+
+
+@pytest.fixture(scope="module")
+def slotless_master(tmp_path_factory):
+    """A master whose own agent has NO slots: every trial must run on a remote det-agent."""
+    from determined_b200 import _build
+
+    _build.build_core()
+    tmp = tmp_path_factory.mktemp("m2")
+    port_file = tmp / "port"
+    env = dict(os.environ, DET_CONFIG_DIR=str(tmp / "cfg"))
+    proc = subprocess.Popen([str(LIB / "det-master"), "--port", "0", "--data-dir", str(tmp / "data"), "--slot-type", "none", "--repo-root", str(ROOT),
+                             "--python", sys.executable, "--print-port-file", str(port_file)],
+                            stdout=open(tmp / "master.log", "w"), stderr=subprocess.STDOUT, env=env)
+    for _ in range(200):
+        if port_file.exists() and port_file.read_text().strip():
+            break
+        time.sleep(0.05)
+    port = int(port_file.read_text())
+    os.environ["DET_CONFIG_DIR"] = str(tmp / "cfg")
+    agent = subprocess.Popen([str(LIB / "det-agent"), "--master-host", "127.0.0.1", "--master-port", str(port), "--agent-id", "remote-1",
+                              "--artificial-slots", "2"], stdout=open(tmp / "agent.log", "w"), stderr=subprocess.STDOUT)
+    yield {"url": f"127.0.0.1:{port}", "port": port, "tmp": tmp}
+    for p in (agent, proc):
+        p.terminate()
+        try:
+            p.wait(timeout=5)
+        except Exception:
+            p.kill()
+
+
+def test_trial_runs_on_remote_agent(slotless_master):
+    d = Determined(slotless_master["url"])
+    for _ in range(100):
+        agents = d._session.get("/api/v1/agents")
+        if any(a["id"] == "remote-1" for a in agents):
+            break
+        time.sleep(0.1)
+    assert any(a["id"] == "remote-1" and a["num_slots"] == 2 for a in agents)
+    cfg = {"entrypoint": "model_def:XorTrial", "hyperparameters": {"global_batch_size": 8, "hidden_size": 4, "learning_rate": 0.5},
+           "searcher": {"name": "single", "metric": "validation_loss", "max_length": {"batches": 20}}, "scheduling_unit": 10,
+           "checkpoint_storage": {"type": "shared_fs", "host_path": str(slotless_master["tmp"] / "ckpts")}}
+    exp = d.create_experiment(cfg, MODEL_DIR)
+    assert exp.wait(timeout=180) == "COMPLETED"
+    t = exp.describe()["trials"][0]
+    assert t["total_batches_processed"] == 20
+    logs = d.get_trial(t["id"]).logs()
+    assert logs, "the remote agent's log lines reached the master"
+
+
+def test_rw_coordinator_leases(slotless_master):
+    c = MasterClient("127.0.0.1", slotless_master["port"])
+    r1 = c.request("POST", "/api/v1/rw_coordinator/ds1/read_lock", {"wait_ms": 1000})
+    r2 = c.request("POST", "/api/v1/rw_coordinator/ds1/read_lock", {"wait_ms": 1000})
+    assert r1["granted"] and r2["granted"] and r1["lease"] != r2["lease"]
+    w = c.request("POST", "/api/v1/rw_coordinator/ds1/write_lock", {"wait_ms": 300})
+    assert not w["granted"], "a writer must wait for the readers"
+    got = {}
+
+    def writer():
+        got["w"] = MasterClient("127.0.0.1", slotless_master["port"]).request("POST", "/api/v1/rw_coordinator/ds1/write_lock", {"wait_ms": 5000})
+
+    th = threading.Thread(target=writer)
+    th.start()
+    time.sleep(0.3)
+    st = c.request("GET", "/api/v1/rw_coordinator/ds1/stats")
+    assert st["readers"] == 2 and st["waiting"] == 1
+    late_reader = c.request("POST", "/api/v1/rw_coordinator/ds1/read_lock", {"wait_ms": 200})
+    assert not late_reader["granted"], "readers queue behind a waiting writer (no writer starvation)"
+    for r in (r1, r2):
+        assert c.request("POST", "/api/v1/rw_coordinator/ds1/unlock", {"lease": r["lease"]})["ok"]
+    th.join(timeout=10)
+    assert got["w"]["granted"]
+    assert not c.request("POST", "/api/v1/rw_coordinator/ds1/read_lock", {"wait_ms": 200})["granted"]
+    c.request("POST", "/api/v1/rw_coordinator/ds1/unlock", {"lease": got["w"]["lease"]})
+    # an abandoned lease expires
+    lease = c.request("POST", "/api/v1/rw_coordinator/ds2/write_lock", {"wait_ms": 200, "ttl_ms": 300})
+    assert lease["granted"]
+    time.sleep(0.5)
+    assert c.request("POST", "/api/v1/rw_coordinator/ds2/write_lock", {"wait_ms": 500})["granted"]
+
+
+def test_provisioner_scale_decider():
+    cfg = {"max_instances": 3, "slots_per_instance": 8, "max_idle_agent_period": 60, "max_agent_starting_period": 120}
+    # demand for 20 slots, nothing running: launch ceil(20/8) = 3
+    d = _core.scale_decide(cfg, {"now": 1000, "instances": [], "agents": [], "demand": {"pending_slots": 20}})
+    assert d["launch"] == 3 and d["terminate"] == []
+    # one instance still starting covers part of the demand; cap still applies
+    d = _core.scale_decide(cfg, {"now": 1000, "instances": [{"id": "i1", "state": "starting", "launch_time": 950, "agent": ""}], "agents": [],
+                                 "demand": {"pending_slots": 20}})
+    assert d["launch"] == 2
+    snap = {"now": 1000, "demand": {"pending_slots": 0},
+            "instances": [{"id": "idle", "state": "running", "launch_time": 0, "agent": "a1"},
+                          {"id": "busy", "state": "running", "launch_time": 0, "agent": "a2"},
+                          {"id": "lost", "state": "running", "launch_time": 100, "agent": ""},
+                          {"id": "fresh", "state": "starting", "launch_time": 990, "agent": ""},
+                          {"id": "dead", "state": "stopped", "launch_time": 0, "agent": ""}],
+            "agents": [{"id": "a1", "idle_since": 900, "connected": True}, {"id": "a2", "idle_since": None, "connected": True}]}
+    d = _core.scale_decide(cfg, snap)
+    assert d["launch"] == 0 and sorted(d["terminate"]) == ["dead", "idle", "lost"]
+    assert "idle" in d["reasons"]["idle"]
+    # pool above the cap: shed idle first
+    cfg2 = dict(cfg, max_instances=1, max_idle_agent_period=1e9)
+    d = _core.scale_decide(cfg2, {"now": 10, "demand": {"pending_slots": 0},
+                                  "instances": [{"id": "x", "state": "running", "launch_time": 0, "agent": "a1"},
+                                                {"id": "y", "state": "running", "launch_time": 1, "agent": "a2"}],
+                                  "agents": [{"id": "a1", "idle_since": None, "connected": True}, {"id": "a2", "idle_since": 5, "connected": True}]})
+    assert d["terminate"] == ["y"]
+
+
+def test_det_deploy_local_up_down(tmp_path):
+    env = dict(os.environ, DET_DEPLOY_DIR=str(tmp_path), DET_CONFIG_DIR=str(tmp_path / "cfg"))
+    up = subprocess.run([sys.executable, str(ROOT / "det-deploy"), "local", "cluster-up", "--cluster-name", "t", "--master-port", "0",
+                         "--artificial-slots", "2", "--agents", "1"], capture_output=True, text=True, env=env, timeout=120)
+    assert up.returncode == 0, up.stderr
+    info = json.loads(up.stdout.strip().splitlines()[-1])
+    try:
+        c = MasterClient(*info["master"].split(":")[:1], int(info["master"].split(":")[1]))
+        for _ in range(100):
+            agents = c.request("GET", "/api/v1/agents")
+            if len(agents) == 2:
+                break
+            time.sleep(0.1)
+        assert {a["id"] for a in agents} == {"agent-local", "agent-1"}
+        import urllib.request
+        page = urllib.request.urlopen(f"http://{info['master']}/ui", timeout=5).read().decode()
+        assert "determined_b200 master" in page
+    finally:
+        down = subprocess.run([sys.executable, str(ROOT / "det-deploy"), "local", "cluster-down", "--cluster-name", "t"], capture_output=True,
+                              text=True, env=env, timeout=60)
+    assert down.returncode == 0 and len(json.loads(down.stdout)["stopped"]) == 2
+
+
+def test_data_layer_builds_once_and_serves_cached_copy(tmp_path):
+    calls = []
+    dl = data_layer.DataLayer({"type": "lfs", "container_storage_path": str(tmp_path)})
+
+    @dl.cache_train_dataset("mnist-like", "v1", shuffle=True)
+    def make():
+        calls.append(1)
+        return torch.utils.data.TensorDataset(torch.arange(12.0).view(6, 2), torch.arange(6))
+
+    a = make()
+    b = make()
+    assert len(calls) == 1 and dl.builds == 1
+    assert len(a) == len(b) == 6 and torch.equal(b[3][0], torch.tensor([6.0, 7.0])) and int(b[3][1]) == 3
+    xs, ys = b.__getitems__([0, 5])
+    assert xs.shape == (2, 2) and ys.tolist() == [0, 5]
+    # a new version is a new cache entry; a second process-level DataLayer finds the old one on disk
+    dl2 = data_layer.DataLayer({"type": "lfs", "container_storage_path": str(tmp_path)})
+    again = dl2.cache_train_dataset("mnist-like", "v1")(lambda: pytest.fail("must not rebuild"))()
+    assert len(again) == 6 and dl2.builds == 0
+    with pytest.raises(NotImplementedError):
+        data_layer.DataLayer({"type": "s3", "bucket": "b"})
+
+
+def test_check_and_gpu_helpers():
+    check.true(1)
+    check.eq(2, 2)
+    check.is_in("a", {"a"})
+    check.len_eq([1, 2], 2)
+    with pytest.raises(check.CheckFailedError, match="does not equal"):
+        check.eq(1, 2, "numbers")
+    with pytest.raises(check.CheckFailedError):
+        check.is_instance(1, str)
+    assert isinstance(gpu.get_gpus(), list)          # empty on a CPU box
+    assert gpu.get_gpu_uuids_and_validate(False, []) == []
