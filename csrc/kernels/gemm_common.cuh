@@ -1,0 +1,195 @@
+// gemm_common.cuh — parameter block, fused-epilogue math and the per-chunk epilogue shared by the 1-CTA and the
+// CTA-pair (cta_group::2) GEMM kernels.
+#pragma once
+#include "host_utils.h"
+#include "sm100_ptx.cuh"
+
+namespace det {
+
+enum GemmEpilogue : int {
+  EPI_NONE = 0,
+  EPI_BIAS = 1,        // C = acc + bias
+  EPI_BIAS_GELU = 2,   // Z = acc + bias -> aux_out (optional); C = gelu(Z)
+  EPI_DGELU = 3,       // C = acc * gelu'(aux_in)
+  EPI_BIAS_RESID = 4,  // C = dropout(acc + bias) + aux_in
+};
+enum GemmOut : int { OUT_BF16 = 0, OUT_F32 = 1, OUT_F32_ATOMIC_ADD = 2 };
+
+struct GemmParams {
+  int M, N, K;
+  int tiles_m, tiles_n, splitk, kb_per_split, num_kb;
+  void* C;
+  long long ldc;
+  int out_mode;
+  int epi;
+  float alpha;
+  const float* bias;             // [N] fp32 or null
+  const __nv_bfloat16* aux_in;   // [M, ld_aux] bf16 or null
+  __nv_bfloat16* aux_out;        // [M, ld_aux] bf16 or null
+  long long ld_aux;
+  uint32_t drop_threshold;  // 0 = no dropout
+  float drop_scale;
+  uint32_t drop_seed;
+  const uint32_t* drop_seed_dev;  // optional per-step seed in device memory (CUDA-graph friendly)
+};
+
+// erf GELU through the Abramowitz–Stegun 7.1.26 rational form (|error| < 1.5e-7, far below bf16 resolution): one
+// reciprocal, one exp2 and six FMAs per element instead of libdevice erff's branchy ~40 instructions. The epilogue
+// is instruction-issue bound, so this is what keeps it under the MMA time of a tile.
+__device__ __forceinline__ void phi_terms(float x, float& cdf, float& e) {
+  const float ax = fabsf(x) * 0.70710678118654752f;
+  const float t = __frcp_rn(fmaf(0.3275911f, ax, 1.0f));
+  e = exp2f(-1.4426950408889634f * ax * ax);  // exp(-x^2/2)
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  const float half_erfc = 0.5f * poly * t * e;      // 0.5 * erfc(|x|/sqrt2)
+  cdf = x >= 0.0f ? 1.0f - half_erfc : half_erfc;
+}
+__device__ __forceinline__ float gelu_erf(float x) {
+  float cdf, e;
+  phi_terms(x, cdf, e);
+  return x * cdf;
+}
+__device__ __forceinline__ float dgelu_erf(float x) {
+  float cdf, e;
+  phi_terms(x, cdf, e);
+  return fmaf(x * 0.3989422804014327f, e, cdf);
+}
+
+// Epilogue of one tcgen05.ld chunk: v[CW] = accumulator values of `row`, columns col0 .. col0+CW-1.
+template <int CW>
+__device__ __forceinline__ void gemm_epilogue_chunk(const GemmParams& p, float (&v)[CW], const int row, const bool row_ok, const int col0) {
+  if (col0 >= p.N) return;  // warp-uniform
+  const bool full_cols = (col0 + CW <= p.N);
+  if (p.alpha != 1.0f) {
+#pragma unroll
+    for (int j = 0; j < CW; ++j) v[j] *= p.alpha;
+  }
+  if (p.bias != nullptr) {
+    if (full_cols) {
+      const float4* b4 = reinterpret_cast<const float4*>(p.bias + col0);
+#pragma unroll
+      for (int j = 0; j < CW / 4; ++j) {
+        const float4 b = __ldg(b4 + j);
+        v[4 * j + 0] += b.x; v[4 * j + 1] += b.y; v[4 * j + 2] += b.z; v[4 * j + 3] += b.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < CW; ++j)
+        if (col0 + j < p.N) v[j] += __ldg(p.bias + col0 + j);
+    }
+  }
+  if (row_ok) {
+    const long long aux_off = static_cast<long long>(row) * p.ld_aux + col0;
+    if (p.epi == EPI_BIAS_GELU) {
+      if (p.aux_out != nullptr) {
+        if (full_cols) {
+          uint4* zo = reinterpret_cast<uint4*>(p.aux_out + aux_off);
+#pragma unroll
+          for (int j = 0; j < CW / 8; ++j) {
+            uint4 u;
+            u.x = ptx::pack_bf16x2(v[8 * j + 0], v[8 * j + 1]);
+            u.y = ptx::pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
+            u.z = ptx::pack_bf16x2(v[8 * j + 4], v[8 * j + 5]);
+            u.w = ptx::pack_bf16x2(v[8 * j + 6], v[8 * j + 7]);
+            zo[j] = u;
+          }
+        } else {
+          #pragma unroll
+          for (int j = 0; j < CW; ++j)
+            if (col0 + j < p.N) p.aux_out[aux_off + j] = __float2bfloat16_rn(v[j]);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < CW; ++j) v[j] = gelu_erf(v[j]);
+    } else if (p.epi == EPI_DGELU) {
+      if (full_cols) {
+        const uint4* zi = reinterpret_cast<const uint4*>(p.aux_in + aux_off);
+#pragma unroll
+        for (int j = 0; j < CW / 8; ++j) {
+          const uint4 u = __ldg(zi + j);
+          v[8 * j + 0] *= dgelu_erf(ptx::bf16_lo(u.x)); v[8 * j + 1] *= dgelu_erf(ptx::bf16_hi(u.x));
+          v[8 * j + 2] *= dgelu_erf(ptx::bf16_lo(u.y)); v[8 * j + 3] *= dgelu_erf(ptx::bf16_hi(u.y));
+          v[8 * j + 4] *= dgelu_erf(ptx::bf16_lo(u.z)); v[8 * j + 5] *= dgelu_erf(ptx::bf16_hi(u.z));
+          v[8 * j + 6] *= dgelu_erf(ptx::bf16_lo(u.w)); v[8 * j + 7] *= dgelu_erf(ptx::bf16_hi(u.w));
+        }
+      } else {
+        #pragma unroll
+        for (int j = 0; j < CW; ++j)
+          if (col0 + j < p.N) v[j] *= dgelu_erf(__bfloat162float(p.aux_in[aux_off + j]));
+      }
+    } else if (p.epi == EPI_BIAS_RESID) {
+      if (p.drop_threshold != 0u) {
+        const uint32_t base = static_cast<uint32_t>(row) * static_cast<uint32_t>(p.N) + static_cast<uint32_t>(col0);
+        const uint32_t dseed = p.drop_seed + (p.drop_seed_dev ? __ldg(p.drop_seed_dev) * 0x9E3779B9u : 0u);
+#pragma unroll
+        for (int j = 0; j < CW; ++j)
+          v[j] = dropout_keep(dseed, base + j, p.drop_threshold) ? v[j] * p.drop_scale : 0.0f;
+      }
+      if (full_cols) {
+        const uint4* ri = reinterpret_cast<const uint4*>(p.aux_in + aux_off);
+#pragma unroll
+        for (int j = 0; j < CW / 8; ++j) {
+          const uint4 u = __ldg(ri + j);
+          v[8 * j + 0] += ptx::bf16_lo(u.x); v[8 * j + 1] += ptx::bf16_hi(u.x);
+          v[8 * j + 2] += ptx::bf16_lo(u.y); v[8 * j + 3] += ptx::bf16_hi(u.y);
+          v[8 * j + 4] += ptx::bf16_lo(u.z); v[8 * j + 5] += ptx::bf16_hi(u.z);
+          v[8 * j + 6] += ptx::bf16_lo(u.w); v[8 * j + 7] += ptx::bf16_hi(u.w);
+        }
+      } else {
+        #pragma unroll
+        for (int j = 0; j < CW; ++j)
+          if (col0 + j < p.N) v[j] += __bfloat162float(p.aux_in[aux_off + j]);
+      }
+    }
+    // ---- store ----
+    const long long c_off = static_cast<long long>(row) * p.ldc + col0;
+    if (p.out_mode == OUT_BF16) {
+      __nv_bfloat16* cp = reinterpret_cast<__nv_bfloat16*>(p.C) + c_off;
+      if (full_cols && ((reinterpret_cast<uintptr_t>(cp) & 15) == 0)) {
+        uint4* co = reinterpret_cast<uint4*>(cp);
+#pragma unroll
+        for (int j = 0; j < CW / 8; ++j) {
+          uint4 u;
+          u.x = ptx::pack_bf16x2(v[8 * j + 0], v[8 * j + 1]);
+          u.y = ptx::pack_bf16x2(v[8 * j + 2], v[8 * j + 3]);
+          u.z = ptx::pack_bf16x2(v[8 * j + 4], v[8 * j + 5]);
+          u.w = ptx::pack_bf16x2(v[8 * j + 6], v[8 * j + 7]);
+          co[j] = u;
+        }
+      } else {
+        #pragma unroll
+        for (int j = 0; j < CW; ++j)
+          if (col0 + j < p.N) cp[j] = __float2bfloat16_rn(v[j]);
+      }
+    } else if (p.out_mode == OUT_F32) {
+      float* cp = reinterpret_cast<float*>(p.C) + c_off;
+      if (full_cols && ((reinterpret_cast<uintptr_t>(cp) & 15) == 0)) {
+        float4* co = reinterpret_cast<float4*>(cp);
+#pragma unroll
+        for (int j = 0; j < CW / 4; ++j) co[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      } else {
+        #pragma unroll
+        for (int j = 0; j < CW; ++j)
+          if (col0 + j < p.N) cp[j] = v[j];
+      }
+    } else {
+      float* cp = reinterpret_cast<float*>(p.C) + c_off;
+      if (full_cols && ((reinterpret_cast<uintptr_t>(cp) & 15) == 0)) {
+#pragma unroll
+        for (int j = 0; j < CW / 4; ++j)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(cp + 4 * j),
+                       "f"(v[4 * j]), "f"(v[4 * j + 1]), "f"(v[4 * j + 2]), "f"(v[4 * j + 3])
+                       : "memory");
+      } else {
+        #pragma unroll
+        for (int j = 0; j < CW; ++j)
+          if (col0 + j < p.N) atomicAdd(cp + j, v[j]);
+      }
+    }
+  }
+}
+
+}  // namespace det

@@ -39,7 +39,7 @@ def main():
     for (M, N, K) in [(256, 256, 128), (384, 512, 320), (1000, 776, 200)]:
         for a_mn in (0, 1):
             for b_mn in (0, 1):
-                for bn in (64, 128, 256):
+                for bn in (64, 128, 256, 512):   # 512 = CTA-pair kernel (256 x 256 over two SMs)
                     A = torch.randn(M, K, device=dev).bfloat16()
                     B = torch.randn(N, K, device=dev).bfloat16()
                     ref = A.float() @ B.float().t()
@@ -65,6 +65,13 @@ def main():
     C = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
     gemm(A, B, C, M, N, K, 0, 0, epi=1, bias=bias)
     report("epi bias", rel_err(C, acc + bias), 1.5e-2)
+    C.zero_()
+    gemm(A, B, C, M, N, K, 0, 0, epi=1, bias=bias, force_bn=512)
+    report("epi bias (CTA pair)", rel_err(C, acc + bias), 1.5e-2)
+    Zp = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+    gemm(A, B, C, M, N, K, 0, 0, epi=2, bias=bias, aux_out=Zp, force_bn=512)
+    report("epi bias_gelu C (CTA pair)", rel_err(C, torch.nn.functional.gelu(acc + bias)), 1.5e-2)
+    report("epi bias_gelu Z (CTA pair)", rel_err(Zp, acc + bias), 1.5e-2)
     Z = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
     gemm(A, B, C, M, N, K, 0, 0, epi=2, bias=bias, aux_out=Z)
     report("epi bias_gelu C", rel_err(C, torch.nn.functional.gelu(acc + bias)), 1.5e-2)
@@ -99,6 +106,16 @@ def main():
     G.zero_()
     gemm(dY, X, G, M2, N2, K2, 1, 1, out_mode=2, splitk=1)
     report("wgrad splitk=1 atomic", rel_err(G, ref), 1e-3)
+    G.zero_()
+    gemm(dY, X, G, M2, N2, K2, 1, 1, out_mode=2, force_bn=512)
+    report("wgrad splitk auto (CTA pair)", rel_err(G, ref), 1e-3)
+    # a long persistent run: many tiles per cluster, both TMEM buffers and every smem stage wrap several times
+    Ml, Nl, Kl = 6144, 3072, 768
+    Al = torch.randn(Ml, Kl, device=dev).bfloat16()
+    Bl = (torch.randn(Nl, Kl, device=dev) * 0.05).bfloat16()
+    Cl = torch.empty(Ml, Nl, device=dev, dtype=torch.bfloat16)
+    gemm(Al, Bl, Cl, Ml, Nl, Kl, 0, 0, force_bn=512)
+    report("CTA pair 6144x3072x768", rel_err(Cl, Al.float() @ Bl.float().t()), 1.5e-2)
 
     # timing
     def bench(fn, iters=20):
@@ -119,11 +136,26 @@ def main():
         B = torch.randn(N, K, device=dev).bfloat16()
         C = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
         row = {"M": M, "N": N, "K": K}
-        for bn in (0, 128, 256):
+        for bn in (0, 128, 256, 512):
             ms = bench(lambda: gemm(A, B, C, M, N, K, 0, 0, force_bn=bn))
             row[f"det_bn{bn}_ms"] = round(ms, 4)
             row[f"det_bn{bn}_tflops"] = round(2 * M * N * K / ms / 1e9, 1)
         ms = bench(lambda: torch.matmul(A, B.t(), out=C))
+        row["cublas_ms"] = round(ms, 4)
+        row["cublas_tflops"] = round(2 * M * N * K / ms / 1e9, 1)
+        timing.append(row)
+        print(json.dumps(row), flush=True)
+    # dgrad timing (B MN-major)
+    for (M, N, K) in [(6144, 768, 2304), (6144, 768, 3072), (6144, 3072, 768)]:
+        dY = torch.randn(M, K, device=dev).bfloat16()
+        Wt = torch.randn(K, N, device=dev).bfloat16()
+        dX = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+        row = {"dgrad": True, "M": M, "N": N, "K": K}
+        for bn in (0, 512):
+            ms = bench(lambda: gemm(dY, Wt, dX, M, N, K, 0, 1, force_bn=bn))
+            row[f"det_bn{bn}_ms"] = round(ms, 4)
+            row[f"det_bn{bn}_tflops"] = round(2 * M * N * K / ms / 1e9, 1)
+        ms = bench(lambda: torch.matmul(dY, Wt, out=dX))
         row["cublas_ms"] = round(ms, 4)
         row["cublas_tflops"] = round(2 * M * N * K / ms / 1e9, 1)
         timing.append(row)
@@ -136,7 +168,9 @@ def main():
         ms = bench(lambda: gemm(dY, X, G, M, N, K, 1, 1, out_mode=2))
         Gb = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
         ms2 = bench(lambda: torch.matmul(dY.t(), X, out=Gb))
+        msp = bench(lambda: gemm(dY, X, G, M, N, K, 1, 1, out_mode=2, force_bn=512))
         row = {"wgrad": True, "M": M, "N": N, "K": K, "det_ms": round(ms, 4), "det_tflops": round(2 * M * N * K / ms / 1e9, 1),
+               "det_pair_ms": round(msp, 4), "det_pair_tflops": round(2 * M * N * K / msp / 1e9, 1),
                "cublas_ms": round(ms2, 4), "cublas_tflops": round(2 * M * N * K / ms2 / 1e9, 1)}
         timing.append(row)
         print(json.dumps(row), flush=True)
