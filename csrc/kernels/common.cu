@@ -140,6 +140,10 @@ int make_tma_nd_bf16(CUtensorMap* out, const void* gptr, int rank, const uint64_
   return 0;
 }
 
+// SMs the persistent kernels may occupy (0 = all). Lowered by the host while a gradient all-reduce runs on a side
+// stream, so that the collective's CTAs find free SMs instead of queueing behind full-width persistent grids.
+static int g_sm_limit = 0;
+
 int sm_count() {
   static int counts[64] = {0};
   int dev = 0;
@@ -150,6 +154,7 @@ int sm_count() {
       n = 148;
     counts[dev] = n;
   }
+  if (g_sm_limit > 0 && g_sm_limit < counts[dev]) return g_sm_limit;
   return counts[dev];
 }
 
@@ -158,3 +163,9 @@ int sm_count() {
 extern "C" const char* det_last_error() { return det::g_last_error.c_str(); }
 
 extern "C" int det_kernels_abi_version() { return 1; }
+
+// Limit the SM count every launcher in this library sizes its grid from (0 restores the device's count).
+extern "C" int det_set_sm_limit(int n) {
+  det::g_sm_limit = n < 0 ? 0 : n;
+  return 0;
+}

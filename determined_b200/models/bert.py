@@ -27,7 +27,8 @@ import torch
 import torch.nn as nn
 
 from ..ops import functional as F
-from ..ops.modules import accumulate_bgrad, accumulate_wgrad, grad_buffer, shadow_of
+from ..ops.modules import (accumulate_bgrad, accumulate_wgrad, grad_buffer, note_param_use, notify_grads_written,
+                           shadow_of)
 
 
 @dataclasses.dataclass
@@ -79,6 +80,7 @@ class _BertLayerFn(torch.autograd.Function):
         x2, mean2, rstd2 = F.layernorm_fwd(h2, layer.ln2_weight, layer.ln2_bias, c.layer_norm_eps)
         ctx.save_for_backward(x, qkv, lse, att, h1, mean1, rstd1, x1, z, a, h2, mean2, rstd2)
         ctx.layer, ctx.mask, ctx.dims, ctx.drop = layer, mask, (B, S), (p_h, p_a)
+        note_param_use(ctx, *layer.parameters())
         return x2
 
     @staticmethod
@@ -121,6 +123,7 @@ class _BertLayerFn(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx = torch.empty(T, Hd, dtype=bf, device=dev)
             F.gemm(dqkv, shadow_of(L.qkv_weight), dx, T, Hd, 3 * Hd, b_mn=True, epi=F.EPI_BIAS_RESID, aux_in=dh1)
+        notify_grads_written(*L.parameters())   # this layer's slice of the gradient bucket is final: its all-reduce may start
         return dx, None, None, None, None, None
 
 
@@ -184,6 +187,7 @@ class _BertEmbedFn(torch.autograd.Function):
         x0, mean, rstd = F.layernorm_fwd(e, emb.ln_weight, emb.ln_bias, c.layer_norm_eps, p, emb.seed)
         ctx.save_for_backward(ids, tts, e, mean, rstd)
         ctx.emb, ctx.S, ctx.p = emb, S, p
+        note_param_use(ctx, *emb.parameters())
         return x0
 
     @staticmethod
@@ -194,6 +198,7 @@ class _BertEmbedFn(torch.autograd.Function):
                                 grad_buffer(emb.ln_bias), in_dropout_p=ctx.p, in_seed=emb.seed)
         F.embed_scatter(ids, tts, de, grad_buffer(emb.word_embeddings), grad_buffer(emb.position_embeddings),
                         grad_buffer(emb.token_type_embeddings), ctx.S)
+        notify_grads_written(*emb.parameters())
         return None, None, None, None, None, None
 
 
@@ -245,6 +250,7 @@ class _BertHeadFn(torch.autograd.Function):
         F.gemm_small(pd, head.classifier_weight, logits, B, C, Hd, (Hd, 1), (Hd, 1), (C, 1), bias=head.classifier_bias)
         ctx.save_for_backward(x, pooled, keep, pd)
         ctx.head, ctx.dims = head, (B, S)
+        note_param_use(ctx, *head.parameters())
         return logits
 
     @staticmethod
@@ -271,6 +277,7 @@ class _BertHeadFn(torch.autograd.Function):
         F.gemm(dpre, shadow_of(head.pooler_weight), dcls, B, Hd, Hd, b_mn=True)
         dx = torch.zeros_like(x)
         dx.view(B, S, Hd)[:, 0] = dcls
+        notify_grads_written(*head.parameters())
         return dx, None, None, None, None
 
 

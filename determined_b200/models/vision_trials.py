@@ -130,6 +130,8 @@ class MNistTrial(_ClassifierTrial):
         self.model = context.wrap_model(MnistCNN(int(hp.get("n_filters1", 32)), int(hp.get("n_filters2", 64)),
                                                  float(hp.get("dropout1", 0.25)), float(hp.get("dropout2", 0.5))))
         self.optimizer = context.wrap_optimizer(torch.optim.Adadelta(self.model.parameters(), lr=float(hp.get("learning_rate", 1.0))))
+        if hp.get("overlap_grad_allreduce", False):
+            context.experimental.enable_grad_overlap(chunk_mb=int(hp.get("overlap_chunk_mb", 1)))
 
 
 class CIFARTrial(_ClassifierTrial):
@@ -166,6 +168,8 @@ class ResNet50Trial(_ClassifierTrial):
         self.lr_scheduler = context.wrap_lr_scheduler(
             torch.optim.lr_scheduler.StepLR(self.optimizer, step_size=int(hp.get("lr_step_epochs", 30)), gamma=0.1),
             dp.LRScheduler.StepMode.STEP_EVERY_EPOCH)
+        if hp.get("overlap_grad_allreduce", True):
+            context.experimental.enable_grad_overlap()
         if hp.get("use_cuda_graphs", False):
             context.experimental.enable_cuda_graphs()
 

@@ -64,6 +64,7 @@ _SIGNATURES = {
     "det_ipc_export": [c_void_p, ctypes.c_char_p],
     "det_ipc_import": [ctypes.c_char_p, ctypes.POINTER(c_void_p)],
     "det_ipc_close": [c_void_p],
+    "det_set_sm_limit": [c_int],
 }
 
 

@@ -34,7 +34,7 @@ import torch
 import torch.nn as nn
 
 from . import functional as F
-from .modules import accumulate_bgrad, grad_buffer, shadow_of
+from .modules import accumulate_bgrad, grad_buffer, note_param_use, notify_grads_written, shadow_of
 
 _ACT_CODES = {None: F.ACT_NONE, "relu": F.ACT_RELU, "leaky_relu": F.ACT_LEAKY, "tanh": F.ACT_TANH, "sigmoid": F.ACT_SIGMOID}
 
@@ -109,6 +109,7 @@ class _Conv2dFn(torch.autograd.Function):
         ctx.save_for_backward(x, y if relu else None)
         ctx.weight, ctx.bias = weight, bias
         ctx.cfg = (kind, stride, ph, pw, relu)
+        note_param_use(ctx, weight, bias)
         return y
 
     @staticmethod
@@ -164,6 +165,7 @@ class _Conv2dFn(torch.autograd.Function):
                 dcol = torch.empty(M, Kp, dtype=torch.bfloat16, device=x.device)
                 F.gemm(dyp, wk, dcol, M, Kp, Cp, b_mn=True)
                 dx = F.col2im(dcol, N, H, W, Cin, R, S, stride, ph, pw, Kp)
+        notify_grads_written(weight, bias)
         return dx, None, None, None, None, None
 
 
@@ -237,6 +239,7 @@ class _ConvT2dFn(torch.autograd.Function):
         ctx.save_for_backward(x)
         ctx.weight, ctx.bias = weight, bias
         ctx.cfg = (stride, pad, Hy, Wy)
+        note_param_use(ctx, weight, bias)
         return y
 
     @staticmethod
@@ -270,6 +273,7 @@ class _ConvT2dFn(torch.autograd.Function):
             dxp = torch.empty(M, Cp, dtype=torch.bfloat16, device=x.device)
             F.gemm(col, wk, dxp, M, Cin, Kp)
             dx = (dxp if Cp == Cin else dxp[:, :Cin].contiguous()).view(N, Hx, Wx, Cin)
+        notify_grads_written(weight, bias)
         return dx, None, None, None, None
 
 
@@ -305,6 +309,7 @@ class _BatchNormFn(torch.autograd.Function):
         ctx.save_for_backward(x, y if act != F.ACT_NONE else None, mean, rstd)
         ctx.gamma, ctx.beta = gamma, beta
         ctx.cfg = (act, slope, resid is not None)
+        note_param_use(ctx, gamma, beta)
         return y
 
     @staticmethod
@@ -318,6 +323,7 @@ class _BatchNormFn(torch.autograd.Function):
                             want_dresid=has_resid and ctx.needs_input_grad[1])
         if has_resid and ctx.needs_input_grad[1] and act == F.ACT_NONE:
             dres = dy
+        notify_grads_written(gamma, beta)
         return dx, dres, None, None, None, None, None, None
 
 

@@ -35,6 +35,16 @@ def native_available() -> bool:
     return torch.cuda.is_available() and _native.available()
 
 
+def set_sm_limit(n: int) -> None:
+    """Cap the SM count the persistent kernels size their grids from (0 = whole device); host-side, affects launches
+    (and graph captures) made afterwards."""
+    _native.check(_native.load().det_set_sm_limit(int(n)))
+
+
+def device_sm_count(device=None) -> int:
+    return torch.cuda.get_device_properties(device if device is not None else torch.cuda.current_device()).multi_processor_count
+
+
 # ------------------------------------------------------------------------------------------------
 # Per-step dropout seed (device resident so CUDA-graph replays draw fresh masks)
 # ------------------------------------------------------------------------------------------------

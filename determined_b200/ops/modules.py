@@ -55,6 +55,54 @@ def grad_buffer(p: torch.Tensor) -> torch.Tensor:
     return g
 
 
+# ------------------------------------------------------------------------------------------------
+# Gradient-readiness notifications (what Horovod gets from per-parameter autograd hooks)
+# ------------------------------------------------------------------------------------------------
+# The autograd nodes in this package write parameter gradients themselves and return ``None`` for them, so torch's
+# post-accumulate hooks never fire. Instead every node reports (a) in forward, which trainable parameters it used, and
+# (b) at the end of backward, that their gradients for this use are complete. ``parallel.overlap.GradOverlap`` turns
+# that into "this slice of the flat gradient bucket is final → start its all-reduce now".
+_PARAM_USES: dict = {}
+GRAD_OBSERVERS: list = []
+
+
+def note_param_use(ctx, *params: Optional[torch.Tensor]) -> None:
+    """Forward side (called from ``autograd.Function.forward``): count one pending gradient contribution per trainable
+    parameter. No-op without observers, and when this forward will never be differentiated (``torch.no_grad`` or no
+    input requiring grad — grad mode itself is always off inside ``Function.forward``, hence the ctx test)."""
+    if not GRAD_OBSERVERS or not any(ctx.needs_input_grad):
+        return
+    for p in params:
+        if p is not None and p.requires_grad:
+            _PARAM_USES[id(p)] = _PARAM_USES.get(id(p), 0) + 1
+
+
+def pending_uses(p: torch.Tensor) -> int:
+    return _PARAM_USES.get(id(p), 0)
+
+
+def notify_grads_written(*params: Optional[torch.Tensor]) -> None:
+    """Backward side: the contribution counted by :func:`note_param_use` has been written (or skipped because the
+    parameter no longer requires grad)."""
+    if not GRAD_OBSERVERS:
+        return
+    done = []
+    for p in params:
+        if p is None:
+            continue
+        n = _PARAM_USES.get(id(p), 0)
+        if n > 0:
+            _PARAM_USES[id(p)] = n - 1
+            done.append(p)
+    if done:
+        for obs in GRAD_OBSERVERS:
+            obs(done)
+
+
+def reset_param_uses() -> None:
+    _PARAM_USES.clear()
+
+
 def accumulate_wgrad(weight: torch.Tensor, dy: torch.Tensor, x: torch.Tensor) -> None:
     """weight.grad[N_out, K_in] += dy[T, N_out]^T @ x[T, K_in] (both operands MN-major, split-K atomics)."""
     g = grad_buffer(weight)
@@ -84,6 +132,7 @@ class _LinearFn(torch.autograd.Function):
             F.gemm(x, w, out, T, N, K, epi=F.EPI_BIAS if bias is not None else F.EPI_NONE, bias=bias)
         ctx.save_for_backward(x, z)
         ctx.weight, ctx.bias, ctx.gelu = weight, bias, gelu
+        note_param_use(ctx, weight, bias)
         return out
 
     @staticmethod
@@ -109,6 +158,7 @@ class _LinearFn(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx = torch.empty(T, K, dtype=torch.bfloat16, device=x.device)
             F.gemm(dy, w, dx, T, K, N, b_mn=True)
+        notify_grads_written(weight, bias)
         return dx, None, None, None
 
 
@@ -149,6 +199,7 @@ class _LayerNormFn(torch.autograd.Function):
         y, mean, rstd = F.layernorm_fwd(x, gamma, beta, eps)
         ctx.save_for_backward(x, mean, rstd)
         ctx.gamma, ctx.beta = gamma, beta
+        note_param_use(ctx, gamma, beta)
         return y
 
     @staticmethod
@@ -157,6 +208,7 @@ class _LayerNormFn(torch.autograd.Function):
         dg = grad_buffer(ctx.gamma) if ctx.gamma.requires_grad else None
         db = grad_buffer(ctx.beta) if ctx.beta.requires_grad else None
         dx, _ = F.layernorm_bwd(dy.contiguous(), x, ctx.gamma, mean, rstd, dg, db)
+        notify_grads_written(ctx.gamma, ctx.beta)
         return dx, None, None, None
 
 

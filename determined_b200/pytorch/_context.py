@@ -68,6 +68,19 @@ class _Experimental:
         self.cuda_graphs = True
         self.graph_warmup_batches = max(int(warmup_batches), 3)
 
+    def enable_grad_overlap(self, chunk_mb: int = 32, reserved_sms: int = 16) -> None:
+        """Overlap the gradient all-reduce with backward (multi-slot trials on GPUs): slices of the flat gradient
+        bucket are reduced on a side stream as soon as backward has finished writing them. Only for trials that make
+        ONE ``context.backward`` call per optimizer step — see :mod:`determined_b200.parallel.overlap`."""
+        p = self._parent
+        if p.comm.size > 1 and p.device.type == "cuda" and getattr(p.comm, "p2p", False) and p._overlap is None:
+            from ..parallel.overlap import GradOverlap
+
+            p._overlap = GradOverlap(p.comm, chunk_bytes=int(chunk_mb) << 20, reserved_sms=int(reserved_sms))
+            for o in p.optimizers:
+                if isinstance(o, FusedOptimizer):
+                    p._overlap.add_optimizer(o)
+
 
 class PyTorchTrialContext(TrialContext):
     def __init__(self, env: EnvContext, dist: Optional[DistributedContext] = None,
@@ -88,6 +101,7 @@ class PyTorchTrialContext(TrialContext):
         self._loss_scaler: Optional[_LossScaler] = None
         self._scaler_divisor_applied = False
         self.experimental = _Experimental(self)
+        self._overlap: Any = None     # parallel.overlap.GradOverlap when enabled
         self.warned_types: set = set()
 
         opt_cfg = env.experiment_config.get_optimizations_config()
@@ -162,6 +176,8 @@ class PyTorchTrialContext(TrialContext):
                 return self.comm.alloc(n, dtype, kind, dev)
 
             wrapped: torch.optim.Optimizer = FusedOptimizer(optimizer, alloc=alloc)
+            if self._overlap is not None:
+                self._overlap.add_optimizer(wrapped)
         else:
             wrapped = optimizer
         self.optimizers.append(wrapped)
@@ -251,6 +267,10 @@ class PyTorchTrialContext(TrialContext):
         bucket; nothing is communicated until ``step_optimizer``. May be called several times per batch."""
         if self._loss_scaler is not None:
             loss = loss * self._loss_scaler.scale_tensor()
+        if self._overlap is not None and self._should_communicate_and_update():
+            scaler = self._loss_scaler
+            self._overlap.arm(1.0 / self._grad_divisor(), scaler.state[2:3] if scaler is not None else None,
+                              (lambda o: o.found_inf_dev) if scaler is not None else None)
         loss.backward(gradient=gradient, retain_graph=retain_graph, create_graph=create_graph)
 
     def _grad_divisor(self) -> float:
@@ -293,9 +313,13 @@ class PyTorchTrialContext(TrialContext):
             pass
         found_inf = opt.found_inf_dev if scaler is not None else None
         applied_all = True
-        for g in opt.grad_buckets():
-            applied = self.comm.allreduce_grad_bucket(g, 1.0 / divisor, scale_dev=inv_scale_dev, found_inf_dev=found_inf)
-            applied_all = applied_all and applied
+        if self._overlap is not None and self._overlap.armed_for(opt):
+            # slices were reduced on the side stream while backward ran; flush the rest and join
+            applied_all = self._overlap.finish(opt)
+        else:
+            for g in opt.grad_buckets():
+                applied = self.comm.allreduce_grad_bucket(g, 1.0 / divisor, scale_dev=inv_scale_dev, found_inf_dev=found_inf)
+                applied_all = applied_all and applied
         if applied_all and self.comm.size > 1:
             opt.grad_scale_dev.fill_(1.0)
         else:

@@ -16,6 +16,9 @@ extern "C" {
 #endif
 
 const char* det_last_error(void);
+/* Cap the number of SMs the persistent kernels size their grids from (0 = whole device). Used while a collective runs
+ * on a side stream so its CTAs find free SMs. Host-side state, takes effect for subsequent launches. */
+int det_set_sm_limit(int n);
 int det_kernels_abi_version(void);
 
 /* ---- tensor-core GEMM (tcgen05 + TMEM + TMA) -------------------------------------------------------------

@@ -22,10 +22,11 @@ def main() -> None:
     elif case == "xor_agg":
         trial, hp, steps, unit = M.XorTrial, {"hidden_size": 4, "learning_rate": 0.05, "global_batch_size": 8, "shuffle": False}, 4, 2
         cfg = {"optimizations": {"aggregation_frequency": 2, "average_training_metrics": True}}
-    elif case == "mnist_gpu":
+    elif case in ("mnist_gpu", "mnist_gpu_overlap"):
         from determined_b200.models import vision_trials as VT
 
-        trial, hp, steps, unit = VT.MNistTrial, {"global_batch_size": 64, "learning_rate": 1.0, "dropout1": 0.0, "dropout2": 0.0}, 4, 4
+        trial, hp, steps, unit = VT.MNistTrial, {"global_batch_size": 64, "learning_rate": 1.0, "dropout1": 0.0, "dropout2": 0.0,
+                                                 "overlap_grad_allreduce": case.endswith("overlap")}, 4, 4
         cfg = {"data": {"train_size": 1024, "validation_size": 128}, "optimizations": {"average_training_metrics": True}}
     else:
         raise SystemExit(f"unknown case {case}")
@@ -35,7 +36,8 @@ def main() -> None:
     params = torch.cat([p.detach().float().reshape(-1).cpu() for m in controller.context.models for p in m.parameters()])
     gathered = controller.context.comm.allgather_object(params.tolist())
     if rank == 0:
-        report = {"training": tv.training_metrics, "validation": tv.validation_metrics, "params_by_rank": gathered,
+        ov = getattr(controller.context, "_overlap", None)
+        report = {"overlap_launches": len(ov.launch_log) if ov is not None else 0, "training": tv.training_metrics, "validation": tv.validation_metrics, "params_by_rank": gathered,
                   "world": controller.context.comm.size,
                   "comm": controller.context.comm.describe() if hasattr(controller.context.comm, "describe") else {}}
         with open(out_path, "w") as f:

@@ -33,3 +33,17 @@ def test_dp2_trial_on_gpus(tmp_path):
     losses = [m["loss"] for m in rep["training"]]
     assert losses[-1] < losses[0]
     assert rep["comm"].get("p2p") is True, rep["comm"]
+
+
+def test_overlapped_allreduce_matches_step_time_allreduce(tmp_path):
+    """Same trial, same seed: reducing bucket slices on a side stream during backward must give bit-identical
+    parameters to reducing the whole bucket at step time (the collective and its scale are the same, only WHEN slices
+    are reduced differs), and must actually have launched several slices per step."""
+    _need_two()
+    plain = run_ranks(2, "mnist_gpu", tmp_path, timeout=600)
+    over = run_ranks(2, "mnist_gpu_overlap", tmp_path, timeout=600)
+    assert over["overlap_launches"] >= 2 * 16, over["overlap_launches"]
+    a, b = over["params_by_rank"]
+    assert a == b, "replicas diverged with overlap"
+    import numpy as np
+    assert np.allclose(np.array(a), np.array(plain["params_by_rank"][0]), rtol=1e-4, atol=1e-5)
