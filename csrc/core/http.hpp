@@ -69,7 +69,7 @@ class HttpServer {
 
   // Binds and listens; returns the bound port (useful with port 0) or -1.
   int listen(const std::string& host, int port) {
-    fd_ = ::socket(AF_INET, SOCK_STREAM, 0);
+    fd_ = ::socket(AF_INET, SOCK_STREAM | SOCK_CLOEXEC, 0);   // never inherited by the harness processes the master forks
     if (fd_ < 0) return -1;
     int one = 1;
     setsockopt(fd_, SOL_SOCKET, SO_REUSEADDR, &one, sizeof one);
@@ -86,7 +86,7 @@ class HttpServer {
   }
   void serve_forever() {
     while (!stop_) {
-      int c = ::accept(fd_, nullptr, nullptr);
+      int c = ::accept4(fd_, nullptr, nullptr, SOCK_CLOEXEC);
       if (c < 0) { if (stop_) break; continue; }
       int one = 1;
       setsockopt(c, IPPROTO_TCP, TCP_NODELAY, &one, sizeof one);
@@ -218,7 +218,7 @@ class HttpServer {
 // Blocking one-shot client: returns status (or -1) and fills body.
 inline int http_request(const std::string& host, int port, const std::string& method, const std::string& path,
                         const std::string& body, std::string* out, int timeout_s = 60, const std::string& auth = "") {
-  int fd = ::socket(AF_INET, SOCK_STREAM, 0);
+  int fd = ::socket(AF_INET, SOCK_STREAM | SOCK_CLOEXEC, 0);
   if (fd < 0) return -1;
   timeval tv{timeout_s, 0};
   setsockopt(fd, SOL_SOCKET, SO_RCVTIMEO, &tv, sizeof tv);

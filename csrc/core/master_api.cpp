@@ -340,7 +340,7 @@ tick();setInterval(tick,2000);
     if (t.is_null()) return not_found("trial");
     auto actor = m->system.get("experiments/" + std::to_string(t["experiment_id"].as_int()) + "/" + t["request_id"].as_string());
     if (!actor) return ok(obj({{"type", "TERMINATE"}}));
-    Json resp = m->system.ask(actor, "next_workload", Json(), 30000);
+    Json resp = m->system.ask(actor, "next_workload", obj({{"container_id", r.q("container_id", "")}}), 30000);
     return ok(resp.is_null() ? obj({{"type", "WAIT"}}) : resp);
   });
   http.route("POST", "/api/v1/trials/:id/workload_completed", [m](const HttpRequest& r) {

@@ -61,6 +61,12 @@ class TrialActor : public Actor {
       preempt_requested_ = true;
       progress(ctx);
     } else if (t == "next_workload") {
+      // a harness left over from an earlier run of this trial (e.g. it outlived a master restart) is told to exit
+      const std::string cid = msg.body["container_id"].str_or("");
+      if (!cid.empty() && running_ && std::find(containers_.begin(), containers_.end(), cid) == containers_.end()) {
+        msg.respond(obj({{"type", "TERMINATE"}}));
+        return;
+      }
       if (poll_.reply) poll_.respond(obj({{"type", "WAIT"}}));
       poll_ = msg;
       ++poll_seq_;
