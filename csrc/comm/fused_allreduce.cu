@@ -90,9 +90,17 @@ struct AllreduceArgs {
   int* found_inf;         // optional: set to 1 when a non-finite value is seen
 };
 
+// Memory-level parallelism is what sets the bandwidth of one CTA here (a remote load / switch reduction takes a few
+// microseconds): every thread keeps AR_UNROLL independent 16-byte transactions in flight, so a handful of CTAs already
+// saturates the links — which is what lets the collective run next to backward on a few reserved SMs.
+constexpr int AR_THREADS = 1024;
+constexpr int AR_UNROLL_MC = 8;
+constexpr int AR_UNROLL_P2P = 1;   // the peer loads of one element are already `world` independent transactions
+
 template <bool USE_MC>
-__global__ void __launch_bounds__(512)
+__global__ void __launch_bounds__(AR_THREADS)
 fused_allreduce_kernel(const AllreduceArgs a) {
+  constexpr int U = USE_MC ? AR_UNROLL_MC : AR_UNROLL_P2P;
   const int rank = a.rank, world = a.world;
   uint32_t ep = a.epoch[blockIdx.x];
   rank_barrier(a.t, rank, world, ep + 1);  // every rank's gradients for this bucket are complete
@@ -104,38 +112,58 @@ fused_allreduce_kernel(const AllreduceArgs a) {
   const long long lo = std::min<long long>(per * rank, n4), hi = std::min<long long>(lo + per, n4);
   float acc = 0.0f;
   bool bad = false;
-  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  for (long long i = lo + static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < hi; i += stride) {
-    float4 s;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * U;
+  for (long long i0 = lo + static_cast<long long>(blockIdx.x) * blockDim.x * U + threadIdx.x; i0 < hi; i0 += stride) {
+    float4 s[U];
     if (USE_MC) {
-      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
-                   : "=f"(s.x), "=f"(s.y), "=f"(s.z), "=f"(s.w) : "l"(a.mc_ptr + i * 4) : "memory");
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long i = i0 + static_cast<long long>(u) * blockDim.x;
+        if (i < hi)
+          asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                       : "=f"(s[u].x), "=f"(s[u].y), "=f"(s[u].z), "=f"(s[u].w) : "l"(a.mc_ptr + i * 4) : "memory");
+      }
     } else {
-      float4 v[COMM_MAX_RANKS];
+      float4 v[U][COMM_MAX_RANKS];
 #pragma unroll
-      for (int r = 0; r < COMM_MAX_RANKS; ++r)
-        if (r < world) v[r] = ld_f4(reinterpret_cast<const float*>(a.t.buf[(rank + r) % world]) + i * 4);
-      s = v[0];
+      for (int u = 0; u < U; ++u) {
+        const long long i = i0 + static_cast<long long>(u) * blockDim.x;
+        if (i < hi) {
 #pragma unroll
-      for (int r = 1; r < COMM_MAX_RANKS; ++r)
-        if (r < world) { s.x += v[r].x; s.y += v[r].y; s.z += v[r].z; s.w += v[r].w; }
+          for (int r = 0; r < COMM_MAX_RANKS; ++r)
+            if (r < world) v[u][r] = ld_f4(reinterpret_cast<const float*>(a.t.buf[(rank + r) % world]) + i * 4);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        s[u] = v[u][0];
+#pragma unroll
+        for (int r = 1; r < COMM_MAX_RANKS; ++r)
+          if (r < world) { s[u].x += v[u][r].x; s[u].y += v[u][r].y; s[u].z += v[u][r].z; s[u].w += v[u][r].w; }
+      }
     }
-    s.x *= scale; s.y *= scale; s.z *= scale; s.w *= scale;
-    acc += s.x * s.x + s.y * s.y + s.z * s.z + s.w * s.w;
-    bad |= !(isfinite(s.x) && isfinite(s.y) && isfinite(s.z) && isfinite(s.w));
-    if (USE_MC) {
-      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(a.mc_ptr + i * 4),
-                   "f"(s.x), "f"(s.y), "f"(s.z), "f"(s.w) : "memory");
-    } else {
 #pragma unroll
-      for (int r = 0; r < COMM_MAX_RANKS; ++r)
-        if (r < world) st_f4(reinterpret_cast<float*>(a.t.buf[(rank + r) % world]) + i * 4, s);
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + static_cast<long long>(u) * blockDim.x;
+      if (i >= hi) break;
+      float4 t = s[u];
+      t.x *= scale; t.y *= scale; t.z *= scale; t.w *= scale;
+      acc += t.x * t.x + t.y * t.y + t.z * t.z + t.w * t.w;
+      bad |= !(isfinite(t.x) && isfinite(t.y) && isfinite(t.z) && isfinite(t.w));
+      if (USE_MC) {
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(a.mc_ptr + i * 4),
+                     "f"(t.x), "f"(t.y), "f"(t.z), "f"(t.w) : "memory");
+      } else {
+#pragma unroll
+        for (int r = 0; r < COMM_MAX_RANKS; ++r)
+          if (r < world) st_f4(reinterpret_cast<float*>(a.t.buf[(rank + r) % world]) + i * 4, t);
+      }
     }
   }
   if (a.sumsq != nullptr || a.found_inf != nullptr) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    __shared__ float red[16];
+    __shared__ float red[AR_THREADS / 32];
     __shared__ int sbad;
     if (threadIdx.x == 0) sbad = 0;
     __syncthreads();
@@ -241,12 +269,13 @@ extern "C" int det_fused_allreduce(void* const* peer_bufs, void* const* peer_fla
   a.n = n_f32; a.rank = rank; a.world = world; a.scale = scale; a.scale_dev = scale_dev;
   a.sumsq = sumsq_dev; a.found_inf = found_inf_dev;
   const long long per4 = ((n_f32 >> 2) + world - 1) / world;
-  int blocks = static_cast<int>(std::min<long long>((per4 + 511) / 512, std::min(sm_count(), COMM_MAX_BLOCKS)));
+  const long long per_block = static_cast<long long>(AR_THREADS) * (mc_ptr != nullptr && world > 1 ? AR_UNROLL_MC : AR_UNROLL_P2P);
+  int blocks = static_cast<int>(std::min<long long>((per4 + per_block - 1) / per_block, std::min(sm_count(), COMM_MAX_BLOCKS)));
   if (max_blocks > 0) blocks = std::min(blocks, max_blocks);
   blocks = std::max(blocks, 1);
   // Every rank must launch the same grid: blocks depends only on (n, world, SM count, max_blocks).
-  if (mc_ptr != nullptr && world > 1) fused_allreduce_kernel<true><<<blocks, 512, 0, stream>>>(a);
-  else fused_allreduce_kernel<false><<<blocks, 512, 0, stream>>>(a);
+  if (mc_ptr != nullptr && world > 1) fused_allreduce_kernel<true><<<blocks, AR_THREADS, 0, stream>>>(a);
+  else fused_allreduce_kernel<false><<<blocks, AR_THREADS, 0, stream>>>(a);
   DET_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

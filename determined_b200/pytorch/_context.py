@@ -68,7 +68,7 @@ class _Experimental:
         self.cuda_graphs = True
         self.graph_warmup_batches = max(int(warmup_batches), 3)
 
-    def enable_grad_overlap(self, chunk_mb: int = 32, reserved_sms: int = 16) -> None:
+    def enable_grad_overlap(self, chunk_mb: int = 32, reserved_sms: int = 8) -> None:
         """Overlap the gradient all-reduce with backward (multi-slot trials on GPUs): slices of the flat gradient
         bucket are reduced on a side stream as soon as backward has finished writing them. Only for trials that make
         ONE ``context.backward`` call per optimizer step — see :mod:`determined_b200.parallel.overlap`."""
@@ -76,7 +76,11 @@ class _Experimental:
         if p.comm.size > 1 and p.device.type == "cuda" and getattr(p.comm, "p2p", False) and p._overlap is None:
             from ..parallel.overlap import GradOverlap
 
-            p._overlap = GradOverlap(p.comm, chunk_bytes=int(chunk_mb) << 20, reserved_sms=int(reserved_sms))
+            import os
+
+            reserved = int(os.environ.get("DET_OVERLAP_SMS", reserved_sms))
+            p._overlap = GradOverlap(p.comm, chunk_bytes=int(os.environ.get("DET_OVERLAP_CHUNK_MB", chunk_mb)) << 20,
+                                     reserved_sms=reserved, comm_blocks=int(os.environ.get("DET_OVERLAP_BLOCKS", reserved)))
             for o in p.optimizers:
                 if isinstance(o, FusedOptimizer):
                     p._overlap.add_optimizer(o)
