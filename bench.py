@@ -107,7 +107,7 @@ def hparams(n_gpus: int) -> Dict[str, Any]:
     return {"global_batch_size": PER_SLOT_BATCH * n_gpus, "learning_rate": 2e-5, "adam_epsilon": 1e-8,
             "weight_decay": 0.0, "num_warmup_steps": 0, "num_training_steps": 100000, "max_seq_length": SEQ_LEN,
             "max_grad_norm": 1.0, "dataset_size": 4096, "validation_size": 96, "use_cuda_graphs": True,
-            "overlap_grad_allreduce": os.environ.get("DET_OVERLAP", "1") == "1"}
+            "overlap_grad_allreduce": os.environ.get("DET_OVERLAP", "0") == "1"}
 
 
 def exp_config(n_gpus: int) -> Dict[str, Any]:

@@ -74,8 +74,8 @@ class BertGlueTrial(dp.PyTorchTrial):
             dp.LRScheduler.StepMode.STEP_EVERY_BATCH)
         self.max_grad_norm = float(hp.get("max_grad_norm", 1.0))
         self.clip = dp.ClipGradsL2Norm(self.max_grad_norm) if self.max_grad_norm > 0 else None
-        if hp.get("overlap_grad_allreduce", True):
-            context.experimental.enable_grad_overlap()   # no-op on one slot; one backward per step, so it is safe here
+        if hp.get("overlap_grad_allreduce", False):
+            context.experimental.enable_grad_overlap()   # opt-in: measured slower than the step-time all-reduce, see DESIGN.md
         if hp.get("use_cuda_graphs", False):
             context.experimental.enable_cuda_graphs()
 

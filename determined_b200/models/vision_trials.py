@@ -168,7 +168,7 @@ class ResNet50Trial(_ClassifierTrial):
         self.lr_scheduler = context.wrap_lr_scheduler(
             torch.optim.lr_scheduler.StepLR(self.optimizer, step_size=int(hp.get("lr_step_epochs", 30)), gamma=0.1),
             dp.LRScheduler.StepMode.STEP_EVERY_EPOCH)
-        if hp.get("overlap_grad_allreduce", True):
+        if hp.get("overlap_grad_allreduce", False):
             context.experimental.enable_grad_overlap()
         if hp.get("use_cuda_graphs", False):
             context.experimental.enable_cuda_graphs()

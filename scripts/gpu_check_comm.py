@@ -110,6 +110,13 @@ def main():
     t_nccl = timeit(nccl_path)
     t_nccl_only = timeit(lambda: dist.all_reduce(nccl_buf))
     bytes_moved = 2 * (world - 1) / world * n * 4
+    # bandwidth against the number of CTAs: what a collective squeezed onto a few reserved SMs can deliver
+    by_blocks = {}
+    for mb in (2, 4, 8, 16, 32, 64, 0):
+        t = timeit(lambda: comm.allreduce_grad_bucket(g, 1.0 / world, max_blocks=mb), iters=5)
+        by_blocks[str(mb or "all")] = {"ms": round(t, 3), "busbw_gbs": round(bytes_moved / t / 1e6, 1)}
+    if rank == 0:
+        print("allreduce vs CTAs:", json.dumps(by_blocks), flush=True)
     results = {"world": world, "bucket_mb": n * 4 / 1e6, "fused_ms": round(t_fused, 3), "nccl_allreduce_only_ms": round(t_nccl_only, 3),
                "nccl_plus_scale_finite_norm_ms": round(t_nccl, 3), "fused_busbw_gbs": round(bytes_moved / t_fused / 1e6, 1),
                "nccl_busbw_gbs": round(bytes_moved / t_nccl_only / 1e6, 1), "comm": comm.describe()}
