@@ -71,12 +71,14 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  ptx::pdl_launch_dependents();   // the next kernel may start its prologue as soon as SMs free up
 
   const int total_work = p.tiles_m * p.tiles_n * p.splitk;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
+      ptx::pdl_wait();            // operands may be the previous kernel's output
       uint32_t it = 0;
       for (int w = blockIdx.x; w < total_work; w += gridDim.x) {
         const int ks = w % p.splitk;
@@ -153,6 +155,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     const int half = ew >> 2;          // which quarter of the BN columns (0..3)
     constexpr int COLS_PER_WARP = BN / 4;
     constexpr int CW = COLS_PER_WARP < 32 ? COLS_PER_WARP : 32;  // columns per tcgen05.ld chunk (16 when BN == 64)
+    ptx::pdl_wait();              // bias / aux_in / C belong to earlier kernels
     uint32_t lt = 0;
     for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++lt) {
       const int tile = w / p.splitk;
@@ -199,7 +202,18 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
     DET_CHECK_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     attr_set[dev] = true;
   }
-  kfn<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, p);
+  static const bool pdl = [] { const char* e = getenv("DET_PDL"); return e && e[0] == '1'; }();
+  if (pdl) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(GEMM_THREADS); cfg.dynamicSmemBytes = Cfg::SMEM_BYTES; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    DET_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kfn, ta, tb, p));
+  } else {
+    kfn<<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, p);
+  }
   DET_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -171,6 +171,13 @@ __device__ __forceinline__ void umma_commit(uint32_t bar) {
                : "memory");
 }
 
+// Programmatic dependent launch: a kernel launched with the programmatic-stream-serialization attribute may start
+// while its predecessor in the stream is still draining; everything before pdl_wait() (barrier init, TMEM allocation,
+// descriptor prefetch) overlaps that tail, everything that touches global memory must come after it. Both are no-ops
+// for a kernel launched the ordinary way.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---------------------------------------------------------------------------------------------
 // CTA-pair (cta_group::2) variants: two CTAs of a 2-cluster (same TPC) run ONE MMA of M = 256. Each CTA stages its own
 // 128 rows of A and its half of B; the leader (cluster rank 0) issues the MMA, accumulators land in both CTAs' TMEM.
