@@ -47,7 +47,7 @@ std::string md5_hex(const std::string& s) {
 MasterConfig MasterConfig::from_json(const Json& j) {
   static const std::set<std::string> known = {"host", "port", "data_dir", "scheduler", "fitting_policy", "preemption", "checkpoint_storage",
                                               "python", "repo_root", "slot_type", "visible_gpus", "artificial_slots", "auth_required",
-                                              "cluster_name", "scheduler_tick_ms", "terminate_timeout_ms", "resource_pools", "db", "telemetry",
+                                              "cluster_name", "scheduler_tick_ms", "terminate_timeout_ms", "resource_pools", "db", "telemetry", "provisioner",
                                               "security", "task_container_defaults"};
   MasterConfig c;
   for (auto& kv : j.obj())
@@ -72,6 +72,7 @@ MasterConfig MasterConfig::from_json(const Json& j) {
   c.artificial_slots = static_cast<int>(j["artificial_slots"].as_int(0));
   c.auth_required = j["auth_required"].as_bool(false) || j["security"]["auth_required"].as_bool(false);
   c.cluster_name = j["cluster_name"].str_or(c.cluster_name);
+  c.provisioner = j["provisioner"];
   c.scheduler_tick_ms = static_cast<int>(j["scheduler_tick_ms"].as_int(c.scheduler_tick_ms));
   c.terminate_timeout_ms = static_cast<int>(j["terminate_timeout_ms"].as_int(c.terminate_timeout_ms));
   if (c.scheduler != "fair_share" && c.scheduler != "priority" && c.scheduler != "round_robin") throw ConfigError("scheduler must be fair_share, priority or round_robin");
@@ -356,6 +357,7 @@ int Master::start() {
                                    {"addresses", Json(Json::array_t{Json("127.0.0.1")})}, {"driver_version", nvidia_driver_version()}}));
   register_routes();
   const int port = http.listen(cfg.host, cfg.port);
+  if (port >= 0 && cfg.provisioner.is_object()) provisioner = system.actor_of("provisioner", make_provisioner(this, cfg.provisioner));
   if (port < 0) throw std::runtime_error("cannot bind " + cfg.host + ":" + std::to_string(cfg.port));
   log("info", "master listening on " + cfg.host + ":" + std::to_string(port) + " with " + std::to_string(devices.size()) + " local slots (" + cfg.scheduler + ")");
   restore_experiments();

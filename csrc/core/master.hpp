@@ -42,6 +42,7 @@ struct MasterConfig {
   int artificial_slots = 0;
   bool auth_required = false;
   std::string cluster_name = "b200-box";
+  Json provisioner;                      // {max_instances, slots_per_instance, max_idle_agent_period, ...} or null
   int scheduler_tick_ms = 500;
   int terminate_timeout_ms = 60000;
 
@@ -67,7 +68,7 @@ class Master {
   HttpServer http;
   std::unique_ptr<ContainerManager> containers;
   std::vector<Device> devices;
-  ActorRef rm, logger, experiments_root, commands_root;
+  ActorRef rm, logger, experiments_root, commands_root, provisioner;
   RWCoordinator rw;
   std::mutex agent_cmd_mu_;
   std::condition_variable agent_cmd_cv_;
@@ -111,5 +112,6 @@ std::unique_ptr<Actor> make_trial_logger(Master* m);
 std::unique_ptr<Actor> make_experiment(Master* m, long long id, bool restoring);
 std::unique_ptr<Actor> make_command(Master* m, long long id, const Json& spec);
 std::unique_ptr<Actor> make_root();
+std::unique_ptr<Actor> make_provisioner(Master* m, const Json& cfg);
 
 }  // namespace det

@@ -85,6 +85,12 @@ void Master::register_routes() {
     m->rw.stats(r.params.at("resource"), readers, writer, waiting);
     return ok(obj({{"readers", static_cast<long long>(readers)}, {"writer", static_cast<long long>(writer)}, {"waiting", static_cast<long long>(waiting)}}));
   });
+  http.route("GET", "/api/v1/provisioner", [m](const HttpRequest&) {
+    if (!m->provisioner) return ok(obj({{"enabled", false}}));
+    Json s = m->system.ask(m->provisioner, "summary");
+    s["enabled"] = true;
+    return ok(s);
+  });
   // ---- provisioner decision preview (reference: provisioner scale decider; providers are out of scope offline) ----
   http.route("POST", "/api/v1/provisioner/decide", [](const HttpRequest& r) {
     Json b = r.json();

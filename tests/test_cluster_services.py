@@ -186,3 +186,47 @@ def test_check_and_gpu_helpers():
         check.is_instance(1, str)
     assert isinstance(gpu.get_gpus(), list)          # empty on a CPU box
     assert gpu.get_gpu_uuids_and_validate(False, []) == []
+
+
+def test_provisioner_scales_up_on_demand_and_down_when_idle(tmp_path):
+    """A master with no slots of its own and a provisioner: submitting an experiment makes it start a det-agent
+    instance, the trial runs there, and the idle instance is terminated afterwards."""
+    import json as _json
+
+    port_file = tmp_path / "port"
+    env = dict(os.environ, DET_CONFIG_DIR=str(tmp_path / "cfg"))
+    prov = {"max_instances": 2, "slots_per_instance": 1, "max_idle_agent_period": 2, "max_agent_starting_period": 30, "tick_ms": 300}
+    proc = subprocess.Popen([str(LIB / "det-master"), "--port", "0", "--data-dir", str(tmp_path / "data"), "--slot-type", "none", "--repo-root", str(ROOT),
+                             "--python", sys.executable, "--print-port-file", str(port_file), "--provisioner", _json.dumps(prov)],
+                            stdout=open(tmp_path / "master.log", "w"), stderr=subprocess.STDOUT, env=env, start_new_session=True)
+    try:
+        for _ in range(200):
+            if port_file.exists() and port_file.read_text().strip():
+                break
+            time.sleep(0.05)
+        port = int(port_file.read_text())
+        os.environ["DET_CONFIG_DIR"] = str(tmp_path / "cfg")
+        d = Determined(f"127.0.0.1:{port}")
+        c = MasterClient("127.0.0.1", port)
+        assert c.request("GET", "/api/v1/provisioner")["instances"] == []
+        cfg = {"entrypoint": "model_def:XorTrial", "hyperparameters": {"global_batch_size": 8, "hidden_size": 4, "learning_rate": 0.5},
+               "searcher": {"name": "single", "metric": "validation_loss", "max_length": {"batches": 20}}, "scheduling_unit": 10,
+               "checkpoint_storage": {"type": "shared_fs", "host_path": str(tmp_path / "ckpts")}}
+        exp = d.create_experiment(cfg, MODEL_DIR)
+        assert exp.wait(timeout=180) == "COMPLETED"
+        s = c.request("GET", "/api/v1/provisioner")
+        assert s["launched_total"] >= 1
+        for _ in range(100):            # idle for > 2 s → scaled down
+            s = c.request("GET", "/api/v1/provisioner")
+            if s["terminated_total"] >= 1 and not s["instances"]:
+                break
+            time.sleep(0.2)
+        assert s["terminated_total"] >= 1 and s["instances"] == []
+        assert all(a["id"] == "agent-local" for a in c.request("GET", "/api/v1/agents"))
+    finally:
+        import signal as _signal
+        os.killpg(proc.pid, _signal.SIGTERM)
+        try:
+            proc.wait(timeout=5)
+        except Exception:
+            os.killpg(proc.pid, _signal.SIGKILL)
