@@ -297,11 +297,14 @@ __global__ void bn_param_grad_kernel(const float* __restrict__ sums, float* dgam
   if (dgamma != nullptr) dgamma[c] += sums[C + c];
 }
 
-static dim3 strip_grid(long long M, int C) {
+// `reduce` kernels end with one global atomic per channel per block onto the SAME 2*C addresses, so their grid is kept
+// at two blocks per SM (ncu: with eight per SM a 25 MB statistics pass spent most of its 25 us in those atomics);
+// the elementwise kernels take the full eight.
+static dim3 strip_grid(long long M, int C, bool reduce = false) {
   const int vpr = (C < BN_CHUNK ? C : BN_CHUNK) / 8;
   const int rpi = BN_THREADS / vpr;
   long long bx = (M + static_cast<long long>(rpi) * BN_UNROLL - 1) / (static_cast<long long>(rpi) * BN_UNROLL);
-  const long long cap = static_cast<long long>(sm_count()) * 8;
+  const long long cap = static_cast<long long>(sm_count()) * (reduce ? 2 : 8);
   if (bx > cap) bx = cap;
   if (bx < 1) bx = 1;
   return dim3(static_cast<unsigned>(bx), static_cast<unsigned>((C + BN_CHUNK - 1) / BN_CHUNK), 1);
@@ -318,7 +321,7 @@ extern "C" int det_bn_stats(const void* x, float* sums_scratch, float* mean, flo
   DET_REQUIRE(M > 0 && C > 0 && C % 8 == 0, "BatchNorm needs C % 8 == 0");
   DET_REQUIRE(C <= det::BN_CHUNK || C % det::BN_CHUNK == 0, "BatchNorm: C above 2048 must be a multiple of 2048");
   DET_CHECK_CUDA(cudaMemsetAsync(sums_scratch, 0, sizeof(float) * 2 * C, stream));
-  det::bn_stats_kernel<<<det::strip_grid(M, C), det::BN_THREADS, 0, stream>>>((const bf16*)x, sums_scratch, M, C);
+  det::bn_stats_kernel<<<det::strip_grid(M, C, true), det::BN_THREADS, 0, stream>>>((const bf16*)x, sums_scratch, M, C);
   det::bn_finalize_kernel<<<(C + 127) / 128, 128, 0, stream>>>(sums_scratch, mean, rstd, running_mean, running_var, M, C, eps, momentum);
   DET_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -348,11 +351,12 @@ extern "C" int det_bn_bwd(const void* dy, const void* x, const void* a, const fl
   DET_REQUIRE(act == 0 || a != nullptr, "BatchNorm backward through an activation needs the saved output");
   DET_CHECK_CUDA(cudaMemsetAsync(sums_scratch, 0, sizeof(float) * 2 * C, stream));
   const dim3 grid = det::strip_grid(M, C);
+  const dim3 rgrid = det::strip_grid(M, C, true);
   if (act != 0) {
-    det::bn_bwd_reduce_kernel<true><<<grid, det::BN_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)x, (const bf16*)a, mean, rstd, sums_scratch, M, C, act, slope);
+    det::bn_bwd_reduce_kernel<true><<<rgrid, det::BN_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)x, (const bf16*)a, mean, rstd, sums_scratch, M, C, act, slope);
     det::bn_bwd_apply_kernel<true><<<grid, det::BN_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)x, (const bf16*)a, mean, rstd, gamma, sums_scratch, (bf16*)dx, (bf16*)dresid, M, C, act, slope);
   } else {
-    det::bn_bwd_reduce_kernel<false><<<grid, det::BN_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)x, nullptr, mean, rstd, sums_scratch, M, C, act, slope);
+    det::bn_bwd_reduce_kernel<false><<<rgrid, det::BN_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)x, nullptr, mean, rstd, sums_scratch, M, C, act, slope);
     det::bn_bwd_apply_kernel<false><<<grid, det::BN_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)x, nullptr, mean, rstd, gamma, sums_scratch, (bf16*)dx, (bf16*)dresid, M, C, act, slope);
   }
   if (dgamma != nullptr || dbeta != nullptr)

@@ -55,20 +55,25 @@ im2col_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ c
         outv = __ldg(reinterpret_cast<const uint4*>(x + ((static_cast<long long>(n) * g.H + h) * g.W + w) * g.C + c));
     }
   } else {
-    float f[8];
+    // few-channel layers (RGB stem): decode (tap row, tap column, channel) once, then step — no division per element
+    uint32_t bits[8];
+    int k = k8 * 8;
+    const int tap0 = k / g.C;
+    int c = k - tap0 * g.C;
+    int fr = tap0 / g.S, fs = tap0 - fr * g.S;
+    const long long img = static_cast<long long>(n) * g.H;
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int k = k8 * 8 + j;
-      f[j] = 0.0f;
+    for (int j = 0; j < 8; ++j, ++k) {
+      bits[j] = 0;
       if (k < K) {
-        const int tap = k / g.C, c = k - tap * g.C;
-        const int fr = tap / g.S, fs = tap - fr * g.S;
         const int h = ho * g.stride + fr - g.pad_h, w = wo * g.stride + fs - g.pad_w;
         if (h >= 0 && h < g.H && w >= 0 && w < g.W)
-          f[j] = __bfloat162float(x[((static_cast<long long>(n) * g.H + h) * g.W + w) * g.C + c]);
+          bits[j] = __ldg(reinterpret_cast<const unsigned short*>(x) + ((img + h) * g.W + w) * g.C + c);
       }
+      if (++c == g.C) { c = 0; if (++fs == g.S) { fs = 0; ++fr; } }
     }
-    outv = pack8(f);
+    outv.x = bits[0] | (bits[1] << 16); outv.y = bits[2] | (bits[3] << 16);
+    outv.z = bits[4] | (bits[5] << 16); outv.w = bits[6] | (bits[7] << 16);
   }
   *reinterpret_cast<uint4*>(col + row * g.Kp + k8 * 8) = outv;
 }

@@ -106,6 +106,9 @@ class _Conv2dFn(torch.autograd.Function):
             y = (yp if Cp == Cout else yp[:, :Cout].contiguous()).view(N, Ho, Wo, Cout)
             if relu:
                 y = F.act_fwd(y, F.ACT_RELU)
+            # first layer of a network (no input gradient wanted): its few-channel gather is the expensive kind, so the
+            # column matrix is kept for the weight gradient instead of being rebuilt in backward
+            ctx.col = col if not ctx.needs_input_grad[0] else None
         ctx.save_for_backward(x, y if relu else None)
         ctx.weight, ctx.bias = weight, bias
         ctx.cfg = (kind, stride, ph, pw, relu)
@@ -150,7 +153,9 @@ class _Conv2dFn(torch.autograd.Function):
             Kp, Cp = _round8(K), _round8(Cout)
             dyp = _pad_cols(dy.view(M, Cout), Cp)
             if weight.requires_grad:
-                col = F.im2col(x, N, H, W, Cin, R, S, stride, ph, pw, Kp)  # recomputed: cheaper than keeping it alive
+                col = getattr(ctx, "col", None)
+                if col is None:   # recomputed: cheaper than keeping it alive through the whole forward/backward
+                    col = F.im2col(x, N, H, W, Cin, R, S, stride, ph, pw, Kp)
                 g = grad_buffer(weight).view(Cout, K)
                 if Kp == K and Cp == Cout:
                     F.gemm(dyp, col, g, Cout, K, M, a_mn=True, b_mn=True, out_mode=F.OUT_F32_ATOMIC_ADD)
