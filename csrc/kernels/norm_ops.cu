@@ -117,17 +117,21 @@ layernorm_fwd_kernel(const __nv_bfloat16* __restrict__ x, const float* __restric
 //                                              i.e. the GEMM epilogue in front of the residual add)
 //   dgamma += sum_rows dy_eff * xhat ; dbeta += sum_rows dy_eff      (fp32 atomics)
 // ------------------------------------------------------------------------------------------------
+// Twelve rows in flight per block: every block ends with one atomic per column onto the same 2*H addresses, so fewer,
+// fatter blocks (one per SM) keep that serialised tail short (the BatchNorm reductions taught the same lesson).
+constexpr int LN_BWD_WARPS = 12;   // 160 registers per thread: 12 warps fill the register file with ONE block per SM
+
 template <int CH>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(LN_BWD_WARPS * 32)
 layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                      const float* __restrict__ gamma, const float* __restrict__ mean,
                      const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx,
                      __nv_bfloat16* __restrict__ dx_masked, float* __restrict__ dgamma,
                      float* __restrict__ dbeta, int T, DropCfg drop_in, DropCfg drop_out) {
   constexpr int H = CH * 256;
-  __shared__ float red[4][CH * 256 + 8];
+  __shared__ float red[LN_BWD_WARPS][CH * 256];   // 48 KB at H = 1024
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int warps_total = gridDim.x * 4;
+  const int warps_total = gridDim.x * LN_BWD_WARPS;
   const uint32_t seed_in = eff_seed(drop_in), seed_out = eff_seed(drop_out);
   float g[CH * 8], dg[CH * 8], db[CH * 8];
 #pragma unroll
@@ -141,7 +145,7 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
 #pragma unroll
   for (int i = 0; i < CH * 8; ++i) { dg[i] = 0.0f; db[i] = 0.0f; }
 
-  for (int row = blockIdx.x * 4 + warp; row < T; row += warps_total) {
+  for (int row = blockIdx.x * LN_BWD_WARPS + warp; row < T; row += warps_total) {
     const long long off = static_cast<long long>(row) * H;
     const uint4* xr = reinterpret_cast<const uint4*>(x + off);
     const uint4* dr = reinterpret_cast<const uint4*>(dy + off);
@@ -200,8 +204,12 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
     __syncthreads();
     float* dst = pass == 0 ? dgamma : dbeta;
     if (dst != nullptr)
-      for (int col = threadIdx.x; col < H; col += 128)
-        atomicAdd(dst + col, red[0][col] + red[1][col] + red[2][col] + red[3][col]);
+      for (int col = threadIdx.x; col < H; col += LN_BWD_WARPS * 32) {
+        float acc = 0.0f;
+#pragma unroll
+        for (int w = 0; w < LN_BWD_WARPS; ++w) acc += red[w][col];
+        atomicAdd(dst + col, acc);
+      }
     __syncthreads();
   }
 }
@@ -372,8 +380,8 @@ static int launch_ln_fwd(const void* x, const float* g, const float* b, void* y,
 template <int CH>
 static int launch_ln_bwd(const void* dy, const void* x, const float* g, const float* mean, const float* rstd,
                          void* dx, void* dxm, float* dg, float* db, int T, DropCfg din, DropCfg dout, cudaStream_t st) {
-  const int blocks = min((T + 3) / 4, sm_count() * 4);
-  layernorm_bwd_kernel<CH><<<blocks, 128, 0, st>>>(
+  const int blocks = min((T + LN_BWD_WARPS - 1) / LN_BWD_WARPS, sm_count());
+  layernorm_bwd_kernel<CH><<<blocks, LN_BWD_WARPS * 32, 0, st>>>(
       reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(x), g, mean, rstd,
       reinterpret_cast<__nv_bfloat16*>(dx), reinterpret_cast<__nv_bfloat16*>(dxm), dg, db, T, din, dout);
   DET_CHECK_CUDA(cudaGetLastError());
