@@ -4,6 +4,7 @@
 // Parity: reference master/pkg/actor/{system.go:10-110, ref.go, context.go, actors/timer.go, actors/stop.go}.
 #pragma once
 #include <atomic>
+#include <cstdio>
 #include <chrono>
 #include <condition_variable>
 #include <deque>
@@ -157,6 +158,34 @@ class ActorSystem {
   }
   void stop(const ActorRef& a) { tell(a, Message{"__stop__", Json(), nullptr, nullptr}); }
 
+  // Tracing (role of the reference's OpenTracing spans around every Receive, master/pkg/actor/trace.go:26-106, which
+  // it enables at link time): DET_ACTOR_TRACE=<file> or enable_trace(file) at run time makes every Receive a complete
+  // event ("ph":"X") in Chrome trace-event JSON lines — load the file in chrome://tracing or Perfetto. Timer ticks are
+  // filtered like the reference filters its noisy timers.
+  void enable_trace(const std::string& path) {
+    std::lock_guard<std::mutex> g(trace_mu_);
+    if (trace_) fclose(trace_);
+    trace_ = path.empty() ? nullptr : fopen(path.c_str(), "a");
+    trace_origin_ = std::chrono::steady_clock::now();
+  }
+  // [{address, mailbox, children, stopped}] for /debug/actors
+  Json describe_actors() {
+    std::lock_guard<std::mutex> g(mu_);
+    Json out = Json::array();
+    for (auto& kv : registry_) {
+      Json a = Json::object();
+      a["address"] = kv.first;
+      {
+        std::lock_guard<std::mutex> g2(kv.second->mu_);
+        a["mailbox"] = static_cast<long long>(kv.second->mailbox_.size());
+        a["children"] = static_cast<long long>(kv.second->children_.size());
+      }
+      a["stopped"] = kv.second->stopped();
+      out.push_back(a);
+    }
+    return out;
+  }
+
  private:
   friend class Context;
   struct Timer {
@@ -182,7 +211,26 @@ class ActorSystem {
     }
   }
   void finish_stop(const ActorRef& cell);
+  void trace_receive(const std::string& actor, const std::string& type, const std::string& sender,
+                     std::chrono::steady_clock::time_point t0) {
+    if (type == "tick" || type == "poll_timeout") return;   // periodic timers would drown everything else
+    using namespace std::chrono;
+    const auto t1 = steady_clock::now();
+    Json e = Json::object();
+    e["name"] = type; e["cat"] = "actor"; e["ph"] = "X"; e["pid"] = 1;
+    e["tid"] = actor;
+    e["ts"] = static_cast<long long>(duration_cast<microseconds>(t0 - trace_origin_).count());
+    e["dur"] = static_cast<long long>(duration_cast<microseconds>(t1 - t0).count());
+    Json args = Json::object();
+    args["sender"] = sender;
+    e["args"] = args;
+    std::lock_guard<std::mutex> g(trace_mu_);
+    if (trace_) { fputs((e.dump() + "\n").c_str(), trace_); fflush(trace_); }
+  }
 
+  std::mutex trace_mu_;
+  FILE* trace_ = nullptr;
+  std::chrono::steady_clock::time_point trace_origin_;
   std::mutex mu_;
   std::condition_variable cv_;
   std::deque<ActorRef> run_queue_;
@@ -255,7 +303,13 @@ inline void ActorSystem::worker() {
         } else if (msg.type == "__child_failed__") {
           cell->actor_->child_failed(ctx, msg.sender, msg.body.as_string());
         } else if (!cell->stopped()) {
-          cell->actor_->receive(ctx, msg);
+          if (trace_) {
+            const auto t0 = std::chrono::steady_clock::now();
+            cell->actor_->receive(ctx, msg);
+            trace_receive(cell->address(), msg.type, msg.sender ? msg.sender->address() : std::string(), t0);
+          } else {
+            cell->actor_->receive(ctx, msg);
+          }
         } else {
           msg.respond(Json());
         }

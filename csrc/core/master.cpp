@@ -341,6 +341,7 @@ void Master::restore_experiments() {
 
 int Master::start() {
   started_at = static_cast<long long>(std::time(nullptr));
+  if (const char* tf = getenv("DET_ACTOR_TRACE")) system.enable_trace(tf);
   Json cl = store.get("cluster", "id");
   if (cl.is_null()) { cluster_id = random_hex(16); store.put("cluster", "id", obj({{"cluster_id", cluster_id}})); }
   else cluster_id = cl["cluster_id"].as_string();

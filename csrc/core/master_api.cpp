@@ -67,6 +67,12 @@ void Master::register_routes() {
                    {"uptime_s", static_cast<long long>(std::time(nullptr)) - m->started_at.load()}, {"scheduler", m->cfg.scheduler}}));
   };
   http.route("GET", "/info", info);
+  // ---- debugging (role of the reference's /debug/pprof and actor tracing, master/internal/core.go:564-568) ----
+  http.route("GET", "/debug/actors", [m](const HttpRequest&) { return ok(m->system.describe_actors()); });
+  http.route("POST", "/debug/trace", [m](const HttpRequest& r) {   // {"file": "/tmp/actors.trace"} or {"file": ""} to stop
+    m->system.enable_trace(r.json()["file"].str_or(""));
+    return ok(Json::object());
+  });
   // ---- data-layer reader/writer leases (reference: /ws/data-layer/{resource}, master/internal/rw_coordinator.go) ----
   http.route("POST", "/api/v1/rw_coordinator/:resource/:verb", [m](const HttpRequest& r) {
     const std::string verb = r.params.at("verb");

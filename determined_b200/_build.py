@@ -118,11 +118,29 @@ def build_core(force: bool = False, verbose: bool = False) -> Path:
     return lib
 
 
+def build_selftest_tsan(verbose: bool = False) -> Path:
+    """``det-selftest`` compiled together with the whole control-plane library under ThreadSanitizer
+    (``build/det-selftest-tsan``). Run it directly; it exits non-zero on a failed expectation or a reported race."""
+    cxx = os.environ.get("CXX", "g++")
+    out = ROOT / "build" / "det-selftest-tsan"
+    out.parent.mkdir(parents=True, exist_ok=True)
+    srcs = [s for s in core_sources() if not s.stem.startswith("main_") or s.stem == "main_selftest"]
+    flags = [f for f in CXX_FLAGS if f not in ("-O2", "-O3", "-fPIC")]
+    cmd = [cxx, *flags, "-O1", "-g", "-fsanitize=thread", "-fno-omit-frame-pointer", *map(str, srcs), "-o", str(out), "-pthread"]
+    if verbose:
+        print("[build] " + " ".join(cmd), file=sys.stderr)
+    _run(cmd)
+    return out
+
+
 def build_all(force: bool = False, verbose: bool = False) -> None:
     build_kernels(force=force, verbose=verbose)
     build_core(force=force, verbose=verbose)
 
 
 if __name__ == "__main__":
+    if "--tsan" in sys.argv:
+        print("built:", build_selftest_tsan(verbose=True))
+        sys.exit(0)
     build_all(force="--force" in sys.argv, verbose=True)
     print("built:", sorted(p.name for p in LIB_DIR.iterdir()))

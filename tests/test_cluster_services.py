@@ -230,3 +230,15 @@ def test_provisioner_scales_up_on_demand_and_down_when_idle(tmp_path):
             proc.wait(timeout=5)
         except Exception:
             os.killpg(proc.pid, _signal.SIGKILL)
+
+
+def test_actor_trace_and_debug_endpoints(slotless_master, tmp_path):
+    c = MasterClient("127.0.0.1", slotless_master["port"])
+    actors = c.request("GET", "/debug/actors")
+    assert {"rm", "trial_logger", "experiments"} <= {a["address"] for a in actors}
+    trace = tmp_path / "actors.trace"
+    c.request("POST", "/debug/trace", {"file": str(trace)})
+    c.request("GET", "/api/v1/agents")           # an ask to the resource manager
+    c.request("POST", "/debug/trace", {"file": ""})
+    events = [json.loads(l) for l in trace.read_text().splitlines() if l.strip()]
+    assert any(e["tid"] == "rm" and e["name"] == "summary" and e["ph"] == "X" and e["dur"] >= 0 for e in events)
