@@ -16,7 +16,7 @@ import shutil
 import subprocess
 import sys
 from pathlib import Path
-from typing import List, Sequence
+from typing import Optional,  List, Sequence
 
 ROOT = Path(__file__).resolve().parent.parent
 CSRC = ROOT / "csrc"
@@ -121,16 +121,22 @@ def build_core(force: bool = False, verbose: bool = False) -> Path:
 def build_selftest_tsan(verbose: bool = False) -> Path:
     """``det-selftest`` compiled together with the whole control-plane library under ThreadSanitizer
     (``build/det-selftest-tsan``). Run it directly; it exits non-zero on a failed expectation or a reported race."""
-    cxx = os.environ.get("CXX", "g++")
     out = ROOT / "build" / "det-selftest-tsan"
     out.parent.mkdir(parents=True, exist_ok=True)
     srcs = [s for s in core_sources() if not s.stem.startswith("main_") or s.stem == "main_selftest"]
     flags = [f for f in CXX_FLAGS if f not in ("-O2", "-O3", "-fPIC")]
-    cmd = [cxx, *flags, "-O1", "-g", "-fsanitize=thread", "-fno-omit-frame-pointer", *map(str, srcs), "-o", str(out), "-pthread"]
-    if verbose:
-        print("[build] " + " ".join(cmd), file=sys.stderr)
-    _run(cmd)
-    return out
+    last: Optional[Exception] = None
+    # not every toolchain ships the sanitizer runtimes: try $CXX first, then the distribution compiler
+    for cxx in dict.fromkeys([os.environ.get("CXX") or "g++", "g++", "/usr/bin/g++"]):
+        cmd = [cxx, *flags, "-O1", "-g", "-fsanitize=thread", "-fno-omit-frame-pointer", *map(str, srcs), "-o", str(out), "-pthread"]
+        if verbose:
+            print("[build] " + " ".join(cmd[:12]) + " ...", file=sys.stderr)
+        try:
+            _run(cmd)
+            return out
+        except (RuntimeError, FileNotFoundError) as e:
+            last = e
+    raise RuntimeError(f"no compiler with a ThreadSanitizer (tsan) runtime found: {last}")
 
 
 def build_all(force: bool = False, verbose: bool = False) -> None:
