@@ -13,3 +13,21 @@ import numpy as _np
 for _n, _t in (("float", float), ("int", int), ("bool", bool), ("object", object), ("complex", complex), ("str", str)):
     if _n not in _np.__dict__:
         setattr(_np, _n, _t)
+
+# torch 1.4's torch.load unpickled anything; torch >= 2.6 defaults to weights_only=True, which refuses the numpy RNG
+# state every Determined checkpoint carries (reference: harness/determined/pytorch/_pytorch_trial.py:634 calls
+# torch.load(path, map_location="cpu")). Restore the old default for the reference process only.
+import functools as _functools
+
+import torch as _torch
+
+_orig_torch_load = _torch.load
+
+
+@_functools.wraps(_orig_torch_load)
+def _load_like_torch_1_4(*args, **kwargs):
+    kwargs.setdefault("weights_only", False)
+    return _orig_torch_load(*args, **kwargs)
+
+
+_torch.load = _load_like_torch_1_4
