@@ -225,6 +225,10 @@ class _GANBase(dp.PyTorchTrial):
         self.lr_g = self.context.wrap_lr_scheduler(
             torch.optim.lr_scheduler.LambdaLR(self.opt_g, lr_lambda=lambda epoch: 0.95 ** epoch),
             dp.LRScheduler.StepMode.STEP_EVERY_EPOCH)
+        if hp.get("use_cuda_graphs", False):
+            # both updates of a batch (generator, then discriminator) are captured into one graph: the requires_grad_
+            # toggling is a fixed pattern and the noise is drawn on the device
+            self.context.experimental.enable_cuda_graphs()
 
 
 class GANTrial(_GANBase):

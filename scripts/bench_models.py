@@ -62,7 +62,7 @@ class TorchResNet50Trial(VT.ResNet50Trial):
 
 MODELS = {
     "resnet50": (VT.ResNet50Trial, {"learning_rate": 0.1, "use_cuda_graphs": True}, (3, 224, 224), "images/s"),
-    "dcgan": (VT.DCGANTrial, {"latent_dim": 128}, (3, 64, 64), "images/s"),
+    "dcgan": (VT.DCGANTrial, {"latent_dim": 128, "use_cuda_graphs": True}, (3, 64, 64), "images/s"),
     "cifar": (VT.CIFARTrial, {"learning_rate": 1e-4}, (3, 32, 32), "images/s"),
     "mnist": (VT.MNistTrial, {"learning_rate": 1.0}, (1, 28, 28), "images/s"),
 }
