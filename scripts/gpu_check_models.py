@@ -19,8 +19,8 @@ CASES = [
     ("cifar", VT.CIFARTrial, {"global_batch_size": 64, "learning_rate": 1e-3}, {"train_size": 2048, "validation_size": 256}, 6, 8),
     ("gan_mnist", VT.GANTrial, {"global_batch_size": 64, "latent_dim": 128}, {"train_size": 1024, "validation_size": 128}, 3, 8),
     ("dcgan", VT.DCGANTrial, {"global_batch_size": 64, "latent_dim": 128}, {"train_size": 512, "validation_size": 128}, 3, 4),
-    ("resnet50", VT.ResNet50Trial, {"global_batch_size": 32, "learning_rate": 0.02}, {"train_size": 256, "validation_size": 64}, 4, 4),
-    ("resnet50_graphs", VT.ResNet50Trial, {"global_batch_size": 32, "learning_rate": 0.02, "use_cuda_graphs": True},
+    ("resnet50", VT.ResNet50Trial, {"global_batch_size": 32, "learning_rate": 0.002}, {"train_size": 256, "validation_size": 64}, 4, 4),
+    ("resnet50_graphs", VT.ResNet50Trial, {"global_batch_size": 32, "learning_rate": 0.002, "use_cuda_graphs": True},
      {"train_size": 256, "validation_size": 64}, 6, 4),
 ]
 bad = []
