@@ -364,3 +364,13 @@ extern "C" int det_bn_bwd(const void* dy, const void* x, const void* a, const fl
   DET_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
+
+// mean / rstd (and the running statistics) from column sums produced elsewhere — by det_bn_stats' reduction or by the
+// fused epilogues det_gemm_bf16_stats / det_conv2d_fprop_stats. sums = [sum | sum of squares], 2*C floats.
+extern "C" int det_bn_finalize(const float* sums, float* mean, float* rstd, float* running_mean, float* running_var, long long M,
+                               int C, float eps, float momentum, cudaStream_t stream) {
+  DET_REQUIRE(M > 0 && C > 0, "empty BatchNorm");
+  det::bn_finalize_kernel<<<(C + 127) / 128, 128, 0, stream>>>(sums, mean, rstd, running_mean, running_var, M, C, eps, momentum);
+  DET_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}

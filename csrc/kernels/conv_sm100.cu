@@ -18,8 +18,7 @@
 // (reference: examples/computer_vision/cifar10_pytorch/model_def.py:49-74,
 // examples/tutorials/mnist_pytorch/model_def.py:34-53). Strided convolutions and the few-channel first layers
 // take the explicit gather path in conv_ops.cu + the plain GEMM.
-#include "host_utils.h"
-#include "sm100_ptx.cuh"
+#include "gemm_common.cuh"
 
 namespace det {
 
@@ -40,6 +39,7 @@ struct ConvParams {
   long long ldc;
   const float* bias;          // fprop only, fp32 [Cout] or null
   int relu;                   // fprop only
+  float* colstats;            // fprop only, optional [2 * Cout]: += per-channel sum and sum of squares of the output
 };
 
 constexpr int CONV_BM = 128;
@@ -53,7 +53,7 @@ struct ConvCfg {
   static constexpr uint32_t A_BYTES = CONV_BM * CONV_BK * 2;
   static constexpr uint32_t B_BYTES = BN * CONV_BK * 2;
   static constexpr uint32_t TMEM_COLS = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
-  static constexpr uint32_t SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + 1024 + 256;
+  static constexpr uint32_t SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + 1024 + 256 + GEMM_STATS_SMEM_BYTES;
 };
 
 template <int BN, int MODE>
@@ -209,11 +209,28 @@ conv_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     const int part = ew >> 2;
     constexpr int COLS_PER_WARP = BN / 4;
     constexpr int CW = COLS_PER_WARP < 32 ? COLS_PER_WARP : 32;
+    constexpr int EPI_THREADS = CONV_EPI_WARPS * 32;
+    const bool stats = MODE == CONV_FPROP && p.colstats != nullptr;   // kernel-uniform
+    float* s_stat = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);   // [2][BN]
+    const int tid_e = ew * 32 + lane;
+    int stat_nt = -1;
+    if (stats) {
+      for (int i = tid_e; i < 2 * BN; i += EPI_THREADS) s_stat[i] = 0.0f;
+      epilogue_bar_sync(EPI_THREADS);
+    }
     uint32_t lt = 0;
     for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++lt) {
       const int tile = w / p.splitk;
       const int mt = tile % p.tiles_m;
       const int nt = tile / p.tiles_m;
+      if (stats && stat_nt != nt) {
+        if (stat_nt >= 0) {
+          epilogue_bar_sync(EPI_THREADS);
+          stats_flush(s_stat, BN, p.colstats, p.Cn, stat_nt * BN, tid_e);
+          epilogue_bar_sync(EPI_THREADS);
+        }
+        stat_nt = nt;
+      }
       const uint32_t buf = lt & 1;
       const uint32_t aph = (lt >> 1) & 1;
       const int r = q * 32 + lane;
@@ -300,10 +317,15 @@ conv_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
               if (ch0 + j < col_lim) cp[j] = __float2bfloat16_rn(v[j]);
           }
         }
+        if (stats) stats_accumulate<CW>(s_stat, BN, v, row_ok, c, lane);   // every lane takes part in the shuffles
       }
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&tempty_bar[buf]));
+    }
+    if (stats && stat_nt >= 0) {
+      epilogue_bar_sync(EPI_THREADS);
+      stats_flush(s_stat, BN, p.colstats, p.Cn, stat_nt * BN, tid_e);
     }
   }
 
@@ -359,10 +381,11 @@ static void pick_box(int PN, int PH, int PW, int maxrows, ConvParams& p) {
 //   mode 1 (dgrad): src = dy [N,Ho,Wo,Cout], other = weight, out = dx bf16 [N,H,W,Cin]
 //   mode 2 (wgrad): src = dy [N,Ho,Wo,Cout], other = x,      out = dW fp32 [Cout,R,S,Cin]  (accumulated)
 // Ho = H + 2*pad_h - R + 1, Wo = W + 2*pad_w - S + 1. Cin and Cout must be multiples of 8.
-extern "C" int det_conv2d_implicit(int mode, const void* src, const void* other, void* out, int N, int H, int W,
-                                   int Cin, int Cout, int R, int S, int pad_h, int pad_w, const float* bias,
-                                   int relu, int splitk, int force_bn, cudaStream_t stream) {
+static int conv_launch_impl(int mode, const void* src, const void* other, void* out, int N, int H, int W,
+                            int Cin, int Cout, int R, int S, int pad_h, int pad_w, const float* bias,
+                            int relu, int splitk, int force_bn, float* colstats, cudaStream_t stream) {
   using namespace det;
+  DET_REQUIRE(colstats == nullptr || mode == CONV_FPROP, "column statistics exist for the forward convolution only");
   DET_REQUIRE(mode >= 0 && mode <= 2, "conv mode must be 0 (fprop), 1 (dgrad) or 2 (wgrad)");
   DET_REQUIRE(N > 0 && H > 0 && W > 0 && Cin > 0 && Cout > 0 && R > 0 && S > 0, "empty convolution");
   DET_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0, "implicit conv needs channel counts that are multiples of 8");
@@ -372,7 +395,7 @@ extern "C" int det_conv2d_implicit(int mode, const void* src, const void* other,
   ConvParams p;
   std::memset(&p, 0, sizeof(p));
   p.S = S; p.taps = R * S;
-  p.out = out; p.bias = bias; p.relu = relu;
+  p.out = out; p.bias = bias; p.relu = relu; p.colstats = colstats;
   const int Cn = (mode == CONV_FPROP) ? Cout : Cin;
   p.Cn = Cn;
   int bn = force_bn;
@@ -446,4 +469,17 @@ extern "C" int det_conv2d_implicit(int mode, const void* src, const void* other,
   if (bn == 128) { DET_CONV_DISPATCH(128) }
   DET_CONV_DISPATCH(64)
 #undef DET_CONV_DISPATCH
+}
+
+extern "C" int det_conv2d_implicit(int mode, const void* src, const void* other, void* out, int N, int H, int W,
+                                   int Cin, int Cout, int R, int S, int pad_h, int pad_w, const float* bias,
+                                   int relu, int splitk, int force_bn, cudaStream_t stream) {
+  return conv_launch_impl(mode, src, other, out, N, H, W, Cin, Cout, R, S, pad_h, pad_w, bias, relu, splitk, force_bn, nullptr, stream);
+}
+
+// Forward convolution that also accumulates colstats[0:Cout] += per-channel sum and colstats[Cout:2*Cout] += sum of
+// squares of the bf16 output (the caller clears colstats): BatchNorm batch statistics without a pass over the output.
+extern "C" int det_conv2d_fprop_stats(const void* x, const void* weight, void* y, int N, int H, int W, int Cin, int Cout, int R,
+                                      int S, int pad_h, int pad_w, const float* bias, float* colstats, cudaStream_t stream) {
+  return conv_launch_impl(0, x, weight, y, N, H, W, Cin, Cout, R, S, pad_h, pad_w, bias, 0, 0, 0, colstats, stream);
 }

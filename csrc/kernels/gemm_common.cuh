@@ -31,6 +31,7 @@ struct GemmParams {
   float drop_scale;
   uint32_t drop_seed;
   const uint32_t* drop_seed_dev;  // optional per-step seed in device memory (CUDA-graph friendly)
+  float* colstats;                // optional [2 * N] fp32: += column sums and sums of squares of the (bf16-rounded) output
 };
 
 // erf GELU through the Abramowitz–Stegun 7.1.26 rational form (|error| < 1.5e-7, far below bf16 resolution): one
@@ -56,6 +57,65 @@ __device__ __forceinline__ float dgelu_erf(float x) {
   float cdf, e;
   phi_terms(x, cdf, e);
   return fmaf(x * 0.3989422804014327f, e, cdf);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Column statistics of the output tile, fused into the epilogue (BatchNorm batch statistics of a convolution output
+// without re-reading it). tcgen05.ld leaves one ROW per lane, so a column sum is a reduction ACROSS lanes: a butterfly
+// that halves the number of live columns per step leaves lane j holding the total of column j after 31 shuffles.
+// Totals go to a per-CTA shared-memory accumulator (all tiles of one n-tile share it) and reach global memory with one
+// atomic per column per CTA when the n-tile changes or the kernel ends.
+// ------------------------------------------------------------------------------------------------
+constexpr int GEMM_STATS_SMEM_BYTES = 2 * 256 * 4;
+
+template <int N_>
+__device__ __forceinline__ void col_reduce_step(float* a, int lane, int off) {
+  const bool up = (lane & off) != 0;
+#pragma unroll
+  for (int j = 0; j < N_; ++j) {
+    const float send = up ? a[j] : a[j + N_];
+    const float keep = up ? a[j + N_] : a[j];
+    a[j] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+  }
+}
+// in: a[32] = this lane's row; out: a[0] = total of column `lane` over the warp's 32 rows
+__device__ __forceinline__ void col_reduce32(float* a, int lane) {
+  col_reduce_step<16>(a, lane, 16);
+  col_reduce_step<8>(a, lane, 8);
+  col_reduce_step<4>(a, lane, 4);
+  col_reduce_step<2>(a, lane, 2);
+  col_reduce_step<1>(a, lane, 1);
+}
+__device__ __forceinline__ void epilogue_bar_sync(int threads) { asm volatile("bar.sync 1, %0;" ::"r"(threads) : "memory"); }
+
+// v[CW] final values of this lane's row (valid = row in range); c = first column of the chunk inside the tile
+template <int CW>
+__device__ __forceinline__ void stats_accumulate(float* s_stat, int bn, const float* v, bool valid, int c, int lane) {
+  float a[32], b[32];
+#pragma unroll
+  for (int j = 0; j < 32; ++j) {
+    const float x = (valid && j < CW) ? __bfloat162float(__float2bfloat16_rn(v[j < CW ? j : 0])) : 0.0f;
+    a[j] = x;
+    b[j] = x * x;
+  }
+  col_reduce32(a, lane);
+  col_reduce32(b, lane);
+  if (lane < CW) {
+    atomicAdd(s_stat + c + lane, a[0]);
+    atomicAdd(s_stat + bn + c + lane, b[0]);
+  }
+}
+// all epilogue threads call this between two epilogue_bar_sync(); tid_e = index among the epilogue threads
+__device__ __forceinline__ void stats_flush(float* s_stat, int bn, float* colstats, int N, int n0, int tid_e) {
+  if (tid_e < bn) {
+    const int col = n0 + tid_e;
+    if (col < N) {
+      atomicAdd(colstats + col, s_stat[tid_e]);
+      atomicAdd(colstats + N + col, s_stat[bn + tid_e]);
+    }
+    s_stat[tid_e] = 0.0f;
+    s_stat[bn + tid_e] = 0.0f;
+  }
 }
 
 // Epilogue of one tcgen05.ld chunk: v[CW] = accumulator values of `row`, columns col0 .. col0+CW-1.

@@ -30,7 +30,8 @@ struct GemmCfg {
   static constexpr uint32_t A_BYTES = GEMM_BM * GEMM_BK * 2;
   static constexpr uint32_t B_BYTES = BN * GEMM_BK * 2;
   static constexpr uint32_t TMEM_COLS = (2 * BN <= 32) ? 32 : (2 * BN <= 64 ? 64 : (2 * BN <= 128 ? 128 : (2 * BN <= 256 ? 256 : 512)));
-  static constexpr uint32_t SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr uint32_t SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + 1024 /*align slack*/ + 256 /*barriers*/ +
+                                         GEMM_STATS_SMEM_BYTES /*column statistics*/;
 };
 
 template <int BN, int A_MN, int B_MN>
@@ -155,12 +156,29 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     const int half = ew >> 2;          // which quarter of the BN columns (0..3)
     constexpr int COLS_PER_WARP = BN / 4;
     constexpr int CW = COLS_PER_WARP < 32 ? COLS_PER_WARP : 32;  // columns per tcgen05.ld chunk (16 when BN == 64)
+    constexpr int EPI_THREADS = GEMM_EPI_WARPS * 32;
+    const bool stats = p.colstats != nullptr;      // kernel-uniform
+    float* s_stat = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);   // [2][BN]
+    const int tid_e = ew * 32 + lane;
+    int stat_n0 = -1;                               // n-tile whose sums currently sit in s_stat
+    if (stats) {
+      for (int i = tid_e; i < 2 * BN; i += EPI_THREADS) s_stat[i] = 0.0f;
+      epilogue_bar_sync(EPI_THREADS);
+    }
     ptx::pdl_wait();              // bias / aux_in / C belong to earlier kernels
     uint32_t lt = 0;
     for (int w = blockIdx.x; w < total_work; w += gridDim.x, ++lt) {
       const int tile = w / p.splitk;
       const int m0 = (tile % p.tiles_m) * GEMM_BM;
       const int n0 = (tile / p.tiles_m) * BN;
+      if (stats && stat_n0 != n0) {
+        if (stat_n0 >= 0) {
+          epilogue_bar_sync(EPI_THREADS);
+          stats_flush(s_stat, BN, p.colstats, p.N, stat_n0, tid_e);
+          epilogue_bar_sync(EPI_THREADS);
+        }
+        stat_n0 = n0;
+      }
       const uint32_t buf = lt & 1;
       const uint32_t aph = (lt >> 1) & 1;
       ptx::mbar_wait(ptx::smem_u32(&tfull_bar[buf]), aph);
@@ -175,10 +193,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         else ptx::tmem_ld_32x32b_x16(taddr + c, v);
         ptx::tmem_ld_wait();
         gemm_epilogue_chunk<CW>(p, v, row, row_ok, n0 + c);
+        if (stats && n0 + c < p.N) stats_accumulate<CW>(s_stat, BN, v, row_ok, c, lane);
       }
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&tempty_bar[buf]));
+    }
+    if (stats && stat_n0 >= 0) {
+      epilogue_bar_sync(EPI_THREADS);
+      stats_flush(s_stat, BN, p.colstats, p.N, stat_n0, tid_e);
     }
   }
 
@@ -430,14 +453,18 @@ static int pick_bn(int M, int N, int sms, bool splitk_ok) {
 // A: a_mn == 0 -> row-major [M, K] (ld = lda); a_mn == 1 -> stored [K, M] with M contiguous.
 // B: b_mn == 0 -> row-major [N, K] (ld = ldb); b_mn == 1 -> stored [K, N] with N contiguous.
 // splitk <= 0 picks automatically (only > 1 when out_mode == OUT_F32_ATOMIC_ADD).
-extern "C" int det_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int a_mn,
-                             int b_mn, long long lda, long long ldb, long long ldc, int out_mode,
-                             int epi, float alpha, const float* bias, const void* aux_in,
-                             void* aux_out, long long ld_aux, float dropout_p,
-                             unsigned int dropout_seed, const unsigned int* dropout_seed_dev, int splitk,
-                             int force_bn,
-                             cudaStream_t stream) {
+static int gemm_launch_impl(const void* A, const void* B, void* C, int M, int N, int K, int a_mn,
+                            int b_mn, long long lda, long long ldb, long long ldc, int out_mode,
+                            int epi, float alpha, const float* bias, const void* aux_in,
+                            void* aux_out, long long ld_aux, float dropout_p,
+                            unsigned int dropout_seed, const unsigned int* dropout_seed_dev, int splitk,
+                            int force_bn, float* colstats,
+                            cudaStream_t stream) {
   using namespace det;
+  if (colstats != nullptr) {
+    DET_REQUIRE(out_mode == OUT_BF16, "column statistics are defined for bf16 outputs");
+    if (force_bn <= 0 || force_bn == 512) force_bn = N <= 64 ? 64 : (N <= 128 ? 128 : 256);   // the pair kernel has no statistics path
+  }
   DET_REQUIRE(M > 0 && N > 0 && K > 0, "empty GEMM");
   DET_REQUIRE(out_mode >= 0 && out_mode <= 2, "bad out_mode");
   const int sms = sm_count();
@@ -482,6 +509,7 @@ extern "C" int det_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   }
   p.drop_seed = dropout_seed;
   p.drop_seed_dev = dropout_seed_dev;
+  p.colstats = colstats;
 
   CUtensorMap ta, tb;
   int rc;
@@ -509,4 +537,22 @@ extern "C" int det_gemm_bf16(const void* A, const void* B, void* C, int M, int N
   if (bn == 128) { DET_GEMM_DISPATCH(128) }
   DET_GEMM_DISPATCH(64)
 #undef DET_GEMM_DISPATCH
+}
+
+extern "C" int det_gemm_bf16(const void* A, const void* B, void* C, int M, int N, int K, int a_mn,
+                             int b_mn, long long lda, long long ldb, long long ldc, int out_mode,
+                             int epi, float alpha, const float* bias, const void* aux_in,
+                             void* aux_out, long long ld_aux, float dropout_p,
+                             unsigned int dropout_seed, const unsigned int* dropout_seed_dev, int splitk,
+                             int force_bn, cudaStream_t stream) {
+  return gemm_launch_impl(A, B, C, M, N, K, a_mn, b_mn, lda, ldb, ldc, out_mode, epi, alpha, bias, aux_in, aux_out, ld_aux,
+                          dropout_p, dropout_seed, dropout_seed_dev, splitk, force_bn, nullptr, stream);
+}
+
+// Same GEMM, and colstats[0:N] += column sums, colstats[N:2N] += column sums of squares of the bf16 output (the caller
+// clears colstats). Serves BatchNorm batch statistics of 1x1 convolutions without a second pass over the output.
+extern "C" int det_gemm_bf16_stats(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb,
+                                   long long ldc, int epi, const float* bias, float* colstats, cudaStream_t stream) {
+  return gemm_launch_impl(A, B, C, M, N, K, 0, 0, lda, ldb, ldc, 0, epi, 1.0f, bias, nullptr, nullptr, 0, 0.0f, 0, nullptr, 0, 0,
+                          colstats, stream);
 }

@@ -16,7 +16,7 @@ from typing import List, Optional
 import torch
 import torch.nn as nn
 
-from ..ops.conv import BatchNorm2d, Conv2d, GlobalAvgPool2d, MaxPool2d
+from ..ops.conv import BatchNorm2d, Conv2d, GlobalAvgPool2d, MaxPool2d, conv_bn
 from ..ops.modules import Linear
 
 
@@ -34,10 +34,10 @@ class Bottleneck(nn.Module):
         self.downsample = downsample
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        identity = x if self.downsample is None else self.downsample(x)
-        out = self.bn1(self.conv1(x))
-        out = self.bn2(self.conv2(out))
-        return self.bn3(self.conv3(out), identity)
+        identity = x if self.downsample is None else conv_bn(self.downsample[0], self.downsample[1], x)
+        out = conv_bn(self.conv1, self.bn1, x)
+        out = conv_bn(self.conv2, self.bn2, out)
+        return conv_bn(self.conv3, self.bn3, out, identity)
 
 
 class BasicBlock(nn.Module):
@@ -52,8 +52,8 @@ class BasicBlock(nn.Module):
         self.downsample = downsample
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        identity = x if self.downsample is None else self.downsample(x)
-        return self.bn2(self.conv2(self.bn1(self.conv1(x))), identity)
+        identity = x if self.downsample is None else conv_bn(self.downsample[0], self.downsample[1], x)
+        return conv_bn(self.conv2, self.bn2, conv_bn(self.conv1, self.bn1, x), identity)
 
 
 class ResNet(nn.Module):
@@ -84,7 +84,7 @@ class ResNet(nn.Module):
         return nn.Sequential(*layers)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        x = self.maxpool(self.bn1(self.conv1(x)))
+        x = self.maxpool(conv_bn(self.conv1, self.bn1, x))
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         return self.fc(self.avgpool(x))
 

@@ -34,6 +34,10 @@ _SIGNATURES = {
     "det_cast_f32_bf16": [c_void_p, c_void_p, c_ll, c_void_p],
     "det_conv2d_implicit": [c_int, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                             c_int, c_int, c_void_p, c_int, c_int, c_int, c_void_p],
+    "det_conv2d_fprop_stats": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                               c_void_p, c_void_p, c_void_p],
+    "det_gemm_bf16_stats": [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_ll, c_ll, c_ll, c_int, c_void_p, c_void_p, c_void_p],
+    "det_bn_finalize": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_int, c_float, c_float, c_void_p],
     "det_im2col": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p],
     "det_col2im": [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p],
     "det_bn_stats": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_int, c_float, c_float, c_void_p],

@@ -76,7 +76,7 @@ def _pad_cols(t: torch.Tensor, cols: int) -> torch.Tensor:
 # ------------------------------------------------------------------------------------------------
 class _Conv2dFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, pad, relu):
+    def forward(ctx, x, weight, bias, stride, pad, relu, want_stats=False):
         N, H, W, Cin = x.shape
         Cout, R, S, _ = weight.shape
         ph, pw = pad
@@ -84,17 +84,26 @@ class _Conv2dFn(torch.autograd.Function):
         M = N * Ho * Wo
         w = shadow_of(weight)
         aligned = Cin % 8 == 0 and Cout % 8 == 0
+        # per-channel sum / sum of squares of the output, accumulated by the producing kernel's epilogue (BatchNorm
+        # statistics without a pass over the output); only where the epilogue writes the final values
+        sums = torch.zeros(2 * Cout, dtype=torch.float32, device=x.device) if (want_stats and aligned and not relu) else None
         if aligned and stride == 1 and R == 1 and S == 1 and ph == 0 and pw == 0:
             kind = "gemm"
             y = torch.empty(N, Ho, Wo, Cout, dtype=torch.bfloat16, device=x.device)
-            F.gemm(x.view(M, Cin), w.view(Cout, Cin), y.view(M, Cout), M, Cout, Cin,
-                   epi=F.EPI_BIAS if bias is not None else F.EPI_NONE, bias=bias)
+            if sums is not None:
+                F.gemm_stats(x.view(M, Cin), w.view(Cout, Cin), y.view(M, Cout), M, Cout, Cin, sums, bias=bias)
+            else:
+                F.gemm(x.view(M, Cin), w.view(Cout, Cin), y.view(M, Cout), M, Cout, Cin,
+                       epi=F.EPI_BIAS if bias is not None else F.EPI_NONE, bias=bias)
             if relu:
                 y = F.act_fwd(y, F.ACT_RELU)
         elif aligned and stride == 1:
             kind = "implicit"
             y = torch.empty(N, Ho, Wo, Cout, dtype=torch.bfloat16, device=x.device)
-            F.conv2d_implicit(F.CONV_FPROP, x, w, y, N, H, W, Cin, Cout, R, S, ph, pw, bias=bias, relu=relu)
+            if sums is not None:
+                F.conv2d_fprop_stats(x, w, y, N, H, W, Cin, Cout, R, S, ph, pw, sums, bias=bias)
+            else:
+                F.conv2d_implicit(F.CONV_FPROP, x, w, y, N, H, W, Cin, Cout, R, S, ph, pw, bias=bias, relu=relu)
         else:
             kind = "explicit"
             K = R * S * Cin
@@ -102,7 +111,10 @@ class _Conv2dFn(torch.autograd.Function):
             col = F.im2col(x, N, H, W, Cin, R, S, stride, ph, pw, Kp)
             wk = _pad_cols(w.view(Cout, K), Kp)
             yp = torch.empty(M, Cp, dtype=torch.bfloat16, device=x.device)
-            F.gemm(col, wk, yp, M, Cout, Kp, epi=F.EPI_BIAS if bias is not None else F.EPI_NONE, bias=bias)
+            if sums is not None:     # aligned ⇒ Cp == Cout
+                F.gemm_stats(col, wk, yp, M, Cout, Kp, sums, bias=bias)
+            else:
+                F.gemm(col, wk, yp, M, Cout, Kp, epi=F.EPI_BIAS if bias is not None else F.EPI_NONE, bias=bias)
             y = (yp if Cp == Cout else yp[:, :Cout].contiguous()).view(N, Ho, Wo, Cout)
             if relu:
                 y = F.act_fwd(y, F.ACT_RELU)
@@ -113,10 +125,15 @@ class _Conv2dFn(torch.autograd.Function):
         ctx.weight, ctx.bias = weight, bias
         ctx.cfg = (kind, stride, ph, pw, relu)
         note_param_use(ctx, weight, bias)
+        if want_stats:
+            if sums is None:   # this path's epilogue cannot produce them: signal the caller to run the reduction kernel
+                sums = torch.empty(0, dtype=torch.float32, device=x.device)
+            ctx.mark_non_differentiable(sums)
+            return y, sums
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, _dsums=None):
         x, y = ctx.saved_tensors
         weight, bias = ctx.weight, ctx.bias
         kind, stride, ph, pw, relu = ctx.cfg
@@ -171,7 +188,7 @@ class _Conv2dFn(torch.autograd.Function):
                 F.gemm(dyp, wk, dcol, M, Kp, Cp, b_mn=True)
                 dx = F.col2im(dcol, N, H, W, Cin, R, S, stride, ph, pw, Kp)
         notify_grads_written(weight, bias)
-        return dx, None, None, None, None, None
+        return dx, None, None, None, None, None, None
 
 
 class Conv2d(nn.Module):
@@ -198,7 +215,7 @@ class Conv2d(nn.Module):
         if not x.is_cuda:
             y = nn.functional.conv2d(x.float(), self.weight.permute(0, 3, 1, 2), self.bias, self.stride, self.padding)
             return torch.relu(y) if self.activation == "relu" else y
-        y = _Conv2dFn.apply(to_nhwc(x), self.weight, self.bias, self.stride, self.padding, self.activation == "relu")
+        y = _Conv2dFn.apply(to_nhwc(x), self.weight, self.bias, self.stride, self.padding, self.activation == "relu", False)
         return from_nhwc(y)
 
     def _save_to_state_dict(self, destination, prefix, keep_vars):
@@ -401,6 +418,30 @@ class BatchNorm2d(nn.BatchNorm2d):
             rstd = torch.rsqrt(self.running_var + self.eps)
             y = _FrozenBatchNormFn.apply(xn, rn, self.weight, self.bias, self.running_mean, rstd, act, self.negative_slope)
         return from_nhwc(y)
+
+
+def conv_bn(conv: "Conv2d", bn: "BatchNorm2d", x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``bn(conv(x), residual)`` with the BatchNorm batch statistics taken from the convolution's own epilogue: the
+    kernel that writes the convolution output also accumulates per-channel sum and sum of squares, so training-mode
+    BatchNorm needs no statistics pass over that tensor. Falls back to the two separate modules whenever that is not
+    possible (CPU, eval mode, fused ReLU in the convolution, unaligned channel counts)."""
+    C = bn.num_features
+    use_batch = bn.training or not bn.track_running_stats
+    if not (x.is_cuda and use_batch and conv.activation is None and C % 8 == 0 and (C <= 2048 or C % 2048 == 0)):
+        return bn(conv(x), residual)
+    y, sums = _Conv2dFn.apply(to_nhwc(x), conv.weight, conv.bias, conv.stride, conv.padding, False, True)
+    rn = to_nhwc(residual) if residual is not None else None
+    track = bn.training and bn.track_running_stats
+    if track and bn.num_batches_tracked is not None:
+        bn.num_batches_tracked.add_(1)
+    mom = 0.0 if bn.momentum is None else bn.momentum
+    rm, rv = (bn.running_mean, bn.running_var) if track else (None, None)
+    if sums.numel() == 2 * C:
+        mean, rstd = F.bn_finalize(sums, y.numel() // C, C, rm, rv, bn.eps, mom)
+    else:
+        mean, rstd = F.bn_stats(y, C, rm, rv, bn.eps, mom)
+    out = _BatchNormFn.apply(y, rn, bn.weight, bn.bias, mean, rstd, _ACT_CODES[bn.activation], bn.negative_slope)
+    return from_nhwc(out)
 
 
 # ------------------------------------------------------------------------------------------------

@@ -363,3 +363,29 @@ def u8_nhwc_to_bf16(x: torch.Tensor, mean, std) -> torch.Tensor:
     s = (ctypes.c_float * C)(*[float(v) for v in std])
     _native.call("det_u8_to_bf16_norm", _p(x), _p(out), x.numel(), C, m, s, _stream())
     return out
+
+
+def gemm_stats(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: int, K: int, colstats: torch.Tensor, *,
+               bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``out = a @ b.T (+ bias)`` and ``colstats[0:N] += column sums``, ``colstats[N:2N] += column sums of squares`` of the
+    bf16 output, from the GEMM epilogue (``colstats`` fp32, cleared by the caller)."""
+    _native.call("det_gemm_bf16_stats", _p(a), _p(b), _p(out), M, N, K, a.stride(0), b.stride(0), out.stride(0),
+                 EPI_BIAS if bias is not None else EPI_NONE, _p(bias), _p(colstats), _stream())
+    return out
+
+
+def conv2d_fprop_stats(x: torch.Tensor, w: torch.Tensor, y: torch.Tensor, N: int, H: int, W: int, Cin: int, Cout: int, R: int,
+                       S: int, pad_h: int, pad_w: int, colstats: torch.Tensor, *, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Implicit-GEMM forward convolution that also accumulates per-channel sum / sum of squares of its output."""
+    _native.call("det_conv2d_fprop_stats", _p(x), _p(w), _p(y), N, H, W, Cin, Cout, R, S, pad_h, pad_w, _p(bias), _p(colstats),
+                 _stream())
+    return y
+
+
+def bn_finalize(sums: torch.Tensor, M: int, C: int, running_mean: Optional[torch.Tensor], running_var: Optional[torch.Tensor],
+                eps: float, momentum: float) -> Tuple[torch.Tensor, torch.Tensor]:
+    mean = torch.empty(C, dtype=torch.float32, device=sums.device)
+    rstd = torch.empty(C, dtype=torch.float32, device=sums.device)
+    _native.call("det_bn_finalize", _p(sums), _p(mean), _p(rstd), _p(running_mean), _p(running_var), M, C, float(eps), float(momentum),
+                 _stream())
+    return mean, rstd

@@ -112,6 +112,14 @@ int det_ipc_close(void* p);
 int det_conv2d_implicit(int mode, const void* src, const void* other, void* out, int N, int H, int W, int Cin,
                         int Cout, int R, int S, int pad_h, int pad_w, const float* bias, int relu, int splitk,
                         int force_bn, cudaStream_t stream);
+/* Forward variants that also accumulate per-output-channel sum and sum of squares of the bf16 output into
+ * colstats [2*Cout] (caller clears it): BatchNorm batch statistics fused into the producing kernel's epilogue. */
+int det_conv2d_fprop_stats(const void* x, const void* weight, void* y, int N, int H, int W, int Cin, int Cout, int R, int S,
+                           int pad_h, int pad_w, const float* bias, float* colstats, cudaStream_t stream);
+int det_gemm_bf16_stats(const void* A, const void* B, void* C, int M, int N, int K, long long lda, long long ldb,
+                        long long ldc, int epi, const float* bias, float* colstats, cudaStream_t stream);
+int det_bn_finalize(const float* sums, float* mean, float* rstd, float* running_mean, float* running_var, long long M, int C,
+                    float eps, float momentum, cudaStream_t stream);
 /* gather path for strided / few-channel convolutions: col [N*Ho*Wo, Kp] with column (r, s, c); Kp % 8 == 0 */
 int det_im2col(const void* x, void* col, int N, int H, int W, int C, int R, int S, int stride, int pad_h, int pad_w,
                int Kp, cudaStream_t stream);

@@ -171,3 +171,35 @@ def test_resnet50_tracks_torchvision():
         tr.append(l1.item())
         tm.append(l2.item())
     assert all(abs(a - b) / abs(a) < 0.3 for a, b in zip(tr, tm)), (tr, tm)
+
+
+@pytest.mark.parametrize("N,H,Cin,Cout,k,s,p", [(4, 14, 64, 256, 1, 1, 0), (3, 14, 64, 64, 3, 1, 1), (2, 28, 128, 128, 3, 2, 1), (2, 9, 72, 136, 3, 1, 1)])
+def test_conv_bn_fused_statistics(N, H, Cin, Cout, k, s, p):
+    """conv_bn takes the BatchNorm batch statistics from the convolution's epilogue (GEMM, implicit-GEMM and gather
+    paths): output, running statistics and all gradients must match conv -> bn run as two separate torch modules."""
+    from determined_b200.ops import conv as C
+
+    torch.manual_seed(Cin + Cout + k)
+    x = _bf(torch.randn(N, Cin, H, H, device="cuda"))
+    rconv = nn.Conv2d(Cin, Cout, k, s, p, bias=False).cuda()
+    rbn = nn.BatchNorm2d(Cout).cuda()
+    with torch.no_grad():
+        rconv.weight.copy_(_bf(rconv.weight))
+        rbn.weight.copy_(torch.rand(Cout, device="cuda") + 0.5)
+        rbn.bias.copy_(torch.randn(Cout, device="cuda") * 0.2)
+    mconv = C.Conv2d(Cin, Cout, k, s, p, bias=False).cuda()
+    mbn = C.BatchNorm2d(Cout, activation="relu").cuda()
+    mconv.load_state_dict(rconv.state_dict())
+    mbn.load_state_dict(rbn.state_dict())
+    xr = x.clone().requires_grad_(True)
+    xm = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    yr = torch.relu(rbn(rconv(xr)))
+    ym = C.conv_bn(mconv, mbn, xm)
+    assert _rel(ym, yr) < 3e-2
+    assert _rel(mbn.running_mean, rbn.running_mean) < 2e-2 and _rel(mbn.running_var, rbn.running_var) < 2e-2
+    g = _bf(torch.randn_like(yr))
+    yr.backward(g)
+    ym.backward(g.to(torch.bfloat16))
+    assert _rel(xm.grad, xr.grad) < 4e-2
+    assert _rel(mconv.weight.grad.permute(0, 3, 1, 2), rconv.weight.grad) < 4e-2
+    assert _rel(mbn.weight.grad, rbn.weight.grad) < 3e-2 and _rel(mbn.bias.grad, rbn.bias.grad) < 3e-2
