@@ -56,7 +56,7 @@ struct ConvCfg {
   static constexpr uint32_t SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + 1024 + 256 + GEMM_STATS_SMEM_BYTES;
 };
 
-template <int BN, int MODE>
+template <int BN, int MODE, bool STATS = false>
 __global__ void __launch_bounds__(CONV_THREADS, 1)
 conv_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                     const ConvParams p) {
@@ -210,7 +210,7 @@ conv_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
     constexpr int COLS_PER_WARP = BN / 4;
     constexpr int CW = COLS_PER_WARP < 32 ? COLS_PER_WARP : 32;
     constexpr int EPI_THREADS = CONV_EPI_WARPS * 32;
-    const bool stats = MODE == CONV_FPROP && p.colstats != nullptr;   // kernel-uniform
+    constexpr bool stats = STATS && MODE == CONV_FPROP;
     float* s_stat = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);   // [2][BN]
     const int tid_e = ew * 32 + lane;
     int stat_nt = -1;
@@ -337,10 +337,10 @@ conv_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_cons
   }
 }
 
-template <int BN, int MODE>
+template <int BN, int MODE, bool STATS = false>
 static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, int grid, cudaStream_t stream) {
   using Cfg = ConvCfg<BN>;
-  auto kfn = conv_tcgen05_kernel<BN, MODE>;
+  auto kfn = conv_tcgen05_kernel<BN, MODE, STATS>;
   static bool attr_set[64] = {false};
   int dev = 0;
   DET_CHECK_CUDA(cudaGetDevice(&dev));
@@ -461,6 +461,11 @@ static int conv_launch_impl(int mode, const void* src, const void* other, void* 
     p.splitk = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
   }
   const int grid = min(p.tiles_m * p.tiles_n * p.splitk, sms);
+  if (colstats != nullptr) {
+    if (bn == 256) return launch_conv<256, CONV_FPROP, true>(ta, tb, p, grid, stream);
+    if (bn == 128) return launch_conv<128, CONV_FPROP, true>(ta, tb, p, grid, stream);
+    return launch_conv<64, CONV_FPROP, true>(ta, tb, p, grid, stream);
+  }
 #define DET_CONV_DISPATCH(BN_)                                                              \
   if (mode == CONV_FPROP) return launch_conv<BN_, CONV_FPROP>(ta, tb, p, grid, stream);     \
   if (mode == CONV_DGRAD) return launch_conv<BN_, CONV_DGRAD>(ta, tb, p, grid, stream);     \

@@ -34,7 +34,9 @@ struct GemmCfg {
                                          GEMM_STATS_SMEM_BYTES /*column statistics*/;
 };
 
-template <int BN, int A_MN, int B_MN>
+// STATS = true additionally accumulates per-column sum / sum of squares of the output (BatchNorm statistics); it is a
+// template parameter, not a run-time branch: even a never-taken branch in the epilogue cost the BERT GEMMs 4 %.
+template <int BN, int A_MN, int B_MN, bool STATS = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
                          const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
@@ -157,7 +159,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     constexpr int COLS_PER_WARP = BN / 4;
     constexpr int CW = COLS_PER_WARP < 32 ? COLS_PER_WARP : 32;  // columns per tcgen05.ld chunk (16 when BN == 64)
     constexpr int EPI_THREADS = GEMM_EPI_WARPS * 32;
-    const bool stats = p.colstats != nullptr;      // kernel-uniform
+    constexpr bool stats = STATS;
     float* s_stat = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);   // [2][BN]
     const int tid_e = ew * 32 + lane;
     int stat_n0 = -1;                               // n-tile whose sums currently sit in s_stat
@@ -213,11 +215,11 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   }
 }
 
-template <int BN, int A_MN, int B_MN>
+template <int BN, int A_MN, int B_MN, bool STATS = false>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid,
                        cudaStream_t stream) {
   using Cfg = GemmCfg<BN>;
-  auto kfn = gemm_bf16_tcgen05_kernel<BN, A_MN, B_MN>;
+  auto kfn = gemm_bf16_tcgen05_kernel<BN, A_MN, B_MN, STATS>;
   static bool attr_set[64] = {false};
   int dev = 0;
   DET_CHECK_CUDA(cudaGetDevice(&dev));
@@ -528,6 +530,12 @@ static int gemm_launch_impl(const void* A, const void* B, void* C, int M, int N,
     return launch_gemm2<1, 1>(ta, tb, p, grid2, stream);
   }
   const int grid = min(tiles * p.splitk, sms);
+  if (colstats != nullptr) {
+    DET_REQUIRE(a_mn == 0 && b_mn == 0, "column statistics need K-major operands");
+    if (bn == 256) return launch_gemm<256, 0, 0, true>(ta, tb, p, grid, stream);
+    if (bn == 128) return launch_gemm<128, 0, 0, true>(ta, tb, p, grid, stream);
+    return launch_gemm<64, 0, 0, true>(ta, tb, p, grid, stream);
+  }
 #define DET_GEMM_DISPATCH(BN_)                                                     \
   if (a_mn == 0 && b_mn == 0) return launch_gemm<BN_, 0, 0>(ta, tb, p, grid, stream); \
   if (a_mn == 0 && b_mn == 1) return launch_gemm<BN_, 0, 1>(ta, tb, p, grid, stream); \
