@@ -176,7 +176,9 @@ def test_resnet50_tracks_torchvision():
 @pytest.mark.parametrize("N,H,Cin,Cout,k,s,p", [(4, 14, 64, 256, 1, 1, 0), (3, 14, 64, 64, 3, 1, 1), (2, 28, 128, 128, 3, 2, 1), (2, 9, 72, 136, 3, 1, 1)])
 def test_conv_bn_fused_statistics(N, H, Cin, Cout, k, s, p):
     """conv_bn takes the BatchNorm batch statistics from the convolution's epilogue (GEMM, implicit-GEMM and gather
-    paths): output, running statistics and all gradients must match conv -> bn run as two separate torch modules."""
+    paths). Against torch (fp32): output and running statistics. Against the SAME modules run unfused (identical bf16
+    numerics, statistics from the separate reduction kernel): output and every gradient, tightly — comparing gradients
+    with fp32 torch here would mostly measure ReLU-mask flips of near-zero activations, not the fusion."""
     from determined_b200.ops import conv as C
 
     torch.manual_seed(Cin + Cout + k)
@@ -187,19 +189,27 @@ def test_conv_bn_fused_statistics(N, H, Cin, Cout, k, s, p):
         rconv.weight.copy_(_bf(rconv.weight))
         rbn.weight.copy_(torch.rand(Cout, device="cuda") + 0.5)
         rbn.bias.copy_(torch.randn(Cout, device="cuda") * 0.2)
-    mconv = C.Conv2d(Cin, Cout, k, s, p, bias=False).cuda()
-    mbn = C.BatchNorm2d(Cout, activation="relu").cuda()
-    mconv.load_state_dict(rconv.state_dict())
-    mbn.load_state_dict(rbn.state_dict())
-    xr = x.clone().requires_grad_(True)
-    xm = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)
-    yr = torch.relu(rbn(rconv(xr)))
-    ym = C.conv_bn(mconv, mbn, xm)
-    assert _rel(ym, yr) < 3e-2
-    assert _rel(mbn.running_mean, rbn.running_mean) < 2e-2 and _rel(mbn.running_var, rbn.running_var) < 2e-2
-    g = _bf(torch.randn_like(yr))
-    yr.backward(g)
-    ym.backward(g.to(torch.bfloat16))
-    assert _rel(xm.grad, xr.grad) < 8e-2      # bf16 through conv -> BN -> ReLU backward: two rounded tensors in the chain
-    assert _rel(mconv.weight.grad.permute(0, 3, 1, 2), rconv.weight.grad) < 8e-2
-    assert _rel(mbn.weight.grad, rbn.weight.grad) < 3e-2 and _rel(mbn.bias.grad, rbn.bias.grad) < 3e-2
+
+    def mine():
+        conv = C.Conv2d(Cin, Cout, k, s, p, bias=False).cuda()
+        bn = C.BatchNorm2d(Cout, activation="relu").cuda()
+        conv.load_state_dict(rconv.state_dict())
+        bn.load_state_dict(rbn.state_dict())
+        return conv, bn
+
+    fconv, fbn = mine()
+    uconv, ubn = mine()
+    xf = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    xu = xf.detach().clone().requires_grad_(True)
+    yr = torch.relu(rbn(rconv(x)))
+    yf = C.conv_bn(fconv, fbn, xf)
+    yu = ubn(uconv(xu))
+    assert _rel(yf, yr) < 3e-2
+    assert _rel(fbn.running_mean, rbn.running_mean) < 2e-2 and _rel(fbn.running_var, rbn.running_var) < 2e-2
+    assert _rel(yf, yu) < 1e-2 and _rel(fbn.running_var, ubn.running_var) < 1e-3
+    g = _bf(torch.randn_like(yr)).to(torch.bfloat16)
+    yf.backward(g)
+    yu.backward(g)
+    assert _rel(xf.grad, xu.grad) < 2e-2
+    assert _rel(fconv.weight.grad, uconv.weight.grad) < 2e-2
+    assert _rel(fbn.weight.grad, ubn.weight.grad) < 2e-2 and _rel(fbn.bias.grad, ubn.bias.grad) < 2e-2
