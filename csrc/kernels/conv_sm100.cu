@@ -53,7 +53,8 @@ struct ConvCfg {
   static constexpr uint32_t A_BYTES = CONV_BM * CONV_BK * 2;
   static constexpr uint32_t B_BYTES = BN * CONV_BK * 2;
   static constexpr uint32_t TMEM_COLS = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
-  static constexpr uint32_t SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + 1024 + 256 + GEMM_STATS_SMEM_BYTES;
+  static constexpr uint32_t SMEM_BYTES = STAGES * (A_BYTES + B_BYTES) + 1024 + 256;   // see GemmCfg on the carve-out
+  static constexpr uint32_t SMEM_BYTES_STATS = SMEM_BYTES + GEMM_STATS_SMEM_BYTES;
 };
 
 template <int BN, int MODE, bool STATS = false>
@@ -341,14 +342,15 @@ template <int BN, int MODE, bool STATS = false>
 static int launch_conv(const CUtensorMap& ta, const CUtensorMap& tb, const ConvParams& p, int grid, cudaStream_t stream) {
   using Cfg = ConvCfg<BN>;
   auto kfn = conv_tcgen05_kernel<BN, MODE, STATS>;
+  constexpr uint32_t SMEM = STATS ? Cfg::SMEM_BYTES_STATS : Cfg::SMEM_BYTES;
   static bool attr_set[64] = {false};
   int dev = 0;
   DET_CHECK_CUDA(cudaGetDevice(&dev));
   if (dev < 64 && !attr_set[dev]) {
-    DET_CHECK_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    DET_CHECK_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
     attr_set[dev] = true;
   }
-  kfn<<<grid, CONV_THREADS, Cfg::SMEM_BYTES, stream>>>(ta, tb, p);
+  kfn<<<grid, CONV_THREADS, SMEM, stream>>>(ta, tb, p);
   DET_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

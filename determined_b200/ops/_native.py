@@ -12,7 +12,8 @@ from pathlib import Path
 from typing import Optional
 
 _LIB: Optional[ctypes.CDLL] = None
-_LIB_PATH = Path(__file__).resolve().parent.parent / "_lib" / "libdet_kernels.so"
+# DET_KERNELS_LIB points at an alternative build of the same ABI (A/B timing of two kernel versions on one box).
+_LIB_PATH = Path(os.environ.get("DET_KERNELS_LIB") or Path(__file__).resolve().parent.parent / "_lib" / "libdet_kernels.so")
 
 c_void_p, c_int, c_ll, c_float, c_uint = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float, ctypes.c_uint
 
@@ -103,7 +104,12 @@ def load(build_if_missing: bool = True) -> ctypes.CDLL:
     lib.det_comm_flag_bytes.restype = c_ll
     lib.det_comm_epoch_bytes.restype = c_ll
     for name, sig in _SIGNATURES.items():
-        fn = getattr(lib, name)
+        try:
+            fn = getattr(lib, name)
+        except AttributeError:
+            if os.environ.get("DET_KERNELS_LIB"):
+                continue      # an older build loaded for comparison may lack newer entry points
+            raise
         fn.argtypes = sig
         fn.restype = c_int
     _LIB = lib
