@@ -271,7 +271,11 @@ extern "C" int det_fused_allreduce(void* const* peer_bufs, void* const* peer_fla
   const long long per4 = ((n_f32 >> 2) + world - 1) / world;
   const long long per_block = static_cast<long long>(AR_THREADS) * (mc_ptr != nullptr && world > 1 ? AR_UNROLL_MC : AR_UNROLL_P2P);
   int blocks = static_cast<int>(std::min<long long>((per4 + per_block - 1) / per_block, std::min(sm_count(), COMM_MAX_BLOCKS)));
-  if (max_blocks > 0) blocks = std::min(blocks, max_blocks);
+  // Measured (profiles/allreduce_vs_ctas_8gpu_r1.txt, overlap_sweep_2gpu_r1.txt): with 8 switch reductions in flight
+  // per thread the links saturate at 2-8 CTAs and MORE CTAs are slower (8 GPUs: 0.98 ms with 8 CTAs, 1.09 ms with 148;
+  // 2 GPUs: 1.15 vs 1.20 ms) — extra CTAs only add flag-barrier traffic. Default to 16.
+  if (max_blocks <= 0) max_blocks = 16;
+  blocks = std::min(blocks, max_blocks);
   blocks = std::max(blocks, 1);
   // Every rank must launch the same grid: blocks depends only on (n, world, SM count, max_blocks).
   if (mc_ptr != nullptr && world > 1) fused_allreduce_kernel<true><<<blocks, AR_THREADS, 0, stream>>>(a);
