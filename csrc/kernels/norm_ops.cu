@@ -353,6 +353,29 @@ gemm_small_kernel(const void* __restrict__ A, const void* __restrict__ B, void* 
   }
 }
 
+// Same contract for very short contractions (K <= 8, e.g. the input gradient of a two-logit head): a thread per output.
+__global__ void __launch_bounds__(256)
+gemm_smallk_kernel(const void* __restrict__ A, const void* __restrict__ B, void* __restrict__ C, int M, int N, int K,
+                   long long sam, long long sak, long long sbn, long long sbk, long long scm, long long scn, int a_f32,
+                   int b_f32, int c_f32, const float* bias, int act, float alpha, int accumulate) {
+  const long long o = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (o >= static_cast<long long>(M) * N) return;
+  const int m = static_cast<int>(o / N), n = static_cast<int>(o % N);
+  float acc = 0.0f;
+  for (int k = 0; k < K; ++k) acc += load_any(A, m * sam + k * sak, a_f32) * load_any(B, n * sbn + k * sbk, b_f32);
+  acc *= alpha;
+  if (bias != nullptr) acc += bias[n];
+  if (act == 1) acc = tanhf(acc);
+  const long long ci = m * scm + n * scn;
+  if (c_f32) {
+    float* c = reinterpret_cast<float*>(C);
+    c[ci] = accumulate ? c[ci] + acc : acc;
+  } else {
+    __nv_bfloat16* c = reinterpret_cast<__nv_bfloat16*>(C);
+    c[ci] = __float2bfloat16_rn(accumulate ? __bfloat162float(c[ci]) + acc : acc);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------
 // fp32 -> bf16 cast (shadow weights) and bf16 transposed copy helpers
 // ------------------------------------------------------------------------------------------------
@@ -388,6 +411,150 @@ static int launch_ln_bwd(const void* dy, const void* x, const float* g, const fl
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------------
+// LayerNorm for any width (H % 8 == 0; ALBERT's 128-wide embeddings, 4096-wide xxlarge layers): a warp per row,
+// lanes striding over 16-byte vectors, the row re-read from L1 for each pass. Same dropout semantics as above.
+// ------------------------------------------------------------------------------------------------
+constexpr int LNG_WARPS = 8;
+
+__global__ void __launch_bounds__(LNG_WARPS * 32)
+layernorm_fwd_generic_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma,
+                             const float* __restrict__ beta, __nv_bfloat16* __restrict__ y, float* __restrict__ mean,
+                             float* __restrict__ rstd, int T, int H, float eps, DropCfg drop) {
+  const int lane = threadIdx.x & 31;
+  const int nvec = H / 8;
+  const float inv_h = 1.0f / static_cast<float>(H);
+  const uint32_t dseed = eff_seed(drop);
+  for (int row = blockIdx.x * LNG_WARPS + (threadIdx.x >> 5); row < T; row += gridDim.x * LNG_WARPS) {
+    const uint4* xr = reinterpret_cast<const uint4*>(x + static_cast<long long>(row) * H);
+    float s = 0.0f;
+    for (int v = lane; v < nvec; v += 32) {
+      float f[8];
+      unpack8(xr[v], f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) s += f[e];
+    }
+    const float mu = warp_sum(s) * inv_h;
+    float ss = 0.0f;
+    for (int v = lane; v < nvec; v += 32) {
+      float f[8];
+      unpack8(xr[v], f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { const float d = f[e] - mu; ss += d * d; }
+    }
+    const float rs = rsqrtf(warp_sum(ss) * inv_h + eps);
+    if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
+    uint4* yr = reinterpret_cast<uint4*>(y + static_cast<long long>(row) * H);
+    for (int v = lane; v < nvec; v += 32) {
+      float f[8], o[8];
+      unpack8(xr[v], f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int col = v * 8 + e;
+        float t = (f[e] - mu) * rs * __ldg(gamma + col) + __ldg(beta + col);
+        if (drop.threshold != 0u)
+          t = dropout_keep(dseed, static_cast<uint32_t>(row) * H + col, drop.threshold) ? t * drop.scale : 0.0f;
+        o[e] = t;
+      }
+      yr[v] = pack8(o);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(LNG_WARPS * 32)
+layernorm_bwd_generic_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                             const float* __restrict__ gamma, const float* __restrict__ mean,
+                             const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx,
+                             __nv_bfloat16* __restrict__ dx_masked, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                             int T, int H, DropCfg drop_in, DropCfg drop_out) {
+  extern __shared__ float lng_red[];   // [2][H]: per-block dgamma / dbeta
+  float* sg = lng_red;
+  float* sb = lng_red + H;
+  for (int i = threadIdx.x; i < 2 * H; i += blockDim.x) lng_red[i] = 0.0f;
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int nvec = H / 8;
+  const float inv_h = 1.0f / static_cast<float>(H);
+  const uint32_t seed_in = eff_seed(drop_in), seed_out = eff_seed(drop_out);
+  for (int row = blockIdx.x * LNG_WARPS + (threadIdx.x >> 5); row < T; row += gridDim.x * LNG_WARPS) {
+    const long long off = static_cast<long long>(row) * H;
+    const uint4* xr = reinterpret_cast<const uint4*>(x + off);
+    const uint4* dr = reinterpret_cast<const uint4*>(dy + off);
+    const float mu = __ldg(mean + row), rs = __ldg(rstd + row);
+    float s1 = 0.0f, s2 = 0.0f;
+    for (int v = lane; v < nvec; v += 32) {
+      float xf[8], d[8];
+      unpack8(xr[v], xf);
+      unpack8(dr[v], d);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int col = v * 8 + e;
+        if (drop_in.threshold != 0u)
+          d[e] = dropout_keep(seed_in, static_cast<uint32_t>(row) * H + col, drop_in.threshold) ? d[e] * drop_in.scale : 0.0f;
+        const float xh = (xf[e] - mu) * rs;
+        atomicAdd(sg + col, d[e] * xh);
+        atomicAdd(sb + col, d[e]);
+        const float dgm = d[e] * __ldg(gamma + col);
+        s1 += dgm;
+        s2 += dgm * xh;
+      }
+    }
+    s1 = warp_sum(s1) * inv_h;
+    s2 = warp_sum(s2) * inv_h;
+    uint4* oxr = reinterpret_cast<uint4*>(dx + off);
+    uint4* omr = dx_masked ? reinterpret_cast<uint4*>(dx_masked + off) : nullptr;
+    for (int v = lane; v < nvec; v += 32) {
+      float xf[8], d[8], o[8];
+      unpack8(xr[v], xf);
+      unpack8(dr[v], d);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int col = v * 8 + e;
+        if (drop_in.threshold != 0u)
+          d[e] = dropout_keep(seed_in, static_cast<uint32_t>(row) * H + col, drop_in.threshold) ? d[e] * drop_in.scale : 0.0f;
+        const float xh = (xf[e] - mu) * rs;
+        o[e] = rs * (d[e] * __ldg(gamma + col) - s1 - xh * s2);
+      }
+      oxr[v] = pack8(o);
+      if (omr != nullptr) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+          if (drop_out.threshold != 0u)
+            o[e] = dropout_keep(seed_out, static_cast<uint32_t>(row) * H + v * 8 + e, drop_out.threshold) ? o[e] * drop_out.scale : 0.0f;
+        omr[v] = pack8(o);
+      }
+    }
+  }
+  __syncthreads();
+  for (int col = threadIdx.x; col < H; col += blockDim.x) {
+    if (dgamma != nullptr) atomicAdd(dgamma + col, sg[col]);
+    if (dbeta != nullptr) atomicAdd(dbeta + col, sb[col]);
+  }
+}
+
+static int launch_ln_fwd_generic(const void* x, const float* g, const float* b, void* y, float* mean, float* rstd, int T,
+                                 int H, float eps, DropCfg d, cudaStream_t st) {
+  const int blocks = min((T + LNG_WARPS - 1) / LNG_WARPS, sm_count() * 8);
+  layernorm_fwd_generic_kernel<<<blocks, LNG_WARPS * 32, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(x), g, b,
+                                                                 reinterpret_cast<__nv_bfloat16*>(y), mean, rstd, T, H, eps, d);
+  DET_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+static int launch_ln_bwd_generic(const void* dy, const void* x, const float* g, const float* mean, const float* rstd,
+                                 void* dx, void* dxm, float* dg, float* db, int T, int H, DropCfg din, DropCfg dout,
+                                 cudaStream_t st) {
+  const size_t smem = sizeof(float) * 2 * H;
+  DET_REQUIRE(smem <= 200 * 1024, "layernorm: hidden size too large");
+  if (smem > 48 * 1024)
+    DET_CHECK_CUDA(cudaFuncSetAttribute(layernorm_bwd_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
+  const int blocks = min((T + LNG_WARPS - 1) / LNG_WARPS, sm_count() * 2);
+  layernorm_bwd_generic_kernel<<<blocks, LNG_WARPS * 32, smem, st>>>(
+      reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(x), g, mean, rstd,
+      reinterpret_cast<__nv_bfloat16*>(dx), reinterpret_cast<__nv_bfloat16*>(dxm), dg, db, T, H, din, dout);
+  DET_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
 }  // namespace det
 
 #define DET_LN_DISPATCH(FN, ...)                                           \
@@ -398,14 +565,15 @@ static int launch_ln_bwd(const void* dy, const void* x, const float* g, const fl
     case 4: return det::FN<4>(__VA_ARGS__);                                \
     default: break;                                                        \
   }                                                                        \
-  det::set_last_error("layernorm: hidden size must be 256, 512, 768 or 1024"); \
+  det::set_last_error("layernorm: unexpected hidden size");               \
   return 2;
 
 extern "C" int det_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y,
                                  float* mean, float* rstd, int T, int H, float eps, float dropout_p,
                                  unsigned int seed, const unsigned int* seed_dev, cudaStream_t stream) {
-  DET_REQUIRE(H % 256 == 0, "layernorm hidden size must be a multiple of 256");
+  DET_REQUIRE(H >= 8 && H % 8 == 0, "layernorm hidden size must be a multiple of 8");
   det::DropCfg d = det::make_drop(dropout_p, seed, seed_dev);
+  if (H % 256 != 0 || H > 1024) return det::launch_ln_fwd_generic(x, gamma, beta, y, mean, rstd, T, H, eps, d, stream);
   DET_LN_DISPATCH(launch_ln_fwd, x, gamma, beta, y, mean, rstd, T, eps, d, stream)
 }
 
@@ -414,9 +582,11 @@ extern "C" int det_layernorm_bwd(const void* dy, const void* x, const float* gam
                                  float* dbeta, int T, int H, float in_dropout_p, unsigned int in_seed,
                                  float out_dropout_p, unsigned int out_seed,
                                  const unsigned int* seed_dev, cudaStream_t stream) {
-  DET_REQUIRE(H % 256 == 0, "layernorm hidden size must be a multiple of 256");
+  DET_REQUIRE(H >= 8 && H % 8 == 0, "layernorm hidden size must be a multiple of 8");
   det::DropCfg din = det::make_drop(in_dropout_p, in_seed, seed_dev);
   det::DropCfg dout = det::make_drop(out_dropout_p, out_seed, seed_dev);
+  if (H % 256 != 0 || H > 1024)
+    return det::launch_ln_bwd_generic(dy, x, gamma, mean, rstd, dx, dx_masked, dgamma, dbeta, T, H, din, dout, stream);
   DET_LN_DISPATCH(launch_ln_bwd, dy, x, gamma, mean, rstd, dx, dx_masked, dgamma, dbeta, T, din, dout, stream)
 }
 
@@ -476,6 +646,12 @@ extern "C" int det_gemm_small(const void* A, const void* B, void* C, int M, int 
                               int accumulate, cudaStream_t stream) {
   const long long outs = static_cast<long long>(M) * N;
   DET_REQUIRE(outs > 0 && outs < (1LL << 31), "gemm_small: bad output size");
+  if (K <= 8) {
+    det::gemm_smallk_kernel<<<static_cast<unsigned>((outs + 255) / 256), 256, 0, stream>>>(
+        A, B, C, M, N, K, sam, sak, sbn, sbk, scm, scn, a_f32, b_f32, c_f32, bias, act, alpha, accumulate);
+    DET_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
   det::gemm_small_kernel<<<static_cast<unsigned>((outs + 7) / 8), 256, 0, stream>>>(
       A, B, C, M, N, K, sam, sak, sbn, sbk, scm, scn, a_f32, b_f32, c_f32, bias, act, alpha, accumulate);
   DET_CHECK_CUDA(cudaGetLastError());

@@ -56,12 +56,12 @@ def _gelu(x: torch.Tensor) -> torch.Tensor:
 # ------------------------------------------------------------------------------------------------
 class _BertLayerFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, mask, layer: "BertLayer", B: int, S: int, training: bool):
+    def forward(ctx, x, mask, layer: "BertLayer", B: int, S: int, training: bool, seed_base: Optional[int] = None):
         c = layer.cfg
         T, Hd, I, NH = x.shape[0], c.hidden_size, c.intermediate_size, c.num_attention_heads
         p_h = c.hidden_dropout_prob if training else 0.0
         p_a = c.attention_probs_dropout_prob if training else 0.0
-        sd = layer.seed_base
+        sd = layer.seed_base if seed_base is None else seed_base   # a layer shared across depths draws a mask per depth
         dev = x.device
         bf = torch.bfloat16
         qkv = torch.empty(T, 3 * Hd, dtype=bf, device=dev)
@@ -79,7 +79,7 @@ class _BertLayerFn(torch.autograd.Function):
                dropout_p=p_h, seed=sd + 2)
         x2, mean2, rstd2 = F.layernorm_fwd(h2, layer.ln2_weight, layer.ln2_bias, c.layer_norm_eps)
         ctx.save_for_backward(x, qkv, lse, att, h1, mean1, rstd1, x1, z, a, h2, mean2, rstd2)
-        ctx.layer, ctx.mask, ctx.dims, ctx.drop = layer, mask, (B, S), (p_h, p_a)
+        ctx.layer, ctx.mask, ctx.dims, ctx.drop, ctx.sd = layer, mask, (B, S), (p_h, p_a), sd
         note_param_use(ctx, *layer.parameters())
         return x2
 
@@ -90,7 +90,7 @@ class _BertLayerFn(torch.autograd.Function):
         c = L.cfg
         B, S = ctx.dims
         p_h, p_a = ctx.drop
-        sd = L.seed_base
+        sd = ctx.sd
         T, Hd, I, NH = x.shape[0], c.hidden_size, c.intermediate_size, c.num_attention_heads
         dev, bf = x.device, torch.bfloat16
         dx2 = dx2.contiguous()
@@ -116,7 +116,7 @@ class _BertLayerFn(torch.autograd.Function):
         accumulate_bgrad(L.out_bias, dh1m)
         datt = torch.empty(T, Hd, dtype=bf, device=dev)
         F.gemm(dh1m, shadow_of(L.out_weight), datt, T, Hd, Hd, b_mn=True)
-        dqkv = F.attention_bwd(qkv, datt, ctx.mask, lse, B, S, NH, p_a, sd + 0)
+        dqkv = F.attention_bwd(qkv, datt, ctx.mask, lse, B, S, NH, p_a, sd + 0, att)
         accumulate_wgrad(L.qkv_weight, dqkv, x)
         accumulate_bgrad(L.qkv_bias, dqkv)
         dx = None
@@ -124,7 +124,7 @@ class _BertLayerFn(torch.autograd.Function):
             dx = torch.empty(T, Hd, dtype=bf, device=dev)
             F.gemm(dqkv, shadow_of(L.qkv_weight), dx, T, Hd, 3 * Hd, b_mn=True, epi=F.EPI_BIAS_RESID, aux_in=dh1)
         notify_grads_written(*L.parameters())   # this layer's slice of the gradient bucket is final: its all-reduce may start
-        return dx, None, None, None, None, None
+        return dx, None, None, None, None, None, None
 
 
 class BertLayer(nn.Module):
@@ -147,13 +147,9 @@ class BertLayer(nn.Module):
         self.ln2_weight = nn.Parameter(torch.ones(Hd))
         self.ln2_bias = nn.Parameter(torch.zeros(Hd))
 
-    def forward(self, x: torch.Tensor, mask: Optional[torch.Tensor], B: int, S: int) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, mask: Optional[torch.Tensor], B: int, S: int, seed_base: Optional[int] = None) -> torch.Tensor:
         if x.is_cuda:
-            if not torch.is_grad_enabled() or not x.requires_grad:
-                # the fused node wants a graph edge on x even for layer 0 whose input comes from the
-                # embedding node; eval / no-grad simply runs the forward kernels
-                pass
-            return _BertLayerFn.apply(x, mask, self, B, S, self.training)
+            return _BertLayerFn.apply(x, mask, self, B, S, self.training, seed_base)
         return self._reference_forward(x, mask, B, S)
 
     def _reference_forward(self, x, mask, B, S):
@@ -317,8 +313,6 @@ class BertForSequenceClassification(nn.Module):
     def forward(self, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None,
                 token_type_ids: Optional[torch.Tensor] = None, labels: Optional[torch.Tensor] = None) -> Tuple:
         B, S = input_ids.shape
-        if input_ids.is_cuda and S > 128:
-            raise ValueError("fused attention supports sequences of at most 128 tokens")
         mask = None
         if attention_mask is not None:
             mask = ((1.0 - attention_mask.to(torch.float32)) * -10000.0).contiguous()
@@ -337,3 +331,130 @@ class BertForSequenceClassification(nn.Module):
         per_tok = 2 * (4 * c.hidden_size * c.hidden_size + 2 * c.hidden_size * c.intermediate_size)
         attn = 4 * seq_len * c.hidden_size
         return 3.0 * c.num_hidden_layers * seq_len * (per_tok + attn)
+
+
+# ------------------------------------------------------------------------------------------------
+# Extractive question answering (SQuAD shape: seq 384) — BERT and ALBERT
+# ------------------------------------------------------------------------------------------------
+class _QAHeadFn(torch.autograd.Function):
+    """start/end logits = x W^T + b with W [2, hidden]: two output columns, so the CUDA-core strided GEMM."""
+
+    @staticmethod
+    def forward(ctx, x, head: "BertQAHead"):
+        T, Hd = x.shape
+        logits = torch.empty(T, 2, dtype=torch.float32, device=x.device)
+        F.gemm_small(x, head.weight, logits, T, 2, Hd, (Hd, 1), (Hd, 1), (2, 1), bias=head.bias)
+        ctx.save_for_backward(x)
+        ctx.head = head
+        note_param_use(ctx, head.weight, head.bias)
+        return logits
+
+    @staticmethod
+    def backward(ctx, dlogits):
+        (x,) = ctx.saved_tensors
+        head: BertQAHead = ctx.head
+        T, Hd = x.shape
+        dlogits = dlogits.float().contiguous()
+        F.gemm_small(dlogits, x, grad_buffer(head.weight), 2, Hd, T, (1, 2), (1, Hd), (Hd, 1), accumulate=True)
+        grad_buffer(head.bias).add_(dlogits.sum(0))
+        dx = torch.empty(T, Hd, dtype=torch.bfloat16, device=x.device)
+        F.gemm_small(dlogits, head.weight, dx, T, Hd, 2, (2, 1), (1, Hd), (Hd, 1))
+        notify_grads_written(head.weight, head.bias)
+        return dx, None
+
+
+class BertQAHead(nn.Module):
+    def __init__(self, hidden_size: int, std: float) -> None:
+        super().__init__()
+        self.weight = nn.Parameter(torch.randn(2, hidden_size) * std)
+        self.bias = nn.Parameter(torch.zeros(2))
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if x.is_cuda:
+            return _QAHeadFn.apply(x, self)
+        return x.float() @ self.weight.t() + self.bias
+
+
+def _qa_outputs(logits: torch.Tensor, B: int, S: int, start_positions, end_positions) -> Tuple:
+    """[B*S, 2] logits → HF's (loss?, start_logits, end_logits); loss = (CE(start) + CE(end)) / 2, positions clamped
+    into the sequence like HF's ``ignored_index`` handling of out-of-span answers."""
+    lg = logits.view(B, S, 2)
+    start_logits, end_logits = lg[..., 0], lg[..., 1]
+    if start_positions is None or end_positions is None:
+        return start_logits, end_logits
+    from ..ops.modules import cross_entropy
+
+    both = lg.transpose(1, 2).reshape(2 * B, S)                       # row 2b = start logits of b, row 2b+1 = end logits
+    labels = torch.stack([start_positions.reshape(-1), end_positions.reshape(-1)], dim=1).reshape(-1).clamp(0, S - 1)
+    return cross_entropy(both, labels), start_logits, end_logits
+
+
+class BertForQuestionAnswering(nn.Module):
+    """HF ``BertForQuestionAnswering`` calling convention (reference: ``examples/nlp/bert_squad_pytorch/model_def.py``):
+    ``forward(input_ids, attention_mask, token_type_ids, start_positions=None, end_positions=None)``. Sequences longer
+    than 128 tokens run the tiled attention kernels."""
+
+    def __init__(self, cfg: Optional[BertConfig] = None) -> None:
+        super().__init__()
+        self.cfg = cfg or BertConfig()
+        if self.cfg.hidden_size != self.cfg.num_attention_heads * 64:
+            raise ValueError("the fused attention kernels are built for head_dim 64")
+        self.embeddings = BertEmbeddings(self.cfg)
+        self.layers = nn.ModuleList([BertLayer(self.cfg, i) for i in range(self.cfg.num_hidden_layers)])
+        self.qa_outputs = BertQAHead(self.cfg.hidden_size, self.cfg.initializer_range)
+
+    def forward(self, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None,
+                token_type_ids: Optional[torch.Tensor] = None, start_positions: Optional[torch.Tensor] = None,
+                end_positions: Optional[torch.Tensor] = None) -> Tuple:
+        B, S = input_ids.shape
+        mask = None
+        if attention_mask is not None:
+            mask = ((1.0 - attention_mask.to(torch.float32)) * -10000.0).contiguous()
+        x = self.embeddings(input_ids, token_type_ids, S)
+        for layer in self.layers:
+            x = layer(x, mask, B, S)
+        return _qa_outputs(self.qa_outputs(x), B, S, start_positions, end_positions)
+
+
+@dataclasses.dataclass
+class AlbertConfig(BertConfig):
+    """ALBERT: factorised embeddings (``embedding_size`` → ``hidden_size`` projection) and ONE encoder layer whose
+    parameters are shared by every depth (reference: ``examples/nlp/albert_squad_pytorch``, HF ``AlbertModel``).
+    Defaults are albert-base-v2; xxlarge is hidden 4096 / 64 heads / intermediate 16384."""
+    vocab_size: int = 30000
+    embedding_size: int = 128
+    hidden_dropout_prob: float = 0.0
+    attention_probs_dropout_prob: float = 0.0
+
+
+class AlbertForQuestionAnswering(nn.Module):
+    """Shared-layer encoder + span head. The layer is the BERT layer of this module (post-LN, erf-GELU; HF ALBERT uses
+    the tanh GELU approximation, which differs by < 1e-3 per activation). Gradients of the shared parameters accumulate
+    across depths in the flat fp32 bucket exactly like ``aggregation_frequency`` micro-batches do."""
+
+    def __init__(self, cfg: Optional[AlbertConfig] = None) -> None:
+        super().__init__()
+        from ..ops.modules import Linear
+
+        self.cfg = cfg or AlbertConfig()
+        c = self.cfg
+        if c.hidden_size != c.num_attention_heads * 64:
+            raise ValueError("the fused attention kernels are built for head_dim 64")
+        self.embeddings = BertEmbeddings(dataclasses.replace(c, hidden_size=c.embedding_size))
+        self.embedding_hidden_mapping_in = Linear(c.embedding_size, c.hidden_size)
+        self.shared_layer = BertLayer(c, 0)
+        self.qa_outputs = BertQAHead(c.hidden_size, c.initializer_range)
+
+    def forward(self, input_ids: torch.Tensor, attention_mask: Optional[torch.Tensor] = None,
+                token_type_ids: Optional[torch.Tensor] = None, start_positions: Optional[torch.Tensor] = None,
+                end_positions: Optional[torch.Tensor] = None) -> Tuple:
+        B, S = input_ids.shape
+        mask = None
+        if attention_mask is not None:
+            mask = ((1.0 - attention_mask.to(torch.float32)) * -10000.0).contiguous()
+        x = self.embedding_hidden_mapping_in(self.embeddings(input_ids, token_type_ids, S))
+        if x.is_cuda and x.dtype != torch.bfloat16:
+            x = x.to(torch.bfloat16)
+        for depth in range(self.cfg.num_hidden_layers):
+            x = self.shared_layer(x, mask, B, S, seed_base=0x1000 + 16 * depth)
+        return _qa_outputs(self.qa_outputs(x), B, S, start_positions, end_positions)

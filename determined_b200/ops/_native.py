@@ -22,6 +22,9 @@ _SIGNATURES = {
                       c_float, c_void_p, c_void_p, c_void_p, c_ll, c_float, c_uint, c_void_p, c_int, c_int, c_void_p],
     "det_attention_fwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_uint, c_void_p, c_void_p],
     "det_attention_bwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_uint, c_void_p, c_void_p],
+    "det_attention_flash_fwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_uint, c_void_p, c_void_p],
+    "det_attention_flash_bwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
+                                c_float, c_uint, c_void_p, c_void_p],
     "det_layernorm_fwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_uint, c_void_p, c_void_p],
     "det_layernorm_bwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                           c_int, c_int, c_float, c_uint, c_float, c_uint, c_void_p, c_void_p],

@@ -116,20 +116,34 @@ def gemm_small(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, M: int, N: i
 # ------------------------------------------------------------------------------------------------
 # Attention / LayerNorm / misc
 # ------------------------------------------------------------------------------------------------
+ATTENTION_SINGLE_TILE = 128   # sequences up to this length take the one-CTA-per-head kernel, longer ones the tiled one
+
+
 def attention_fwd(qkv: torch.Tensor, mask: Optional[torch.Tensor], B: int, S: int, H: int, dropout_p: float,
                   seed: int) -> Tuple[torch.Tensor, torch.Tensor]:
     ctx = torch.empty(B * S, H * 64, dtype=torch.bfloat16, device=qkv.device)
     lse = torch.empty(B, H, S, dtype=torch.float32, device=qkv.device)
-    _native.call("det_attention_fwd", _p(qkv), _p(mask), _p(ctx), _p(lse), B, S, H, float(dropout_p),
+    name = "det_attention_fwd" if S <= ATTENTION_SINGLE_TILE else "det_attention_flash_fwd"
+    _native.call(name, _p(qkv), _p(mask), _p(ctx), _p(lse), B, S, H, float(dropout_p),
                  int(seed) & 0xFFFFFFFF, _p(step_seed_tensor(qkv.device)) if dropout_p > 0 else None, _stream())
     return ctx, lse
 
 
 def attention_bwd(qkv: torch.Tensor, dctx: torch.Tensor, mask: Optional[torch.Tensor], lse: torch.Tensor, B: int,
-                  S: int, H: int, dropout_p: float, seed: int) -> torch.Tensor:
+                  S: int, H: int, dropout_p: float, seed: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``out`` is the forward output; the tiled kernel (S > 128) needs it for delta = rowsum(dO * O)."""
     dqkv = torch.empty_like(qkv)
-    _native.call("det_attention_bwd", _p(qkv), _p(dctx), _p(mask), _p(lse), _p(dqkv), B, S, H, float(dropout_p),
-                 int(seed) & 0xFFFFFFFF, _p(step_seed_tensor(qkv.device)) if dropout_p > 0 else None, _stream())
+    seed_dev = _p(step_seed_tensor(qkv.device)) if dropout_p > 0 else None
+    if S <= ATTENTION_SINGLE_TILE:
+        _native.call("det_attention_bwd", _p(qkv), _p(dctx), _p(mask), _p(lse), _p(dqkv), B, S, H, float(dropout_p),
+                     int(seed) & 0xFFFFFFFF, seed_dev, _stream())
+        return dqkv
+    if out is None:
+        raise ValueError("attention_bwd for sequences longer than 128 needs the forward output")
+    dq_accum = torch.empty(B * S, H * 64, dtype=torch.float32, device=qkv.device)
+    delta = torch.empty(B, H, S, dtype=torch.float32, device=qkv.device)
+    _native.call("det_attention_flash_bwd", _p(qkv), _p(dctx), _p(out), _p(mask), _p(lse), _p(dqkv), _p(dq_accum), _p(delta),
+                 B, S, H, float(dropout_p), int(seed) & 0xFFFFFFFF, seed_dev, _stream())
     return dqkv
 
 

@@ -213,12 +213,13 @@ class _LayerNormFn(torch.autograd.Function):
 
 
 class LayerNorm(nn.LayerNorm):
-    """``nn.LayerNorm`` over the last dimension; CUDA path = one-warp-per-row kernels (hidden size a
-    multiple of 256, up to 1024), gamma/beta gradients accumulated with fp32 atomics."""
+    """``nn.LayerNorm`` over the last dimension; CUDA path = one-warp-per-row kernels (register-resident
+    rows for hidden sizes 256/512/768/1024, a strided variant for any other multiple of 8), gamma/beta gradients
+    accumulated with fp32 atomics."""
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         H = x.shape[-1]
-        if not (_use_native(x) and H % 256 == 0 and H <= 1024 and self.elementwise_affine):
+        if not (_use_native(x) and H % 8 == 0 and H <= 16384 and self.elementwise_affine):
             return super().forward(x)
         lead = x.shape[:-1]
         x2 = x.reshape(-1, H).to(torch.bfloat16).contiguous()
@@ -257,21 +258,26 @@ class _AttentionFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, qkv, mask, B, S, H, p, seed):
         out, lse = F.attention_fwd(qkv, mask, B, S, H, p, seed)
-        ctx.save_for_backward(qkv, lse)
+        if S > F.ATTENTION_SINGLE_TILE:
+            ctx.save_for_backward(qkv, lse, out)      # the tiled backward needs delta = rowsum(dO * O)
+        else:
+            ctx.save_for_backward(qkv, lse)
         ctx.mask, ctx.dims, ctx.p, ctx.seed = mask, (B, S, H), p, seed
         return out
 
     @staticmethod
     def backward(ctx, dctx):
-        qkv, lse = ctx.saved_tensors
+        qkv, lse = ctx.saved_tensors[:2]
+        out = ctx.saved_tensors[2] if len(ctx.saved_tensors) > 2 else None
         B, S, H = ctx.dims
-        dqkv = F.attention_bwd(qkv, dctx.contiguous(), ctx.mask, lse, B, S, H, ctx.p, ctx.seed)
+        dqkv = F.attention_bwd(qkv, dctx.contiguous(), ctx.mask, lse, B, S, H, ctx.p, ctx.seed, out)
         return dqkv, None, None, None, None, None, None
 
 
 def fused_self_attention(qkv: torch.Tensor, mask: Optional[torch.Tensor], B: int, S: int, H: int,
                          dropout_p: float = 0.0, seed: int = 0) -> torch.Tensor:
-    """softmax(QK^T/8 + mask) V for packed ``qkv`` [B*S, 3*H*64] bf16 → [B*S, H*64]; S ≤ 128."""
+    """softmax(QK^T/8 + mask) V for packed ``qkv`` [B*S, 3*H*64] bf16 → [B*S, H*64] (one CTA per head up to
+    128 tokens, the tiled online-softmax kernel beyond)."""
     return _AttentionFn.apply(qkv, mask, B, S, H, dropout_p, seed)
 
 

@@ -43,6 +43,14 @@ int det_attention_bwd(const void* qkv, const void* dctx, const float* mask, cons
                       int S, int H, float dropout_p, unsigned int seed, const unsigned int* seed_dev,
                       cudaStream_t stream);
 
+/* ---- tiled (online-softmax) self-attention, any sequence length, head_dim 64; same tensors as above.
+ *      bwd also takes the forward output `ctx`, an fp32 scratch dq_accum[B*S, H*64] and an fp32 scratch delta[B, H, S]. */
+int det_attention_flash_fwd(const void* qkv, const float* mask, void* ctx, float* lse, int B, int S, int H,
+                            float dropout_p, unsigned int seed, const unsigned int* seed_dev, cudaStream_t stream);
+int det_attention_flash_bwd(const void* qkv, const void* dctx, const void* ctx, const float* mask, const float* lse,
+                            void* dqkv, float* dq_accum, float* delta, int B, int S, int H, float dropout_p,
+                            unsigned int seed, const unsigned int* seed_dev, cudaStream_t stream);
+
 /* ---- LayerNorm / reductions / embeddings / loss (reference: torch.nn.LayerNorm, Embedding, CrossEntropyLoss) */
 int det_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
                       int T, int H, float eps, float dropout_p, unsigned int seed, const unsigned int* seed_dev,

@@ -24,6 +24,7 @@ from bench import ClockSampler, _barrier_sync, _dist_env, _max_over_ranks  # noq
 from determined_b200 import _execution, load  # noqa: E402
 from determined_b200 import pytorch as dp  # noqa: E402
 from determined_b200 import workload as wl  # noqa: E402
+from determined_b200.models import squad_trials as ST
 from determined_b200.models import vision_trials as VT  # noqa: E402
 from determined_b200.ops import _native  # noqa: E402
 
@@ -65,6 +66,11 @@ MODELS = {
     "dcgan": (VT.DCGANTrial, {"latent_dim": 128, "use_cuda_graphs": True}, (3, 64, 64), "images/s"),
     "cifar": (VT.CIFARTrial, {"learning_rate": 1e-4}, (3, 32, 32), "images/s"),
     "mnist": (VT.MNistTrial, {"learning_rate": 1.0}, (1, 28, 28), "images/s"),
+    # BERT-base span model at the SQuAD shape (seq 384): the tiled attention kernels + span head
+    "bert_squad": (ST.BertSquadTrial, {"learning_rate": 3e-5, "max_seq_length": 384, "use_cuda_graphs": True}, (1, 1, 384), "samples/s"),
+    # ALBERT-xxlarge sizes (hidden 4096, 64 heads, one shared layer applied 12 times)
+    "albert_xxlarge_squad": (ST.AlbertSquadTrial, {"learning_rate": 5e-5, "max_seq_length": 384, "hidden_size": 4096,
+                                                   "num_attention_heads": 64, "intermediate_size": 16384}, (1, 1, 384), "samples/s"),
 }
 
 
@@ -146,7 +152,8 @@ def main() -> None:
            "dtype": "bf16" if (args.impl == "ours" or args.amp) else "fp32", "data": "synthetic", "impl": args.impl,
            "config": {"model": args.model, "global_batch": per_step, "per_slot_batch": args.batch, "parallelism": f"dp{world}",
                       "cuda_graphs": bool(getattr(controller, "_graphed", None))},
-           "e2e": {"h2d_bytes_per_step": args.batch * (n_in * (1 if args.model == "resnet50" else 4) + 8), "d2h_bytes_per_step": 4},
+           "e2e": {"h2d_bytes_per_step": args.batch * (3 * 384 * 8 + 16 if "squad" in args.model else n_in * (1 if args.model == "resnet50" else 4) + 8),
+                   "d2h_bytes_per_step": 4},
            "gpu_launches": int(timing["launches"]), "clocks": clocks,
            "first_loss": timing["losses"][0] if timing["losses"] else None,
            "final_loss": timing["losses"][-1] if timing["losses"] else None}
