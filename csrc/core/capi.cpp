@@ -10,6 +10,7 @@
 #include "lttb.hpp"
 #include "model.hpp"
 #include "nprand.hpp"
+#include "kubernetes.hpp"
 #include "provisioner.hpp"
 #include "scheduler.hpp"
 #include "searcher.hpp"
@@ -265,6 +266,24 @@ char* det_core_lttb(const char* in) {
       out.push_back(q);
     }
     return out;
+  });
+}
+// in: {"container": {container_id, task_id, description, argv, env, cwd, devices:[{id,type,...}]}, "config": {kubernetes RM config},
+//      "cluster_id": s, "node": s, "host_network": b} -> the pod manifest the Kubernetes back-end would POST
+char* det_core_pod_spec(const char* in) {
+  return guarded([&] {
+    Json j = Json::parse(in);
+    const Json& c = j["container"];
+    ContainerSpec spec;
+    spec.container_id = c["container_id"].str_or("");
+    spec.task_id = c["task_id"].str_or(spec.container_id);
+    spec.description = c["description"].str_or("");
+    spec.cwd = c["cwd"].str_or("");
+    if (c["argv"].is_array()) for (auto& a : c["argv"].arr()) spec.argv.push_back(a.as_string());
+    if (c["env"].is_object()) for (auto& kv : c["env"].obj()) spec.env[kv.first] = kv.second.as_string();
+    if (c["devices"].is_array())
+      for (auto& d : c["devices"].arr()) spec.devices.push_back(Device{static_cast<int>(d["id"].as_int()), d["brand"].str_or(""), d["uuid"].str_or(""), d["type"].str_or("gpu")});
+    return make_pod_spec(spec, KubeConfig::from_json(j["config"]), j["cluster_id"].str_or("cluster"), j["node"].str_or(""), j["host_network"].as_bool(false));
   });
 }
 unsigned long long det_core_md5_low64(const char* s) { return md5_low64(s); }

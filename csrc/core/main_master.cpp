@@ -51,6 +51,7 @@ int main(int argc, char** argv) {
       else if (a == "--python") j["python"] = next();
       else if (a == "--slot-type") j["slot_type"] = next();
       else if (a == "--provisioner") j["provisioner"] = det::Json::parse(next());   // JSON object, see docs/cluster-config.md
+      else if (a == "--resource-manager") j["resource_manager"] = det::Json::parse(next());   // {"type": "kubernetes", ...}
       else if (a == "--visible-gpus") j["visible_gpus"] = next();
       else if (a == "--auth-required") j["auth_required"] = true;
       else if (a == "--print-port-file") port_file = next();

@@ -47,7 +47,7 @@ std::string md5_hex(const std::string& s) {
 MasterConfig MasterConfig::from_json(const Json& j) {
   static const std::set<std::string> known = {"host", "port", "data_dir", "scheduler", "fitting_policy", "preemption", "checkpoint_storage",
                                               "python", "repo_root", "slot_type", "visible_gpus", "artificial_slots", "auth_required",
-                                              "cluster_name", "scheduler_tick_ms", "terminate_timeout_ms", "resource_pools", "db", "telemetry", "provisioner",
+                                              "cluster_name", "scheduler_tick_ms", "terminate_timeout_ms", "resource_pools", "db", "telemetry", "provisioner", "resource_manager",
                                               "security", "task_container_defaults"};
   MasterConfig c;
   for (auto& kv : j.obj())
@@ -73,6 +73,11 @@ MasterConfig MasterConfig::from_json(const Json& j) {
   c.auth_required = j["auth_required"].as_bool(false) || j["security"]["auth_required"].as_bool(false);
   c.cluster_name = j["cluster_name"].str_or(c.cluster_name);
   c.provisioner = j["provisioner"];
+  c.resource_manager = j["resource_manager"];
+  if (c.resource_manager.is_object()) {
+    const std::string t = c.resource_manager["type"].str_or("agent");
+    if (t != "agent" && t != "kubernetes") throw ConfigError("resource_manager.type must be agent or kubernetes");
+  }
   c.scheduler_tick_ms = static_cast<int>(j["scheduler_tick_ms"].as_int(c.scheduler_tick_ms));
   c.terminate_timeout_ms = static_cast<int>(j["terminate_timeout_ms"].as_int(c.terminate_timeout_ms));
   if (c.scheduler != "fair_share" && c.scheduler != "priority" && c.scheduler != "round_robin") throw ConfigError("scheduler must be fair_share, priority or round_robin");
@@ -83,7 +88,7 @@ Json MasterConfig::to_json() const {
   return obj({{"host", host}, {"port", port}, {"data_dir", data_dir}, {"scheduler", scheduler}, {"fitting_policy", fitting_policy},
               {"preemption", preemption}, {"checkpoint_storage", checkpoint_storage}, {"python", python}, {"repo_root", repo_root},
               {"slot_type", slot_type}, {"artificial_slots", artificial_slots}, {"auth_required", auth_required},
-              {"cluster_name", cluster_name}, {"scheduler_tick_ms", scheduler_tick_ms}});
+              {"cluster_name", cluster_name}, {"scheduler_tick_ms", scheduler_tick_ms}, {"resource_manager", resource_manager}});
 }
 
 // ---- command tasks (generic commands, notebooks, shells, tensorboards) ---------------------------------------------
@@ -173,6 +178,12 @@ void Master::unregister_container(const std::string& cid) {
 }
 void Master::start_container(const std::string& agent_id, const ContainerSpec& spec) {
   if (agent_id == "agent-local") { containers->start(spec); return; }
+  if (kube && KubernetesPods::owns(agent_id)) {
+    // multi-container trials talk NCCL / rendezvous between nodes: give those pods the host network (reference task.go:286-289)
+    const auto it = spec.env.find("DET_NUM_CONTAINERS");
+    kube->create(agent_id, spec, it != spec.env.end() && atoi(it->second.c_str()) > 1);
+    return;
+  }
   Json j = obj({{"type", "start"}, {"container_id", spec.container_id}, {"task_id", spec.task_id}, {"description", spec.description},
                 {"cwd", spec.cwd}});
   Json argv = Json::array();
@@ -190,6 +201,7 @@ void Master::start_container(const std::string& agent_id, const ContainerSpec& s
   agent_cmd_cv_.notify_all();
 }
 void Master::signal_container(const std::string& container_id, int sig) {
+  if (kube && kube->has_container(container_id)) { kube->remove(container_id, sig == SIGKILL); return; }
   {
     std::lock_guard<std::mutex> g(agent_cmd_mu_);
     auto it = container_agent_.find(container_id);
@@ -351,22 +363,40 @@ int Master::start() {
   commands_root = system.actor_of("commands", make_root());
   rm = system.actor_of("rm", make_resource_pool(this));
   logger = system.actor_of("trial_logger", make_trial_logger(this));
-  devices = detect_devices(cfg.slot_type, cfg.visible_gpus, cfg.artificial_slots);
-  Json devs = Json::array();
-  for (auto& d : devices) devs.push_back(d.to_json());
-  system.ask(rm, "add_agent", obj({{"id", "agent-local"}, {"label", ""}, {"devices", devs}, {"registered_time", now_rfc3339()},
-                                   {"addresses", Json(Json::array_t{Json("127.0.0.1")})}, {"driver_version", nvidia_driver_version()}}));
+  const bool k8s = cfg.resource_manager.is_object() && cfg.resource_manager["type"].str_or("agent") == "kubernetes";
+  if (k8s) {
+    // Pods replace agents: every schedulable node with allocatable slot resources joins the pool as "k8s-<node>".
+    const KubeConfig kc = KubeConfig::from_json(cfg.resource_manager);
+    kube.reset(new KubernetesPods(
+        kc, cluster_id, [this](const ContainerEvent& ev) { route_container_event(ev); }, [this](const LogLine& l) { route_log(l); },
+        [this, kc](const std::string& node, int slots, bool present) {
+          const std::string id = "k8s-" + node;
+          if (!present) { system.tell(rm, "remove_agent", obj({{"id", id}})); return; }
+          Json devs = Json::array();
+          for (int i = 0; i < slots; ++i) devs.push_back(Device{i, kc.slot_resource, node + "-" + std::to_string(i), "gpu"}.to_json());
+          system.tell(rm, "add_agent", obj({{"id", id}, {"label", ""}, {"devices", devs}, {"registered_time", now_rfc3339()},
+                                            {"addresses", Json(Json::array_t{Json(node)})}, {"driver_version", "kubernetes"}}));
+        }));
+  } else {
+    devices = detect_devices(cfg.slot_type, cfg.visible_gpus, cfg.artificial_slots);
+    Json devs = Json::array();
+    for (auto& d : devices) devs.push_back(d.to_json());
+    system.ask(rm, "add_agent", obj({{"id", "agent-local"}, {"label", ""}, {"devices", devs}, {"registered_time", now_rfc3339()},
+                                     {"addresses", Json(Json::array_t{Json("127.0.0.1")})}, {"driver_version", nvidia_driver_version()}}));
+  }
   register_routes();
   const int port = http.listen(cfg.host, cfg.port);
   if (port >= 0 && cfg.provisioner.is_object()) provisioner = system.actor_of("provisioner", make_provisioner(this, cfg.provisioner));
   if (port < 0) throw std::runtime_error("cannot bind " + cfg.host + ":" + std::to_string(cfg.port));
   log("info", "master listening on " + cfg.host + ":" + std::to_string(port) + " with " + std::to_string(devices.size()) + " local slots (" + cfg.scheduler + ")");
+  if (kube) kube->start();
   restore_experiments();
   return port;
 }
 void Master::run_forever() { http.serve_forever(); }
 void Master::stop() {
   http.stop();
+  if (kube) kube->stop();
   if (containers) containers->kill_all();
   system.shutdown();
 }

@@ -17,6 +17,7 @@
 #include "agent.hpp"
 #include "http.hpp"
 #include "json.hpp"
+#include "kubernetes.hpp"
 #include "model.hpp"
 #include "provisioner.hpp"
 #include "rw_coordinator.hpp"
@@ -43,6 +44,7 @@ struct MasterConfig {
   bool auth_required = false;
   std::string cluster_name = "b200-box";
   Json provisioner;                      // {max_instances, slots_per_instance, max_idle_agent_period, ...} or null
+  Json resource_manager;                 // null / {type: agent} or {type: kubernetes, namespace, api_server, image, ...}
   int scheduler_tick_ms = 500;
   int terminate_timeout_ms = 60000;
 
@@ -67,6 +69,7 @@ class Master {
   ActorSystem system;
   HttpServer http;
   std::unique_ptr<ContainerManager> containers;
+  std::unique_ptr<KubernetesPods> kube;  // set when resource_manager.type == kubernetes
   std::vector<Device> devices;
   ActorRef rm, logger, experiments_root, commands_root, provisioner;
   RWCoordinator rw;

@@ -97,6 +97,11 @@ void Master::register_routes() {
     s["enabled"] = true;
     return ok(s);
   });
+  // ---- Kubernetes back-end: pods owned by this master (reference: master/internal/kubernetes/pods.go summaries) ----
+  http.route("GET", "/api/v1/kubernetes/pods", [m](const HttpRequest&) {
+    if (!m->kube) return ok(obj({{"enabled", false}}));
+    return ok(obj({{"enabled", true}, {"pods", m->kube->summary()}}));
+  });
   // ---- provisioner decision preview (reference: provisioner scale decider; providers are out of scope offline) ----
   http.route("POST", "/api/v1/provisioner/decide", [](const HttpRequest& r) {
     Json b = r.json();

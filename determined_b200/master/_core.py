@@ -49,7 +49,7 @@ def load() -> ctypes.CDLL:
         "det_core_sequencer_complete_cached_checkpoints": ([vp], vp), "det_core_sequencer_preclose_checkpoint": ([vp], vp),
         "det_core_sequencer_terminate_workload": ([vp], vp), "det_core_sequencer_roll_back": ([vp], ci),
         "det_core_sequencer_state": ([vp], vp),
-        "det_core_schedule": ([cp], vp), "det_core_lttb": ([cp], vp), "det_core_scale_decide": ([cp], vp), "det_core_md5_low64": ([cp], ctypes.c_ulonglong),
+        "det_core_schedule": ([cp], vp), "det_core_lttb": ([cp], vp), "det_core_scale_decide": ([cp], vp), "det_core_pod_spec": ([cp], vp), "det_core_md5_low64": ([cp], ctypes.c_ulonglong),
     }
     for name, (args, res) in sigs.items():
         fn = getattr(lib, name)
@@ -234,6 +234,12 @@ def schedule(request: Dict[str, Any]) -> Dict[str, Any]:
 def scale_decide(config: Dict[str, Any], snapshot: Dict[str, Any]) -> Dict[str, Any]:
     """Provisioner decision for one snapshot: ``{"launch": n, "terminate": [ids], "reasons": {...}}``."""
     return _take_json(load().det_core_scale_decide(_enc({"config": config, "snapshot": snapshot})))
+
+
+def pod_spec(container: Dict[str, Any], config: Dict[str, Any], cluster_id: str = "cluster", node: str = "", host_network: bool = False) -> Dict[str, Any]:
+    """The pod manifest the Kubernetes back-end creates for one task container (reference: master/internal/kubernetes/spec.go)."""
+    return _take_json(load().det_core_pod_spec(_enc({"container": container, "config": config, "cluster_id": cluster_id, "node": node,
+                                                     "host_network": host_network})))
 
 
 def lttb(points: List[List[float]], threshold: int) -> List[List[float]]:
