@@ -10,6 +10,7 @@
 #include "lttb.hpp"
 #include "model.hpp"
 #include "nprand.hpp"
+#include "cloud_providers.hpp"
 #include "kubernetes.hpp"
 #include "provisioner.hpp"
 #include "scheduler.hpp"
@@ -284,6 +285,37 @@ char* det_core_pod_spec(const char* in) {
     if (c["devices"].is_array())
       for (auto& d : c["devices"].arr()) spec.devices.push_back(Device{static_cast<int>(d["id"].as_int()), d["brand"].str_or(""), d["uuid"].str_or(""), d["type"].str_or("gpu")});
     return make_pod_spec(spec, KubeConfig::from_json(j["config"]), j["cluster_id"].str_or("cluster"), j["node"].str_or(""), j["host_network"].as_bool(false));
+  });
+}
+// in: {"provider": {type: aws|gcp, ...}, "op": "launch"|"list"|"terminate", "count": n, "ids": [...], "names": [...],
+//      "cluster_id": s, "master_host": s, "master_port": n} -> {"argv": [...]} ; op "parse" + "output": <cli json> -> {"instances": [...]}
+char* det_core_cloud_command(const char* in) {
+  return guarded([&] {
+    Json j = Json::parse(in);
+    CloudProviderConfig c = cloud_config_from_json(j["provider"], j["cluster_id"].str_or("cluster"), j["master_host"].str_or("127.0.0.1"),
+                                                   static_cast<int>(j["master_port"].as_int(8080)), static_cast<int>(j["slots_per_instance"].as_int(8)));
+    const std::string op = j["op"].str_or("list");
+    std::vector<std::string> ids;
+    if (j["ids"].is_array()) for (auto& i : j["ids"].arr()) ids.push_back(i.as_string());
+    Json out = Json::object();
+    if (op == "parse") {
+      Json arr = Json::array();
+      for (auto& i : (c.type == "aws" ? aws_parse_list(j["output"]) : gcp_parse_list(j["output"]))) {
+        Json o = Json::object();
+        o["id"] = i.id; o["state"] = i.state;
+        arr.push_back(o);
+      }
+      out["instances"] = arr;
+      return out;
+    }
+    std::vector<std::string> argv;
+    if (c.type == "aws") argv = op == "launch" ? aws_launch_argv(c, static_cast<int>(j["count"].as_int(1))) : (op == "terminate" ? aws_terminate_argv(c, ids) : aws_list_argv(c));
+    else if (c.type == "gcp") argv = op == "launch" ? gcp_launch_argv(c, ids) : (op == "terminate" ? gcp_terminate_argv(c, ids) : gcp_list_argv(c));
+    else throw ConfigError("provider.type must be aws or gcp");
+    Json a = Json::array();
+    for (auto& s : argv) a.push_back(Json(s));
+    out["argv"] = a;
+    return out;
   });
 }
 unsigned long long det_core_md5_low64(const char* s) { return md5_low64(s); }

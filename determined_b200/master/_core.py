@@ -49,7 +49,7 @@ def load() -> ctypes.CDLL:
         "det_core_sequencer_complete_cached_checkpoints": ([vp], vp), "det_core_sequencer_preclose_checkpoint": ([vp], vp),
         "det_core_sequencer_terminate_workload": ([vp], vp), "det_core_sequencer_roll_back": ([vp], ci),
         "det_core_sequencer_state": ([vp], vp),
-        "det_core_schedule": ([cp], vp), "det_core_lttb": ([cp], vp), "det_core_scale_decide": ([cp], vp), "det_core_pod_spec": ([cp], vp), "det_core_md5_low64": ([cp], ctypes.c_ulonglong),
+        "det_core_schedule": ([cp], vp), "det_core_lttb": ([cp], vp), "det_core_scale_decide": ([cp], vp), "det_core_pod_spec": ([cp], vp), "det_core_cloud_command": ([cp], vp), "det_core_md5_low64": ([cp], ctypes.c_ulonglong),
     }
     for name, (args, res) in sigs.items():
         fn = getattr(lib, name)
@@ -240,6 +240,12 @@ def pod_spec(container: Dict[str, Any], config: Dict[str, Any], cluster_id: str 
     """The pod manifest the Kubernetes back-end creates for one task container (reference: master/internal/kubernetes/spec.go)."""
     return _take_json(load().det_core_pod_spec(_enc({"container": container, "config": config, "cluster_id": cluster_id, "node": node,
                                                      "host_network": host_network})))
+
+
+def cloud_command(provider: Dict[str, Any], op: str, **kw: Any) -> Dict[str, Any]:
+    """What the provisioner's AWS / GCP provider would run for ``op`` (launch | list | terminate) as ``{"argv": [...]}``, or with
+    ``op="parse", output=<CLI JSON>`` the instances it reads from a listing (reference: master/internal/provisioner/aws.go, gcp.go)."""
+    return _take_json(load().det_core_cloud_command(_enc(dict(kw, provider=provider, op=op))))
 
 
 def lttb(points: List[List[float]], threshold: int) -> List[List[float]]:
