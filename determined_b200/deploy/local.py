@@ -122,7 +122,7 @@ def status(name: str) -> dict:
 
 
 def main(argv: Optional[List[str]] = None) -> None:
-    ap = argparse.ArgumentParser(prog="det-deploy", description="bring a single-box determined_b200 cluster up or down")
+    ap = argparse.ArgumentParser(prog="det-deploy", description="bring a determined_b200 cluster up or down: local processes, AWS CloudFormation, GCP Terraform")
     sub = ap.add_subparsers(dest="flavour", required=True)
     local = sub.add_parser("local")
     lsub = local.add_subparsers(dest="verb", required=True)
@@ -138,11 +138,13 @@ def main(argv: Optional[List[str]] = None) -> None:
     st.add_argument("--cluster-name", default="determined")
     lg = lsub.add_parser("logs")
     lg.add_argument("--cluster-name", default="determined")
-    for flavour in ("aws", "gcp"):
-        sub.add_parser(flavour)
+    from . import cloud
+
+    cloud.add_parsers(sub)
     args = ap.parse_args(argv)
     if args.flavour != "local":
-        raise SystemExit(f"det-deploy {args.flavour}: cloud deployments are not available offline; use `det-deploy local`")
+        print(json.dumps(cloud.run(args), indent=1))
+        return
     if args.verb == "cluster-up":
         port = master_up(args.cluster_name, args.master_port, args.artificial_slots, args.scheduler)
         for i in range(args.agents):
