@@ -275,32 +275,55 @@ __global__ void flash_dq_convert_kernel(const float* __restrict__ acc, __nv_bflo
 
 // ------------------------------------------------------------------------------------------------
 // Backward: 512 threads = 4 lane quarters x 4 column groups (32 keys each); 1 CTA per SM; one CTA per key tile.
+//
+// Software pipeline over the query tiles (Q/dO in a 3-stage TMA ring). Per tile i:
+//   A  wait S_i, dP'_i (MMA1)        -> registers;            barrier: TMEM S/dP free
+//   B  issue MMA1 of tile i+1        (tensor pipe works while the CUDA cores do C)
+//   C  P'_i, dS_i in registers;  wait MMA2 of tile i-1;  refill the ring stage it freed;  dQ_{i-1} -> red.add;
+//      P'_i, dS_i -> smem;                                    barrier: smem operands visible
+//   D  issue MMA2 of tile i:  dV += P'^T dO,  dK += dS^T Q,  dQ_i = dS K
 // ------------------------------------------------------------------------------------------------
 constexpr int FA_BWD_THREADS = 512;
-constexpr uint32_t FA_BWD_SMEM = 8 * FA_TILE + 1024 + 64 + FA_T * 4;
+constexpr int FA_BWD_STAGES = 3;
+constexpr uint32_t FA_BWD_SMEM = (6 + 2 * FA_BWD_STAGES) * FA_TILE + 1024 + 64 + FA_T * 4;
+
+__device__ __forceinline__ void fa_dq_flush(const FlashParams& p, uint32_t tdQ, uint32_t lane_base, int cg, int row0, int h, int qg) {
+  float d[16];
+  ptx::tmem_ld_32x32b_x16(tdQ + lane_base + cg * 16, d);
+  ptx::tmem_ld_wait();
+  if (qg < p.S) {
+    float* dst = p.dq_accum + (static_cast<long long>(row0) + qg) * p.hidden + h * FA_D + cg * 16;
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 4 * u), "f"(d[4 * u]), "f"(d[4 * u + 1]),
+                   "f"(d[4 * u + 2]), "f"(d[4 * u + 3]) : "memory");
+  }
+}
 
 __global__ void __launch_bounds__(FA_BWD_THREADS, 1)
 flash_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_constant__ CUtensorMap tma_do,
                  const FlashParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sQ = smem;
-  uint8_t* sK = smem + FA_TILE;
-  uint8_t* sV = smem + 2 * FA_TILE;
-  uint8_t* sdO = smem + 3 * FA_TILE;
-  uint8_t* sP = smem + 4 * FA_TILE;    // 2 chunks
-  uint8_t* sdS = smem + 6 * FA_TILE;   // 2 chunks
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 8 * FA_TILE);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
-  float* smask = reinterpret_cast<float*>(smem + 8 * FA_TILE + 64);   // [128], this CTA's keys
+  uint8_t* sK = smem;
+  uint8_t* sV = smem + FA_TILE;
+  uint8_t* sP = smem + 2 * FA_TILE;    // 2 chunks
+  uint8_t* sdS = smem + 4 * FA_TILE;   // 2 chunks
+  uint8_t* sQ = smem + 6 * FA_TILE;    // FA_BWD_STAGES tiles
+  uint8_t* sdO = sQ + FA_BWD_STAGES * FA_TILE;
+  uint8_t* tail = sdO + FA_BWD_STAGES * FA_TILE;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tail);   // kv, mma1, mma2, q[STAGES]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3 + FA_BWD_STAGES);
+  float* smask = reinterpret_cast<float*>(tail + 64);   // [128], this CTA's keys
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int kt = blockIdx.x % p.nkv;
   const int bh = blockIdx.x / p.nkv;
   const int b = bh / p.H, h = bh % p.H;
   const uint32_t kv_bar = ptx::smem_u32(&bars[0]);
-  const uint32_t q_bar = ptx::smem_u32(&bars[1]);
-  const uint32_t mma_bar = ptx::smem_u32(&bars[2]);
+  const uint32_t bar1 = ptx::smem_u32(&bars[1]);
+  const uint32_t bar2 = ptx::smem_u32(&bars[2]);
+  const uint32_t q_bar0 = ptx::smem_u32(&bars[3]);
 
   if (tid < FA_T) {
     const int key = kt * FA_T + tid;
@@ -309,9 +332,7 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_const
   if (tid == 0) {
     ptx::tma_prefetch_desc(&tma_qkv);
     ptx::tma_prefetch_desc(&tma_do);
-    ptx::mbar_init(kv_bar, 1);
-    ptx::mbar_init(q_bar, 1);
-    ptx::mbar_init(mma_bar, 1);
+    for (int i = 0; i < 3 + FA_BWD_STAGES; ++i) ptx::mbar_init(ptx::smem_u32(&bars[i]), 1);
     ptx::fence_mbar_init();
   }
   if (warp == 0) ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 512);
@@ -322,13 +343,40 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_const
   const uint32_t tS = tmem, tdP = tmem + 128, tdV = tmem + 256, tdQ = tmem + 320, tdK = tmem + 384;
 
   const int row0 = b * p.S;
+  auto load_q = [&](int tile) {   // tid 0 only
+    const int st = tile % FA_BWD_STAGES;
+    const uint32_t qb = q_bar0 + 8 * st;
+    ptx::mbar_expect_tx(qb, 2 * FA_TILE);
+    ptx::tma_load_2d(ptx::smem_u32(sQ + st * FA_TILE), &tma_qkv, qb, h * FA_D, row0 + tile * FA_T);
+    ptx::tma_load_2d(ptx::smem_u32(sdO + st * FA_TILE), &tma_do, qb, h * FA_D, row0 + tile * FA_T);
+  };
+  auto issue_mma1 = [&](int tile) {   // tid 0 only: S = Q K^T, dP' = dO V^T
+    const int st = tile % FA_BWD_STAGES;
+    ptx::mbar_wait(q_bar0 + 8 * st, (tile / FA_BWD_STAGES) & 1);
+    ptx::tc_fence_after();
+    constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(128, 128, 0, 0);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint64_t ad = ptx::make_smem_desc_sw128(ptx::smem_u32(sQ + st * FA_TILE) + k * 32, 16, 1024);
+      const uint64_t bd = ptx::make_smem_desc_sw128(ptx::smem_u32(sK) + k * 32, 16, 1024);
+      ptx::umma_bf16_ss(tS, ad, bd, idesc, k > 0);
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const uint64_t ad = ptx::make_smem_desc_sw128(ptx::smem_u32(sdO + st * FA_TILE) + k * 32, 16, 1024);
+      const uint64_t bd = ptx::make_smem_desc_sw128(ptx::smem_u32(sV) + k * 32, 16, 1024);
+      ptx::umma_bf16_ss(tdP, ad, bd, idesc, k > 0);
+    }
+    ptx::umma_commit(bar1);
+  };
+
   if (tid == 0) {
     ptx::mbar_expect_tx(kv_bar, 2 * FA_TILE);
     ptx::tma_load_2d(ptx::smem_u32(sK), &tma_qkv, kv_bar, p.hidden + h * FA_D, row0 + kt * FA_T);
     ptx::tma_load_2d(ptx::smem_u32(sV), &tma_qkv, kv_bar, 2 * p.hidden + h * FA_D, row0 + kt * FA_T);
-    ptx::mbar_expect_tx(q_bar, 2 * FA_TILE);
-    ptx::tma_load_2d(ptx::smem_u32(sQ), &tma_qkv, q_bar, h * FA_D, row0);
-    ptx::tma_load_2d(ptx::smem_u32(sdO), &tma_do, q_bar, h * FA_D, row0);
+    for (int t = 0; t < FA_BWD_STAGES && t < p.nq; ++t) load_q(t);
+    ptx::mbar_wait(kv_bar, 0);
+    issue_mma1(0);
   }
 
   const int q = (warp & 3) * 32 + lane;
@@ -339,72 +387,72 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_const
   const long long stat_base = (static_cast<long long>(b) * p.H + h) * p.S;
 
   for (int i = 0; i < p.nq; ++i) {
-    if (tid == 0) {
-      if (i == 0) ptx::mbar_wait(kv_bar, 0);
-      ptx::mbar_wait(q_bar, i & 1);
-      ptx::tc_fence_after();
-      constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(128, 128, 0, 0);
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {   // S = Q K^T
-        const uint64_t ad = ptx::make_smem_desc_sw128(ptx::smem_u32(sQ) + k * 32, 16, 1024);
-        const uint64_t bd = ptx::make_smem_desc_sw128(ptx::smem_u32(sK) + k * 32, 16, 1024);
-        ptx::umma_bf16_ss(tS, ad, bd, idesc, k > 0);
-      }
-#pragma unroll
-      for (int k = 0; k < 4; ++k) {   // dP' = dO V^T
-        const uint64_t ad = ptx::make_smem_desc_sw128(ptx::smem_u32(sdO) + k * 32, 16, 1024);
-        const uint64_t bd = ptx::make_smem_desc_sw128(ptx::smem_u32(sV) + k * 32, 16, 1024);
-        ptx::umma_bf16_ss(tdP, ad, bd, idesc, k > 0);
-      }
-      ptx::umma_commit(mma_bar);
-    }
+    const int st = i % FA_BWD_STAGES;
     const int qg = i * FA_T + q;
     const bool q_ok = qg < p.S;
     const float lse2 = q_ok ? __ldg(p.lse + stat_base + qg) * FA_LOG2E : 0.0f;
     const float delta = q_ok ? __ldg(p.delta + stat_base + qg) : 0.0f;
     const uint32_t didx0 = ((static_cast<uint32_t>(b) * p.H + h) * p.S + qg) * p.S + kt * FA_T + cg * 32;
-    ptx::mbar_wait(mma_bar, 0);
-    ptx::tc_fence_after();
 
+    // ---- A: scores of tile i into registers ----
+    float pr[32], dp[32];
+    ptx::mbar_wait(bar1, i & 1);
+    ptx::tc_fence_after();
+    ptx::tmem_ld_32x32b_x32(tS + lane_base + cg * 32, pr);
+    ptx::tmem_ld_32x32b_x32(tdP + lane_base + cg * 32, dp);
+    ptx::tmem_ld_wait();
+    ptx::tc_fence_before();
+    __syncthreads();
+
+    // ---- B: the tensor pipe starts on tile i+1 while this tile's softmax math runs ----
+    if (tid == 0 && i + 1 < p.nq) issue_mma1(i + 1);
+
+    // ---- C: P' and dS (packed to bf16 right away to keep registers for the dQ read-out below) ----
+    uint4 pk_p[4], pk_s[4];
     {
-      float pr[32], dp[32];
-      ptx::tmem_ld_32x32b_x32(tS + lane_base + cg * 32, pr);
-      ptx::tmem_ld_32x32b_x32(tdP + lane_base + cg * 32, dp);
-      ptx::tmem_ld_wait();
-      float pd[32];
 #pragma unroll
       for (int e = 0; e < 32; ++e) {
         const float pv = q_ok ? exp2f(fmaf(pr[e], sc, smask[cg * 32 + e]) - lse2) : 0.0f;
         float keep = 1.0f;
         if (p.drop_threshold != 0u) keep = dropout_keep(dseed, didx0 + e, p.drop_threshold) ? p.drop_scale : 0.0f;
-        pd[e] = pv * keep;
-        pr[e] = pv * (dp[e] * keep - delta) * p.scale;   // dS
+        pr[e] = pv * keep;                                // P'
+        dp[e] = pv * (dp[e] * keep - delta) * p.scale;    // dS
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const uint32_t gu = cg * 4 + u;   // 16-byte unit 0..15 across the 128 keys
-        *reinterpret_cast<uint4*>(sP + (gu >> 3) * FA_TILE + ptx::sw128_offset(q, gu & 7)) = fa_pack8(pd + 8 * u);
-        *reinterpret_cast<uint4*>(sdS + (gu >> 3) * FA_TILE + ptx::sw128_offset(q, gu & 7)) = fa_pack8(pr + 8 * u);
-      }
+      for (int u = 0; u < 4; ++u) { pk_p[u] = fa_pack8(pr + 8 * u); pk_s[u] = fa_pack8(dp + 8 * u); }
+    }
+    if (i > 0) {
+      ptx::mbar_wait(bar2, (i - 1) & 1);   // MMA2 of tile i-1 done: sP / sdS / its ring stage are free, dQ_{i-1} is in TMEM
+      ptx::tc_fence_after();
+      if (tid == 0 && i + 2 < p.nq) load_q(i + 2);   // (i + 2) % 3 == (i - 1) % 3
+      fa_dq_flush(p, tdQ, lane_base, cg, row0, h, qg - FA_T);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const uint32_t gu = cg * 4 + u;   // 16-byte unit 0..15 across the 128 keys
+      *reinterpret_cast<uint4*>(sP + (gu >> 3) * FA_TILE + ptx::sw128_offset(q, gu & 7)) = pk_p[u];
+      *reinterpret_cast<uint4*>(sdS + (gu >> 3) * FA_TILE + ptx::sw128_offset(q, gu & 7)) = pk_s[u];
     }
     ptx::fence_proxy_async_smem();
     ptx::tc_fence_before();
     __syncthreads();
 
+    // ---- D: accumulate into dV, dK; fresh dQ tile ----
     if (tid == 0) {
       ptx::tc_fence_after();
       constexpr uint32_t idesc_tn = ptx::make_idesc_bf16_f32(128, 64, 1, 1);
       constexpr uint32_t idesc_nn = ptx::make_idesc_bf16_f32(128, 64, 0, 1);
+      const uint32_t q_s = ptx::smem_u32(sQ + st * FA_TILE), do_s = ptx::smem_u32(sdO + st * FA_TILE);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {   // dV[key, d] += sum_q P'[q, key] dO[q, d]
         const uint64_t ad = ptx::make_smem_desc_sw128(ptx::smem_u32(sP) + k * 2048, FA_TILE, 1024);
-        const uint64_t bd = ptx::make_smem_desc_sw128(ptx::smem_u32(sdO) + k * 2048, 8192, 1024);
+        const uint64_t bd = ptx::make_smem_desc_sw128(do_s + k * 2048, 8192, 1024);
         ptx::umma_bf16_ss(tdV, ad, bd, idesc_tn, (i > 0 || k > 0) ? 1u : 0u);
       }
 #pragma unroll
       for (int k = 0; k < 8; ++k) {   // dK[key, d] += sum_q dS[q, key] Q[q, d]
         const uint64_t ad = ptx::make_smem_desc_sw128(ptx::smem_u32(sdS) + k * 2048, FA_TILE, 1024);
-        const uint64_t bd = ptx::make_smem_desc_sw128(ptx::smem_u32(sQ) + k * 2048, 8192, 1024);
+        const uint64_t bd = ptx::make_smem_desc_sw128(q_s + k * 2048, 8192, 1024);
         ptx::umma_bf16_ss(tdK, ad, bd, idesc_tn, (i > 0 || k > 0) ? 1u : 0u);
       }
 #pragma unroll
@@ -413,31 +461,13 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_const
         const uint64_t bd = ptx::make_smem_desc_sw128(ptx::smem_u32(sK) + k * 2048, 8192, 1024);
         ptx::umma_bf16_ss(tdQ, ad, bd, idesc_nn, k > 0);
       }
-      ptx::umma_commit(mma_bar);
+      ptx::umma_commit(bar2);
     }
-    ptx::mbar_wait(mma_bar, 1);
-    ptx::tc_fence_after();
-    if (tid == 0 && i + 1 < p.nq) {   // Q / dO buffers are free
-      ptx::mbar_expect_tx(q_bar, 2 * FA_TILE);
-      ptx::tma_load_2d(ptx::smem_u32(sQ), &tma_qkv, q_bar, h * FA_D, row0 + (i + 1) * FA_T);
-      ptx::tma_load_2d(ptx::smem_u32(sdO), &tma_do, q_bar, h * FA_D, row0 + (i + 1) * FA_T);
-    }
-    {
-      float d[16];
-      ptx::tmem_ld_32x32b_x16(tdQ + lane_base + cg * 16, d);
-      ptx::tmem_ld_wait();
-      if (q_ok) {
-        float* dst = p.dq_accum + (static_cast<long long>(row0) + qg) * p.hidden + h * FA_D + cg * 16;
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 4 * u), "f"(d[4 * u]), "f"(d[4 * u + 1]),
-                       "f"(d[4 * u + 2]), "f"(d[4 * u + 3]) : "memory");
-      }
-    }
-    ptx::tc_fence_before();
-    __syncthreads();
   }
 
+  ptx::mbar_wait(bar2, (p.nq - 1) & 1);
+  ptx::tc_fence_after();
+  fa_dq_flush(p, tdQ, lane_base, cg, row0, h, (p.nq - 1) * FA_T + q);
   // dK, dV of this key tile: 128 columns [dK | dV], column group cg takes 32 of them.
   {
     const int key = kt * FA_T + q;

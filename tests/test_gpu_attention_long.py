@@ -146,7 +146,9 @@ def test_squad_models_match_cpu_reference(kind):
     assert abs(out_r[0].item() - out_g[0].item()) < 3e-2
     assert rel(out_g[1][:, :300].cpu(), out_r[1][:, :300]) < 5e-2
     for (n, pr), (_, pg) in zip(ref.named_parameters(), gpu.named_parameters()):
-        if n.endswith("_anchor") or n == "qa_outputs.bias":   # the span softmax is shift invariant: that gradient is identically 0
+        # the span softmax is shift invariant, so the gradients of qa_outputs.bias and of the last LayerNorm bias are
+        # identically zero (rounding noise in both implementations): nothing to compare
+        if n.endswith("_anchor") or pr.grad.abs().max() < 1e-6:
             continue
         cos = torch.nn.functional.cosine_similarity(pr.grad.flatten(), pg.grad.cpu().flatten(), dim=0).item()
         assert cos > 0.99, (n, cos)
