@@ -458,3 +458,84 @@ class AlbertForQuestionAnswering(nn.Module):
         for depth in range(self.cfg.num_hidden_layers):
             x = self.shared_layer(x, mask, B, S, seed_base=0x1000 + 16 * depth)
         return _qa_outputs(self.qa_outputs(x), B, S, start_positions, end_positions)
+
+
+# ------------------------------------------------------------------------------------------------
+# Hugging Face checkpoint interchange
+# ------------------------------------------------------------------------------------------------
+_HF_LAYER = {
+    "attention.output.dense.weight": "out_weight", "attention.output.dense.bias": "out_bias",
+    "attention.output.LayerNorm.weight": "ln1_weight", "attention.output.LayerNorm.bias": "ln1_bias",
+    "intermediate.dense.weight": "ffn1_weight", "intermediate.dense.bias": "ffn1_bias",
+    "output.dense.weight": "ffn2_weight", "output.dense.bias": "ffn2_bias",
+    "output.LayerNorm.weight": "ln2_weight", "output.LayerNorm.bias": "ln2_bias",
+}
+_HF_TOP = {
+    "bert.embeddings.word_embeddings.weight": "embeddings.word_embeddings",
+    "bert.embeddings.position_embeddings.weight": "embeddings.position_embeddings",
+    "bert.embeddings.token_type_embeddings.weight": "embeddings.token_type_embeddings",
+    "bert.embeddings.LayerNorm.weight": "embeddings.ln_weight", "bert.embeddings.LayerNorm.bias": "embeddings.ln_bias",
+    "bert.pooler.dense.weight": "head.pooler_weight", "bert.pooler.dense.bias": "head.pooler_bias",
+    "classifier.weight": "head.classifier_weight", "classifier.bias": "head.classifier_bias",
+    "qa_outputs.weight": "qa_outputs.weight", "qa_outputs.bias": "qa_outputs.bias",
+}
+
+
+def convert_hf_state_dict(hf: dict) -> dict:
+    """``transformers`` BERT ``state_dict`` (``BertForSequenceClassification`` / ``BertForQuestionAnswering`` / bare
+    ``BertModel``) → the parameter names of this module: per-layer query / key / value projections are concatenated into
+    the packed ``qkv_weight`` the fused kernels read, everything else is renamed. The reference's trials start from
+    ``from_pretrained`` weights (``examples/nlp/bert_glue_pytorch/model_def.py:60-68``); this is how such a checkpoint
+    gets into the sm_100a model."""
+    hf = {(k if k.startswith(("bert.", "classifier.", "qa_outputs.")) else "bert." + k): v for k, v in hf.items()}
+    out = {}
+    for k, name in _HF_TOP.items():
+        if k in hf:
+            out[name] = hf[k]
+    n = 0
+    while f"bert.encoder.layer.{n}.attention.self.query.weight" in hf:
+        pre = f"bert.encoder.layer.{n}."
+        out[f"layers.{n}.qkv_weight"] = torch.cat([hf[pre + f"attention.self.{t}.weight"] for t in ("query", "key", "value")], dim=0)
+        out[f"layers.{n}.qkv_bias"] = torch.cat([hf[pre + f"attention.self.{t}.bias"] for t in ("query", "key", "value")], dim=0)
+        for src, dst in _HF_LAYER.items():
+            out[f"layers.{n}.{dst}"] = hf[pre + src]
+        n += 1
+    return out
+
+
+def to_hf_state_dict(model: nn.Module) -> dict:
+    """The inverse of :func:`convert_hf_state_dict`: a ``state_dict`` ``transformers`` can load."""
+    sd = model.state_dict()
+    out = {}
+    for k, name in _HF_TOP.items():
+        if name in sd:
+            out[k] = sd[name]
+    n = 0
+    while f"layers.{n}.qkv_weight" in sd:
+        pre = f"bert.encoder.layer.{n}."
+        for t, w, b in zip(("query", "key", "value"), sd[f"layers.{n}.qkv_weight"].chunk(3, dim=0), sd[f"layers.{n}.qkv_bias"].chunk(3, dim=0)):
+            out[pre + f"attention.self.{t}.weight"], out[pre + f"attention.self.{t}.bias"] = w.clone(), b.clone()
+        for src, dst in _HF_LAYER.items():
+            out[pre + src] = sd[f"layers.{n}.{dst}"]
+        n += 1
+    return out
+
+
+def load_hf_state_dict(model: nn.Module, hf: dict) -> None:
+    """Load a ``transformers`` BERT checkpoint into ``model`` (heads the checkpoint does not carry keep their init)."""
+    own = set(model.state_dict())
+    mine = {k: v for k, v in convert_hf_state_dict(hf).items() if k in own or not k.startswith(("head.", "qa_outputs."))}
+    missing, unexpected = model.load_state_dict(mine, strict=False)
+    bad = [k for k in missing if not (k.endswith("_anchor") or k.startswith(("head.", "qa_outputs.")))]
+    if bad or unexpected:
+        raise KeyError(f"checkpoint does not match the model: missing {bad}, unexpected {list(unexpected)}")
+
+
+def config_from_hf(hf_config) -> BertConfig:
+    """``transformers.BertConfig`` → :class:`BertConfig`."""
+    g = lambda k, d: getattr(hf_config, k, d)  # noqa: E731
+    return BertConfig(vocab_size=g("vocab_size", 30522), hidden_size=g("hidden_size", 768), num_hidden_layers=g("num_hidden_layers", 12),
+                      num_attention_heads=g("num_attention_heads", 12), intermediate_size=g("intermediate_size", 3072),
+                      max_position_embeddings=g("max_position_embeddings", 512), type_vocab_size=g("type_vocab_size", 2),
+                      hidden_dropout_prob=g("hidden_dropout_prob", 0.1), attention_probs_dropout_prob=g("attention_probs_dropout_prob", 0.1),
+                      layer_norm_eps=g("layer_norm_eps", 1e-12), initializer_range=g("initializer_range", 0.02), num_labels=g("num_labels", 2))
