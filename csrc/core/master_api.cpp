@@ -108,10 +108,29 @@ void Master::register_routes() {
     return ok(scale_decide(ProvisionerConfig::from_json(b["config"]), b["snapshot"]));
   });
   // ---- minimal status page (the reference ships a React SPA; this is one static page over the same REST API) ----
-  http.route("GET", "/ui", [](const HttpRequest&) {
+  // ---- WebUI: determined_b200/master/webui/index.html (dashboard, experiments with metric charts, trials with logs, tasks,
+  //      cluster, master logs — the page set of the reference's React app, webui/react/src/pages) served from the repo
+  //      root; a build without that file answers with the embedded status page below ----
+  http.route("GET", "/", [](const HttpRequest&) {
     HttpResponse resp;
     resp.status = 200;
     resp.content_type = "text/html; charset=utf-8";
+    resp.body = "<!doctype html><meta http-equiv=\"refresh\" content=\"0; url=/ui\"><a href=\"/ui\">WebUI</a>";
+    return resp;
+  });
+  http.route("GET", "/ui", [m](const HttpRequest&) {
+    HttpResponse resp;
+    resp.status = 200;
+    resp.content_type = "text/html; charset=utf-8";
+    {
+      std::ifstream f(m->cfg.repo_root + "/determined_b200/master/webui/index.html");
+      if (f) {
+        std::stringstream ss;
+        ss << f.rdbuf();
+        resp.body = ss.str();
+        return resp;
+      }
+    }
     resp.body = R"HTML(<!doctype html><html><head><meta charset="utf-8"><title>determined_b200</title>
 <style>body{font:14px system-ui,sans-serif;margin:2em;color:#222}table{border-collapse:collapse;margin:1em 0}
 td,th{border:1px solid #ccc;padding:4px 10px;text-align:left}th{background:#f3f3f3}h2{margin-top:1.5em}.bar{background:#ddd;width:120px;height:10px}

@@ -145,7 +145,9 @@ def test_det_deploy_local_up_down(tmp_path):
         assert {a["id"] for a in agents} == {"agent-local", "agent-1"}
         import urllib.request
         page = urllib.request.urlopen(f"http://{info['master']}/ui", timeout=5).read().decode()
-        assert "determined_b200 master" in page
+        assert "<title>determined_b200</title>" in page and "#/experiments" in page     # the WebUI, not the embedded fallback
+        root = urllib.request.urlopen(f"http://{info['master']}/", timeout=5).read().decode()
+        assert "/ui" in root
     finally:
         down = subprocess.run([sys.executable, str(ROOT / "det-deploy"), "local", "cluster-down", "--cluster-name", "t"], capture_output=True,
                               text=True, env=env, timeout=60)
