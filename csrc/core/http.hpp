@@ -17,6 +17,8 @@
 #include <thread>
 #include <vector>
 
+#include <netdb.h>
+
 #include "json.hpp"
 
 namespace det {
@@ -215,6 +217,24 @@ class HttpServer {
   std::thread thread_;
 };
 
+// Dotted quad, resolvable name, or — for this machine's own host name when the resolver does not know it — loopback.
+inline in_addr_t resolve_ipv4(const std::string& host) {
+  if (host == "localhost") return inet_addr("127.0.0.1");
+  in_addr_t a = inet_addr(host.c_str());
+  if (a != INADDR_NONE) return a;
+  addrinfo hints{}, *res = nullptr;
+  hints.ai_family = AF_INET;
+  hints.ai_socktype = SOCK_STREAM;
+  if (getaddrinfo(host.c_str(), nullptr, &hints, &res) == 0 && res != nullptr) {
+    a = reinterpret_cast<sockaddr_in*>(res->ai_addr)->sin_addr.s_addr;
+    freeaddrinfo(res);
+    return a;
+  }
+  char self[256] = {0};
+  if (gethostname(self, sizeof self - 1) == 0 && host == self) return inet_addr("127.0.0.1");
+  return INADDR_NONE;
+}
+
 // Blocking one-shot client: returns status (or -1) and fills body.
 inline int http_request(const std::string& host, int port, const std::string& method, const std::string& path,
                         const std::string& body, std::string* out, int timeout_s = 60, const std::string& auth = "") {
@@ -225,7 +245,7 @@ inline int http_request(const std::string& host, int port, const std::string& me
   sockaddr_in addr{};
   addr.sin_family = AF_INET;
   addr.sin_port = htons(static_cast<uint16_t>(port));
-  addr.sin_addr.s_addr = inet_addr(host == "localhost" ? "127.0.0.1" : host.c_str());
+  addr.sin_addr.s_addr = resolve_ipv4(host);
   if (::connect(fd, reinterpret_cast<sockaddr*>(&addr), sizeof addr) < 0) { ::close(fd); return -1; }
   std::ostringstream os;
   os << method << " " << path << " HTTP/1.1\r\nHost: " << host << "\r\nContent-Type: application/json\r\nContent-Length: " << body.size()
@@ -245,6 +265,67 @@ inline int http_request(const std::string& host, int port, const std::string& me
   sscanf(buf.c_str(), "HTTP/%*s %d", &status);
   if (out) *out = buf.substr(he + 4);
   return status;
+}
+
+// Reverse-proxy helper: replay one request against host:port and hand back status / content type / body.
+inline HttpResponse http_forward(const std::string& host, int port, const HttpRequest& req, const std::string& path, int timeout_s = 60) {
+  HttpResponse out;
+  int fd = ::socket(AF_INET, SOCK_STREAM | SOCK_CLOEXEC, 0);
+  if (fd < 0) return HttpResponse::error(502, "proxy: socket() failed");
+  timeval tv{timeout_s, 0};
+  setsockopt(fd, SOL_SOCKET, SO_RCVTIMEO, &tv, sizeof tv);
+  sockaddr_in addr{};
+  addr.sin_family = AF_INET;
+  addr.sin_port = htons(static_cast<uint16_t>(port));
+  addr.sin_addr.s_addr = resolve_ipv4(host);
+  if (::connect(fd, reinterpret_cast<sockaddr*>(&addr), sizeof addr) < 0) { ::close(fd); return HttpResponse::error(502, "proxy: task is not accepting connections"); }
+  std::ostringstream os;
+  os << req.method << " " << path << " HTTP/1.1\r\nHost: " << host << ":" << port << "\r\nConnection: close\r\nContent-Length: " << req.body.size() << "\r\n";
+  for (auto& kv : req.headers) {
+    std::string k = kv.first;
+    for (auto& ch : k) ch = static_cast<char>(tolower(ch));
+    if (k == "host" || k == "connection" || k == "content-length" || k == "authorization") continue;
+    os << kv.first << ": " << kv.second << "\r\n";
+  }
+  os << "\r\n" << req.body;
+  const std::string wire = os.str();
+  if (::send(fd, wire.data(), wire.size(), MSG_NOSIGNAL) < 0) { ::close(fd); return HttpResponse::error(502, "proxy: send failed"); }
+  std::string buf;
+  char tmp[16384];
+  ssize_t n;
+  while ((n = ::recv(fd, tmp, sizeof tmp, 0)) > 0) buf.append(tmp, static_cast<size_t>(n));
+  ::close(fd);
+  const auto he = buf.find("\r\n\r\n");
+  if (he == std::string::npos) return HttpResponse::error(502, "proxy: malformed response from task");
+  int status = 502;
+  sscanf(buf.c_str(), "HTTP/%*s %d", &status);
+  out.status = status;
+  out.body = buf.substr(he + 4);
+  out.content_type = "application/octet-stream";
+  std::string head = buf.substr(0, he);
+  std::string lower = head;
+  for (auto& ch : lower) ch = static_cast<char>(tolower(ch));
+  const auto ct = lower.find("\r\ncontent-type:");
+  if (ct != std::string::npos) {
+    const size_t b = ct + 15, e = head.find("\r\n", b);
+    std::string v = head.substr(b, e == std::string::npos ? std::string::npos : e - b);
+    while (!v.empty() && v.front() == ' ') v.erase(v.begin());
+    out.content_type = v;
+  }
+  if (lower.find("transfer-encoding: chunked") != std::string::npos) {   // de-chunk: our own reply carries Content-Length
+    std::string body;
+    size_t pos = 0;
+    while (pos < out.body.size()) {
+      const size_t nl = out.body.find("\r\n", pos);
+      if (nl == std::string::npos) break;
+      const size_t len = strtoul(out.body.substr(pos, nl - pos).c_str(), nullptr, 16);
+      if (len == 0) break;
+      body.append(out.body, nl + 2, len);
+      pos = nl + 2 + len + 2;
+    }
+    out.body = body;
+  }
+  return out;
 }
 
 }  // namespace det

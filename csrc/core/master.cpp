@@ -111,14 +111,46 @@ class CommandActor : public Actor {
       spec.cwd = spec_["cwd"].str_or("");
       for (auto& kv : spec_["env"].obj()) spec.env[kv.first] = kv.second.as_string();
       for (auto& d : a["devices"].arr()) spec.devices.push_back(Device{static_cast<int>(d["id"].as_int()), d["brand"].as_string(), d["uuid"].as_string(), d["type"].as_string()});
+      // Service tasks (notebooks, TensorBoards, anything submitted with "proxy": true) get a port of their own: it replaces
+      // "{port}" in argv, is exported as DET_TASK_PORT, and /proxy/<id>/... on the master forwards to it once the
+      // readiness check has seen the service answer (reference: command.go readiness checks + internal/proxy).
+      port_ = static_cast<int>(spec_["proxy_port"].as_int(0));
+      if (port_ > 0) {
+        const std::string ps = std::to_string(port_);
+        for (auto& arg : spec.argv) {
+          size_t at;
+          while ((at = arg.find("{port}")) != std::string::npos) arg.replace(at, 6, ps);
+          while ((at = arg.find("{prefix}")) != std::string::npos) arg.replace(at, 8, "/proxy/" + std::to_string(id_) + "/");
+        }
+        spec.env["DET_TASK_PORT"] = ps;
+        spec.env["DET_TENSORBOARD_PORT"] = ps;
+        spec.env["DET_PROXY_PREFIX"] = "/proxy/" + std::to_string(id_) + "/";
+        const Json& addrs = a["addresses"];
+        host_ = a["agent"].as_string() == "agent-local" ? "127.0.0.1" : (addrs.is_array() && addrs.size() ? addrs.at(0).str_or("127.0.0.1") : "127.0.0.1");
+        m_->store.update("commands", id_, obj({{"proxy_host", host_}, {"proxy_port", port_}, {"is_ready", false},
+                                               {"service_address", "/proxy/" + std::to_string(id_) + "/"}}));
+        ctx.system().notify_after(ctx.self(), 300, "check_ready");
+      }
       container_ = spec.container_id;
       m_->register_container(container_, ctx.self(), -id_);
       set_state("RUNNING");
       m_->start_container(a["agent"].as_string(), spec);
+    } else if (msg.type == "check_ready") {
+      if (container_.empty() || ready_) return;
+      std::string body;
+      const int st = http_request(host_, port_, "GET", spec_["ready_path"].str_or("/"), "", &body, 2);
+      if (st > 0 && st < 500) {
+        ready_ = true;
+        m_->store.update("commands", id_, obj({{"is_ready", true}, {"ready_time", now_rfc3339()}}));
+        m_->log("info", task_id_ + " is ready at /proxy/" + std::to_string(id_) + "/");
+      } else {
+        ctx.system().notify_after(ctx.self(), 500, "check_ready");
+      }
     } else if (msg.type == "container_event") {
       if (msg.body["state"].as_string() == "TERMINATED") {
         m_->unregister_container(container_);
-        m_->store.update("commands", id_, obj({{"exit_code", msg.body["exit_code"]}, {"end_time", now_rfc3339()}}));
+        container_.clear();
+        m_->store.update("commands", id_, obj({{"exit_code", msg.body["exit_code"]}, {"end_time", now_rfc3339()}, {"is_ready", false}}));
         set_state("TERMINATED");
         ctx.tell(m_->rm, "release", obj({{"task_id", task_id_}}));
         ctx.stop_self();
@@ -137,7 +169,9 @@ class CommandActor : public Actor {
   Master* m_;
   long long id_;
   Json spec_;
-  std::string task_id_, container_;
+  std::string task_id_, container_, host_;
+  int port_ = 0;
+  bool ready_ = false;
 };
 }  // namespace
 

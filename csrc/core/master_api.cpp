@@ -11,6 +11,23 @@
 
 namespace det {
 
+// A TCP port nobody is listening on right now (bind to 0, read it back, release it).
+static int free_tcp_port() {
+  int fd = ::socket(AF_INET, SOCK_STREAM | SOCK_CLOEXEC, 0);
+  if (fd < 0) return 0;
+  sockaddr_in addr{};
+  addr.sin_family = AF_INET;
+  addr.sin_addr.s_addr = htonl(INADDR_LOOPBACK);
+  addr.sin_port = 0;
+  socklen_t len = sizeof addr;
+  int port = 0;
+  if (::bind(fd, reinterpret_cast<sockaddr*>(&addr), sizeof addr) == 0 && ::getsockname(fd, reinterpret_cast<sockaddr*>(&addr), &len) == 0)
+    port = ntohs(addr.sin_port);
+  ::close(fd);
+  return port;
+}
+
+
 namespace {
 Json obj(std::initializer_list<std::pair<const char*, Json>> kv) {
   Json j = Json::object();
@@ -97,6 +114,22 @@ void Master::register_routes() {
     s["enabled"] = true;
     return ok(s);
   });
+  // ---- reverse proxy to service tasks (reference: master/internal/proxy/proxy.go; HTTP only, no WebSocket upgrade) ----
+  for (const char* method : {"GET", "POST", "PUT", "PATCH", "DELETE"}) {
+    auto fwd = [m](const HttpRequest& r) {
+      Json c = m->store.get("commands", r.params.at("id"));
+      if (c.is_null()) return not_found("task");
+      if (c["proxy_port"].as_int(0) <= 0) return HttpResponse::error(404, "task exposes no service");
+      if (c["state"].str_or("") != "RUNNING") return HttpResponse::error(502, "task is " + c["state"].str_or("not running"));
+      std::string path = "/";
+      auto it = r.params.find("*");
+      if (it != r.params.end()) path += it->second;
+      if (!r.query_string.empty()) path += "?" + r.query_string;
+      return http_forward(c["proxy_host"].str_or("127.0.0.1"), static_cast<int>(c["proxy_port"].as_int()), r, path);
+    };
+    http.route(method, "/proxy/:id", fwd);
+    http.route(method, "/proxy/:id/*", fwd);
+  }
   // ---- Kubernetes back-end: pods owned by this master (reference: master/internal/kubernetes/pods.go summaries) ----
   http.route("GET", "/api/v1/kubernetes/pods", [m](const HttpRequest&) {
     if (!m->kube) return ok(obj({{"enabled", false}}));
@@ -521,6 +554,11 @@ tick();setInterval(tick,2000);
       const long long id = m->store.next_id("commands");
       Json spec = obj({{"type", type}, {"description", b["description"].str_or(type)}, {"slots", b["slots"].as_int(0)}, {"argv", b["argv"]},
                        {"env", b["env"].is_object() ? b["env"] : Json::object()}, {"cwd", b["cwd"].str_or("")}});
+      const bool service = b.contains("proxy") ? b["proxy"].as_bool(false) : (type == "notebook" || type == "tensorboard");
+      if (service) {
+        spec["proxy_port"] = b["port"].as_int(0) > 0 ? b["port"].as_int() : static_cast<long long>(free_tcp_port());
+        spec["ready_path"] = b["ready_path"].str_or("/");
+      }
       m->store.put("commands", id, obj({{"id", id}, {"type", type}, {"state", "PENDING"}, {"spec", spec}, {"start_time", now_rfc3339()}}));
       m->system.actor_of("commands/" + std::to_string(id), make_command(m, id, spec), m->commands_root);
       return HttpResponse::json(m->store.get("commands", id), 201);

@@ -131,6 +131,7 @@ class ResourcePoolActor : public Actor {
           req.allocations.push_back(al);
           Json a = Json::object();
           a["agent"] = al.agent_id; a["container_id"] = al.container_id; a["rank"] = rank++;
+          a["addresses"] = agent_info_[al.agent_id]["addresses"];
           Json devs = Json::array();
           const Json& info = agent_info_[al.agent_id]["devices"];
           for (int dev : al.devices)

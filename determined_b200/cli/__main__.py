@@ -419,12 +419,18 @@ def command_run(kind: str):
     def run(a: argparse.Namespace) -> int:
         s = Session(a.master, a.user)
         argv = a.command if getattr(a, "command", None) else {
-            "notebooks": [sys.executable, "-m", "jupyter", "lab", "--ip=127.0.0.1", "--no-browser"],
+            "notebooks": [sys.executable, "-m", "jupyter", "lab", "--ip=127.0.0.1", "--no-browser", "--port={port}", "--ServerApp.token=",
+                          "--ServerApp.base_url=" + "{prefix}"],
             "shells": ["/bin/sh", "-c", "sleep infinity"],
             "tensorboards": [sys.executable, "-m", "determined_b200.exec.tensorboard"] + [str(x) for x in getattr(a, "experiment_ids", [])],
         }[kind]
-        out = s.post(f"/api/v1/{kind}", {"argv": argv, "slots": getattr(a, "slots", 0), "description": " ".join(argv)[:60]})
+        body = {"argv": argv, "slots": getattr(a, "slots", 0), "description": " ".join(argv)[:60]}
+        if getattr(a, "proxy", False):
+            body["proxy"] = True
+        out = s.post(f"/api/v1/{kind}", body)
         print(f"Started {kind[:-1]} {out['id']}")
+        if out["spec"].get("proxy_port"):
+            print(f"Service address (once ready): {s.master}/proxy/{out['id']}/")
         if getattr(a, "detach", False):
             return 0
         seen = 0
@@ -535,7 +541,8 @@ def build_parser() -> argparse.ArgumentParser:
     for name, kind in (("cmd", "commands"), ("notebook", "notebooks"), ("shell", "shells"), ("tensorboard", "tensorboards")):
         g = group(name)
         extra = [A("command", nargs=argparse.REMAINDER)] if name == "cmd" else ([A("experiment_ids", nargs="*", type=int)] if name == "tensorboard" else [])
-        cmd(g, "run" if name == "cmd" else "start", command_run(kind), *extra, A("--slots", type=int, default=0), A("--detach", "-d", action="store_true"))
+        cmd(g, "run" if name == "cmd" else "start", command_run(kind), *extra, A("--slots", type=int, default=0), A("--detach", "-d", action="store_true"),
+            A("--proxy", action="store_true", help="give the task a port ({port} in the command, $DET_TASK_PORT) reachable at /proxy/<id>/ on the master"))
         cmd(g, "list", command_list(kind), aliases=["ls"])
         cmd(g, "kill", command_kill(kind), A("id"))
     return p

@@ -244,3 +244,47 @@ def test_actor_trace_and_debug_endpoints(slotless_master, tmp_path):
     c.request("POST", "/debug/trace", {"file": ""})
     events = [json.loads(l) for l in trace.read_text().splitlines() if l.strip()]
     assert any(e["tid"] == "rm" and e["name"] == "summary" and e["ph"] == "X" and e["dur"] >= 0 for e in events)
+
+
+def test_service_task_readiness_and_proxy(slotless_master, tmp_path):
+    """A command submitted with ``proxy: true`` gets a port ({port} in argv, DET_TASK_PORT), turns ``is_ready`` once it
+    answers HTTP, and is reachable through ``/proxy/<id>/...`` on the master (reference: master/internal/command readiness
+    checks + master/internal/proxy/proxy.go; notebooks and TensorBoards use the same path)."""
+    import urllib.error
+    import urllib.request
+
+    (tmp_path / "hello.txt").write_text("served through the master\n")
+    (tmp_path / "sub").mkdir()
+    (tmp_path / "sub" / "data.json").write_text('{"x": 1}')
+    c = MasterClient("127.0.0.1", slotless_master["port"])
+    cmd = c.request("POST", "/api/v1/commands", {"argv": [sys.executable, "-m", "http.server", "{port}", "--bind", "127.0.0.1"], "cwd": str(tmp_path),
+                                                "proxy": True, "description": "file server"})
+    assert cmd["spec"]["proxy_port"] > 0
+    try:
+        for _ in range(150):
+            cur = c.request("GET", f"/api/v1/commands/{cmd['id']}")
+            if cur.get("is_ready"):
+                break
+            time.sleep(0.1)
+        assert cur["is_ready"] and cur["state"] == "RUNNING" and cur["service_address"] == f"/proxy/{cmd['id']}/"
+        base = f"http://127.0.0.1:{slotless_master['port']}/proxy/{cmd['id']}"
+        assert urllib.request.urlopen(base + "/hello.txt", timeout=10).read() == b"served through the master\n"
+        r = urllib.request.urlopen(base + "/sub/data.json", timeout=10)
+        assert json.loads(r.read()) == {"x": 1} and "json" in r.headers["Content-Type"]
+        assert b"hello.txt" in urllib.request.urlopen(base + "/", timeout=10).read()        # directory listing of the task's cwd
+        with pytest.raises(urllib.error.HTTPError) as e:
+            urllib.request.urlopen(base + "/missing", timeout=10)
+        assert e.value.code == 404
+    finally:
+        c.request("POST", f"/api/v1/commands/{cmd['id']}/kill")
+    for _ in range(100):
+        cur = c.request("GET", f"/api/v1/commands/{cmd['id']}")
+        if cur["state"] == "TERMINATED":
+            break
+        time.sleep(0.1)
+    assert cur["state"] == "TERMINATED" and not cur["is_ready"]
+    with pytest.raises(urllib.error.HTTPError) as e:
+        urllib.request.urlopen(f"http://127.0.0.1:{slotless_master['port']}/proxy/{cmd['id']}/hello.txt", timeout=10)
+    assert e.value.code == 502
+    plain = c.request("POST", "/api/v1/commands", {"argv": ["/bin/true"]})
+    assert "proxy_port" not in plain["spec"]
