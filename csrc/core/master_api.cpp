@@ -135,15 +135,16 @@ void Master::register_routes() {
     if (!m->kube) return ok(obj({{"enabled", false}}));
     return ok(obj({{"enabled", true}, {"pods", m->kube->summary()}}));
   });
-  // ---- provisioner decision preview (reference: provisioner scale decider; providers are out of scope offline) ----
+  // ---- provisioner decision preview (reference: master/internal/provisioner/scale_decider.go) ----
   http.route("POST", "/api/v1/provisioner/decide", [](const HttpRequest& r) {
     Json b = r.json();
     return ok(scale_decide(ProvisionerConfig::from_json(b["config"]), b["snapshot"]));
   });
   // ---- minimal status page (the reference ships a React SPA; this is one static page over the same REST API) ----
-  // ---- WebUI: determined_b200/master/webui/index.html (dashboard, experiments with metric charts, trials with logs, tasks,
-  //      cluster, master logs — the page set of the reference's React app, webui/react/src/pages) served from the repo
-  //      root; a build without that file answers with the embedded status page below ----
+  // ---- WebUI ----
+  // determined_b200/master/webui/index.html (dashboard, experiments with metric charts, trials with logs, tasks, cluster,
+  // master logs — the page set of the reference's React app, webui/react/src/pages) served from the repo root; a build
+  // without that file answers with the embedded status page below.
   http.route("GET", "/", [](const HttpRequest&) {
     HttpResponse resp;
     resp.status = 200;

@@ -127,3 +127,11 @@ def test_pages_present():
     s = _script()
     for page in ("dashboard", "experiments", "experiment", "trial", "tasks", "cluster", "logs", "login"):
         assert re.search(r"\b%s\(" % page, s), page
+
+
+def test_rest_api_doc_is_current():
+    import subprocess
+    import sys
+
+    assert subprocess.run([sys.executable, str(ROOT / "scripts" / "gen_rest_api_doc.py"), "--check"]).returncode == 0, \
+        "docs/rest-api.md is stale: run python scripts/gen_rest_api_doc.py"
