@@ -213,3 +213,21 @@ def test_conv_bn_fused_statistics(N, H, Cin, Cout, k, s, p):
     assert _rel(xf.grad, xu.grad) < 2e-2
     assert _rel(fconv.weight.grad, uconv.weight.grad) < 2e-2
     assert _rel(fbn.weight.grad, ubn.weight.grad) < 2e-2 and _rel(fbn.bias.grad, ubn.bias.grad) < 2e-2
+
+
+def test_protonet_meta_learns_on_gpu():
+    """Few-shot episodes through the conv stack (1-channel stem → gather path, fused BN+ReLU, pooling) and the controller."""
+    from determined_b200.models import protonet_trial as P
+    from determined_b200.ops import _native
+    from tests.harness_utils import TrainAndValidate, make_controller
+
+    before = _native.launch_count
+    hp = {"global_batch_size": 2, "val_batch_size": 2, "learning_rate": 2e-3, "num_classes_train": 20, "num_support_train": 1,
+          "num_query_train": 5, "num_classes_val": 5, "num_support_val": 1, "num_query_val": 5, "hidden_dim": 64, "embedding_dim": 64}
+    tv = TrainAndValidate()
+    make_controller(P.OmniglotProtoNetTrial, hp, tv.send(steps=3, validation_freq=3, scheduling_unit=10),
+                    exp_config={"data": {"tasks_per_epoch_train": 60, "tasks_per_epoch_val": 20, "num_characters": 200},
+                                "searcher": {"name": "single", "metric": "loss", "max_length": {"batches": 100}}}).run()
+    losses = [m["loss"] for m in tv.training_metrics]
+    assert sum(losses[-5:]) < sum(losses[:5]) and tv.validation_metrics[-1]["acc"] > 0.5
+    assert _native.launch_count > before
