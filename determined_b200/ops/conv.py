@@ -237,6 +237,79 @@ class Conv2d(nn.Module):
 
 
 # ------------------------------------------------------------------------------------------------
+# Depthwise convolution (groups == channels): stride, padding, dilation
+# ------------------------------------------------------------------------------------------------
+class _DepthwiseFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, stride, pad, dil, relu):
+        R, S, _ = weight.shape
+        y = F.dwconv2d_fwd(x, weight, bias, R, S, stride, pad, dil, relu)
+        ctx.save_for_backward(x, y if relu else None)
+        ctx.weight, ctx.bias, ctx.cfg = weight, bias, (R, S, stride, pad, dil, relu)
+        note_param_use(ctx, weight, bias)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y = ctx.saved_tensors
+        R, S, stride, pad, dil, relu = ctx.cfg
+        dy = dy.contiguous()
+        if relu:
+            dy = F.act_bwd(dy, y, F.ACT_RELU)
+        F.dwconv2d_wgrad(x, dy, grad_buffer(ctx.weight), R, S, stride, pad, dil)
+        if ctx.bias is not None:
+            accumulate_bgrad(ctx.bias, dy.view(-1, dy.shape[-1]))
+        dx = F.dwconv2d_dgrad(dy, ctx.weight, tuple(x.shape), R, S, stride, pad, dil) if ctx.needs_input_grad[0] else None
+        notify_grads_written(ctx.weight, ctx.bias)
+        return dx, None, None, None, None, None, None
+
+
+class DepthwiseConv2d(nn.Module):
+    """``nn.Conv2d(C, C, k, groups=C)`` with stride / padding / dilation — the building block of separable and dilated
+    convolutions (DARTS ``SepConv`` / ``DilConv``, MobileNet blocks). No channel reduction means no tensor-core work: the
+    kernels (``dwconv_ops.cu``) are bandwidth-shaped. Weight is ``[R, S, C]`` fp32 (tap-major, read directly by the
+    kernels); ``state_dict`` speaks torch's ``[C, 1, R, S]``."""
+
+    def __init__(self, channels: int, kernel_size, stride: int = 1, padding: int = 0, dilation: int = 1, bias: bool = False,
+                 activation: Optional[str] = None) -> None:
+        super().__init__()
+        if activation not in (None, "relu"):
+            raise ValueError("DepthwiseConv2d fuses only ReLU")
+        self.channels, self.kernel_size = channels, _pair(kernel_size)
+        self.stride, self.padding, self.dilation, self.activation = int(stride), int(padding), int(dilation), activation
+        ref = nn.Conv2d(channels, channels, self.kernel_size, groups=channels, bias=bias)
+        self.weight = nn.Parameter(ref.weight.detach()[:, 0].permute(1, 2, 0).contiguous())
+        self.bias = nn.Parameter(ref.bias.detach().clone()) if bias else None
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if not x.is_cuda or self.channels % 8 != 0:
+            w = self.weight.permute(2, 0, 1).unsqueeze(1)
+            y = nn.functional.conv2d(x.float() if not x.is_cuda else x, w.to(x.dtype if x.is_cuda else torch.float32),
+                                     None if self.bias is None else self.bias.to(x.dtype if x.is_cuda else torch.float32),
+                                     self.stride, self.padding, self.dilation, groups=self.channels)
+            return torch.relu(y) if self.activation == "relu" else y
+        y = _DepthwiseFn.apply(to_nhwc(x), self.weight, self.bias, self.stride, self.padding, self.dilation, self.activation == "relu")
+        return from_nhwc(y)
+
+    def _save_to_state_dict(self, destination, prefix, keep_vars):
+        nn.Module._save_to_state_dict(self, destination, prefix, keep_vars)
+        k = prefix + "weight"
+        if k in destination:
+            destination[k] = destination[k].detach().permute(2, 0, 1).unsqueeze(1).contiguous()
+
+    def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
+        k = prefix + "weight"
+        if k in state_dict and state_dict[k].dim() == 4:
+            state_dict = dict(state_dict)
+            state_dict[k] = state_dict[k][:, 0].permute(1, 2, 0).contiguous()
+        nn.Module._load_from_state_dict(self, state_dict, prefix, *args, **kwargs)
+
+    def extra_repr(self) -> str:
+        return (f"{self.channels}, kernel_size={self.kernel_size}, stride={self.stride}, padding={self.padding}, "
+                f"dilation={self.dilation}, activation={self.activation}")
+
+
+# ------------------------------------------------------------------------------------------------
 # ConvTranspose2d  (= the data-gradient of a convolution)
 # ------------------------------------------------------------------------------------------------
 class _ConvT2dFn(torch.autograd.Function):
@@ -471,6 +544,32 @@ class MaxPool2d(nn.Module):
         if not x.is_cuda or x.shape[1] % 8 != 0:
             return nn.functional.max_pool2d(x, self.kernel_size, self.stride, self.padding)
         return from_nhwc(_MaxPoolFn.apply(to_nhwc(x), self.kernel_size, self.stride, self.padding))
+
+
+class _AvgPool2dFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, k, stride, pad, include_pad):
+        ctx.cfg = (tuple(x.shape), k, stride, pad, include_pad)
+        return F.avgpool2d_fwd(x, k, stride, pad, include_pad)
+
+    @staticmethod
+    def backward(ctx, dy):
+        shape, k, stride, pad, include_pad = ctx.cfg
+        return F.avgpool2d_bwd(dy.contiguous(), shape, k, stride, pad, include_pad), None, None, None, None
+
+
+class AvgPool2d(nn.Module):
+    """``nn.AvgPool2d`` (square window) on the NHWC kernels."""
+
+    def __init__(self, kernel_size: int, stride: Optional[int] = None, padding: int = 0, count_include_pad: bool = True) -> None:
+        super().__init__()
+        self.kernel_size, self.stride, self.padding = int(kernel_size), int(stride or kernel_size), int(padding)
+        self.count_include_pad = bool(count_include_pad)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if not x.is_cuda or x.shape[1] % 8 != 0:
+            return nn.functional.avg_pool2d(x, self.kernel_size, self.stride, self.padding, count_include_pad=self.count_include_pad)
+        return from_nhwc(_AvgPool2dFn.apply(to_nhwc(x), self.kernel_size, self.stride, self.padding, self.count_include_pad))
 
 
 class _AvgPoolFn(torch.autograd.Function):

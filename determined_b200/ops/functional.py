@@ -310,6 +310,46 @@ def bn_bwd(dy: torch.Tensor, x: torch.Tensor, a: Optional[torch.Tensor], mean: t
     return dx, dresid
 
 
+def dwconv_out_size(n: int, k: int, stride: int, pad: int, dil: int) -> int:
+    return (n + 2 * pad - dil * (k - 1) - 1) // stride + 1
+
+
+def dwconv2d_fwd(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor], R: int, S: int, stride: int, pad: int, dil: int,
+                 relu: bool = False) -> torch.Tensor:
+    """Depthwise convolution: x [N,H,W,C] bf16, w fp32 [R,S,C] → y [N,Ho,Wo,C] bf16."""
+    N, H, W, C = x.shape
+    y = torch.empty(N, dwconv_out_size(H, R, stride, pad, dil), dwconv_out_size(W, S, stride, pad, dil), C, dtype=torch.bfloat16, device=x.device)
+    _native.call("det_dwconv2d_fwd", _p(x), _p(w), _p(bias), _p(y), N, H, W, C, R, S, stride, pad, dil, int(relu), _stream())
+    return y
+
+
+def dwconv2d_dgrad(dy: torch.Tensor, w: torch.Tensor, in_shape, R: int, S: int, stride: int, pad: int, dil: int) -> torch.Tensor:
+    N, H, W, C = in_shape
+    dx = torch.empty(N, H, W, C, dtype=torch.bfloat16, device=dy.device)
+    _native.call("det_dwconv2d_dgrad", _p(dy), _p(w), _p(dx), N, H, W, C, R, S, stride, pad, dil, _stream())
+    return dx
+
+
+def dwconv2d_wgrad(x: torch.Tensor, dy: torch.Tensor, dw: torch.Tensor, R: int, S: int, stride: int, pad: int, dil: int) -> None:
+    """dw (fp32 [R,S,C]) += the weight gradient."""
+    N, H, W, C = x.shape
+    _native.call("det_dwconv2d_wgrad", _p(x), _p(dy), _p(dw), N, H, W, C, R, S, stride, pad, dil, _stream())
+
+
+def avgpool2d_fwd(x: torch.Tensor, k: int, stride: int, pad: int, count_include_pad: bool) -> torch.Tensor:
+    N, H, W, C = x.shape
+    y = torch.empty(N, conv_out_size(H, k, stride, pad), conv_out_size(W, k, stride, pad), C, dtype=torch.bfloat16, device=x.device)
+    _native.call("det_avgpool2d_fwd", _p(x), _p(y), N, H, W, C, k, stride, pad, int(count_include_pad), _stream())
+    return y
+
+
+def avgpool2d_bwd(dy: torch.Tensor, in_shape, k: int, stride: int, pad: int, count_include_pad: bool) -> torch.Tensor:
+    N, H, W, C = in_shape
+    dx = torch.empty(N, H, W, C, dtype=torch.bfloat16, device=dy.device)
+    _native.call("det_avgpool2d_bwd", _p(dy), _p(dx), N, H, W, C, k, stride, pad, int(count_include_pad), _stream())
+    return dx
+
+
 def maxpool_fwd(x: torch.Tensor, k: int, stride: int, pad: int) -> Tuple[torch.Tensor, torch.Tensor]:
     N, H, W, C = x.shape
     Ho, Wo = conv_out_size(H, k, stride, pad), conv_out_size(W, k, stride, pad)

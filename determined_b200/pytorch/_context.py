@@ -61,6 +61,25 @@ class _Experimental:
         self._parent = parent
         self.cuda_graphs = False
         self.graph_warmup_batches = 3
+        self._step_dev: Optional[torch.Tensor] = None
+        self._step_host: Optional[torch.Tensor] = None
+
+    def step_info(self) -> torch.Tensor:
+        """Device tensor ``[epoch_idx, batch_idx]`` (fp32) of the batch being trained, refreshed by the controller BEFORE
+        every ``train_batch`` — also before graph replays, where the Python arguments of ``train_batch`` are frozen at
+        their capture-time values. Schedules that depend on training progress (drop-path ramps, loss-weight warm-ups)
+        read it instead of ``epoch_idx`` when CUDA graphs are on."""
+        if self._step_dev is None:
+            dev = self._parent.device
+            self._step_dev = torch.zeros(2, dtype=torch.float32, device=dev)
+            self._step_host = torch.zeros(2, dtype=torch.float32, pin_memory=(dev.type == "cuda"))
+        return self._step_dev
+
+    def _set_step_info(self, epoch_idx: int, batch_idx: int) -> None:
+        if self._step_dev is None:
+            return
+        self._step_host[0], self._step_host[1] = float(epoch_idx), float(batch_idx)
+        self._step_dev.copy_(self._step_host, non_blocking=True)
 
     def enable_cuda_graphs(self, warmup_batches: int = 3) -> None:
         """Capture ``train_batch`` (forward, backward, all-reduce, optimizer) into CUDA graphs after a few eager

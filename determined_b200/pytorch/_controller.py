@@ -256,6 +256,7 @@ class PyTorchTrialController:
             num_inputs += _data.data_length(batch)
             ctx._set_current_batch(batch_idx, epoch_len)
             epoch_idx = batch_idx // epoch_len if epoch_len else 0
+            self.context.experimental._set_step_info(epoch_idx, batch_idx)
             if self._graphed is not None:
                 tr = self._graphed.run(batch, epoch_idx, batch_idx)
             else:

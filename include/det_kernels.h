@@ -51,6 +51,22 @@ int det_attention_flash_bwd(const void* qkv, const void* dctx, const void* ctx, 
                             void* dqkv, float* dq_accum, float* delta, int B, int S, int H, float dropout_p,
                             unsigned int seed, const unsigned int* seed_dev, cudaStream_t stream);
 
+/* ---- depthwise convolution (groups == channels), NHWC bf16, stride / padding / dilation; w and dw are fp32 tap-major
+ *      [R*S, C]; dgrad takes the INPUT sizes H, W; wgrad accumulates (+=). Replaces torch.nn.Conv2d(groups=C) → cuDNN of the
+ *      reference's NAS examples (examples/hp_search_benchmarks/darts_cifar10_pytorch/operations.py). */
+int det_dwconv2d_fwd(const void* x, const float* w, const float* bias, void* y, int N, int H, int W, int C, int R, int S,
+                     int stride, int pad, int dil, int relu, cudaStream_t stream);
+int det_dwconv2d_dgrad(const void* dy, const float* w, void* dx, int N, int H, int W, int C, int R, int S, int stride, int pad,
+                       int dil, cudaStream_t stream);
+int det_dwconv2d_wgrad(const void* x, const void* dy, float* dw, int N, int H, int W, int C, int R, int S, int stride, int pad,
+                       int dil, cudaStream_t stream);
+
+/* windowed average pooling (torch.nn.AvgPool2d); bwd takes the INPUT sizes H, W */
+int det_avgpool2d_fwd(const void* x, void* y, int N, int H, int W, int C, int k, int stride, int pad, int count_include_pad,
+                      cudaStream_t stream);
+int det_avgpool2d_bwd(const void* dy, void* dx, int N, int H, int W, int C, int k, int stride, int pad, int count_include_pad,
+                      cudaStream_t stream);
+
 /* ---- LayerNorm / reductions / embeddings / loss (reference: torch.nn.LayerNorm, Embedding, CrossEntropyLoss) */
 int det_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
                       int T, int H, float eps, float dropout_p, unsigned int seed, const unsigned int* seed_dev,

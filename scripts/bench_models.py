@@ -24,6 +24,7 @@ from bench import ClockSampler, _barrier_sync, _dist_env, _max_over_ranks  # noq
 from determined_b200 import _execution, load  # noqa: E402
 from determined_b200 import pytorch as dp  # noqa: E402
 from determined_b200 import workload as wl  # noqa: E402
+from determined_b200.models import darts_trial as DT
 from determined_b200.models import squad_trials as ST
 from determined_b200.models import vision_trials as VT  # noqa: E402
 from determined_b200.ops import _native  # noqa: E402
@@ -66,6 +67,8 @@ MODELS = {
     "dcgan": (VT.DCGANTrial, {"latent_dim": 128, "use_cuda_graphs": True}, (3, 64, 64), "images/s"),
     "cifar": (VT.CIFARTrial, {"learning_rate": 1e-4}, (3, 32, 32), "images/s"),
     "mnist": (VT.MNistTrial, {"learning_rate": 1.0}, (1, 28, 28), "images/s"),
+    # DARTS CIFAR-10 evaluation network (20 cells, separable / dilated convolutions), reference batch 96
+    "darts": (DT.DARTSCNNTrial, {"learning_rate": 0.025, "init_channels": 32, "layers": 20, "use_cuda_graphs": True}, (3, 32, 32), "images/s"),
     # BERT-base span model at the SQuAD shape (seq 384): the tiled attention kernels + span head
     "bert_squad": (ST.BertSquadTrial, {"learning_rate": 3e-5, "max_seq_length": 384, "use_cuda_graphs": True}, (1, 1, 384), "samples/s"),
     # ALBERT-xxlarge sizes (hidden 4096, 64 heads, one shared layer applied 12 times)

@@ -231,3 +231,81 @@ def test_protonet_meta_learns_on_gpu():
     losses = [m["loss"] for m in tv.training_metrics]
     assert sum(losses[-5:]) < sum(losses[:5]) and tv.validation_metrics[-1]["acc"] > 0.5
     assert _native.launch_count > before
+
+
+@pytest.mark.parametrize("C_,k,s,p,d,H", [(64, 3, 1, 1, 1, 16), (32, 5, 1, 2, 1, 9), (128, 3, 2, 1, 1, 17), (16, 3, 1, 2, 2, 12), (72, 5, 2, 4, 2, 15),
+                                          (512, 3, 1, 1, 1, 8)])
+def test_depthwise_conv2d(C_, k, s, p, d, H):
+    from determined_b200.ops import conv as C
+
+    torch.manual_seed(C_ + k + d)
+    x = _bf(torch.randn(3, C_, H, H + 2, device="cuda"))
+    ref = nn.Conv2d(C_, C_, k, s, p, d, groups=C_, bias=True).cuda()
+    mine = C.DepthwiseConv2d(C_, k, stride=s, padding=p, dilation=d, bias=True).cuda()
+    mine.load_state_dict(ref.state_dict())
+    xr = x.clone().requires_grad_(True)
+    xm = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last).requires_grad_(True)
+    yr, ym = ref(xr), mine(xm)
+    assert ym.shape == yr.shape and _rel(ym, yr) < 1e-2
+    g = _bf(torch.randn_like(yr))
+    yr.backward(g)
+    ym.backward(g.to(torch.bfloat16))
+    assert _rel(xm.grad, xr.grad) < 2e-2
+    assert _rel(mine.weight.grad.permute(2, 0, 1).unsqueeze(1), ref.weight.grad) < 2e-2
+    assert _rel(mine.bias.grad, ref.bias.grad) < 2e-2
+
+
+@pytest.mark.parametrize("k,s,p,inc", [(3, 1, 1, False), (3, 2, 1, False), (5, 3, 0, False), (2, 2, 0, True), (3, 2, 1, True)])
+def test_avgpool2d(k, s, p, inc):
+    from determined_b200.ops import conv as C
+
+    torch.manual_seed(k + s)
+    x = _bf(torch.randn(3, 24, 17, 14, device="cuda"))
+    _compare(C.AvgPool2d(k, s, p, count_include_pad=inc), nn.AvgPool2d(k, s, p, count_include_pad=inc), x, tol=1e-2)
+
+
+def test_darts_network_matches_cpu_and_trains():
+    """Same weights, same batch: the sm_100a network follows the fp32 CPU statement of the same graph (every primitive in
+    use), and the trial learns through the controller."""
+    from determined_b200.models import darts as D
+    from determined_b200.models.darts_trial import DARTSCNNTrial
+    from determined_b200.ops import _native
+    from tests.harness_utils import TrainAndValidate, make_controller
+
+    torch.manual_seed(0)
+    hp, ops, j = {}, D.PRIMITIVES[1:], 0
+    for cell in ("normal", "reduce"):
+        for i in range(1, 5):
+            for e in range(1, 3):
+                hp[f"{cell}_node{i}_edge{e}_op"] = ops[j % len(ops)]
+                hp[f"{cell}_node{i}_edge{e}"] = j % (i + 1)
+                j += 1
+    g = D.genotype_from_hparams(hp)
+    cpu = D.DartsNetworkCIFAR(16, 10, layers=3, auxiliary=True, genotype=g)
+    gpu = D.DartsNetworkCIFAR(16, 10, layers=3, auxiliary=True, genotype=g)
+    gpu.load_state_dict(cpu.state_dict())
+    gpu.cuda()
+    x = torch.randn(16, 3, 32, 32)
+    before = _native.launch_count
+    lc, ac = cpu(x)
+    lg, ag = gpu(x.cuda())
+    assert _native.launch_count - before > 50
+    assert _rel(lg.cpu(), lc) < 0.1 and _rel(ag.cpu(), ac) < 0.1
+    (lc.square().mean() + ac.square().mean()).backward()
+    (lg.float().square().mean() + ag.float().square().mean()).backward()
+    cos = []
+    for (n, pc), (_, pg) in zip(cpu.named_parameters(), gpu.named_parameters()):
+        if pc.grad is None or pc.grad.abs().max() < 1e-7:
+            continue
+        a, b = pc.grad.flatten(), pg.grad.cpu().flatten().float()
+        cos.append(torch.nn.functional.cosine_similarity(a, b, dim=0).item())
+    cos.sort()
+    assert cos[len(cos) // 2] > 0.93 and cos[len(cos) // 10] > 0.8, cos[:10]      # bf16 through ~20 conv / BN layers, batch of 16
+    hp2 = dict(hp, global_batch_size=32, learning_rate=0.05, init_channels=16, layers=3, train_epochs=5, drop_path_prob=0.1, cutout_length=8,
+               use_cuda_graphs=True)
+    tv = TrainAndValidate()
+    make_controller(DARTSCNNTrial, hp2, tv.send(steps=2, validation_freq=2, scheduling_unit=10),
+                    exp_config={"data": {"train_size": 128, "validation_size": 64},
+                                "searcher": {"name": "single", "metric": "top1_accuracy", "smaller_is_better": False, "max_length": {"batches": 100}}}).run()
+    losses = [m["loss"] for m in tv.training_metrics]
+    assert sum(losses[-5:]) < sum(losses[:5]), losses
