@@ -359,6 +359,214 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Backward, persistent form: one CTA per SM walks (batch, head) items, so TMEM allocation, barrier setup and the
+// TMA round trip of an item are paid under the previous item's work instead of once per 12 us CTA (ncu on the
+// one-shot kernel: half of all warp samples wait on TMA / MMA barriers, tensor pipe 5 % busy). Per item i:
+//   A  wait S_i, dP'_i                 -> registers;  barrier: TMEM S/dP free
+//   C  P'_i, delta, dS_i in registers;  wait MMA2 of item i-1 -> its Q/K/V/dO stage is refilled with item i+1 and its
+//      dQ/dK/dV are stored;  P'_i, dS_i -> smem;  barrier
+//   D  issue MMA2(i), then MMA1(i+1) as soon as its tiles have landed
+// Two stages of {Q, K, V, dO} + P + dS = 12 tiles (192 KB).
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t ATT_BWDP_SMEM = 12 * ATT_TILE + 1024 + 64 + 4 * ATT_S * 4 + 2 * ATT_S * 4;
+
+__global__ void __launch_bounds__(ATT_BWD_THREADS, 1)
+attention_bwd_persistent_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_constant__ CUtensorMap tma_do,
+                                const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sIn = smem;                       // stage s: Q, K, V, dO at sIn + (4 * s + {0,1,2,3}) * TILE
+  uint8_t* sP = smem + 8 * ATT_TILE;         // 2 chunks
+  uint8_t* sdS = smem + 10 * ATT_TILE;       // 2 chunks
+  uint8_t* tail = smem + 12 * ATT_TILE;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(tail);      // ld[0], ld[1], mma1, mma2
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 4);
+  float* red_delta = reinterpret_cast<float*>(tail + 64);  // [4][128]
+  float* smask = red_delta + 4 * ATT_S;                    // [2][128]
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int total = p.B * p.H;
+  const int n_items = (total - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+  const uint32_t ld_bar0 = ptx::smem_u32(&bars[0]);
+  const uint32_t bar1 = ptx::smem_u32(&bars[2]);
+  const uint32_t bar2 = ptx::smem_u32(&bars[3]);
+
+  if (tid == 0) {
+    ptx::tma_prefetch_desc(&tma_qkv);
+    ptx::tma_prefetch_desc(&tma_do);
+    for (int i = 0; i < 4; ++i) ptx::mbar_init(ptx::smem_u32(&bars[i]), 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 0) ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 512);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem, tdP = tmem + 128, tdV = tmem + 256, tdQ = tmem + 320, tdK = tmem + 384;
+
+  auto item_of = [&](int i) { return static_cast<int>(blockIdx.x) + i * static_cast<int>(gridDim.x); };
+  auto load_item = [&](int i) {   // tid 0 only
+    const int w = item_of(i), st = i & 1;
+    const int b = w / p.H, h = w % p.H, row0 = b * p.S;
+    const uint32_t lb = ld_bar0 + 8 * st;
+    uint8_t* base = sIn + 4 * st * ATT_TILE;
+    ptx::mbar_expect_tx(lb, 4 * ATT_TILE);
+    ptx::tma_load_2d(ptx::smem_u32(base), &tma_qkv, lb, h * ATT_D, row0);
+    ptx::tma_load_2d(ptx::smem_u32(base + ATT_TILE), &tma_qkv, lb, p.hidden + h * ATT_D, row0);
+    ptx::tma_load_2d(ptx::smem_u32(base + 2 * ATT_TILE), &tma_qkv, lb, 2 * p.hidden + h * ATT_D, row0);
+    ptx::tma_load_2d(ptx::smem_u32(base + 3 * ATT_TILE), &tma_do, lb, h * ATT_D, row0);
+  };
+  auto issue_mma1 = [&](int i) {  // tid 0 only
+    const int st = i & 1;
+    ptx::mbar_wait(ld_bar0 + 8 * st, (i >> 1) & 1);
+    ptx::tc_fence_after();
+    const uint32_t q_s = ptx::smem_u32(sIn + 4 * st * ATT_TILE), k_s = q_s + ATT_TILE, v_s = q_s + 2 * ATT_TILE, do_s = q_s + 3 * ATT_TILE;
+    constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(128, 128, 0, 0);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      ptx::umma_bf16_ss(tS, ptx::make_smem_desc_sw128(q_s + k * 32, 16, 1024), ptx::make_smem_desc_sw128(k_s + k * 32, 16, 1024), idesc, k > 0);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      ptx::umma_bf16_ss(tdP, ptx::make_smem_desc_sw128(do_s + k * 32, 16, 1024), ptx::make_smem_desc_sw128(v_s + k * 32, 16, 1024), idesc, k > 0);
+    ptx::umma_commit(bar1);
+  };
+
+  const int q = (warp & 3) * 32 + lane;
+  const int cg = warp >> 2;
+  const bool q_ok = q < p.S;
+  const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
+  const float sc = p.scale * LOG2E;
+  const uint32_t dseed = p.drop_seed + (p.drop_seed_dev ? __ldg(p.drop_seed_dev) * 0x9E3779B9u : 0u);
+
+  auto stage_mask = [&](int i) {  // threads 0..127
+    const int b = item_of(i) / p.H;
+    smask[(i & 1) * ATT_S + tid] = tid < p.S ? (p.mask != nullptr ? __ldg(p.mask + b * p.S + tid) * LOG2E : 0.0f) : -INFINITY;
+  };
+  auto store_item = [&](int i) {  // read dQ | dK | dV of item i out of TMEM (192 columns, 48 per column group)
+    const int w = item_of(i);
+    const int b = w / p.H, h = w % p.H;
+    const long long out_row = (static_cast<long long>(b) * p.S + q) * (3LL * p.hidden) + h * ATT_D;
+#pragma unroll
+    for (int t = 0; t < 3; ++t) {
+      const int c16 = cg * 3 + t;
+      const int which = c16 >> 2;
+      const int col = (c16 & 3) * 16;
+      const uint32_t src = (which == 0) ? tdQ : (which == 1 ? tdK : tdV);
+      float o[16];
+      ptx::tmem_ld_32x32b_x16(src + lane_base + col, o);
+      ptx::tmem_ld_wait();
+      if (q_ok) {
+        uint4* dst = reinterpret_cast<uint4*>(p.out + out_row + static_cast<long long>(which) * p.hidden + col);
+        dst[0] = pack8_bf16(o);
+        dst[1] = pack8_bf16(o + 8);
+      }
+    }
+  };
+
+  if (n_items > 0) {
+    if (tid < ATT_S) stage_mask(0);
+    if (tid == 0) {
+      load_item(0);
+      if (n_items > 1) load_item(1);
+      issue_mma1(0);
+    }
+  }
+
+  for (int i = 0; i < n_items; ++i) {
+    const int w = item_of(i);
+    const int b = w / p.H, h = w % p.H;
+    if (tid < ATT_S && i + 1 < n_items) stage_mask(i + 1);
+    const float lse2 = q_ok ? __ldg(p.lse + (static_cast<long long>(b) * p.H + h) * p.S + q) * LOG2E : 0.0f;
+    const uint32_t didx0 = ((static_cast<uint32_t>(b) * p.H + h) * p.S + q) * p.S + cg * 32;
+    const float* mk = smask + (i & 1) * ATT_S;
+
+    // ---- A ----
+    float pr[32], dp[32];
+    ptx::mbar_wait(bar1, i & 1);
+    ptx::tc_fence_after();
+    ptx::tmem_ld_32x32b_x32(tS + lane_base + cg * 32, pr);
+    ptx::tmem_ld_32x32b_x32(tdP + lane_base + cg * 32, dp);
+    ptx::tmem_ld_wait();
+    ptx::tc_fence_before();
+    __syncthreads();   // also publishes this item's staged mask (written one iteration ago, or in the prologue)
+
+    // ---- C ----
+    uint4 pk_p[4];
+    float delta = 0.0f;
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      float pd[8];
+#pragma unroll
+      for (int v = 0; v < 8; ++v) {
+        const int e = u * 8 + v;
+        const float pv = q_ok ? exp2f(fmaf(pr[e], sc, mk[cg * 32 + e]) - lse2) : 0.0f;
+        float keep = 1.0f;
+        if (p.drop_threshold != 0u) keep = dropout_keep(dseed, didx0 + e, p.drop_threshold) ? p.drop_scale : 0.0f;
+        dp[e] *= keep;
+        delta = fmaf(pv, dp[e], delta);
+        pr[e] = pv;
+        pd[v] = pv * keep;
+      }
+      pk_p[u] = pack8_bf16(pd);
+    }
+    red_delta[cg * ATT_S + q] = delta;
+    if (i > 0) {
+      ptx::mbar_wait(bar2, (i - 1) & 1);   // item i-1 is complete: its input stage, sP / sdS and the dQ/dK/dV columns are free
+      ptx::tc_fence_after();
+      if (tid == 0 && i + 1 < n_items) load_item(i + 1);
+      store_item(i - 1);
+    }
+    __syncthreads();   // delta exchange
+    delta = red_delta[q] + red_delta[ATT_S + q] + red_delta[2 * ATT_S + q] + red_delta[3 * ATT_S + q];
+#pragma unroll
+    for (int e = 0; e < 32; ++e) pr[e] = pr[e] * (dp[e] - delta) * p.scale;   // dS
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const uint32_t gu = cg * 4 + u;
+      *reinterpret_cast<uint4*>(sP + (gu >> 3) * ATT_TILE + ptx::sw128_offset(q, gu & 7)) = pk_p[u];
+      *reinterpret_cast<uint4*>(sdS + (gu >> 3) * ATT_TILE + ptx::sw128_offset(q, gu & 7)) = pack8_bf16(pr + 8 * u);
+    }
+    ptx::fence_proxy_async_smem();
+    ptx::tc_fence_before();
+    __syncthreads();
+
+    // ---- D ----
+    if (tid == 0) {
+      ptx::tc_fence_after();
+      const int st = i & 1;
+      const uint32_t q_s = ptx::smem_u32(sIn + 4 * st * ATT_TILE), k_s = q_s + ATT_TILE, do_s = q_s + 3 * ATT_TILE;
+      constexpr uint32_t idesc_tn = ptx::make_idesc_bf16_f32(128, 64, 1, 1);
+      constexpr uint32_t idesc_nn = ptx::make_idesc_bf16_f32(128, 64, 0, 1);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)   // dV = P'^T dO
+        ptx::umma_bf16_ss(tdV, ptx::make_smem_desc_sw128(ptx::smem_u32(sP) + k * 2048, ATT_TILE, 1024),
+                          ptx::make_smem_desc_sw128(do_s + k * 2048, 8192, 1024), idesc_tn, k > 0);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)   // dQ = dS K
+        ptx::umma_bf16_ss(tdQ, ptx::make_smem_desc_sw128(ptx::smem_u32(sdS) + (k >> 2) * ATT_TILE + (k & 3) * 32, 16, 1024),
+                          ptx::make_smem_desc_sw128(k_s + k * 2048, 8192, 1024), idesc_nn, k > 0);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)   // dK = dS^T Q
+        ptx::umma_bf16_ss(tdK, ptx::make_smem_desc_sw128(ptx::smem_u32(sdS) + k * 2048, ATT_TILE, 1024),
+                          ptx::make_smem_desc_sw128(q_s + k * 2048, 8192, 1024), idesc_tn, k > 0);
+      ptx::umma_commit(bar2);
+      if (i + 1 < n_items) issue_mma1(i + 1);
+    }
+  }
+  if (n_items > 0) {
+    ptx::mbar_wait(bar2, (n_items - 1) & 1);
+    ptx::tc_fence_after();
+    store_item(n_items - 1);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem, 512);
+  }
+}
+
 static int fill_params(AttnParams& p, int B, int S, int H, const float* mask, float* lse, void* out,
                        float dropout_p, unsigned seed, const unsigned* seed_dev) {
   DET_REQUIRE(S >= 1 && S <= ATT_S, "fused attention supports sequence length <= 128");
@@ -422,7 +630,14 @@ extern "C" int det_attention_bwd(const void* qkv, const void* dctx, const float*
   DET_CHECK_CUDA(cudaGetDevice(&dev));
   if (dev < 64 && !attr_set[dev]) {
     DET_CHECK_CUDA(cudaFuncSetAttribute(attention_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_BWD_SMEM));
+    DET_CHECK_CUDA(cudaFuncSetAttribute(attention_bwd_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_BWDP_SMEM));
     attr_set[dev] = true;
+  }
+  static const int one_shot = [] { const char* e = getenv("DET_ATTN_ONESHOT"); return e != nullptr && e[0] == '1' ? 1 : 0; }();
+  if (!one_shot && B * H > sm_count()) {
+    attention_bwd_persistent_kernel<<<std::min(B * H, sm_count()), ATT_BWD_THREADS, ATT_BWDP_SMEM, stream>>>(tq, td, p);
+    DET_CHECK_CUDA(cudaGetLastError());
+    return 0;
   }
   attention_bwd_kernel<<<B * H, ATT_BWD_THREADS, ATT_BWD_SMEM, stream>>>(tq, td, p);
   DET_CHECK_CUDA(cudaGetLastError());
