@@ -127,10 +127,16 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
                      const float* __restrict__ gamma, const float* __restrict__ mean,
                      const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx,
                      __nv_bfloat16* __restrict__ dx_masked, float* __restrict__ dgamma,
-                     float* __restrict__ dbeta, int T, DropCfg drop_in, DropCfg drop_out) {
+                     float* __restrict__ dbeta, float* __restrict__ dxsum, int T, DropCfg drop_in, DropCfg drop_out) {
   constexpr int H = CH * 256;
-  __shared__ float red[LN_BWD_WARPS][CH * 256];   // 48 KB at H = 1024
+  extern __shared__ float ln_bwd_smem[];           // [LN_BWD_WARPS + 1][H]: 52 KB at H = 1024
+  float (*red)[CH * 256] = reinterpret_cast<float (*)[CH * 256]>(ln_bwd_smem);
+  float* sacc = ln_bwd_smem + LN_BWD_WARPS * H;    // column sums of the gradient this kernel hands to the producer GEMM
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (dxsum != nullptr) {
+    for (int i = threadIdx.x; i < H; i += LN_BWD_WARPS * 32) sacc[i] = 0.0f;
+    __syncthreads();
+  }
   const int warps_total = gridDim.x * LN_BWD_WARPS;
   const uint32_t seed_in = eff_seed(drop_in), seed_out = eff_seed(drop_out);
   float g[CH * 8], dg[CH * 8], db[CH * 8];
@@ -191,7 +197,15 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
                        ? o[e] * drop_out.scale : 0.0f;
         omr[c * 32 + lane] = pack8(o);
       }
+      if (dxsum != nullptr) {   // bias gradient of the GEMM in front: column sums of what that GEMM's backward reads
+#pragma unroll
+        for (int e = 0; e < 8; ++e) atomicAdd(sacc + c * 256 + lane * 8 + e, o[e]);
+      }
     }
+  }
+  if (dxsum != nullptr) {
+    __syncthreads();
+    for (int col = threadIdx.x; col < H; col += LN_BWD_WARPS * 32) atomicAdd(dxsum + col, sacc[col]);
   }
   // block reduce of dgamma / dbeta, then one atomic per column per block
 #pragma unroll 1
@@ -413,11 +427,17 @@ static int launch_ln_fwd(const void* x, const float* g, const float* b, void* y,
 }
 template <int CH>
 static int launch_ln_bwd(const void* dy, const void* x, const float* g, const float* mean, const float* rstd,
-                         void* dx, void* dxm, float* dg, float* db, int T, DropCfg din, DropCfg dout, cudaStream_t st) {
+                         void* dx, void* dxm, float* dg, float* db, float* dxsum, int T, DropCfg din, DropCfg dout, cudaStream_t st) {
   const int blocks = min((T + LN_BWD_WARPS - 1) / LN_BWD_WARPS, sm_count());
-  layernorm_bwd_kernel<CH><<<blocks, LN_BWD_WARPS * 32, 0, st>>>(
+  constexpr int smem = (LN_BWD_WARPS + 1) * CH * 256 * static_cast<int>(sizeof(float));
+  static bool attr_set = false;
+  if (smem > 48 * 1024 && !attr_set) {
+    DET_CHECK_CUDA(cudaFuncSetAttribute(layernorm_bwd_kernel<CH>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    attr_set = true;
+  }
+  layernorm_bwd_kernel<CH><<<blocks, LN_BWD_WARPS * 32, smem, st>>>(
       reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(x), g, mean, rstd,
-      reinterpret_cast<__nv_bfloat16*>(dx), reinterpret_cast<__nv_bfloat16*>(dxm), dg, db, T, din, dout);
+      reinterpret_cast<__nv_bfloat16*>(dx), reinterpret_cast<__nv_bfloat16*>(dxm), dg, db, dxsum, T, din, dout);
   DET_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -477,11 +497,12 @@ layernorm_bwd_generic_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bf
                              const float* __restrict__ gamma, const float* __restrict__ mean,
                              const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dx,
                              __nv_bfloat16* __restrict__ dx_masked, float* __restrict__ dgamma, float* __restrict__ dbeta,
-                             int T, int H, DropCfg drop_in, DropCfg drop_out) {
-  extern __shared__ float lng_red[];   // [2][H]: per-block dgamma / dbeta
+                             float* __restrict__ dxsum, int T, int H, DropCfg drop_in, DropCfg drop_out) {
+  extern __shared__ float lng_red[];   // [3][H]: per-block dgamma / dbeta / column sums of the outgoing gradient
   float* sg = lng_red;
   float* sb = lng_red + H;
-  for (int i = threadIdx.x; i < 2 * H; i += blockDim.x) lng_red[i] = 0.0f;
+  float* sx = lng_red + 2 * H;
+  for (int i = threadIdx.x; i < 3 * H; i += blockDim.x) lng_red[i] = 0.0f;
   __syncthreads();
   const int lane = threadIdx.x & 31;
   const int nvec = H / 8;
@@ -534,12 +555,17 @@ layernorm_bwd_generic_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bf
             o[e] = dropout_keep(seed_out, static_cast<uint32_t>(row) * H + v * 8 + e, drop_out.threshold) ? o[e] * drop_out.scale : 0.0f;
         omr[v] = pack8(o);
       }
+      if (dxsum != nullptr) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) atomicAdd(sx + v * 8 + e, o[e]);
+      }
     }
   }
   __syncthreads();
   for (int col = threadIdx.x; col < H; col += blockDim.x) {
     if (dgamma != nullptr) atomicAdd(dgamma + col, sg[col]);
     if (dbeta != nullptr) atomicAdd(dbeta + col, sb[col]);
+    if (dxsum != nullptr) atomicAdd(dxsum + col, sx[col]);
   }
 }
 
@@ -552,16 +578,16 @@ static int launch_ln_fwd_generic(const void* x, const float* g, const float* b, 
   return 0;
 }
 static int launch_ln_bwd_generic(const void* dy, const void* x, const float* g, const float* mean, const float* rstd,
-                                 void* dx, void* dxm, float* dg, float* db, int T, int H, DropCfg din, DropCfg dout,
+                                 void* dx, void* dxm, float* dg, float* db, float* dxsum, int T, int H, DropCfg din, DropCfg dout,
                                  cudaStream_t st) {
-  const size_t smem = sizeof(float) * 2 * H;
+  const size_t smem = sizeof(float) * 3 * H;
   DET_REQUIRE(smem <= 200 * 1024, "layernorm: hidden size too large");
   if (smem > 48 * 1024)
     DET_CHECK_CUDA(cudaFuncSetAttribute(layernorm_bwd_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
   const int blocks = min((T + LNG_WARPS - 1) / LNG_WARPS, sm_count() * 2);
   layernorm_bwd_generic_kernel<<<blocks, LNG_WARPS * 32, smem, st>>>(
       reinterpret_cast<const __nv_bfloat16*>(dy), reinterpret_cast<const __nv_bfloat16*>(x), g, mean, rstd,
-      reinterpret_cast<__nv_bfloat16*>(dx), reinterpret_cast<__nv_bfloat16*>(dxm), dg, db, T, H, din, dout);
+      reinterpret_cast<__nv_bfloat16*>(dx), reinterpret_cast<__nv_bfloat16*>(dxm), dg, db, dxsum, T, H, din, dout);
   DET_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -590,15 +616,15 @@ extern "C" int det_layernorm_fwd(const void* x, const float* gamma, const float*
 
 extern "C" int det_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean,
                                  const float* rstd, void* dx, void* dx_masked, float* dgamma,
-                                 float* dbeta, int T, int H, float in_dropout_p, unsigned int in_seed,
+                                 float* dbeta, float* dxsum, int T, int H, float in_dropout_p, unsigned int in_seed,
                                  float out_dropout_p, unsigned int out_seed,
                                  const unsigned int* seed_dev, cudaStream_t stream) {
   DET_REQUIRE(H >= 8 && H % 8 == 0, "layernorm hidden size must be a multiple of 8");
   det::DropCfg din = det::make_drop(in_dropout_p, in_seed, seed_dev);
   det::DropCfg dout = det::make_drop(out_dropout_p, out_seed, seed_dev);
   if (H % 256 != 0 || H > 1024)
-    return det::launch_ln_bwd_generic(dy, x, gamma, mean, rstd, dx, dx_masked, dgamma, dbeta, T, H, din, dout, stream);
-  DET_LN_DISPATCH(launch_ln_bwd, dy, x, gamma, mean, rstd, dx, dx_masked, dgamma, dbeta, T, din, dout, stream)
+    return det::launch_ln_bwd_generic(dy, x, gamma, mean, rstd, dx, dx_masked, dgamma, dbeta, dxsum, T, H, din, dout, stream);
+  DET_LN_DISPATCH(launch_ln_bwd, dy, x, gamma, mean, rstd, dx, dx_masked, dgamma, dbeta, dxsum, T, din, dout, stream)
 }
 
 extern "C" int det_colsum_bf16(const void* x, float* out, int T, int N, long long ld, cudaStream_t stream) {

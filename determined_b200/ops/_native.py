@@ -26,7 +26,7 @@ _SIGNATURES = {
     "det_attention_flash_bwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                 c_float, c_uint, c_void_p, c_void_p],
     "det_layernorm_fwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_float, c_uint, c_void_p, c_void_p],
-    "det_layernorm_bwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+    "det_layernorm_bwd": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                           c_int, c_int, c_float, c_uint, c_float, c_uint, c_void_p, c_void_p],
     "det_colsum_bf16": [c_void_p, c_void_p, c_int, c_int, c_ll, c_void_p],
     "det_colsum_select_bf16": [c_void_p, c_void_p, c_ll, c_void_p, c_int, c_int, c_ll, c_void_p],

@@ -162,14 +162,15 @@ def layernorm_fwd(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps:
 def layernorm_bwd(dy: torch.Tensor, x: torch.Tensor, gamma: torch.Tensor, mean: torch.Tensor, rstd: torch.Tensor,
                   dgamma: Optional[torch.Tensor], dbeta: Optional[torch.Tensor], *, want_masked: bool = False,
                   in_dropout_p: float = 0.0, in_seed: int = 0, out_dropout_p: float = 0.0,
-                  out_seed: int = 0) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
-    """Returns (dx, dx_masked). dgamma/dbeta (fp32) are ACCUMULATED into."""
+                  out_seed: int = 0, dxsum: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, Optional[torch.Tensor]]:
+    """Returns (dx, dx_masked). dgamma/dbeta (fp32) are ACCUMULATED into; so is ``dxsum`` (fp32 [H]) with the column sums of
+    dx_masked (of dx when no masked copy is produced) — the bias gradient of the GEMM that produced the LayerNorm input."""
     T, H = x.shape
     dx = torch.empty_like(x)
     dxm = torch.empty_like(x) if want_masked else None
     any_drop = in_dropout_p > 0 or out_dropout_p > 0
     _native.call("det_layernorm_bwd", _p(dy), _p(x), _p(gamma), _p(mean), _p(rstd), _p(dx), _p(dxm), _p(dgamma),
-                 _p(dbeta), T, H, float(in_dropout_p), int(in_seed) & 0xFFFFFFFF, float(out_dropout_p),
+                 _p(dbeta), _p(dxsum), T, H, float(in_dropout_p), int(in_seed) & 0xFFFFFFFF, float(out_dropout_p),
                  int(out_seed) & 0xFFFFFFFF, _p(step_seed_tensor(x.device)) if any_drop else None, _stream())
     return dx, dxm
 

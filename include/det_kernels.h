@@ -72,7 +72,7 @@ int det_layernorm_fwd(const void* x, const float* gamma, const float* beta, void
                       int T, int H, float eps, float dropout_p, unsigned int seed, const unsigned int* seed_dev,
                       cudaStream_t stream);
 int det_layernorm_bwd(const void* dy, const void* x, const float* gamma, const float* mean, const float* rstd,
-                      void* dx, void* dx_masked, float* dgamma, float* dbeta, int T, int H, float in_dropout_p,
+                      void* dx, void* dx_masked, float* dgamma, float* dbeta, float* dxsum, int T, int H, float in_dropout_p,
                       unsigned int in_seed, float out_dropout_p, unsigned int out_seed,
                       const unsigned int* seed_dev, cudaStream_t stream);
 int det_colsum_bf16(const void* x, float* out, int T, int N, long long ld, cudaStream_t stream);

@@ -113,9 +113,12 @@ def test_layernorm_any_width(H):
     assert rel(y, ref) < 1e-2
     dy = torch.randn(T, H, device="cuda").bfloat16()
     dg, db = torch.zeros(H, device="cuda"), torch.zeros(H, device="cuda")
-    dx, _ = F.layernorm_bwd(dy, x, g, mean, rstd, dg, db)
+    dxs = torch.zeros(H, device="cuda")
+    dx, _ = F.layernorm_bwd(dy, x, g, mean, rstd, dg, db, dxsum=dxs)
     ref.backward(dy.float())
     assert rel(dx, xf.grad) < 1.5e-2 and rel(dg, gf.grad) < 1e-2 and rel(db, bf.grad) < 1e-2
+    want = xf.grad.sum(0)
+    assert (dxs - want).abs().max().item() < 2e-2 * max(want.abs().max().item(), 1.0) + 0.05
 
 
 @pytest.mark.parametrize("kind", ["bert", "albert"])

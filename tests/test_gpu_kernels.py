@@ -123,9 +123,16 @@ def test_layernorm(H):
     assert rel(y, ref) < 1e-2
     dy = torch.randn(T, H, device="cuda").bfloat16()
     dg, db = torch.zeros(H, device="cuda"), torch.zeros(H, device="cuda")
-    dx, _ = F.layernorm_bwd(dy, x, g, mean, rstd, dg, db)
+    dxs = torch.ones(H, device="cuda")
+    dx, _ = F.layernorm_bwd(dy, x, g, mean, rstd, dg, db, dxsum=dxs)
     ref.backward(dy.float())
     assert rel(dx, xf.grad) < 1.5e-2 and rel(dg, gf.grad) < 1e-2 and rel(db, bf.grad) < 1e-2
+    # fused bias gradient of the producer GEMM: column sums of dx, accumulated (+=) into the buffer
+    want = xf.grad.sum(0)
+    assert ((dxs - 1.0) - want).abs().max().item() < 2e-2 * max(want.abs().max().item(), 1.0) + 0.05
+    dxs2 = torch.zeros(H, device="cuda")
+    _, dxm = F.layernorm_bwd(dy, x, g, mean, rstd, None, None, want_masked=True, out_dropout_p=0.25, out_seed=9, dxsum=dxs2)
+    assert (dxs2 - dxm.float().sum(0)).abs().max().item() < 0.05 * max(dxm.float().sum(0).abs().max().item(), 1.0)
 
 
 def test_dropout_mask_consistency_gemm_vs_layernorm_bwd():
