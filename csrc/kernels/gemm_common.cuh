@@ -35,11 +35,12 @@ struct GemmParams {
 };
 
 // erf GELU through the Abramowitz–Stegun 7.1.26 rational form (|error| < 1.5e-7, far below bf16 resolution): one
-// reciprocal, one exp2 and six FMAs per element instead of libdevice erff's branchy ~40 instructions. The epilogue
+// approximate reciprocal, one exp2 and six FMAs per element instead of libdevice erff's branchy ~40 instructions. The epilogue
 // is instruction-issue bound, so this is what keeps it under the MMA time of a tile.
 __device__ __forceinline__ void phi_terms(float x, float& cdf, float& e) {
   const float ax = fabsf(x) * 0.70710678118654752f;
-  const float t = __frcp_rn(fmaf(0.3275911f, ax, 1.0f));
+  float t;   // rcp.approx (one MUFU op, 1 ulp) instead of the IEEE-rounded reciprocal's Newton fix-up sequence
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, ax, 1.0f)));
   e = exp2f(-1.4426950408889634f * ax * ax);  // exp(-x^2/2)
   float poly = fmaf(1.061405429f, t, -1.453152027f);
   poly = fmaf(poly, t, 1.421413741f);
