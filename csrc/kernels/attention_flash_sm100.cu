@@ -152,7 +152,7 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FlashParams 
     __syncthreads();
     const float m_new = fmaxf(m_run, fmaxf(red_max[q], red_max[FA_T + q]));
     const float m_use = (m_new == -INFINITY) ? 0.0f : m_new;          // a fully masked prefix keeps everything at zero
-    const float alpha = (m_run == -INFINITY) ? 0.0f : exp2f(m_run - m_use);
+    const float alpha = (m_run == -INFINITY) ? 0.0f : fast_exp2(m_run - m_use);
     m_run = m_new;
 
     // pass 2: probabilities, running sum, P' -> smem
@@ -164,7 +164,7 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FlashParams 
       ptx::tmem_ld_wait();
 #pragma unroll
       for (int e = 0; e < 32; ++e) {
-        s[e] = exp2f(fmaf(s[e], sc, smask[cg * 64 + hf * 32 + e]) - m_use);
+        s[e] = fast_exp2(fmaf(s[e], sc, smask[cg * 64 + hf * 32 + e]) - m_use);
         lsum += s[e];
       }
       if (p.drop_threshold != 0u) {
@@ -412,7 +412,7 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_const
     {
 #pragma unroll
       for (int e = 0; e < 32; ++e) {
-        const float pv = q_ok ? exp2f(fmaf(pr[e], sc, smask[cg * 32 + e]) - lse2) : 0.0f;
+        const float pv = q_ok ? fast_exp2(fmaf(pr[e], sc, smask[cg * 32 + e]) - lse2) : 0.0f;
         float keep = 1.0f;
         if (p.drop_threshold != 0u) keep = dropout_keep(dseed, didx0 + e, p.drop_threshold) ? p.drop_scale : 0.0f;
         pr[e] = pv * keep;                                // P'

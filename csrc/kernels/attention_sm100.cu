@@ -132,7 +132,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnPara
   float sum = 0.0f;
 #pragma unroll
   for (int e = 0; e < 64; ++e) {
-    s[e] = exp2f(s[e] - mx);
+    s[e] = fast_exp2(s[e] - mx);
     sum += s[e];
   }
   red_sum[cg * ATT_S + q] = sum;
@@ -278,7 +278,7 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
 #pragma unroll
     for (int e = 0; e < 32; ++e) {
       const int j = cg * 32 + e;
-      const float pv = q_ok ? exp2f(fmaf(pr[e], sc, smask[j]) - lse2) : 0.0f;  // exp2(-inf) = 0 past the sequence end
+      const float pv = q_ok ? fast_exp2(fmaf(pr[e], sc, smask[j]) - lse2) : 0.0f;  // exp2(-inf) = 0 past the sequence end
       float keep = 1.0f;
       if (p.drop_threshold != 0u) keep = dropout_keep(dseed, didx0 + e, p.drop_threshold) ? p.drop_scale : 0.0f;
       pr[e] = pv;
@@ -500,7 +500,7 @@ attention_bwd_persistent_kernel(const __grid_constant__ CUtensorMap tma_qkv, con
 #pragma unroll
       for (int v = 0; v < 8; ++v) {
         const int e = u * 8 + v;
-        const float pv = q_ok ? exp2f(fmaf(pr[e], sc, mk[cg * 32 + e]) - lse2) : 0.0f;
+        const float pv = q_ok ? fast_exp2(fmaf(pr[e], sc, mk[cg * 32 + e]) - lse2) : 0.0f;
         float keep = 1.0f;
         if (p.drop_threshold != 0u) keep = dropout_keep(dseed, didx0 + e, p.drop_threshold) ? p.drop_scale : 0.0f;
         dp[e] *= keep;

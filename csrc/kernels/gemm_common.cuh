@@ -41,7 +41,7 @@ __device__ __forceinline__ void phi_terms(float x, float& cdf, float& e) {
   const float ax = fabsf(x) * 0.70710678118654752f;
   float t;   // rcp.approx (one MUFU op, 1 ulp) instead of the IEEE-rounded reciprocal's Newton fix-up sequence
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, ax, 1.0f)));
-  e = exp2f(-1.4426950408889634f * ax * ax);  // exp(-x^2/2)
+  e = fast_exp2(-1.4426950408889634f * ax * ax);  // exp(-x^2/2)
   float poly = fmaf(1.061405429f, t, -1.453152027f);
   poly = fmaf(poly, t, 1.421413741f);
   poly = fmaf(poly, t, -0.284496736f);

@@ -284,6 +284,14 @@ __device__ __forceinline__ uint32_t sw128_offset(uint32_t row, uint32_t unit16) 
 // Counter-based dropout: a stateless keep/drop decision per (seed, element index), identical in
 // forward and backward so no mask tensor is ever stored. 32-bit mix (two rounds of multiply /
 // xorshift) -> uniform 32 bits; keep iff bits >= threshold where threshold = p * 2^32.
+// 2^x on the MUFU unit without exp2f()'s range fix-ups for denormal results (they flush to zero here): softmax and GELU
+// epilogues are instruction-issue bound, and every input they pass is <= 0 or moderate.
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 __host__ __device__ __forceinline__ uint32_t dropout_bits(uint32_t seed, uint32_t idx) {
   uint32_t x = idx * 0x9E3779B1u + seed;
   x ^= x >> 16;
