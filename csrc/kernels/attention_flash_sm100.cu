@@ -105,7 +105,7 @@ flash_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const FlashParams 
   const int qg = qt * FA_T + q;           // query position in the sequence
   const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
   const float sc = p.scale * FA_LOG2E;
-  const uint32_t dseed = p.drop_seed + (p.drop_seed_dev ? __ldg(p.drop_seed_dev) * 0x9E3779B9u : 0u);
+  const uint32_t dseed = dropout_effective_seed(p.drop_seed, p.drop_seed_dev);
   const uint32_t drow = ((static_cast<uint32_t>(b) * p.H + h) * p.S + qg) * p.S;
 
   float o[32];
@@ -383,7 +383,7 @@ flash_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const __grid_const
   const int cg = warp >> 2;   // keys [32*cg, 32*cg + 32) of the tile
   const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
   const float sc = p.scale * FA_LOG2E;
-  const uint32_t dseed = p.drop_seed + (p.drop_seed_dev ? __ldg(p.drop_seed_dev) * 0x9E3779B9u : 0u);
+  const uint32_t dseed = dropout_effective_seed(p.drop_seed, p.drop_seed_dev);
   const long long stat_base = (static_cast<long long>(b) * p.H + h) * p.S;
 
   for (int i = 0; i < p.nq; ++i) {

@@ -141,7 +141,7 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnPara
   const float inv = 1.0f / sum;
   if (cg == 0 && q < p.S) p.lse[(static_cast<long long>(b) * p.H + h) * p.S + q] = (mx + log2f(sum)) * (1.0f / LOG2E);
   const uint32_t didx0 = ((static_cast<uint32_t>(b) * p.H + h) * p.S + q) * p.S + cg * 64;
-  const uint32_t dseed = p.drop_seed + (p.drop_seed_dev ? __ldg(p.drop_seed_dev) * 0x9E3779B9u : 0u);
+  const uint32_t dseed = dropout_effective_seed(p.drop_seed, p.drop_seed_dev);
 #pragma unroll
   for (int u = 0; u < 8; ++u) {  // 16-byte units of 8 keys; this half is exactly smem chunk `cg`
     float v[8];
@@ -265,7 +265,7 @@ attention_bwd_kernel(const __grid_constant__ CUtensorMap tma_qkv,
   const float sc = p.scale * LOG2E;
   const float lse2 = q_ok ? p.lse[(static_cast<long long>(b) * p.H + h) * p.S + q] * LOG2E : 0.0f;
   const uint32_t didx0 = ((static_cast<uint32_t>(b) * p.H + h) * p.S + q) * p.S + cg * 32;
-  const uint32_t dseed = p.drop_seed + (p.drop_seed_dev ? __ldg(p.drop_seed_dev) * 0x9E3779B9u : 0u);
+  const uint32_t dseed = dropout_effective_seed(p.drop_seed, p.drop_seed_dev);
 
   float pr[32], dp[32];
   ptx::tmem_ld_32x32b_x32(tS + lane_base + cg * 32, pr);
@@ -437,7 +437,7 @@ attention_bwd_persistent_kernel(const __grid_constant__ CUtensorMap tma_qkv, con
   const bool q_ok = q < p.S;
   const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
   const float sc = p.scale * LOG2E;
-  const uint32_t dseed = p.drop_seed + (p.drop_seed_dev ? __ldg(p.drop_seed_dev) * 0x9E3779B9u : 0u);
+  const uint32_t dseed = dropout_effective_seed(p.drop_seed, p.drop_seed_dev);
 
   auto stage_mask = [&](int i) {  // threads 0..127
     const int b = item_of(i) / p.H;

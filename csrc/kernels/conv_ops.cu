@@ -297,7 +297,7 @@ dropout_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ 
                float scale, uint32_t seed, const uint32_t* __restrict__ seed_dev) {
   const long long i = (static_cast<long long>(blockIdx.x) * 256 + threadIdx.x) * 8;
   if (i >= n) return;
-  const uint32_t s = seed + (seed_dev ? __ldg(seed_dev) * 0x9E3779B9u : 0u);
+  const uint32_t s = dropout_effective_seed(seed, seed_dev);
   float f[8];
   if (i + 8 <= n) unpack8(__ldg(reinterpret_cast<const uint4*>(x + i)), f);
   else for (int j = 0; j < 8; ++j) f[j] = i + j < n ? __bfloat162float(x[i + j]) : 0.0f;

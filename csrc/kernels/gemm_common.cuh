@@ -184,7 +184,7 @@ __device__ __forceinline__ void gemm_epilogue_chunk(const GemmParams& p, float (
     } else if (p.epi == EPI_BIAS_RESID) {
       if (p.drop_threshold != 0u) {
         const uint32_t base = static_cast<uint32_t>(row) * static_cast<uint32_t>(p.N) + static_cast<uint32_t>(col0);
-        const uint32_t dseed = p.drop_seed + (p.drop_seed_dev ? __ldg(p.drop_seed_dev) * 0x9E3779B9u : 0u);
+        const uint32_t dseed = dropout_effective_seed(p.drop_seed, p.drop_seed_dev);
 #pragma unroll
         for (int j = 0; j < CW; ++j)
           v[j] = dropout_keep(dseed, base + j, p.drop_threshold) ? v[j] * p.drop_scale : 0.0f;

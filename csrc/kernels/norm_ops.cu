@@ -44,7 +44,7 @@ struct DropCfg {
   const uint32_t* seed_dev;
 };
 __device__ __forceinline__ uint32_t eff_seed(const DropCfg& d) {
-  return d.seed + (d.seed_dev ? __ldg(d.seed_dev) * 0x9E3779B9u : 0u);
+  return dropout_effective_seed(d.seed, d.seed_dev);
 }
 static DropCfg make_drop(float p, unsigned seed, const unsigned* seed_dev) {
   DropCfg d;
