@@ -188,6 +188,155 @@ attention_fwd_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnPara
 }
 
 // ------------------------------------------------------------------------------------------------
+// Forward, persistent form: two CTAs per SM walk (batch, head) items. The Q/K buffers are free as soon as S sits in
+// TMEM and the V buffer as soon as O does, so the next item's tiles are fetched under this item's softmax / PV / store
+// and TMEM allocation and barrier setup are paid once per CTA instead of once per item.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(ATT_FWD_THREADS, 2)
+attention_fwd_persistent_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + ATT_TILE;
+  uint8_t* sV = smem + 2 * ATT_TILE;
+  uint8_t* sP = smem + 3 * ATT_TILE;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 5 * ATT_TILE);   // qk, v, mma
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
+  float* red_max = reinterpret_cast<float*>(smem + 5 * ATT_TILE + 64);
+  float* red_sum = red_max + 2 * ATT_S;
+  float* smask = red_sum + 2 * ATT_S;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int total = p.B * p.H;
+  const int n_items = (total - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+  const uint32_t qk_bar = ptx::smem_u32(&bars[0]);
+  const uint32_t v_bar = ptx::smem_u32(&bars[1]);
+  const uint32_t mma_bar = ptx::smem_u32(&bars[2]);
+
+  if (tid == 0) {
+    ptx::tma_prefetch_desc(&tma_qkv);
+    ptx::mbar_init(qk_bar, 1);
+    ptx::mbar_init(v_bar, 1);
+    ptx::mbar_init(mma_bar, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 0) ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 256);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  const uint32_t tS = tmem, tO = tmem + 128;
+
+  auto item_of = [&](int i) { return static_cast<int>(blockIdx.x) + i * static_cast<int>(gridDim.x); };
+  auto load_qk = [&](int i) {   // tid 0 only
+    const int w = item_of(i), b = w / p.H, h = w % p.H, row0 = b * p.S;
+    ptx::mbar_expect_tx(qk_bar, 2 * ATT_TILE);
+    ptx::tma_load_2d(ptx::smem_u32(sQ), &tma_qkv, qk_bar, h * ATT_D, row0);
+    ptx::tma_load_2d(ptx::smem_u32(sK), &tma_qkv, qk_bar, p.hidden + h * ATT_D, row0);
+  };
+  auto load_v = [&](int i) {    // tid 0 only
+    const int w = item_of(i), b = w / p.H, h = w % p.H, row0 = b * p.S;
+    ptx::mbar_expect_tx(v_bar, ATT_TILE);
+    ptx::tma_load_2d(ptx::smem_u32(sV), &tma_qkv, v_bar, 2 * p.hidden + h * ATT_D, row0);
+  };
+  if (tid == 0 && n_items > 0) { load_qk(0); load_v(0); }
+
+  const int q = (warp & 3) * 32 + lane;
+  const int cg = warp >> 2;
+  const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
+  const float sc = p.scale * LOG2E;
+  const uint32_t dseed = dropout_effective_seed(p.drop_seed, p.drop_seed_dev);
+
+  for (int i = 0; i < n_items; ++i) {
+    const int w = item_of(i), b = w / p.H, h = w % p.H;
+    if (tid < ATT_S) smask[tid] = tid < p.S ? (p.mask != nullptr ? __ldg(p.mask + b * p.S + tid) * LOG2E : 0.0f) : -INFINITY;
+    if (tid == 0) {
+      ptx::mbar_wait(qk_bar, i & 1);
+      ptx::tc_fence_after();
+      constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(128, 128, 0, 0);
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        ptx::umma_bf16_ss(tS, ptx::make_smem_desc_sw128(ptx::smem_u32(sQ) + k * 32, 16, 1024),
+                          ptx::make_smem_desc_sw128(ptx::smem_u32(sK) + k * 32, 16, 1024), idesc, k > 0);
+      ptx::umma_commit(mma_bar);
+    }
+    __syncthreads();   // key mask staged
+    ptx::mbar_wait(mma_bar, 0);
+    ptx::tc_fence_after();
+    if (tid == 0 && i + 1 < n_items) load_qk(i + 1);   // S is in TMEM: Q / K buffers are free
+
+    float s[64];
+    ptx::tmem_ld_32x32b_x32(tS + lane_base + cg * 64, s);
+    ptx::tmem_ld_32x32b_x32(tS + lane_base + cg * 64 + 32, s + 32);
+    ptx::tmem_ld_wait();
+    float mx = -INFINITY;
+#pragma unroll
+    for (int e = 0; e < 64; ++e) {
+      s[e] = fmaf(s[e], sc, smask[cg * 64 + e]);
+      mx = fmaxf(mx, s[e]);
+    }
+    red_max[cg * ATT_S + q] = mx;
+    __syncthreads();
+    mx = fmaxf(red_max[q], red_max[ATT_S + q]);
+    float sum = 0.0f;
+#pragma unroll
+    for (int e = 0; e < 64; ++e) {
+      s[e] = fast_exp2(s[e] - mx);
+      sum += s[e];
+    }
+    red_sum[cg * ATT_S + q] = sum;
+    __syncthreads();
+    sum = red_sum[q] + red_sum[ATT_S + q];
+    const float inv = 1.0f / sum;
+    if (cg == 0 && q < p.S) p.lse[(static_cast<long long>(b) * p.H + h) * p.S + q] = (mx + log2f(sum)) * (1.0f / LOG2E);
+    const uint32_t didx0 = ((static_cast<uint32_t>(b) * p.H + h) * p.S + q) * p.S + cg * 64;
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      float v[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        float pv = s[u * 8 + e] * inv;
+        if (p.drop_threshold != 0u)
+          pv = dropout_keep(dseed, didx0 + u * 8 + e, p.drop_threshold) ? pv * p.drop_scale : 0.0f;
+        v[e] = pv;
+      }
+      *reinterpret_cast<uint4*>(sP + cg * ATT_TILE + ptx::sw128_offset(q, u)) = pack8_bf16(v);
+    }
+    ptx::fence_proxy_async_smem();
+    ptx::tc_fence_before();
+    __syncthreads();
+
+    if (tid == 0) {
+      ptx::mbar_wait(v_bar, i & 1);
+      ptx::tc_fence_after();
+      constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(128, 64, 0, 1);
+#pragma unroll
+      for (int k = 0; k < 8; ++k)
+        ptx::umma_bf16_ss(tO, ptx::make_smem_desc_sw128(ptx::smem_u32(sP) + (k >> 2) * ATT_TILE + (k & 3) * 32, 16, 1024),
+                          ptx::make_smem_desc_sw128(ptx::smem_u32(sV) + k * 2048, 8192, 1024), idesc, k > 0);
+      ptx::umma_commit(mma_bar);
+    }
+    ptx::mbar_wait(mma_bar, 1);
+    ptx::tc_fence_after();
+    if (tid == 0 && i + 1 < n_items) load_v(i + 1);    // O is in TMEM: the V buffer is free
+    float o[32];
+    ptx::tmem_ld_32x32b_x32(tO + lane_base + cg * 32, o);
+    ptx::tmem_ld_wait();
+    if (q < p.S) {
+      uint4* dst = reinterpret_cast<uint4*>(p.out + (static_cast<long long>(b) * p.S + q) * p.hidden + h * ATT_D + cg * 32);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) dst[u] = pack8_bf16(o + 8 * u);
+    }
+    ptx::tc_fence_before();
+    __syncthreads();   // S / O / P / exchange buffers are free for the next item
+  }
+  if (warp == 0) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem, 256);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Backward: 512 threads = 4 lane quarters x 4 column groups (32 keys each); 1 CTA per SM.
 // ------------------------------------------------------------------------------------------------
 constexpr int ATT_BWD_THREADS = 512;
@@ -605,7 +754,14 @@ extern "C" int det_attention_fwd(const void* qkv, const float* mask, void* ctx, 
   DET_CHECK_CUDA(cudaGetDevice(&dev));
   if (dev < 64 && !attr_set[dev]) {
     DET_CHECK_CUDA(cudaFuncSetAttribute(attention_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_FWD_SMEM));
+    DET_CHECK_CUDA(cudaFuncSetAttribute(attention_fwd_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_FWD_SMEM));
     attr_set[dev] = true;
+  }
+  static const int one_shot = [] { const char* e = getenv("DET_ATTN_ONESHOT"); return e != nullptr && e[0] == '1' ? 1 : 0; }();
+  if (!one_shot && B * H > 2 * sm_count()) {
+    attention_fwd_persistent_kernel<<<2 * sm_count(), ATT_FWD_THREADS, ATT_FWD_SMEM, stream>>>(tq, p);
+    DET_CHECK_CUDA(cudaGetLastError());
+    return 0;
   }
   attention_fwd_kernel<<<B * H, ATT_FWD_THREADS, ATT_FWD_SMEM, stream>>>(tq, p);
   DET_CHECK_CUDA(cudaGetLastError());

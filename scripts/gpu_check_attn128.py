@@ -36,6 +36,6 @@ for B, S, H, p in [(48, 128, 12, 0.1), (48, 128, 12, 0.0), (64, 100, 16, 0.1), (
     t_f = timeit(lambda: F.attention_fwd(qkv, mask, B, S, H, p, 3))
     row = {"B": B, "S": S, "H": H, "dropout": p, "oneshot": os.environ.get("DET_ATTN_ONESHOT", "0"), "fwd_us": round(t_f * 1e3, 2),
            "bwd_us": round(t_b * 1e3, 2), "checksum": float(d.float().abs().sum()), "finite": bool(torch.isfinite(d.float()).all())}
-    torch.save(d.cpu(), f"gpurun_out/attn128_{B}_{S}_{H}_{p}_{row['oneshot']}.pt")
+    torch.save(torch.cat([d.float().flatten(), ctx.float().flatten(), lse.flatten()]).cpu(), f"gpurun_out/attn128_{B}_{S}_{H}_{p}_{row['oneshot']}.pt")
     print(json.dumps(row), flush=True)
     out.append(row)
