@@ -305,7 +305,7 @@ embed_scatter_kernel(const long long* __restrict__ ids, const long long* __restr
   const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
   if (row >= T) return;
   float* w = dword + ids[row] * H;
-  float* p = dpos + static_cast<long long>(row % S) * H;
+  float* p = dpos ? dpos + static_cast<long long>(row % S) * H : nullptr;   // null: the caller reduces positions over the batch
   float* ty = dtype ? dtype + (tts ? tts[row] : 0) * H : nullptr;
   for (int c = lane * 8; c < H; c += 256) {
     float f[8];
@@ -313,7 +313,7 @@ embed_scatter_kernel(const long long* __restrict__ ids, const long long* __restr
 #pragma unroll
     for (int e = 0; e < 8; ++e) {
       atomicAdd(w + c + e, f[e]);
-      atomicAdd(p + c + e, f[e]);
+      if (dpos != nullptr) atomicAdd(p + c + e, f[e]);
       if (dtype != nullptr) atomicAdd(ty + c + e, f[e]);
     }
   }

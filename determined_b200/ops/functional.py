@@ -193,7 +193,13 @@ def embed_gather(ids: torch.Tensor, type_ids: Optional[torch.Tensor], word: torc
 def embed_scatter(ids: torch.Tensor, type_ids: Optional[torch.Tensor], de: torch.Tensor, dword: torch.Tensor,
                   dpos: torch.Tensor, dtyp: torch.Tensor, S: int) -> None:
     T, H = de.shape
-    _native.call("det_embed_scatter", _p(ids), _p(type_ids), _p(de), _p(dword), _p(dpos), None, T, S, H, _stream())
+    if T % S == 0 and (S * H) % 8 == 0 and de.is_contiguous():
+        # every position occurs once per sequence: its gradient is a sum over the batch — a column sum of de viewed as
+        # [B, S*H] — instead of B-way contended atomics on the same S*H addresses
+        _native.call("det_embed_scatter", _p(ids), _p(type_ids), _p(de), _p(dword), None, None, T, S, H, _stream())
+        _native.call("det_colsum_bf16", _p(de), _p(dpos), T // S, S * H, S * H, _stream())
+    else:
+        _native.call("det_embed_scatter", _p(ids), _p(type_ids), _p(de), _p(dword), _p(dpos), None, T, S, H, _stream())
     # token-type rows are few: reduce instead of hammering two addresses with atomics
     if type_ids is None:
         _native.call("det_colsum_bf16", _p(de), _p(dtyp[0]), T, H, de.stride(0), _stream())
