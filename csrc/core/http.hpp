@@ -25,6 +25,7 @@ namespace det {
 
 struct HttpRequest {
   std::string method, path, query_string, body;
+  std::string remote_addr;   // peer IPv4 address of the connection
   std::map<std::string, std::string> headers, query, params;
   Json json() const { return body.empty() ? Json::object() : Json::parse(body); }
   std::string q(const std::string& k, const std::string& def = "") const {
@@ -88,11 +89,15 @@ class HttpServer {
   }
   void serve_forever() {
     while (!stop_) {
-      int c = ::accept4(fd_, nullptr, nullptr, SOCK_CLOEXEC);
+      sockaddr_in peer{};
+      socklen_t plen = sizeof peer;
+      int c = ::accept4(fd_, reinterpret_cast<sockaddr*>(&peer), &plen, SOCK_CLOEXEC);
       if (c < 0) { if (stop_) break; continue; }
       int one = 1;
       setsockopt(c, IPPROTO_TCP, TCP_NODELAY, &one, sizeof one);
-      std::thread([this, c] { handle(c); }).detach();
+      char ip[INET_ADDRSTRLEN] = {0};
+      inet_ntop(AF_INET, &peer.sin_addr, ip, sizeof ip);
+      std::thread([this, c, addr = std::string(ip)] { handle(c, addr); }).detach();
     }
   }
   void start() { thread_ = std::thread([this] { serve_forever(); }); }
@@ -161,8 +166,9 @@ class HttpServer {
     }
     return true;
   }
-  void handle(int c) {
+  void handle(int c, const std::string& remote_addr) {
     HttpRequest req;
+    req.remote_addr = remote_addr;
     if (read_request(c, req)) {
       HttpResponse resp = dispatch(req);
       static const std::map<int, const char*> reason = {{200, "OK"}, {201, "Created"}, {204, "No Content"}, {400, "Bad Request"},

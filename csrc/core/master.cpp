@@ -276,8 +276,14 @@ void Master::route_log(const LogLine& l) {
     auto it = container_owner_.find(l.container_id);
     if (it != container_owner_.end()) { owner = it->second.first; trial_id = it->second.second; }
   }
+  std::string agent_id = "agent-local";
+  {
+    std::lock_guard<std::mutex> g(agent_cmd_mu_);
+    auto it = container_agent_.find(l.container_id);
+    if (it != container_agent_.end()) agent_id = it->second;
+  }
   Json row = obj({{"trial_id", trial_id}, {"container_id", l.container_id}, {"timestamp", now_rfc3339()}, {"stdtype", l.stdtype},
-                  {"rank", l.rank >= 0 ? Json(l.rank) : Json()}, {"message", l.message}, {"source", "agent"}, {"agent_id", "agent-local"},
+                  {"rank", l.rank >= 0 ? Json(l.rank) : Json()}, {"message", l.message}, {"source", "agent"}, {"agent_id", agent_id},
                   {"level", l.stdtype == "stderr" ? "INFO" : "INFO"}});
   if (trial_id > 0) system.tell(logger, "log", row);
   else if (owner) system.tell(owner, "log", row);

@@ -487,6 +487,14 @@ tick();setInterval(tick,2000);
       Json b = r.json();
       b["id"] = r.params.at("agent");
       b["registered_time"] = now_rfc3339();
+      // the address other nodes reach this agent at is where its connection came from (host names need not resolve);
+      // the name it reported stays as a second entry
+      if (!r.remote_addr.empty()) {
+        Json addrs = Json::array();
+        addrs.push_back(Json(r.remote_addr));
+        if (b["addresses"].is_array()) for (auto& a : b["addresses"].arr()) addrs.push_back(a);
+        b["addresses"] = addrs;
+      }
       m->system.ask(m->rm, "add_agent", b);
       return ok(obj({{"master_set_agent_options", obj({{"master_info", obj({{"cluster_id", m->cluster_id}})}})}}));
     }

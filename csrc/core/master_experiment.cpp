@@ -186,6 +186,14 @@ class TrialActor : public Actor {
     ++run_id_;
     containers_.clear();
     const int n = static_cast<int>(allocations.size());
+    int world_slots = 0, rank_offset = 0;
+    for (auto& a : allocations.arr()) world_slots += static_cast<int>(a["devices"].size());
+    std::string chief_addr = "127.0.0.1";
+    if (n > 1) {   // the chief is the rank-0 container; a single-container trial keeps everything on loopback
+      const Json& c0 = allocations.at(0);
+      if (c0["agent"].str_or("") == "agent-local") chief_addr = m_->cfg.host == "0.0.0.0" || m_->cfg.host.empty() ? "127.0.0.1" : m_->cfg.host;
+      else if (c0["addresses"].is_array() && c0["addresses"].size() > 0) chief_addr = c0["addresses"].at(0).str_or("127.0.0.1");
+    }
     for (auto& a : allocations.arr()) {
       ContainerSpec spec;
       spec.container_id = a["container_id"].as_string();
@@ -215,6 +223,14 @@ class TrialActor : public Actor {
       e["DET_AGENT_ID"] = a["agent"].as_string();
       e["DET_CONTAINER_RANK"] = std::to_string(a["rank"].as_int());
       e["DET_NUM_CONTAINERS"] = std::to_string(n);
+      // Rendezvous of a trial that spans containers (reference: RENDEZVOUS_INFO pushed by trial.go:813-908 — addresses and
+      // ranks of every container): every worker joins ONE process group hosted by the chief container; a worker's global
+      // rank is its local rank plus the slots of the containers ranked before its own.
+      e["DET_CHIEF_ADDR"] = chief_addr;
+      e["DET_CHIEF_PORT"] = std::to_string(20000 + (trial_id_ * 7 + run_id_) % 20000);
+      e["DET_RANK_OFFSET"] = std::to_string(rank_offset);
+      e["DET_WORLD_SLOTS"] = std::to_string(world_slots);
+      rank_offset += static_cast<int>(a["devices"].size());
       e["DET_DEBUG"] = config_["debug"].as_bool(false) ? "true" : "false";
       const char* pp = getenv("PYTHONPATH");
       e["PYTHONPATH"] = spec.cwd + ":" + m_->cfg.repo_root + (pp ? std::string(":") + pp : "");

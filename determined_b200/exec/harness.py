@@ -63,14 +63,26 @@ def _pump(stream, rank: int, out) -> None:
         out.flush()
 
 
+def rendezvous_env(n_local: int, environ=os.environ) -> dict:
+    """Process-group coordinates of this container's workers. A trial inside one container meets on loopback at a free
+    port; a trial that spans containers (several agents / pods — the reference's multi-machine Horovod job,
+    ``layers/_worker_process.py:113-199``) meets at the chief container's address, and a worker's global rank is its local
+    rank plus the slots of the containers ranked before its own (``DET_RANK_OFFSET``, set by the master)."""
+    if int(environ.get("DET_NUM_CONTAINERS", "1")) > 1:
+        return {"addr": environ.get("DET_CHIEF_ADDR", "127.0.0.1"), "port": int(environ["DET_CHIEF_PORT"]),
+                "offset": int(environ.get("DET_RANK_OFFSET", "0")), "world": int(environ.get("DET_WORLD_SLOTS", str(n_local)))}
+    return {"addr": "127.0.0.1", "port": _free_port(), "offset": 0, "world": n_local}
+
+
 def launch_workers(n: int) -> int:
     """One worker process per slot on this machine; any worker failing takes the gang down."""
-    port = _free_port()
+    rdv = rendezvous_env(n)
     procs: List[subprocess.Popen] = []
     threads = []
-    for rank in range(n):
-        env = dict(os.environ, RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(n), LOCAL_WORLD_SIZE=str(n),
-                   MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), DET_WORKER_PROCESS="1")
+    for local in range(n):
+        rank = rdv["offset"] + local
+        env = dict(os.environ, RANK=str(rank), LOCAL_RANK=str(local), WORLD_SIZE=str(rdv["world"]), LOCAL_WORLD_SIZE=str(n),
+                   MASTER_ADDR=rdv["addr"], MASTER_PORT=str(rdv["port"]), DET_WORKER_PROCESS="1")
         p = subprocess.Popen([sys.executable, "-m", "determined_b200.exec.harness"], env=env, stdout=subprocess.PIPE,
                              stderr=subprocess.STDOUT)
         procs.append(p)
@@ -115,6 +127,8 @@ def run_worker() -> int:
     logging.basicConfig(level=logging.DEBUG if env.debug else logging.INFO, format="%(levelname)s: %(message)s")
     dist = DistributedContext.from_environ()
     is_chief = dist.get_rank() == 0
+    logging.info(f"worker rank {dist.get_rank()} of {dist.get_size()} (local rank {dist.get_local_rank()}, "
+                 f"{dist.get_num_agents()} container(s)) on {os.environ.get('DET_AGENT_ID', 'this host')}")
     n_slots = max(len(env.slot_ids), 1)
     env.experiment_config.setdefault("resources", {})["slots_per_trial"] = max(dist.get_size(), 1) if dist.get_size() > 1 else env.experiment_config.get("resources", {}).get("slots_per_trial", 1)
     env._per_slot_batch_size, env._global_batch_size = env._calculate_batch_sizes()
@@ -174,6 +188,8 @@ def main() -> int:
     cfg = json.loads(os.environ.get("DET_EXPERIMENT_CONFIG", "{}"))
     native_parallel = cfg.get("resources", {}).get("native_parallel", False)
     n = len(slot_ids)
+    if int(os.environ.get("DET_NUM_CONTAINERS", "1")) > 1:
+        return launch_workers(max(n, 1))      # one of several containers of a trial: join the trial-wide process group
     if n > 1:
         # `native_parallel: true` (nn.DataParallel in the reference) maps onto the same multi-process path
         if native_parallel:

@@ -95,7 +95,9 @@ class TorchDistCommunicator(Communicator):
         self.device = device
         if use_p2p is None:
             use_p2p = os.environ.get("DET_DISABLE_P2P") != "1"
-        self.p2p = bool(use_p2p and device.type == "cuda" and self.size <= 8 and F.native_available())
+        # the peer-memory arena spans ONE node (NVLink / NVSwitch); a trial over several nodes reduces with NCCL
+        single_node = int(os.environ.get("LOCAL_WORLD_SIZE", str(self.size))) == self.size
+        self.p2p = bool(use_p2p and device.type == "cuda" and self.size <= 8 and single_node and F.native_available())
         self._regions: List[_SymmetricRegion] = []
         self._flags: Optional[_SymmetricRegion] = None
         self._epoch: Optional[torch.Tensor] = None
