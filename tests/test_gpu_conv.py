@@ -309,3 +309,24 @@ def test_darts_network_matches_cpu_and_trains():
                                 "searcher": {"name": "single", "metric": "top1_accuracy", "smaller_is_better": False, "max_length": {"batches": 100}}}).run()
     losses = [m["loss"] for m in tv.training_metrics]
     assert sum(losses[-5:]) < sum(losses[:5]), losses
+
+
+def test_gaea_supernet_on_gpu():
+    """The weight-sharing supernet (every candidate operation on every edge) trains on the sm_100a modules: both the
+    shared weights and the simplex-constrained architecture parameters move."""
+    from determined_b200.models import gaea_search as G
+    from determined_b200.ops import _native
+    from tests.harness_utils import TrainAndValidate, make_controller
+
+    before = _native.launch_count
+    hp = {"global_batch_size": 32, "learning_rate": 0.05, "arch_learning_rate": 0.5, "init_channels": 16, "layers": 3, "train_epochs": 5}
+    tv = TrainAndValidate()
+    c = make_controller(G.GAEASearchTrial, hp, tv.send(steps=2, validation_freq=2, scheduling_unit=5),
+                        exp_config={"data": {"train_size": 128, "validation_size": 64},
+                                    "searcher": {"name": "single", "metric": "top1_accuracy", "smaller_is_better": False, "max_length": {"batches": 100}}})
+    c.run()
+    a = c.trial.model.alphas_normal.detach().float().cpu()
+    assert torch.allclose(a.sum(-1), torch.ones(14), atol=1e-4) and (a - 1 / 8).abs().max() > 1e-4
+    assert all(torch.isfinite(torch.tensor(m["loss"])) for m in tv.training_metrics)
+    assert _native.launch_count - before > 500
+    assert len(c.trial.model.genotype().normal) == 8
