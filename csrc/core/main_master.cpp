@@ -50,6 +50,7 @@ int main(int argc, char** argv) {
       else if (a == "--repo-root") j["repo_root"] = next();
       else if (a == "--python") j["python"] = next();
       else if (a == "--slot-type") j["slot_type"] = next();
+      else if (a == "--telemetry") j["telemetry"] = det::Json::parse(next());     // {"enabled": true, "sink": "/path/events.jsonl"}
       else if (a == "--provisioner") j["provisioner"] = det::Json::parse(next());   // JSON object, see docs/cluster-config.md
       else if (a == "--resource-manager") j["resource_manager"] = det::Json::parse(next());   // {"type": "kubernetes", ...}
       else if (a == "--visible-gpus") j["visible_gpus"] = next();

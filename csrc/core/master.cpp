@@ -73,6 +73,7 @@ MasterConfig MasterConfig::from_json(const Json& j) {
   c.auth_required = j["auth_required"].as_bool(false) || j["security"]["auth_required"].as_bool(false);
   c.cluster_name = j["cluster_name"].str_or(c.cluster_name);
   c.provisioner = j["provisioner"];
+  c.telemetry = j["telemetry"];
   c.resource_manager = j["resource_manager"];
   if (c.resource_manager.is_object()) {
     const std::string t = c.resource_manager["type"].str_or("agent");
@@ -183,6 +184,15 @@ Master::Master(const MasterConfig& c) : cfg(c), store(c.data_dir), system(16) {
 }
 Master::~Master() { stop(); }
 
+void Master::report_telemetry(const std::string& event, const Json& properties) {
+  if (!cfg.telemetry.is_object() || !cfg.telemetry["enabled"].as_bool(false)) return;
+  const std::string sink = cfg.telemetry["sink"].str_or(cfg.data_dir + "/telemetry.jsonl");
+  Json e = obj({{"event", event}, {"timestamp", now_rfc3339()}, {"cluster_id", cluster_id}, {"version", "0.13.10.dev0+b200.1"},
+                {"properties", properties}});
+  std::lock_guard<std::mutex> g(log_mu_);
+  std::ofstream f(sink, std::ios::app);
+  if (f) f << e.dump() << "\n";
+}
 void Master::log(const std::string& level, const std::string& msg) {
   Json e = obj({{"time", now_rfc3339()}, {"level", level}, {"message", msg}});
   {
@@ -311,6 +321,8 @@ long long Master::create_experiment(const Json& config, const Json& model_defini
                                     {"description", config["description"]}, {"labels", config["labels"]}, {"best_validation", Json()}}));
   system.actor_of("experiments/" + std::to_string(id), make_experiment(this, id, false), experiments_root);
   log("info", "created experiment " + std::to_string(id));
+  report_telemetry("experiment_created", obj({{"id", id}, {"searcher", config["searcher"]["name"]}, {"slots_per_trial", config["resources"]["slots_per_trial"]},
+                                              {"num_hparams", static_cast<long long>(config["hyperparameters"].size())}}));
   return id;
 }
 
@@ -430,6 +442,8 @@ int Master::start() {
   if (port < 0) throw std::runtime_error("cannot bind " + cfg.host + ":" + std::to_string(cfg.port));
   log("info", "master listening on " + cfg.host + ":" + std::to_string(port) + " with " + std::to_string(devices.size()) + " local slots (" + cfg.scheduler + ")");
   if (kube) kube->start();
+  report_telemetry("master_started", obj({{"scheduler", cfg.scheduler}, {"resource_manager", kube ? "kubernetes" : "agent"},
+                                          {"local_slots", static_cast<long long>(devices.size())}, {"provisioner", cfg.provisioner.is_object()}}));
   restore_experiments();
   return port;
 }

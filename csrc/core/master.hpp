@@ -45,6 +45,7 @@ struct MasterConfig {
   std::string cluster_name = "b200-box";
   Json provisioner;                      // {max_instances, slots_per_instance, max_idle_agent_period, ...} or null
   Json resource_manager;                 // null / {type: agent} or {type: kubernetes, namespace, api_server, image, ...}
+  Json telemetry;                        // {enabled: bool, sink: path}; events go to a local JSONL file (no network here)
   int scheduler_tick_ms = 500;
   int terminate_timeout_ms = 60000;
 
@@ -82,6 +83,8 @@ class Master {
 
   // log ring served at /logs (reference: master/pkg/logger LogBuffer)
   void log(const std::string& level, const std::string& msg);
+  // usage telemetry (reference: master/internal/telemetry — Segment track calls): one JSON line per event, opt-in
+  void report_telemetry(const std::string& event, const Json& properties);
   std::vector<Json> recent_logs(size_t limit);
 
   // services used by actors

@@ -539,6 +539,7 @@ class ExperimentActor : public Actor {
     const std::string terminal = state_ == "STOPPING_COMPLETED" ? "COMPLETED" : state_ == "STOPPING_CANCELED" ? "CANCELED" : "ERROR";
     set_state(ctx, terminal);
     m_->log("info", "experiment " + std::to_string(id_) + " finished: " + terminal);
+    m_->report_telemetry("experiment_state_changed", obj({{"id", id_}, {"state", terminal}, {"num_trials", static_cast<long long>(m_->store.list("trials", [this](const Json& r) { return r["experiment_id"].as_int() == id_; }).size())}}));
     m_->spawn_checkpoint_gc(id_);
     ctx.stop_self();
   }

@@ -288,3 +288,43 @@ def test_service_task_readiness_and_proxy(slotless_master, tmp_path):
     assert e.value.code == 502
     plain = c.request("POST", "/api/v1/commands", {"argv": ["/bin/true"]})
     assert "proxy_port" not in plain["spec"]
+
+
+def test_telemetry_sink_is_opt_in(tmp_path):
+    """Usage telemetry (reference: master/internal/telemetry, Segment): off unless configured; when on, one JSON line per
+    event in a local file."""
+    def run_master(extra):
+        port_file = tmp_path / f"port-{len(extra)}"
+        proc = subprocess.Popen([str(LIB / "det-master"), "--port", "0", "--data-dir", str(tmp_path / f"data{len(extra)}"), "--artificial-slots", "1",
+                                 "--repo-root", str(ROOT), "--python", sys.executable, "--print-port-file", str(port_file)] + extra,
+                                stdout=open(tmp_path / "master.log", "a"), stderr=subprocess.STDOUT, env=dict(os.environ, DET_CONFIG_DIR=str(tmp_path / "cfg")))
+        for _ in range(200):
+            if port_file.exists() and port_file.read_text().strip():
+                break
+            time.sleep(0.05)
+        return proc, int(port_file.read_text())
+
+    sink = tmp_path / "events.jsonl"
+    proc, port = run_master(["--telemetry", json.dumps({"enabled": True, "sink": str(sink)})])
+    try:
+        os.environ["DET_CONFIG_DIR"] = str(tmp_path / "cfg")
+        d = Determined(f"127.0.0.1:{port}")
+        cfg = {"entrypoint": "model_def:XorTrial", "hyperparameters": {"global_batch_size": 8, "hidden_size": 4, "learning_rate": 0.5},
+               "searcher": {"name": "single", "metric": "validation_loss", "max_length": {"batches": 10}}, "scheduling_unit": 10,
+               "checkpoint_storage": {"type": "shared_fs", "host_path": str(tmp_path / "ckpts")}}
+        exp = d.create_experiment(cfg, MODEL_DIR)
+        assert exp.wait(timeout=120) == "COMPLETED"
+        time.sleep(0.3)
+    finally:
+        proc.terminate()
+        proc.wait(timeout=5)
+    events = [json.loads(l) for l in sink.read_text().splitlines()]
+    names = [e["event"] for e in events]
+    assert names[0] == "master_started" and "experiment_created" in names and "experiment_state_changed" in names
+    created = events[names.index("experiment_created")]
+    assert created["properties"]["searcher"] == "single" and created["cluster_id"]
+    assert events[names.index("experiment_state_changed")]["properties"]["state"] == "COMPLETED"
+    proc, _ = run_master([])
+    proc.terminate()
+    proc.wait(timeout=5)
+    assert not (tmp_path / "data0" / "telemetry.jsonl").exists()
