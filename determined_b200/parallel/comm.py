@@ -92,6 +92,7 @@ class TorchDistCommunicator(Communicator):
         self.dist = dist
         self.rank, self.size = dist.get_rank(), dist.get_world_size()
         self.local_rank = int(os.environ.get("LOCAL_RANK", self.rank))
+        self.compress_gradients = False    # set from optimizations.gradient_compression by the trial context
         self.device = device
         if use_p2p is None:
             use_p2p = os.environ.get("DET_DISABLE_P2P") != "1"
@@ -196,7 +197,17 @@ class TorchDistCommunicator(Communicator):
     def allreduce_grad_bucket(self, flat_g, scale, scale_dev=None, sumsq_dev=None, found_inf_dev=None, max_blocks: int = 0) -> bool:
         region = self._region_of(flat_g) if self.p2p else None
         if region is None:
-            self.dist.all_reduce(flat_g)
+            if self.compress_gradients:
+                # `optimizations.gradient_compression` (reference: hvd.Compression.fp16, _pytorch_context.py:191-198): halve
+                # the bytes on the wire of the library collective — the path a job takes once it leaves the NVSwitch domain,
+                # where bandwidth is the scarce thing. bf16 keeps fp32's range, so no overflow handling is needed; gloo
+                # (CPU tests) has no bf16 sum and gets fp16 like the reference.
+                wire = torch.bfloat16 if flat_g.is_cuda else torch.float16
+                packed = flat_g.to(wire)
+                self.dist.all_reduce(packed)
+                flat_g.copy_(packed)
+            else:
+                self.dist.all_reduce(flat_g)
             return False
         off = flat_g.data_ptr() - region.base
         n = flat_g.numel()
@@ -219,7 +230,12 @@ class TorchDistCommunicator(Communicator):
 
     def allreduce_tensors(self, tensors, scale) -> None:
         for t in tensors:
-            self.dist.all_reduce(t)
+            if self.compress_gradients and t.dtype == torch.float32:
+                packed = t.to(torch.bfloat16 if t.is_cuda else torch.float16)     # see allreduce_grad_bucket
+                self.dist.all_reduce(packed)
+                t.copy_(packed)
+            else:
+                self.dist.all_reduce(t)
             if scale != 1.0:
                 t.mul_(scale)
 

@@ -131,6 +131,10 @@ class PyTorchTrialContext(TrialContext):
         self.aggregation_frequency = int(opt_cfg.get("aggregation_frequency", 1))
         self.average_aggregated_gradients = bool(opt_cfg.get("average_aggregated_gradients", True))
         self.gradient_compression = bool(opt_cfg.get("gradient_compression", False))
+        if self.gradient_compression and hasattr(self.comm, "compress_gradients"):
+            # Inside one NVSwitch domain the fused fp32 all-reduce is ~4 % of a BERT-base step and stays fp32; the flag
+            # takes effect on the NCCL path (trials spanning nodes, or DET_DISABLE_P2P=1).
+            self.comm.compress_gradients = True
         if self.aggregation_frequency < 1:
             raise ValueError("optimizations.aggregation_frequency must be >= 1")
         self.device = self._init_device()

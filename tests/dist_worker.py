@@ -22,6 +22,12 @@ def main() -> None:
     elif case == "xor_agg":
         trial, hp, steps, unit = M.XorTrial, {"hidden_size": 4, "learning_rate": 0.05, "global_batch_size": 8, "shuffle": False}, 4, 2
         cfg = {"optimizations": {"aggregation_frequency": 2, "average_training_metrics": True}}
+    elif case == "xor_compressed":
+        trial, hp, steps, unit = M.XorTrial, {"hidden_size": 4, "learning_rate": 0.05, "global_batch_size": 8, "shuffle": False}, 4, 2
+        cfg = {"optimizations": {"gradient_compression": True, "average_training_metrics": True}}
+    elif case == "xor_plain":
+        trial, hp, steps, unit = M.XorTrial, {"hidden_size": 4, "learning_rate": 0.05, "global_batch_size": 8, "shuffle": False}, 4, 2
+        cfg = {"optimizations": {"average_training_metrics": True}}
     elif case in ("mnist_gpu", "mnist_gpu_overlap"):
         from determined_b200.models import vision_trials as VT
 

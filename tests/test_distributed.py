@@ -67,3 +67,17 @@ def test_dp2_aggregation_frequency_keeps_replicas_identical(tmp_path):
     a, b = rep["params_by_rank"]
     assert a == b
     assert len(rep["training"]) == 8 and all(np.isfinite(m["loss"]) for m in rep["training"])
+
+
+def test_dp2_gradient_compression_half_precision_wire(tmp_path):
+    """optimizations.gradient_compression (reference: hvd.Compression.fp16): gradients cross the wire in half precision;
+    replicas stay identical and the trajectory stays within half-precision rounding of the uncompressed one."""
+    (tmp_path / "a").mkdir()
+    (tmp_path / "b").mkdir()
+    comp = run_ranks(2, "xor_compressed", tmp_path / "a", {"CUDA_VISIBLE_DEVICES": ""})
+    plain = run_ranks(2, "xor_plain", tmp_path / "b", {"CUDA_VISIBLE_DEVICES": ""})
+    a, b = comp["params_by_rank"]
+    assert a == b
+    pa = np.array(a), np.array(plain["params_by_rank"][0])
+    assert not np.array_equal(*pa), "compression left no trace: the flag did not reach the collective"
+    assert np.abs(pa[0] - pa[1]).max() < 5e-3 * max(1.0, np.abs(pa[1]).max())
