@@ -21,6 +21,7 @@ from __future__ import annotations
 
 import dataclasses
 import math
+import os
 from typing import Optional, Tuple
 
 import torch
@@ -50,7 +51,7 @@ class BertConfig:
 # The LayerNorm backward kernel can also emit the bias gradient of the GEMM in front of it (column sums of its output).
 # Measured on B200 it LOSES to the separate column-sum kernel — 25.61 vs 24.71 ms per BERT-base step — because the sums go
 # through shared-memory atomics inside the row loop; it stays opt-in (DET_LN_FUSED_BIAS=1) for shapes where launches dominate.
-_FUSED_BIAS = __import__("os").environ.get("DET_LN_FUSED_BIAS", "0") == "1"
+_FUSED_BIAS = os.environ.get("DET_LN_FUSED_BIAS", "0") == "1"
 
 
 def _gelu(x: torch.Tensor) -> torch.Tensor:
