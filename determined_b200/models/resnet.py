@@ -34,8 +34,12 @@ class Bottleneck(nn.Module):
         self.downsample = downsample
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        identity = x if self.downsample is None else conv_bn(self.downsample[0], self.downsample[1], x)
-        out = conv_bn(self.conv1, self.bn1, x)
+        if self.downsample is None:
+            # the skip connection leaves through conv1's autograd node: its gradient is added in conv1's dgrad epilogue
+            out, identity = conv_bn(self.conv1, self.bn1, x, passthrough=True)
+        else:
+            identity = conv_bn(self.downsample[0], self.downsample[1], x)
+            out = conv_bn(self.conv1, self.bn1, x)
         out = conv_bn(self.conv2, self.bn2, out)
         return conv_bn(self.conv3, self.bn3, out, identity)
 

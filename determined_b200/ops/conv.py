@@ -76,7 +76,10 @@ def _pad_cols(t: torch.Tensor, cols: int) -> torch.Tensor:
 # ------------------------------------------------------------------------------------------------
 class _Conv2dFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, pad, relu, want_stats=False):
+    def forward(ctx, x, weight, bias, stride, pad, relu, want_stats=False, passthrough=False):
+        # passthrough: also hand x back as an output. A residual block reads its input twice (first convolution + skip
+        # connection); routing the skip through this node lets backward ADD the skip gradient in the data-gradient GEMM's
+        # epilogue instead of leaving a separate elementwise add to autograd.
         N, H, W, Cin = x.shape
         Cout, R, S, _ = weight.shape
         ph, pw = pad
@@ -124,16 +127,22 @@ class _Conv2dFn(torch.autograd.Function):
         ctx.save_for_backward(x, y if relu else None)
         ctx.weight, ctx.bias = weight, bias
         ctx.cfg = (kind, stride, ph, pw, relu)
+        ctx.outs = (bool(want_stats), bool(passthrough))
         note_param_use(ctx, weight, bias)
+        outs = [y]
         if want_stats:
             if sums is None:   # this path's epilogue cannot produce them: signal the caller to run the reduction kernel
                 sums = torch.empty(0, dtype=torch.float32, device=x.device)
             ctx.mark_non_differentiable(sums)
-            return y, sums
-        return y
+            outs.append(sums)
+        if passthrough:
+            outs.append(x.view_as(x))
+        return outs[0] if len(outs) == 1 else tuple(outs)
 
     @staticmethod
-    def backward(ctx, dy, _dsums=None):
+    def backward(ctx, dy, *rest):
+        want_stats, passthrough = ctx.outs
+        dskip = rest[int(want_stats)] if passthrough else None      # gradient that arrived through the passthrough output
         x, y = ctx.saved_tensors
         weight, bias = ctx.weight, ctx.bias
         kind, stride, ph, pw, relu = ctx.cfg
@@ -158,7 +167,12 @@ class _Conv2dFn(torch.autograd.Function):
                        a_mn=True, b_mn=True, out_mode=F.OUT_F32_ATOMIC_ADD)
             if need_dx:
                 dx = torch.empty_like(x)
-                F.gemm(dy.view(M, Cout), w.view(Cout, Cin), dx.view(M, Cin), M, Cin, Cout, b_mn=True)
+                if dskip is not None:      # dx = dy W + dskip in one kernel
+                    F.gemm(dy.view(M, Cout), w.view(Cout, Cin), dx.view(M, Cin), M, Cin, Cout, b_mn=True, epi=F.EPI_BIAS_RESID,
+                           aux_in=dskip.contiguous().view(M, Cin))
+                    dskip = None
+                else:
+                    F.gemm(dy.view(M, Cout), w.view(Cout, Cin), dx.view(M, Cin), M, Cin, Cout, b_mn=True)
         elif kind == "implicit":
             if weight.requires_grad:
                 F.conv2d_implicit(F.CONV_WGRAD, dy, x, grad_buffer(weight), N, H, W, Cin, Cout, R, S, ph, pw)
@@ -187,8 +201,10 @@ class _Conv2dFn(torch.autograd.Function):
                 dcol = torch.empty(M, Kp, dtype=torch.bfloat16, device=x.device)
                 F.gemm(dyp, wk, dcol, M, Kp, Cp, b_mn=True)
                 dx = F.col2im(dcol, N, H, W, Cin, R, S, stride, ph, pw, Kp)
+        if dskip is not None:
+            dx = dskip if dx is None else dx + dskip
         notify_grads_written(weight, bias)
-        return dx, None, None, None, None, None, None
+        return dx, None, None, None, None, None, None, None
 
 
 class Conv2d(nn.Module):
@@ -493,7 +509,7 @@ class BatchNorm2d(nn.BatchNorm2d):
         return from_nhwc(y)
 
 
-def conv_bn(conv: "Conv2d", bn: "BatchNorm2d", x: torch.Tensor, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+def conv_bn(conv: "Conv2d", bn: "BatchNorm2d", x: torch.Tensor, residual: Optional[torch.Tensor] = None, passthrough: bool = False):
     """``bn(conv(x), residual)`` with the BatchNorm batch statistics taken from the convolution's own epilogue: the
     kernel that writes the convolution output also accumulates per-channel sum and sum of squares, so training-mode
     BatchNorm needs no statistics pass over that tensor. Falls back to the two separate modules whenever that is not
@@ -501,8 +517,10 @@ def conv_bn(conv: "Conv2d", bn: "BatchNorm2d", x: torch.Tensor, residual: Option
     C = bn.num_features
     use_batch = bn.training or not bn.track_running_stats
     if not (x.is_cuda and use_batch and conv.activation is None and C % 8 == 0 and (C <= 2048 or C % 2048 == 0)):
-        return bn(conv(x), residual)
-    y, sums = _Conv2dFn.apply(to_nhwc(x), conv.weight, conv.bias, conv.stride, conv.padding, False, True)
+        out = bn(conv(x), residual)
+        return (out, x) if passthrough else out
+    res = _Conv2dFn.apply(to_nhwc(x), conv.weight, conv.bias, conv.stride, conv.padding, False, True, passthrough)
+    y, sums = res[0], res[1]
     rn = to_nhwc(residual) if residual is not None else None
     track = bn.training and bn.track_running_stats
     if track and bn.num_batches_tracked is not None:
@@ -514,7 +532,7 @@ def conv_bn(conv: "Conv2d", bn: "BatchNorm2d", x: torch.Tensor, residual: Option
     else:
         mean, rstd = F.bn_stats(y, C, rm, rv, bn.eps, mom)
     out = _BatchNormFn.apply(y, rn, bn.weight, bn.bias, mean, rstd, _ACT_CODES[bn.activation], bn.negative_slope)
-    return from_nhwc(out)
+    return (from_nhwc(out), from_nhwc(res[2])) if passthrough else from_nhwc(out)
 
 
 # ------------------------------------------------------------------------------------------------
