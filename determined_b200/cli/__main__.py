@@ -2,7 +2,7 @@
 
 Verbs follow the reference CLI (``cli/determined_cli/cli.py:40-283``, ``experiment.py:630-924``):
 ``experiment {list,describe,config,create,activate,pause,cancel,kill,archive,unarchive,delete,wait,label,set,
-list-trials,list-checkpoints,download-model-def}``, ``trial {describe,logs,kill,download}``,
+list-trials,list-checkpoints,download,download-model-def}``, ``trial {describe,logs,kill,download}``,
 ``checkpoint {describe,download}``, ``task list``, ``preview-search``, ``slot``/``agent``, ``master {config,logs,info}``,
 ``user``, ``template``, ``model``, ``cmd``/``notebook``/``shell``/``tensorboard``, plus ``master up`` / ``agent detect``
 that wrap the native daemons.
@@ -224,6 +224,19 @@ def trial_logs(a: argparse.Namespace) -> int:
 def trial_kill(a: argparse.Namespace) -> int:
     Determined(a.master, a.user).get_trial(a.trial_id).kill()
     print(f"Killed trial {a.trial_id}")
+    return 0
+
+
+def experiment_download(a: argparse.Namespace) -> int:
+    """Best ``--top-n`` checkpoints of the experiment, one directory per checkpoint uuid (reference:
+    ``cli/determined_cli/experiment.py:384-398``)."""
+    exp = Determined(a.master, a.user).get_experiment(a.experiment_id)
+    smaller = None if a.smaller_is_better is None else a.smaller_is_better.lower() in ("1", "true", "yes")
+    top = pathlib.Path(a.output_dir)
+    top.mkdir(parents=True, exist_ok=True)
+    for ck in exp.top_n_checkpoints(a.top_n, sort_by=a.sort_by, smaller_is_better=smaller):
+        path = ck.download(str(top / ck.uuid))
+        print(path if a.quiet else f"Checkpoint {ck.uuid} (trial {ck.trial_id}, batch {ck.batch_number}): {path}")
     return 0
 
 
@@ -492,6 +505,8 @@ def build_parser() -> argparse.ArgumentParser:
     cmd(e, "label", experiment_label, A("action", choices=["add", "remove"]), A("experiment_id", type=int), A("label"))
     cmd(e, "list-trials", experiment_list_trials, A("experiment_id", type=int), aliases=["lt"])
     cmd(e, "list-checkpoints", experiment_list_checkpoints, A("experiment_id", type=int), aliases=["lc"])
+    cmd(e, "download", experiment_download, A("experiment_id", type=int), A("--output-dir", "-o", default="checkpoints"), A("--top-n", type=int, default=1),
+        A("--sort-by"), A("--smaller-is-better"), A("--quiet", "-q", action="store_true"))
     cmd(e, "download-model-def", experiment_download_model_def, A("experiment_id", type=int), A("--output-dir", "-o"))
     t = group("trial", ["t"])
     cmd(t, "describe", trial_describe, A("trial_id", type=int), A("--metrics", action="store_true"), A("--json", action="store_true"))

@@ -68,6 +68,12 @@ def test_single_experiment_completes_with_checkpoint_and_logs(master):
     assert any("Saved trial to checkpoint" in l["message"] or "checkpoint" in l["message"].lower() for l in logs)
     ck.add_metadata({"note": "best"})
     assert d.get_checkpoint(ck.uuid).metadata["note"] == "best"
+    # `det experiment download`: the experiment's best checkpoint, one directory per uuid
+    out = subprocess.run([sys.executable, "-m", "determined_b200.cli", "-m", master["url"], "experiment", "download", str(exp.id),
+                          "-o", str(master["tmp"] / "dl3"), "--quiet"], capture_output=True, text=True, cwd=str(ROOT), timeout=120)
+    assert out.returncode == 0, out.stderr
+    got = pathlib.Path(out.stdout.strip().splitlines()[-1])
+    assert got.parent == master["tmp"] / "dl3" and (got / "state_dict.pth").exists() and (got / "metadata.json").exists()
 
 
 def test_adaptive_asha_packs_trials_and_gc_runs(master):
