@@ -80,6 +80,10 @@ class PyTorchTrialController:
         self._load()
         self._broadcast_initial_state()
         self._graphed: Optional[GraphedTrainBatch] = None
+        if context.device.type == "cuda":
+            # the dropout kernels hash (seed, step counter, element index); the counter starts at a point fixed by the
+            # trial seed and the batches already trained, so a resumed trial does not redraw the masks it began with
+            F.set_step_seed(env.trial_seed + env.initial_workload.total_batches_processed, context.device)
         if context.experimental.cuda_graphs and context.device.type == "cuda":
             self._graphed = GraphedTrainBatch(self.trial, context)
 
@@ -263,6 +267,8 @@ class PyTorchTrialController:
                 batch = ctx.to_device(batch)
                 with ctx.autocast():
                     tr = self.trial.train_batch(batch=batch, epoch_idx=epoch_idx, batch_idx=batch_idx)
+                if ctx.device.type == "cuda":
+                    F.advance_step_seed(ctx.device)     # fresh dropout masks for the next batch
             if isinstance(tr, torch.Tensor):
                 tr = {"loss": tr}
             if not isinstance(tr, dict) or "loss" not in tr:

@@ -59,7 +59,9 @@ class GraphedTrainBatch:
     def _eager(self, host_batch: Any, epoch_idx: int, batch_idx: int) -> Any:
         batch = self.context.to_device(host_batch)
         with self.context.autocast():
-            return self.trial.train_batch(batch=batch, epoch_idx=epoch_idx, batch_idx=batch_idx)
+            out = self.trial.train_batch(batch=batch, epoch_idx=epoch_idx, batch_idx=batch_idx)
+        F.advance_step_seed(self.context.device)
+        return out
 
     def _stage(self, host_batch: Any) -> None:
         leaves: List[torch.Tensor] = []

@@ -25,6 +25,8 @@ from determined_b200 import _execution, load  # noqa: E402
 from determined_b200 import pytorch as dp  # noqa: E402
 from determined_b200 import workload as wl  # noqa: E402
 from determined_b200.models import darts_trial as DT
+from determined_b200.models import darts_rnn_trial as DR
+from determined_b200.models import detr_trial as DETR
 from determined_b200.models import squad_trials as ST
 from determined_b200.models import vision_trials as VT  # noqa: E402
 from determined_b200.ops import _native  # noqa: E402
@@ -69,6 +71,13 @@ MODELS = {
     "mnist": (VT.MNistTrial, {"learning_rate": 1.0}, (1, 28, 28), "images/s"),
     # DARTS CIFAR-10 evaluation network (20 cells, separable / dilated convolutions), reference batch 96
     "darts": (DT.DARTSCNNTrial, {"learning_rate": 0.025, "init_channels": 32, "layers": 20, "use_cuda_graphs": True}, (3, 32, 32), "images/s"),
+    # DARTS recurrent cell language model at the published sizes (850 wide, vocabulary 10,000, 35-token windows, batch 64)
+    "darts_rnn": (DR.DARTSRNNTrial, dict({f"node{i + 1}_edge": e for i, e in enumerate([0, 1, 1, 1, 2, 5, 3, 5])},
+                                         **{f"node{i + 1}_op": o for i, o in enumerate(["sigmoid", "relu", "relu", "identity", "tanh", "sigmoid", "tanh", "relu"])},
+                                         learning_rate=20.0, fixed_seq_len=True, use_cuda_graphs=True, train_tokens=400_000),
+                  (1, 1, 35), "windows/s"),
+    # DETR (ResNet-50 trunk, 6 + 6 transformer layers, 100 queries, Hungarian matching on the host) on padded ~512 px scenes
+    "detr": (DETR.DETRTrial, {"lr": 1e-4, "lr_backbone": 1e-5, "image_size": 512, "num_classes": 91, "dataset_size": 512}, (3, 512, 512), "images/s"),
     # BERT-base span model at the SQuAD shape (seq 384): the tiled attention kernels + span head
     "bert_squad": (ST.BertSquadTrial, {"learning_rate": 3e-5, "max_seq_length": 384, "use_cuda_graphs": True}, (1, 1, 384), "samples/s"),
     # ALBERT-xxlarge sizes (hidden 4096, 64 heads, one shared layer applied 12 times)
