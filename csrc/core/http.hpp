@@ -18,6 +18,7 @@
 #include <vector>
 
 #include <netdb.h>
+#include <poll.h>
 
 #include "json.hpp"
 
@@ -42,6 +43,9 @@ struct HttpResponse {
   int status = 200;
   std::string content_type = "application/json";
   std::string body;
+  // When set, the server hands the client socket to this function instead of writing a response (protocol upgrades:
+  // the handler speaks for itself and returns when the conversation is over; the server closes the socket afterwards).
+  std::function<void(int)> hijack;
   static HttpResponse json(const Json& j, int status = 200) { HttpResponse r; r.status = status; r.body = j.dump(); return r; }
   static HttpResponse error(int status, const std::string& msg) {
     Json j = Json::object();
@@ -171,6 +175,11 @@ class HttpServer {
     req.remote_addr = remote_addr;
     if (read_request(c, req)) {
       HttpResponse resp = dispatch(req);
+      if (resp.hijack) {
+        resp.hijack(c);
+        ::close(c);
+        return;
+      }
       static const std::map<int, const char*> reason = {{200, "OK"}, {201, "Created"}, {204, "No Content"}, {400, "Bad Request"},
                                                         {401, "Unauthorized"}, {403, "Forbidden"}, {404, "Not Found"},
                                                         {409, "Conflict"}, {500, "Internal Server Error"}};
@@ -332,6 +341,58 @@ inline HttpResponse http_forward(const std::string& host, int port, const HttpRe
     out.body = body;
   }
   return out;
+}
+
+// Protocol-upgrade tunnel (WebSocket): replay the upgrade request against host:port, then copy bytes both ways between
+// the client socket and the task until either side closes or nothing moves for `idle_s` seconds. The 101 response is the
+// task's own; the master does not interpret frames.
+inline void http_tunnel(const std::string& host, int port, const HttpRequest& req, const std::string& path, int client, int idle_s = 3600) {
+  auto send_all = [](int fd, const char* p, size_t n) {
+    while (n > 0) {
+      ssize_t k = ::send(fd, p, n, MSG_NOSIGNAL);
+      if (k <= 0) return false;
+      p += k;
+      n -= static_cast<size_t>(k);
+    }
+    return true;
+  };
+  int fd = ::socket(AF_INET, SOCK_STREAM | SOCK_CLOEXEC, 0);
+  sockaddr_in addr{};
+  addr.sin_family = AF_INET;
+  addr.sin_port = htons(static_cast<uint16_t>(port));
+  addr.sin_addr.s_addr = resolve_ipv4(host);
+  if (fd < 0 || ::connect(fd, reinterpret_cast<sockaddr*>(&addr), sizeof addr) < 0) {
+    static const char bad[] = "HTTP/1.1 502 Bad Gateway\r\nContent-Length: 0\r\nConnection: close\r\n\r\n";
+    send_all(client, bad, sizeof bad - 1);
+    if (fd >= 0) ::close(fd);
+    return;
+  }
+  std::ostringstream os;
+  os << req.method << " " << path << " HTTP/1.1\r\nHost: " << host << ":" << port << "\r\n";
+  for (auto& kv : req.headers) {
+    if (kv.first == "host" || kv.first == "content-length" || kv.first == "authorization") continue;
+    os << kv.first << ": " << kv.second << "\r\n";
+  }
+  os << "\r\n" << req.body;
+  const std::string head = os.str();
+  if (send_all(fd, head.data(), head.size())) {
+    pollfd fds[2] = {{client, POLLIN, 0}, {fd, POLLIN, 0}};
+    char buf[16384];
+    bool open = true;
+    while (open) {
+      const int ready = ::poll(fds, 2, idle_s * 1000);
+      if (ready <= 0) break;
+      for (int i = 0; i < 2 && open; ++i) {
+        if (fds[i].revents & POLLIN) {
+          const ssize_t n = ::recv(fds[i].fd, buf, sizeof buf, 0);
+          if (n <= 0 || !send_all(fds[1 - i].fd, buf, static_cast<size_t>(n))) open = false;
+        } else if (fds[i].revents & (POLLHUP | POLLERR | POLLNVAL)) {
+          open = false;
+        }
+      }
+    }
+  }
+  ::close(fd);
 }
 
 }  // namespace det

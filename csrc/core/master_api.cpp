@@ -114,7 +114,7 @@ void Master::register_routes() {
     s["enabled"] = true;
     return ok(s);
   });
-  // ---- reverse proxy to service tasks (reference: master/internal/proxy/proxy.go; HTTP only, no WebSocket upgrade) ----
+  // ---- reverse proxy to service tasks (reference: master/internal/proxy/proxy.go; HTTP replayed, Upgrade / WebSocket handshakes tunnelled) ----
   for (const char* method : {"GET", "POST", "PUT", "PATCH", "DELETE"}) {
     auto fwd = [m](const HttpRequest& r) {
       Json c = m->store.get("commands", r.params.at("id"));
@@ -125,7 +125,15 @@ void Master::register_routes() {
       auto it = r.params.find("*");
       if (it != r.params.end()) path += it->second;
       if (!r.query_string.empty()) path += "?" + r.query_string;
-      return http_forward(c["proxy_host"].str_or("127.0.0.1"), static_cast<int>(c["proxy_port"].as_int()), r, path);
+      const std::string host = c["proxy_host"].str_or("127.0.0.1");
+      const int port = static_cast<int>(c["proxy_port"].as_int());
+      auto up = r.headers.find("upgrade");
+      if (up != r.headers.end() && !up->second.empty()) {
+        HttpResponse t;
+        t.hijack = [host, port, r, path](int client) { http_tunnel(host, port, r, path, client); };
+        return t;
+      }
+      return http_forward(host, port, r, path);
     };
     http.route(method, "/proxy/:id", fwd);
     http.route(method, "/proxy/:id/*", fwd);

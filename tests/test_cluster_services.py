@@ -290,6 +290,42 @@ def test_service_task_readiness_and_proxy(slotless_master, tmp_path):
     assert "proxy_port" not in plain["spec"]
 
 
+def test_proxy_tunnels_protocol_upgrades(slotless_master):
+    """A request with an ``Upgrade:`` header (WebSocket) is not replayed as HTTP: the master forwards the handshake and
+    then copies bytes both ways, so interactive services (Jupyter kernels, terminals) work behind ``/proxy/<id>/``."""
+    import socket
+
+    c = MasterClient("127.0.0.1", slotless_master["port"])
+    script = str(ROOT / "tests" / "fixtures" / "ws_echo.py")
+    cmd = c.request("POST", "/api/v1/commands", {"argv": [sys.executable, script, "{port}"], "proxy": True, "description": "ws echo"})
+    try:
+        for _ in range(150):
+            cur = c.request("GET", f"/api/v1/commands/{cmd['id']}")
+            if cur.get("is_ready"):
+                break
+            time.sleep(0.1)
+        assert cur["is_ready"]
+        s = socket.create_connection(("127.0.0.1", slotless_master["port"]), timeout=10)
+        s.sendall((f"GET /proxy/{cmd['id']}/api/kernels/1/channels?session_id=7 HTTP/1.1\r\nHost: x\r\nUpgrade: websocket\r\n"
+                   "Connection: Upgrade\r\nSec-WebSocket-Key: abc123==\r\nSec-WebSocket-Version: 13\r\n\r\n").encode())
+        head = b""
+        while b"\r\n\r\n" not in head:
+            head += s.recv(4096)
+        text = head.decode()
+        assert text.startswith("HTTP/1.1 101") and "X-Path: /api/kernels/1/channels?session_id=7" in text and "X-Key: abc123==" in text
+        for msg in (b"hello", b"second frame"):
+            s.sendall(msg)
+            got = b""
+            while len(got) < len(msg):
+                got += s.recv(4096)
+            assert got == msg.upper()
+        s.sendall(b"bye")
+        assert s.recv(4096) == b""          # the task closed its side; the tunnel closes ours
+        s.close()
+    finally:
+        c.request("POST", f"/api/v1/commands/{cmd['id']}/kill")
+
+
 def test_telemetry_sink_is_opt_in(tmp_path):
     """Usage telemetry (reference: master/internal/telemetry, Segment): off unless configured; when on, one JSON line per
     event in a local file."""
