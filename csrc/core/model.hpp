@@ -300,8 +300,10 @@ inline Json resolve_experiment_config(const Json& user, const Json* master_stora
   Json cfg = default_experiment_config();
   if (master_storage && master_storage->is_object()) cfg["checkpoint_storage"] = master_storage->deep_copy();
   if (tmpl && tmpl->is_object()) json_merge(cfg, *tmpl);
-  // a user-supplied checkpoint_storage of a different type replaces the default wholesale (keeps save_* defaults)
+  // a user-supplied checkpoint_storage of a different type replaces the default wholesale (keeps save_* defaults); one
+  // that names no type (only save_* policies, say) is merged into the default location
   if (user.contains("checkpoint_storage") && user["checkpoint_storage"].is_object() &&
+      user["checkpoint_storage"].contains("type") &&
       user["checkpoint_storage"]["type"].str_or("") != cfg["checkpoint_storage"]["type"].str_or("")) {
     Json keep = Json::object();
     for (const char* k : {"save_experiment_best", "save_trial_best", "save_trial_latest"}) keep[k] = cfg["checkpoint_storage"][k];

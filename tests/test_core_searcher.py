@@ -159,6 +159,14 @@ def test_config_resolution_and_validation():
     assert cfg["scheduling_unit"] == 100 and cfg["max_restarts"] == 5 and cfg["resources"]["slots_per_trial"] == 1
     assert cfg["optimizations"]["aggregation_frequency"] == 1 and cfg["optimizations"]["mixed_precision"] == "O0"
     assert cfg["checkpoint_storage"]["save_trial_best"] == 1 and cfg["reproducibility"]["experiment_seed"] == 5
+    # a checkpoint_storage section that only sets retention policies keeps the default location; one of another type
+    # replaces the location but keeps the policy defaults
+    base = {"entrypoint": "model_def:T", "hyperparameters": {"global_batch_size": 64},
+            "searcher": {"name": "single", "metric": "loss", "max_length": {"batches": 10}}}
+    cs = core.resolve_config(dict(base, checkpoint_storage={"save_trial_latest": 5}))["checkpoint_storage"]
+    assert cs["type"] == "shared_fs" and cs["host_path"] and cs["save_trial_latest"] == 5
+    cs = core.resolve_config(dict(base, checkpoint_storage={"type": "s3", "bucket": "b"}))["checkpoint_storage"]
+    assert cs["type"] == "s3" and "host_path" not in cs and cs["save_trial_best"] == 1
     errs = core.check_config({"entrypoint": "m:T", "hyperparameters": {}, "searcher": {"name": "random", "metric": "x"}})
     joined = " ".join(errs)
     assert "global_batch_size" in joined and "max_trials" in joined and "max_length" in joined
