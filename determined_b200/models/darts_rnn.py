@@ -13,14 +13,19 @@ What is different is the schedule, which is what decides the speed of a strictly
   ``x W0[:ninp]`` is ONE ``[T·B, ninp] × [ninp, 2·nhid]`` GEMM per sequence instead of ``T`` small ones;
 * nodes that share a predecessor read the same state, so their weight matrices are concatenated once per sequence and
   each group is one GEMM per time step — the default genotype needs 5 recurrent GEMMs per step instead of 9;
+* on a GPU the gate of all nodes of such a group — sigmoid, activation, highway mix, the dropout-masked copy that feeds
+  the next GEMM — is ONE kernel forward and one backward (``csrc/kernels/rnn_ops.cu``) instead of five elementwise
+  launches per node forward and a dozen backward: at batch 64 × width 850 every one of those moves ~100 KB, so the
+  recurrence is bound by launch and dependency latency;
 * the trial can fix the sequence length (``fixed_seq_len``) so that the whole training step has static shapes and replays
   as a CUDA graph, which removes the launch overhead that otherwise dominates ``T × 5`` small GEMMs.
 
 The hidden width of the published configuration (850) is not a multiple of 8, which the TMA descriptors of the in-tree GEMM
-need, so the GEMMs here are torch's (cuBLAS, bf16 under autocast).
+need, so the GEMMs here are torch's (cuBLAS, bf16 under autocast); ``DET_RNN_FUSED_GATE=0`` selects the all-torch path.
 """
 from __future__ import annotations
 
+import os
 from collections import namedtuple
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -57,6 +62,34 @@ def locked_mask(like: torch.Tensor, batch: int, width: int, drop: float) -> torc
     return torch.bernoulli(torch.full((batch, width), keep, device=like.device, dtype=torch.float32)).to(like.dtype) / keep
 
 
+class _HighwayGateFn(torch.autograd.Function):
+    """``(ch [B, k*2*nh], sp [B, nh], mask) → k node states (+ k masked copies)`` through the fused gate kernels."""
+
+    @staticmethod
+    def forward(ctx, ch, sp, mask, acts):
+        from ..ops import functional as F
+
+        states, masked = F.highway_gate_fwd(ch, sp, mask, acts)
+        ctx.save_for_backward(ch, sp, mask)
+        ctx.acts = acts
+        ctx.set_materialize_grads(False)
+        return tuple(states + masked)
+
+    @staticmethod
+    def backward(ctx, *grads):
+        from ..ops import functional as F
+
+        ch, sp, mask = ctx.saved_tensors
+        k = len(ctx.acts)
+        grads = [None if g is None else g.contiguous() for g in grads]
+        dch, dsp = F.highway_gate_bwd(ch, sp, mask, grads[:k], grads[k:] if mask is not None else [None] * k, ctx.acts)
+        return dch, dsp, None, None
+
+
+def fused_gate_enabled(x: torch.Tensor, nhid: int) -> bool:
+    return x.is_cuda and x.dtype == torch.bfloat16 and nhid % 2 == 0 and os.environ.get("DET_RNN_FUSED_GATE", "1") != "0"
+
+
 class DARTSCell(nn.Module):
     def __init__(self, ninp: int, nhid: int, dropouth: float, dropoutx: float, genotype: Genotype, init_op: str = "tanh") -> None:
         super().__init__()
@@ -71,10 +104,10 @@ class DARTSCell(nn.Module):
         # ascending predecessor order is a valid schedule: a node's predecessor always has a smaller index than the node
         self.groups: List[Tuple[int, List[int]]] = sorted(groups.items())
 
-    def forward(self, inputs: torch.Tensor, hidden: torch.Tensor,
-                masks: Optional[Tuple[torch.Tensor, torch.Tensor]] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    def forward(self, inputs: torch.Tensor, hidden: torch.Tensor, masks: Optional[Tuple[torch.Tensor, torch.Tensor]] = None,
+                fused: Optional[bool] = None) -> Tuple[torch.Tensor, torch.Tensor]:
         """``inputs`` [T, B, ninp], ``hidden`` [1, B, nhid] → (all hidden states [T, B, nhid], last one [1, B, nhid]).
-        ``masks = (x_mask, h_mask)`` overrides the sampled dropout masks (tests)."""
+        ``masks = (x_mask, h_mask)`` overrides the sampled dropout masks and ``fused`` the choice of gate path (tests)."""
         T, B, _ = inputs.shape
         x_mask = h_mask = None
         if masks is not None:
@@ -92,8 +125,31 @@ class DARTSCell(nn.Module):
         f0 = ACTIVATIONS[self.init_op]
         n_states = len(self.genotype.recurrent) + 1
         concat = list(self.genotype.concat)
-        h = hidden[0].to(inputs.dtype)
+        h = hidden[0].to(inputs.dtype).contiguous()
         out = []
+        if fused_gate_enabled(inputs, nh) if fused is None else fused:
+            from ..ops import _native
+            from ..ops.functional import GATE_ACTS
+
+            _native.load()
+            if h_mask is not None:
+                h_mask = h_mask.to(inputs.dtype).contiguous()
+            init_act = (GATE_ACTS[self.init_op],)
+            group_acts = [tuple(GATE_ACTS[self.genotype.recurrent[i][0]] for i in members) for _, members in self.groups]
+            for t in range(T):
+                hm = h if h_mask is None else h * h_mask
+                res = _HighwayGateFn.apply(torch.addmm(xproj[t], hm, w0h), h, h_mask, init_act)
+                states = [res[0]] + [None] * (n_states - 1)
+                feeds = [res[-1]] + [None] * (n_states - 1)        # what the next GEMM reads: the masked copy, if any
+                for (pred, members), w, ga in zip(self.groups, wcat, group_acts):
+                    res = _HighwayGateFn.apply(feeds[pred] @ w, states[pred], h_mask, ga)
+                    k = len(members)
+                    for j, i in enumerate(members):
+                        states[i + 1], feeds[i + 1] = res[j], res[-k + j]
+                h = torch.stack([states[i] for i in concat], dim=-1).mean(-1)
+                out.append(h)
+            hiddens = torch.stack(out)
+            return hiddens, hiddens[-1].unsqueeze(0)
         for t in range(T):
             hm = h if h_mask is None else h * h_mask
             c0, h0 = (xproj[t] + hm @ w0h).split(nh, dim=-1)

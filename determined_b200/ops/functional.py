@@ -450,3 +450,45 @@ def bn_finalize(sums: torch.Tensor, M: int, C: int, running_mean: Optional[torch
     _native.call("det_bn_finalize", _p(sums), _p(mean), _p(rstd), _p(running_mean), _p(running_var), M, C, float(eps), float(momentum),
                  _stream())
     return mean, rstd
+
+
+# ------------------------------------------------------------------------------------------------
+# Recurrent-cell gate (csrc/kernels/rnn_ops.cu)
+# ------------------------------------------------------------------------------------------------
+GATE_ACTS = {"tanh": 0, "relu": 1, "sigmoid": 2, "identity": 3}
+
+
+def _ptr_array(tensors):
+    arr = (ctypes.c_void_p * len(tensors))(*[None if t is None else t.data_ptr() for t in tensors])
+    return arr, ctypes.cast(arr, ctypes.c_void_p)
+
+
+def highway_gate_fwd(ch: torch.Tensor, sp: torch.Tensor, mask: Optional[torch.Tensor], acts: Tuple[int, ...]):
+    """``s_j = sp + sigmoid(c_j) * (f_j(h_j) - sp)`` for the ``k = len(acts)`` nodes whose ``[c_j | h_j]`` blocks are the
+    columns of ``ch`` [B, k*2*nh]; returns ``(states, masked)`` — ``masked[j] = states[j] * mask`` when a mask is given."""
+    k = len(acts)
+    B, nh = sp.shape
+    assert ch.shape == (B, 2 * nh * k) and ch.is_contiguous() and sp.is_contiguous() and ch.dtype == sp.dtype == torch.bfloat16
+    s = [torch.empty_like(sp) for _ in range(k)]
+    sm = [torch.empty_like(sp) for _ in range(k)] if mask is not None else []
+    s_keep, s_arr = _ptr_array(s)
+    m_keep, m_arr = _ptr_array(sm) if sm else (None, None)
+    acts_arr = (ctypes.c_int * k)(*acts)
+    _native.call("det_highway_gate_fwd", _p(ch), _p(sp), _p(mask), s_arr, m_arr, ctypes.cast(acts_arr, ctypes.c_void_p), k, B, nh, _stream())
+    del s_keep, m_keep
+    return s, sm
+
+
+def highway_gate_bwd(ch: torch.Tensor, sp: torch.Tensor, mask: Optional[torch.Tensor], ds, dsm, acts: Tuple[int, ...]):
+    """Gradients of :func:`highway_gate_fwd`: ``ds[j]`` / ``dsm[j]`` (either may be ``None``) are the gradients of node j's
+    state and of its masked copy; returns ``(d_ch [B, k*2*nh], d_sp [B, nh])``."""
+    k = len(acts)
+    B, nh = sp.shape
+    dch, dsp = torch.empty_like(ch), torch.empty_like(sp)
+    a_keep, a_arr = _ptr_array(ds)
+    b_keep, b_arr = _ptr_array(dsm) if mask is not None else (None, None)
+    acts_arr = (ctypes.c_int * k)(*acts)
+    _native.call("det_highway_gate_bwd", _p(ch), _p(sp), _p(mask), a_arr, b_arr, _p(dch), _p(dsp),
+                 ctypes.cast(acts_arr, ctypes.c_void_p), k, B, nh, _stream())
+    del a_keep, b_keep
+    return dch, dsp

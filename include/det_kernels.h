@@ -67,6 +67,14 @@ int det_avgpool2d_fwd(const void* x, void* y, int N, int H, int W, int C, int k,
 int det_avgpool2d_bwd(const void* dy, void* dx, int N, int H, int W, int C, int k, int stride, int pad, int count_include_pad,
                       cudaStream_t stream);
 
+/* ---- recurrent-cell gate: s_j = sp + sigmoid(c_j) * (f_j(h_j) - sp) for the k nodes sharing predecessor sp; ch is
+ * [B, k*2*nh] with node j's [c | h] at columns j*2*nh; acts: 0 tanh, 1 relu, 2 sigmoid, 3 identity; mask [B, nh] or null
+ * (then the masked copies s_j * mask are written too). Pointer arrays are host arrays of k device pointers. */
+int det_highway_gate_fwd(const void* ch, const void* sp, const void* mask, void* const* s_out, void* const* sm_out,
+                         const int* acts, int k, int B, int nh, cudaStream_t stream);
+int det_highway_gate_bwd(const void* ch, const void* sp, const void* mask, const void* const* ds, const void* const* dsm,
+                         void* dch, void* dsp, const int* acts, int k, int B, int nh, cudaStream_t stream);
+
 /* ---- LayerNorm / reductions / embeddings / loss (reference: torch.nn.LayerNorm, Embedding, CrossEntropyLoss) */
 int det_layernorm_fwd(const void* x, const float* gamma, const float* beta, void* y, float* mean, float* rstd,
                       int T, int H, float eps, float dropout_p, unsigned int seed, const unsigned int* seed_dev,

@@ -102,3 +102,62 @@ def test_darts_rnn_trial_trains_on_gpu(graphs):
     assert tv.validation_metrics[-1]["perplexity"] < 64 * 0.6
     if graphs:
         assert controller._graphed is not None and controller._graphed.replays > 100
+
+
+@pytest.mark.parametrize("k,use_mask", [(1, False), (3, True), (2, True)])
+def test_highway_gate_kernels_match_fp32_reference(k, use_mask):
+    from determined_b200.ops import functional as F
+
+    _load()
+    torch.manual_seed(k)
+    B, nh = 5, 850
+    acts = tuple((i * 3 + 1) % 4 for i in range(k))
+    ch = torch.randn(B, 2 * nh * k, device="cuda").bfloat16()
+    sp = torch.randn(B, nh, device="cuda").bfloat16()
+    mask = (torch.bernoulli(torch.full((B, nh), 0.75, device="cuda")) / 0.75).bfloat16() if use_mask else None
+    fns = [torch.tanh, torch.relu, torch.sigmoid, lambda t: t]
+    chf, spf = ch.float().requires_grad_(True), sp.float().requires_grad_(True)
+    ref_s = []
+    for j, a in enumerate(acts):
+        c, h = chf[:, 2 * nh * j:2 * nh * (j + 1)].split(nh, -1)
+        ref_s.append(spf + torch.sigmoid(c) * (fns[a](h) - spf))
+    s, sm = F.highway_gate_fwd(ch, sp, mask, acts)
+    for j in range(k):
+        assert (s[j].float() - ref_s[j]).abs().max() < 2e-2
+        if use_mask:
+            assert (sm[j].float() - ref_s[j] * mask.float()).abs().max() < 4e-2
+    ds = [torch.randn(B, nh, device="cuda").bfloat16() if j != 1 else None for j in range(k)]
+    dsm = [torch.randn(B, nh, device="cuda").bfloat16() for _ in range(k)] if use_mask else [None] * k
+    loss = sum((ref_s[j] * ds[j].float()).sum() for j in range(k) if ds[j] is not None)
+    if use_mask:
+        loss = loss + sum((ref_s[j] * mask.float() * dsm[j].float()).sum() for j in range(k))
+    loss.backward()
+    dch, dsp = F.highway_gate_bwd(ch, sp, mask, ds, dsm, acts)
+    assert (dch.float() - chf.grad).abs().max() < 3e-2 * max(1.0, chf.grad.abs().max().item())
+    assert (dsp.float() - spf.grad).abs().max() < 3e-2 * max(1.0, spf.grad.abs().max().item())
+
+
+def test_darts_cell_fused_gates_match_torch_path():
+    from determined_b200.models import darts_rnn as R
+
+    _load()
+    torch.manual_seed(0)
+    T, B, H = 9, 6, 850
+    cell = R.DARTSCell(H, H, 0.25, 0.75, R.DARTS_V2).cuda()
+    x = torch.randn(T, B, H, device="cuda").bfloat16()
+    h0 = (torch.randn(1, B, H, device="cuda") * 0.1).bfloat16()
+    xm, hm = R.locked_mask(x, B, H, 0.75), R.locked_mask(x, B, H, 0.25)
+    outs, grads = {}, {}
+    for fused in (False, True):
+        for p in cell.parameters():
+            p.grad = None
+        out = cell(x, h0, masks=(xm, hm), fused=fused)[0]
+        out.float().pow(2).mean().backward()
+        outs[fused], grads[fused] = out.float(), [p.grad.clone() for p in cell.parameters()]
+    assert (outs[True] - outs[False]).abs().max() < 3e-2 * max(outs[False].abs().max().item(), 0.1)
+    for a, b in zip(grads[True], grads[False]):
+        cos = torch.nn.functional.cosine_similarity(a.flatten(), b.flatten(), dim=0).item()
+        assert cos > 0.995, cos
+    cell.eval()                                             # no masks: the gate feeds the next GEMM directly
+    a, b = cell(x, h0, fused=True)[0].float(), cell(x, h0, fused=False)[0].float()
+    assert (a - b).abs().max() < 3e-2 * max(b.abs().max().item(), 0.1)
