@@ -201,8 +201,8 @@ class RNNModel(nn.Module):
             keep = 1.0 - self.dropoute
             w = w * (torch.bernoulli(torch.full((w.shape[0], 1), keep, device=w.device)) / keep)     # whole words dropped
         emb = self._lockdrop(nn.functional.embedding(tokens, w), self.dropouti)
-        if torch.is_autocast_enabled():
-            emb = emb.to(torch.get_autocast_dtype(emb.device.type))
+        if emb.is_cuda:
+            emb = emb.to(torch.bfloat16)      # bf16 activations and GEMM operands on the GPU; weights stay fp32 masters
         raw = emb
         new_hidden, raw_outputs = [], []
         for cell, h in zip(self.rnns, hidden):
@@ -210,7 +210,7 @@ class RNNModel(nn.Module):
             new_hidden.append(new_h)
             raw_outputs.append(raw)
         output = self._lockdrop(raw, self.dropout)
-        logits = self.decoder(output)
+        logits = nn.functional.linear(output, self.decoder.weight.to(output.dtype), self.decoder.bias.to(output.dtype))
         return logits, new_hidden, raw_outputs, [output]
 
 
