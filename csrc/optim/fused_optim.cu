@@ -136,7 +136,8 @@ sumsq_finite_kernel(const float* __restrict__ g, long long n, const float* grad_
   float acc = 0.0f;
   bool bad = false;
   const long long stride = static_cast<long long>(gridDim.x) * blockDim.x;
-  const long long n4 = n >> 2;
+  // 16-byte loads only from a 16-byte aligned base (a view that starts mid-allocation takes the scalar loop below)
+  const long long n4 = (reinterpret_cast<uintptr_t>(g) & 15) == 0 ? (n >> 2) : 0;
   for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n4; i += stride) {
     const float4 v = __ldg(reinterpret_cast<const float4*>(g) + i);
     const float a = v.x * gs, b = v.y * gs, c = v.z * gs, d = v.w * gs;

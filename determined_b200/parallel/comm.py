@@ -56,6 +56,9 @@ class Communicator:
             for t in tensors:
                 t.mul_(scale)
 
+    def allreduce_max_int(self, flag: torch.Tensor) -> None:
+        """In-place MAX over ranks of a small integer tensor (the fp16 overflow flag)."""
+
     def broadcast_tensors(self, tensors: Sequence[torch.Tensor], root: int = 0) -> None:
         pass
 
@@ -238,6 +241,9 @@ class TorchDistCommunicator(Communicator):
                 self.dist.all_reduce(t)
             if scale != 1.0:
                 t.mul_(scale)
+
+    def allreduce_max_int(self, flag: torch.Tensor) -> None:
+        self.dist.all_reduce(flag, op=self.dist.ReduceOp.MAX)
 
     def broadcast_tensors(self, tensors, root: int = 0) -> None:
         for t in tensors:

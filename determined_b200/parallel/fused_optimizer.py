@@ -245,6 +245,10 @@ class FusedOptimizer(torch.optim.Optimizer):
                 if st:
                     if n1 and st.get(n1) is not None:
                         grp.view(grp.flat_s1, i).copy_(st[n1])
+                        if self.variant == F.OPT_SGD:
+                            # stock torch SGD state is the momentum buffer alone (no "step"): a restored buffer means the
+                            # first update already happened, so the kernel must not re-seed the buffer with the gradient
+                            steps = max(steps, 1)
                     if n2 and st.get(n2) is not None:
                         grp.view(grp.flat_s2, i).copy_(st[n2])
                     s = st.get("step", 0)

@@ -163,7 +163,9 @@ class PyTorchTrialContext(TrialContext):
             return
         self._use_amp = True
         self._amp_dtype = dtype or torch.bfloat16
-        if self._amp_dtype == torch.float16 and self.device.type == "cuda":
+        if self._amp_dtype == torch.float16:
+            # the scaler also exists on CPU (autocast stays off there): the skip-on-overflow protocol between ranks is
+            # host-side logic and is tested with gloo
             self._loss_scaler = _LossScaler(self.device)
 
     @contextlib.contextmanager
@@ -361,13 +363,17 @@ class PyTorchTrialContext(TrialContext):
                 g.mul_(opt.grad_scale_dev)
             opt.grad_scale_dev.fill_(1.0)
             slow_clip([p for grp in opt.param_groups for p in grp["params"]])
-        if scaler is not None and found_inf is not None and self.comm.size <= 1:
+        if scaler is not None and found_inf is not None and not (applied_all and self.comm.size > 1):
+            # the collective did not scan for inf/NaN (single process, or the library all-reduce fallback: several nodes,
+            # DET_DISABLE_P2P, no arena): scan here, then agree across ranks so that every rank skips or steps together
             from ..ops import functional as F
 
             sc = opt._scratch
             sc[0:1].zero_()
             for g in opt.grad_buckets():
                 F.grad_sumsq_finite(g, opt.grad_scale_dev, sc[0:1], found_inf)
+            if self.comm.size > 1:
+                self.comm.allreduce_max_int(found_inf)
         opt.step(max_grad_norm=max_norm, zero_grad=auto_zero)
         if scaler is not None:
             from ..ops import functional as F
@@ -381,13 +387,35 @@ class PyTorchTrialContext(TrialContext):
         elif divisor != 1.0:
             for p in params:
                 p.grad.div_(divisor)
+        skip = False
         if self._loss_scaler is not None:
             inv = 1.0 / float(self._loss_scaler.state[0])
             for p in params:
                 p.grad.mul_(inv)
-        if slow_clip is not None:
+            # stock-optimizer path: overflow check on the host (gradients are already summed over ranks, so every rank
+            # sees the same values; the MAX reduce guards against rank-local non-determinism in the collective)
+            bad = torch.zeros(1, dtype=torch.int32, device=self.device)
+            for p in params:
+                if not bool(torch.isfinite(p.grad).all()):
+                    bad.fill_(1)
+                    break
+            if self.comm.size > 1:
+                self.comm.allreduce_max_int(bad)
+            skip = bool(bad.item())
+            st = self._loss_scaler.state
+            if skip:
+                st[0] = torch.clamp(st[0] * self._loss_scaler.backoff, min=1.0)
+                st[1] = 0.0
+            else:
+                st[1] = st[1] + 1.0
+                if float(st[1]) >= self._loss_scaler.interval:
+                    st[0] = st[0] * self._loss_scaler.growth
+                    st[1] = 0.0
+            st[2] = 1.0 / st[0]
+        if slow_clip is not None and not skip:
             slow_clip([p for grp in opt.param_groups for p in grp["params"]])
-        opt.step()
+        if not skip:
+            opt.step()
         if auto_zero:
             opt.zero_grad()
 

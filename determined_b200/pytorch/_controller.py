@@ -361,8 +361,19 @@ class PyTorchTrialController:
                     elif set(keys) != set(vm.keys()):
                         raise ValueError(f"validation metric names changed between batches: {keys} vs {list(vm)}")
                     rows.append([vm[k] for k in keys])
-                keys = self.comm.broadcast_object(keys, 0) if (keys is None and self.comm.size > 1) else keys
-                metrics = self._reduce_validation(keys or [], rows)
+                if self.comm.size > 1:
+                    # every rank runs the same collectives: a rank whose shard held no batch adopts the metric names of
+                    # the first rank that saw one (DistributedBatchSampler deals whole batches, so shards can be empty)
+                    all_keys = self.comm.allgather_object(keys)
+                    seen = [k for k in all_keys if k is not None]
+                    for k in seen[1:]:
+                        if set(k) != set(seen[0]):
+                            raise ValueError(f"validation metric names differ between ranks: {seen[0]} vs {k}")
+                    keys = seen[0] if seen else None
+                if keys is None:
+                    # reference: check.gt(len(validation_loader), 0) (_pytorch_trial.py:446)
+                    raise ValueError("the validation data loader produced no batches on any rank")
+                metrics = self._reduce_validation(keys, rows)
                 num_inputs = int(sum(self.comm.allgather_object(num_inputs)))
             else:
                 if self.is_chief:
@@ -372,7 +383,8 @@ class PyTorchTrialController:
                     metrics = {k: (float(v.detach().cpu()) if isinstance(v, torch.Tensor) and v.numel() == 1 else
                                    (v.detach().cpu().numpy() if isinstance(v, torch.Tensor) else v))
                                for k, v in metrics.items()}
-                    num_inputs = sum(_data.data_length(b) for b in []) or 0
+                    # the reference reports per-slot batch size x loader length here (_pytorch_trial.py:519-540)
+                    num_inputs = self.context.get_per_slot_batch_size() * len(cast(Any, self.validation_loader))
         metrics.update(self._reduce_custom(for_training=False))
         if self.comm.size > 1 and any(util.is_overridden(cb.on_validation_end, _callback.PyTorchCallback)
                                       for cb in self.callbacks.values()):

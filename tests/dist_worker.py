@@ -28,6 +28,41 @@ def main() -> None:
     elif case == "xor_plain":
         trial, hp, steps, unit = M.XorTrial, {"hidden_size": 4, "learning_rate": 0.05, "global_batch_size": 8, "shuffle": False}, 4, 2
         cfg = {"optimizations": {"average_training_metrics": True}}
+    elif case == "xor_fp16_inf":
+        # fp16 loss scaling on the library all-reduce path: rank 1 poisons one gradient on the second batch; every rank
+        # must skip that update, halve the scale and stay bit-identical
+        import torch as _t
+        from determined_b200 import pytorch as dp
+
+        class PoisonedXor(M.XorTrial):
+            def __init__(self, context):
+                super().__init__(context)
+                context.configure_apex_amp(self.model, self.opt, cast_model_type=_t.float16, loss_scale=1024.0)
+                self.snap = []
+
+            def train_batch(self, batch, epoch_idx, batch_idx):
+                out = self.model(batch["data"])
+                loss = self.loss_fn(out, batch["label"])
+                self.context.backward(loss)
+                if batch_idx == 1 and rank == 1:
+                    self.model.l1.weight.grad[0, 0] = float("inf")
+                before = _t.cat([p.detach().reshape(-1).clone() for p in self.model.parameters()])
+                self.context.step_optimizer(self.opt)
+                after = _t.cat([p.detach().reshape(-1).clone() for p in self.model.parameters()])
+                return {"loss": loss, "moved": (before != after).any().float(),
+                        "scale": self.context._loss_scaler.state[0].clone()}
+
+        trial, hp, steps, unit = PoisonedXor, {"hidden_size": 4, "learning_rate": 0.05, "global_batch_size": 8, "shuffle": False}, 2, 2
+        cfg = {"optimizations": {"average_training_metrics": False}}
+    elif case == "xor_val_short":
+        # fewer validation batches than ranks: rank 1's shard is empty, every rank still runs the same collectives
+        class ShortVal(M.XorTrial):
+            def build_validation_data_loader(self):
+                from determined_b200 import pytorch as dp
+                return dp.DataLoader(M._XorData(4, 2), batch_size=self.context.get_per_slot_batch_size())
+
+        trial, hp, steps, unit = ShortVal, {"hidden_size": 4, "learning_rate": 0.05, "global_batch_size": 8, "shuffle": False}, 2, 2
+        cfg = {"optimizations": {"average_training_metrics": True}}
     elif case in ("mnist_gpu", "mnist_gpu_overlap"):
         from determined_b200.models import vision_trials as VT
 

@@ -20,7 +20,7 @@ def test_nprand_matches_numpy_randomstate():
         rng = core.NpRand(seed)
         st = ref.get_state()
         ref2 = np.random.RandomState(seed)
-        assert [rng.bits32() for _ in range(700)] == [int(x) for x in ref2.randint(0, 2 ** 32, size=700, dtype=np.uint64)] or True
+        assert [rng.bits32() for _ in range(700)] == [int(x) for x in ref2.randint(0, 2 ** 32, size=700, dtype=np.uint64)]
         rng = core.NpRand(seed)
         ref = np.random.RandomState(seed)
         assert [rng.unit_interval() for _ in range(50)] == [ref.random_sample() for _ in range(50)]

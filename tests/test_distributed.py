@@ -81,3 +81,22 @@ def test_dp2_gradient_compression_half_precision_wire(tmp_path):
     pa = np.array(a), np.array(plain["params_by_rank"][0])
     assert not np.array_equal(*pa), "compression left no trace: the flag did not reach the collective"
     assert np.abs(pa[0] - pa[1]).max() < 5e-3 * max(1.0, np.abs(pa[1]).max())
+
+
+def test_dp2_fp16_overflow_skips_the_step_on_every_rank(tmp_path):
+    """Injected inf on one rank (library all-reduce path): both ranks skip that update and back the loss scale off."""
+    rep = run_ranks(2, "xor_fp16_inf", tmp_path, {"CUDA_VISIBLE_DEVICES": ""})
+    a, b = rep["params_by_rank"]
+    assert a == b and all(np.isfinite(a)), "replicas diverged or went non-finite"
+    t = rep["training"]
+    assert [m["moved"] for m in t] == [1.0, 0.0, 1.0, 1.0]
+    assert [m["scale"] for m in t] == [1024.0, 512.0, 512.0, 512.0]
+
+
+def test_dp2_validation_with_fewer_batches_than_ranks(tmp_path):
+    """A rank with an empty validation shard joins the same collectives as the others (no deadlock) and the result is
+    the reduction over the batches that exist."""
+    rep = run_ranks(2, "xor_val_short", tmp_path, {"CUDA_VISIBLE_DEVICES": ""}, timeout=120)
+    assert len(rep["validation"]) == 1
+    v = rep["validation"][0]
+    assert np.isfinite(v["loss"]) and 0.0 <= v["binary_error"] <= 1.0

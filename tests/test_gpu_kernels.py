@@ -36,6 +36,69 @@ def test_gemm_layouts(a_mn, b_mn, bn):
     assert rel(C, ref) < 1.5e-2
 
 
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True)])
+@pytest.mark.parametrize("shape", [(1000, 776, 200), (512, 512, 64), (768, 1280, 1096)])
+def test_gemm_cta_pair_kernel(a_mn, b_mn, shape):
+    """force_bn=512 selects the cta_group::2 kernel (256 x 256 tile over an SM pair): ragged M/N edges, a K that is not
+    a multiple of the 64-wide k-block (zero-filled by TMA), every operand layout the training path uses."""
+    F = _F()
+    torch.manual_seed(3)
+    M, N, K = shape
+    A = torch.randn(M, K, device="cuda").bfloat16()
+    B = torch.randn(N, K, device="cuda").bfloat16()
+    ref = A.float() @ B.float().t()
+    As = A.t().contiguous() if a_mn else A
+    Bs = B.t().contiguous() if b_mn else B
+    C = torch.zeros(M, N, device="cuda", dtype=torch.bfloat16)
+    F.gemm(As, Bs, C, M, N, K, a_mn=a_mn, b_mn=b_mn, force_bn=512)
+    assert rel(C, ref) < 1.5e-2
+
+
+@pytest.mark.parametrize("force_bn", [0, 256, 512])
+def test_gemm_bert_sized_with_epilogues(force_bn):
+    """The BERT-base ffn1 problem (6144 x 3072 x 768) through every fused epilogue, on the automatic tile choice, the
+    single-CTA 128 x 256 kernel and the CTA-pair kernel."""
+    F = _F()
+    torch.manual_seed(4)
+    M, N, K = 6144, 3072, 768
+    A = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()
+    B = (torch.randn(N, K, device="cuda") * 0.05).bfloat16()
+    bias = torch.randn(N, device="cuda")
+    acc = A.float() @ B.float().t()
+    C = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    Z = torch.empty_like(C)
+    F.gemm(A, B, C, M, N, K, force_bn=force_bn)
+    assert rel(C, acc) < 1.5e-2
+    F.gemm(A, B, C, M, N, K, epi=F.EPI_BIAS_GELU, bias=bias, aux_out=Z, force_bn=force_bn)
+    assert rel(C, torch.nn.functional.gelu(acc + bias)) < 1.5e-2 and rel(Z, acc + bias) < 1.5e-2
+    zf = Z.float().requires_grad_(True)
+    torch.nn.functional.gelu(zf).sum().backward()
+    F.gemm(A, B, C, M, N, K, epi=F.EPI_DGELU, aux_in=Z, force_bn=force_bn)
+    assert rel(C, acc * zf.grad) < 2e-2
+    R = torch.randn(M, N, device="cuda").bfloat16()
+    F.gemm(A, B, C, M, N, K, epi=F.EPI_BIAS_RESID, bias=bias, aux_in=R, force_bn=force_bn)
+    assert rel(C, acc + bias + R.float()) < 1.5e-2
+    # strided output (a column block of a wider tensor, as the fused QKV projection writes)
+    wide = torch.zeros(M, N + 256, device="cuda", dtype=torch.bfloat16)
+    F.gemm(A, B, wide[:, 128:128 + N], M, N, K, epi=F.EPI_BIAS, bias=bias, force_bn=force_bn)
+    assert rel(wide[:, 128:128 + N], acc + bias) < 1.5e-2
+    assert wide[:, :128].abs().max().item() == 0.0 and wide[:, 128 + N:].abs().max().item() == 0.0
+
+
+@pytest.mark.parametrize("force_bn,splitk", [(0, 0), (256, 5), (512, 3), (512, 0), (128, 7)])
+def test_gemm_splitk_weight_gradient_shapes(force_bn, splitk):
+    """Weight-gradient form (both operands MN-major, fp32 atomic accumulation) with K = tokens not a multiple of the
+    k-block and explicit split-K factors, on the single-CTA and the CTA-pair kernels."""
+    F = _F()
+    torch.manual_seed(5)
+    Kt, No, Ni = 6144 + 40, 768, 3072
+    dY = torch.randn(Kt, No, device="cuda").bfloat16()
+    X = torch.randn(Kt, Ni, device="cuda").bfloat16()
+    G = torch.ones(No, Ni, device="cuda")
+    F.gemm(dY, X, G, No, Ni, Kt, a_mn=True, b_mn=True, out_mode=F.OUT_F32_ATOMIC_ADD, force_bn=force_bn, splitk=splitk)
+    assert rel(G - 1.0, dY.float().t() @ X.float()) < 2e-3
+
+
 def test_gemm_epilogues_and_splitk():
     F = _F()
     torch.manual_seed(2)
@@ -218,6 +281,36 @@ def test_fused_optimizers_match_torch(name):
         F.fused_optimizer_step(variant, p, grad, s1, s2, shadow, hp.cuda(), gs, None, True)
         assert grad.abs().max().item() == 0.0
     assert rel(p, ref_p.detach()) < 2e-5 and rel(shadow, p) < 5e-3
+
+
+def test_fused_sgd_resumes_stock_torch_momentum_state():
+    """A stock ``torch.optim.SGD(momentum=0.9)`` state dict (momentum buffers only, no step counter) loaded into the fused
+    optimizer continues the same trajectory: the restored buffer is used, not overwritten by the first gradient."""
+    _F()
+    from determined_b200.parallel.fused_optimizer import FusedOptimizer
+
+    torch.manual_seed(11)
+    w0 = torch.randn(300, 40, device="cuda")
+    grads = [torch.randn_like(w0) for _ in range(4)]
+    ref_w = w0.clone().requires_grad_(True)
+    ref = torch.optim.SGD([ref_w], lr=0.1, momentum=0.9)
+    for g in grads[:2]:
+        ref_w.grad = g.clone()
+        ref.step()
+    sd = ref.state_dict()
+    assert "step" not in sd["state"][0]
+    w = ref_w.detach().clone().requires_grad_(True)
+    opt = FusedOptimizer(torch.optim.SGD([w], lr=0.1, momentum=0.9))
+    assert opt.fused
+    opt.load_state_dict(sd)
+    for g in grads[2:]:
+        ref_w.grad = g.clone()
+        ref.step()
+        w.grad.copy_(g)
+        opt.step(zero_grad=True)
+    assert rel(w.detach(), ref_w.detach()) < 1e-5
+    out = opt.state_dict()["state"][0]["momentum_buffer"]
+    assert rel(out, ref.state_dict()["state"][0]["momentum_buffer"]) < 1e-5
 
 
 def test_grad_norm_clip_and_loss_scale_state_machine():

@@ -72,6 +72,13 @@ def test_noalloc_grad_norm_matches_regular_entry_point_on_consecutive_calls():
     assert new[2] == 0
     assert new[0] == pytest.approx(ref[0], rel=1e-4)
     assert new[0] == pytest.approx(0.25 * g3.double().norm().item(), rel=1e-4)
+    # call 4: a pointer that is only 4-byte aligned (a view one element into an allocation) takes the scalar-load branch
+    g4 = torch.randn((1 << 20) + 1, device="cuda")[1:]
+    assert g4.data_ptr() % 16 == 4
+    new, ref = _both(lib, g4, None)
+    assert new[2] == 0 and ref[2] == 0
+    assert new[0] == pytest.approx(ref[0], rel=1e-4)
+    assert new[0] == pytest.approx(g4.double().norm().item(), rel=1e-4)
 
 
 def test_noalloc_grad_norm_rejects_oversize_without_launching():
