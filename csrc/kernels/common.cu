@@ -83,6 +83,39 @@ int make_tma_2d_bf16(CUtensorMap* out, const void* gptr, uint64_t inner, uint64_
   return 0;
 }
 
+// 2-D fp32 tensor map, SWIZZLE_128B (box_inner = 32 floats = 128 B): the fp32 store / reduce-add epilogues of the GEMM.
+int make_tma_2d_f32(CUtensorMap* out, const void* gptr, uint64_t inner, uint64_t outer, uint64_t ld_elems,
+                    uint32_t box_inner, uint32_t box_outer) {
+  static std::mutex mu;
+  static std::unordered_map<TmaKey, CUtensorMap, TmaKeyHash> cache;
+  TmaKey key{gptr, inner, outer, ld_elems, box_inner, box_outer};
+  {
+    std::lock_guard<std::mutex> g(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) { *out = it->second; return 0; }
+  }
+  EncodeTiledFn fn = get_encode_fn();
+  DET_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+  DET_REQUIRE((reinterpret_cast<uintptr_t>(gptr) & 15) == 0, "TMA base must be 16-byte aligned");
+  DET_REQUIRE((ld_elems * 4) % 16 == 0, "TMA row pitch must be a multiple of 16 bytes");
+  DET_REQUIRE(box_inner == 32, "SWIZZLE_128B box needs 32 fp32 in the inner dimension");
+  cuuint64_t gdim[2] = {inner, outer};
+  cuuint64_t gstr[1] = {ld_elems * 4};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(gptr), gdim, gstr, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_last_error("cuTensorMapEncodeTiled (fp32) failed with CUresult " + std::to_string((int)r));
+    return 3;
+  }
+  std::lock_guard<std::mutex> g(mu);
+  if (cache.size() > 65536) cache.clear();
+  cache.emplace(key, *out);
+  return 0;
+}
+
 // N-D (rank 2..4) bf16 tensor map, SWIZZLE_128B, innermost box = 64 elements. dims/box are innermost first;
 // strides_bytes has rank-1 entries (dims 1..rank-1). Cached on every argument.
 int make_tma_nd_bf16(CUtensorMap* out, const void* gptr, int rank, const uint64_t* dims,

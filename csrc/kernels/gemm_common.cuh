@@ -6,6 +6,10 @@
 
 namespace det {
 
+constexpr int GEMM_BK = 64;
+constexpr int GEMM_EPI_WARPS = 16;  // 4 per TMEM lane quarter: the epilogue is issue-bound, so give every SMSP 4 warps
+constexpr int GEMM_THREADS = 64 + 32 * GEMM_EPI_WARPS;
+
 enum GemmEpilogue : int {
   EPI_NONE = 0,
   EPI_BIAS = 1,        // C = acc + bias
@@ -33,6 +37,11 @@ struct GemmParams {
   const uint32_t* drop_seed_dev;  // optional per-step seed in device memory (CUDA-graph friendly)
   float* colstats;                // optional [2 * N] fp32: += column sums and sums of squares of the (bf16-rounded) output
 };
+
+// CTA-pair kernel (gemm_pair_sm100.cu). `p` carries the problem, output and epilogue fields; tiling fields are set inside.
+bool pair_gemm_supported(const GemmParams& p, const void* A, const void* B, long long lda, long long ldb);
+int launch_pair_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams p, int a_mn, int b_mn, int splitk,
+                     cudaStream_t stream);
 
 // erf GELU through the Abramowitz–Stegun 7.1.26 rational form (|error| < 1.5e-7, far below bf16 resolution): one
 // approximate reciprocal, one exp2 and six FMAs per element instead of libdevice erff's branchy ~40 instructions. The epilogue

@@ -20,9 +20,6 @@
 namespace det {
 
 constexpr int GEMM_BM = 128;
-constexpr int GEMM_BK = 64;
-constexpr int GEMM_EPI_WARPS = 16;  // 4 per TMEM lane quarter: the epilogue is issue-bound, so give every SMSP 4 warps
-constexpr int GEMM_THREADS = 64 + 32 * GEMM_EPI_WARPS;
 
 template <int BN>
 struct GemmCfg {
@@ -247,192 +244,6 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmP
   return 0;
 }
 
-// ------------------------------------------------------------------------------------------------
-// CTA-pair GEMM: a 2-cluster computes a 256 x 256 tile with tcgen05.mma.cta_group::2. Each CTA stages its own 128 rows
-// of A and HALF of the B tile (128 of the 256 columns), so per k-block a CTA pulls 32 KB through TMA instead of the
-// 48 KB of the 128 x 256 single-CTA tile — the single-CTA kernel is L2/TMA-feed bound on the BERT shapes (tensor pipe
-// 24-34 % busy in ncu), so operand traffic per FLOP is what limits it.
-//   full[s]    lives in the leader (cluster rank 0): leader arrives with expect_tx for BOTH CTAs' bytes, both producers'
-//              TMA loads credit it (cp.async.bulk.tensor ... .cta_group::2 with the leader's cluster address);
-//   empty[s]   one per CTA: the leader's tcgen05.commit.cta_group::2 multicasts the arrival to both;
-//   tfull[b]   one per CTA (multicast commit), tempty[b] in the leader, count = epilogue warps of both CTAs.
-// ------------------------------------------------------------------------------------------------
-constexpr int G2_STAGES = 6;
-constexpr uint32_t G2_A_BYTES = 128 * GEMM_BK * 2;
-constexpr uint32_t G2_B_BYTES = 128 * GEMM_BK * 2;
-constexpr uint32_t G2_SMEM_BYTES = G2_STAGES * (G2_A_BYTES + G2_B_BYTES) + 1024 + 256;
-constexpr int G2_BN = 256;
-
-template <int A_MN, int B_MN>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
-gemm2_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b, const GemmParams p) {
-  constexpr int STAGES = G2_STAGES;
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sA = smem;
-  uint8_t* sB = smem + STAGES * G2_A_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + STAGES * G2_B_BYTES);
-  uint64_t* full_bar = bars;
-  uint64_t* empty_bar = bars + STAGES;
-  uint64_t* tfull_bar = bars + 2 * STAGES;
-  uint64_t* tempty_bar = bars + 2 * STAGES + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
-
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
-  const uint32_t cta_rank = ptx::cluster_ctarank();
-  const bool leader = cta_rank == 0;
-  const int cluster_id = blockIdx.x >> 1;
-  const int num_clusters = gridDim.x >> 1;
-
-  if (warp == 0 && lane == 0) {
-    ptx::tma_prefetch_desc(&tma_a);
-    ptx::tma_prefetch_desc(&tma_b);
-    for (int i = 0; i < STAGES; ++i) {
-      ptx::mbar_init(ptx::smem_u32(&full_bar[i]), 1);
-      ptx::mbar_init(ptx::smem_u32(&empty_bar[i]), 1);
-    }
-    for (int i = 0; i < 2; ++i) {
-      ptx::mbar_init(ptx::smem_u32(&tfull_bar[i]), 1);
-      ptx::mbar_init(ptx::smem_u32(&tempty_bar[i]), 2 * GEMM_EPI_WARPS);
-    }
-    ptx::fence_mbar_init();
-  }
-  if (warp == 1) ptx::tmem_alloc_2cta(ptx::smem_u32(tmem_slot), 512);
-  ptx::tc_fence_before();
-  ptx::cluster_sync_all();
-  ptx::tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
-
-  const int total_work = p.tiles_m * p.tiles_n * p.splitk;   // tiles_m counts 256-row pair tiles here
-
-  if (warp == 0) {
-    // ===================== TMA producer (both CTAs) =====================
-    if (lane == 0) {
-      uint32_t it = 0;
-      for (int w = cluster_id; w < total_work; w += num_clusters) {
-        const int ks = w % p.splitk;
-        const int tile = w / p.splitk;
-        const int m0 = (tile % p.tiles_m) * 256 + static_cast<int>(cta_rank) * 128;
-        const int n0 = (tile / p.tiles_m) * G2_BN + static_cast<int>(cta_rank) * 128;
-        const int kb0 = ks * p.kb_per_split;
-        const int kb1 = min(kb0 + p.kb_per_split, p.num_kb);
-        for (int kb = kb0; kb < kb1; ++kb, ++it) {
-          const uint32_t s = it % STAGES;
-          const uint32_t ph = (it / STAGES) & 1;
-          ptx::mbar_wait(ptx::smem_u32(&empty_bar[s]), ph ^ 1);
-          if (leader) ptx::mbar_expect_tx(ptx::smem_u32(&full_bar[s]), 2 * (G2_A_BYTES + G2_B_BYTES));
-          const uint32_t fb = ptx::mapa_shared(ptx::smem_u32(&full_bar[s]), 0);
-          const uint32_t a_dst = ptx::smem_u32(sA + s * G2_A_BYTES);
-          const uint32_t b_dst = ptx::smem_u32(sB + s * G2_B_BYTES);
-          const int k0 = kb * GEMM_BK;
-          if (A_MN == 0) {
-            ptx::tma_load_2d_2cta(a_dst, &tma_a, fb, k0, m0);
-          } else {
-#pragma unroll
-            for (int j = 0; j < 2; ++j) ptx::tma_load_2d_2cta(a_dst + j * 8192, &tma_a, fb, m0 + 64 * j, k0);
-          }
-          if (B_MN == 0) {
-            ptx::tma_load_2d_2cta(b_dst, &tma_b, fb, k0, n0);
-          } else {
-#pragma unroll
-            for (int j = 0; j < 2; ++j) ptx::tma_load_2d_2cta(b_dst + j * 8192, &tma_b, fb, n0 + 64 * j, k0);
-          }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ===================== MMA issuer (leader CTA only) =====================
-    if (leader && lane == 0) {
-      constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(256, G2_BN, A_MN, B_MN);
-      uint32_t it = 0;
-      uint32_t lt = 0;
-      for (int w = cluster_id; w < total_work; w += num_clusters, ++lt) {
-        const int ks = w % p.splitk;
-        const int kb0 = ks * p.kb_per_split;
-        const int kb1 = min(kb0 + p.kb_per_split, p.num_kb);
-        const uint32_t buf = lt & 1;
-        const uint32_t aph = (lt >> 1) & 1;
-        ptx::mbar_wait(ptx::smem_u32(&tempty_bar[buf]), aph ^ 1);
-        ptx::tc_fence_after();
-        const uint32_t tmem_d = tmem_base + buf * G2_BN;
-        for (int kb = kb0; kb < kb1; ++kb, ++it) {
-          const uint32_t s = it % STAGES;
-          const uint32_t ph = (it / STAGES) & 1;
-          ptx::mbar_wait(ptx::smem_u32(&full_bar[s]), ph);
-          ptx::tc_fence_after();
-          const uint32_t a_base = ptx::smem_u32(sA + s * G2_A_BYTES);
-          const uint32_t b_base = ptx::smem_u32(sB + s * G2_B_BYTES);
-#pragma unroll
-          for (int k = 0; k < GEMM_BK / 16; ++k) {
-            const uint64_t adesc = A_MN ? ptx::make_smem_desc_sw128(a_base + k * 2048, 8192, 1024)
-                                        : ptx::make_smem_desc_sw128(a_base + k * 32, 16, 1024);
-            const uint64_t bdesc = B_MN ? ptx::make_smem_desc_sw128(b_base + k * 2048, 8192, 1024)
-                                        : ptx::make_smem_desc_sw128(b_base + k * 32, 16, 1024);
-            ptx::umma_bf16_ss_2cta(tmem_d, adesc, bdesc, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
-          }
-          ptx::umma_commit_2cta(ptx::smem_u32(&empty_bar[s]), 3);   // frees the stage in both CTAs
-        }
-        ptx::umma_commit_2cta(ptx::smem_u32(&tfull_bar[buf]), 3);   // accumulators ready in both CTAs
-      }
-    }
-  } else {
-    // ===================== Epilogue warps (both CTAs, each on its own 128 rows) =====================
-    const int ew = warp - 2;
-    const int q = warp & 3;
-    const int part = ew >> 2;
-    constexpr int COLS_PER_WARP = G2_BN / 4;
-    constexpr int CW = 32;
-    const uint32_t leader_tempty0 = ptx::mapa_shared(ptx::smem_u32(&tempty_bar[0]), 0);
-    const uint32_t leader_tempty1 = ptx::mapa_shared(ptx::smem_u32(&tempty_bar[1]), 0);
-    uint32_t lt = 0;
-    for (int w = cluster_id; w < total_work; w += num_clusters, ++lt) {
-      const int tile = w / p.splitk;
-      const int m0 = (tile % p.tiles_m) * 256 + static_cast<int>(cta_rank) * 128;
-      const int n0 = (tile / p.tiles_m) * G2_BN;
-      const uint32_t buf = lt & 1;
-      const uint32_t aph = (lt >> 1) & 1;
-      ptx::mbar_wait(ptx::smem_u32(&tfull_bar[buf]), aph);
-      ptx::tc_fence_after();
-      const int row = m0 + q * 32 + lane;
-      const bool row_ok = row < p.M;
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + buf * G2_BN;
-#pragma unroll 1
-      for (int c = part * COLS_PER_WARP; c < (part + 1) * COLS_PER_WARP; c += CW) {
-        float v[CW];
-        ptx::tmem_ld_32x32b_x32(taddr + c, v);
-        ptx::tmem_ld_wait();
-        gemm_epilogue_chunk<CW>(p, v, row, row_ok, n0 + c);
-      }
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) ptx::mbar_arrive_cluster(buf ? leader_tempty1 : leader_tempty0);
-    }
-  }
-
-  ptx::tc_fence_before();
-  ptx::cluster_sync_all();
-  if (warp == 1) {
-    ptx::tc_fence_after();
-    ptx::tmem_dealloc_2cta(tmem_base, 512);
-  }
-}
-
-template <int A_MN, int B_MN>
-static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t stream) {
-  auto kfn = gemm2_bf16_tcgen05_kernel<A_MN, B_MN>;
-  static bool attr_set[64] = {false};
-  int dev = 0;
-  DET_CHECK_CUDA(cudaGetDevice(&dev));
-  if (dev < 64 && !attr_set[dev]) {
-    DET_CHECK_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, G2_SMEM_BYTES));
-    attr_set[dev] = true;
-  }
-  kfn<<<grid, GEMM_THREADS, G2_SMEM_BYTES, stream>>>(ta, tb, p);
-  DET_CHECK_CUDA(cudaGetLastError());
-  return 0;
-}
-
 static int pick_bn(int M, int N, int sms, bool splitk_ok) {
   // with split-K available the grid is filled along K, so take the tile with the best arithmetic intensity
   if (splitk_ok && N >= 192) return 256;
@@ -474,34 +285,13 @@ static int gemm_launch_impl(const void* A, const void* B, void* C, int M, int N,
   DET_REQUIRE(M > 0 && N > 0 && K > 0, "empty GEMM");
   DET_REQUIRE(out_mode >= 0 && out_mode <= 2, "bad out_mode");
   const int sms = sm_count();
-  // force_bn == 512 selects the CTA-pair kernel (256 x 256 tile over two SMs); automatic choice: DET_GEMM_2CTA=1
-  static const int pair_auto = [] { const char* e = getenv("DET_GEMM_2CTA"); return (e && e[0] == '1') ? 1 : 0; }();
-  // Measured on B200 (profiles/gemm_timing_r1_v3_pair.json): the pair kernel wins once the problem is large enough to be
-  // operand-feed bound (8192^3: 1394 vs 1294 TFLOP/s, cuBLAS 1044) and loses a few percent on ~30 us BERT-sized GEMMs,
-  // where fixed launch/prologue cost dominates — so it is picked automatically only for big problems.
-  const bool big = static_cast<double>(M) * N * K >= 6.0e10 && M >= 1024 && N >= 1024 && K >= 1024;
-  const bool pair = force_bn == 512 || (force_bn <= 0 && M >= 256 && N >= 256 && (pair_auto || big));
-  int bn = pair ? 256 : (force_bn > 0 ? force_bn : pick_bn(M, N, sms, out_mode == OUT_F32_ATOMIC_ADD));
-  DET_REQUIRE(bn == 64 || bn == 128 || bn == 256, "BN must be 64, 128 or 256 (512 = CTA pair)");
-  const int tile_m = pair ? 256 : GEMM_BM;
-  const int units = pair ? sms / 2 : sms;       // schedulable units: CTA pairs or CTAs
+  // force_bn == 512 selects the CTA-pair kernel (gemm_pair_sm100.cu: 256 x 256 tile over two SMs, TMA-store epilogue).
+  // Automatic choice: every problem large enough to give most pairs a tile; DET_GEMM_2CTA=0 switches it off.
+  static const int pair_auto = [] { const char* e = getenv("DET_GEMM_2CTA"); return (e && e[0] == '0') ? 0 : 1; }();
+  const bool pair_wanted = force_bn == 512 || (force_bn <= 0 && pair_auto && M >= 1024 && N >= 256 &&
+                                               static_cast<long long>(M) * N >= (1LL << 21));
   GemmParams p;
   p.M = M; p.N = N; p.K = K;
-  p.tiles_m = (M + tile_m - 1) / tile_m;
-  p.tiles_n = (N + bn - 1) / bn;
-  p.num_kb = (K + GEMM_BK - 1) / GEMM_BK;
-  const int tiles = p.tiles_m * p.tiles_n;
-  if (out_mode != OUT_F32_ATOMIC_ADD) {
-    splitk = 1;
-  } else if (splitk <= 0) {
-    splitk = 1;
-    // largest split that still fits ONE wave: rounding up instead (54 tiles x 3 = 162 items on 148 SMs) costs a second,
-    // nearly empty wave — 35.3 vs 25.6 us on the 2304 x 768 x 6144 weight gradient (profiles/wgrad_sweep_r1.json)
-    if (tiles < units) splitk = max(1, min(p.num_kb / 4, units / tiles));
-  }
-  splitk = max(1, min(splitk, p.num_kb));
-  p.kb_per_split = (p.num_kb + splitk - 1) / splitk;
-  p.splitk = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
   p.C = C; p.ldc = ldc; p.out_mode = out_mode; p.epi = epi; p.alpha = alpha;
   p.bias = bias;
   p.aux_in = reinterpret_cast<const __nv_bfloat16*>(aux_in);
@@ -519,6 +309,12 @@ static int gemm_launch_impl(const void* A, const void* B, void* C, int M, int N,
   p.drop_seed_dev = dropout_seed_dev;
   p.colstats = colstats;
 
+  const bool pair = pair_wanted && pair_gemm_supported(p, A, B, lda, ldb);
+  DET_REQUIRE(pair || force_bn != 512,
+              "the CTA-pair kernel needs 16-byte aligned outputs whose row pitch is a multiple of 16 bytes");
+  const int bn = pair ? 256 : (force_bn > 0 ? force_bn : pick_bn(M, N, sms, out_mode == OUT_F32_ATOMIC_ADD));
+  DET_REQUIRE(bn == 64 || bn == 128 || bn == 256, "BN must be 64, 128 or 256 (512 = CTA pair)");
+
   CUtensorMap ta, tb;
   int rc;
   if (a_mn == 0) rc = make_tma_2d_bf16(&ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, 64, GEMM_BM);
@@ -527,14 +323,24 @@ static int gemm_launch_impl(const void* A, const void* B, void* C, int M, int N,
   if (b_mn == 0) rc = make_tma_2d_bf16(&tb, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, 64, pair ? 128u : (uint32_t)bn);
   else           rc = make_tma_2d_bf16(&tb, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, 64);
   if (rc) return rc;
+  if (pair) return launch_pair_gemm(ta, tb, p, a_mn, b_mn, splitk, stream);
 
-  if (pair) {
-    const int grid2 = 2 * min(tiles * p.splitk, units);
-    if (a_mn == 0 && b_mn == 0) return launch_gemm2<0, 0>(ta, tb, p, grid2, stream);
-    if (a_mn == 0 && b_mn == 1) return launch_gemm2<0, 1>(ta, tb, p, grid2, stream);
-    if (a_mn == 1 && b_mn == 0) return launch_gemm2<1, 0>(ta, tb, p, grid2, stream);
-    return launch_gemm2<1, 1>(ta, tb, p, grid2, stream);
+  p.tiles_m = (M + GEMM_BM - 1) / GEMM_BM;
+  p.tiles_n = (N + bn - 1) / bn;
+  p.num_kb = (K + GEMM_BK - 1) / GEMM_BK;
+  const int tiles = p.tiles_m * p.tiles_n;
+  if (out_mode != OUT_F32_ATOMIC_ADD) {
+    splitk = 1;
+  } else if (splitk <= 0) {
+    splitk = 1;
+    // largest split that still fits ONE wave: rounding up instead (54 tiles x 3 = 162 items on 148 SMs) costs a second,
+    // nearly empty wave — 35.3 vs 25.6 us on the 2304 x 768 x 6144 weight gradient (profiles/wgrad_sweep_r1.json)
+    if (tiles < sms) splitk = max(1, min(p.num_kb / 4, sms / tiles));
   }
+  splitk = max(1, min(splitk, p.num_kb));
+  p.kb_per_split = (p.num_kb + splitk - 1) / splitk;
+  p.splitk = (p.num_kb + p.kb_per_split - 1) / p.kb_per_split;
+
   const int grid = min(tiles * p.splitk, sms);
   if (colstats != nullptr) {
     DET_REQUIRE(a_mn == 0 && b_mn == 0, "column statistics need K-major operands");

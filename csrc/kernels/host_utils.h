@@ -38,6 +38,10 @@ void set_last_error(const std::string& s);  // defined in common.cu
 int make_tma_2d_bf16(CUtensorMap* out, const void* gptr, uint64_t inner, uint64_t outer,
                      uint64_t ld_elems, uint32_t box_inner, uint32_t box_outer);
 
+// Same for fp32 tensors (box_inner must be 32 floats = 128 B).
+int make_tma_2d_f32(CUtensorMap* out, const void* gptr, uint64_t inner, uint64_t outer,
+                    uint64_t ld_elems, uint32_t box_inner, uint32_t box_outer);
+
 // Rank 2..4 variant (dims/box innermost first, strides in bytes for dims 1..rank-1); box[0] must be 64.
 int make_tma_nd_bf16(CUtensorMap* out, const void* gptr, int rank, const uint64_t* dims,
                      const uint64_t* strides_bytes, const uint32_t* box);

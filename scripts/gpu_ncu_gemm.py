@@ -1,4 +1,5 @@
-"""Tiny driver for ncu: a few launches of the BERT FFN1 forward GEMM (6144 x 3072 x 768, bias+GELU) and the wgrad shape."""
+"""Tiny driver for ncu: the BERT FFN1 GEMM (6144 x 3072 x 768) through the CTA-pair kernel — bare, with the
+bias + GELU + aux epilogue, and the weight-gradient shape (fp32 reduce-add output) — a few launches each."""
 import os
 import sys
 
@@ -14,7 +15,8 @@ bias = torch.randn(N, device="cuda")
 C = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
 Z = torch.empty_like(C)
 G = torch.zeros(N, K, device="cuda")
-for _ in range(6):
+for _ in range(3):
+    F.gemm(A, B, C, M, N, K)
     F.gemm(A, B, C, M, N, K, epi=F.EPI_BIAS_GELU, bias=bias, aux_out=Z)
     F.gemm(C, A, G, N, K, M, a_mn=True, b_mn=True, out_mode=F.OUT_F32_ATOMIC_ADD)
 torch.cuda.synchronize()
