@@ -103,11 +103,40 @@ def _barrier_sync(device) -> None:
     torch.cuda.synchronize(device)
 
 
+def _comm_check(comm, device) -> Dict[str, Any]:
+    """Multi-GPU correctness inside the benchmark process group: all-reduce one scratch bucket with the fused
+    peer-memory kernel (default 1024-thread CTAs and the 128-thread CTAs of the overlapped path) and with NCCL, and
+    report the largest difference over ranks."""
+    import torch
+    import torch.distributed as dist
+
+    n = 8 << 20
+    g = torch.Generator(device=device).manual_seed(1000 + comm.rank)
+    src = torch.randn(n, generator=g, device=device)
+    ref = src.clone()
+    dist.all_reduce(ref)
+    ref.mul_(1.0 / comm.size)
+    buf = comm.alloc(n, torch.float32, "grad", device)
+    errs = []
+    for threads in (0, 128):
+        buf.copy_(src)
+        applied = comm.allreduce_grad_bucket(buf, 1.0 / comm.size, max_blocks=64 if threads else 0, cta_threads=threads)
+        if not applied:
+            buf.mul_(1.0 / comm.size)
+        errs.append(float((buf - ref).abs().max()))
+    err = torch.tensor([max(errs)], device=device)
+    dist.all_reduce(err, op=dist.ReduceOp.MAX)
+    d = comm.describe() if hasattr(comm, "describe") else {}
+    return {"max_abs_err_vs_nccl": float(err.item()), "elements": n, "nvls": bool(d.get("nvls")), "p2p": bool(d.get("p2p")),
+            "ref_abs_max": float(ref.abs().max())}
+
+
 def hparams(n_gpus: int) -> Dict[str, Any]:
     return {"global_batch_size": PER_SLOT_BATCH * n_gpus, "learning_rate": 2e-5, "adam_epsilon": 1e-8,
             "weight_decay": 0.0, "num_warmup_steps": 0, "num_training_steps": 100000, "max_seq_length": SEQ_LEN,
             "max_grad_norm": 1.0, "dataset_size": 4096, "validation_size": 96, "use_cuda_graphs": True,
-            "overlap_grad_allreduce": os.environ.get("DET_OVERLAP", "0") == "1"}
+            # all-reduce of finished bucket slices on a side stream under the closing micro-batch's backward
+            "overlap_grad_allreduce": os.environ.get("DET_OVERLAP", "1") == "1" and n_gpus > 1}
 
 
 def exp_config(n_gpus: int) -> Dict[str, Any]:
@@ -132,6 +161,9 @@ def run_ours(args) -> Dict[str, Any]:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run --nproc-per-node {args.gpus}")
     device = torch.device("cuda", local_rank)
     torch.cuda.set_device(device)
+    # the product's data plane is the peer-memory collective: a box where the arena cannot be built must fail loudly
+    # here instead of timing the NCCL fallback under this name
+    os.environ.setdefault("DET_REQUIRE_P2P", "1")
     cfg = exp_config(world)
     env, dist_ctx = _execution.make_local_execution_env(True, cfg, hparams=cfg["hyperparameters"], seed=1234)
     env.experiment_config["resources"]["slots_per_trial"] = world
@@ -187,6 +219,7 @@ def run_ours(args) -> Dict[str, Any]:
     # ---- device-only pass: same step, inputs resident on the device, no host traffic in the loop ----
     g = controller._graphed
     ctx = controller.context
+    comm_check = _comm_check(ctx.comm, device) if world > 1 else None
     batch = ctx.to_device(next(controller.training_iterator))
     total = timing["total_batches"]
 
@@ -233,6 +266,7 @@ def run_ours(args) -> Dict[str, Any]:
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "path": "PyTorchTrialController.run() over RUN_STEP workloads; pinned DataLoader -> device copy per batch; metrics D2H per workload"},
         "gpu_launches": int(timing["launches"]),
+        "comm_check": comm_check,
         "clocks": clocks,
         "final_loss": timing["losses"][-1] if timing.get("losses") else None,
     }

@@ -254,10 +254,13 @@ extern "C" long long det_comm_flag_bytes() { return 1LL * det::COMM_MAX_BLOCKS *
 extern "C" long long det_comm_epoch_bytes() { return 1LL * det::COMM_MAX_BLOCKS * 4; }
 
 // peer_bufs / peer_flags: host arrays of `world` device pointers (this rank's view of every rank).
-extern "C" int det_fused_allreduce(void* const* peer_bufs, void* const* peer_flags, void* mc_ptr,
-                                   void* epoch_dev, long long n_f32, int rank, int world, float scale,
-                                   const float* scale_dev, float* sumsq_dev, int* found_inf_dev,
-                                   int max_blocks, cudaStream_t stream) {
+// threads: CTA size. 1024 (default) suits a collective that has the GPU to itself; 128 makes a CTA small enough
+// (8 K registers, ~130 B of shared memory) to sit NEXT to a resident GEMM CTA on the same SM, which is how the
+// overlapped all-reduce runs under backward without taking SMs away from it.
+static int fused_allreduce_launch(void* const* peer_bufs, void* const* peer_flags, void* mc_ptr,
+                                  void* epoch_dev, long long n_f32, int rank, int world, float scale,
+                                  const float* scale_dev, float* sumsq_dev, int* found_inf_dev,
+                                  int max_blocks, int threads, cudaStream_t stream) {
   using namespace det;
   if (n_f32 <= 0) return 0;
   DET_REQUIRE(n_f32 % 4 == 0, "bucket length must be a multiple of 4 floats");
@@ -269,7 +272,9 @@ extern "C" int det_fused_allreduce(void* const* peer_bufs, void* const* peer_fla
   a.n = n_f32; a.rank = rank; a.world = world; a.scale = scale; a.scale_dev = scale_dev;
   a.sumsq = sumsq_dev; a.found_inf = found_inf_dev;
   const long long per4 = ((n_f32 >> 2) + world - 1) / world;
-  const long long per_block = static_cast<long long>(AR_THREADS) * (mc_ptr != nullptr && world > 1 ? AR_UNROLL_MC : AR_UNROLL_P2P);
+  if (threads <= 0) threads = AR_THREADS;
+  DET_REQUIRE(threads % 32 == 0 && threads >= 32 && threads <= AR_THREADS, "CTA size must be a multiple of 32 in [32, 1024]");
+  const long long per_block = static_cast<long long>(threads) * (mc_ptr != nullptr && world > 1 ? AR_UNROLL_MC : AR_UNROLL_P2P);
   int blocks = static_cast<int>(std::min<long long>((per4 + per_block - 1) / per_block, std::min(sm_count(), COMM_MAX_BLOCKS)));
   // Measured (profiles/allreduce_vs_ctas_8gpu_r1.txt, overlap_sweep_2gpu_r1.txt): with 8 switch reductions in flight
   // per thread the links saturate at 2-8 CTAs and MORE CTAs are slower (8 GPUs: 0.98 ms with 8 CTAs, 1.09 ms with 148;
@@ -278,10 +283,26 @@ extern "C" int det_fused_allreduce(void* const* peer_bufs, void* const* peer_fla
   blocks = std::min(blocks, max_blocks);
   blocks = std::max(blocks, 1);
   // Every rank must launch the same grid: blocks depends only on (n, world, SM count, max_blocks).
-  if (mc_ptr != nullptr && world > 1) fused_allreduce_kernel<true><<<blocks, AR_THREADS, 0, stream>>>(a);
-  else fused_allreduce_kernel<false><<<blocks, AR_THREADS, 0, stream>>>(a);
+  if (mc_ptr != nullptr && world > 1) fused_allreduce_kernel<true><<<blocks, threads, 0, stream>>>(a);
+  else fused_allreduce_kernel<false><<<blocks, threads, 0, stream>>>(a);
   DET_CHECK_CUDA(cudaGetLastError());
   return 0;
+}
+
+extern "C" int det_fused_allreduce(void* const* peer_bufs, void* const* peer_flags, void* mc_ptr,
+                                   void* epoch_dev, long long n_f32, int rank, int world, float scale,
+                                   const float* scale_dev, float* sumsq_dev, int* found_inf_dev,
+                                   int max_blocks, cudaStream_t stream) {
+  return fused_allreduce_launch(peer_bufs, peer_flags, mc_ptr, epoch_dev, n_f32, rank, world, scale, scale_dev, sumsq_dev,
+                                found_inf_dev, max_blocks, 0, stream);
+}
+
+extern "C" int det_fused_allreduce_cta(void* const* peer_bufs, void* const* peer_flags, void* mc_ptr,
+                                       void* epoch_dev, long long n_f32, int rank, int world, float scale,
+                                       const float* scale_dev, float* sumsq_dev, int* found_inf_dev,
+                                       int max_blocks, int threads, cudaStream_t stream) {
+  return fused_allreduce_launch(peer_bufs, peer_flags, mc_ptr, epoch_dev, n_f32, rank, world, scale, scale_dev, sumsq_dev,
+                                found_inf_dev, max_blocks, threads, stream);
 }
 
 extern "C" int det_p2p_broadcast(void* const* peer_bufs, void* const* peer_flags, void* epoch_dev,

@@ -288,8 +288,8 @@ static int gemm_launch_impl(const void* A, const void* B, void* C, int M, int N,
   // force_bn == 512 selects the CTA-pair kernel (gemm_pair_sm100.cu: 256 x 256 tile over two SMs, TMA-store epilogue).
   // Automatic choice: every problem large enough to give most pairs a tile; DET_GEMM_2CTA=0 switches it off.
   static const int pair_auto = [] { const char* e = getenv("DET_GEMM_2CTA"); return (e && e[0] == '0') ? 0 : 1; }();
-  const bool pair_wanted = force_bn == 512 || (force_bn <= 0 && pair_auto && M >= 1024 && N >= 256 &&
-                                               static_cast<long long>(M) * N >= (1LL << 21));
+  const bool pair_wanted = force_bn == 512 || (force_bn <= 0 && pair_auto && (M >= 1024 || out_mode == OUT_F32_ATOMIC_ADD) && M >= 256 && N >= 256 &&
+                                               static_cast<long long>(M) * N >= (out_mode == OUT_F32_ATOMIC_ADD ? (1LL << 19) : (1LL << 21)));
   GemmParams p;
   p.M = M; p.N = N; p.K = K;
   p.C = C; p.ldc = ldc; p.out_mode = out_mode; p.epi = epi; p.alpha = alpha;

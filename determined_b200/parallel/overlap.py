@@ -10,9 +10,11 @@ This is what Horovod's per-parameter hooks + background fusion thread do for the
 * readiness comes from the autograd nodes of :mod:`determined_b200.ops` (``note_param_use`` in forward,
   ``notify_grads_written`` at the end of backward): a chunk is launched when every pending use of every parameter in it
   has reported — a parameter used twice in one graph (a GAN discriminator run on real and fake batches) counts twice;
-* the collective is the fused peer-memory kernel (sum + scale + unscale + non-finite flag), launched with a small grid;
-  while a window is open the persistent GEMM / convolution kernels size their grids for ``sm_count - reserved`` SMs so
-  the collective's CTAs are never queued behind a full-width grid (``det_set_sm_limit``).
+* the collective is the fused peer-memory kernel (sum + scale + unscale + non-finite flag) launched as many SMALL CTAs
+  (128 threads, 8 K registers, ~130 B of shared memory) on a high-priority side stream: a CTA of that size fits next to
+  a resident GEMM CTA (576 threads x 96 registers, 226 KB of shared memory) on the same SM, so backward keeps all 148
+  SMs and the collective's loads and switch reductions ride along in its issue slots. Reserving SMs instead
+  (``reserved_sms > 0`` -> ``det_set_sm_limit``) remains possible but costs the persistent GEMMs a whole wave.
 
 Contract: between ``arm()`` (called by ``context.backward`` on the batch that closes an aggregation window) and
 ``finish(optimizer)`` (called by ``context.step_optimizer``) every gradient of that optimizer must be produced by ONE
@@ -39,10 +41,11 @@ class _Chunk:
 
 
 class GradOverlap:
-    def __init__(self, comm: Any, chunk_bytes: int = 32 << 20, reserved_sms: int = 16, comm_blocks: int = 16) -> None:
+    def __init__(self, comm: Any, chunk_bytes: int = 32 << 20, reserved_sms: int = 0, comm_blocks: int = 64,
+                 cta_threads: int = 128) -> None:
         self.comm = comm
         self.chunk_elems = max(chunk_bytes // 4, 1)
-        self.reserved_sms, self.comm_blocks = reserved_sms, comm_blocks
+        self.reserved_sms, self.comm_blocks, self.cta_threads = reserved_sms, comm_blocks, cta_threads
         self.chunks: List[_Chunk] = []
         self.by_param: Dict[int, _Chunk] = {}
         self.known_opts: List[FusedOptimizer] = []
@@ -95,8 +98,9 @@ class GradOverlap:
             dev = self.chunks[0].bucket.device if self.chunks else None
             if dev is not None and dev.type == "cuda":
                 if self.stream is None:
-                    self.stream = torch.cuda.Stream(device=dev)
-                F.set_sm_limit(max(F.device_sm_count(dev) - self.reserved_sms, 8))
+                    self.stream = torch.cuda.Stream(device=dev, priority=-1)
+                if self.reserved_sms > 0:
+                    F.set_sm_limit(max(F.device_sm_count(dev) - self.reserved_sms, 8))
 
     def _on_notify(self, params: List[torch.Tensor]) -> None:
         if not self.open:
@@ -121,8 +125,11 @@ class GradOverlap:
             self.stream.wait_event(ev)
             with torch.cuda.stream(self.stream):
                 # small grid while backward is still running next to it; full width for the final flush
-                self.comm.allreduce_grad_bucket(view, scale, scale_dev=scale_dev, found_inf_dev=found_inf,
-                                                max_blocks=self.comm_blocks if overlapped else 0)
+                if overlapped:
+                    self.comm.allreduce_grad_bucket(view, scale, scale_dev=scale_dev, found_inf_dev=found_inf,
+                                                    max_blocks=self.comm_blocks, cta_threads=self.cta_threads)
+                else:
+                    self.comm.allreduce_grad_bucket(view, scale, scale_dev=scale_dev, found_inf_dev=found_inf)
         else:
             self.comm.allreduce_grad_bucket(view, scale, scale_dev=scale_dev, found_inf_dev=found_inf)
 
@@ -144,6 +151,6 @@ class GradOverlap:
             ch.pending = 0
         if not any(ch.launched for ch in self.chunks):
             self.open = False
-            if self.stream is not None:
+            if self.stream is not None and self.reserved_sms > 0:
                 F.set_sm_limit(0)
         return True

@@ -87,7 +87,7 @@ class _Experimental:
         self.cuda_graphs = True
         self.graph_warmup_batches = max(int(warmup_batches), 3)
 
-    def enable_grad_overlap(self, chunk_mb: int = 32, reserved_sms: int = 8) -> None:
+    def enable_grad_overlap(self, chunk_mb: int = 32, reserved_sms: int = 0) -> None:
         """Overlap the gradient all-reduce with backward (multi-slot trials on GPUs): slices of the flat gradient
         bucket are reduced on a side stream as soon as backward has finished writing them. Only for trials that make
         ONE ``context.backward`` call per optimizer step — see :mod:`determined_b200.parallel.overlap`."""
@@ -99,7 +99,8 @@ class _Experimental:
 
             reserved = int(os.environ.get("DET_OVERLAP_SMS", reserved_sms))
             p._overlap = GradOverlap(p.comm, chunk_bytes=int(os.environ.get("DET_OVERLAP_CHUNK_MB", chunk_mb)) << 20,
-                                     reserved_sms=reserved, comm_blocks=int(os.environ.get("DET_OVERLAP_BLOCKS", reserved)))
+                                     reserved_sms=reserved, comm_blocks=int(os.environ.get("DET_OVERLAP_BLOCKS", 64)),
+                                     cta_threads=int(os.environ.get("DET_OVERLAP_CTA_THREADS", 128)))
             for o in p.optimizers:
                 if isinstance(o, FusedOptimizer):
                     p._overlap.add_optimizer(o)
