@@ -32,6 +32,7 @@
 #include <algorithm>
 
 #include "host_utils.h"
+#include "sm100_ptx.cuh"
 
 namespace det {
 
@@ -78,6 +79,16 @@ __device__ __forceinline__ void st_f4(float* p, const float4& v) {
                "f"(v.z), "f"(v.w) : "memory");
 }
 
+// Layout of the symmetric flag region (uint32 words): [COMM_MAX_BLOCKS][COMM_MAX_RANKS] barrier flags, then the
+// gradient-statistics mailbox: SS_VALUE + r = rank r's sum of squares of its slice (+inf when it saw a non-finite
+// value), SS_TAG + r = the launch number that value belongs to. The local epoch array carries, after its
+// COMM_MAX_BLOCKS per-block counters: [SS_EPOCH] launch number, [SS_DONE] blocks finished, [SS_PART] running partial.
+constexpr int SS_VALUE = COMM_MAX_BLOCKS * COMM_MAX_RANKS;
+constexpr int SS_TAG = SS_VALUE + COMM_MAX_RANKS;
+constexpr int FLAG_WORDS = SS_TAG + COMM_MAX_RANKS;
+constexpr int SS_EPOCH = COMM_MAX_BLOCKS, SS_DONE = COMM_MAX_BLOCKS + 1, SS_PART = COMM_MAX_BLOCKS + 2;
+constexpr int EPOCH_WORDS = COMM_MAX_BLOCKS + 4;
+
 struct AllreduceArgs {
   PeerTable t;
   float* mc_ptr;          // multicast (NVLS) address of the bucket, or null
@@ -86,9 +97,47 @@ struct AllreduceArgs {
   int rank, world;
   const float* scale_dev; // optional device scalar multiplied into `scale`
   float scale;
-  float* sumsq;           // optional: += sum of squares of the reduced, scaled slice owned by this rank
-  int* found_inf;         // optional: set to 1 when a non-finite value is seen
+  float* sumsq;           // optional: += sum of squares of the WHOLE reduced, scaled bucket (all ranks' slices)
+  int* found_inf;         // optional: set to 1 when ANY rank saw a non-finite value in its slice
 };
+
+// Gradient statistics across ranks without a second launch: every rank reduces only its own slice, so the sum of squares
+// (grad-norm clipping) and the non-finite flag (fp16 loss scaling) of the whole bucket exist only as `world` partials. The
+// last block of each rank to finish publishes the rank's partial into every peer's mailbox, waits for the other ranks'
+// partials of the same launch and adds them up in rank order — every rank computes bit-identical totals, so every rank
+// derives the same clip coefficient and takes the same skip decision.
+__device__ __forceinline__ void exchange_grad_stats(const AllreduceArgs& a, float block_sum, bool block_bad) {
+  // called by thread 0 of every block
+  float* part = reinterpret_cast<float*>(a.epoch + SS_PART);
+  atomicAdd(part, block_bad ? INFINITY : block_sum);
+  __threadfence();
+  const uint32_t done = atomicAdd(a.epoch + SS_DONE, 1u);
+  if (done != gridDim.x - 1) return;
+  __threadfence();
+  const float mine = atomicExch(part, 0.0f);
+  a.epoch[SS_DONE] = 0;
+  const uint32_t tag = a.epoch[SS_EPOCH] + 1;
+  a.epoch[SS_EPOCH] = tag;
+  for (int r = 0; r < a.world; ++r) {
+    uint32_t* f = a.t.flags[r];
+    asm volatile("st.relaxed.sys.global.f32 [%0], %1;" ::"l"(reinterpret_cast<float*>(f + SS_VALUE + a.rank)), "f"(mine) : "memory");
+    __threadfence_system();
+    st_release_sys(f + SS_TAG + a.rank, tag);
+  }
+  float total = 0.0f;
+  const long long t0 = clock64();
+  for (int r = 0; r < a.world; ++r) {
+    const uint32_t* f = a.t.flags[a.rank];
+    while (static_cast<int32_t>(ld_acquire_sys(f + SS_TAG + r) - tag) < 0) {
+      if (clock64() - t0 > 20000000000LL) __trap();
+    }
+    float v;
+    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(reinterpret_cast<const float*>(f + SS_VALUE + r)) : "memory");
+    total += v;
+  }
+  if (a.sumsq != nullptr && isfinite(total)) atomicAdd(a.sumsq, total);
+  if (a.found_inf != nullptr && !isfinite(total)) atomicExch(a.found_inf, 1);
+}
 
 // Memory-level parallelism is what sets the bandwidth of one CTA here (a remote load / switch reduction takes a few
 // microseconds): every thread keeps AR_UNROLL independent 16-byte transactions in flight, so a handful of CTAs already
@@ -173,12 +222,127 @@ fused_allreduce_kernel(const AllreduceArgs a) {
     if (threadIdx.x == 0) {
       float s = 0.0f;
       for (int w = 0; w < (blockDim.x >> 5); ++w) s += red[w];
-      if (a.sumsq) atomicAdd(a.sumsq, s);
-      if (sbad && a.found_inf) atomicExch(a.found_inf, 1);
+      exchange_grad_stats(a, s, sbad != 0);
     }
   }
   rank_barrier(a.t, rank, world, ep + 2);  // every slice has landed everywhere
   if (threadIdx.x == 0) a.epoch[blockIdx.x] = ep + 2;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// TMA-driven all-reduce. The LSU kernel above keeps (threads x unroll) 16-byte requests in flight; a load over NVLink
+// takes microseconds, so it needs thousands of resident threads to fill the links. Here ONE thread per CTA moves the
+// data: for every chunk of this rank's slice it issues `world` bulk loads (cp.async.bulk global -> shared, one per
+// rank's copy of the chunk, unicast, peer memory included), the CTA's threads add the copies up in shared memory (fixed
+// rank order: deterministic sums), apply scale / unscale, look for non-finite values and accumulate the grad-norm
+// partial, and the same thread pushes the finished chunk to every rank's bucket with bulk stores. Three 64 KB stages
+// per CTA keep ~190 KB in flight per SM, so a dozen CTAs saturate the links. Per GPU the wire carries (world-1)/world
+// of the bucket in each direction — the minimum for an all-reduce — where the multimem path moves the whole bucket out
+// and 1 + 1/world of it in.
+// ------------------------------------------------------------------------------------------------------------------
+constexpr int BK_THREADS = 256;
+constexpr int BK_STAGES = 3;
+constexpr int BK_STAGE_BYTES = 65536;
+constexpr int BK_SMEM_BYTES = BK_STAGES * BK_STAGE_BYTES;
+
+__global__ void __launch_bounds__(BK_THREADS)
+fused_allreduce_bulk_kernel(const AllreduceArgs a, const int ch_bytes) {
+  extern __shared__ __align__(128) uint8_t bk_smem[];
+  __shared__ uint64_t full[BK_STAGES];
+  const int rank = a.rank, world = a.world;
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    for (int s = 0; s < BK_STAGES; ++s) ptx::mbar_init(ptx::smem_u32(&full[s]), 1);
+    ptx::fence_mbar_init();
+  }
+  uint32_t ep = a.epoch[blockIdx.x];
+  rank_barrier(a.t, rank, world, ep + 1);  // every rank's gradients for this bucket are complete (also orders the init)
+
+  const float scale = a.scale * (a.scale_dev ? *a.scale_dev : 1.0f);
+  const long long n4 = a.n >> 2;
+  const long long per = (n4 + world - 1) / world;
+  const long long lo = std::min<long long>(per * rank, n4), hi = std::min<long long>(lo + per, n4);
+  const long long slice_bytes = (hi - lo) * 16;
+  const long long base_bytes = lo * 16;
+  const long long num_chunks = (slice_bytes + ch_bytes - 1) / ch_bytes;
+  float acc = 0.0f;
+  bool bad = false;
+
+  auto issue_loads = [&](long long c, int stage) {
+    const long long off = c * ch_bytes;
+    const uint32_t bytes = static_cast<uint32_t>(std::min<long long>(ch_bytes, slice_bytes - off));
+    const uint32_t bar = ptx::smem_u32(&full[stage]);
+    ptx::mbar_expect_tx(bar, bytes * world);
+    for (int r = 0; r < world; ++r)
+      ptx::bulk_load(ptx::smem_u32(bk_smem + stage * BK_STAGE_BYTES + r * ch_bytes),
+                     reinterpret_cast<const uint8_t*>(a.t.buf[r]) + base_bytes + off, bytes, bar);
+  };
+
+  // prologue: STAGES - 1 chunks in flight
+  if (tid == 0) {
+    ptx::fence_proxy_async_all();   // the barrier's acquire was a generic-proxy read; the bulk loads are async-proxy reads
+    for (int j = 0; j < BK_STAGES - 1; ++j) {
+      const long long c = blockIdx.x + static_cast<long long>(j) * gridDim.x;
+      if (c < num_chunks) issue_loads(c, j);
+    }
+  }
+  uint32_t it = 0;
+  for (long long c = blockIdx.x; c < num_chunks; c += gridDim.x, ++it) {
+    const int stage = it % BK_STAGES;
+    if (tid == 0) {
+      // the stage that iteration it-1 used is free once its stores have read it; refill it with chunk it + STAGES - 1
+      const long long cn = c + static_cast<long long>(BK_STAGES - 1) * gridDim.x;
+      if (cn < num_chunks) {
+        ptx::bulk_wait_group_read0();
+        issue_loads(cn, (it + BK_STAGES - 1) % BK_STAGES);
+      }
+    }
+    ptx::mbar_wait(ptx::smem_u32(&full[stage]), (it / BK_STAGES) & 1);
+    const long long off = c * ch_bytes;
+    const int bytes = static_cast<int>(std::min<long long>(ch_bytes, slice_bytes - off));
+    uint8_t* sbase = bk_smem + stage * BK_STAGE_BYTES;
+    for (int i = tid * 16; i < bytes; i += BK_THREADS * 16) {
+      float4 s = *reinterpret_cast<const float4*>(sbase + i);
+      for (int r = 1; r < world; ++r) {
+        const float4 v = *reinterpret_cast<const float4*>(sbase + r * ch_bytes + i);
+        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+      }
+      s.x *= scale; s.y *= scale; s.z *= scale; s.w *= scale;
+      acc += s.x * s.x + s.y * s.y + s.z * s.z + s.w * s.w;
+      bad |= !(isfinite(s.x) && isfinite(s.y) && isfinite(s.z) && isfinite(s.w));
+      *reinterpret_cast<float4*>(sbase + i) = s;
+    }
+    ptx::fence_proxy_async_smem();
+    __syncthreads();
+    if (tid == 0) {
+      for (int r = 0; r < world; ++r)
+        ptx::bulk_store(reinterpret_cast<uint8_t*>(a.t.buf[(rank + r) % world]) + base_bytes + off, ptx::smem_u32(sbase),
+                        static_cast<uint32_t>(bytes));
+      ptx::bulk_commit_group();
+    }
+  }
+  if (tid == 0) {
+    ptx::bulk_wait_group0();       // every pushed chunk has been written
+    ptx::fence_proxy_async_all();  // ... and is ordered before the flag stores of the closing barrier
+  }
+  if (a.sumsq != nullptr || a.found_inf != nullptr) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    __shared__ float red[BK_THREADS / 32];
+    __shared__ int sbad;
+    if (tid == 0) sbad = 0;
+    __syncthreads();
+    if ((tid & 31) == 0) red[tid >> 5] = acc;
+    if (bad) sbad = 1;
+    __syncthreads();
+    if (tid == 0) {
+      float s = 0.0f;
+      for (int w = 0; w < BK_THREADS / 32; ++w) s += red[w];
+      exchange_grad_stats(a, s, sbad != 0);
+    }
+  }
+  rank_barrier(a.t, rank, world, ep + 2);  // every slice has landed everywhere
+  if (tid == 0) a.epoch[blockIdx.x] = ep + 2;
 }
 
 struct BcastArgs {
@@ -250,8 +414,8 @@ static int fill_table(PeerTable& t, void* const* bufs, void* const* flags, int w
 }  // namespace det
 
 // Bytes a flag table needs on each rank (zero-initialised once), and the epoch counter array.
-extern "C" long long det_comm_flag_bytes() { return 1LL * det::COMM_MAX_BLOCKS * det::COMM_MAX_RANKS * 4; }
-extern "C" long long det_comm_epoch_bytes() { return 1LL * det::COMM_MAX_BLOCKS * 4; }
+extern "C" long long det_comm_flag_bytes() { return 1LL * det::FLAG_WORDS * 4; }
+extern "C" long long det_comm_epoch_bytes() { return 1LL * det::EPOCH_WORDS * 4; }
 
 // peer_bufs / peer_flags: host arrays of `world` device pointers (this rank's view of every rank).
 // threads: CTA size. 1024 (default) suits a collective that has the GPU to itself; 128 makes a CTA small enough
@@ -260,7 +424,7 @@ extern "C" long long det_comm_epoch_bytes() { return 1LL * det::COMM_MAX_BLOCKS 
 static int fused_allreduce_launch(void* const* peer_bufs, void* const* peer_flags, void* mc_ptr,
                                   void* epoch_dev, long long n_f32, int rank, int world, float scale,
                                   const float* scale_dev, float* sumsq_dev, int* found_inf_dev,
-                                  int max_blocks, int threads, cudaStream_t stream) {
+                                  int max_blocks, int threads, int algo, cudaStream_t stream) {
   using namespace det;
   if (n_f32 <= 0) return 0;
   DET_REQUIRE(n_f32 % 4 == 0, "bucket length must be a multiple of 4 floats");
@@ -273,17 +437,45 @@ static int fused_allreduce_launch(void* const* peer_bufs, void* const* peer_flag
   a.sumsq = sumsq_dev; a.found_inf = found_inf_dev;
   const long long per4 = ((n_f32 >> 2) + world - 1) / world;
   if (threads <= 0) threads = AR_THREADS;
+  // algo: 0 = automatic, 1 = multimem (NVLS), 2 = LSU peer loads / stores, 3 = TMA bulk copies over peer memory
+  static const int algo_env = [] { const char* e = getenv("DET_AR_ALGO"); return e ? atoi(e) : 0; }();
+  if (algo == 0) algo = algo_env;
   DET_REQUIRE(threads % 32 == 0 && threads >= 32 && threads <= AR_THREADS, "CTA size must be a multiple of 32 in [32, 1024]");
-  const long long per_block = static_cast<long long>(threads) * (mc_ptr != nullptr && world > 1 ? AR_UNROLL_MC : AR_UNROLL_P2P);
+  // Automatic choice, from the bytes each algorithm puts on a GPU's links: peer copies move 2 (world-1)/world of the
+  // bucket per direction, the switch reduction moves 1 + 1/world. Two ranks: 1.0 against 1.5 — bulk copies win (measured
+  // 0.70 against 1.15 ms on the 461 MB bucket); from four ranks on the in-switch reduction moves less. CTAs smaller than
+  // the default (the co-resident overlapped collective) cannot hold the bulk kernel's stages.
+  if (algo == 0) algo = (threads < AR_THREADS || world > 2) ? (mc_ptr != nullptr ? 1 : (threads < AR_THREADS ? 2 : 3)) : 3;
+  if (world <= 1) algo = 2;
+  if (algo == 1 && mc_ptr == nullptr) algo = 2;
+  const long long per_block = static_cast<long long>(threads) * (algo == 1 ? AR_UNROLL_MC : AR_UNROLL_P2P);
   int blocks = static_cast<int>(std::min<long long>((per4 + per_block - 1) / per_block, std::min(sm_count(), COMM_MAX_BLOCKS)));
   // Measured (profiles/allreduce_vs_ctas_8gpu_r1.txt, overlap_sweep_2gpu_r1.txt): with 8 switch reductions in flight
   // per thread the links saturate at 2-8 CTAs and MORE CTAs are slower (8 GPUs: 0.98 ms with 8 CTAs, 1.09 ms with 148;
   // 2 GPUs: 1.15 vs 1.20 ms) — extra CTAs only add flag-barrier traffic. Default to 16.
+  if (algo == 3) {
+    const int ch_bytes = (BK_STAGE_BYTES / world) & ~127;
+    const long long slice_bytes = per4 * 16;
+    const long long chunks = (slice_bytes + ch_bytes - 1) / ch_bytes;
+    static const int bulk_blocks_env = [] { const char* e = getenv("DET_AR_BULK_BLOCKS"); return e ? atoi(e) : 0; }();
+    int bb = max_blocks > 0 ? max_blocks : (bulk_blocks_env > 0 ? bulk_blocks_env : 48);
+    bb = static_cast<int>(std::max<long long>(1, std::min<long long>(std::min<long long>(bb, chunks), std::min(sm_count(), COMM_MAX_BLOCKS))));
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    DET_CHECK_CUDA(cudaGetDevice(&dev));
+    if (dev < 64 && !attr_set[dev]) {
+      DET_CHECK_CUDA(cudaFuncSetAttribute(fused_allreduce_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BK_SMEM_BYTES));
+      attr_set[dev] = true;
+    }
+    fused_allreduce_bulk_kernel<<<bb, BK_THREADS, BK_SMEM_BYTES, stream>>>(a, ch_bytes);
+    DET_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
   if (max_blocks <= 0) max_blocks = 16;
   blocks = std::min(blocks, max_blocks);
   blocks = std::max(blocks, 1);
   // Every rank must launch the same grid: blocks depends only on (n, world, SM count, max_blocks).
-  if (mc_ptr != nullptr && world > 1) fused_allreduce_kernel<true><<<blocks, threads, 0, stream>>>(a);
+  if (algo == 1 && world > 1) fused_allreduce_kernel<true><<<blocks, threads, 0, stream>>>(a);
   else fused_allreduce_kernel<false><<<blocks, threads, 0, stream>>>(a);
   DET_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -294,15 +486,15 @@ extern "C" int det_fused_allreduce(void* const* peer_bufs, void* const* peer_fla
                                    const float* scale_dev, float* sumsq_dev, int* found_inf_dev,
                                    int max_blocks, cudaStream_t stream) {
   return fused_allreduce_launch(peer_bufs, peer_flags, mc_ptr, epoch_dev, n_f32, rank, world, scale, scale_dev, sumsq_dev,
-                                found_inf_dev, max_blocks, 0, stream);
+                                found_inf_dev, max_blocks, 0, 0, stream);
 }
 
 extern "C" int det_fused_allreduce_cta(void* const* peer_bufs, void* const* peer_flags, void* mc_ptr,
                                        void* epoch_dev, long long n_f32, int rank, int world, float scale,
                                        const float* scale_dev, float* sumsq_dev, int* found_inf_dev,
-                                       int max_blocks, int threads, cudaStream_t stream) {
+                                       int max_blocks, int threads, int algo, cudaStream_t stream) {
   return fused_allreduce_launch(peer_bufs, peer_flags, mc_ptr, epoch_dev, n_f32, rank, world, scale, scale_dev, sumsq_dev,
-                                found_inf_dev, max_blocks, threads, stream);
+                                found_inf_dev, max_blocks, threads, algo, stream);
 }
 
 extern "C" int det_p2p_broadcast(void* const* peer_bufs, void* const* peer_flags, void* epoch_dev,

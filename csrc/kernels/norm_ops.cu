@@ -297,6 +297,10 @@ embed_gather_kernel(const long long* __restrict__ ids, const long long* __restri
   }
 }
 
+__device__ __forceinline__ void red_add_f32x4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 __global__ void __launch_bounds__(128)
 embed_scatter_kernel(const long long* __restrict__ ids, const long long* __restrict__ tts,
                      const __nv_bfloat16* __restrict__ de, float* __restrict__ dword,
@@ -310,11 +314,17 @@ embed_scatter_kernel(const long long* __restrict__ ids, const long long* __restr
   for (int c = lane * 8; c < H; c += 256) {
     float f[8];
     unpack8(__ldg(reinterpret_cast<const uint4*>(de + static_cast<long long>(row) * H + c)), f);
-#pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      atomicAdd(w + c + e, f[e]);
-      if (dpos != nullptr) atomicAdd(p + c + e, f[e]);
-      if (dtype != nullptr) atomicAdd(ty + c + e, f[e]);
+    // 16-byte vector reductions: two per lane cover its 8 columns (scalar atomics here were 4.7 M requests per BERT
+    // micro-batch, each warp instruction touching 32 sectors — 210 us for a 19 MB update)
+    red_add_f32x4(w + c, f[0], f[1], f[2], f[3]);
+    red_add_f32x4(w + c + 4, f[4], f[5], f[6], f[7]);
+    if (dpos != nullptr) {
+      red_add_f32x4(p + c, f[0], f[1], f[2], f[3]);
+      red_add_f32x4(p + c + 4, f[4], f[5], f[6], f[7]);
+    }
+    if (dtype != nullptr) {
+      red_add_f32x4(ty + c, f[0], f[1], f[2], f[3]);
+      red_add_f32x4(ty + c + 4, f[4], f[5], f[6], f[7]);
     }
   }
 }

@@ -47,7 +47,7 @@ class Communicator:
     def allreduce_grad_bucket(self, flat_g: torch.Tensor, scale: float, scale_dev: Optional[torch.Tensor] = None,
                               sumsq_dev: Optional[torch.Tensor] = None,
                               found_inf_dev: Optional[torch.Tensor] = None, max_blocks: int = 0,
-                              cta_threads: int = 0) -> bool:
+                              cta_threads: int = 0, algo: int = 0) -> bool:
         """Sum ``flat_g`` over ranks and multiply by ``scale`` in place. Returns True when the scale (and the
         optional sumsq / found_inf side outputs) were applied by the collective itself."""
         return False
@@ -199,7 +199,7 @@ class TorchDistCommunicator(Communicator):
 
     # ---- data plane ------------------------------------------------------------------------------------
     def allreduce_grad_bucket(self, flat_g, scale, scale_dev=None, sumsq_dev=None, found_inf_dev=None, max_blocks: int = 0,
-                              cta_threads: int = 0) -> bool:
+                              cta_threads: int = 0, algo: int = 0) -> bool:
         region = self._region_of(flat_g) if self.p2p else None
         if region is None:
             if self.compress_gradients:
@@ -220,18 +220,11 @@ class TorchDistCommunicator(Communicator):
         mc = region.multicast_ptr + off if (region.multicast_ptr and os.environ.get("DET_DISABLE_NVLS") != "1") else None
         _native.call("det_fused_allreduce_cta", region.table(off), self._flags.table(), ctypes.c_void_p(mc) if mc else None,
                      ctypes.c_void_p(self._epoch.data_ptr()), n, self.rank, self.size, float(scale),
-                     F._p(scale_dev), F._p(sumsq_dev), F._p(found_inf_dev), int(max_blocks), int(cta_threads), F._stream())
-        if sumsq_dev is not None:
-            # each rank holds the sum of squares of ITS slice: finish with a tiny metric reduce
-            self._sum_scalar_inplace(sumsq_dev)
+                     F._p(scale_dev), F._p(sumsq_dev), F._p(found_inf_dev), int(max_blocks), int(cta_threads), int(algo),
+                     F._stream())
+        # sumsq_dev / found_inf_dev now describe the WHOLE bucket on every rank: the kernel's last block exchanges the
+        # per-rank partials through the flag region (no second launch)
         return True
-
-    def _sum_scalar_inplace(self, t: torch.Tensor) -> None:
-        reg = self._metric_region
-        n = t.numel()
-        reg.local[:n].copy_(t.reshape(-1))
-        _native.call("det_metric_allreduce", reg.table(), self._flags.table(), ctypes.c_void_p(self._epoch.data_ptr()),
-                     F._p(t), None, n, self.rank, self.size, F.RED_SUM, F._stream())
 
     def allreduce_tensors(self, tensors, scale) -> None:
         for t in tensors:

@@ -166,15 +166,18 @@ class FusedOptimizer(torch.optim.Optimizer):
             grp.step_count += 1
             self._fill_hyper(grp, pg)
 
-    def device_step(self, max_grad_norm: float = 0.0, zero_grad: bool = True) -> None:
-        """Device half of a step (capturable): hyper H2D, optional fused clip, fused update."""
+    def device_step(self, max_grad_norm: float = 0.0, zero_grad: bool = True, sumsq_ready: bool = False) -> None:
+        """Device half of a step (capturable): hyper H2D, optional fused clip, fused update. ``sumsq_ready``: the
+        gradient all-reduce already left the bucket's sum of squares in ``_scratch[0]`` (and raised ``found_inf_dev``),
+        so the bucket is not read again."""
         assert self.fused
         scale = self.grad_scale_dev
         if max_grad_norm and max_grad_norm > 0:
             sc = self._scratch
-            sc[0:1].zero_()
-            for grp in self.groups:
-                F.grad_sumsq_finite(grp.flat_g, scale, sc[0:1], self.found_inf_dev)
+            if not sumsq_ready:
+                sc[0:1].zero_()
+                for grp in self.groups:
+                    F.grad_sumsq_finite(grp.flat_g, scale, sc[0:1], self.found_inf_dev)
             F.clip_coef(sc[0:1], max_grad_norm, scale, sc[2:4])
             scale = sc[2:3]
             self.last_grad_norm_dev = sc[3:4]
@@ -184,7 +187,7 @@ class FusedOptimizer(torch.optim.Optimizer):
                                    grp.flat_s2, grp.flat_shadow, grp.hyper_dev, scale, self.found_inf_dev, zero_grad)
 
     @torch.no_grad()
-    def step(self, closure=None, max_grad_norm: float = 0.0, zero_grad: bool = False):  # type: ignore[override]
+    def step(self, closure=None, max_grad_norm: float = 0.0, zero_grad: bool = False, sumsq_ready: bool = False):  # type: ignore[override]
         loss = None
         if closure is not None:
             with torch.enable_grad():
@@ -193,7 +196,7 @@ class FusedOptimizer(torch.optim.Optimizer):
             self.inner.step()
             return loss
         self.host_prepare()
-        self.device_step(max_grad_norm=max_grad_norm, zero_grad=zero_grad)
+        self.device_step(max_grad_norm=max_grad_norm, zero_grad=zero_grad, sumsq_ready=sumsq_ready)
         for observer in STEP_OBSERVERS:
             observer(self)
         return loss

@@ -53,6 +53,7 @@ class GradOverlap:
         self.args: Tuple[float, Optional[torch.Tensor], Optional[Callable[[FusedOptimizer], Optional[torch.Tensor]]]] = (1.0, None, None)
         self.stream: Optional[torch.cuda.Stream] = None
         self.launch_log: List[Tuple[int, int]] = []   # (start, n) in launch order, for tests / diagnostics
+        self.collects_sumsq = True   # every slice's collective adds the slice's sum of squares to opt._scratch[0]
         if self._on_notify not in M.GRAD_OBSERVERS:
             M.GRAD_OBSERVERS.append(self._on_notify)
 
@@ -86,6 +87,9 @@ class GradOverlap:
         """Called right before ``loss.backward()`` on a communicating batch: (re)compute what every unlaunched chunk is
         still waiting for from the forward-side use counts."""
         self.args = (scale, scale_dev, found_inf_of)
+        if not self.open:
+            for o in self.known_opts:   # grad-norm accumulator of this window (before any slice is launched)
+                o._scratch[0:1].zero_()
         for ch in self.chunks:
             if not ch.launched:
                 # Early launch only when EVERY trainable parameter of the chunk is tracked by a notifying autograd node
@@ -117,6 +121,7 @@ class GradOverlap:
         scale, scale_dev, found_inf_of = self.args
         found_inf = found_inf_of(ch.opt) if found_inf_of is not None else None
         view = ch.bucket[ch.start:ch.start + ch.n]
+        sumsq = ch.opt._scratch[0:1] if self.collects_sumsq else None
         ch.launched = True
         self.launch_log.append((ch.start, ch.n))
         if self.stream is not None:
@@ -126,12 +131,12 @@ class GradOverlap:
             with torch.cuda.stream(self.stream):
                 # small grid while backward is still running next to it; full width for the final flush
                 if overlapped:
-                    self.comm.allreduce_grad_bucket(view, scale, scale_dev=scale_dev, found_inf_dev=found_inf,
+                    self.comm.allreduce_grad_bucket(view, scale, scale_dev=scale_dev, found_inf_dev=found_inf, sumsq_dev=sumsq,
                                                     max_blocks=self.comm_blocks, cta_threads=self.cta_threads)
                 else:
-                    self.comm.allreduce_grad_bucket(view, scale, scale_dev=scale_dev, found_inf_dev=found_inf)
+                    self.comm.allreduce_grad_bucket(view, scale, scale_dev=scale_dev, found_inf_dev=found_inf, sumsq_dev=sumsq)
         else:
-            self.comm.allreduce_grad_bucket(view, scale, scale_dev=scale_dev, found_inf_dev=found_inf)
+            self.comm.allreduce_grad_bucket(view, scale, scale_dev=scale_dev, found_inf_dev=found_inf, sumsq_dev=sumsq)
 
     def armed_for(self, opt: FusedOptimizer) -> bool:
         return self.open and any(o is opt for o in self.known_opts)

@@ -301,6 +301,7 @@ class PyTorchTrialContext(TrialContext):
             scaler = self._loss_scaler
             self._overlap.arm(1.0 / self._grad_divisor(), scaler.state[2:3] if scaler is not None else None,
                               (lambda o: o.found_inf_dev) if scaler is not None else None)
+
         loss.backward(gradient=gradient, retain_graph=retain_graph, create_graph=create_graph)
 
     def _grad_divisor(self) -> float:
@@ -343,13 +344,20 @@ class PyTorchTrialContext(TrialContext):
             pass
         found_inf = opt.found_inf_dev if scaler is not None else None
         applied_all = True
+        # the collective also leaves the sum of squares of the whole reduced bucket (grad-norm clipping) when asked to
+        want_sumsq = max_norm > 0 and self.comm.size > 1 and slow_clip is None
         if self._overlap is not None and self._overlap.armed_for(opt):
             # slices were reduced on the side stream while backward ran; flush the rest and join
             applied_all = self._overlap.finish(opt)
+            want_sumsq = want_sumsq and self._overlap.collects_sumsq
         else:
+            if want_sumsq:
+                opt._scratch[0:1].zero_()
             for g in opt.grad_buckets():
-                applied = self.comm.allreduce_grad_bucket(g, 1.0 / divisor, scale_dev=inv_scale_dev, found_inf_dev=found_inf)
+                applied = self.comm.allreduce_grad_bucket(g, 1.0 / divisor, scale_dev=inv_scale_dev, found_inf_dev=found_inf,
+                                                          sumsq_dev=opt._scratch[0:1] if want_sumsq else None)
                 applied_all = applied_all and applied
+        sumsq_ready = bool(want_sumsq and applied_all)
         if applied_all and self.comm.size > 1:
             opt.grad_scale_dev.fill_(1.0)
         else:
@@ -375,7 +383,7 @@ class PyTorchTrialContext(TrialContext):
                 F.grad_sumsq_finite(g, opt.grad_scale_dev, sc[0:1], found_inf)
             if self.comm.size > 1:
                 self.comm.allreduce_max_int(found_inf)
-        opt.step(max_grad_norm=max_norm, zero_grad=auto_zero)
+        opt.step(max_grad_norm=max_norm, zero_grad=auto_zero, sumsq_ready=sumsq_ready)
         if scaler is not None:
             from ..ops import functional as F
 

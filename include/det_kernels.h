@@ -126,11 +126,15 @@ long long det_comm_epoch_bytes(void);
 int det_fused_allreduce(void* const* peer_bufs, void* const* peer_flags, void* mc_ptr, void* epoch_dev,
                         long long n_f32, int rank, int world, float scale, const float* scale_dev,
                         float* sumsq_dev, int* found_inf_dev, int max_blocks, cudaStream_t stream);
-/* Same collective with an explicit CTA size: `threads` = 128 gives CTAs small enough to be co-resident with a GEMM CTA on
- * the same SM (the overlapped all-reduce); 0 = the default 1024. */
+/* Same collective with an explicit CTA size and algorithm. `threads` = 128 gives CTAs small enough to be co-resident with
+ * a GEMM CTA on the same SM; 0 = the default 1024. `algo`: 0 = automatic (also DET_AR_ALGO), 1 = multimem.ld_reduce /
+ * multimem.st through the NVLS multicast address, 2 = 16-byte peer loads / stores, 3 = TMA bulk copies over peer memory
+ * (cp.async.bulk, 3 x 64 KB stages per CTA). On return sumsq_dev / found_inf_dev describe the WHOLE bucket on every rank
+ * (the per-rank partials are exchanged inside the kernel). */
 int det_fused_allreduce_cta(void* const* peer_bufs, void* const* peer_flags, void* mc_ptr, void* epoch_dev,
                             long long n_f32, int rank, int world, float scale, const float* scale_dev,
-                            float* sumsq_dev, int* found_inf_dev, int max_blocks, int threads, cudaStream_t stream);
+                            float* sumsq_dev, int* found_inf_dev, int max_blocks, int threads, int algo,
+                            cudaStream_t stream);
 int det_p2p_broadcast(void* const* peer_bufs, void* const* peer_flags, void* epoch_dev, long long nbytes, int rank,
                       int world, int root, cudaStream_t stream);
 int det_metric_allreduce(void* const* peer_bufs, void* const* peer_flags, void* epoch_dev, float* out_dev,

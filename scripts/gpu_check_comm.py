@@ -22,7 +22,9 @@ def main():
     if rank == 0:
         print("comm:", comm.describe(), flush=True)
     results = {}
-    for n in (4096, 1 << 20, 25 * (1 << 20) + 64):
+    ALGOS = {"auto": 0, "nvls": 1, "lsu": 2, "bulk": 3}
+    for algo_name, n in [(a, n) for a in ALGOS for n in (4096, 1 << 20, 25 * (1 << 20) + 64)]:
+        algo = ALGOS[algo_name]
         torch.manual_seed(100 + rank)
         g = comm.alloc(n, torch.float32, "grad", dev)
         g.copy_(torch.randn(n, device=dev))
@@ -31,7 +33,7 @@ def main():
         ref *= 0.125
         sumsq = torch.zeros(1, device=dev)
         finf = torch.zeros(1, dtype=torch.int32, device=dev)
-        applied = comm.allreduce_grad_bucket(g, 0.125, sumsq_dev=sumsq, found_inf_dev=finf)
+        applied = comm.allreduce_grad_bucket(g, 0.125, sumsq_dev=sumsq, found_inf_dev=finf, algo=algo)
         torch.cuda.synchronize()
         err = ((g - ref).abs().max() / ref.abs().max()).item()
         ss_ref = ref.double().pow(2).sum().item()
@@ -39,20 +41,21 @@ def main():
         good = applied and err < 1e-5 and ss_err < 1e-3 and finf.item() == 0
         ok &= good
         if rank == 0:
-            print(f"{'PASS' if good else 'FAIL'} allreduce n={n} applied={applied} err={err:.2e} sumsq_err={ss_err:.2e}", flush=True)
+            print(f"{'PASS' if good else 'FAIL'} allreduce[{algo_name}] n={n} applied={applied} err={err:.2e} sumsq_err={ss_err:.2e}", flush=True)
         # non-finite propagation
         g.copy_(torch.randn(n, device=dev))
         if rank == world - 1:
             g[n // 2] = float("nan")
         finf.zero_()
-        comm.allreduce_grad_bucket(g, 1.0, found_inf_dev=finf)
+        comm.allreduce_grad_bucket(g, 1.0, found_inf_dev=finf, algo=algo)
         torch.cuda.synchronize()
         flags = comm.allgather_object(int(finf.item()))
-        # the owner of the slice containing n//2 must have seen it
-        good = sum(flags) >= 1
+        # only the owner of the slice containing n//2 scans it, but the flag is exchanged inside the kernel: every rank
+        # must have raised it, or ranks would disagree about skipping the step
+        good = all(f == 1 for f in flags)
         ok &= good
         if rank == 0:
-            print(f"{'PASS' if good else 'FAIL'} allreduce found_inf flags={flags}", flush=True)
+            print(f"{'PASS' if good else 'FAIL'} allreduce[{algo_name}] found_inf flags={flags}", flush=True)
     # broadcast
     p = comm.alloc(1 << 20, torch.float32, "param", dev)
     p.fill_(float(rank + 1))
@@ -110,6 +113,15 @@ def main():
     t_nccl = timeit(nccl_path)
     t_nccl_only = timeit(lambda: dist.all_reduce(nccl_buf))
     bytes_moved = 2 * (world - 1) / world * n * 4
+    by_algo = {}
+    for algo_name, algo in ALGOS.items():
+        if algo == 0:
+            continue
+        for mb in ((0,) if algo != 3 else (24, 48, 64, 96, 128, 148)):
+            t = timeit(lambda: comm.allreduce_grad_bucket(g, 1.0 / world, sumsq_dev=sumsq, found_inf_dev=finf, algo=algo, max_blocks=mb), iters=8)
+            by_algo[f"{algo_name}_b{mb}"] = {"ms": round(t, 3), "busbw_gbs": round(bytes_moved / t / 1e6, 1)}
+    if rank == 0:
+        print("allreduce by algorithm:", json.dumps(by_algo), flush=True)
     # bandwidth against the number of CTAs: what a collective squeezed onto a few reserved SMs can deliver
     by_blocks = {}
     for mb in (2, 4, 8, 16, 32, 64, 0):
@@ -119,7 +131,7 @@ def main():
         print("allreduce vs CTAs:", json.dumps(by_blocks), flush=True)
     results = {"world": world, "bucket_mb": n * 4 / 1e6, "fused_ms": round(t_fused, 3), "nccl_allreduce_only_ms": round(t_nccl_only, 3),
                "nccl_plus_scale_finite_norm_ms": round(t_nccl, 3), "fused_busbw_gbs": round(bytes_moved / t_fused / 1e6, 1),
-               "nccl_busbw_gbs": round(bytes_moved / t_nccl_only / 1e6, 1), "comm": comm.describe()}
+               "nccl_busbw_gbs": round(bytes_moved / t_nccl_only / 1e6, 1), "by_algo": by_algo, "comm": comm.describe()}
     if rank == 0:
         print(json.dumps(results), flush=True)
         os.makedirs("gpurun_out", exist_ok=True)

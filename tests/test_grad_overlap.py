@@ -14,7 +14,7 @@ class FakeComm:
     def __init__(self):
         self.calls = []
 
-    def allreduce_grad_bucket(self, view, scale, scale_dev=None, found_inf_dev=None, max_blocks=0):
+    def allreduce_grad_bucket(self, view, scale, scale_dev=None, found_inf_dev=None, sumsq_dev=None, max_blocks=0, cta_threads=0):
         self.calls.append((view.data_ptr(), view.numel(), scale))
         return True
 
@@ -27,7 +27,7 @@ def make_opt(sizes):
         off += (n + 63) // 64 * 64
     flat = torch.zeros(off)
     grp = types.SimpleNamespace(params=params, offsets=offsets, total=off, flat_g=flat)
-    opt = types.SimpleNamespace(fused=True, groups=[grp], found_inf_dev=None)
+    opt = types.SimpleNamespace(fused=True, groups=[grp], found_inf_dev=None, _scratch=torch.zeros(4))
     return opt, params, flat
 
 
