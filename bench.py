@@ -300,12 +300,93 @@ def run_ours(args) -> Dict[str, Any]:
     return out
 
 
+BLOCKS = {
+    # BASELINE configs #2 and #4: name -> (trial, hparams, input shape, per-slot batch, H2D bytes per sample)
+    "resnet50": ("ResNet50Trial", {"learning_rate": 0.1, "use_cuda_graphs": True}, (3, 224, 224), 128, 224 * 224 * 3 + 8,
+                 "ResNet-50 (torchvision shape, 25.6M params), synthetic 224x224 uint8 NHWC batches, SGD momentum 0.9"),
+    "dcgan": ("DCGANTrial", {"latent_dim": 128, "use_cuda_graphs": True}, (3, 64, 64), 128, 3 * 64 * 64 * 4 + 8,
+              "DCGAN 64x64 generator + discriminator, two wrapped models / two Adam optimizers, both updates in one CUDA graph"),
+}
+
+
+def run_block(name: str, args, device, rank: int, world: int) -> Dict[str, Any]:
+    """One more trial through the public API (PyTorchTrialController over RUN_STEP workloads, one batch per step): every batch
+    is copied from pinned host memory, every workload's metrics are read back. Device-timed, max over ranks."""
+    import gc
+
+    import torch
+
+    from determined_b200 import _execution, load
+    from determined_b200 import workload as wl
+    from determined_b200.models import vision_trials as VT
+    from determined_b200.ops import _native
+
+    trial_name, hp, shape, batch, h2d_per_sample, desc = BLOCKS[name]
+    hp = dict(hp, global_batch_size=batch * world)
+    cfg = {"description": f"{name}_bench", "hyperparameters": hp,
+           "data": {"train_size": max(4 * batch * world, 512), "validation_size": batch * world},
+           "searcher": {"name": "single", "metric": "validation_loss", "max_length": {"batches": 1000}},
+           "resources": {"slots_per_trial": world}}
+    env, dist_ctx = _execution.make_local_execution_env(True, cfg, hparams=hp, seed=7)
+    env.experiment_config["resources"]["slots_per_trial"] = world
+    env._per_slot_batch_size, env._global_batch_size = env._calculate_batch_sizes()
+    timing: Dict[str, Any] = {}
+    box: Dict[str, Any] = {}
+    W, K = args.warmup, args.steps
+
+    def launches() -> int:
+        g = getattr(box.get("c"), "_graphed", None)
+        return _native.launch_count + (g.replayed_launches if g is not None else 0)
+
+    def workloads():
+        icpt = wl.WorkloadResponseInterceptor()
+        total = 0
+        for i in range(W + 6):   # graph capture needs a few eager batches first
+            yield from icpt.send(wl.train_workload(i + 1, num_batches=1, total_batches_processed=total), [])
+            total += 1
+        _barrier_sync(device)
+        n0 = launches()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        losses = []
+        for i in range(K):
+            yield from icpt.send(wl.train_workload(W + 7 + i, num_batches=1, total_batches_processed=total), [])
+            total += 1
+            r = icpt.result()
+            if not isinstance(r, wl.Skipped):
+                losses.append(r["metrics"]["avg_metrics"]["loss"])
+        e1.record()
+        _barrier_sync(device)
+        timing["ms"] = e0.elapsed_time(e1)
+        timing["launches"] = launches() - n0
+        timing["loss"] = losses[-1] if losses else None
+        yield from icpt.send(wl.terminate_workload(), [])
+
+    controller = load.load_controller_from_trial(getattr(VT, trial_name), env, workloads(), None, None, dist_ctx)
+    box["c"] = controller
+    controller.run()
+    ms = _max_over_ranks(timing["ms"], device)
+    value = batch * world * K / (ms / 1e3)
+    out = {"value": round(value, 1), "unit": "images/s", "ms_per_step": round(ms / K, 4),
+           "e2e": {"value": round(value, 1), "unit": "images/s", "h2d_bytes_per_step": batch * h2d_per_sample, "d2h_bytes_per_step": 4,
+                   "path": "PyTorchTrialController.run() over RUN_STEP workloads (one batch each); the timed region IS the public-API path"},
+           "config": {"model": desc, "global_batch": batch * world, "per_slot_batch": batch, "parallelism": f"dp{world}",
+                      "cuda_graphs": bool(getattr(controller, "_graphed", None)), "dtype": "bf16"},
+           "gpu_launches": int(timing["launches"]), "final_loss": timing["loss"]}
+    del controller, box
+    gc.collect()
+    torch.cuda.empty_cache()
+    return out
+
+
 def main() -> None:
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--models", default=os.environ.get("DET_BENCH_MODELS", "bert,resnet50,dcgan"),
+                    help="bert is the headline metric; resnet50 / dcgan add BASELINE configs #2 / #4 as extra blocks of the line")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     rank = int(os.environ.get("RANK", "0"))
@@ -315,6 +396,14 @@ def main() -> None:
         out = reference_arm.run(args)
     else:
         out = run_ours(args)
+        import torch
+
+        device = torch.device("cuda", int(os.environ.get("LOCAL_RANK", "0")))
+        for name in [m for m in args.models.split(",") if m in BLOCKS]:
+            try:
+                out[name] = run_block(name, args, device, rank, args.gpus)
+            except Exception as e:  # the headline number must survive a failing extra block
+                out[name] = {"error": repr(e)[:300]}
     if rank == 0:
         print(json.dumps(out), flush=True)
     try:
