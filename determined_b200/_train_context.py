@@ -12,9 +12,10 @@ from ._env import DistributedContext, EnvContext
 
 
 class TrialContext:
-    def __init__(self, env: EnvContext, dist: Optional[DistributedContext] = None) -> None:
+    def __init__(self, env: EnvContext, dist: Optional[DistributedContext] = None, comm: Any = None) -> None:
         self.env = env
         self.distributed = dist or DistributedContext()
+        self.comm = comm          # the trial's communicator (None outside a multi-slot trial); front-ends may replace it
         self._stop_requested = False
 
     @classmethod

@@ -27,6 +27,7 @@ import torch
 
 from .. import workload as wl
 from .._env import DistributedContext, EnvContext, RendezvousInfo
+from .._trial_controller import LoopTrialController
 from ..ops import functional as F
 from ..parallel.fused_optimizer import FusedOptimizer
 from ..utils import util
@@ -55,20 +56,14 @@ def _to_scalar_tensor(v: Any, device: torch.device) -> Optional[torch.Tensor]:
     return None
 
 
-class PyTorchTrialController:
+class PyTorchTrialController(LoopTrialController):
     def __init__(self, trial_inst: PyTorchTrial, context: PyTorchTrialContext, env: EnvContext,
                  workloads: wl.Stream, load_path: Optional[pathlib.Path] = None,
                  rendezvous_info: Optional[RendezvousInfo] = None) -> None:
         if not isinstance(trial_inst, PyTorchTrial):
             raise TypeError("PyTorchTrialController needs a PyTorchTrial instance")
+        super().__init__(context, env, workloads, load_path, rendezvous_info)
         self.trial = trial_inst
-        self.context = context
-        self.env = env
-        self.workloads = workloads
-        self.load_path = load_path
-        self.rendezvous_info = rendezvous_info
-        self.comm = context.comm
-        self.is_chief = self.comm.rank == 0
         self.callbacks = self.trial.build_callbacks()
         self._apply_backwards_compatibility()
         if not context.models:

@@ -11,11 +11,12 @@ from typing import Any, Dict, Union
 
 import torch
 
+from .._trial import Trial
 from . import _callback, _data, _reducer
 from ._context import PyTorchTrialContext
 
 
-class PyTorchTrial(metaclass=abc.ABCMeta):
+class PyTorchTrial(Trial):
     trial_context_class = PyTorchTrialContext
 
     @abc.abstractmethod

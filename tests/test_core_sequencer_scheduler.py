@@ -204,3 +204,69 @@ def test_fitting_single_agent_first_then_dedicated_multi_agent():
     req = {"scheduler": "fair_share", "agents": agents(4, label="a100"), "groups": [{"id": "g"}],
            "tasks": [{"id": "t", "group": "g", "slots_needed": 1, "label": "b200"}]}
     assert core.schedule(req)["to_allocate"] == []
+
+
+def test_reference_scenario_validation_and_checkpoint_periods_with_rollback_and_cached_checkpoint():
+    """The long scripted scenario the reference pins (master/internal/trial_workload_sequencer_test.go:17-268):
+    Train(500) + Validate + Checkpoint requested up front, min_validation_period 200, min_checkpoint_period 400,
+    checkpoint_policy none, scheduling_unit 100. Expected workload order, the pre-close checkpoint at each point, the
+    roll-back to the last completed checkpoint, and the searcher Checkpoint op being satisfied by the checkpoint that was
+    taken before the validation (a cached completion)."""
+    s = make_seq(min_val=200, min_ckpt=400, policy="none", scheduling_unit=100, searcher_len={"batches": 500})
+    assert s.up_to_date()
+    s.operation_requested({"kind": "train", "request_id": RID, "length": {"batches": 500}})
+    assert not s.up_to_date()
+    s.operation_requested({"kind": "validate", "request_id": RID})
+    s.operation_requested({"kind": "checkpoint", "request_id": RID})
+
+    def expect(kind, step, total):
+        w = s.workload()
+        assert (w["kind"], w["step_id"], w["total_batches_processed"]) == (kind, step, total), w
+        return w
+
+    w = expect("RUN_STEP", 1, 0)
+    assert s.preclose_checkpoint_workload() is None                     # nothing trained yet
+    assert complete(s, w)["op"] is None
+    w = expect("RUN_STEP", 2, 100)
+    pc = s.preclose_checkpoint_workload()
+    assert (pc["kind"], pc["step_id"], pc["total_batches_processed"]) == ("CHECKPOINT_MODEL", 1, 100)
+    assert complete(s, w)["op"] is None
+    w = expect("COMPUTE_VALIDATION_METRICS", 2, 200)                     # min_validation_period
+    assert s.preclose_checkpoint_workload()["step_id"] == 2
+    assert complete(s, w)["op"] is None
+    assert complete(s, expect("RUN_STEP", 3, 200))["op"] is None
+    assert complete(s, expect("RUN_STEP", 4, 300))["op"] is None
+    assert complete(s, expect("COMPUTE_VALIDATION_METRICS", 4, 400))["op"] is None
+    assert complete(s, expect("CHECKPOINT_MODEL", 4, 400))["op"] is None  # min_checkpoint_period
+    assert s.preclose_checkpoint_workload() is None
+    r = complete(s, expect("RUN_STEP", 5, 400))
+    assert r["op"]["kind"] == "train"                                    # the searcher's Train(500) is done
+    expect("CHECKPOINT_MODEL", 5, 500)                                   # a searcher Validate checkpoints first
+    assert s.roll_back() == 4                                            # back to the snapshot of the step-4 checkpoint
+    r = complete(s, expect("RUN_STEP", 5, 400))                          # step 5 is replayed
+    assert r["op"]["kind"] == "train"
+    assert complete(s, expect("CHECKPOINT_MODEL", 5, 500))["op"] is None
+    r = complete(s, expect("COMPUTE_VALIDATION_METRICS", 5, 500))
+    assert r["op"]["kind"] == "validate"
+    assert s.preclose_checkpoint_workload() is None
+    r = s.complete_cached_checkpoints()
+    assert r["op"]["kind"] == "checkpoint"                               # satisfied by the step-5 checkpoint already taken
+    assert s.up_to_date()
+    with pytest.raises(core.CoreError):
+        s.workload()
+
+
+def test_failed_checkpoint_marks_early_exit_and_short_record_lengths_round_up_to_one_batch():
+    s = make_seq(min_ckpt=100, policy="none")
+    s.operation_requested({"kind": "train", "request_id": RID, "length": {"batches": 500}})
+    complete(s, s.workload())
+    w = s.workload()
+    assert w["kind"] == "CHECKPOINT_MODEL"
+    r = s.workload_completed({"workload": w, "exited_reason": "ERRORED"}, False)
+    assert r["op"] is None and s.state()["exiting_early"] is True
+    # Train(24 records) at global_batch_size 64 is one batch
+    s = make_seq(gbs=64, searcher_len={"records": 24})
+    s.operation_requested({"kind": "train", "request_id": RID, "length": {"records": 24}})
+    w = s.workload()
+    assert (w["kind"], w["num_batches"]) == ("RUN_STEP", 1)
+    assert complete(s, w)["op"]["kind"] == "train"

@@ -142,3 +142,25 @@ def test_cluster_endpoints_and_registry(master):
         time.sleep(0.1)
     assert c["state"] == "TERMINATED" and any("hello-from-command" in l["message"] for l in c["logs"])
     del m
+
+
+def test_adaptive_search_survives_random_failures(master):
+    """The blueprint's step-3 exit test (reference: e2e_tests/tests/fixtures/no_op/adaptive_chaos.yaml): an adaptive search
+    whose trials fail 5 % of their workloads at random still reaches COMPLETED — every failed trial is rolled back to its
+    last checkpoint and rescheduled (max_restarts 1000) — and the restarts really happened."""
+    import yaml
+
+    d = Determined(master["url"])
+    noop = ROOT / "tests" / "fixtures" / "no_op"
+    cfg = yaml.safe_load((noop / "adaptive_chaos.yaml").read_text())
+    cfg["checkpoint_storage"] = {"type": "shared_fs", "host_path": str(master["tmp"] / "ckpts")}
+    exp = d.create_experiment(cfg, str(noop))
+    assert exp.wait(timeout=900) == "COMPLETED"
+    desc = exp.describe()
+    trials = desc["trials"]
+    assert len(trials) >= 5 and all(t["state"] == "COMPLETED" for t in trials)
+    assert desc["progress"] == 1.0
+    assert sum(t["restarts"] for t in trials) >= 1, "no workload failed: the chaos knob did not reach the trial"
+    # successive halving: most trials stop at the bottom rung, at least one is promoted to the full length
+    lens = sorted(t["total_batches_processed"] for t in trials)
+    assert lens[-1] == 320 and lens[0] < 320
