@@ -96,9 +96,8 @@ def test_adaptive_asha_bracket_arithmetic_through_behaviour():
     got = sim(cfg)
     starts = collections.Counter(k.split()[0] for k, n in got.items() for _ in range(n))
     assert starts == {"100B": 70, "400B": 22, "1600B": 8}
-    # brackets of 4 and 3 rungs, divisor 3: 50 trials split 35 / 15
+    # brackets of 4, 3 and 2 rungs, divisor 3: weights 27/4, 9/3, 3/2 -> 50 trials split 31 / 13 / 6 (remainder to the first)
     cfg = dict(cfg, max_trials=50, max_rungs=4, mode="standard", divisor=3, max_length={"batches": 2700})
-    cfg["mode"] = "standard"
-    got = sim(dict(cfg, max_rungs=4))
+    got = sim(cfg)
     starts = collections.Counter(k.split()[0] for k, n in got.items() for _ in range(n))
-    assert starts == {"100B": 35, "300B": 15}
+    assert starts == {"100B": 31, "300B": 13, "900B": 6}
