@@ -21,6 +21,7 @@
 #include <poll.h>
 
 #include "json.hpp"
+#include "tls.hpp"
 
 namespace det {
 
@@ -73,6 +74,13 @@ class HttpServer {
   using Handler = std::function<HttpResponse(const HttpRequest&)>;
   void route(const std::string& method, const std::string& pattern, Handler h) { routes_.push_back(Route{method, split(pattern), std::move(h)}); }
   void set_middleware(std::function<bool(const HttpRequest&, HttpResponse&)> mw) { middleware_ = std::move(mw); }
+  // Serve HTTPS instead of HTTP (PEM certificate chain + key). Call before listen(); returns false and fills *err when the
+  // files cannot be loaded.
+  bool enable_tls(const std::string& cert_file, const std::string& key_file, std::string* err) {
+    tls_ctx_ = tls_server_context(cert_file, key_file, err);
+    return tls_ctx_ != nullptr;
+  }
+  bool tls_enabled() const { return tls_ctx_ != nullptr; }
 
   // Binds and listens; returns the bound port (useful with port 0) or -1.
   int listen(const std::string& host, int port) {
@@ -121,12 +129,12 @@ class HttpServer {
     while (std::getline(ss, item, '/')) if (!item.empty()) out.push_back(item);
     return out;
   }
-  static bool read_request(int c, HttpRequest& req) {
+  static bool read_request(Stream& c, HttpRequest& req) {
     std::string buf;
     char tmp[8192];
     size_t header_end = std::string::npos;
     while (header_end == std::string::npos) {
-      ssize_t n = ::recv(c, tmp, sizeof tmp, 0);
+      ssize_t n = c.read(tmp, sizeof tmp);
       if (n <= 0) return false;
       buf.append(tmp, static_cast<size_t>(n));
       header_end = buf.find("\r\n\r\n");
@@ -161,23 +169,60 @@ class HttpServer {
     }
     size_t content_len = 0;
     auto it = req.headers.find("content-length");
-    if (it != req.headers.end()) content_len = static_cast<size_t>(atoll(it->second.c_str()));
+    if (it != req.headers.end()) {
+      // digits only, and bounded: a model-definition upload is capped at 96 MB by the clients; nothing legitimate is larger
+      const std::string& v = it->second;
+      if (v.empty() || v.size() > 10 || v.find_first_not_of("0123456789") != std::string::npos) return false;
+      const long long n = atoll(v.c_str());
+      if (n < 0 || n > (256LL << 20)) return false;
+      content_len = static_cast<size_t>(n);
+    }
     req.body = buf.substr(header_end + 4);
     while (req.body.size() < content_len) {
-      ssize_t n = ::recv(c, tmp, sizeof tmp, 0);
+      ssize_t n = c.read(tmp, sizeof tmp);
       if (n <= 0) return false;
       req.body.append(tmp, static_cast<size_t>(n));
     }
     return true;
   }
-  void handle(int c, const std::string& remote_addr) {
+  void handle(int cfd, const std::string& remote_addr) {
+    Stream c(cfd);
+    if (tls_ctx_ && !c.accept_tls(tls_ctx_)) return;   // not a TLS client (or a failed handshake): drop the connection
     HttpRequest req;
     req.remote_addr = remote_addr;
     if (read_request(c, req)) {
       HttpResponse resp = dispatch(req);
       if (resp.hijack) {
-        resp.hijack(c);
-        ::close(c);
+        if (!c.tls()) {
+          resp.hijack(c.fd());
+        } else {
+          // the handler speaks plain bytes on a socket of its own; pump them through the TLS session
+          int sv[2];
+          if (::socketpair(AF_UNIX, SOCK_STREAM | SOCK_CLOEXEC, 0, sv) == 0) {
+            std::thread pump([&c, fd = sv[0]] {
+              pollfd fds[2] = {{c.fd(), POLLIN, 0}, {fd, POLLIN, 0}};
+              char buf[16384];
+              for (;;) {
+                if (!c.pending() && ::poll(fds, 2, 3600 * 1000) <= 0) break;
+                if (c.pending() || (fds[0].revents & POLLIN)) {
+                  const ssize_t n = c.read(buf, sizeof buf);
+                  if (n <= 0 || ::send(fd, buf, static_cast<size_t>(n), MSG_NOSIGNAL) <= 0) break;
+                }
+                if (fds[1].revents & POLLIN) {
+                  const ssize_t n = ::recv(fd, buf, sizeof buf, 0);
+                  if (n <= 0 || !c.write_all(buf, static_cast<size_t>(n))) break;
+                }
+                if ((fds[0].revents | fds[1].revents) & (POLLHUP | POLLERR | POLLNVAL)) break;
+              }
+              ::shutdown(fd, SHUT_RDWR);
+            });
+            resp.hijack(sv[1]);
+            ::shutdown(sv[1], SHUT_RDWR);
+            pump.join();
+            ::close(sv[0]);
+            ::close(sv[1]);
+          }
+        }
         return;
       }
       static const std::map<int, const char*> reason = {{200, "OK"}, {201, "Created"}, {204, "No Content"}, {400, "Bad Request"},
@@ -189,14 +234,8 @@ class HttpServer {
          << "Content-Type: " << resp.content_type << "\r\nContent-Length: " << resp.body.size()
          << "\r\nAccess-Control-Allow-Origin: *\r\nConnection: close\r\n\r\n" << resp.body;
       const std::string out = os.str();
-      size_t sent = 0;
-      while (sent < out.size()) {
-        ssize_t n = ::send(c, out.data() + sent, out.size() - sent, MSG_NOSIGNAL);
-        if (n <= 0) break;
-        sent += static_cast<size_t>(n);
-      }
+      c.write_all(out.data(), out.size());
     }
-    ::close(c);
   }
   HttpResponse dispatch(HttpRequest& req) {
     try {
@@ -228,6 +267,7 @@ class HttpServer {
   std::vector<Route> routes_;
   std::function<bool(const HttpRequest&, HttpResponse&)> middleware_;
   int fd_ = -1, port_ = 0;
+  SSL_CTX* tls_ctx_ = nullptr;
   std::atomic<bool> stop_{false};
   std::thread thread_;
 };
@@ -250,9 +290,11 @@ inline in_addr_t resolve_ipv4(const std::string& host) {
   return INADDR_NONE;
 }
 
-// Blocking one-shot client: returns status (or -1) and fills body.
+// Blocking one-shot client: returns status (or -1) and fills body. With tls.enabled the request goes over TLS and the
+// server's certificate is checked against tls.ca_file / tls.cert_name (see tls.hpp).
 inline int http_request(const std::string& host, int port, const std::string& method, const std::string& path,
-                        const std::string& body, std::string* out, int timeout_s = 60, const std::string& auth = "") {
+                        const std::string& body, std::string* out, int timeout_s = 60, const std::string& auth = "",
+                        const TlsClientOptions& tls = TlsClientOptions()) {
   int fd = ::socket(AF_INET, SOCK_STREAM | SOCK_CLOEXEC, 0);
   if (fd < 0) return -1;
   timeval tv{timeout_s, 0};
@@ -262,18 +304,26 @@ inline int http_request(const std::string& host, int port, const std::string& me
   addr.sin_port = htons(static_cast<uint16_t>(port));
   addr.sin_addr.s_addr = resolve_ipv4(host);
   if (::connect(fd, reinterpret_cast<sockaddr*>(&addr), sizeof addr) < 0) { ::close(fd); return -1; }
+  Stream c(fd);
+  if (tls.enabled) {
+    std::string err;
+    SSL_CTX* ctx = tls_client_context(tls, &err);
+    if (ctx == nullptr || !c.connect_tls(ctx, host, tls, &err)) {
+      if (out) *out = err;
+      return -1;
+    }
+  }
   std::ostringstream os;
   os << method << " " << path << " HTTP/1.1\r\nHost: " << host << "\r\nContent-Type: application/json\r\nContent-Length: " << body.size()
      << "\r\nConnection: close\r\n";
   if (!auth.empty()) os << "Authorization: Bearer " << auth << "\r\n";
   os << "\r\n" << body;
   const std::string req = os.str();
-  if (::send(fd, req.data(), req.size(), MSG_NOSIGNAL) < 0) { ::close(fd); return -1; }
+  if (!c.write_all(req.data(), req.size())) return -1;
   std::string buf;
   char tmp[8192];
   ssize_t n;
-  while ((n = ::recv(fd, tmp, sizeof tmp, 0)) > 0) buf.append(tmp, static_cast<size_t>(n));
-  ::close(fd);
+  while ((n = c.read(tmp, sizeof tmp)) > 0) buf.append(tmp, static_cast<size_t>(n));
   auto he = buf.find("\r\n\r\n");
   if (he == std::string::npos) return -1;
   int status = -1;

@@ -3,7 +3,10 @@
 // serves extra nodes: it long-polls the master for container commands (start / signal), runs them under its own
 // ContainerManager with the slot's CUDA_VISIBLE_DEVICES mask, and posts container state changes and log lines back.
 //   det-agent [--master-host H] [--master-port N] [--agent-id ID] [--label L] [--slot-type auto|gpu|cpu|none]
-//             [--visible-gpus LIST] [--artificial-slots N] [--detect-only]
+//             [--visible-gpus LIST] [--artificial-slots N] [--detect-only] [--container-master-host H]
+//             [--security-tls-enabled] [--security-tls-skip-verify] [--security-tls-master-cert FILE]
+//             [--security-tls-master-cert-name NAME] [--config-file agent.yaml-as-json]
+// Every flag can also come from DET_AGENT_<FLAG> (upper case, dashes as underscores), flags win.
 // (reference: agent/cmd/determined-agent/run.go, agent/internal/options.go:12-103, agent.go:60-150)
 #include <unistd.h>
 
@@ -20,9 +23,17 @@ static void on_signal(int) { g_stop = true; }
 
 int main(int argc, char** argv) {
   using namespace det;
-  std::string host = "127.0.0.1", id, label, slot_type = "auto", visible;
+  std::string host = "127.0.0.1", id, label, slot_type = "auto", visible, container_master_host;
   int port = 8080, artificial = 0;
   bool detect_only = false;
+  TlsClientOptions tls;
+  auto envs = [](const char* k, std::string& dst) { if (const char* v = getenv(k)) dst = v; };
+  auto envb = [](const char* k, bool& dst) { if (const char* v = getenv(k)) dst = std::string(v) == "1" || std::string(v) == "true"; };
+  envs("DET_AGENT_MASTER_HOST", host); envs("DET_AGENT_LABEL", label); envs("DET_AGENT_SLOT_TYPE", slot_type);
+  envs("DET_AGENT_VISIBLE_GPUS", visible); envs("DET_AGENT_CONTAINER_MASTER_HOST", container_master_host);
+  envb("DET_AGENT_SECURITY_TLS_ENABLED", tls.enabled); envb("DET_AGENT_SECURITY_TLS_SKIP_VERIFY", tls.skip_verify);
+  envs("DET_AGENT_SECURITY_TLS_MASTER_CERT", tls.ca_file); envs("DET_AGENT_SECURITY_TLS_MASTER_CERT_NAME", tls.cert_name);
+  if (const char* v = getenv("DET_AGENT_MASTER_PORT")) port = atoi(v);
   char hostname[256] = "agent";
   gethostname(hostname, sizeof hostname);
   id = std::string("agent-") + hostname;
@@ -37,6 +48,11 @@ int main(int argc, char** argv) {
     else if (a == "--visible-gpus") visible = next();
     else if (a == "--artificial-slots") artificial = atoi(next().c_str());
     else if (a == "--detect-only") detect_only = true;
+    else if (a == "--container-master-host") container_master_host = next();
+    else if (a == "--security-tls-enabled") tls.enabled = true;
+    else if (a == "--security-tls-skip-verify") tls.skip_verify = true;
+    else if (a == "--security-tls-master-cert") tls.ca_file = next();
+    else if (a == "--security-tls-master-cert-name") tls.cert_name = next();
     else if (a == "--repo-root" || a == "--python") next();   // accepted for symmetry with det-master; specs carry both
     else { std::cerr << "unknown flag " << a << "\n"; return 2; }
   }
@@ -55,9 +71,9 @@ int main(int argc, char** argv) {
   signal(SIGTERM, on_signal);
   std::string out;
   while (!g_stop) {
-    const int st = http_request(host, port, "POST", "/api/v1/agents/" + id + "/register", body.dump(), &out, 10);
+    const int st = http_request(host, port, "POST", "/api/v1/agents/" + id + "/register", body.dump(), &out, 10, "", tls);
     if (st == 200) break;
-    std::cerr << "det-agent: master not reachable at " << host << ":" << port << " (status " << st << "); retrying\n";
+    std::cerr << "det-agent: master not reachable at " << host << ":" << port << " (status " << st << (st < 0 && !out.empty() ? ": " + out : std::string()) << "); retrying\n";
     sleep(2);
   }
   std::cerr << "det-agent " << id << ": registered " << devices.size() << " slots with " << host << ":" << port << "\n";
@@ -91,7 +107,7 @@ int main(int argc, char** argv) {
       }
       std::string o;
       for (int attempt = 0; attempt < 20 && !g_stop; ++attempt) {
-        if (http_request(host, port, "POST", "/api/v1/agents/" + id + "/events", b.dump(), &o, 10) == 200) break;
+        if (http_request(host, port, "POST", "/api/v1/agents/" + id + "/events", b.dump(), &o, 10, "", tls) == 200) break;
         sleep(1);
       }
     }
@@ -99,7 +115,7 @@ int main(int argc, char** argv) {
   time_t last_register = time(nullptr);
   while (!g_stop) {
     std::string resp;
-    const int st = http_request(host, port, "GET", "/api/v1/agents/" + id + "/commands?wait_ms=5000", "", &resp, 15);
+    const int st = http_request(host, port, "GET", "/api/v1/agents/" + id + "/commands?wait_ms=5000", "", &resp, 15, "", tls);
     if (st != 200) { sleep(2); }
     else {
       Json cmds = Json::parse(resp)["commands"];
@@ -110,6 +126,15 @@ int main(int argc, char** argv) {
           spec.description = c["description"].as_string(); spec.cwd = c["cwd"].as_string();
           for (auto& a : c["argv"].arr()) spec.argv.push_back(a.as_string());
           for (auto& kv : c["env"].obj()) spec.env[kv.first] = kv.second.as_string();
+          // tasks on this node reach the master the way this agent does: its address (or the configured override) and the
+          // certificate this agent pins (reference agent/internal/options.go: container_master_host, security.tls.master_cert)
+          if (!container_master_host.empty()) { spec.env["DET_MASTER_ADDR"] = container_master_host; spec.env["DET_MASTER_HOST"] = container_master_host; }
+          if (tls.enabled) {
+            spec.env["DET_USE_TLS"] = "true";
+            if (tls.skip_verify) spec.env["DET_MASTER_CERT_FILE"] = "noverify";
+            else if (!tls.ca_file.empty()) spec.env["DET_MASTER_CERT_FILE"] = tls.ca_file;
+            if (!tls.cert_name.empty()) spec.env["DET_MASTER_CERT_NAME"] = tls.cert_name;
+          }
           for (auto& d : c["devices"].arr())
             spec.devices.push_back(Device{static_cast<int>(d["id"].as_int()), d["brand"].as_string(), d["uuid"].as_string(), d["type"].as_string()});
           cm.start(spec);
@@ -120,11 +145,11 @@ int main(int argc, char** argv) {
     }
     if (time(nullptr) - last_register >= 5) {  // heartbeat: re-register if the master restarted
       last_register = time(nullptr);
-      http_request(host, port, "POST", "/api/v1/agents/" + id + "/register", body.dump(), &out, 10);
+      http_request(host, port, "POST", "/api/v1/agents/" + id + "/register", body.dump(), &out, 10, "", tls);
     }
   }
   cm.kill_all();
   flusher.join();
-  http_request(host, port, "POST", "/api/v1/agents/" + id + "/unregister", "{}", &out, 5);
+  http_request(host, port, "POST", "/api/v1/agents/" + id + "/unregister", "{}", &out, 5, "", tls);
   return 0;
 }

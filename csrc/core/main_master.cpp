@@ -55,6 +55,13 @@ int main(int argc, char** argv) {
       else if (a == "--resource-manager") j["resource_manager"] = det::Json::parse(next());   // {"type": "kubernetes", ...}
       else if (a == "--visible-gpus") j["visible_gpus"] = next();
       else if (a == "--auth-required") j["auth_required"] = true;
+      else if (a == "--security-tls-cert" || a == "--security-tls-key" || a == "--security-tls-master-cert-name") {
+        det::Json sec = j["security"].is_object() ? j["security"] : det::Json::object();
+        det::Json t = sec["tls"].is_object() ? sec["tls"] : det::Json::object();
+        t[a == "--security-tls-cert" ? "cert" : (a == "--security-tls-key" ? "key" : "master_cert_name")] = next();
+        sec["tls"] = t;
+        j["security"] = sec;
+      }
       else if (a == "--print-port-file") port_file = next();
       else if (a == "--help" || a == "-h") { std::cout << "usage: det-master [--config F] [--port N] [--host H] [--data-dir D] [--scheduler fair_share|priority|round_robin] [--artificial-slots N] [--repo-root P] [--python EXE]\n"; return 0; }
       else throw ConfigError("unknown flag " + a);

@@ -71,6 +71,18 @@ MasterConfig MasterConfig::from_json(const Json& j) {
   c.visible_gpus = j["visible_gpus"].str_or("");
   c.artificial_slots = static_cast<int>(j["artificial_slots"].as_int(0));
   c.auth_required = j["auth_required"].as_bool(false) || j["security"]["auth_required"].as_bool(false);
+  if (j["security"].is_object()) {
+    static const std::set<std::string> sec_known = {"auth_required", "tls", "default_task"};
+    for (auto& kv : j["security"].obj())
+      if (!sec_known.count(kv.first)) throw ConfigError("unknown field in master config: 'security." + kv.first + "'");
+    const Json& t = j["security"]["tls"];
+    if (t.is_object()) {
+      c.tls_cert = t["cert"].str_or("");
+      c.tls_key = t["key"].str_or("");
+      c.tls_cert_name = t["master_cert_name"].str_or("");
+      if (c.tls_cert.empty() != c.tls_key.empty()) throw ConfigError("security.tls needs both cert and key");
+    }
+  }
   c.cluster_name = j["cluster_name"].str_or(c.cluster_name);
   c.provisioner = j["provisioner"];
   c.telemetry = j["telemetry"];
@@ -437,10 +449,14 @@ int Master::start() {
                                      {"addresses", Json(Json::array_t{Json("127.0.0.1")})}, {"driver_version", nvidia_driver_version()}}));
   }
   register_routes();
+  if (!cfg.tls_cert.empty()) {
+    std::string err;
+    if (!http.enable_tls(cfg.tls_cert, cfg.tls_key, &err)) throw std::runtime_error("security.tls: " + err);
+  }
   const int port = http.listen(cfg.host, cfg.port);
   if (port >= 0 && cfg.provisioner.is_object()) provisioner = system.actor_of("provisioner", make_provisioner(this, cfg.provisioner));
   if (port < 0) throw std::runtime_error("cannot bind " + cfg.host + ":" + std::to_string(cfg.port));
-  log("info", "master listening on " + cfg.host + ":" + std::to_string(port) + " with " + std::to_string(devices.size()) + " local slots (" + cfg.scheduler + ")");
+  log("info", std::string("master listening on ") + (http.tls_enabled() ? "https://" : "http://") + cfg.host + ":" + std::to_string(port) + " with " + std::to_string(devices.size()) + " local slots (" + cfg.scheduler + ")");
   if (kube) kube->start();
   report_telemetry("master_started", obj({{"scheduler", cfg.scheduler}, {"resource_manager", kube ? "kubernetes" : "agent"},
                                           {"local_slots", static_cast<long long>(devices.size())}, {"provisioner", cfg.provisioner.is_object()}}));

@@ -42,6 +42,8 @@ struct MasterConfig {
   std::string visible_gpus;
   int artificial_slots = 0;
   bool auth_required = false;
+  std::string tls_cert, tls_key;         // security.tls.{cert,key}: serve HTTPS (reference master/internal/config.go:252-256)
+  std::string tls_cert_name;             // security.tls.master_cert_name: the name tasks and agents expect in the certificate
   std::string cluster_name = "b200-box";
   Json provisioner;                      // {max_instances, slots_per_instance, max_idle_agent_period, ...} or null
   Json resource_manager;                 // null / {type: agent} or {type: kubernetes, namespace, api_server, image, ...}

@@ -2,6 +2,7 @@
 // reference uses WebSockets (/ws/trial/:exp/:trial/:container). Route groups follow the reference's
 // master/internal/core.go:313-606 and api_*.go: experiments, trials, checkpoints, tasks, searcher preview, agents/slots,
 // users/auth, templates, models, commands/notebooks/shells/tensorboards, master info/logs/config.
+#include <sys/stat.h>
 #include <algorithm>
 #include <fstream>
 #include <sstream>
@@ -69,10 +70,20 @@ Json trial_detail(Store& store, const Json& t, bool with_metrics) {
 void Master::register_routes() {
   Master* m = this;
   http.set_middleware([m](const HttpRequest& req, HttpResponse& resp) {
-    // harness / agent callbacks and login are exempt; everything else needs a session when auth is required
-    static const char* open[] = {"/api/v1/auth/login", "/api/v1/trials/", "/api/v1/trial_logs", "/api/v1/master", "/info", "/api/v1/agents/",
-                                 "/api/v1/rw_coordinator/", "/ui"};
-    for (auto* p : open) if (req.path.rfind(p, 0) == 0) return true;
+    // Exempt are exact (method, route) pairs only: login, the harness's workload exchange and log shipping, the agents'
+    // register / commands / events calls, the data-layer lease service used from inside tasks, and the public info pages.
+    // Everything that changes cluster state from outside a task (trial kill, agent unregister, slot enable / disable,
+    // master config, tracing) needs a session when auth is required.
+    auto ends_with = [](const std::string& s, const char* suf) { const size_t n = strlen(suf); return s.size() >= n && s.compare(s.size() - n, n, suf) == 0; };
+    const std::string& p = req.path;
+    const bool get = req.method == "GET", post = req.method == "POST";
+    if (post && p == "/api/v1/auth/login") return true;
+    if (get && (p == "/info" || p == "/api/v1/master" || p.rfind("/ui", 0) == 0 || p == "/")) return true;
+    if (p.rfind("/api/v1/trials/", 0) == 0 && ((get && ends_with(p, "/next_workload")) || (post && ends_with(p, "/workload_completed")))) return true;
+    if (post && p == "/api/v1/trial_logs") return true;
+    if (p.rfind("/api/v1/agents/", 0) == 0 && p.find("/slots/") == std::string::npos &&
+        ((post && (ends_with(p, "/register") || ends_with(p, "/events"))) || (get && ends_with(p, "/commands")))) return true;
+    if (p.rfind("/api/v1/rw_coordinator/", 0) == 0) return true;
     if (m->check_auth(req, nullptr)) return true;
     resp = HttpResponse::error(401, "authentication required: POST /api/v1/auth/login");
     return false;
@@ -86,9 +97,17 @@ void Master::register_routes() {
   http.route("GET", "/info", info);
   // ---- debugging (role of the reference's /debug/pprof and actor tracing, master/internal/core.go:564-568) ----
   http.route("GET", "/debug/actors", [m](const HttpRequest&) { return ok(m->system.describe_actors()); });
-  http.route("POST", "/debug/trace", [m](const HttpRequest& r) {   // {"file": "/tmp/actors.trace"} or {"file": ""} to stop
-    m->system.enable_trace(r.json()["file"].str_or(""));
-    return ok(Json::object());
+  http.route("POST", "/debug/trace", [m](const HttpRequest& r) {   // {"file": "actors.trace"} (written under <data_dir>/traces/) or {"file": ""} to stop
+    // the trace is written under <data_dir>/traces/: a caller chooses a file NAME, never a path
+    std::string name = r.json()["file"].str_or("");
+    if (name.empty()) { m->system.enable_trace(""); return ok(Json::object()); }
+    const auto slash = name.find_last_of('/');
+    if (slash != std::string::npos) name = name.substr(slash + 1);
+    if (name.empty() || name == "." || name == "..") return HttpResponse::error(400, "file must be a plain file name");
+    const std::string dir = m->cfg.data_dir + "/traces";
+    ::mkdir(dir.c_str(), 0755);
+    m->system.enable_trace(dir + "/" + name);
+    return ok(obj({{"file", dir + "/" + name}}));
   });
   // ---- data-layer reader/writer leases (reference: /ws/data-layer/{resource}, master/internal/rw_coordinator.go) ----
   http.route("POST", "/api/v1/rw_coordinator/:resource/:verb", [m](const HttpRequest& r) {

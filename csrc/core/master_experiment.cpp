@@ -206,6 +206,12 @@ class TrialActor : public Actor {
       e["DET_MASTER_ADDR"] = m_->cfg.host == "0.0.0.0" ? "127.0.0.1" : m_->cfg.host;
       e["DET_MASTER_PORT"] = std::to_string(m_->http.port());
       e["DET_MASTER_HOST"] = e["DET_MASTER_ADDR"];
+      if (m_->http.tls_enabled()) {   // the task pins the master's own certificate (reference tasks/task.go: master cert archive)
+        e["DET_USE_TLS"] = "true";
+        e["DET_MASTER_CERT_FILE"] = m_->cfg.tls_cert;
+        if (!m_->cfg.tls_cert_name.empty()) e["DET_MASTER_CERT_NAME"] = m_->cfg.tls_cert_name;
+      }
+      e["DET_TRIAL_UNIQUE_PORT_OFFSET"] = std::to_string(trial_id_ % 16);
       e["DET_EXPERIMENT_ID"] = std::to_string(exp_id_);
       e["DET_TRIAL_ID"] = std::to_string(trial_id_);
       e["DET_TRIAL_SEED"] = std::to_string(create_.trial_seed);

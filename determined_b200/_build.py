@@ -109,12 +109,12 @@ def build_core(force: bool = False, verbose: bool = False) -> Path:
         list(ex.map(_run, jobs))
     lib_objs = [o for o, s in zip(objs, srcs) if not s.stem.startswith("main_")]
     if force or jobs or not lib.exists():
-        _run([cxx, "-shared", "-o", str(lib), *map(str, lib_objs), "-pthread"])
+        _run([cxx, "-shared", "-o", str(lib), *map(str, lib_objs), "-pthread", "-lssl", "-lcrypto"])
     for o, s in zip(objs, srcs):
         if s.stem.startswith("main_"):
             exe = LIB_DIR / ("det-" + s.stem[len("main_"):].replace("_", "-"))
             if force or jobs or not exe.exists():
-                _run([cxx, "-o", str(exe), str(o), *map(str, lib_objs), "-pthread"])
+                _run([cxx, "-o", str(exe), str(o), *map(str, lib_objs), "-pthread", "-lssl", "-lcrypto"])
     return lib
 
 
@@ -128,7 +128,7 @@ def build_selftest_tsan(verbose: bool = False) -> Path:
     last: Optional[Exception] = None
     # not every toolchain ships the sanitizer runtimes: try $CXX first, then the distribution compiler
     for cxx in dict.fromkeys([os.environ.get("CXX") or "g++", "g++", "/usr/bin/g++"]):
-        cmd = [cxx, *flags, "-O1", "-g", "-fsanitize=thread", "-fno-omit-frame-pointer", *map(str, srcs), "-o", str(out), "-pthread"]
+        cmd = [cxx, *flags, "-O1", "-g", "-fsanitize=thread", "-fno-omit-frame-pointer", *map(str, srcs), "-o", str(out), "-pthread", "-lssl", "-lcrypto"]
         if verbose:
             print("[build] " + " ".join(cmd[:12]) + " ...", file=sys.stderr)
         try:

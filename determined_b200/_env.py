@@ -118,8 +118,12 @@ class EnvContext:
                  debug: bool = False, workload_manager_type: str = "TRIAL_WORKLOAD_MANAGER",
                  det_rendezvous_ports: str = "", det_trial_runner_network_interface: str = "",
                  det_trial_id: str = "1", det_experiment_id: str = "1", det_cluster_id: str = "local",
-                 trial_seed: int = 0, managed_training: bool = True) -> None:
+                 trial_seed: int = 0, managed_training: bool = True, use_tls: bool = False,
+                 master_cert_file: Optional[str] = None, master_cert_name: Optional[str] = None,
+                 det_trial_unique_port_offset: int = 0) -> None:
         self.master_addr, self.master_port = master_addr, master_port
+        self.use_tls, self.master_cert_file, self.master_cert_name = use_tls, master_cert_file, master_cert_name
+        self.det_trial_unique_port_offset = det_trial_unique_port_offset
         self.container_id = container_id
         self.experiment_config = ExperimentConfig(experiment_config or {})
         self.hparams = dict(hparams or {})

@@ -54,7 +54,10 @@ def build_env():
         debug=e.get("DET_DEBUG", "false").lower() == "true", workload_manager_type=e["DET_WORKLOAD_MANAGER_TYPE"],
         det_rendezvous_ports=e["DET_RENDEZVOUS_PORTS"],
         det_trial_runner_network_interface=e["DET_TRIAL_RUNNER_NETWORK_INTERFACE"], det_trial_id=e["DET_TRIAL_ID"],
-        det_experiment_id=e["DET_EXPERIMENT_ID"], det_cluster_id=e["DET_CLUSTER_ID"], trial_seed=int(e["DET_TRIAL_SEED"]))
+        det_experiment_id=e["DET_EXPERIMENT_ID"], det_cluster_id=e["DET_CLUSTER_ID"], trial_seed=int(e["DET_TRIAL_SEED"]),
+        use_tls=e.get("DET_USE_TLS", "false").lower() == "true", master_cert_file=e.get("DET_MASTER_CERT_FILE") or None,
+        master_cert_name=e.get("DET_MASTER_CERT_NAME") or None,
+        det_trial_unique_port_offset=int(e.get("DET_TRIAL_UNIQUE_PORT_OFFSET", "0")))
 
 
 def _pump(stream, rank: int, out) -> None:

@@ -37,6 +37,9 @@ class Session:
         if "://" not in master:
             master = "http://" + master
         self.master = master.rstrip("/")
+        from ..utils import tls
+
+        self._opener = tls.build_opener()     # https:// masters: DET_MASTER_CERT_FILE / DET_MASTER_CERT_NAME pin the certificate
         self.user = user or os.environ.get("DET_USER", "determined")
         self.token: Optional[str] = self._load_token()
 
@@ -69,7 +72,7 @@ class Session:
             headers["Authorization"] = f"Bearer {self.token}"
         req = urllib.request.Request(self.master + path, data=data, method=method, headers=headers)
         try:
-            with urllib.request.urlopen(req, timeout=timeout) as resp:
+            with self._opener.open(req, timeout=timeout) as resp:
                 text = resp.read().decode()
                 return json.loads(text) if text else None
         except urllib.error.HTTPError as e:

@@ -25,9 +25,13 @@ def _now() -> str:
 
 
 class MasterClient:
-    def __init__(self, host: str, port: int, timeout: float = 40.0) -> None:
-        self.base = f"http://{host}:{port}"
+    def __init__(self, host: str, port: int, timeout: float = 40.0, use_tls: bool = False, cert_file: Optional[str] = None,
+                 cert_name: Optional[str] = None) -> None:
+        from ..utils import tls
+
+        self.base = f"{'https' if use_tls else 'http'}://{host}:{port}"
         self.timeout = timeout
+        self._opener = tls.build_opener(cert_file, cert_name)
 
     def request(self, method: str, path: str, body: Any = None, retries: int = 5) -> Any:
         data = None if body is None else util.json_encode(body).encode()
@@ -36,7 +40,7 @@ class MasterClient:
             try:
                 req = urllib.request.Request(self.base + path, data=data, method=method,
                                              headers={"Content-Type": "application/json"})
-                with urllib.request.urlopen(req, timeout=self.timeout) as resp:
+                with self._opener.open(req, timeout=self.timeout) as resp:
                     text = resp.read().decode()
                     return json.loads(text) if text else None
             except urllib.error.HTTPError as e:
@@ -52,7 +56,9 @@ class MasterWorkloadSource(wl.Source):
 
     def __init__(self, env: EnvContext, client: Optional[MasterClient] = None) -> None:
         self.env = env
-        self.client = client or MasterClient(env.master_addr, env.master_port)
+        self.client = client or MasterClient(env.master_addr, env.master_port, use_tls=bool(getattr(env, "use_tls", False)),
+                                             cert_file=getattr(env, "master_cert_file", None),
+                                             cert_name=getattr(env, "master_cert_name", None))
         self.trial_id = env.det_trial_id
 
     current: Optional[wl.Workload] = None

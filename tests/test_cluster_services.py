@@ -238,8 +238,10 @@ def test_actor_trace_and_debug_endpoints(slotless_master, tmp_path):
     c = MasterClient("127.0.0.1", slotless_master["port"])
     actors = c.request("GET", "/debug/actors")
     assert {"rm", "trial_logger", "experiments"} <= {a["address"] for a in actors}
-    trace = tmp_path / "actors.trace"
-    c.request("POST", "/debug/trace", {"file": str(trace)})
+    # the caller names a file; the master decides the directory (<data_dir>/traces) — a path is reduced to its last component
+    where = c.request("POST", "/debug/trace", {"file": str(tmp_path / "actors.trace")})["file"]
+    assert where.endswith("/traces/actors.trace") and not where.startswith(str(tmp_path))
+    trace = pathlib.Path(where)
     c.request("GET", "/api/v1/agents")           # an ask to the resource manager
     c.request("POST", "/debug/trace", {"file": ""})
     events = [json.loads(l) for l in trace.read_text().splitlines() if l.strip()]
