@@ -43,30 +43,29 @@ bool pair_gemm_supported(const GemmParams& p, const void* A, const void* B, long
 int launch_pair_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams p, int a_mn, int b_mn, int splitk,
                      cudaStream_t stream);
 
-// erf GELU through the Abramowitz–Stegun 7.1.26 rational form (|error| < 1.5e-7, far below bf16 resolution): one
-// approximate reciprocal, one exp2 and six FMAs per element instead of libdevice erff's branchy ~40 instructions. The epilogue
-// is instruction-issue bound, so this is what keeps it under the MMA time of a tile.
-__device__ __forceinline__ void phi_terms(float x, float& cdf, float& e) {
-  const float ax = fabsf(x) * 0.70710678118654752f;
-  float t;   // rcp.approx (one MUFU op, 1 ulp) instead of the IEEE-rounded reciprocal's Newton fix-up sequence
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, ax, 1.0f)));
-  e = fast_exp2(-1.4426950408889634f * ax * ax);  // exp(-x^2/2)
-  float poly = fmaf(1.061405429f, t, -1.453152027f);
-  poly = fmaf(poly, t, 1.421413741f);
-  poly = fmaf(poly, t, -0.284496736f);
-  poly = fmaf(poly, t, 0.254829592f);
-  const float half_erfc = 0.5f * poly * t * e;      // 0.5 * erfc(|x|/sqrt2)
-  cdf = x >= 0.0f ? 1.0f - half_erfc : half_erfc;
+// GELU in the tanh form, x * 0.5 * (1 + tanh(sqrt(2/pi) (x + 0.044715 x^3))) — the form of the original BERT code — on the
+// hardware tanh (one MUFU op, relative error 2^-11): six FP32 instructions and one MUFU per element. The epilogue is
+// instruction-issue bound (16 warps share four schedulers with 32 K elements per tile), and the erf form used before —
+// a rational erfc with a reciprocal, an exp2 and five FMAs — cost about three times as much: 38.6 against 27.9 us for
+// the FFN GEMM with and without it. The two forms differ by at most 5e-4 in absolute value, below the bf16 resolution of
+// the outputs for all but tiny activations; forward and backward use the same function, so gradients are consistent.
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
 }
-__device__ __forceinline__ float gelu_erf(float x) {
-  float cdf, e;
-  phi_terms(x, cdf, e);
-  return x * cdf;
+__device__ __forceinline__ float gelu_erf(float x) {   // name kept: the activation every `epi = BIAS_GELU` caller gets
+  const float x2 = x * x;
+  const float t = tanh_approx(x * fmaf(0.035677408136300125f, x2, 0.7978845608028654f));
+  const float hx = 0.5f * x;
+  return fmaf(hx, t, hx);
 }
 __device__ __forceinline__ float dgelu_erf(float x) {
-  float cdf, e;
-  phi_terms(x, cdf, e);
-  return fmaf(x * 0.3989422804014327f, e, cdf);
+  const float x2 = x * x;
+  const float t = tanh_approx(x * fmaf(0.035677408136300125f, x2, 0.7978845608028654f));
+  const float q = fmaf(0.10703222440890037f, x2, 0.7978845608028654f);     // d/dx of the tanh argument
+  const float s = fmaf(-t, t, 1.0f);                                       // sech^2
+  return fmaf(0.5f * x * s, q, fmaf(0.5f, t, 0.5f));
 }
 
 // ------------------------------------------------------------------------------------------------

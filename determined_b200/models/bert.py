@@ -28,7 +28,7 @@ import torch
 import torch.nn as nn
 
 from ..ops import functional as F
-from ..ops.modules import (accumulate_bgrad, accumulate_wgrad, grad_buffer, note_param_use, notify_grads_written,
+from ..ops.modules import (accumulate_bgrad, accumulate_wgrad, grad_buffer, note_param_use, notify_grads_written, side_grads,
                            shadow_of)
 
 
@@ -55,7 +55,8 @@ _FUSED_BIAS = os.environ.get("DET_LN_FUSED_BIAS", "0") == "1"
 
 
 def _gelu(x: torch.Tensor) -> torch.Tensor:
-    return 0.5 * x * (1.0 + torch.erf(x * 0.7071067811865476))
+    # tanh form, as in the original BERT code and in the GEMM epilogue (csrc/kernels/gemm_common.cuh)
+    return nn.functional.gelu(x, approximate="tanh")
 
 
 # ------------------------------------------------------------------------------------------------
@@ -101,6 +102,21 @@ class _BertLayerFn(torch.autograd.Function):
         T, Hd, I, NH = x.shape[0], c.hidden_size, c.intermediate_size, c.num_attention_heads
         dev, bf = x.device, torch.bfloat16
         dx2 = dx2.contiguous()
+        with side_grads(dev):    # weight / bias gradients run beside the data-gradient chain, joined on the way out
+            out = _BertLayerFn._backward_body(ctx, dx2, (x, qkv, lse, att, h1, mean1, rstd1, x1, z, a, h2, mean2, rstd2))
+        notify_grads_written(*L.parameters())   # this layer's slice of the gradient bucket is final: its all-reduce may start
+        return out
+
+    @staticmethod
+    def _backward_body(ctx, dx2, saved):
+        x, qkv, lse, att, h1, mean1, rstd1, x1, z, a, h2, mean2, rstd2 = saved
+        L: BertLayer = ctx.layer
+        c = L.cfg
+        B, S = ctx.dims
+        p_h, p_a = ctx.drop
+        sd = ctx.sd
+        T, Hd, I, NH = x.shape[0], c.hidden_size, c.intermediate_size, c.num_attention_heads
+        dev, bf = x.device, torch.bfloat16
         masked = p_h > 0.0
         # LN2 backward: dh2 (residual branch) and dh2m (dropout-masked: gradient of FFN2's pre-dropout output)
         dh2, dh2m = F.layernorm_bwd(dx2, h2, L.ln2_weight, mean2, rstd2, grad_buffer(L.ln2_weight),
@@ -134,7 +150,6 @@ class _BertLayerFn(torch.autograd.Function):
         if ctx.needs_input_grad[0]:
             dx = torch.empty(T, Hd, dtype=bf, device=dev)
             F.gemm(dqkv, shadow_of(L.qkv_weight), dx, T, Hd, 3 * Hd, b_mn=True, epi=F.EPI_BIAS_RESID, aux_in=dh1)
-        notify_grads_written(*L.parameters())   # this layer's slice of the gradient bucket is final: its all-reduce may start
         return dx, None, None, None, None, None, None
 
 

@@ -103,15 +103,60 @@ def reset_param_uses() -> None:
     _PARAM_USES.clear()
 
 
+# ------------------------------------------------------------------------------------------------
+# Parameter gradients on a side stream
+# ------------------------------------------------------------------------------------------------
+# In a layer's backward the data-gradient kernels form a chain (each needs the previous one's output) while the weight /
+# bias gradients hang off that chain as leaves: nothing in backward reads them. Launched on a second stream they become
+# independent work the GPU can start as soon as SMs drain from a chain kernel's tail, instead of every kernel paying its
+# own ramp-up and tail in sequence. ``side_grads(device)`` opens such a window; inside it ``accumulate_wgrad`` /
+# ``accumulate_bgrad`` run on the side stream after whatever the main stream has enqueued so far, and leaving the window
+# makes the main stream wait for them (so every tensor they read is still referenced by the caller's frame). Works the
+# same under CUDA-graph capture, where the two streams become parallel branches of the graph.
+import contextlib
+import os
+
+_SIDE_STREAMS: dict = {}
+_SIDE_ACTIVE: list = []
+_SIDE_ENABLED = os.environ.get("DET_SIDE_GRADS", "1") == "1"
+
+
+@contextlib.contextmanager
+def side_grads(device: torch.device):
+    if not _SIDE_ENABLED or device.type != "cuda":
+        yield
+        return
+    side = _SIDE_STREAMS.get(device)
+    if side is None:
+        side = _SIDE_STREAMS[device] = torch.cuda.Stream(device=device)
+    _SIDE_ACTIVE.append(side)
+    try:
+        yield
+    finally:
+        _SIDE_ACTIVE.pop()
+        torch.cuda.current_stream(device).wait_stream(side)
+
+
+def _on_side(fn) -> None:
+    if not _SIDE_ACTIVE:
+        fn()
+        return
+    side = _SIDE_ACTIVE[-1]
+    side.wait_stream(torch.cuda.current_stream(side.device))
+    with torch.cuda.stream(side):
+        fn()
+
+
 def accumulate_wgrad(weight: torch.Tensor, dy: torch.Tensor, x: torch.Tensor) -> None:
     """weight.grad[N_out, K_in] += dy[T, N_out]^T @ x[T, K_in] (both operands MN-major, split-K atomics)."""
     g = grad_buffer(weight)
     n_out, k_in = weight.shape
-    F.gemm(dy, x, g, n_out, k_in, dy.shape[0], a_mn=True, b_mn=True, out_mode=F.OUT_F32_ATOMIC_ADD)
+    _on_side(lambda: F.gemm(dy, x, g, n_out, k_in, dy.shape[0], a_mn=True, b_mn=True, out_mode=F.OUT_F32_ATOMIC_ADD))
 
 
 def accumulate_bgrad(bias: torch.Tensor, dy: torch.Tensor) -> None:
-    F.colsum_accum(dy, grad_buffer(bias))
+    g = grad_buffer(bias)
+    _on_side(lambda: F.colsum_accum(dy, g))
 
 
 # ------------------------------------------------------------------------------------------------
@@ -147,8 +192,9 @@ class _LinearFn(torch.autograd.Function):
             # dz = dy * gelu'(z): fold into a copy through the dgrad-free path (elementwise in torch
             # would re-read; use the GEMM epilogue only when an input gradient is needed)
             zf = z.float()
-            dyz = (dy.float() * (0.5 * (1 + torch.erf(zf * 0.7071067811865476))
-                                 + zf * torch.exp(-0.5 * zf * zf) * 0.3989422804014327)).to(torch.bfloat16)
+            z2 = zf * zf
+            t = torch.tanh(zf * (0.7978845608028654 + 0.035677408136300125 * z2))      # tanh-form GELU, as the epilogue
+            dyz = (dy.float() * (0.5 * (1 + t) + 0.5 * zf * (1 - t * t) * (0.7978845608028654 + 0.10703222440890037 * z2))).to(torch.bfloat16)
             dy = dyz
         if weight.requires_grad:
             accumulate_wgrad(weight, dy, x)
@@ -180,7 +226,7 @@ class Linear(nn.Linear):
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if not (_use_native(x) and _tma_ok(x.numel() // x.shape[-1], self.in_features, self.out_features)):
             y = nn.functional.linear(x, self.weight.to(x.dtype), None if self.bias is None else self.bias.to(x.dtype))
-            return nn.functional.gelu(y) if self.activation == "gelu" else y
+            return nn.functional.gelu(y, approximate="tanh") if self.activation == "gelu" else y
         lead = x.shape[:-1]
         x2 = x.reshape(-1, self.in_features)
         if x2.dtype != torch.bfloat16:
