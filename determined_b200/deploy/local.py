@@ -87,6 +87,24 @@ def agent_up(name: str, master_port: int, agent_id: str, slots: int = 0) -> int:
     return proc.pid
 
 
+def grpc_up(name: str, master_port: int, grpc_port: int) -> int:
+    """The gRPC front (determined.api.v1.Determined) as a sidecar of the master; stopped with the cluster."""
+    d = _state_dir(name)
+    pf = d / "grpc.port"
+    pf.unlink(missing_ok=True)
+    proc = subprocess.Popen([sys.executable, "-m", "determined_b200.master.grpc_gateway", "--master", f"127.0.0.1:{master_port}",
+                             "--port", str(grpc_port), "--print-port-file", str(pf)], cwd=str(ROOT),
+                            stdout=open(d / "grpc.log", "a"), stderr=subprocess.STDOUT, start_new_session=True)
+    (d / "agent-grpc-gateway.pid").write_text(str(proc.pid))
+    for _ in range(200):
+        if pf.exists() and pf.read_text().strip():
+            return int(pf.read_text())
+        if proc.poll() is not None:
+            raise SystemExit(f"grpc gateway exited with code {proc.returncode}; see {d / 'grpc.log'}")
+        time.sleep(0.05)
+    return grpc_port
+
+
 def cluster_down(name: str) -> List[int]:
     d = _state_dir(name)
     stopped = []
@@ -132,6 +150,7 @@ def main(argv: Optional[List[str]] = None) -> None:
     up.add_argument("--agents", type=int, default=0, help="extra det-agent processes besides the master's in-process agent")
     up.add_argument("--artificial-slots", type=int, default=0, help="CPU slots instead of detected GPUs (testing)")
     up.add_argument("--scheduler", default="fair_share", choices=["fair_share", "priority", "round_robin"])
+    up.add_argument("--grpc-port", type=int, default=-1, help="also start the gRPC gateway on this port (0 = any free port)")
     down = lsub.add_parser("cluster-down")
     down.add_argument("--cluster-name", default="determined")
     st = lsub.add_parser("status")
@@ -149,7 +168,8 @@ def main(argv: Optional[List[str]] = None) -> None:
         port = master_up(args.cluster_name, args.master_port, args.artificial_slots, args.scheduler)
         for i in range(args.agents):
             agent_up(args.cluster_name, port, f"agent-{i + 1}", args.artificial_slots)
-        print(json.dumps({"master": f"127.0.0.1:{port}", "ui": f"http://127.0.0.1:{port}/ui", **status(args.cluster_name)}))
+        extra = {"grpc": f"127.0.0.1:{grpc_up(args.cluster_name, port, args.grpc_port)}"} if args.grpc_port >= 0 else {}
+        print(json.dumps({"master": f"127.0.0.1:{port}", "ui": f"http://127.0.0.1:{port}/ui", **extra, **status(args.cluster_name)}))
     elif args.verb == "cluster-down":
         print(json.dumps({"stopped": cluster_down(args.cluster_name)}))
     elif args.verb == "status":
