@@ -7,6 +7,8 @@
 // 8-GPU box the isolation unit is the process + its GPU mask, which removes image pulls and container start-up from
 // the trial launch path.
 #pragma once
+#include <sys/stat.h>
+#include <limits.h>
 #include <fcntl.h>
 #include <signal.h>
 #include <sys/types.h>
@@ -112,6 +114,37 @@ struct LogLine {
   int rank = -1;
 };
 
+// bind_mounts of a process "container" (see task_spec.hpp): every `host|container|mode` line makes the container path point
+// at the host path. Runs in the forked child, in the task's working directory, right before exec.
+inline bool apply_bind_mounts(const std::string& lines) {
+  size_t pos = 0;
+  while (pos < lines.size()) {
+    size_t nl = lines.find('\n', pos);
+    if (nl == std::string::npos) nl = lines.size();
+    const std::string line = lines.substr(pos, nl - pos);
+    pos = nl + 1;
+    const size_t a = line.find('|'), b = line.rfind('|');
+    if (line.empty() || a == std::string::npos || b == a) continue;
+    const std::string host = line.substr(0, a), target = line.substr(a + 1, b - a - 1);
+    char have[4096], want[4096];
+    if (realpath(host.c_str(), want) == nullptr) { fprintf(stderr, "bind mount: host path %s does not exist\n", host.c_str()); return false; }
+    if (realpath(target.c_str(), have) != nullptr) {
+      if (strcmp(have, want) == 0) continue;                       // already the same place
+      fprintf(stderr, "bind mount: %s exists and is not %s\n", target.c_str(), host.c_str());
+      return false;
+    }
+    const size_t slash = target.find_last_of('/');
+    if (slash != std::string::npos && slash > 0) {
+      std::string dir = target.substr(0, slash);
+      for (size_t i = 1; i <= dir.size(); ++i)
+        if (i == dir.size() || dir[i] == '/') ::mkdir(dir.substr(0, i).c_str(), 0755);
+    }
+    ::unlink(target.c_str());   // a dangling link left by an earlier run
+    if (::symlink(want, target.c_str()) != 0) { perror(("bind mount: symlink " + target).c_str()); return false; }
+  }
+  return true;
+}
+
 class ContainerManager {
  public:
   using EventFn = std::function<void(const ContainerEvent&)>;
@@ -146,6 +179,10 @@ class ContainerManager {
       close(out_pipe[0]); close(out_pipe[1]); close(err_pipe[0]); close(err_pipe[1]);
       if (!spec.cwd.empty() && chdir(spec.cwd.c_str()) != 0) { perror("chdir"); _exit(126); }
       for (auto& kv : env) setenv(kv.first.c_str(), kv.second.c_str(), 1);
+      {
+        auto bm = env.find("DET_BIND_MOUNTS");
+        if (bm != env.end() && !apply_bind_mounts(bm->second)) _exit(125);
+      }
       std::vector<char*> argv;
       for (auto& a : spec.argv) argv.push_back(const_cast<char*>(a.c_str()));
       argv.push_back(nullptr);

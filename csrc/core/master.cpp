@@ -1,4 +1,5 @@
 // master.cpp — Master bootstrap, configuration, container routing, command tasks, checkpoint GC, restore.
+#include "task_spec.hpp"
 #include "master.hpp"
 
 #include <sys/stat.h>
@@ -124,6 +125,13 @@ class CommandActor : public Actor {
       spec.cwd = spec_["cwd"].str_or("");
       for (auto& kv : spec_["env"].obj()) spec.env[kv.first] = kv.second.as_string();
       for (auto& d : a["devices"].arr()) spec.devices.push_back(Device{static_cast<int>(d["id"].as_int()), d["brand"].as_string(), d["uuid"].as_string(), d["type"].as_string()});
+      if (spec_["config"].is_object()) {   // commands / notebooks / shells take bind_mounts, environment and resources like trials do
+        const std::string slot_type = (!spec.devices.empty() && spec.devices[0].type == "gpu" && spec.devices[0].brand != "Artificial") ? "gpu" : "cpu";
+        std::string warning;
+        const std::string bad = apply_task_config(spec_["config"], slot_type, 0, false, spec.env, spec.argv, &warning);
+        if (!bad.empty()) m_->log("error", task_id_ + ": " + bad);
+        if (!warning.empty()) m_->log("warn", task_id_ + ": " + warning);
+      }
       // Service tasks (notebooks, TensorBoards, anything submitted with "proxy": true) get a port of their own: it replaces
       // "{port}" in argv, is exported as DET_TASK_PORT, and /proxy/<id>/... on the master forwards to it once the
       // readiness check has seen the service answer (reference: command.go readiness checks + internal/proxy).

@@ -589,7 +589,7 @@ tick();setInterval(tick,2000);
       if (!b["argv"].is_array() || b["argv"].size() == 0) return HttpResponse::error(400, "argv (list of strings) is required");
       const long long id = m->store.next_id("commands");
       Json spec = obj({{"type", type}, {"description", b["description"].str_or(type)}, {"slots", b["slots"].as_int(0)}, {"argv", b["argv"]},
-                       {"env", b["env"].is_object() ? b["env"] : Json::object()}, {"cwd", b["cwd"].str_or("")}});
+                       {"env", b["env"].is_object() ? b["env"] : Json::object()}, {"cwd", b["cwd"].str_or("")}, {"config", b["config"]}});
       const bool service = b.contains("proxy") ? b["proxy"].as_bool(false) : (type == "notebook" || type == "tensorboard");
       if (service) {
         spec["proxy_port"] = b["port"].as_int(0) > 0 ? b["port"].as_int() : static_cast<long long>(free_tcp_port());

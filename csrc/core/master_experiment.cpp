@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cmath>
 
+#include "task_spec.hpp"
 #include "master.hpp"
 
 namespace det {
@@ -240,7 +241,13 @@ class TrialActor : public Actor {
       e["DET_DEBUG"] = config_["debug"].as_bool(false) ? "true" : "false";
       const char* pp = getenv("PYTHONPATH");
       e["PYTHONPATH"] = spec.cwd + ":" + m_->cfg.repo_root + (pp ? std::string(":") + pp : "");
-      for (auto& kv : config_["environment"]["environment_variables"].obj()) e[kv.first] = kv.second.is_string() ? kv.second.as_string() : kv.second.dump();
+      {
+        const std::string slot_type = (!spec.devices.empty() && spec.devices[0].type == "gpu" && spec.devices[0].brand != "Artificial") ? "gpu" : "cpu";
+        std::string warning;
+        const std::string bad = apply_task_config(config_, slot_type, trial_id_ % 16, true, e, spec.argv, &warning);
+        if (!bad.empty()) m_->log("error", task_id_ + ": " + bad);
+        if (!warning.empty()) m_->log("warn", task_id_ + ": " + warning);
+      }
       m_->register_container(spec.container_id, ctx.self(), trial_id_);
       containers_.push_back(spec.container_id);
       m_->start_container(a["agent"].as_string(), spec);

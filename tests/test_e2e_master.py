@@ -164,3 +164,42 @@ def test_adaptive_search_survives_random_failures(master):
     # successive halving: most trials stop at the bottom rung, at least one is promoted to the full length
     lens = sorted(t["total_batches_processed"] for t in trials)
     assert lens[-1] == 320 and lens[0] < 320
+
+
+def test_task_spec_environment_bind_mounts_ports_and_startup_hook(master, tmp_path):
+    """What the experiment config contributes to a task's container spec (reference master/pkg/tasks/task.go:172-331,
+    entrypoint.sh): environment variables (list form), a bind mount (container path -> host path), ports shifted by the
+    trial's offset, shm size, and startup-hook.sh sourced before the harness starts."""
+    import json
+    import shutil
+
+    d = Determined(master["url"])
+    model_dir = tmp_path / "model"
+    src = pathlib.Path(MODEL_DIR)
+    shutil.copytree(src, model_dir)
+    host_data = tmp_path / "host_data"
+    host_data.mkdir()
+    (host_data / "hello.txt").write_text("from the host\n")
+    (model_dir / "startup-hook.sh").write_text("export HOOK_SAYS=ran\ntouch startup-hook-ran\n")
+    (model_dir / "model_def.py").write_text((src / "model_def.py").read_text() + '''
+
+import json as _json
+import os as _os
+
+_offset = int(_os.environ["DET_TRIAL_UNIQUE_PORT_OFFSET"])
+assert _os.environ["FROM_CONFIG"] == "a=b", _os.environ.get("FROM_CONFIG")
+assert _os.environ["HOOK_SAYS"] == "ran" and _os.path.isfile("startup-hook-ran")
+assert open("data/hello.txt").read() == "from the host\\n"
+assert _json.loads(_os.environ["DET_PORTS"]) == {"metrics": 9100 + _offset}
+assert int(_os.environ["DET_SHM_SIZE"]) == 64 * 1024 * 1024
+''')
+    cfg = base_config(master["tmp"], {"name": "single", "metric": "validation_loss", "max_length": {"batches": 10}}, max_restarts=0,
+                      bind_mounts=[{"host_path": str(host_data), "container_path": "data", "read_only": True}],
+                      environment={"environment_variables": ["FROM_CONFIG=a=b"], "ports": {"metrics": 9100}},
+                      resources={"shm_size": "64MB"})
+    exp = d.create_experiment(cfg, str(model_dir))
+    state = exp.wait(timeout=180)
+    t = exp.describe()["trials"][0]
+    logs = "\\n".join(l["message"] for l in d.get_trial(t["id"]).logs()[-15:])
+    assert state == "COMPLETED", logs
+    del json
