@@ -445,4 +445,57 @@ inline void http_tunnel(const std::string& host, int port, const HttpRequest& re
   ::close(fd);
 }
 
+// Raw TCP tunnel (`det tunnel`, the ProxyCommand of `det shell`): the client asks with `Upgrade: det-tcp`; the master
+// connects to the task's port, answers 101 itself and then copies bytes both ways — nothing of the HTTP request reaches
+// the task, which may speak any protocol (sshd). (reference: master/internal/proxy/tcp.go, cli/determined_cli/tunnel.py)
+inline void tcp_tunnel(const std::string& host, int port, int client, int idle_s = 3600) {
+  auto send_all = [](int fd, const char* p, size_t n) {
+    while (n > 0) {
+      ssize_t k = ::send(fd, p, n, MSG_NOSIGNAL);
+      if (k <= 0) return false;
+      p += k;
+      n -= static_cast<size_t>(k);
+    }
+    return true;
+  };
+  int fd = ::socket(AF_INET, SOCK_STREAM | SOCK_CLOEXEC, 0);
+  sockaddr_in addr{};
+  addr.sin_family = AF_INET;
+  addr.sin_port = htons(static_cast<uint16_t>(port));
+  addr.sin_addr.s_addr = resolve_ipv4(host);
+  if (fd < 0 || ::connect(fd, reinterpret_cast<sockaddr*>(&addr), sizeof addr) < 0) {
+    static const char bad[] = "HTTP/1.1 502 Bad Gateway\r\nContent-Length: 0\r\nConnection: close\r\n\r\n";
+    send_all(client, bad, sizeof bad - 1);
+    if (fd >= 0) ::close(fd);
+    return;
+  }
+  static const char ok[] = "HTTP/1.1 101 Switching Protocols\r\nUpgrade: det-tcp\r\nConnection: Upgrade\r\n\r\n";
+  if (send_all(client, ok, sizeof ok - 1)) {
+    // each direction ends on its own: an EOF from one side is passed on as a half-close (shutdown of the write side of the
+    // other socket) and the opposite direction keeps flowing until it ends too — `echo request | det tunnel` must still
+    // receive the answer after its stdin closed
+    pollfd fds[2] = {{client, POLLIN, 0}, {fd, POLLIN, 0}};
+    bool live[2] = {true, true};
+    char buf[16384];
+    while (live[0] || live[1]) {
+      fds[0].events = live[0] ? POLLIN : 0;
+      fds[1].events = live[1] ? POLLIN : 0;
+      if (::poll(fds, 2, idle_s * 1000) <= 0) break;
+      bool broken = false;
+      for (int i = 0; i < 2; ++i) {
+        if (!live[i]) continue;
+        if (fds[i].revents & (POLLIN | POLLHUP)) {
+          const ssize_t n = ::recv(fds[i].fd, buf, sizeof buf, 0);
+          if (n > 0) { if (!send_all(fds[1 - i].fd, buf, static_cast<size_t>(n))) broken = true; }
+          else { live[i] = false; ::shutdown(fds[1 - i].fd, SHUT_WR); }
+        } else if (fds[i].revents & (POLLERR | POLLNVAL)) {
+          broken = true;
+        }
+      }
+      if (broken) break;
+    }
+  }
+  ::close(fd);
+}
+
 }  // namespace det

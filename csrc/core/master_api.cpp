@@ -147,6 +147,11 @@ void Master::register_routes() {
       const std::string host = c["proxy_host"].str_or("127.0.0.1");
       const int port = static_cast<int>(c["proxy_port"].as_int());
       auto up = r.headers.find("upgrade");
+      if (up != r.headers.end() && up->second == "det-tcp") {   // raw byte tunnel to the task's port (`det tunnel`)
+        HttpResponse t;
+        t.hijack = [host, port](int client) { tcp_tunnel(host, port, client); };
+        return t;
+      }
       if (up != r.headers.end() && !up->second.empty()) {
         HttpResponse t;
         t.hijack = [host, port, r, path](int client) { http_tunnel(host, port, r, path, client); };
@@ -290,6 +295,11 @@ tick();setInterval(tick,2000);
     std::string user;
     m->check_auth(r, &user);
     const long long id = m->create_experiment(cfg, b["model_definition"], b["parent_id"].as_int(0), b["activate"].is_null() ? true : b["activate"].as_bool(true), user);
+    if (b["git"].is_object()) {   // `det experiment create --git`: where the model definition came from (remote, commit, committer, date)
+      Json g = Json::object();
+      for (const char* k : {"git_remote", "git_commit", "git_committer", "git_commit_date"}) g[k] = b["git"][k].str_or("");
+      m->store.update("experiments", std::to_string(id), g);
+    }
     return HttpResponse::json(obj({{"id", id}, {"config", cfg}}), 201);
   });
   http.route("GET", "/api/v1/experiments", [m](const HttpRequest& r) {

@@ -26,7 +26,19 @@ LIB = pathlib.Path(__file__).resolve().parent.parent / "_lib"
 ROOT = pathlib.Path(__file__).resolve().parent.parent.parent
 
 
+OUTPUT = {"csv": False}     # `det --csv <list command>`: rows as CSV instead of a table (reference render.tabulate_or_csv)
+
+
 def _table(rows: List[List[Any]], headers: List[str]) -> str:
+    if OUTPUT["csv"]:
+        import csv
+        import io
+
+        buf = io.StringIO()
+        w = csv.writer(buf, lineterminator="\n")
+        w.writerow(headers)
+        w.writerows(rows)
+        return buf.getvalue().rstrip("\n")
     try:
         from tabulate import tabulate
 
@@ -65,6 +77,30 @@ def _follow_logs(d: Determined, exp_id: int) -> str:
         time.sleep(1.0)
 
 
+def git_metadata(model_def: str) -> Dict[str, str]:
+    """``experiment create --git`` (reference cli/determined_cli/experiment.py:124-186): record where the model definition
+    came from. The directory must be a git work tree with a remote, nothing uncommitted, and a HEAD that has been pushed."""
+    import subprocess
+
+    def git(*args: str) -> str:
+        p = subprocess.run(["git", "-C", model_def, *args], capture_output=True, text=True)
+        if p.returncode != 0:
+            raise SystemExit(f"--git: `git {' '.join(args)}` failed in {model_def}: {p.stderr.strip() or p.stdout.strip()}")
+        return p.stdout.strip()
+
+    if git("rev-parse", "--is-inside-work-tree") != "true":
+        raise SystemExit(f"--git: {model_def} is not inside a git work tree")
+    if git("status", "--porcelain", "--", "."):
+        raise SystemExit("--git: the model definition has uncommitted changes; commit them (or drop --git)")
+    remote = git("config", "--get", "remote.origin.url")
+    commit = git("rev-parse", "HEAD")
+    on_remote = subprocess.run(["git", "-C", model_def, "branch", "-r", "--contains", commit], capture_output=True, text=True).stdout.strip()
+    if not on_remote:
+        raise SystemExit("--git: HEAD has not been pushed to the remote; push it (or drop --git)")
+    return {"git_remote": remote, "git_commit": commit, "git_committer": git("log", "-1", "--format=%cn <%ce>"),
+            "git_commit_date": git("log", "-1", "--format=%cI")}
+
+
 # ---- experiment ------------------------------------------------------------------------------------------------------
 def experiment_create(a: argparse.Namespace) -> int:
     cfg = _load_config(a.config_file, a.config)
@@ -84,7 +120,8 @@ def experiment_create(a: argparse.Namespace) -> int:
         from .._execution import make_test_experiment_config
 
         cfg = make_test_experiment_config(cfg)
-    exp = d.create_experiment(cfg, a.model_def, activate=not a.paused, template=a.template)
+    exp = d.create_experiment(cfg, a.model_def, activate=not a.paused, template=a.template,
+                              git=git_metadata(a.model_def) if a.git else None)
     print(f"Created experiment {exp.id}")
     if a.follow or a.test_mode:
         state = _follow_logs(d, exp.id)
@@ -474,10 +511,21 @@ def command_kill(kind: str):
 
 
 # ---- parser ---------------------------------------------------------------------------------------------------------------
+def tunnel(a: argparse.Namespace) -> int:
+    from . import tunnel as T
+
+    d = Determined(a.master, a.user)
+    if a.listener is not None:
+        return T.listen_tunnel(d._session.master, a.task_id, a.listener, d._session.token,
+                               ready=lambda port: print(f"listening on 127.0.0.1:{port}", flush=True))
+    return T.stdio_tunnel(d._session.master, a.task_id, d._session.token)
+
+
 def build_parser() -> argparse.ArgumentParser:
     p = argparse.ArgumentParser(prog="det", description="Determined (B200-native) command line")
     p.add_argument("-m", "--master", default=None, help="master address (default $DET_MASTER or localhost:8080)")
     p.add_argument("-u", "--user", default=None)
+    p.add_argument("--csv", action="store_true", help="print list output as CSV")
     sub = p.add_subparsers(dest="group")
 
     def group(name: str, aliases: List[str] = []) -> Any:
@@ -494,7 +542,8 @@ def build_parser() -> argparse.ArgumentParser:
     A = lambda *n, **k: (n, k)  # noqa: E731
     e = group("experiment", ["e"])
     cmd(e, "create", experiment_create, A("config_file"), A("model_def"), A("--local", action="store_true"), A("--test-mode", "--test", action="store_true"),
-        A("--paused", action="store_true"), A("--follow", "-f", action="store_true"), A("--template"), A("--config", action="append"))
+        A("--paused", action="store_true"), A("--follow", "-f", action="store_true"), A("--template"), A("--config", action="append"),
+        A("--git", action="store_true", help="record the git remote / commit of the model definition with the experiment"))
     cmd(e, "list", experiment_list, A("--all", "-a", action="store_true"), aliases=["ls"])
     cmd(e, "describe", experiment_describe, A("experiment_ids"), A("--metrics", action="store_true"), A("--json", action="store_true"))
     cmd(e, "config", experiment_config, A("experiment_id", type=int))
@@ -518,6 +567,10 @@ def build_parser() -> argparse.ArgumentParser:
     cmd(c, "download", checkpoint_download, A("uuid"), A("--output-dir", "-o"))
     tk = group("task")
     cmd(tk, "list", task_list, aliases=["ls"])
+    tn = sub.add_parser("tunnel", help="byte tunnel to a service task through the master (ssh ProxyCommand, or --listener PORT)")
+    tn.add_argument("task_id")
+    tn.add_argument("--listener", type=int, default=None, help="listen on this local port instead of using stdin / stdout")
+    tn.set_defaults(func=tunnel)
     ps = sub.add_parser("preview-search")
     ps.add_argument("config_file"), ps.add_argument("--seed", type=int, default=0), ps.add_argument("--offline", action="store_true")
     ps.set_defaults(func=lambda a: preview_search_local(a) if a.offline else preview_search(a))
@@ -569,6 +622,7 @@ def main(argv: Optional[List[str]] = None) -> int:
     if not getattr(args, "func", None):
         parser.print_help()
         return 2
+    OUTPUT["csv"] = bool(getattr(args, "csv", False))
     try:
         return int(args.func(args) or 0)
     except APIError as e:

@@ -359,8 +359,10 @@ class Determined:
         self._session = Session(master, user)
 
     def create_experiment(self, config: Dict[str, Any], model_dir: str, activate: bool = True, template: Optional[str] = None,
-                          parent_id: Optional[int] = None) -> ExperimentReference:
-        body = {"config": config, "model_definition": read_context(model_dir), "activate": activate}
+                          parent_id: Optional[int] = None, git: Optional[Dict[str, str]] = None) -> ExperimentReference:
+        body: Dict[str, Any] = {"config": config, "model_definition": read_context(model_dir), "activate": activate}
+        if git:
+            body["git"] = git
         if template:
             body["template"] = template
         if parent_id:

@@ -1,0 +1,53 @@
+"""CLI pieces that need no cluster: ``experiment create --git`` metadata checks and CSV rendering
+(reference cli/determined_cli/experiment.py:124-186, render.py)."""
+import subprocess
+
+import pytest
+
+from determined_b200.cli import __main__ as cli
+
+
+def _git(cwd, *args):
+    subprocess.run(["git", "-C", str(cwd), *args], check=True, capture_output=True,
+                   env={"GIT_AUTHOR_NAME": "t", "GIT_AUTHOR_EMAIL": "t@example.com", "GIT_COMMITTER_NAME": "t", "GIT_COMMITTER_EMAIL": "t@example.com",
+                        "HOME": str(cwd), "PATH": "/usr/bin:/bin:/usr/local/bin"})
+
+
+def test_git_metadata_requires_a_clean_pushed_tree(tmp_path):
+    remote = tmp_path / "remote.git"
+    work = tmp_path / "work"
+    subprocess.run(["git", "init", "--bare", "-q", str(remote)], check=True)
+    subprocess.run(["git", "init", "-q", str(work)], check=True)
+    (work / "model_def.py").write_text("x = 1\n")
+    with pytest.raises(SystemExit, match="uncommitted"):
+        cli.git_metadata(str(work))                      # untracked file
+    _git(work, "add", ".")
+    _git(work, "commit", "-q", "-m", "first")
+    with pytest.raises(SystemExit, match="remote|failed"):
+        cli.git_metadata(str(work))                      # no remote configured
+    _git(work, "remote", "add", "origin", str(remote))
+    with pytest.raises(SystemExit, match="not been pushed"):
+        cli.git_metadata(str(work))
+    branch = subprocess.run(["git", "-C", str(work), "rev-parse", "--abbrev-ref", "HEAD"], capture_output=True, text=True).stdout.strip()
+    _git(work, "push", "-q", "origin", branch)
+    md = cli.git_metadata(str(work))
+    assert md["git_remote"] == str(remote) and len(md["git_commit"]) == 40 and md["git_committer"] == "t <t@example.com>"
+    assert md["git_commit_date"][:2] == "20"
+    (work / "model_def.py").write_text("x = 2\n")
+    with pytest.raises(SystemExit, match="uncommitted"):
+        cli.git_metadata(str(work))
+
+
+def test_csv_rendering_of_list_output():
+    cli.OUTPUT["csv"] = True
+    try:
+        assert cli._table([[1, "a,b", None], [2, 'q"uote', 3.5]], ["id", "name", "v"]) == 'id,name,v\n1,"a,b",\n2,"q""uote",3.5'
+    finally:
+        cli.OUTPUT["csv"] = False
+    assert "id" in cli._table([[1, "x"]], ["id", "name"])
+    args = cli.build_parser().parse_args(["--csv", "experiment", "list"])
+    assert args.csv and args.func is cli.experiment_list
+    args = cli.build_parser().parse_args(["e", "create", "c.yaml", "dir", "--git"])
+    assert args.git
+    args = cli.build_parser().parse_args(["tunnel", "7", "--listener", "2222"])
+    assert args.task_id == "7" and args.listener == 2222

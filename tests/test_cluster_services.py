@@ -366,3 +366,52 @@ def test_telemetry_sink_is_opt_in(tmp_path):
     proc.terminate()
     proc.wait(timeout=5)
     assert not (tmp_path / "data0" / "telemetry.jsonl").exists()
+
+
+def test_det_tunnel_carries_raw_tcp_to_a_service_task(slotless_master, tmp_path):
+    """``det tunnel``: the master answers ``Upgrade: det-tcp`` with 101 and then copies bytes to the task's port, so a task
+    that speaks a non-HTTP protocol (sshd for ``det shell``; here a line-echo server) is reachable through the master —
+    once over stdin/stdout (ssh ProxyCommand style) and once through ``--listener`` (reference cli/determined_cli/tunnel.py,
+    master/internal/proxy/tcp.go)."""
+    import socket
+
+    server = tmp_path / "echo.py"
+    server.write_text(
+        "import socket, sys\n"
+        "s = socket.socket(); s.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1); s.bind(('127.0.0.1', int(sys.argv[1]))); s.listen(8)\n"
+        "while True:\n"
+        "    c, _ = s.accept()\n"
+        "    c.sendall(b'BANNER echo-1.0\\n')\n"
+        "    f = c.makefile('rwb', buffering=0)\n"
+        "    for line in f:\n"
+        "        f.write(b'echo: ' + line)\n"
+        "    c.close()\n")
+    c = MasterClient("127.0.0.1", slotless_master["port"])
+    cmd = c.request("POST", "/api/v1/commands", {"argv": [sys.executable, str(server), "{port}"], "proxy": True, "description": "echo"})
+    try:
+        port = cmd["spec"]["proxy_port"]
+        for _ in range(100):     # no HTTP readiness for a raw service: wait until the port accepts
+            try:
+                socket.create_connection(("127.0.0.1", port), timeout=0.2).close()
+                break
+            except OSError:
+                time.sleep(0.1)
+        out = subprocess.run([sys.executable, "-m", "determined_b200.cli", "-m", slotless_master["url"], "tunnel", str(cmd["id"])],
+                             input=b"hello\nworld\n", capture_output=True, cwd=str(ROOT), timeout=60)
+        assert out.returncode == 0, out.stderr.decode()
+        assert out.stdout == b"BANNER echo-1.0\necho: hello\necho: world\n"
+        lst = subprocess.Popen([sys.executable, "-m", "determined_b200.cli", "-m", slotless_master["url"], "tunnel", str(cmd["id"]), "--listener", "0"],
+                               stdout=subprocess.PIPE, stderr=subprocess.STDOUT, cwd=str(ROOT), text=True)
+        try:
+            line = lst.stdout.readline()
+            local = int(line.strip().rsplit(":", 1)[1])
+            s = socket.create_connection(("127.0.0.1", local), timeout=10)
+            f = s.makefile("rwb", buffering=0)
+            assert f.readline() == b"BANNER echo-1.0\n"
+            f.write(b"via listener\n")
+            assert f.readline() == b"echo: via listener\n"
+            s.close()
+        finally:
+            lst.terminate()
+    finally:
+        c.request("POST", f"/api/v1/commands/{cmd['id']}/kill")
