@@ -55,6 +55,7 @@ int main(int argc, char** argv) {
       else if (a == "--resource-manager") j["resource_manager"] = det::Json::parse(next());   // {"type": "kubernetes", ...}
       else if (a == "--visible-gpus") j["visible_gpus"] = next();
       else if (a == "--auth-required") j["auth_required"] = true;
+      else if (a == "--logging") j["logging"] = det::Json::parse(next());   // {"type": "elastic", "host": "...", "port": 9200}
       else if (a == "--security-tls-cert" || a == "--security-tls-key" || a == "--security-tls-master-cert-name") {
         det::Json sec = j["security"].is_object() ? j["security"] : det::Json::object();
         det::Json t = sec["tls"].is_object() ? sec["tls"] : det::Json::object();

@@ -1,4 +1,5 @@
 // master.cpp — Master bootstrap, configuration, container routing, command tasks, checkpoint GC, restore.
+#include "elastic_logs.hpp"
 #include "task_spec.hpp"
 #include "master.hpp"
 
@@ -49,7 +50,7 @@ MasterConfig MasterConfig::from_json(const Json& j) {
   static const std::set<std::string> known = {"host", "port", "data_dir", "scheduler", "fitting_policy", "preemption", "checkpoint_storage",
                                               "python", "repo_root", "slot_type", "visible_gpus", "artificial_slots", "auth_required",
                                               "cluster_name", "scheduler_tick_ms", "terminate_timeout_ms", "resource_pools", "db", "telemetry", "provisioner", "resource_manager",
-                                              "security", "task_container_defaults"};
+                                              "security", "task_container_defaults", "logging"};
   MasterConfig c;
   for (auto& kv : j.obj())
     if (!known.count(kv.first)) throw ConfigError("unknown field in master config: '" + kv.first + "'");
@@ -87,6 +88,12 @@ MasterConfig MasterConfig::from_json(const Json& j) {
   c.cluster_name = j["cluster_name"].str_or(c.cluster_name);
   c.provisioner = j["provisioner"];
   c.telemetry = j["telemetry"];
+  c.logging = j["logging"];
+  if (c.logging.is_object()) {
+    const std::string t = c.logging["type"].str_or("default");
+    if (t != "default" && t != "elastic") throw ConfigError("logging.type must be default or elastic");
+    if (t == "elastic" && c.logging["host"].str_or("").empty()) throw ConfigError("logging.type elastic needs logging.host");
+  }
   c.resource_manager = j["resource_manager"];
   if (c.resource_manager.is_object()) {
     const std::string t = c.resource_manager["type"].str_or("agent");
@@ -455,6 +462,21 @@ int Master::start() {
     for (auto& d : devices) devs.push_back(d.to_json());
     system.ask(rm, "add_agent", obj({{"id", "agent-local"}, {"label", ""}, {"devices", devs}, {"registered_time", now_rfc3339()},
                                      {"addresses", Json(Json::array_t{Json("127.0.0.1")})}, {"driver_version", nvidia_driver_version()}}));
+  }
+  if (cfg.logging.is_object() && cfg.logging["type"].str_or("default") == "elastic") {
+    auto es = std::make_shared<ElasticLogs>(cfg.logging["host"].as_string(), static_cast<int>(cfg.logging["port"].as_int(9200)),
+                                            cfg.logging["index"].str_or("determined-triallogs"));
+    store.log_append_hook = [this, es](long long trial, const std::vector<Json>& lines) {
+      std::string err;
+      if (!es->append(trial, lines, &err)) log("error", "trial logs: " + err);
+    };
+    store.log_read_hook = [this, es](long long trial, size_t offset, size_t limit) {
+      std::string err;
+      auto rows = es->read(trial, offset, limit, &err);
+      if (!err.empty()) log("error", "trial logs: " + err);
+      return rows;
+    };
+    log("info", "trial logs go to elasticsearch at " + cfg.logging["host"].as_string() + ":" + std::to_string(cfg.logging["port"].as_int(9200)));
   }
   register_routes();
   if (!cfg.tls_cert.empty()) {

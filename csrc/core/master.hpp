@@ -47,6 +47,7 @@ struct MasterConfig {
   std::string cluster_name = "b200-box";
   Json provisioner;                      // {max_instances, slots_per_instance, max_idle_agent_period, ...} or null
   Json resource_manager;                 // null / {type: agent} or {type: kubernetes, namespace, api_server, image, ...}
+  Json logging;                          // {type: default | elastic, host, port, index}: where trial logs are kept
   Json telemetry;                        // {enabled: bool, sink: path}; events go to a local JSONL file (no network here)
   int scheduler_tick_ms = 500;
   int terminate_timeout_ms = 60000;

@@ -101,12 +101,17 @@ class Store {
   }
 
   // ---- trial logs: one file per trial ----
+  // an external log store (Elasticsearch, elastic_logs.hpp) replaces the per-trial files when both hooks are set
+  std::function<void(long long, const std::vector<Json>&)> log_append_hook;
+  std::function<std::vector<Json>(long long, size_t, size_t)> log_read_hook;
   void append_logs(long long trial_id, const std::vector<Json>& lines) {
+    if (log_append_hook) { log_append_hook(trial_id, lines); return; }
     std::lock_guard<std::mutex> g(log_mu_);
     std::ofstream f(dir_ + "/logs/trial-" + std::to_string(trial_id) + ".jsonl", std::ios::app);
     for (auto& l : lines) f << l.dump() << "\n";
   }
   std::vector<Json> read_logs(long long trial_id, size_t offset, size_t limit) {
+    if (log_read_hook) return log_read_hook(trial_id, offset, limit);
     std::lock_guard<std::mutex> g(log_mu_);
     std::vector<Json> out;
     std::ifstream f(dir_ + "/logs/trial-" + std::to_string(trial_id) + ".jsonl");

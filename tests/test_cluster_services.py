@@ -415,3 +415,41 @@ def test_det_tunnel_carries_raw_tcp_to_a_service_task(slotless_master, tmp_path)
             lst.terminate()
     finally:
         c.request("POST", f"/api/v1/commands/{cmd['id']}/kill")
+
+
+def test_trial_logs_in_elasticsearch(tmp_path):
+    """``logging: {type: elastic}``: trial log rows are bulk-indexed into Elasticsearch and read back through the same REST
+    route, position-addressed (reference master/internal/elastic/elastic_trial_logs.go). Runs against tests/fake_elastic.py."""
+    import urllib.request
+
+    es = subprocess.Popen([sys.executable, str(ROOT / "tests" / "fake_elastic.py"), "0"], stdout=subprocess.PIPE, text=True)
+    es_port = int(es.stdout.readline())
+    port_file = tmp_path / "port"
+    master = subprocess.Popen([str(LIB / "det-master"), "--port", "0", "--data-dir", str(tmp_path / "data"), "--artificial-slots", "1",
+                               "--repo-root", str(ROOT), "--python", sys.executable, "--print-port-file", str(port_file),
+                               "--logging", json.dumps({"type": "elastic", "host": "127.0.0.1", "port": es_port, "index": "det-logs-test"})],
+                              stdout=open(tmp_path / "master.log", "w"), stderr=subprocess.STDOUT, env=dict(os.environ, DET_CONFIG_DIR=str(tmp_path / "cfg")))
+    try:
+        for _ in range(200):
+            if port_file.exists() and port_file.read_text().strip():
+                break
+            time.sleep(0.05)
+        c = MasterClient("127.0.0.1", int(port_file.read_text()))
+        rows = [{"trial_id": 7, "message": f"line {i}", "level": "INFO", "rank": i % 2, "stdtype": "stdout"} for i in range(25)]
+        c.request("POST", "/api/v1/trial_logs", {"logs": rows[:10]})
+        c.request("POST", "/api/v1/trial_logs", {"logs": rows[10:] + [{"trial_id": 8, "message": "other trial", "level": "INFO"}]})
+        got = c.request("GET", "/api/v1/trials/7/logs")
+        assert [l["message"] for l in got] == [f"line {i}" for i in range(25)]
+        page = c.request("GET", "/api/v1/trials/7/logs?offset=20&limit=3")
+        assert [l["message"] for l in page] == ["line 20", "line 21", "line 22"]
+        assert [l["message"] for l in c.request("GET", "/api/v1/trials/8/logs")] == ["other trial"]
+        counts = json.loads(urllib.request.urlopen(f"http://127.0.0.1:{es_port}/_count", timeout=5).read())
+        assert counts["indices"] == {"det-logs-test": 26}
+        assert not (tmp_path / "data" / "logs" / "trial-7.jsonl").exists()      # nothing was written to the file store
+    finally:
+        for p in (master, es):
+            p.terminate()
+            try:
+                p.wait(timeout=5)
+            except Exception:
+                p.kill()
