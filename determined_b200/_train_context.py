@@ -78,12 +78,18 @@ class TrialContext:
 
 
 class NativeContext(TrialContext):
-    """Context for the "native" (script-style) API: the user script calls ``context.train(...)`` style
-    entrypoints instead of subclassing a Trial. (Reference: ``_train_context.py:140-183``.)"""
+    """Context handed back by a framework's ``init()`` in the Native API: the user script keeps building its model
+    with it and finally calls the framework's train entry, which runs ``_train_fn`` — under the harness that unwinds
+    the script so the controller can take over. (Reference ``_train_context.py:158-170``.)"""
 
-    def __init__(self, env: EnvContext, dist: Optional[DistributedContext] = None) -> None:
-        super().__init__(env, dist)
-        self._train_fn = None
+    def __init__(self, env: EnvContext, dist: Optional[DistributedContext] = None, comm: Any = None) -> None:
+        super().__init__(env, dist, comm)
+        self._train_fn: Any = None
 
-    def _set_train_fn(self, fn) -> None:
-        self._train_fn = fn
+    def _set_train_fn(self, train_fn: Any) -> None:
+        self._train_fn = train_fn
+
+    def _run_train_fn(self) -> None:
+        if self._train_fn is None:
+            raise RuntimeError("this context is not attached to a training run")
+        self._train_fn()

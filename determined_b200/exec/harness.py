@@ -194,9 +194,12 @@ def main() -> int:
     if int(os.environ.get("DET_NUM_CONTAINERS", "1")) > 1:
         return launch_workers(max(n, 1))      # one of several containers of a trial: join the trial-wide process group
     if n > 1:
-        # `native_parallel: true` (nn.DataParallel in the reference) maps onto the same multi-process path
         if native_parallel:
-            print("native_parallel requested: using the multi-process data-parallel path", flush=True)
+            # one process that sees every slot of the container; wrap_model() puts nn.DataParallel around the model
+            # (reference _pytorch_context.py:135-144). Multi-container trials cannot use it (checked by the master).
+            print(f"native_parallel: one worker process over {n} slots", flush=True)
+            os.environ["DET_NATIVE_PARALLEL_GPUS"] = str(n)
+            return run_worker()
         return launch_workers(n)
     return run_worker()
 

@@ -1,8 +1,8 @@
 """``det.experimental`` — native API and the Python SDK (reference: ``harness/determined/experimental`` and
 ``common/determined_common/experimental``)."""
-from ._native import create, create_trial_instance, test_one_batch
+from ._native import create, create_trial_instance, init_native, test_one_batch
 
-__all__ = ["create", "create_trial_instance", "test_one_batch", "Determined", "Checkpoint"]
+__all__ = ["create", "create_trial_instance", "init_native", "test_one_batch", "Determined", "Checkpoint"]
 
 
 def __getattr__(name):  # lazy: the SDK client pulls in HTTP machinery only when used

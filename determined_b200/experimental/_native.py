@@ -48,26 +48,38 @@ def _make_test_workloads(checkpoint_dir: pathlib.Path, config: Dict[str, Any], r
     yield from interceptor.send(wl.terminate_workload(1), [])
 
 
-def test_one_batch(controller_cls: Optional[Type] = None, trial_class: Optional[Type] = None,
-                   config: Optional[Dict[str, Any]] = None, checkpoint_dir: Optional[str] = None) -> Dict[str, Any]:
-    """Run one batch of training, one validation and one checkpoint of ``trial_class`` locally."""
-    if trial_class is None:
-        raise ValueError("test_one_batch needs a trial_class")
+def test_one_batch(controller_cls: Optional[Type] = None, native_context_cls: Optional[Type] = None,
+                   trial_class: Optional[Type] = None, config: Optional[Dict[str, Any]] = None,
+                   checkpoint_dir: Optional[str] = None) -> Any:
+    """Run one batch of training, one validation and one checkpoint locally. Trial API (``trial_class``): runs now and
+    returns the results. Native API (``controller_cls`` + ``native_context_cls``): returns the context; the run happens
+    when the script reaches its train call (reference ``_native.py:189-251``)."""
     cfg = dict(config or {})
     cfg["scheduling_unit"] = 1
-    log.info("Running a minimal test experiment locally")
     results: Dict[str, Any] = {}
-    with tempfile.TemporaryDirectory() as tmp:
-        ckpt = pathlib.Path(checkpoint_dir) if checkpoint_dir else pathlib.Path(tmp) / "checkpoint"
-        env, dist = _execution.make_local_execution_env(True, cfg, limit_gpus=1)
-        workloads = _make_test_workloads(ckpt, cfg, results)
-        log.info(f"Using hyperparameters: {env.hparams}")
-        controller = load.load_controller_from_trial(trial_class, env, workloads, None, None, dist)
-        controller.run()
-        if not (ckpt / "state_dict.pth").exists():
-            raise AssertionError("checkpoint workload did not write state_dict.pth")
-        results["checkpoint_files"] = sorted(p.name for p in ckpt.iterdir())
-    log.info("The test experiment passed")
+
+    def run(build: Any) -> None:
+        log.info("Running a minimal test experiment locally")
+        with tempfile.TemporaryDirectory() as tmp:
+            ckpt = pathlib.Path(checkpoint_dir) if checkpoint_dir else pathlib.Path(tmp) / "checkpoint"
+            controller = build(_make_test_workloads(ckpt, cfg, results))
+            controller.run()
+            if trial_class is not None and not (ckpt / "state_dict.pth").exists():
+                raise AssertionError("checkpoint workload did not write state_dict.pth")
+            results["checkpoint_files"] = sorted(p.name for p in ckpt.iterdir()) if ckpt.exists() else []
+        log.info("The test experiment passed")
+
+    env, dist = _execution.make_local_execution_env(True, cfg, limit_gpus=1)
+    log.info(f"Using hyperparameters: {env.hparams}")
+    if native_context_cls is not None and controller_cls is not None:
+        controller_cls.pre_execute_hook(env, dist)
+        context = native_context_cls(env, dist)
+        context._test_results = results
+        context._set_train_fn(lambda: run(lambda w: controller_cls.from_native(context=context, env=env, workloads=w)))
+        return context
+    if trial_class is None:
+        raise ValueError("test_one_batch needs a trial_class, or a controller_cls and a native_context_cls")
+    run(lambda w: load.load_controller_from_trial(trial_class, env, w, None, None, dist))
     return results
 
 
@@ -78,6 +90,42 @@ def create_trial_instance(trial_def: Type, checkpoint_dir: str, config: Optional
     env, dist = _execution.make_local_execution_env(False, config, hparams=hparams, limit_gpus=1)
     controller = load.load_controller_from_trial(trial_def, env, iter([]), pathlib.Path(checkpoint_dir), None, dist)
     return controller.trial
+
+
+def init_native(trial_def: Optional[Type] = None, controller_cls: Optional[Type] = None,
+                native_context_cls: Optional[Type] = None, config: Optional[Dict[str, Any]] = None, local: bool = False,
+                test: bool = False, context_dir: str = "", command: Optional[List[str]] = None,
+                master_url: Optional[str] = None) -> Any:
+    """Entry of both user APIs (reference ``_native.py:254-292``).
+
+    Trial API (``trial_def``): same as :func:`create`. Native API (``controller_cls`` + ``native_context_cls``): under the
+    harness, build the context, register it and return it to the script — its train call then unwinds the script;
+    outside the harness, submit the script (``command``) as an experiment, or with ``local=True`` run the one-batch
+    smoke test."""
+    if trial_def is not None:
+        return create(trial_def, config=config, local=local, test=test or local, context_dir=context_dir,
+                      command=command, master_url=master_url)
+    if controller_cls is None or native_context_cls is None:
+        raise ValueError("pass trial_def (Trial API) or controller_cls and native_context_cls (Native API)")
+    if load.RunpyGlobals.is_initialized():
+        g = load.RunpyGlobals.get_instance()
+        controller_cls.pre_execute_hook(g.env, g.dist)
+        context = native_context_cls(g.env, g.dist)
+        load.RunpyGlobals.set_runpy_native_result(context, controller_cls)
+        context._set_train_fn(load.stop_loading_implementation)
+        return context
+    if local:
+        return test_one_batch(controller_cls=controller_cls, native_context_cls=native_context_cls, config=config)
+    import sys
+
+    from .client import Determined
+
+    cfg = dict(config or {})
+    if test:
+        cfg = _execution.make_test_experiment_config(cfg)
+    cfg.setdefault("internal", {})["native"] = {"command": list(command or sys.argv)}
+    exp = Determined(master_url).create_experiment(cfg, context_dir or ".")
+    return exp
 
 
 def create(trial_def: Type, config: Optional[Dict[str, Any]] = None, local: bool = False, test: bool = False,

@@ -66,6 +66,7 @@ class RunpyGlobals:
     def __init__(self, env: EnvContext, dist: DistributedContext) -> None:
         self.env, self.dist = env, dist
         self.trial_cls: Optional[Type] = None
+        self.controller_cls: Optional[Type] = None
         self.context: Any = None
 
     def __enter__(self) -> "RunpyGlobals":
@@ -93,13 +94,26 @@ class RunpyGlobals:
         raise _StopLoadingImplementation()
 
 
+    @classmethod
+    def set_runpy_native_result(cls, context: Any, controller_cls: Type) -> None:
+        """Native API: remember the context the script will keep using and which controller drives it; the script
+        continues until it calls the framework's train entry (reference ``_load_implementation.py:117-128``)."""
+        g = cls.get_instance()
+        g.context, g.controller_cls = context, controller_cls
+
+
+def stop_loading_implementation() -> None:
+    raise _StopLoadingImplementation()
+
+
 class _StopLoadingImplementation(Exception):
     pass
 
 
-def load_native_implementation(env: EnvContext, dist: DistributedContext, command: List[str]) -> Type:
-    """Execute the user's script (``internal.native.command``) until it calls
-    ``det.experimental.create(trial_def=...)``, which records the class and unwinds."""
+def load_native_implementation(env: EnvContext, dist: DistributedContext, command: List[str]) -> Any:
+    """Execute the user's script (``internal.native.command``) until it either calls
+    ``det.experimental.create(trial_def=...)`` (Trial API: returns the class) or, after an ``init_native(controller_cls=,
+    native_context_cls=)``, reaches its train call (Native API: returns a :class:`NativeImplementation`)."""
     script = pathlib.Path(command[0])
     if script.suffix == ".ipynb":
         script = convert_notebook_to_python_script(script)
@@ -112,15 +126,25 @@ def load_native_implementation(env: EnvContext, dist: DistributedContext, comman
             pass
         finally:
             sys.argv = old_argv
-        if g.trial_cls is None:
-            raise RuntimeError(f"{script} finished without calling det.experimental.create(trial_def=...)")
-        return g.trial_cls
+        if g.trial_cls is not None:
+            return g.trial_cls
+        if g.context is not None and g.controller_cls is not None:
+            return NativeImplementation(g.context, g.controller_cls)
+        raise RuntimeError(f"{script} finished without calling det.experimental.create(trial_def=...) or a framework init()")
+
+
+class NativeImplementation:
+    def __init__(self, context: Any, controller_cls: Type) -> None:
+        self.context, self.controller_cls = context, controller_cls
 
 
 def load_controller_from_trial(trial_class: Type, env: EnvContext, workloads: wl.Stream,
                                load_path: Optional[pathlib.Path] = None, rendezvous_info: Optional[RendezvousInfo] = None,
                                dist: Optional[DistributedContext] = None, comm: Any = None) -> Any:
     """Seed → context → user ``Trial(context)`` → controller, in the reference's order."""
+    if isinstance(trial_class, NativeImplementation):
+        return trial_class.controller_cls.from_native(context=trial_class.context, env=env, workloads=workloads,
+                                                      load_path=load_path, rendezvous_info=rendezvous_info)
     controller_class = getattr(trial_class, "trial_controller_class", None)
     if controller_class is None:
         from .pytorch import PyTorchTrial, PyTorchTrialController

@@ -14,8 +14,10 @@ What is different underneath (B200-first):
 * no apex — ``configure_apex_amp`` / ``optimizations.mixed_precision`` map to native bf16 autocast (O1/O2/O3,
   no loss scaling needed) or fp16 with a device-resident dynamic loss scaler; the reference's restriction
   ``aggregation_frequency == 1 and num_losses == 1`` under AMP + distributed (``:336-352``) is lifted;
-* ``native_parallel: true`` (``nn.DataParallel`` in the reference, ``:135-144``) maps onto the same
-  multi-process path with the same global-batch semantics.
+* ``native_parallel: true`` keeps the reference's meaning (``:135-144``): one process over the container's GPUs,
+  ``wrap_model`` returns ``nn.DataParallel(model)``, the process sees the whole global batch, and
+  ``aggregation_frequency`` must be 1. The stock torch optimizer is kept on that path (replica gradients are
+  already reduced onto device 0 by DataParallel; there is no cross-process collective to fuse).
 """
 from __future__ import annotations
 
@@ -184,9 +186,24 @@ class PyTorchTrialContext(TrialContext):
         if not isinstance(model, nn.Module):
             raise TypeError("wrap_model expects a torch.nn.Module")
         model = model.to(self.device)
+        if self.native_parallel_gpus() > 1:
+            if self.aggregation_frequency != 1:
+                raise ValueError("aggregation_frequency > 1 needs the multi-process path: drop `resources.native_parallel` "
+                                 "(reference _pytorch_context.py:136-142)")
+            model = nn.DataParallel(model, device_ids=list(range(self.native_parallel_gpus())))
+            log.debug("model wrapped for native parallel training")
         self._main_model.add_module(f"model_{len(self.models)}", model)
         self.models.append(model)
         return model
+
+    def native_parallel_gpus(self) -> int:
+        """GPUs this one process drives under ``resources.native_parallel`` (0 when the path is off)."""
+        import os
+
+        if not self.env.experiment_config.native_parallel_enabled() or self.comm.size > 1 or self.device.type != "cuda":
+            return 0
+        want = int(os.environ.get("DET_NATIVE_PARALLEL_GPUS", "0") or 0) or max(self.env.experiment_config.slots_per_trial(), 1)
+        return min(want, torch.cuda.device_count())
 
     def wrap_optimizer(self, optimizer: torch.optim.Optimizer, backward_passes_per_step: int = 1,
                        fused: Optional[bool] = None) -> torch.optim.Optimizer:
@@ -199,7 +216,7 @@ class PyTorchTrialContext(TrialContext):
             raise TypeError("wrap_optimizer expects a torch.optim.Optimizer")
         if backward_passes_per_step < 1:
             raise ValueError("backward_passes_per_step must be >= 1")
-        if self.device.type == "cuda" and fused is not False:
+        if self.device.type == "cuda" and fused is not False and self.native_parallel_gpus() <= 1:
             dev = self.device
 
             def alloc(n: int, dtype: torch.dtype, kind: str) -> torch.Tensor:

@@ -207,3 +207,28 @@ def test_test_one_batch_local_mode():
     assert "state_dict.pth" in res["checkpoint_files"] and "code" in res["checkpoint_files"]
     with pytest.raises(NotImplementedError):
         experimental.create(M.XorTrial, cfg, local=True, test=False)
+
+
+def test_native_parallel_wraps_data_parallel(monkeypatch):
+    """`resources.native_parallel`: one process, nn.DataParallel around the model, whole global batch per process,
+    aggregation_frequency must stay 1 (reference _pytorch_context.py:135-144, _env_context.py:89)."""
+    from determined_b200.pytorch import PyTorchTrialContext
+
+    monkeypatch.setattr(PyTorchTrialContext, "native_parallel_gpus", lambda self: 2)
+    cfg = {"resources": {"slots_per_trial": 2, "native_parallel": True}}
+    tv = TrainAndValidate()
+    c = make_controller(M.XorTrial, XOR_HP, tv.send(steps=2), exp_config=cfg)
+    assert isinstance(c.context.models[0], torch.nn.DataParallel)
+    assert c.context.get_per_slot_batch_size() == c.context.get_global_batch_size() == 4
+    assert type(c.context.optimizers[0]).__name__ != "FusedOptimizer"
+    c.run()
+    assert len(tv.training_metrics) == 2 and "loss" in tv.validation_metrics[0]
+    cfg["optimizations"] = {"aggregation_frequency": 2}
+    with pytest.raises(ValueError, match="native_parallel"):
+        make_controller(M.XorTrial, XOR_HP, tv.send(steps=1), exp_config=cfg)
+
+
+def test_native_parallel_off_on_cpu():
+    tv = TrainAndValidate()
+    c = make_controller(M.XorTrial, XOR_HP, tv.send(steps=1), exp_config={"resources": {"native_parallel": True}})
+    assert c.context.native_parallel_gpus() == 0 and not isinstance(c.context.models[0], torch.nn.DataParallel)
