@@ -6,14 +6,22 @@ Role of the reference's yogadl-backed data layer (``harness/determined/_data_lay
 ``@context.experimental.cache_train_dataset(id, version, shuffle, skip_shuffle_at_epoch_end)`` and
 ``cache_validation_dataset``, LFS / S3 / GCS storage, master RW coordinator ``master/internal/rw_coordinator.go``).
 The reference offers it on its TensorFlow trials (tf.data); here it wraps functions that return a map-style
-``torch.utils.data.Dataset``, materialises them to tensors and serves a ``TensorDataset``-like view. Storage type
-``lfs`` (local file system) is implemented; ``s3`` / ``gcs`` need SDKs that are not in this image and raise.
+``torch.utils.data.Dataset``, materialises them to tensors and serves a ``TensorDataset``-like view that can also be
+read as a stream positioned for this trial (``CachedDataset.stream``: resume offset, seeded per-epoch shuffle, shard of
+this rank — the arguments the reference passes to yogadl at ``_data_layer.py:186-204``).
 
 Experiment config (same keys as the reference)::
 
     data_layer:
-      type: lfs
+      type: shared_fs | lfs
       container_storage_path: /tmp/determined-data-layer      # optional
+
+    data_layer:
+      type: s3 | gcs                       # the bucket holds the built data set, every agent keeps a local copy
+      bucket: my-bucket
+      bucket_directory_path: datasets/cache
+      local_cache_container_path: /tmp/determined-data-layer   # optional
+      access_key / secret_key / endpoint_url                    # s3 only, optional
 """
 from __future__ import annotations
 
@@ -47,6 +55,45 @@ class CachedDataset(torch.utils.data.Dataset):
         idx = torch.as_tensor(idxs, dtype=torch.int64)
         row = tuple(c.index_select(0, idx) for c in self.columns)
         return row if len(row) > 1 else row[0]
+
+    # stream position of the trial that asked for this data set; filled in by DataLayer from the trial's context
+    start_offset = 0
+    shuffle = False
+    shuffle_seed = 0
+    shard_rank = 0
+    num_shards = 1
+    drop_shard_remainder = False
+    skip_shuffle_at_epoch_end = False
+
+    def epoch_order(self, epoch: int) -> torch.Tensor:
+        """Record ids THIS shard reads in ``epoch``: shuffle the whole set (seed + epoch, unless
+        ``skip_shuffle_at_epoch_end`` pins the first permutation), then deal records round-robin to the shards."""
+        n = len(self)
+        if self.shuffle:
+            g = torch.Generator()
+            g.manual_seed(int(self.shuffle_seed) + (0 if self.skip_shuffle_at_epoch_end else epoch))
+            order = torch.randperm(n, generator=g)
+        else:
+            order = torch.arange(n)
+        if self.num_shards > 1:
+            if self.drop_shard_remainder:
+                order = order[: n - n % self.num_shards]
+            order = order[self.shard_rank::self.num_shards]
+        return order
+
+    def stream(self, start_offset: Optional[int] = None, epochs: Optional[int] = None) -> Iterator[Any]:
+        """Records from ``start_offset`` (counted in this shard's records since the start of training, so it may lie
+        many epochs in) onwards; endless unless ``epochs`` bounds it."""
+        offset = self.start_offset if start_offset is None else start_offset
+        per_epoch = len(self.epoch_order(0))
+        if per_epoch == 0:
+            return
+        epoch, skip = divmod(offset, per_epoch)
+        last = None if epochs is None else epoch + epochs
+        while last is None or epoch < last:
+            for i in self.epoch_order(epoch)[skip:].tolist():
+                yield self[i]
+            epoch, skip = epoch + 1, 0
 
 
 def _materialise(ds: Any) -> CachedDataset:
@@ -96,46 +143,91 @@ class _Lease:
 
 
 class DataLayer:
-    def __init__(self, config: Optional[Dict[str, Any]] = None, master: Optional[Any] = None) -> None:
+    def __init__(self, config: Optional[Dict[str, Any]] = None, master: Optional[Any] = None,
+                 position: Optional[Dict[str, int]] = None) -> None:
         cfg = dict(config or {"type": "lfs"})
         kind = cfg.get("type", "lfs")
-        if kind not in ("lfs", "shared_fs"):
-            raise NotImplementedError(f"data_layer.type={kind!r} needs a cloud SDK that is not available here; use 'lfs'")
-        self.root = pathlib.Path(cfg.get("container_storage_path") or cfg.get("host_storage_path") or "/tmp/determined-data-layer")
+        self.remote: Any = None
+        self.remote_dir = ""
+        if kind in ("lfs", "shared_fs"):
+            root = cfg.get("container_storage_path") or cfg.get("host_storage_path")
+        elif kind in ("s3", "gcs"):
+            from .utils import objstore
+
+            if not cfg.get("bucket"):
+                raise ValueError(f"data_layer.type={kind} needs `bucket`")
+            self.remote = (objstore.S3Client(cfg["bucket"], cfg.get("access_key"), cfg.get("secret_key"), cfg.get("endpoint_url"))
+                           if kind == "s3" else objstore.GCSClient(cfg["bucket"]))
+            self.remote_dir = (cfg.get("bucket_directory_path") or "").strip("/")
+            root = cfg.get("local_cache_container_path") or cfg.get("local_cache_host_path")
+        else:
+            raise ValueError(f"data_layer.type={kind!r}: expected one of shared_fs, lfs, s3, gcs")
+        self.root = pathlib.Path(root or "/tmp/determined-data-layer")
         self.master = master
-        self.builds = 0    # how many times THIS process built a data set (tests look at it)
+        self.position = dict(position or {})     # start_offset / shuffle_seed / shard_rank / num_shards of this trial
+        self.builds = 0       # how many times THIS process built a data set (tests look at it)
+        self.downloads = 0    # … and how many it fetched from the bucket
 
     def _path(self, dataset_id: str, version: str, split: str) -> pathlib.Path:
         safe = "".join(c if c.isalnum() or c in "-_." else "_" for c in f"{dataset_id}-{version}-{split}")
         return self.root / f"{safe}.pt"
 
+    def _remote_key(self, path: pathlib.Path) -> str:
+        return f"{self.remote_dir}/{path.name}" if self.remote_dir else path.name
+
+    def _fetch(self, path: pathlib.Path) -> bool:
+        """Local copy present (after pulling it from the bucket when there is one)?"""
+        if path.exists():
+            return True
+        if self.remote is not None and self.remote.exists(self._remote_key(path)):
+            self.root.mkdir(parents=True, exist_ok=True)
+            self.remote.get_file(self._remote_key(path), str(path))
+            self.downloads += 1
+            return True
+        return False
+
     def _cached(self, fn: Callable[[], Any], dataset_id: str, version: str, split: str) -> CachedDataset:
         path = self._path(dataset_id, version, split)
         lease = _Lease(self.master, path.stem, path.with_suffix(".lock"))
-        with lease.hold(write=False):
-            if path.exists():
+        local = _Lease(None, path.stem, path.with_suffix(".lock")) if self.master is not None else None
+        with contextlib.ExitStack() as st:
+            st.enter_context(lease.hold(write=False))
+            if local is not None:       # ranks of one box share the download: the flock serialises them
+                st.enter_context(local.hold(write=True))
+            if self._fetch(path):
                 return CachedDataset(torch.load(path))
         with lease.hold(write=True):
-            if not path.exists():      # somebody else may have built it while we queued for the write lease
+            if not self._fetch(path):      # somebody else may have built it while we queued for the write lease
                 ds = _materialise(fn())
                 self.root.mkdir(parents=True, exist_ok=True)
                 tmp = path.with_suffix(f".tmp{os.getpid()}")
                 torch.save(ds.columns, tmp)
                 os.replace(tmp, path)
+                if self.remote is not None:
+                    self.remote.put_file(self._remote_key(path), str(path))
                 self.builds += 1
                 return ds
-        with lease.hold(write=False):
-            return CachedDataset(torch.load(path))
+        return CachedDataset(torch.load(path))
+
+    def _positioned(self, ds: CachedDataset, training: bool, shuffle: bool, skip_shuffle_at_epoch_end: bool = False) -> CachedDataset:
+        pos = self.position
+        ds.shuffle, ds.skip_shuffle_at_epoch_end = bool(shuffle), bool(skip_shuffle_at_epoch_end)
+        ds.shuffle_seed = int(pos.get("shuffle_seed", 0))
+        ds.shard_rank, ds.num_shards = int(pos.get("shard_rank", 0)), max(int(pos.get("num_shards", 1)), 1)
+        ds.start_offset = int(pos.get("start_offset", 0)) if training else 0
+        ds.drop_shard_remainder = training
+        return ds
 
     def cache_train_dataset(self, dataset_id: str, dataset_version: str, shuffle: bool = False,
                             skip_shuffle_at_epoch_end: bool = False) -> Callable:
-        """Decorator for a function that builds the training data set. ``shuffle`` / ``skip_shuffle_at_epoch_end`` are
-        accepted for signature parity; shuffling is the DataLoader's job here (``det.pytorch.DataLoader(shuffle=True)``
-        reshuffles every epoch, and resumes mid-epoch through the skip sampler)."""
+        """Decorator for a function that builds the training data set. Fed to ``det.pytorch.DataLoader`` the result is a
+        plain map-style data set (the loader shuffles, shards and resumes); read through ``.stream()`` it applies
+        ``shuffle`` / ``skip_shuffle_at_epoch_end`` itself, from this trial's resume offset, seed and shard."""
         def wrap(fn: Callable[..., Any]) -> Callable[..., CachedDataset]:
             @functools.wraps(fn)
             def inner(*a: Any, **k: Any) -> CachedDataset:
-                return self._cached(lambda: fn(*a, **k), dataset_id, dataset_version, "train")
+                return self._positioned(self._cached(lambda: fn(*a, **k), dataset_id, dataset_version, "train"), True,
+                                        shuffle, skip_shuffle_at_epoch_end)
             return inner
         return wrap
 
@@ -143,7 +235,7 @@ class DataLayer:
         def wrap(fn: Callable[..., Any]) -> Callable[..., CachedDataset]:
             @functools.wraps(fn)
             def inner(*a: Any, **k: Any) -> CachedDataset:
-                return self._cached(lambda: fn(*a, **k), dataset_id, dataset_version, "validation")
+                return self._positioned(self._cached(lambda: fn(*a, **k), dataset_id, dataset_version, "validation"), False, shuffle)
             return inner
         return wrap
 
@@ -161,4 +253,12 @@ def from_context(context: Any) -> DataLayer:
             master.request("GET", "/info", retries=1)
         except Exception:
             master = None
-    return DataLayer(cfg, master)
+    position: Dict[str, int] = {}
+    if env is not None:
+        try:     # reference _data_layer.py:57-69: offset = batches already trained x per-slot batch; shard = rank / size
+            position = {"start_offset": int(env.initial_workload.total_batches_processed) * int(env.per_slot_batch_size),
+                        "shuffle_seed": int(env.trial_seed), "shard_rank": int(context.distributed.get_rank()),
+                        "num_shards": int(context.distributed.get_size())}
+        except Exception:
+            position = {}
+    return DataLayer(cfg, master, position)

@@ -156,88 +156,80 @@ class _RemoteStorageManager(StorageManager):
             shutil.rmtree(storage_dir, ignore_errors=True)
 
 
-class S3StorageManager(_RemoteStorageManager):
+class _ObjectStoreManager(_RemoteStorageManager):
+    """Checkpoints as objects ``<prefix><storage_id>/<relative path>`` behind a client with put_file / get_file /
+    put_bytes / delete (``utils/objstore.py``)."""
+
+    client: Any
+    prefix = ""
+
+    def upload(self, storage_id: str, storage_dir: str) -> None:
+        for rel in list_directory(storage_dir):
+            key = f"{self.prefix}{storage_id}/{rel}"
+            if rel.endswith("/"):
+                self.client.put_bytes(key, b"")
+            else:
+                self.client.put_file(key, os.path.join(storage_dir, rel))
+
+    def download(self, metadata: StorageMetadata, storage_dir: str) -> None:
+        for rel in metadata.resources:
+            dst = os.path.join(storage_dir, rel)
+            if rel.endswith("/"):
+                os.makedirs(dst, exist_ok=True)
+                continue
+            os.makedirs(os.path.dirname(dst) or storage_dir, exist_ok=True)
+            self.client.get_file(f"{self.prefix}{metadata.storage_id}/{rel}", dst)
+
+    def delete(self, metadata: StorageMetadata) -> None:
+        for rel in metadata.resources:
+            self.client.delete(f"{self.prefix}{metadata.storage_id}/{rel}")
+
+
+class S3StorageManager(_ObjectStoreManager):
+    """``checkpoint_storage: {type: s3, bucket, access_key?, secret_key?, endpoint_url?, prefix?}`` (reference
+    ``common/determined_common/storage/s3.py``). Talks SigV4 to the endpoint itself; no boto3 needed."""
+
     def __init__(self, bucket: str, access_key: Optional[str] = None, secret_key: Optional[str] = None,
-                 endpoint_url: Optional[str] = None, temp_dir: Optional[str] = None, **_: Any) -> None:
+                 endpoint_url: Optional[str] = None, temp_dir: Optional[str] = None, prefix: Optional[str] = None,
+                 region: Optional[str] = None, **_: Any) -> None:
         super().__init__(temp_dir)
-        try:
-            import boto3  # type: ignore
-        except ImportError as e:  # pragma: no cover - SDK not in this image
-            raise RuntimeError("checkpoint_storage type 's3' needs the boto3 package") from e
+        from ..utils.objstore import S3Client
+
         self.bucket = bucket
-        self.client = boto3.client("s3", endpoint_url=endpoint_url, aws_access_key_id=access_key,
-                                   aws_secret_access_key=secret_key)
-
-    def upload(self, storage_id: str, storage_dir: str) -> None:
-        for rel in list_directory(storage_dir):
-            key = f"{storage_id}/{rel}"
-            if rel.endswith("/"):
-                self.client.put_object(Bucket=self.bucket, Key=key, Body=b"")
-            else:
-                self.client.upload_file(os.path.join(storage_dir, rel), self.bucket, key)
-
-    def download(self, metadata: StorageMetadata, storage_dir: str) -> None:
-        for rel in metadata.resources:
-            dst = os.path.join(storage_dir, rel)
-            if rel.endswith("/"):
-                os.makedirs(dst, exist_ok=True)
-                continue
-            os.makedirs(os.path.dirname(dst) or storage_dir, exist_ok=True)
-            self.client.download_file(self.bucket, f"{metadata.storage_id}/{rel}", dst)
-
-    def delete(self, metadata: StorageMetadata) -> None:
-        objs = [{"Key": f"{metadata.storage_id}/{rel}"} for rel in metadata.resources]
-        for i in range(0, len(objs), 1000):
-            self.client.delete_objects(Bucket=self.bucket, Delete={"Objects": objs[i:i + 1000]})
+        self.prefix = (prefix.strip("/") + "/") if prefix else ""
+        self.client = S3Client(bucket, access_key, secret_key, endpoint_url, region)
 
 
-class GCSStorageManager(_RemoteStorageManager):
-    def __init__(self, bucket: str, temp_dir: Optional[str] = None, **_: Any) -> None:
+class GCSStorageManager(_ObjectStoreManager):
+    """``checkpoint_storage: {type: gcs, bucket, prefix?}`` (reference ``storage/gcs.py``); credentials as in
+    :class:`~determined_b200.utils.objstore.GCSClient`."""
+
+    def __init__(self, bucket: str, temp_dir: Optional[str] = None, prefix: Optional[str] = None, **_: Any) -> None:
         super().__init__(temp_dir)
-        try:
-            from google.cloud import storage as gcs  # type: ignore
-        except ImportError as e:  # pragma: no cover
-            raise RuntimeError("checkpoint_storage type 'gcs' needs the google-cloud-storage package") from e
-        self.bucket = gcs.Client().bucket(bucket)
+        from ..utils.objstore import GCSClient
 
-    def upload(self, storage_id: str, storage_dir: str) -> None:
-        for rel in list_directory(storage_dir):
-            blob = self.bucket.blob(f"{storage_id}/{rel}")
-            if rel.endswith("/"):
-                blob.upload_from_string(b"")
-            else:
-                blob.upload_from_filename(os.path.join(storage_dir, rel))
-
-    def download(self, metadata: StorageMetadata, storage_dir: str) -> None:
-        for rel in metadata.resources:
-            dst = os.path.join(storage_dir, rel)
-            if rel.endswith("/"):
-                os.makedirs(dst, exist_ok=True)
-                continue
-            os.makedirs(os.path.dirname(dst) or storage_dir, exist_ok=True)
-            self.bucket.blob(f"{metadata.storage_id}/{rel}").download_to_filename(dst)
-
-    def delete(self, metadata: StorageMetadata) -> None:
-        for rel in metadata.resources:
-            self.bucket.blob(f"{metadata.storage_id}/{rel}").delete()
+        self.prefix = (prefix.strip("/") + "/") if prefix else ""
+        self.client = GCSClient(bucket)
 
 
-class HDFSStorageManager(_RemoteStorageManager):
+class HDFSStorageManager(_ObjectStoreManager):
+    """``checkpoint_storage: {type: hdfs, hdfs_url, hdfs_path, user?}`` (reference ``storage/hdfs.py``) over WebHDFS."""
+
     def __init__(self, hdfs_url: str, hdfs_path: str, user: Optional[str] = None, temp_dir: Optional[str] = None,
                  **_: Any) -> None:
         super().__init__(temp_dir)
-        try:
-            from hdfs import InsecureClient  # type: ignore
-        except ImportError as e:  # pragma: no cover
-            raise RuntimeError("checkpoint_storage type 'hdfs' needs the hdfs package") from e
+        from ..utils.objstore import WebHDFSClient
+
         self.hdfs_path = hdfs_path
-        self.client = InsecureClient(hdfs_url, root=hdfs_path, user=user)
+        self.client = WebHDFSClient(hdfs_url, hdfs_path, user)
 
     def upload(self, storage_id: str, storage_dir: str) -> None:
-        self.client.upload(storage_id, storage_dir)
-
-    def download(self, metadata: StorageMetadata, storage_dir: str) -> None:
-        self.client.download(metadata.storage_id, storage_dir, overwrite=True)
+        self.client.mkdirs(storage_id)
+        for rel in list_directory(storage_dir):
+            if rel.endswith("/"):
+                self.client.mkdirs(f"{storage_id}/{rel}")
+            else:
+                self.client.put_file(f"{storage_id}/{rel}", os.path.join(storage_dir, rel))
 
     def delete(self, metadata: StorageMetadata) -> None:
         self.client.delete(metadata.storage_id, recursive=True)

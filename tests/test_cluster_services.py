@@ -173,8 +173,68 @@ def test_data_layer_builds_once_and_serves_cached_copy(tmp_path):
     dl2 = data_layer.DataLayer({"type": "lfs", "container_storage_path": str(tmp_path)})
     again = dl2.cache_train_dataset("mnist-like", "v1")(lambda: pytest.fail("must not rebuild"))()
     assert len(again) == 6 and dl2.builds == 0
-    with pytest.raises(NotImplementedError):
-        data_layer.DataLayer({"type": "s3", "bucket": "b"})
+    with pytest.raises(ValueError):
+        data_layer.DataLayer({"type": "tape"})
+
+
+def test_data_layer_bucket_backed_cache(tmp_path, monkeypatch):
+    """type: s3 / gcs — the first builder uploads the built data set; another box (empty local cache) downloads it
+    instead of rebuilding."""
+    from tests import fake_objstore
+
+    def build():
+        return torch.utils.data.TensorDataset(torch.arange(10.0).reshape(5, 2), torch.arange(5))
+
+    srv, url, objects, stats = fake_objstore.make_s3()
+    gsrv, gurl, gobjects = fake_objstore.make_gcs()
+    monkeypatch.setenv("STORAGE_EMULATOR_HOST", gurl)
+    try:
+        for kind, store in (("s3", objects), ("gcs", gobjects)):
+            cfg = {"type": kind, "bucket": "data", "bucket_directory_path": "cache/v1", "access_key": "AKIDEXAMPLE",
+                   "secret_key": "s3cr3t", "endpoint_url": url}
+            a = data_layer.DataLayer(dict(cfg, local_cache_container_path=str(tmp_path / kind / "box-a")))
+            ds = a.cache_train_dataset("toy", "1")(build)()
+            assert a.builds == 1 and a.downloads == 0 and len(ds) == 5
+            assert list(store) == ["cache/v1/toy-1-train.pt"]
+            b = data_layer.DataLayer(dict(cfg, local_cache_container_path=str(tmp_path / kind / "box-b")))
+            ds_b = b.cache_train_dataset("toy", "1")(lambda: pytest.fail("must come from the bucket"))()
+            assert b.builds == 0 and b.downloads == 1 and torch.equal(ds_b.columns[0], ds.columns[0])
+            again = b.cache_train_dataset("toy", "1")(lambda: pytest.fail("must come from the local copy"))()
+            assert b.downloads == 1 and len(again) == 5
+        assert stats["bad_signature"] == 0
+    finally:
+        srv.shutdown()
+        gsrv.shutdown()
+
+
+def test_data_layer_stream_resumes_shards_and_reshuffles(tmp_path):
+    """The positioned stream: per-epoch seeded shuffle, round-robin shards that drop the remainder while training, and a
+    start offset that may lie epochs in (reference _data_layer.py:57-69, 186-204)."""
+    def build():
+        return torch.utils.data.TensorDataset(torch.arange(11))
+
+    def layer(**pos):
+        return data_layer.DataLayer({"type": "lfs", "container_storage_path": str(tmp_path)}, position=pos)
+
+    full = layer(shuffle_seed=7).cache_train_dataset("s", "1", shuffle=True)(build)()
+    e0 = [int(x) for x in full.stream(epochs=1)]
+    e01 = [int(x) for x in full.stream(epochs=2)]
+    assert sorted(e0) == list(range(11)) and e01[:11] == e0 and e01[11:] != e0 and sorted(e01[11:]) == list(range(11))
+    # resume 15 records in == the tail of an uninterrupted read
+    resumed = layer(shuffle_seed=7, start_offset=15).cache_train_dataset("s", "1", shuffle=True)(build)()
+    it = resumed.stream()
+    assert [int(next(it)) for _ in range(7)] == e01[15:22]
+    # two shards: disjoint, equal length (remainder dropped), together one epoch minus the dropped record
+    shards = [[int(x) for x in layer(shuffle_seed=7, shard_rank=r, num_shards=2).cache_train_dataset("s", "1", shuffle=True)(build)()
+               .stream(epochs=1)] for r in range(2)]
+    assert len(shards[0]) == len(shards[1]) == 5 and not set(shards[0]) & set(shards[1])
+    assert sorted(shards[0] + shards[1]) == sorted(e0[:10])
+    # validation keeps the remainder and starts at 0 whatever the training offset is
+    val = layer(start_offset=15, shard_rank=1, num_shards=2).cache_validation_dataset("s", "1")(build)()
+    assert [int(x) for x in val.stream(epochs=1)] == [1, 3, 5, 7, 9]
+    pinned = layer(shuffle_seed=7).cache_train_dataset("s", "1", shuffle=True, skip_shuffle_at_epoch_end=True)(build)()
+    two = [int(x) for x in pinned.stream(epochs=2)]
+    assert two[:11] == two[11:]
 
 
 def test_check_and_gpu_helpers():
