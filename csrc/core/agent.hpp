@@ -152,12 +152,65 @@ class ContainerManager {
   ContainerManager(EventFn on_event, LogFn on_log) : on_event_(std::move(on_event)), on_log_(std::move(on_log)) {}
   ~ContainerManager() { kill_all(); }
 
+  // Warm workers: a Python process per slot that has already imported torch and the package, created its CUDA context and
+  // loaded libdet_kernels.so, and now waits on stdin for a task. A single-slot trial assigned to that slot is handed to it
+  // (environment, working directory) instead of being forked cold — trial start latency is then the trial's own set-up.
+  // The reference pays container start + pip install + sshd per trial (master/static/srv/entrypoint.sh:1-47).
+  // mode: "off"; "gpu" (default: a GPU slot gets its warm worker after its first cold start); "lazy" (the same for CPU /
+  // artificial slots too); "eager" (as lazy, and the owner calls prewarm() for every slot up front). The interpreter and
+  // PYTHONPATH are given, or learnt from the first eligible container spec.
+  void enable_warm(const std::string& mode, const std::string& python, const std::string& pythonpath) {
+    std::lock_guard<std::mutex> g(mu_);
+    warm_mode_ = mode; warm_python_ = python; warm_path_ = pythonpath;
+  }
+  // Byte-code cache for every Python process this manager starts. Images that set PYTHONDONTWRITEBYTECODE and ship no
+  // __pycache__ make each process compile torch's sources again (measured: `import torch` 6.0 s, 1.9 s from a cache).
+  void set_pycache_dir(const std::string& dir) {
+    std::lock_guard<std::mutex> g(mu_);
+    pycache_dir_ = dir;
+  }
+  void prewarm(const std::string& key) {
+    {
+      std::lock_guard<std::mutex> g(mu_);
+      if (warm_mode_ == "off" || warm_mode_.empty() || warm_python_.empty()) return;
+      auto it = warm_.find(key);
+      if (it != warm_.end()) {
+        int st = 0;
+        if (waitpid(it->second.pid, &st, WNOHANG) == 0) return;       // still there
+        close(it->second.in_fd); close(it->second.out_fd); close(it->second.err_fd);
+        warm_.erase(it);
+      }
+    }
+    int in_pipe[2], out_pipe[2], err_pipe[2];
+    if (pipe(in_pipe) != 0 || pipe(out_pipe) != 0 || pipe(err_pipe) != 0) return;
+    pid_t pid = fork();
+    if (pid < 0) return;
+    if (pid == 0) {
+      setpgid(0, 0);
+      dup2(in_pipe[0], 0); dup2(out_pipe[1], 1); dup2(err_pipe[1], 2);
+      for (int fd : {in_pipe[0], in_pipe[1], out_pipe[0], out_pipe[1], err_pipe[0], err_pipe[1]}) close(fd);
+      setenv("CUDA_VISIBLE_DEVICES", key == "cpu" ? "" : key.c_str(), 1);
+      setenv("PYTHONUNBUFFERED", "1", 1);
+      apply_pycache_env();
+      const char* pp = getenv("PYTHONPATH");
+      if (!warm_path_.empty()) setenv("PYTHONPATH", (warm_path_ + (pp ? std::string(":") + pp : "")).c_str(), 1);
+      execlp(warm_python_.c_str(), warm_python_.c_str(), "-m", "determined_b200.exec.warm_worker", (char*)nullptr);
+      _exit(127);
+    }
+    close(in_pipe[0]); close(out_pipe[1]); close(err_pipe[1]);
+    fcntl(in_pipe[1], F_SETFD, FD_CLOEXEC); fcntl(out_pipe[0], F_SETFD, FD_CLOEXEC); fcntl(err_pipe[0], F_SETFD, FD_CLOEXEC);
+    std::lock_guard<std::mutex> g(mu_);
+    warm_[key] = Warm{pid, in_pipe[1], out_pipe[0], err_pipe[0]};
+  }
+  size_t warm_count() {
+    std::lock_guard<std::mutex> g(mu_);
+    return warm_.size();
+  }
+
   bool start(const ContainerSpec& spec) {
     on_event_({spec.container_id, "ASSIGNED", 0, ""});
     on_event_({spec.container_id, "PULLING", 0, ""});   // no image to pull: state kept for protocol parity
     on_event_({spec.container_id, "STARTING", 0, ""});
-    int out_pipe[2], err_pipe[2];
-    if (pipe(out_pipe) != 0 || pipe(err_pipe) != 0) { on_event_({spec.container_id, "TERMINATED", 127, "pipe() failed"}); return false; }
     std::map<std::string, std::string> env = spec.env;
     env["DET_CONTAINER_ID"] = spec.container_id;
     std::string slot_ids = "[", gpu_mask;
@@ -170,7 +223,50 @@ class ContainerManager {
     env["DET_USE_GPU"] = use_gpu ? "true" : "false";
     if (use_gpu) env["CUDA_VISIBLE_DEVICES"] = gpu_mask;
     else if (!spec.devices.empty() || env.count("DET_FORCE_CPU")) env["CUDA_VISIBLE_DEVICES"] = "";
-    pid_t pid = fork();
+    {
+      struct timespec ts;
+      clock_gettime(CLOCK_REALTIME, &ts);
+      env["DET_CONTAINER_START_TS"] = std::to_string(static_cast<double>(ts.tv_sec) + ts.tv_nsec * 1e-9);
+    }
+    const std::string warm_key = use_gpu ? gpu_mask : "cpu";
+    const bool warmable = warm_eligible(spec, env);
+    pid_t pid = -1;
+    int out_pipe[2] = {-1, -1}, err_pipe[2] = {-1, -1};
+    if (warmable) {
+      Warm w{};
+      bool have = false;
+      {
+        std::lock_guard<std::mutex> g(mu_);
+        auto it = warm_.find(warm_key);
+        if (it != warm_.end()) {
+          int st = 0;
+          if (waitpid(it->second.pid, &st, WNOHANG) == 0) { w = it->second; have = true; }
+          else { close(it->second.in_fd); close(it->second.out_fd); close(it->second.err_fd); }
+          warm_.erase(it);
+        }
+      }
+      if (have) {
+        Json task = Json::object();
+        Json e = Json::object();
+        for (auto& kv : env) e[kv.first] = kv.second;
+        task["env"] = e;
+        task["cwd"] = spec.cwd;
+        std::string line = task.dump() + "\n";
+        size_t off = 0;
+        bool ok = true;
+        while (off < line.size()) {
+          ssize_t n = write(w.in_fd, line.data() + off, line.size() - off);
+          if (n <= 0) { ok = false; break; }
+          off += static_cast<size_t>(n);
+        }
+        close(w.in_fd);
+        if (ok) { pid = w.pid; out_pipe[0] = w.out_fd; err_pipe[0] = w.err_fd; }
+        else { ::kill(-w.pid, SIGKILL); close(w.out_fd); close(w.err_fd); }
+      }
+    }
+    if (pid < 0) {
+    if (pipe(out_pipe) != 0 || pipe(err_pipe) != 0) { on_event_({spec.container_id, "TERMINATED", 127, "pipe() failed"}); return false; }
+    pid = fork();
     if (pid < 0) { on_event_({spec.container_id, "TERMINATED", 127, "fork() failed"}); return false; }
     if (pid == 0) {
       setpgid(0, 0);
@@ -178,6 +274,7 @@ class ContainerManager {
       dup2(err_pipe[1], 2);
       close(out_pipe[0]); close(out_pipe[1]); close(err_pipe[0]); close(err_pipe[1]);
       if (!spec.cwd.empty() && chdir(spec.cwd.c_str()) != 0) { perror("chdir"); _exit(126); }
+      if (!env.count("PYTHONPYCACHEPREFIX") && !env.count("PYTHONDONTWRITEBYTECODE")) apply_pycache_env();
       for (auto& kv : env) setenv(kv.first.c_str(), kv.second.c_str(), 1);
       {
         auto bm = env.find("DET_BIND_MOUNTS");
@@ -192,6 +289,8 @@ class ContainerManager {
     }
     close(out_pipe[1]);
     close(err_pipe[1]);
+    }
+    if (warmable) std::thread([this, warm_key] { prewarm(warm_key); }).detach();   // the NEXT trial on this slot
     {
       std::lock_guard<std::mutex> g(mu_);
       pids_[spec.container_id] = pid;
@@ -219,6 +318,9 @@ class ContainerManager {
   void kill_all() {
     std::lock_guard<std::mutex> g(mu_);
     for (auto& kv : pids_) ::kill(-kv.second, SIGKILL);
+    warm_mode_ = "off";
+    for (auto& kv : warm_) { ::kill(-kv.second.pid, SIGKILL); close(kv.second.in_fd); close(kv.second.out_fd); close(kv.second.err_fd); waitpid(kv.second.pid, nullptr, 0); }
+    warm_.clear();
   }
   size_t running() {
     std::lock_guard<std::mutex> g(mu_);
@@ -246,10 +348,52 @@ class ContainerManager {
     if (!pending.empty()) on_log_(LogLine{cid, stdtype, pending, -1});
     close(fd);
   }
+  struct Warm { pid_t pid; int in_fd, out_fd, err_fd; };
+  void apply_pycache_env() {   // in a forked child, before exec
+    if (pycache_dir_.empty()) return;
+    unsetenv("PYTHONDONTWRITEBYTECODE");
+    setenv("PYTHONPYCACHEPREFIX", pycache_dir_.c_str(), 1);
+  }
+  // Only a single-slot harness start in a one-container trial goes to a warm worker, and only when nothing in its
+  // environment has to be in place before the interpreter / CUDA start (loader paths, CUDA_*, NCCL_*, OMP_*, bind mounts).
+  bool warm_eligible(const ContainerSpec& spec, const std::map<std::string, std::string>& env) {
+    if (spec.devices.size() != 1) return false;
+    // the harness command, bare or behind the entrypoint shell that sources startup-hook.sh (task_spec.hpp); a model
+    // definition that ships such a hook needs the shell, so it starts cold
+    const size_t n = spec.argv.size();
+    if (n < 3 || spec.argv[n - 2] != "-m" || spec.argv[n - 1] != "determined_b200.exec.harness") return false;
+    if (n != 3 && !(n == 7 && spec.argv[0] == "sh" && spec.argv[3] == "det-entrypoint")) return false;
+    if (n == 7 && access((spec.cwd + "/startup-hook.sh").c_str(), F_OK) == 0) return false;
+    const std::string& python = spec.argv[n - 3];
+    {
+      std::lock_guard<std::mutex> g(mu_);
+      if (warm_mode_ == "off" || warm_mode_.empty()) return false;
+      const bool gpu = spec.devices[0].type == "gpu" && spec.devices[0].brand != "Artificial";
+      if (warm_mode_ == "gpu" && !gpu) return false;
+      if (warm_python_.empty()) {
+        warm_python_ = python;
+        auto pp = env.find("PYTHONPATH");
+        if (pp != env.end()) warm_path_ = pp->second;
+      }
+      if (python != warm_python_) return false;
+    }
+    auto nc = env.find("DET_NUM_CONTAINERS");
+    if (nc != env.end() && nc->second != "1") return false;
+    for (auto& kv : env) {
+      const std::string& k = kv.first;
+      if (k == "CUDA_VISIBLE_DEVICES" || k == "PYTHONPATH") continue;
+      if (k == "DET_BIND_MOUNTS" || k.rfind("LD_", 0) == 0 || k.rfind("CUDA_", 0) == 0 || k.rfind("NCCL_", 0) == 0 || k.rfind("OMP_", 0) == 0 ||
+          k.rfind("PYTHON", 0) == 0 || k.rfind("TORCH_", 0) == 0 || k.rfind("PYTORCH_", 0) == 0)
+        return false;
+    }
+    return true;
+  }
   EventFn on_event_;
   LogFn on_log_;
   std::mutex mu_;
   std::map<std::string, pid_t> pids_;
+  std::map<std::string, Warm> warm_;
+  std::string warm_mode_, warm_python_, warm_path_, pycache_dir_;
 };
 
 }  // namespace det

@@ -23,7 +23,7 @@ static void on_signal(int) { g_stop = true; }
 
 int main(int argc, char** argv) {
   using namespace det;
-  std::string host = "127.0.0.1", id, label, slot_type = "auto", visible, container_master_host;
+  std::string host = "127.0.0.1", id, label, slot_type = "auto", visible, container_master_host, warm_mode = "gpu", warm_python, warm_root, pycache_dir = std::string(getenv("TMPDIR") ? getenv("TMPDIR") : "/tmp") + "/det-agent-pycache";
   int port = 8080, artificial = 0;
   bool detect_only = false;
   TlsClientOptions tls;
@@ -53,7 +53,10 @@ int main(int argc, char** argv) {
     else if (a == "--security-tls-skip-verify") tls.skip_verify = true;
     else if (a == "--security-tls-master-cert") tls.ca_file = next();
     else if (a == "--security-tls-master-cert-name") tls.cert_name = next();
-    else if (a == "--repo-root" || a == "--python") next();   // accepted for symmetry with det-master; specs carry both
+    else if (a == "--repo-root") warm_root = next();
+    else if (a == "--python") warm_python = next();
+    else if (a == "--warm-workers") warm_mode = next();   // off | gpu | lazy | eager (agent.hpp)
+    else if (a == "--pycache-dir") pycache_dir = next();   // byte-code cache of the task processes ("" = leave Python's defaults)
     else { std::cerr << "unknown flag " << a << "\n"; return 2; }
   }
   auto devices = detect_devices(slot_type, visible, artificial);
@@ -95,6 +98,10 @@ int main(int argc, char** argv) {
         e["rank"] = l.rank >= 0 ? Json(static_cast<long long>(l.rank)) : Json();
         pending_logs.push_back(e);
       });
+  cm.set_pycache_dir(pycache_dir);
+  cm.enable_warm(warm_mode, warm_python, warm_root);
+  if (warm_mode == "eager" && !warm_python.empty())
+    for (auto& d : devices) cm.prewarm(d.type == "gpu" && d.brand != "Artificial" ? std::to_string(d.id) : std::string("cpu"));
   std::thread flusher([&] {
     while (!g_stop) {
       usleep(100 * 1000);

@@ -49,6 +49,7 @@ int main(int argc, char** argv) {
       else if (a == "--artificial-slots") j["artificial_slots"] = static_cast<long long>(atoll(next().c_str()));
       else if (a == "--repo-root") j["repo_root"] = next();
       else if (a == "--python") j["python"] = next();
+      else if (a == "--warm-workers") j["warm_workers"] = next();   // off | gpu | lazy | eager
       else if (a == "--slot-type") j["slot_type"] = next();
       else if (a == "--telemetry") j["telemetry"] = det::Json::parse(next());     // {"enabled": true, "sink": "/path/events.jsonl"}
       else if (a == "--provisioner") j["provisioner"] = det::Json::parse(next());   // JSON object, see docs/cluster-config.md

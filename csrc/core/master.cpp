@@ -50,7 +50,7 @@ MasterConfig MasterConfig::from_json(const Json& j) {
   static const std::set<std::string> known = {"host", "port", "data_dir", "scheduler", "fitting_policy", "preemption", "checkpoint_storage",
                                               "python", "repo_root", "slot_type", "visible_gpus", "artificial_slots", "auth_required",
                                               "cluster_name", "scheduler_tick_ms", "terminate_timeout_ms", "resource_pools", "db", "telemetry", "provisioner", "resource_manager",
-                                              "security", "task_container_defaults", "logging"};
+                                              "security", "task_container_defaults", "logging", "warm_workers"};
   MasterConfig c;
   for (auto& kv : j.obj())
     if (!known.count(kv.first)) throw ConfigError("unknown field in master config: '" + kv.first + "'");
@@ -69,6 +69,9 @@ MasterConfig MasterConfig::from_json(const Json& j) {
   c.checkpoint_storage = j["checkpoint_storage"];
   c.python = j["python"].str_or(c.python);
   c.repo_root = j["repo_root"].str_or(c.repo_root);
+  c.warm_workers = j["warm_workers"].str_or(c.warm_workers);
+  if (c.warm_workers != "off" && c.warm_workers != "gpu" && c.warm_workers != "lazy" && c.warm_workers != "eager")
+    throw ConfigError("warm_workers must be off, gpu, lazy or eager");
   c.slot_type = j["slot_type"].str_or(c.slot_type);
   c.visible_gpus = j["visible_gpus"].str_or("");
   c.artificial_slots = static_cast<int>(j["artificial_slots"].as_int(0));
@@ -458,6 +461,10 @@ int Master::start() {
         }));
   } else {
     devices = detect_devices(cfg.slot_type, cfg.visible_gpus, cfg.artificial_slots);
+    containers->set_pycache_dir(cfg.data_dir + "/pycache");
+    containers->enable_warm(cfg.warm_workers, cfg.python, cfg.repo_root);
+    if (cfg.warm_workers == "eager")
+      for (auto& d : devices) containers->prewarm(d.type == "gpu" && d.brand != "Artificial" ? std::to_string(d.id) : std::string("cpu"));
     Json devs = Json::array();
     for (auto& d : devices) devs.push_back(d.to_json());
     system.ask(rm, "add_agent", obj({{"id", "agent-local"}, {"label", ""}, {"devices", devs}, {"registered_time", now_rfc3339()},

@@ -38,6 +38,7 @@ struct MasterConfig {
   Json checkpoint_storage;               // master-level default
   std::string python = "python";
   std::string repo_root;                 // added to PYTHONPATH of launched harness processes
+  std::string warm_workers = "gpu";      // off | gpu | lazy | eager: pre-started harness processes per slot (agent.hpp)
   std::string slot_type = "auto";
   std::string visible_gpus;
   int artificial_slots = 0;

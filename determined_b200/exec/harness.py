@@ -114,7 +114,29 @@ def launch_workers(n: int) -> int:
     return rc
 
 
+def _report_startup(marks: Dict[str, float]) -> None:
+    """One log line per trial run: where the time between the agent accepting the container and the end of the first
+    workload went (trial start latency). ``assigned_to_entry`` is process start + interpreter + (cold start)
+    nothing else, or (warm worker) just the hand-over."""
+    try:
+        t_assign = float(os.environ.get("DET_CONTAINER_START_TS", "0") or 0) or marks["entered"]
+        out = {"assigned_to_entry": marks["entered"] - t_assign, "imports": marks["imports"] - marks["entered"],
+               "env_comm_storage": marks.get("storage_ready", marks["imports"]) - marks["imports"],
+               "build_controller": marks.get("controller_built", 0) - marks.get("storage_ready", 0),
+               "first_workload": marks["first_workload_done"] - marks.get("controller_built", marks["first_workload_done"]),
+               "assigned_to_first_workload_done": marks["first_workload_done"] - t_assign}
+        out = {k: round(v, 3) for k, v in out.items()}
+        warm = os.environ.get("DET_WARM_WORKER")
+        out["warm_worker"] = json.loads(warm) if warm else None
+        print("startup_timing: " + json.dumps(out), flush=True)
+    except Exception:
+        pass
+
+
 def run_worker() -> int:
+    import time
+
+    marks = {"entered": time.time()}
     import torch
 
     from determined_b200 import load, storage
@@ -124,6 +146,10 @@ def run_worker() -> int:
     from determined_b200.layers import BroadcastWorkloads, HarnessProfiler, MasterWorkloadSource, build_workload_manager
     from determined_b200.parallel.comm import Communicator, make_communicator
 
+    from determined_b200.utils.fast_start import skip_dynamo_shims
+
+    skip_dynamo_shims()
+    marks["imports"] = time.time()
     env = build_env()
     if env.debug:
         faulthandler.dump_traceback_later(30, repeat=True)
@@ -156,6 +182,9 @@ def run_worker() -> int:
             if profiler:
                 profiler.stop()
                 profiler.serialize(f"/tmp/step-{w.step_id}-{w.kind.name}")
+            if "first_workload_done" not in marks:
+                marks["first_workload_done"] = time.time()
+                _report_startup(marks)
 
     chief_stream = iter(build_workload_manager(env, profiled(iter(source)), is_chief=True)) if is_chief else None
     if not is_chief:
@@ -170,7 +199,20 @@ def run_worker() -> int:
             load_path = pathlib.Path(stack.enter_context(storage_mgr.restore_path(meta)))
             logging.info(f"Restoring trial from checkpoint {meta.storage_id}")
         try:
-            controller = load.prepare_controller_with_comm(env, workloads, load_path, dist, comm)
+            marks["storage_ready"] = time.time()
+            if os.environ.get("DET_STARTUP_PROFILE") == "1":       # where does controller construction spend its time?
+                import cProfile
+                import io
+                import pstats
+
+                prof = cProfile.Profile()
+                controller = prof.runcall(load.prepare_controller_with_comm, env, workloads, load_path, dist, comm)
+                buf = io.StringIO()
+                pstats.Stats(prof, stream=buf).sort_stats("cumulative").print_stats(45)
+                print(buf.getvalue(), flush=True)
+            else:
+                controller = load.prepare_controller_with_comm(env, workloads, load_path, dist, comm)
+            marks["controller_built"] = time.time()
             controller.run()
         except InvalidHP as e:
             logging.info(f"InvalidHP raised by the trial: {e}")

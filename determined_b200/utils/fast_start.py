@@ -1,0 +1,32 @@
+"""Trial start latency: keep ``torch._dynamo`` (and with it sympy, triton, FSDP — 5 to 7 s of imports) out of the start path.
+
+``torch.optim.Optimizer.add_param_group / zero_grad / state_dict / load_state_dict`` are wrapped in
+``torch._disable_dynamo``, a shim that imports ``torch._dynamo`` on first call only to mark the method as "do not trace".
+Nothing here runs under ``torch.compile`` (the hot path is hand-written kernels and CUDA graphs), so the mark is
+meaningless and the import is pure start-up cost — paid by every trial as soon as it constructs an optimizer. The shim
+caches its result in ``fn.__dynamo_disable``; pre-seeding that attribute with the undecorated method makes it a
+pass-through. A process that later does import ``torch._dynamo`` for its own reasons is unaffected apart from these four
+methods being traceable.
+"""
+from __future__ import annotations
+
+import sys
+
+
+def skip_dynamo_shims() -> int:
+    """Returns how many methods were short-circuited (0 when dynamo is already loaded: nothing to save)."""
+    if "torch._dynamo" in sys.modules:
+        return 0
+    import torch
+
+    n = 0
+    for name in ("add_param_group", "zero_grad", "state_dict", "load_state_dict"):
+        fn = getattr(torch.optim.Optimizer, name, None)
+        inner = getattr(fn, "__wrapped__", None)
+        if inner is not None and getattr(inner, "__dynamo_disable", None) is None:
+            try:
+                setattr(inner, "__dynamo_disable", inner)
+                n += 1
+            except (AttributeError, TypeError):
+                pass
+    return n

@@ -513,3 +513,52 @@ def test_trial_logs_in_elasticsearch(tmp_path):
                 p.wait(timeout=5)
             except Exception:
                 p.kill()
+
+
+def test_warm_workers_take_over_trial_starts(tmp_path):
+    """`--warm-workers eager`: a pre-started harness process per slot is handed the trial (environment + working
+    directory) instead of a cold fork; a replacement is started for the next trial; the trial log carries the start-up
+    timing line with the warm worker's preload costs."""
+    from determined_b200 import _build
+
+    _build.build_core()
+    port_file = tmp_path / "port"
+    env = dict(os.environ, DET_CONFIG_DIR=str(tmp_path / "cfg"))
+    proc = subprocess.Popen([str(LIB / "det-master"), "--port", "0", "--data-dir", str(tmp_path / "data"), "--artificial-slots", "1",
+                             "--repo-root", str(ROOT), "--python", sys.executable, "--print-port-file", str(port_file),
+                             "--warm-workers", "eager"], stdout=open(tmp_path / "master.log", "w"), stderr=subprocess.STDOUT, env=env)
+    try:
+        for _ in range(200):
+            if port_file.exists() and port_file.read_text().strip():
+                break
+            time.sleep(0.05)
+        os.environ["DET_CONFIG_DIR"] = str(tmp_path / "cfg")
+        d = Determined(f"127.0.0.1:{int(port_file.read_text())}")
+        cfg = {"entrypoint": "model_def:XorTrial", "hyperparameters": {"global_batch_size": 8, "hidden_size": 4, "learning_rate": 0.5},
+               "searcher": {"name": "single", "metric": "validation_loss", "max_length": {"batches": 10}}, "scheduling_unit": 10,
+               "checkpoint_storage": {"type": "shared_fs", "host_path": str(tmp_path / "ckpts")}}
+        timings = []
+        for _ in range(2):       # the second trial runs on the replacement worker
+            exp = d.create_experiment(cfg, MODEL_DIR)
+            assert exp.wait(timeout=180) == "COMPLETED"
+            t = exp.describe()["trials"][0]
+            lines = [l["message"] if isinstance(l, dict) else str(l) for l in d.get_trial(t["id"]).logs()]
+            line = next(l for l in lines if "startup_timing:" in l)
+            timings.append(json.loads(line.split("startup_timing:", 1)[1]))
+        for tm in timings:
+            assert tm["warm_worker"] is not None and "import_torch" in tm["warm_worker"], tm
+            assert tm["imports"] < 0.5, tm            # everything was imported before the trial arrived
+        # an environment that must be in place before the interpreter starts goes down the cold path
+        cold = dict(cfg, environment={"environment_variables": ["OMP_NUM_THREADS=1"]})
+        exp = d.create_experiment(cold, MODEL_DIR)
+        assert exp.wait(timeout=180) == "COMPLETED"
+        t = exp.describe()["trials"][0]
+        lines = [l["message"] if isinstance(l, dict) else str(l) for l in d.get_trial(t["id"]).logs()]
+        tm = json.loads(next(l for l in lines if "startup_timing:" in l).split("startup_timing:", 1)[1])
+        assert tm["warm_worker"] is None
+    finally:
+        proc.terminate()
+        try:
+            proc.wait(timeout=5)
+        except Exception:
+            proc.kill()
