@@ -125,6 +125,11 @@ def _report_startup(marks: Dict[str, float]) -> None:
                "build_controller": marks.get("controller_built", 0) - marks.get("storage_ready", 0),
                "first_workload": marks["first_workload_done"] - marks.get("controller_built", marks["first_workload_done"]),
                "assigned_to_first_workload_done": marks["first_workload_done"] - t_assign}
+        from determined_b200.utils import fast_start
+
+        if fast_start.FIRST_BATCH_TS is not None:
+            out["controller_built_to_first_batch"] = fast_start.FIRST_BATCH_TS - marks.get("controller_built", fast_start.FIRST_BATCH_TS)
+            out["assigned_to_first_batch"] = fast_start.FIRST_BATCH_TS - t_assign
         out = {k: round(v, 3) for k, v in out.items()}
         warm = os.environ.get("DET_WARM_WORKER")
         out["warm_worker"] = json.loads(warm) if warm else None

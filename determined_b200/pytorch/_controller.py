@@ -30,7 +30,7 @@ from .._env import DistributedContext, EnvContext, RendezvousInfo
 from .._trial_controller import LoopTrialController
 from ..ops import functional as F
 from ..parallel.fused_optimizer import FusedOptimizer
-from ..utils import util
+from ..utils import fast_start, util
 from . import _callback, _data, _reducer
 from ._context import PyTorchTrialContext
 from ._graph import GraphedTrainBatch
@@ -270,6 +270,8 @@ class PyTorchTrialController(LoopTrialController):
                 raise ValueError("train_batch() must return the loss tensor or a dict of metrics that includes 'loss'")
             per_batch.append(tr)
             self._auto_step_lr_schedulers(batch_idx)
+            if fast_start.FIRST_BATCH_TS is None:
+                fast_start.mark_first_batch(ctx.device)
         ctx._current_batch_idx = None
         num_inputs *= self.comm.size
         metrics = self._finalize_training_metrics(per_batch)

@@ -11,6 +11,24 @@ methods being traceable.
 from __future__ import annotations
 
 import sys
+import time
+from typing import Any, Optional
+
+FIRST_BATCH_TS: Optional[float] = None     # wall-clock time at which this process finished its first training batch
+
+
+def mark_first_batch(device: Any = None) -> None:
+    """Called once by the controller after the first ``train_batch`` (synchronised, so the time is the batch's, not the
+    launch's); the harness reports it in the ``startup_timing`` line."""
+    global FIRST_BATCH_TS
+    try:
+        if device is not None and getattr(device, "type", "") == "cuda":
+            import torch
+
+            torch.cuda.synchronize(device)
+    except Exception:
+        pass
+    FIRST_BATCH_TS = time.time()
 
 
 def skip_dynamo_shims() -> int:

@@ -21,6 +21,12 @@ for _ in range(3):
     opt.grad_buckets()[0].normal_()
     opt.step(max_grad_norm=1.0, zero_grad=True)
 torch.cuda.synchronize()
+opt.grad_buckets()[0].normal_()
+torch.cuda.synchronize()
+torch.cuda.profiler.start()          # ncu --profile-from-start off: only the launches between start() and stop() are captured
+opt.step(max_grad_norm=1.0, zero_grad=True)
+torch.cuda.synchronize()
+torch.cuda.profiler.stop()
 
 ln = M.LayerNorm(768).to(dev)
 x = torch.randn(6144, 768, device=dev, dtype=torch.bfloat16, requires_grad=True)
@@ -28,6 +34,12 @@ for _ in range(3):
     y = ln(x)
     y.backward(torch.ones_like(y))
 torch.cuda.synchronize()
+go = torch.ones_like(y)
+torch.cuda.profiler.start()
+y = ln(x)
+y.backward(go)
+torch.cuda.synchronize()
+torch.cuda.profiler.stop()
 
 Mm, N, K = 6144, 3072, 768
 A = torch.randn(Mm, K, device=dev).bfloat16()
@@ -35,7 +47,16 @@ B = (torch.randn(N, K, device=dev) * 0.05).bfloat16()
 bias = torch.randn(N, device=dev)
 C = torch.empty(Mm, N, device=dev, dtype=torch.bfloat16)
 Z = torch.empty_like(C)
+G = torch.zeros(N, K, device=dev)
 for _ in range(3):
     F.gemm(A, B, C, Mm, N, K, epi=F.EPI_BIAS_GELU, bias=bias, aux_out=Z)
+    F.gemm(A, B, C, Mm, N, K)
+    F.gemm(C, A, G, N, K, Mm, a_mn=True, b_mn=True, out_mode=F.OUT_F32_ATOMIC_ADD)
 torch.cuda.synchronize()
+torch.cuda.profiler.start()
+F.gemm(A, B, C, Mm, N, K, epi=F.EPI_BIAS_GELU, bias=bias, aux_out=Z)
+F.gemm(A, B, C, Mm, N, K)
+F.gemm(C, A, G, N, K, Mm, a_mn=True, b_mn=True, out_mode=F.OUT_F32_ATOMIC_ADD)
+torch.cuda.synchronize()
+torch.cuda.profiler.stop()
 print("ok")
