@@ -473,6 +473,13 @@ int launch_pair_gemm(const CUtensorMap& ta, const CUtensorMap& tb, GemmParams p,
     work = tiles;
   } else {
     static const int stream_auto = [] { const char* e = getenv("DET_GEMM_STREAMK"); return (e && e[0] == '0') ? 0 : 1; }();
+    static const int one_wave_auto = [] { const char* e = getenv("DET_GEMM_ONEWAVE"); return (e && e[0] == '0') ? 0 : 1; }();
+    if (splitk == 0 && one_wave_auto && tiles < units) {
+      // a static split that fills one wave almost exactly beats stream-K: every pair runs ONE segment with one epilogue
+      // instead of two partial tiles (3072 x 768 x 6144: 25.2 us against 29.0; profiles/gemm_layout_probe_r2.json)
+      const int s1 = units / tiles;
+      if (s1 >= 2 && s1 <= 4 && tiles * s1 * 20 >= units * 19 && p.num_kb / s1 >= 8) splitk = s1;
+    }
     if (splitk == 0) {
       // whole tiles when they fill the pairs evenly, otherwise cut the k-block line into equal ranges
       const long long units_kb = static_cast<long long>(tiles) * p.num_kb;

@@ -240,7 +240,10 @@ class PyTorchTrialController(LoopTrialController):
             raise ValueError("step_id and num_batches must be positive")
         ctx = self.context
         for m in ctx.models:
-            m.train()
+            # same effect as the reference's unconditional model.train() per step, without paying Module.__setattr__ on
+            # every submodule when nothing left training mode (the call sits in the host gap between two workloads)
+            if not all(sub.training for sub in m.modules()):
+                m.train()
         for name, (red, for_train, _) in ctx.reducers.items():
             if for_train:
                 red.reset()

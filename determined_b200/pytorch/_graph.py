@@ -109,7 +109,9 @@ class GraphedTrainBatch:
         n0 = _native.launch_count
         batch = _unflatten(self.skeleton, self.static_leaves)
         try:
-            with torch.cuda.graph(graph):
+            # thread_local: the DataLoader's prefetch thread pins host memory (cudaHostAlloc) while this thread captures;
+            # under the default global mode that call invalidates the capture (cudaErrorStreamCaptureInvalidated)
+            with torch.cuda.graph(graph, capture_error_mode="thread_local"):
                 with ctx.autocast():
                     out = self.trial.train_batch(batch=batch, epoch_idx=epoch_idx, batch_idx=batch_idx)
                 F.advance_step_seed(ctx.device)
