@@ -230,6 +230,133 @@ fused_allreduce_kernel(const AllreduceArgs a) {
 }
 
 // ------------------------------------------------------------------------------------------------------------------
+// bf16 on the wire (`optimizations.gradient_compression`; the reference's hvd.Compression.fp16,
+// _pytorch_context.py:191-198). The fp32 bucket is packed into a bf16 staging buffer of the symmetric arena (local pass),
+// the collective runs on the staging buffers — the switch adds bf16 pairs with fp32 accumulation
+// (multimem.ld_reduce ... .acc::f32 ... .bf16x2), or peers are read with 16-byte loads and summed in fp32 registers —
+// scale / unscale / non-finite test / grad-norm partial happen on the fp32 values exactly as in the fp32 kernel, the
+// result goes back out as bf16 (multimem.st / peer stores) and is unpacked into the fp32 bucket (local pass). Half the
+// bytes cross NVLink; bf16 keeps fp32's exponent range, so no overflow handling is needed.
+// ------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t pack2_bf16(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ float bf16lo_f32(uint32_t v) { return __uint_as_float(v << 16); }
+__device__ __forceinline__ float bf16hi_f32(uint32_t v) { return __uint_as_float(v & 0xffff0000u); }
+
+__global__ void __launch_bounds__(256)
+wire_pack_kernel(const float* __restrict__ g, uint4* __restrict__ wire, long long n8) {
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float4 a = reinterpret_cast<const float4*>(g)[2 * i], b = reinterpret_cast<const float4*>(g)[2 * i + 1];
+    wire[i] = make_uint4(pack2_bf16(a.x, a.y), pack2_bf16(a.z, a.w), pack2_bf16(b.x, b.y), pack2_bf16(b.z, b.w));
+  }
+}
+__global__ void __launch_bounds__(256)
+wire_unpack_kernel(const uint4* __restrict__ wire, float* __restrict__ g, long long n8) {
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n8; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const uint4 w = wire[i];
+    reinterpret_cast<float4*>(g)[2 * i] = make_float4(bf16lo_f32(w.x), bf16hi_f32(w.x), bf16lo_f32(w.y), bf16hi_f32(w.y));
+    reinterpret_cast<float4*>(g)[2 * i + 1] = make_float4(bf16lo_f32(w.z), bf16hi_f32(w.z), bf16lo_f32(w.w), bf16hi_f32(w.w));
+  }
+}
+
+// a.t.buf / a.mc_ptr address the bf16 staging buffers here; a.n counts bf16 elements (multiple of 8).
+template <bool USE_MC>
+__global__ void __launch_bounds__(AR_THREADS)
+fused_allreduce_bf16wire_kernel(const AllreduceArgs a) {
+  constexpr int U = USE_MC ? AR_UNROLL_MC : 1;
+  const int rank = a.rank, world = a.world;
+  uint32_t ep = a.epoch[blockIdx.x];
+  rank_barrier(a.t, rank, world, ep + 1);   // every rank has packed its bucket
+  const float scale = a.scale * (a.scale_dev ? *a.scale_dev : 1.0f);
+  const long long n8 = a.n >> 3;            // 16-byte units of eight bf16
+  const long long per = (n8 + world - 1) / world;
+  const long long lo = std::min<long long>(per * rank, n8), hi = std::min<long long>(lo + per, n8);
+  const char* mc = reinterpret_cast<const char*>(a.mc_ptr);
+  float acc = 0.0f;
+  bool bad = false;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * U;
+  for (long long i0 = lo + static_cast<long long>(blockIdx.x) * blockDim.x * U + threadIdx.x; i0 < hi; i0 += stride) {
+    float f[U][8];
+    if (USE_MC) {
+      uint4 w[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long i = i0 + static_cast<long long>(u) * blockDim.x;
+        if (i < hi)
+          asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                       : "=r"(w[u].x), "=r"(w[u].y), "=r"(w[u].z), "=r"(w[u].w) : "l"(mc + i * 16) : "memory");
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        f[u][0] = bf16lo_f32(w[u].x); f[u][1] = bf16hi_f32(w[u].x); f[u][2] = bf16lo_f32(w[u].y); f[u][3] = bf16hi_f32(w[u].y);
+        f[u][4] = bf16lo_f32(w[u].z); f[u][5] = bf16hi_f32(w[u].z); f[u][6] = bf16lo_f32(w[u].w); f[u][7] = bf16hi_f32(w[u].w);
+      }
+    } else {
+      uint4 v[COMM_MAX_RANKS];
+#pragma unroll
+      for (int r = 0; r < COMM_MAX_RANKS; ++r)
+        if (r < world) {
+          const char* src = reinterpret_cast<const char*>(a.t.buf[(rank + r) % world]) + i0 * 16;
+          asm volatile("ld.global.relaxed.sys.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v[r].x), "=r"(v[r].y), "=r"(v[r].z), "=r"(v[r].w) : "l"(src) : "memory");
+        }
+#pragma unroll
+      for (int e = 0; e < 8; ++e) f[0][e] = 0.0f;
+      // fixed order (rank 0 .. world-1) so that every rank would compute the same sum for the same element
+#pragma unroll
+      for (int r0 = 0; r0 < COMM_MAX_RANKS; ++r0)
+        if (r0 < world) {
+          const uint4 x = v[(r0 - rank + world) % world];
+          f[0][0] += bf16lo_f32(x.x); f[0][1] += bf16hi_f32(x.x); f[0][2] += bf16lo_f32(x.y); f[0][3] += bf16hi_f32(x.y);
+          f[0][4] += bf16lo_f32(x.z); f[0][5] += bf16hi_f32(x.z); f[0][6] += bf16lo_f32(x.w); f[0][7] += bf16hi_f32(x.w);
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + static_cast<long long>(u) * blockDim.x;
+      if (i >= hi) break;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        f[u][e] *= scale;
+        acc += f[u][e] * f[u][e];
+        bad |= !isfinite(f[u][e]);
+      }
+      const uint4 o = make_uint4(pack2_bf16(f[u][0], f[u][1]), pack2_bf16(f[u][2], f[u][3]), pack2_bf16(f[u][4], f[u][5]), pack2_bf16(f[u][6], f[u][7]));
+      if (USE_MC) {
+        asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(mc + i * 16), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
+      } else {
+#pragma unroll
+        for (int r = 0; r < COMM_MAX_RANKS; ++r)
+          if (r < world) {
+            char* dst = reinterpret_cast<char*>(a.t.buf[(rank + r) % world]) + i * 16;
+            asm volatile("st.global.relaxed.sys.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
+          }
+      }
+    }
+  }
+  if (a.sumsq != nullptr || a.found_inf != nullptr) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    __shared__ float red[AR_THREADS / 32];
+    __shared__ int sbad;
+    if (threadIdx.x == 0) sbad = 0;
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+    if (bad) sbad = 1;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float s = 0.0f;
+      for (int w = 0; w < (blockDim.x >> 5); ++w) s += red[w];
+      exchange_grad_stats(a, s, sbad != 0);
+    }
+  }
+  rank_barrier(a.t, rank, world, ep + 2);
+  if (threadIdx.x == 0) a.epoch[blockIdx.x] = ep + 2;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
 // TMA-driven all-reduce. The LSU kernel above keeps (threads x unroll) 16-byte requests in flight; a load over NVLink
 // takes microseconds, so it needs thousands of resident threads to fill the links. Here ONE thread per CTA moves the
 // data: for every chunk of this rank's slice it issues `world` bulk loads (cp.async.bulk global -> shared, one per
@@ -495,6 +622,37 @@ extern "C" int det_fused_allreduce_cta(void* const* peer_bufs, void* const* peer
                                        int max_blocks, int threads, int algo, cudaStream_t stream) {
   return fused_allreduce_launch(peer_bufs, peer_flags, mc_ptr, epoch_dev, n_f32, rank, world, scale, scale_dev, sumsq_dev,
                                 found_inf_dev, max_blocks, threads, algo, stream);
+}
+
+// bf16-wire all-reduce of a fp32 bucket: grad (local fp32, n elements, n % 8 == 0), peer_wire = every rank's bf16 staging
+// buffer of n elements in the symmetric arena, mc_wire = its multicast address or null. Three launches on `stream`: pack,
+// collective, unpack; the side outputs (sumsq / found_inf) mean the same as in det_fused_allreduce.
+extern "C" int det_fused_allreduce_bf16wire(float* grad, void* const* peer_wire, void* const* peer_flags, void* mc_wire,
+                                            void* epoch_dev, long long n, int rank, int world, float scale, const float* scale_dev,
+                                            float* sumsq_dev, int* found_inf_dev, int max_blocks, cudaStream_t stream) {
+  using namespace det;
+  if (n <= 0) return 0;
+  DET_REQUIRE(n % 8 == 0, "bf16-wire bucket length must be a multiple of 8 elements");
+  AllreduceArgs a;
+  int rc = fill_table(a.t, peer_wire, peer_flags, world);
+  if (rc) return rc;
+  a.mc_ptr = reinterpret_cast<float*>(mc_wire);
+  a.epoch = reinterpret_cast<uint32_t*>(epoch_dev);
+  a.n = n; a.rank = rank; a.world = world; a.scale = scale; a.scale_dev = scale_dev;
+  a.sumsq = sumsq_dev; a.found_inf = found_inf_dev;
+  const long long n8 = n >> 3;
+  const int local_blocks = static_cast<int>(std::max<long long>(1, std::min<long long>((n8 + 255) / 256, 8LL * sm_count())));
+  wire_pack_kernel<<<local_blocks, 256, 0, stream>>>(grad, reinterpret_cast<uint4*>(peer_wire[rank]), n8);
+  const long long per8 = (n8 + world - 1) / world;
+  const bool mc = mc_wire != nullptr && world > 1;
+  const long long per_block = static_cast<long long>(AR_THREADS) * (mc ? AR_UNROLL_MC : 1);
+  int blocks = static_cast<int>(std::min<long long>((per8 + per_block - 1) / per_block, std::min(sm_count(), COMM_MAX_BLOCKS)));
+  blocks = std::max(1, std::min(blocks, max_blocks > 0 ? max_blocks : 16));
+  if (mc) fused_allreduce_bf16wire_kernel<true><<<blocks, AR_THREADS, 0, stream>>>(a);
+  else fused_allreduce_bf16wire_kernel<false><<<blocks, AR_THREADS, 0, stream>>>(a);
+  wire_unpack_kernel<<<local_blocks, 256, 0, stream>>>(reinterpret_cast<const uint4*>(peer_wire[rank]), grad, n8);
+  DET_CHECK_CUDA(cudaGetLastError());
+  return 0;
 }
 
 extern "C" int det_p2p_broadcast(void* const* peer_bufs, void* const* peer_flags, void* epoch_dev,

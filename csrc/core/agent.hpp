@@ -165,6 +165,13 @@ class ContainerManager {
   }
   // Byte-code cache for every Python process this manager starts. Images that set PYTHONDONTWRITEBYTECODE and ship no
   // __pycache__ make each process compile torch's sources again (measured: `import torch` 6.0 s, 1.9 s from a cache).
+  // How many slots this manager's node runs tasks on: task processes get DET_AGENT_SLOT_COUNT and size their CPU thread
+  // pools to cores / slots (eight trials x one OpenMP team per core each, spinning between parallel regions, is what made a
+  // 0.3 s workload take 7 s on the 8-GPU box).
+  void set_slot_count(int n) {
+    std::lock_guard<std::mutex> g(mu_);
+    slot_count_ = n;
+  }
   void set_pycache_dir(const std::string& dir) {
     std::lock_guard<std::mutex> g(mu_);
     pycache_dir_ = dir;
@@ -191,6 +198,7 @@ class ContainerManager {
       for (int fd : {in_pipe[0], in_pipe[1], out_pipe[0], out_pipe[1], err_pipe[0], err_pipe[1]}) close(fd);
       setenv("CUDA_VISIBLE_DEVICES", key == "cpu" ? "" : key.c_str(), 1);
       setenv("PYTHONUNBUFFERED", "1", 1);
+      if (slot_count_ > 0) setenv("DET_AGENT_SLOT_COUNT", std::to_string(slot_count_).c_str(), 1);
       apply_pycache_env();
       const char* pp = getenv("PYTHONPATH");
       if (!warm_path_.empty()) setenv("PYTHONPATH", (warm_path_ + (pp ? std::string(":") + pp : "")).c_str(), 1);
@@ -221,6 +229,7 @@ class ContainerManager {
     }
     env["DET_SLOT_IDS"] = slot_ids + "]";
     env["DET_USE_GPU"] = use_gpu ? "true" : "false";
+    if (slot_count_ > 0) env["DET_AGENT_SLOT_COUNT"] = std::to_string(slot_count_);
     if (use_gpu) env["CUDA_VISIBLE_DEVICES"] = gpu_mask;
     else if (!spec.devices.empty() || env.count("DET_FORCE_CPU")) env["CUDA_VISIBLE_DEVICES"] = "";
     {
@@ -394,6 +403,7 @@ class ContainerManager {
   std::map<std::string, pid_t> pids_;
   std::map<std::string, Warm> warm_;
   std::string warm_mode_, warm_python_, warm_path_, pycache_dir_;
+  int slot_count_ = 0;
 };
 
 }  // namespace det

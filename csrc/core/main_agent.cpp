@@ -99,6 +99,7 @@ int main(int argc, char** argv) {
         pending_logs.push_back(e);
       });
   cm.set_pycache_dir(pycache_dir);
+  cm.set_slot_count(static_cast<int>(devices.size()));
   cm.enable_warm(warm_mode, warm_python, warm_root);
   if (warm_mode == "eager" && !warm_python.empty())
     for (auto& d : devices) cm.prewarm(d.type == "gpu" && d.brand != "Artificial" ? std::to_string(d.id) : std::string("cpu"));

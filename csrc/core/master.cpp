@@ -462,6 +462,7 @@ int Master::start() {
   } else {
     devices = detect_devices(cfg.slot_type, cfg.visible_gpus, cfg.artificial_slots);
     containers->set_pycache_dir(cfg.data_dir + "/pycache");
+    containers->set_slot_count(static_cast<int>(devices.size()));
     containers->enable_warm(cfg.warm_workers, cfg.python, cfg.repo_root);
     if (cfg.warm_workers == "eager")
       for (auto& d : devices) containers->prewarm(d.type == "gpu" && d.brand != "Artificial" ? std::to_string(d.id) : std::string("cpu"));

@@ -16,7 +16,6 @@ import random
 import sys
 from typing import Any, Dict, Iterator, Optional, Tuple
 
-import torch
 
 from . import constants
 from . import workload as wl
@@ -89,6 +88,8 @@ def make_local_execution_env(managed_training: bool, config: Optional[Dict[str, 
         cfg.pop(ignored, None)
     hp = hparams if hparams is not None else generate_random_hparam_values(cfg.get("hyperparameters", {}),
                                                                           random.Random(seed) if seed is not None else None)
+    import torch     # not at module level: the multi-slot launcher imports this package and must start fast
+
     use_gpu = torch.cuda.is_available()
     n_gpus = torch.cuda.device_count() if use_gpu else 0
     if limit_gpus is not None:

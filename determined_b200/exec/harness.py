@@ -151,9 +151,10 @@ def run_worker() -> int:
     from determined_b200.layers import BroadcastWorkloads, HarnessProfiler, MasterWorkloadSource, build_workload_manager
     from determined_b200.parallel.comm import Communicator, make_communicator
 
-    from determined_b200.utils.fast_start import skip_dynamo_shims
+    from determined_b200.utils.fast_start import cap_cpu_threads, skip_dynamo_shims
 
     skip_dynamo_shims()
+    cap_cpu_threads()
     marks["imports"] = time.time()
     env = build_env()
     if env.debug:

@@ -25,6 +25,9 @@ def preload() -> dict:
     import torch
 
     cost["import_torch"] = round(time.time() - t, 3)
+    from determined_b200.utils.fast_start import cap_cpu_threads
+
+    cap_cpu_threads()       # also while preloading: eight workers warm up side by side
     t = time.time()
     import determined_b200  # noqa: F401
     from determined_b200 import load, pytorch, storage  # noqa: F401

@@ -74,6 +74,8 @@ _SIGNATURES = {
                             c_void_p, c_int, c_void_p],
     "det_fused_allreduce_cta": [c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_int, c_int, c_float, c_void_p, c_void_p,
                                 c_void_p, c_int, c_int, c_int, c_void_p],
+    "det_fused_allreduce_bf16wire": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_int, c_int, c_float, c_void_p,
+                                     c_void_p, c_void_p, c_int, c_void_p],
     "det_p2p_broadcast": [c_void_p, c_void_p, c_void_p, c_ll, c_int, c_int, c_int, c_void_p],
     "det_metric_allreduce": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p],
     "det_arena_alloc": [c_ll, ctypes.POINTER(c_void_p)],

@@ -107,6 +107,7 @@ class TorchDistCommunicator(Communicator):
         self._flags: Optional[_SymmetricRegion] = None
         self._epoch: Optional[torch.Tensor] = None
         self._metric_region: Optional[_SymmetricRegion] = None
+        self._wire_regions: Dict[int, _SymmetricRegion] = {}      # bf16 staging of a gradient bucket, keyed by its address
         self._backend = "none"
         if self.p2p:
             try:
@@ -124,6 +125,10 @@ class TorchDistCommunicator(Communicator):
     # ---- control plane ---------------------------------------------------------------------------
     def barrier(self) -> None:
         if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)      # a host barrier orders device work only if each rank drained its own
+            if "gloo" in str(self.dist.get_backend()) or "cpu" in str(self.dist.get_backend()):
+                self.dist.all_reduce(torch.zeros(1))                # CPU tensor: rides gloo, never touches NCCL
+                return
             self.dist.barrier(device_ids=[self.device.index if self.device.index is not None else 0])
         else:
             self.dist.barrier()
@@ -217,6 +222,19 @@ class TorchDistCommunicator(Communicator):
         off = flat_g.data_ptr() - region.base
         n = flat_g.numel()
         assert n % 4 == 0
+        if self.compress_gradients and n % 8 == 0 and self.size > 1 and algo == 0:
+            # `optimizations.gradient_compression`: bf16 on the wire inside the arena too (pack -> switch / peer reduction
+            # with fp32 accumulation -> unpack); the staging buffer is one more symmetric region, made on first use by
+            # every rank at the same call
+            wire = self._wire_regions.get(flat_g.data_ptr())
+            if wire is None:
+                wire = self._wire_regions[flat_g.data_ptr()] = self._symmetric_alloc(n, torch.bfloat16)
+                self.barrier()
+            wmc = wire.multicast_ptr if (wire.multicast_ptr and os.environ.get("DET_DISABLE_NVLS") != "1") else None
+            _native.call("det_fused_allreduce_bf16wire", F._p(flat_g), wire.table(), self._flags.table(),
+                         ctypes.c_void_p(wmc) if wmc else None, ctypes.c_void_p(self._epoch.data_ptr()), n, self.rank, self.size,
+                         float(scale), F._p(scale_dev), F._p(sumsq_dev), F._p(found_inf_dev), int(max_blocks), F._stream())
+            return True
         mc = region.multicast_ptr + off if (region.multicast_ptr and os.environ.get("DET_DISABLE_NVLS") != "1") else None
         _native.call("det_fused_allreduce_cta", region.table(off), self._flags.table(), ctypes.c_void_p(mc) if mc else None,
                      ctypes.c_void_p(self._epoch.data_ptr()), n, self.rank, self.size, float(scale),
@@ -301,11 +319,15 @@ def init_process_group_from_env(device: torch.device) -> None:
 
     if dist.is_initialized():
         return
-    backend = "nccl" if device.type == "cuda" else "gloo"
+    # GPUs: gloo carries the control plane (barriers, small objects) and NCCL exists only as the lazy fallback for CUDA
+    # collectives — inside one NVSwitch box the gradient path is the peer-memory arena, so a trial that never leaves it
+    # never pays NCCL's communicator set-up (several seconds of every multi-GPU trial start). DET_PG_BACKEND=nccl restores
+    # an eagerly initialised NCCL group.
+    backend = os.environ.get("DET_PG_BACKEND", "cpu:gloo,cuda:nccl") if device.type == "cuda" else "gloo"
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     os.environ.setdefault("MASTER_PORT", "29511")
     kwargs: Dict[str, Any] = {}
-    if device.type == "cuda":
+    if device.type == "cuda" and backend == "nccl":
         kwargs["device_id"] = device
     dist.init_process_group(backend=backend, rank=int(os.environ.get("RANK", "0")),
                             world_size=int(os.environ.get("WORLD_SIZE", "1")), **kwargs)

@@ -48,3 +48,26 @@ def skip_dynamo_shims() -> int:
             except (AttributeError, TypeError):
                 pass
     return n
+
+
+def cap_cpu_threads() -> int:
+    """Size this process's CPU thread pools to its share of the node: cores / slots of the agent (``DET_AGENT_SLOT_COUNT``),
+    times the slots this process drives. Eight single-GPU trials each running one OpenMP team per core — the default — and
+    spinning between parallel regions is what made a 0.3 s workload take 7 s on the 8-GPU box. An explicit
+    ``OMP_NUM_THREADS`` wins. Returns the thread count in effect."""
+    import os
+
+    import torch
+
+    if os.environ.get("OMP_NUM_THREADS"):
+        return torch.get_num_threads()
+    try:
+        slots = int(os.environ.get("DET_AGENT_SLOT_COUNT", "0") or 0)
+    except ValueError:
+        slots = 0
+    if slots <= 1:
+        return torch.get_num_threads()
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    n = max(1, min(torch.get_num_threads(), cores // slots))
+    torch.set_num_threads(n)
+    return n

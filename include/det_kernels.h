@@ -135,6 +135,12 @@ int det_fused_allreduce_cta(void* const* peer_bufs, void* const* peer_flags, voi
                             long long n_f32, int rank, int world, float scale, const float* scale_dev,
                             float* sumsq_dev, int* found_inf_dev, int max_blocks, int threads, int algo,
                             cudaStream_t stream);
+/* bf16 on the wire (optimizations.gradient_compression): pack `grad` (local fp32, n % 8 == 0) into this rank's bf16 staging
+ * buffer, all-reduce the staging buffers (multimem bf16x2 with fp32 accumulation when mc_wire is given, 16-byte peer loads
+ * summed in fp32 otherwise; scale, non-finite test and grad-norm partial as above), unpack into `grad`. */
+int det_fused_allreduce_bf16wire(float* grad, void* const* peer_wire, void* const* peer_flags, void* mc_wire, void* epoch_dev,
+                                 long long n, int rank, int world, float scale, const float* scale_dev, float* sumsq_dev,
+                                 int* found_inf_dev, int max_blocks, cudaStream_t stream);
 int det_p2p_broadcast(void* const* peer_bufs, void* const* peer_flags, void* epoch_dev, long long nbytes, int rank,
                       int world, int root, cudaStream_t stream);
 int det_metric_allreduce(void* const* peer_bufs, void* const* peer_flags, void* epoch_dev, float* out_dev,

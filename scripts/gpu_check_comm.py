@@ -16,8 +16,14 @@ def main():
     rank, local = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
+    import time
+
+    t0 = time.time()
     comm = make_communicator(dev)
+    t_comm = time.time() - t0
     world = comm.size
+    if rank == 0:
+        print(f"communicator ready in {t_comm:.2f} s (backend {dist.get_backend()})", flush=True)
     ok = True
     if rank == 0:
         print("comm:", comm.describe(), flush=True)
@@ -56,6 +62,46 @@ def main():
         ok &= good
         if rank == 0:
             print(f"{'PASS' if good else 'FAIL'} allreduce[{algo_name}] found_inf flags={flags}", flush=True)
+    # bf16 on the wire (optimizations.gradient_compression): multimem bf16x2 path, then the peer-load path
+    for label, env in (("nvls", None), ("lsu", "1")):
+        if env:
+            os.environ["DET_DISABLE_NVLS"] = env
+        for n in (4096, 25 * (1 << 20) + 64):
+            torch.manual_seed(300 + rank)
+            g = comm.alloc(n, torch.float32, "grad", dev)
+            g.copy_(torch.randn(n, device=dev))
+            ref = g.to(torch.bfloat16).float()          # what each rank puts on the wire
+            dist.all_reduce(ref)
+            ref *= 0.125
+            sumsq = torch.zeros(1, device=dev)
+            finf = torch.zeros(1, dtype=torch.int32, device=dev)
+            comm.compress_gradients = True
+            applied = comm.allreduce_grad_bucket(g, 0.125, sumsq_dev=sumsq, found_inf_dev=finf)
+            comm.compress_gradients = False
+            torch.cuda.synchronize()
+            # two bf16 roundings (the switch's output, the scaled result): relative error of a few 2^-8 per element
+            err = ((g - ref).abs().max() / ref.abs().max()).item()
+            ss_ref = ref.double().pow(2).sum().item()
+            ss_err = abs(sumsq.item() - ss_ref) / ss_ref
+            same = comm.allgather_object(float(g.double().sum().item()))
+            good = applied and err < 2e-2 and ss_err < 1e-2 and finf.item() == 0 and all(x == same[0] for x in same)
+            ok &= good
+            if rank == 0:
+                print(f"{'PASS' if good else 'FAIL'} allreduce[bf16wire/{label}] n={n} err={err:.2e} sumsq_err={ss_err:.2e} identical_on_all_ranks={all(x == same[0] for x in same)}", flush=True)
+            g.copy_(torch.randn(n, device=dev))
+            if rank == world - 1:
+                g[n // 2] = float("inf")
+            finf.zero_()
+            comm.compress_gradients = True
+            comm.allreduce_grad_bucket(g, 1.0, found_inf_dev=finf)
+            comm.compress_gradients = False
+            torch.cuda.synchronize()
+            flags = comm.allgather_object(int(finf.item()))
+            good = all(f == 1 for f in flags)
+            ok &= good
+            if rank == 0:
+                print(f"{'PASS' if good else 'FAIL'} allreduce[bf16wire/{label}] found_inf flags={flags}", flush=True)
+        os.environ.pop("DET_DISABLE_NVLS", None)
     # broadcast
     p = comm.alloc(1 << 20, torch.float32, "param", dev)
     p.fill_(float(rank + 1))
@@ -120,6 +166,10 @@ def main():
         for mb in ((0,) if algo != 3 else (24, 48, 64, 96, 128, 148)):
             t = timeit(lambda: comm.allreduce_grad_bucket(g, 1.0 / world, sumsq_dev=sumsq, found_inf_dev=finf, algo=algo, max_blocks=mb), iters=8)
             by_algo[f"{algo_name}_b{mb}"] = {"ms": round(t, 3), "busbw_gbs": round(bytes_moved / t / 1e6, 1)}
+    comm.compress_gradients = True
+    t = timeit(lambda: comm.allreduce_grad_bucket(g, 1.0 / world, sumsq_dev=sumsq, found_inf_dev=finf), iters=8)
+    comm.compress_gradients = False
+    by_algo["bf16wire_nvls"] = {"ms": round(t, 3), "busbw_gbs_fp32_equiv": round(bytes_moved / t / 1e6, 1)}
     if rank == 0:
         print("allreduce by algorithm:", json.dumps(by_algo), flush=True)
     # bandwidth against the number of CTAs: what a collective squeezed onto a few reserved SMs can deliver
