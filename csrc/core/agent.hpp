@@ -15,6 +15,7 @@
 #include <sys/wait.h>
 #include <unistd.h>
 
+#include <algorithm>
 #include <atomic>
 #include <cstdio>
 #include <cstring>
@@ -180,24 +181,30 @@ class ContainerManager {
     {
       std::lock_guard<std::mutex> g(mu_);
       if (warm_mode_ == "off" || warm_mode_.empty() || warm_python_.empty()) return;
-      auto it = warm_.find(key);
-      if (it != warm_.end()) {
-        int st = 0;
-        if (waitpid(it->second.pid, &st, WNOHANG) == 0) return;       // still there
-        close(it->second.in_fd); close(it->second.out_fd); close(it->second.err_fd);
-        warm_.erase(it);
-      }
+      if (warm_live_[key] > 0) return;            // this slot already has a worker, idle or serving a trial
+      ++warm_live_[key];
     }
-    int in_pipe[2], out_pipe[2], err_pipe[2];
-    if (pipe(in_pipe) != 0 || pipe(out_pipe) != 0 || pipe(err_pipe) != 0) return;
+    int in_pipe[2], out_pipe[2], err_pipe[2], ctl_pipe[2];
+    if (pipe(in_pipe) != 0 || pipe(out_pipe) != 0 || pipe(err_pipe) != 0 || pipe(ctl_pipe) != 0) {
+      std::lock_guard<std::mutex> g(mu_);
+      --warm_live_[key];
+      return;
+    }
     pid_t pid = fork();
-    if (pid < 0) return;
+    if (pid < 0) {
+      std::lock_guard<std::mutex> g(mu_);
+      --warm_live_[key];
+      return;
+    }
     if (pid == 0) {
       setpgid(0, 0);
       dup2(in_pipe[0], 0); dup2(out_pipe[1], 1); dup2(err_pipe[1], 2);
-      for (int fd : {in_pipe[0], in_pipe[1], out_pipe[0], out_pipe[1], err_pipe[0], err_pipe[1]}) close(fd);
+      if (ctl_pipe[1] != 3) dup2(ctl_pipe[1], 3);         // control channel: "ready", "done <rc>" (exec/warm_worker.py)
+      for (int fd : {in_pipe[0], in_pipe[1], out_pipe[0], out_pipe[1], err_pipe[0], err_pipe[1], ctl_pipe[0], ctl_pipe[1]})
+        if (fd > 3) close(fd);
       setenv("CUDA_VISIBLE_DEVICES", key == "cpu" ? "" : key.c_str(), 1);
       setenv("PYTHONUNBUFFERED", "1", 1);
+      setenv("DET_WARM_CONTROL_FD", "3", 1);
       if (slot_count_ > 0) setenv("DET_AGENT_SLOT_COUNT", std::to_string(slot_count_).c_str(), 1);
       apply_pycache_env();
       const char* pp = getenv("PYTHONPATH");
@@ -205,10 +212,18 @@ class ContainerManager {
       execlp(warm_python_.c_str(), warm_python_.c_str(), "-m", "determined_b200.exec.warm_worker", (char*)nullptr);
       _exit(127);
     }
-    close(in_pipe[0]); close(out_pipe[1]); close(err_pipe[1]);
-    fcntl(in_pipe[1], F_SETFD, FD_CLOEXEC); fcntl(out_pipe[0], F_SETFD, FD_CLOEXEC); fcntl(err_pipe[0], F_SETFD, FD_CLOEXEC);
-    std::lock_guard<std::mutex> g(mu_);
-    warm_[key] = Warm{pid, in_pipe[1], out_pipe[0], err_pipe[0]};
+    close(in_pipe[0]); close(out_pipe[1]); close(err_pipe[1]); close(ctl_pipe[1]);
+    for (int fd : {in_pipe[1], out_pipe[0], err_pipe[0], ctl_pipe[0]}) fcntl(fd, F_SETFD, FD_CLOEXEC);
+    auto w = std::make_shared<WarmWorker>();
+    w->pid = pid; w->in_fd = in_pipe[1]; w->key = key;
+    {
+      std::lock_guard<std::mutex> g(mu_);
+      warm_[key] = w;
+      workers_.push_back(w);
+    }
+    std::thread([this, w, fd = out_pipe[0]] { pump_worker(w, fd, "stdout"); }).detach();
+    std::thread([this, w, fd = err_pipe[0]] { pump_worker(w, fd, "stderr"); }).detach();
+    std::thread([this, w, fd = ctl_pipe[0]] { control_loop(w, fd); }).detach();
   }
   size_t warm_count() {
     std::lock_guard<std::mutex> g(mu_);
@@ -242,19 +257,22 @@ class ContainerManager {
     pid_t pid = -1;
     int out_pipe[2] = {-1, -1}, err_pipe[2] = {-1, -1};
     if (warmable) {
-      Warm w{};
-      bool have = false;
+      std::shared_ptr<WarmWorker> w;
       {
         std::lock_guard<std::mutex> g(mu_);
         auto it = warm_.find(warm_key);
         if (it != warm_.end()) {
-          int st = 0;
-          if (waitpid(it->second.pid, &st, WNOHANG) == 0) { w = it->second; have = true; }
-          else { close(it->second.in_fd); close(it->second.out_fd); close(it->second.err_fd); }
+          w = it->second;
           warm_.erase(it);
+          if (::kill(w->pid, 0) != 0) w.reset();      // died while idle; its control loop cleans up
+        }
+        if (w) {
+          std::lock_guard<std::mutex> gw(w->mu);
+          w->cid = spec.container_id;
+          pids_[spec.container_id] = w->pid;
         }
       }
-      if (have) {
+      if (w) {
         Json task = Json::object();
         Json e = Json::object();
         for (auto& kv : env) e[kv.first] = kv.second;
@@ -264,13 +282,23 @@ class ContainerManager {
         size_t off = 0;
         bool ok = true;
         while (off < line.size()) {
-          ssize_t n = write(w.in_fd, line.data() + off, line.size() - off);
+          ssize_t n = write(w->in_fd, line.data() + off, line.size() - off);
           if (n <= 0) { ok = false; break; }
           off += static_cast<size_t>(n);
         }
-        close(w.in_fd);
-        if (ok) { pid = w.pid; out_pipe[0] = w.out_fd; err_pipe[0] = w.err_fd; }
-        else { ::kill(-w.pid, SIGKILL); close(w.out_fd); close(w.err_fd); }
+        if (ok) {
+          // the worker's own pump and control threads already run: its output is attributed to this container from now
+          // on, and "done" / process exit produce the TERMINATED event
+          on_event_({spec.container_id, "RUNNING", 0, ""});
+          return true;
+        }
+        {
+          std::lock_guard<std::mutex> g(mu_);
+          std::lock_guard<std::mutex> gw(w->mu);
+          w->cid.clear();
+          pids_.erase(spec.container_id);
+        }
+        ::kill(-w->pid, SIGKILL);
       }
     }
     if (pid < 0) {
@@ -325,11 +353,15 @@ class ContainerManager {
     if (it != pids_.end()) ::kill(-it->second, sig);  // whole process group (the launcher's worker ranks too)
   }
   void kill_all() {
-    std::lock_guard<std::mutex> g(mu_);
-    for (auto& kv : pids_) ::kill(-kv.second, SIGKILL);
-    warm_mode_ = "off";
-    for (auto& kv : warm_) { ::kill(-kv.second.pid, SIGKILL); close(kv.second.in_fd); close(kv.second.out_fd); close(kv.second.err_fd); waitpid(kv.second.pid, nullptr, 0); }
-    warm_.clear();
+    std::vector<std::shared_ptr<WarmWorker>> ws;
+    {
+      std::lock_guard<std::mutex> g(mu_);
+      for (auto& kv : pids_) ::kill(-kv.second, SIGKILL);
+      warm_mode_ = "off";
+      ws = workers_;
+      warm_.clear();
+    }
+    for (auto& w : ws) ::kill(-w->pid, SIGKILL);
   }
   size_t running() {
     std::lock_guard<std::mutex> g(mu_);
@@ -357,7 +389,79 @@ class ContainerManager {
     if (!pending.empty()) on_log_(LogLine{cid, stdtype, pending, -1});
     close(fd);
   }
-  struct Warm { pid_t pid; int in_fd, out_fd, err_fd; };
+  // A pre-started harness process bound to one slot. It serves one trial at a time and, when the trial ends cleanly,
+  // goes back to the pool with its interpreter, imports, CUDA context and kernel library intact.
+  struct WarmWorker {
+    pid_t pid = -1;
+    int in_fd = -1;
+    std::string key;
+    std::mutex mu;
+    std::string cid;      // container being served ("" while idle)
+  };
+  void emit_log(const std::string& cid, const std::string& stdtype, const std::string& line) {
+    static const std::regex rank_re("^\\[rank=(\\d+)\\] ?(.*)$");
+    LogLine l{cid, stdtype, line, -1};
+    std::smatch m;
+    if (std::regex_match(line, m, rank_re)) { l.rank = atoi(m[1].str().c_str()); l.message = m[2].str(); }
+    on_log_(l);
+  }
+  void pump_worker(std::shared_ptr<WarmWorker> w, int fd, const std::string& stdtype) {
+    std::string pending;
+    char buf[4096];
+    ssize_t n;
+    while ((n = read(fd, buf, sizeof buf)) > 0) {
+      pending.append(buf, static_cast<size_t>(n));
+      size_t nl;
+      while ((nl = pending.find('\n')) != std::string::npos) {
+        std::string line = pending.substr(0, nl);
+        pending.erase(0, nl + 1);
+        std::string cid;
+        { std::lock_guard<std::mutex> g(w->mu); cid = w->cid; }
+        if (!cid.empty()) emit_log(cid, stdtype, line);     // output while idle (preload chatter) belongs to no container
+      }
+    }
+    close(fd);
+  }
+  void control_loop(std::shared_ptr<WarmWorker> w, int fd) {
+    FILE* f = fdopen(fd, "r");
+    char line[256];
+    while (f && fgets(line, sizeof line, f)) {
+      if (strncmp(line, "done", 4) != 0) continue;           // "ready" needs no action: a task sent early just waits in the pipe
+      const int rc = atoi(line + 4);
+      usleep(50 * 1000);                                     // let the pumps drain what the trial wrote before its last line
+      std::string cid;
+      { std::lock_guard<std::mutex> g(w->mu); cid = w->cid; w->cid.clear(); }
+      if (cid.empty()) continue;
+      {
+        std::lock_guard<std::mutex> g(mu_);
+        pids_.erase(cid);
+        if (rc == 0 && warm_mode_ != "off") warm_[w->key] = w;   // back in the pool BEFORE the event: the next trial finds it
+      }
+      ContainerEvent ev{cid, "TERMINATED", rc, ""};
+      if (rc) ev.failure = "container failed with non-zero exit code: " + std::to_string(rc);
+      on_event_(ev);
+    }
+    if (f) fclose(f); else close(fd);
+    int status = 0;
+    waitpid(w->pid, &status, 0);
+    std::string cid;
+    { std::lock_guard<std::mutex> g(w->mu); cid = w->cid; w->cid.clear(); }
+    {
+      std::lock_guard<std::mutex> g(mu_);
+      if (warm_live_[w->key] > 0) --warm_live_[w->key];
+      auto it = warm_.find(w->key);
+      if (it != warm_.end() && it->second == w) warm_.erase(it);
+      if (!cid.empty()) pids_.erase(cid);
+      workers_.erase(std::remove(workers_.begin(), workers_.end(), w), workers_.end());
+    }
+    close(w->in_fd);
+    if (!cid.empty()) {                                        // died (or was killed) while serving a trial
+      ContainerEvent ev{cid, "TERMINATED", 0, ""};
+      if (WIFEXITED(status)) { ev.exit_code = WEXITSTATUS(status); if (ev.exit_code) ev.failure = "container failed with non-zero exit code: " + std::to_string(ev.exit_code); }
+      else if (WIFSIGNALED(status)) { ev.exit_code = 128 + WTERMSIG(status); ev.failure = std::string("container killed by signal ") + strsignal(WTERMSIG(status)); }
+      on_event_(ev);
+    }
+  }
   void apply_pycache_env() {   // in a forked child, before exec
     if (pycache_dir_.empty()) return;
     unsetenv("PYTHONDONTWRITEBYTECODE");
@@ -401,7 +505,9 @@ class ContainerManager {
   LogFn on_log_;
   std::mutex mu_;
   std::map<std::string, pid_t> pids_;
-  std::map<std::string, Warm> warm_;
+  std::map<std::string, std::shared_ptr<WarmWorker>> warm_;   // idle workers by slot key
+  std::map<std::string, int> warm_live_;                       // workers alive (idle or serving) by slot key
+  std::vector<std::shared_ptr<WarmWorker>> workers_;
   std::string warm_mode_, warm_python_, warm_path_, pycache_dir_;
   int slot_count_ = 0;
 };

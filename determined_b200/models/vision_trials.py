@@ -132,6 +132,8 @@ class MNistTrial(_ClassifierTrial):
         self.optimizer = context.wrap_optimizer(torch.optim.Adadelta(self.model.parameters(), lr=float(hp.get("learning_rate", 1.0))))
         if hp.get("overlap_grad_allreduce", False):
             context.experimental.enable_grad_overlap(chunk_mb=int(hp.get("overlap_chunk_mb", 1)))
+        if hp.get("use_cuda_graphs", False):
+            context.experimental.enable_cuda_graphs()
 
 
 class CIFARTrial(_ClassifierTrial):
@@ -146,6 +148,8 @@ class CIFARTrial(_ClassifierTrial):
         self.optimizer = context.wrap_optimizer(torch.optim.RMSprop(
             self.model.parameters(), lr=float(hp.get("learning_rate", 1e-4)), weight_decay=float(hp.get("learning_rate_decay", 1e-6)),
             alpha=0.9))
+        if hp.get("use_cuda_graphs", False):      # small networks are launch-bound in eager mode
+            context.experimental.enable_cuda_graphs()
 
 
 class ResNet50Trial(_ClassifierTrial):

@@ -78,6 +78,16 @@ _SIGNATURES = {
                                      c_void_p, c_void_p, c_int, c_void_p],
     "det_p2p_broadcast": [c_void_p, c_void_p, c_void_p, c_ll, c_int, c_int, c_int, c_void_p],
     "det_metric_allreduce": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p],
+    "det_vmm_multicast_supported": [c_int, ctypes.POINTER(c_int)],
+    "det_vmm_granularity": [c_int, c_int, c_int, ctypes.POINTER(c_ll)],
+    "det_vmm_create": [c_int, c_ll, ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(c_int)],
+    "det_vmm_import": [c_int, ctypes.POINTER(ctypes.c_ulonglong)],
+    "det_vmm_map": [ctypes.c_ulonglong, c_ll, c_ll, c_int, ctypes.POINTER(c_void_p)],
+    "det_vmm_unmap": [c_void_p, c_ll],
+    "det_vmm_release": [ctypes.c_ulonglong],
+    "det_vmm_multicast_create": [c_int, c_ll, ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(c_int)],
+    "det_vmm_multicast_add_device": [ctypes.c_ulonglong, c_int],
+    "det_vmm_multicast_bind": [ctypes.c_ulonglong, ctypes.c_ulonglong, c_ll],
     "det_arena_alloc": [c_ll, ctypes.POINTER(c_void_p)],
     "det_arena_free": [c_void_p],
     "det_ipc_export": [c_void_p, ctypes.c_char_p],

@@ -108,6 +108,7 @@ class TorchDistCommunicator(Communicator):
         self._epoch: Optional[torch.Tensor] = None
         self._metric_region: Optional[_SymmetricRegion] = None
         self._wire_regions: Dict[int, _SymmetricRegion] = {}      # bf16 staging of a gradient bucket, keyed by its address
+        self._vmm: Any = None                                     # (FdExchange, multicast usable) | False | None = not probed
         self._backend = "none"
         if self.p2p:
             try:
@@ -151,7 +152,34 @@ class TorchDistCommunicator(Communicator):
         an NVLS multicast address when the switch supports it). Fallback: cudaMalloc + CUDA IPC handles
         exchanged through the control plane."""
         elem = torch.empty((), dtype=dtype).element_size()
-        if os.environ.get("DET_ARENA_BACKEND", "symm") == "symm":
+        backend = os.environ.get("DET_ARENA_BACKEND", "vmm")
+        if backend == "vmm":
+            # native arena (csrc/comm/vmm_arena.cu + parallel/vmm.py): cuMemCreate + fd exchange + cuMulticast*. Whether it
+            # (and multicast) can be used is agreed by all ranks once; afterwards a failure is fatal, not a fallback.
+            from . import vmm
+
+            if self._vmm is None:
+                idx = self.device.index if self.device.index is not None else 0
+                torch.zeros(1, device=self.device)          # primary context up before the driver API is used
+                ok, mc = vmm.supported(self, idx)
+                self._vmm = (vmm.FdExchange(self), mc) if ok else False
+                if not ok and self.rank == 0:
+                    print("[det] native VMM arena unavailable on this box; using torch symmetric memory", flush=True)
+            if self._vmm:
+                exch, mc = self._vmm
+                idx = self.device.index if self.device.index is not None else 0
+                reg = vmm.allocate(self, exch, idx, n * elem, with_multicast=mc and os.environ.get("DET_DISABLE_NVLS") != "1")
+                local = _tensor_from_ptr(reg.ptrs[self.rank], n, dtype, self.device)
+                local.zero_()
+                torch.cuda.synchronize(self.device)
+                region = _SymmetricRegion(local, reg.ptrs, reg)
+                region.multicast_ptr = reg.multicast_ptr
+                self._backend = "cuda_vmm"
+                self._regions.append(region)
+                self.barrier()                               # every copy is zeroed before anyone writes through a peer mapping
+                return region
+            backend = "symm"
+        if backend == "symm":
             try:
                 import torch.distributed._symmetric_memory as symm
 

@@ -538,7 +538,7 @@ def test_warm_workers_take_over_trial_starts(tmp_path):
                "searcher": {"name": "single", "metric": "validation_loss", "max_length": {"batches": 10}}, "scheduling_unit": 10,
                "checkpoint_storage": {"type": "shared_fs", "host_path": str(tmp_path / "ckpts")}}
         timings = []
-        for _ in range(2):       # the second trial runs on the replacement worker
+        for _ in range(2):       # the second trial runs in the same, re-pooled worker
             exp = d.create_experiment(cfg, MODEL_DIR)
             assert exp.wait(timeout=180) == "COMPLETED"
             t = exp.describe()["trials"][0]
@@ -548,6 +548,8 @@ def test_warm_workers_take_over_trial_starts(tmp_path):
         for tm in timings:
             assert tm["warm_worker"] is not None and "import_torch" in tm["warm_worker"], tm
             assert tm["imports"] < 0.5, tm            # everything was imported before the trial arrived
+        # the SAME process served both: after a clean trial the worker goes back to its slot's pool
+        assert [tm["warm_worker"]["trials_served_before"] for tm in timings] == [0, 1], timings
         # an environment that must be in place before the interpreter starts goes down the cold path
         cold = dict(cfg, environment={"environment_variables": ["OMP_NUM_THREADS=1"]})
         exp = d.create_experiment(cold, MODEL_DIR)
