@@ -11,7 +11,7 @@ from determined_b200 import _execution, load
 from determined_b200 import workload as wl
 
 ROOT = pathlib.Path(__file__).resolve().parent.parent
-sys.path.insert(0, str(ROOT / "tests" / "fixtures" / "no_op"))
+NO_OP_DIR = ROOT / "tests" / "fixtures" / "no_op"
 
 
 def _env(hp, **cfg):
@@ -22,9 +22,13 @@ def _env(hp, **cfg):
 
 
 def _drive(env, dist, stream_fn, load_path=None):
-    import importlib
+    import importlib.util
 
-    md = importlib.import_module("model_def")
+    # by path, under a private name: other test modules of the same xdist worker import their own `model_def`
+    spec = importlib.util.spec_from_file_location("no_op_model_def", NO_OP_DIR / "model_def.py")
+    md = importlib.util.module_from_spec(spec)
+    sys.modules["no_op_model_def"] = md
+    spec.loader.exec_module(md)
     results = []
 
     def stream():
