@@ -85,8 +85,11 @@ __device__ __forceinline__ void st_f4(float* p, const float4& v) {
 // COMM_MAX_BLOCKS per-block counters: [SS_EPOCH] launch number, [SS_DONE] blocks finished, [SS_PART] running partial.
 constexpr int SS_VALUE = COMM_MAX_BLOCKS * COMM_MAX_RANKS;
 constexpr int SS_TAG = SS_VALUE + COMM_MAX_RANKS;
-constexpr int FLAG_WORDS = SS_TAG + COMM_MAX_RANKS;
-constexpr int SS_EPOCH = COMM_MAX_BLOCKS, SS_DONE = COMM_MAX_BLOCKS + 1, SS_PART = COMM_MAX_BLOCKS + 2;
+// TURN + c * COMM_MAX_RANKS + r: 1 once rank r's share of chunk c of the current step's pipelined all-gather has landed
+// in THIS rank's bucket
+constexpr int TURN = SS_TAG + COMM_MAX_RANKS;
+constexpr int FLAG_WORDS = TURN + 8 * COMM_MAX_RANKS;   // 8 = PIPE_MAX_CHUNKS
+constexpr int SS_EPOCH = COMM_MAX_BLOCKS, SS_DONE = COMM_MAX_BLOCKS + 1, SS_PART = COMM_MAX_BLOCKS + 2, AG_DONE = COMM_MAX_BLOCKS + 3;
 constexpr int EPOCH_WORDS = COMM_MAX_BLOCKS + 4;
 
 struct AllreduceArgs {
@@ -227,6 +230,172 @@ fused_allreduce_kernel(const AllreduceArgs a) {
   }
   rank_barrier(a.t, rank, world, ep + 2);  // every slice has landed everywhere
   if (threadIdx.x == 0) a.epoch[blockIdx.x] = ep + 2;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Pipelined form: reduce-scatter now, all-gather chunk by chunk UNDER the optimizer.
+//
+// A fused all-reduce ends before the optimizer starts; with grad-norm clipping nothing can be updated until the whole
+// bucket has been reduced (the norm needs every element). But only the reduce-scatter half feeds the norm. So the bucket
+// is cut into `chunks` contiguous chunks and every chunk into `world` sub-slices, rank r owning sub-slice r of each chunk:
+//   1. reduce_scatter_stats_kernel   every rank reduces ITS sub-slices (switch reduction or peer loads), applies the scale,
+//                                    accumulates Σg² / non-finite, keeps the result in its OWN bucket, and the per-rank
+//                                    statistics are exchanged in-kernel — after it every rank knows the clip coefficient;
+//   2. allgather_send_kernel(c)      every rank multicasts its sub-slice of chunk c into every rank's bucket (all ranks at
+//                                    once: every link busy, as in a plain all-gather) and then raises TURN[c][rank] on every
+//                                    rank; the launches for c = 0, 1, ... follow each other on a side stream;
+//   3. the optimizer kernel for chunk c (one contiguous range) starts on every rank as soon as all of TURN[c][*] are up
+//      there — while chunk c+1 is on the wire. The wire (NVLink in, little HBM) and the optimizer (HBM-bound) use
+//      different resources.
+// Waiting is done by wait_chunk_kernel (one warp) placed in the stream BEFORE the kernel that needs the data, never by the
+// working kernels themselves: the only kernels that ever spin hold one warp and wait for OTHER GPUs' send kernels, which
+// wait for nothing — no two kernels of one GPU wait for each other and nothing can deadlock for SM space.
+// ------------------------------------------------------------------------------------------------------------------
+constexpr int PIPE_MAX_CHUNKS = 8;
+
+struct PipeGeom {
+  long long n4, chunk4, sub4;   // float4 units: bucket, one chunk (= world * sub4), one rank's share of a chunk
+  int chunks;
+};
+__host__ __device__ inline PipeGeom pipe_geom(long long n_f32, int world, int chunks) {
+  PipeGeom g;
+  g.n4 = n_f32 >> 2;
+  g.chunks = chunks;
+  const long long c4 = (g.n4 + chunks - 1) / chunks;
+  g.sub4 = (c4 + world - 1) / world;
+  g.chunk4 = g.sub4 * world;
+  return g;
+}
+
+template <bool USE_MC>
+__global__ void __launch_bounds__(AR_THREADS)
+reduce_scatter_stats_kernel(const AllreduceArgs a, const int chunks) {
+  constexpr int U = USE_MC ? AR_UNROLL_MC : AR_UNROLL_P2P;
+  const int rank = a.rank, world = a.world;
+  uint32_t ep = a.epoch[blockIdx.x];
+  if (blockIdx.x == 0 && threadIdx.x < PIPE_MAX_CHUNKS * COMM_MAX_RANKS)   // last step's turns were all consumed
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(a.t.flags[rank] + TURN + threadIdx.x), "r"(0u) : "memory");
+  rank_barrier(a.t, rank, world, ep + 1);   // gradients complete everywhere; nobody is still gathering the last step
+  const float scale = a.scale * (a.scale_dev ? *a.scale_dev : 1.0f);
+  const PipeGeom g = pipe_geom(a.n, world, chunks);
+  float* mine = reinterpret_cast<float*>(a.t.buf[rank]);
+  float acc = 0.0f;
+  bool bad = false;
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * U;
+  for (int c = 0; c < chunks; ++c) {
+    const long long lo = std::min<long long>(c * g.chunk4 + rank * g.sub4, g.n4), hi = std::min<long long>(lo + g.sub4, g.n4);
+    for (long long i0 = lo + static_cast<long long>(blockIdx.x) * blockDim.x * U + threadIdx.x; i0 < hi; i0 += stride) {
+      float4 s[U];
+      if (USE_MC) {
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const long long i = i0 + static_cast<long long>(u) * blockDim.x;
+          if (i < hi)
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                         : "=f"(s[u].x), "=f"(s[u].y), "=f"(s[u].z), "=f"(s[u].w) : "l"(a.mc_ptr + i * 4) : "memory");
+        }
+      } else {
+        float4 v[U][COMM_MAX_RANKS];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const long long i = i0 + static_cast<long long>(u) * blockDim.x;
+          if (i < hi) {
+#pragma unroll
+            for (int r = 0; r < COMM_MAX_RANKS; ++r)
+              if (r < world) v[u][r] = ld_f4(reinterpret_cast<const float*>(a.t.buf[(rank + r) % world]) + i * 4);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          s[u] = v[u][0];
+#pragma unroll
+          for (int r = 1; r < COMM_MAX_RANKS; ++r)
+            if (r < world) { s[u].x += v[u][r].x; s[u].y += v[u][r].y; s[u].z += v[u][r].z; s[u].w += v[u][r].w; }
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long i = i0 + static_cast<long long>(u) * blockDim.x;
+        if (i >= hi) break;
+        float4 t = s[u];
+        t.x *= scale; t.y *= scale; t.z *= scale; t.w *= scale;
+        acc += t.x * t.x + t.y * t.y + t.z * t.z + t.w * t.w;
+        bad |= !(isfinite(t.x) && isfinite(t.y) && isfinite(t.z) && isfinite(t.w));
+        reinterpret_cast<float4*>(mine)[i] = t;
+      }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  __shared__ float red[AR_THREADS / 32];
+  __shared__ int sbad;
+  if (threadIdx.x == 0) sbad = 0;
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  if (bad) sbad = 1;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.0f;
+    for (int w = 0; w < (blockDim.x >> 5); ++w) t += red[w];
+    exchange_grad_stats(a, t, sbad != 0);
+    a.epoch[blockIdx.x] = ep + 1;
+  }
+}
+
+template <bool USE_MC>
+__global__ void __launch_bounds__(AR_THREADS)
+allgather_send_kernel(const AllreduceArgs a, const int chunks, const int c) {
+  constexpr int U = 8;
+  const int rank = a.rank, world = a.world;
+  const PipeGeom g = pipe_geom(a.n, world, chunks);
+  const long long lo = std::min<long long>(c * g.chunk4 + rank * g.sub4, g.n4), hi = std::min<long long>(lo + g.sub4, g.n4);
+  const float4* mine = reinterpret_cast<const float4*>(a.t.buf[rank]);
+  const long long stride = static_cast<long long>(gridDim.x) * blockDim.x * U;
+  for (long long i0 = lo + static_cast<long long>(blockIdx.x) * blockDim.x * U + threadIdx.x; i0 < hi; i0 += stride) {
+    float4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + static_cast<long long>(u) * blockDim.x;
+      if (i < hi) v[u] = mine[i];
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + static_cast<long long>(u) * blockDim.x;
+      if (i >= hi) break;
+      if (USE_MC) {
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(a.mc_ptr + i * 4),
+                     "f"(v[u].x), "f"(v[u].y), "f"(v[u].z), "f"(v[u].w) : "memory");
+      } else {
+#pragma unroll
+        for (int r = 1; r < COMM_MAX_RANKS; ++r)
+          if (r < world) st_f4(reinterpret_cast<float*>(a.t.buf[(rank + r) % world]) + i * 4, v[u]);
+      }
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const uint32_t done = atomicAdd(a.epoch + AG_DONE, 1u);
+    if (done == gridDim.x - 1) {            // last block: everything this rank sent of chunk c is ordered before the flags
+      __threadfence();
+      a.epoch[AG_DONE] = 0;
+      __threadfence_system();
+      for (int r = 0; r < world; ++r)
+        if (r != rank) st_release_sys(a.t.flags[r] + TURN + c * COMM_MAX_RANKS + rank, 1u);
+    }
+  }
+}
+
+// lanes 0 .. world-1 (except this rank's own) each wait for one sender's flag of chunk c
+__global__ void __launch_bounds__(32)
+wait_chunk_kernel(const uint32_t* flags, const int c, const int rank, const int world) {
+  if (static_cast<int>(threadIdx.x) < world && static_cast<int>(threadIdx.x) != rank) {
+    const uint32_t* f = flags + TURN + c * COMM_MAX_RANKS + threadIdx.x;
+    const long long t0 = clock64();
+    while (ld_acquire_sys(f) == 0u) {
+      if (clock64() - t0 > 20000000000LL) __trap();
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -622,6 +791,73 @@ extern "C" int det_fused_allreduce_cta(void* const* peer_bufs, void* const* peer
                                        int max_blocks, int threads, int algo, cudaStream_t stream) {
   return fused_allreduce_launch(peer_bufs, peer_flags, mc_ptr, epoch_dev, n_f32, rank, world, scale, scale_dev, sumsq_dev,
                                 found_inf_dev, max_blocks, threads, algo, stream);
+}
+
+// Pipelined all-reduce, step 1: reduce-scatter + scale + statistics (sumsq_dev / found_inf_dev describe the WHOLE bucket on
+// every rank afterwards). The bucket is `chunks` chunks of chunk = world * sub floats (det_pipe_chunk_floats); rank r's reduced
+// share of chunk c, [c * chunk + r * sub, + sub), stays in its own bucket; the rest of the bucket still holds local partial
+// sums until det_allgather_send(c) of every rank has landed.
+extern "C" long long det_pipe_chunk_floats(long long n_f32, int world, int chunks) {
+  return det::pipe_geom(n_f32, world, chunks).chunk4 * 4;
+}
+
+extern "C" int det_reduce_scatter_stats(void* const* peer_bufs, void* const* peer_flags, void* mc_ptr, void* epoch_dev,
+                                        long long n_f32, int rank, int world, int chunks, float scale, const float* scale_dev,
+                                        float* sumsq_dev, int* found_inf_dev, int max_blocks, cudaStream_t stream) {
+  using namespace det;
+  if (n_f32 <= 0) return 0;
+  DET_REQUIRE(n_f32 % 4 == 0, "bucket length must be a multiple of 4 floats");
+  DET_REQUIRE(chunks >= 1 && chunks <= PIPE_MAX_CHUNKS, "chunks must be in [1, 8]");
+  AllreduceArgs a;
+  int rc = fill_table(a.t, peer_bufs, peer_flags, world);
+  if (rc) return rc;
+  a.mc_ptr = reinterpret_cast<float*>(mc_ptr);
+  a.epoch = reinterpret_cast<uint32_t*>(epoch_dev);
+  a.n = n_f32; a.rank = rank; a.world = world; a.scale = scale; a.scale_dev = scale_dev;
+  a.sumsq = sumsq_dev; a.found_inf = found_inf_dev;
+  const bool mc = mc_ptr != nullptr && world > 1;
+  const PipeGeom g = pipe_geom(n_f32, world, chunks);
+  const long long per_block = static_cast<long long>(AR_THREADS) * (mc ? AR_UNROLL_MC : AR_UNROLL_P2P);
+  int blocks = static_cast<int>(std::min<long long>((g.sub4 + per_block - 1) / per_block, std::min(sm_count(), COMM_MAX_BLOCKS)));
+  blocks = std::max(1, std::min(blocks, max_blocks > 0 ? max_blocks : 16));
+  if (mc) reduce_scatter_stats_kernel<true><<<blocks, AR_THREADS, 0, stream>>>(a, chunks);
+  else reduce_scatter_stats_kernel<false><<<blocks, AR_THREADS, 0, stream>>>(a, chunks);
+  DET_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Step 2, every rank, c = 0 .. chunks-1 in order: push this rank's reduced share of chunk c into every rank's bucket, then
+// raise its flag for that chunk there.
+extern "C" int det_allgather_send(void* const* peer_bufs, void* const* peer_flags, void* mc_ptr, void* epoch_dev,
+                                  long long n_f32, int rank, int world, int chunks, int c, int max_blocks, cudaStream_t stream) {
+  using namespace det;
+  if (n_f32 <= 0) return 0;
+  DET_REQUIRE(chunks >= 1 && chunks <= PIPE_MAX_CHUNKS && c >= 0 && c < chunks, "chunk index out of range");
+  AllreduceArgs a;
+  int rc = fill_table(a.t, peer_bufs, peer_flags, world);
+  if (rc) return rc;
+  a.mc_ptr = reinterpret_cast<float*>(mc_ptr);
+  a.epoch = reinterpret_cast<uint32_t*>(epoch_dev);
+  a.n = n_f32; a.rank = rank; a.world = world; a.scale = 1.0f; a.scale_dev = nullptr; a.sumsq = nullptr; a.found_inf = nullptr;
+  const bool mc = mc_ptr != nullptr && world > 1;
+  const PipeGeom g = pipe_geom(n_f32, world, chunks);
+  const long long per_block = static_cast<long long>(AR_THREADS) * 8;
+  int blocks = static_cast<int>(std::min<long long>((g.sub4 + per_block - 1) / per_block, std::min(sm_count(), COMM_MAX_BLOCKS)));
+  blocks = std::max(1, std::min(blocks, max_blocks > 0 ? max_blocks : 16));
+  if (mc) allgather_send_kernel<true><<<blocks, AR_THREADS, 0, stream>>>(a, chunks, c);
+  else allgather_send_kernel<false><<<blocks, AR_THREADS, 0, stream>>>(a, chunks, c);
+  DET_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+// Step 3, every rank: hold `stream` until every OTHER rank's share of chunk c has landed in this rank's bucket (one warp
+// spins; put it in front of the kernel that reads the chunk; this rank's own share needs a stream dependency on its send).
+extern "C" int det_wait_chunk(void* local_flags, int c, int rank, int world, cudaStream_t stream) {
+  using namespace det;
+  DET_REQUIRE(c >= 0 && c < PIPE_MAX_CHUNKS, "chunk index out of range");
+  wait_chunk_kernel<<<1, 32, 0, stream>>>(reinterpret_cast<const uint32_t*>(local_flags), c, rank, world);
+  DET_CHECK_CUDA(cudaGetLastError());
+  return 0;
 }
 
 // bf16-wire all-reduce of a fp32 bucket: grad (local fp32, n elements, n % 8 == 0), peer_wire = every rank's bf16 staging

@@ -76,6 +76,10 @@ _SIGNATURES = {
                                 c_void_p, c_int, c_int, c_int, c_void_p],
     "det_fused_allreduce_bf16wire": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_int, c_int, c_float, c_void_p,
                                      c_void_p, c_void_p, c_int, c_void_p],
+    "det_reduce_scatter_stats": [c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_int, c_int, c_int, c_float, c_void_p, c_void_p,
+                                 c_void_p, c_int, c_void_p],
+    "det_allgather_send": [c_void_p, c_void_p, c_void_p, c_void_p, c_ll, c_int, c_int, c_int, c_int, c_int, c_void_p],
+    "det_wait_chunk": [c_void_p, c_int, c_int, c_int, c_void_p],
     "det_p2p_broadcast": [c_void_p, c_void_p, c_void_p, c_ll, c_int, c_int, c_int, c_void_p],
     "det_metric_allreduce": [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p],
     "det_vmm_multicast_supported": [c_int, ctypes.POINTER(c_int)],
@@ -127,6 +131,9 @@ def load(build_if_missing: bool = True) -> ctypes.CDLL:
     lib.det_kernels_abi_version.restype = c_int
     lib.det_comm_flag_bytes.restype = c_ll
     lib.det_comm_epoch_bytes.restype = c_ll
+    if hasattr(lib, "det_pipe_chunk_floats"):
+        lib.det_pipe_chunk_floats.restype = c_ll
+        lib.det_pipe_chunk_floats.argtypes = [c_ll, c_int, c_int]
     for name, sig in _SIGNATURES.items():
         try:
             fn = getattr(lib, name)

@@ -17,7 +17,7 @@ from __future__ import annotations
 import ctypes
 import os
 import pickle
-from typing import Any, Dict, List, Optional, Sequence
+from typing import Any, Dict, List, Optional, Sequence, Tuple
 
 import torch
 
@@ -51,6 +51,9 @@ class Communicator:
         """Sum ``flat_g`` over ranks and multiply by ``scale`` in place. Returns True when the scale (and the
         optional sumsq / found_inf side outputs) were applied by the collective itself."""
         return False
+
+    def pipeline_plan(self, flat_g: torch.Tensor) -> Optional[List[Tuple[int, int]]]:
+        return None
 
     def allreduce_tensors(self, tensors: Sequence[torch.Tensor], scale: float) -> None:
         if scale != 1.0:
@@ -271,6 +274,45 @@ class TorchDistCommunicator(Communicator):
         # sumsq_dev / found_inf_dev now describe the WHOLE bucket on every rank: the kernel's last block exchanges the
         # per-rank partials through the flag region (no second launch)
         return True
+
+    # ---- pipelined all-reduce: reduce-scatter now, all-gather chunk by chunk under the optimizer -----------------------
+    PIPE_CHUNKS = 4
+
+    def pipeline_plan(self, flat_g: torch.Tensor) -> Optional[List[Tuple[int, int]]]:
+        """Chunk bounds (elements) when the bucket qualifies for the pipelined form, else None. It pays where the in-switch
+        reduction is the all-reduce path (more than two ranks, multicast mapping) and the bucket is large."""
+        if not self.p2p or self.size < 2 or self.compress_gradients or os.environ.get("DET_AR_PIPELINE", "1") == "0":
+            return None
+        if self.size == 2 and os.environ.get("DET_AR_PIPELINE") != "1":
+            return None          # two ranks: the TMA bulk all-reduce is already shorter than its reduce-scatter half here
+        region = self._region_of(flat_g)
+        n = flat_g.numel()
+        if region is None or n % 4 != 0 or n < int(os.environ.get("DET_AR_PIPELINE_MIN", str(1 << 22))):
+            return None
+        if not (region.multicast_ptr and os.environ.get("DET_DISABLE_NVLS") != "1") and os.environ.get("DET_AR_PIPELINE") != "1":
+            return None
+        chunks = int(os.environ.get("DET_AR_PIPELINE_CHUNKS", str(self.PIPE_CHUNKS)))
+        chunk = int(_native.load().det_pipe_chunk_floats(n, self.size, chunks))
+        return [(min(c * chunk, n), min((c + 1) * chunk, n)) for c in range(chunks)]
+
+    def _pipe_args(self, flat_g: torch.Tensor):
+        region = self._region_of(flat_g)
+        off = flat_g.data_ptr() - region.base
+        mc = region.multicast_ptr + off if (region.multicast_ptr and os.environ.get("DET_DISABLE_NVLS") != "1") else None
+        return region.table(off), self._flags.table(), (ctypes.c_void_p(mc) if mc else None), ctypes.c_void_p(self._epoch.data_ptr())
+
+    def reduce_scatter_stats(self, flat_g: torch.Tensor, chunks: int, scale: float, scale_dev=None, sumsq_dev=None,
+                             found_inf_dev=None) -> None:
+        bufs, flags, mc, ep = self._pipe_args(flat_g)
+        _native.call("det_reduce_scatter_stats", bufs, flags, mc, ep, flat_g.numel(), self.rank, self.size, int(chunks), float(scale),
+                     F._p(scale_dev), F._p(sumsq_dev), F._p(found_inf_dev), 0, F._stream())
+
+    def allgather_send(self, flat_g: torch.Tensor, chunks: int, c: int) -> None:
+        bufs, flags, mc, ep = self._pipe_args(flat_g)
+        _native.call("det_allgather_send", bufs, flags, mc, ep, flat_g.numel(), self.rank, self.size, int(chunks), int(c), 0, F._stream())
+
+    def wait_chunk(self, c: int) -> None:
+        _native.call("det_wait_chunk", ctypes.c_void_p(self._flags.local.data_ptr()), int(c), self.rank, self.size, F._stream())
 
     def allreduce_tensors(self, tensors, scale) -> None:
         for t in tensors:

@@ -100,6 +100,9 @@ class FusedOptimizer(torch.optim.Optimizer):
         self.found_inf_dev: Optional[torch.Tensor] = None
         self._scratch: Optional[torch.Tensor] = None
         self.last_grad_norm_dev: Optional[torch.Tensor] = None
+        # gradient bucket address -> (slice bounds per owner rank, callable run before a slice is updated); set by the trial
+        # context for the duration of one step when that bucket's all-gather is pipelined with the update
+        self.slice_pipelines: Dict[int, Any] = {}
         if self.fused:
             dev = params[0].device
             if alloc is None:
@@ -183,8 +186,20 @@ class FusedOptimizer(torch.optim.Optimizer):
             self.last_grad_norm_dev = sc[3:4]
         for grp in self.groups:
             grp.hyper_dev.copy_(grp.hyper_host, non_blocking=True)
-            F.fused_optimizer_step(self.variant, grp.flat_p, grp.flat_g, grp.flat_s1,
-                                   grp.flat_s2, grp.flat_shadow, grp.hyper_dev, scale, self.found_inf_dev, zero_grad)
+            pipe = self.slice_pipelines.get(grp.flat_g.data_ptr())
+            if pipe is None:
+                F.fused_optimizer_step(self.variant, grp.flat_p, grp.flat_g, grp.flat_s1,
+                                       grp.flat_s2, grp.flat_shadow, grp.hyper_dev, scale, self.found_inf_dev, zero_grad)
+                continue
+            # the bucket's all-gather is still arriving, one owner's slice at a time (parallel/comm.py, pipelined
+            # all-reduce): update each slice as soon as it is here, under the transfer of the next one
+            bounds, before_chunk = pipe
+            for owner, (lo, hi) in enumerate(bounds):
+                before_chunk(owner)
+                if hi > lo:
+                    cut = lambda t: None if t is None else t[lo:hi]      # noqa: E731
+                    F.fused_optimizer_step(self.variant, grp.flat_p[lo:hi], grp.flat_g[lo:hi], cut(grp.flat_s1), cut(grp.flat_s2),
+                                           cut(grp.flat_shadow), grp.hyper_dev, scale, self.found_inf_dev, zero_grad)
 
     @torch.no_grad()
     def step(self, closure=None, max_grad_norm: float = 0.0, zero_grad: bool = False, sumsq_ready: bool = False):  # type: ignore[override]

@@ -128,6 +128,7 @@ class PyTorchTrialContext(TrialContext):
         self._scaler_divisor_applied = False
         self.experimental = _Experimental(self)
         self._overlap: Any = None     # parallel.overlap.GradOverlap when enabled
+        self._ag_stream: Any = None   # side stream of the pipelined all-gather (created on first use)
         self.warned_types: set = set()
 
         opt_cfg = env.experiment_config.get_optimizations_config()
@@ -370,10 +371,20 @@ class PyTorchTrialContext(TrialContext):
         else:
             if want_sumsq:
                 opt._scratch[0:1].zero_()
+            pipelines: Dict[int, Any] = {}
             for g in opt.grad_buckets():
+                bounds = self.comm.pipeline_plan(g) if (slow_clip is None and auto_zero) else None
+                if bounds is not None:
+                    # reduce-scatter + statistics now; the all-gather travels slice by slice on a side stream while the
+                    # optimizer updates the slices that have already landed (csrc/comm/fused_allreduce.cu, "Pipelined form")
+                    self.comm.reduce_scatter_stats(g, len(bounds), 1.0 / divisor, scale_dev=inv_scale_dev, found_inf_dev=found_inf,
+                                                   sumsq_dev=opt._scratch[0:1] if want_sumsq else None)
+                    pipelines[g.data_ptr()] = (bounds, self._start_allgather(g, len(bounds)))
+                    continue
                 applied = self.comm.allreduce_grad_bucket(g, 1.0 / divisor, scale_dev=inv_scale_dev, found_inf_dev=found_inf,
                                                           sumsq_dev=opt._scratch[0:1] if want_sumsq else None)
                 applied_all = applied_all and applied
+            opt.slice_pipelines = pipelines
         sumsq_ready = bool(want_sumsq and applied_all)
         if applied_all and self.comm.size > 1:
             opt.grad_scale_dev.fill_(1.0)
@@ -400,11 +411,37 @@ class PyTorchTrialContext(TrialContext):
                 F.grad_sumsq_finite(g, opt.grad_scale_dev, sc[0:1], found_inf)
             if self.comm.size > 1:
                 self.comm.allreduce_max_int(found_inf)
-        opt.step(max_grad_norm=max_norm, zero_grad=auto_zero, sumsq_ready=sumsq_ready)
+        try:
+            opt.step(max_grad_norm=max_norm, zero_grad=auto_zero, sumsq_ready=sumsq_ready)
+        finally:
+            opt.slice_pipelines = {}
         if scaler is not None:
             from ..ops import functional as F
 
             F.loss_scale_update(scaler.state, opt.found_inf_dev, scaler.growth, scaler.backoff, scaler.interval, 1.0)
+
+    def _start_allgather(self, g: torch.Tensor, chunks: int) -> Callable[[int], None]:
+        """Launch this rank's sends of a bucket's pipelined all-gather on the side stream (chunk 0, 1, ... back to back) and
+        return what the optimizer runs in front of each chunk's update: a stream dependency on the own send of that chunk
+        (which reads the chunk) plus a one-warp wait for the other ranks' shares of it."""
+        comm = self.comm
+        main = torch.cuda.current_stream(self.device)
+        if self._ag_stream is None:
+            self._ag_stream = torch.cuda.Stream(self.device, priority=-1)
+        side = self._ag_stream
+        side.wait_stream(main)                 # the reduce-scatter (and everything before it) is in front of the sends
+        sent = []
+        with torch.cuda.stream(side):
+            for c in range(chunks):
+                comm.allgather_send(g, chunks, c)
+                ev = torch.cuda.Event()
+                ev.record(side)
+                sent.append(ev)
+
+        def before_chunk(c: int) -> None:
+            main.wait_event(sent[c])           # the last one also joins the side stream back (ends its capture in a graph)
+            comm.wait_chunk(c)
+        return before_chunk
 
     def _step_plain(self, opt: torch.optim.Optimizer, divisor: float, slow_clip, auto_zero: bool) -> None:
         params = [p for grp in opt.param_groups for p in grp["params"] if p.grad is not None]

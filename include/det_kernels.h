@@ -135,6 +135,18 @@ int det_fused_allreduce_cta(void* const* peer_bufs, void* const* peer_flags, voi
                             long long n_f32, int rank, int world, float scale, const float* scale_dev,
                             float* sumsq_dev, int* found_inf_dev, int max_blocks, int threads, int algo,
                             cudaStream_t stream);
+/* Pipelined all-reduce (all-gather under the optimizer). The bucket is `chunks` (<= 8) chunks of det_pipe_chunk_floats()
+ * floats, each chunk `world` equal shares, rank r owning share r of every chunk. 1: reduce-scatter + scale + whole-bucket
+ * statistics, the reduced shares stay in the owner's bucket. 2 (every rank, c = 0 .. chunks-1 in order): push the own share of
+ * chunk c into every rank's bucket and raise its flag there. 3 (every rank): hold the stream until every OTHER rank's share of
+ * chunk c has landed here — one warp spins; the working kernels never wait. */
+long long det_pipe_chunk_floats(long long n_f32, int world, int chunks);
+int det_reduce_scatter_stats(void* const* peer_bufs, void* const* peer_flags, void* mc_ptr, void* epoch_dev, long long n_f32,
+                             int rank, int world, int chunks, float scale, const float* scale_dev, float* sumsq_dev,
+                             int* found_inf_dev, int max_blocks, cudaStream_t stream);
+int det_allgather_send(void* const* peer_bufs, void* const* peer_flags, void* mc_ptr, void* epoch_dev, long long n_f32, int rank,
+                       int world, int chunks, int c, int max_blocks, cudaStream_t stream);
+int det_wait_chunk(void* local_flags, int c, int rank, int world, cudaStream_t stream);
 /* bf16 on the wire (optimizations.gradient_compression): pack `grad` (local fp32, n % 8 == 0) into this rank's bf16 staging
  * buffer, all-reduce the staging buffers (multimem bf16x2 with fp32 accumulation when mc_wire is given, 16-byte peer loads
  * summed in fp32 otherwise; scale, non-finite test and grad-norm partial as above), unpack into `grad`. */

@@ -102,6 +102,49 @@ def main():
             if rank == 0:
                 print(f"{'PASS' if good else 'FAIL'} allreduce[bf16wire/{label}] found_inf flags={flags}", flush=True)
         os.environ.pop("DET_DISABLE_NVLS", None)
+    # pipelined form: reduce-scatter + statistics, then the all-gather slice by slice in rank order (side stream), with the
+    # consumer waiting per slice — here the "optimizer" is a scale-by-2 of each slice as it lands
+    os.environ["DET_AR_PIPELINE"] = "1"
+    for label, env in (("nvls", None), ("lsu", "1")):
+        if env:
+            os.environ["DET_DISABLE_NVLS"] = env
+        for rep in range(3):
+            n = 25 * (1 << 20) + 64
+            torch.manual_seed(500 + rank + 10 * rep)
+            g = comm.alloc(n, torch.float32, "grad", dev)
+            g.copy_(torch.randn(n, device=dev))
+            ref = g.clone()
+            dist.all_reduce(ref)
+            ref *= 0.125
+            bounds = comm.pipeline_plan(g)
+            assert bounds is not None, "bucket does not qualify for the pipelined form"
+            C = len(bounds)
+            sumsq = torch.zeros(1, device=dev)
+            finf = torch.zeros(1, dtype=torch.int32, device=dev)
+            main = torch.cuda.current_stream(dev)
+            side = torch.cuda.Stream(dev, priority=-1)
+            comm.reduce_scatter_stats(g, C, 0.125, sumsq_dev=sumsq, found_inf_dev=finf)
+            side.wait_stream(main)
+            sent = []
+            with torch.cuda.stream(side):
+                for c in range(C):
+                    comm.allgather_send(g, C, c)
+                    ev = torch.cuda.Event()
+                    ev.record(side)
+                    sent.append(ev)
+            for c, (lo, hi) in enumerate(bounds):
+                main.wait_event(sent[c])
+                comm.wait_chunk(c)
+                g[lo:hi].mul_(2.0)
+            torch.cuda.synchronize()
+            err = ((g - 2.0 * ref).abs().max() / ref.abs().max()).item()
+            ss_ref = ref.double().pow(2).sum().item()
+            ss_err = abs(sumsq.item() - ss_ref) / ss_ref
+            good = err < 1e-5 and ss_err < 1e-3 and finf.item() == 0
+            ok &= good
+            if rank == 0:
+                print(f"{'PASS' if good else 'FAIL'} pipelined[{label}] rep={rep} err={err:.2e} sumsq_err={ss_err:.2e}", flush=True)
+        os.environ.pop("DET_DISABLE_NVLS", None)
     # broadcast
     p = comm.alloc(1 << 20, torch.float32, "param", dev)
     p.fill_(float(rank + 1))
@@ -166,6 +209,24 @@ def main():
         for mb in ((0,) if algo != 3 else (24, 48, 64, 96, 128, 148)):
             t = timeit(lambda: comm.allreduce_grad_bucket(g, 1.0 / world, sumsq_dev=sumsq, found_inf_dev=finf, algo=algo, max_blocks=mb), iters=8)
             by_algo[f"{algo_name}_b{mb}"] = {"ms": round(t, 3), "busbw_gbs": round(bytes_moved / t / 1e6, 1)}
+    side = torch.cuda.Stream(dev, priority=-1)
+
+    def pipelined():
+        main = torch.cuda.current_stream(dev)
+        C = comm.PIPE_CHUNKS
+        comm.reduce_scatter_stats(g, C, 1.0 / world, sumsq_dev=sumsq, found_inf_dev=finf)
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            for c in range(C):
+                comm.allgather_send(g, C, c)
+        main.wait_stream(side)
+        for c in range(C):
+            comm.wait_chunk(c)
+
+    t = timeit(pipelined, iters=8)
+    by_algo["pipelined_rs_then_ag_in_chunks"] = {"ms": round(t, 3), "busbw_gbs": round(bytes_moved / t / 1e6, 1)}
+    t = timeit(lambda: comm.reduce_scatter_stats(g, comm.PIPE_CHUNKS, 1.0 / world, sumsq_dev=sumsq, found_inf_dev=finf), iters=8)
+    by_algo["reduce_scatter_stats_only"] = {"ms": round(t, 3)}
     comm.compress_gradients = True
     t = timeit(lambda: comm.allreduce_grad_bucket(g, 1.0 / world, sumsq_dev=sumsq, found_inf_dev=finf), iters=8)
     comm.compress_gradients = False

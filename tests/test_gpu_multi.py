@@ -52,3 +52,16 @@ def test_overlapped_allreduce_matches_step_time_allreduce(tmp_path):
     assert all(abs(x - y) <= 0.05 * max(abs(x), 0.05) for x, y in zip(lp, lo_)), (lp, lo_)
     close = np.isclose(np.array(a), np.array(plain["params_by_rank"][0]), rtol=2e-2, atol=2e-3)
     assert close.mean() > 0.99, f"only {close.mean():.4f} of the parameters agree"
+
+
+def test_pipelined_allgather_under_the_optimizer_keeps_replicas_identical(tmp_path):
+    """Reduce-scatter + statistics first, all-gather slice by slice on a side stream while the optimizer updates the
+    slices that have landed (forced on at two ranks and for a small bucket): replicas stay identical and training
+    tracks the fused all-reduce run."""
+    _need_two()
+    plain = run_ranks(2, "mnist_gpu", tmp_path, timeout=600)
+    piped = run_ranks(2, "mnist_gpu", tmp_path, {"DET_AR_PIPELINE": "1", "DET_AR_PIPELINE_MIN": "1024"}, timeout=600)
+    a, b = piped["params_by_rank"]
+    assert a == b, "replicas diverged with the pipelined all-gather"
+    lp, lq = [m["loss"] for m in plain["training"]], [m["loss"] for m in piped["training"]]
+    assert all(abs(x - y) <= 0.05 * max(abs(x), 0.05) for x, y in zip(lp, lq)), (lp, lq)
