@@ -281,10 +281,12 @@ class TorchDistCommunicator(Communicator):
     def pipeline_plan(self, flat_g: torch.Tensor) -> Optional[List[Tuple[int, int]]]:
         """Chunk bounds (elements) when the bucket qualifies for the pipelined form, else None. It pays where the in-switch
         reduction is the all-reduce path (more than two ranks, multicast mapping) and the bucket is large."""
-        if not self.p2p or self.size < 2 or self.compress_gradients or os.environ.get("DET_AR_PIPELINE", "1") == "0":
+        # Opt-in (DET_AR_PIPELINE=1). Measured on 8 GPUs (profiles/comm_timing_w8_r2.json, bench A/B 19.83 ms fused vs 19.86-19.91
+        # pipelined): split in two, the halves lose the full-duplex overlap they have inside the fused kernel (reduce-scatter
+        # alone 0.69 ms, both halves 1.41 ms against 1.02 ms fused), which eats what hiding the all-gather under the 0.61 ms
+        # optimizer saves. Two ranks: the TMA bulk all-reduce is already shorter than the reduce-scatter half.
+        if not self.p2p or self.size < 2 or self.compress_gradients or os.environ.get("DET_AR_PIPELINE", "0") != "1":
             return None
-        if self.size == 2 and os.environ.get("DET_AR_PIPELINE") != "1":
-            return None          # two ranks: the TMA bulk all-reduce is already shorter than its reduce-scatter half here
         region = self._region_of(flat_g)
         n = flat_g.numel()
         if region is None or n % 4 != 0 or n < int(os.environ.get("DET_AR_PIPELINE_MIN", str(1 << 22))):
