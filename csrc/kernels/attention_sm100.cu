@@ -337,6 +337,143 @@ attention_fwd_persistent_kernel(const __grid_constant__ CUtensorMap tma_qkv, con
 }
 
 // ------------------------------------------------------------------------------------------------
+// Forward, dense form: FOUR CTAs per SM, one (batch, head) item each. An item is a chain of short dependent steps
+// (TMA -> QK^T -> softmax -> PV -> store) that cannot fill an SM by itself; what fills it is several items side by
+// side. To fit four: 48 KB of tiles (P overwrites the Q and K tiles, which are dead once S sits in TMEM), 128 TMEM
+// columns (O reuses S's columns, dead once P is in shared memory) and <= 64 registers — the softmax walks its 64 keys
+// in two 32-column reads of S, twice (max, then exp / sum / pack), instead of holding 64 scores, and P is stored
+// un-normalised: O = P_un V, and each output row is scaled by 1/sum (and the dropout scale) on its way out.
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t ATT_FWD_DENSE_SMEM = 3 * ATT_TILE + 1024 + 64 + ATT_FWD_RED;
+
+__global__ void __launch_bounds__(ATT_FWD_THREADS, 4)
+attention_fwd_dense_kernel(const __grid_constant__ CUtensorMap tma_qkv, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sQ = smem;
+  uint8_t* sK = smem + ATT_TILE;
+  uint8_t* sV = smem + 2 * ATT_TILE;
+  uint8_t* sP = smem;                 // 2 chunks of [128 q][64 keys] over Q | K
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 3 * ATT_TILE);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+  float* red_max = reinterpret_cast<float*>(smem + 3 * ATT_TILE + 64);
+  float* red_sum = red_max + 2 * ATT_S;
+  float* smask = red_sum + 2 * ATT_S;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b = blockIdx.x / p.H, h = blockIdx.x % p.H;
+  const uint32_t tma_bar = ptx::smem_u32(&bars[0]);
+  const uint32_t mma_bar = ptx::smem_u32(&bars[1]);
+
+  if (tid < ATT_S) smask[tid] = tid < p.S ? (p.mask != nullptr ? __ldg(p.mask + b * p.S + tid) * LOG2E : 0.0f) : -INFINITY;
+  if (tid == 0) {
+    ptx::tma_prefetch_desc(&tma_qkv);
+    ptx::mbar_init(tma_bar, 1);
+    ptx::mbar_init(mma_bar, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 0) ptx::tmem_alloc(ptx::smem_u32(tmem_slot), 128);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tS = *tmem_slot;     // 128 columns; O takes the first 64 once S has been consumed
+
+  if (tid == 0) {
+    ptx::mbar_expect_tx(tma_bar, 3 * ATT_TILE);
+    const int row0 = b * p.S;
+    ptx::tma_load_2d(ptx::smem_u32(sQ), &tma_qkv, tma_bar, h * ATT_D, row0);
+    ptx::tma_load_2d(ptx::smem_u32(sK), &tma_qkv, tma_bar, p.hidden + h * ATT_D, row0);
+    ptx::tma_load_2d(ptx::smem_u32(sV), &tma_qkv, tma_bar, 2 * p.hidden + h * ATT_D, row0);
+    ptx::mbar_wait(tma_bar, 0);
+    ptx::tc_fence_after();
+    constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(128, 128, 0, 0);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      ptx::umma_bf16_ss(tS, ptx::make_smem_desc_sw128(ptx::smem_u32(sQ) + k * 32, 16, 1024),
+                        ptx::make_smem_desc_sw128(ptx::smem_u32(sK) + k * 32, 16, 1024), idesc, k > 0);
+    ptx::umma_commit(mma_bar);
+  }
+  ptx::mbar_wait(mma_bar, 0);
+  ptx::tc_fence_after();
+
+  const int q = (warp & 3) * 32 + lane;
+  const int cg = warp >> 2;
+  const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
+  const float sc = p.scale * LOG2E;
+  // ---- pass 1: row maximum over this thread's 64 keys, 32 at a time
+  float mx = -INFINITY;
+#pragma unroll 1
+  for (int c = 0; c < 2; ++c) {
+    float s[32];
+    ptx::tmem_ld_32x32b_x32(tS + lane_base + cg * 64 + c * 32, s);
+    ptx::tmem_ld_wait();
+#pragma unroll
+    for (int e = 0; e < 32; ++e) mx = fmaxf(mx, fmaf(s[e], sc, smask[cg * 64 + c * 32 + e]));
+  }
+  red_max[cg * ATT_S + q] = mx;
+  __syncthreads();
+  mx = fmaxf(red_max[q], red_max[ATT_S + q]);
+  // ---- pass 2: exp, row sum, dropout, un-normalised P -> shared memory (over Q | K: S is complete, they are dead)
+  const uint32_t dseed = dropout_effective_seed(p.drop_seed, p.drop_seed_dev);
+  const uint32_t didx0 = ((static_cast<uint32_t>(b) * p.H + h) * p.S + q) * p.S + cg * 64;
+  float sum = 0.0f;
+#pragma unroll 1
+  for (int c = 0; c < 2; ++c) {
+    float s[32];
+    ptx::tmem_ld_32x32b_x32(tS + lane_base + cg * 64 + c * 32, s);
+    ptx::tmem_ld_wait();
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      float v[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int k = c * 32 + u * 8 + e;
+        float pv = fast_exp2(fmaf(s[u * 8 + e], sc, smask[cg * 64 + k]) - mx);
+        sum += pv;                      // the normaliser counts dropped entries too (dropout acts on probabilities)
+        if (p.drop_threshold != 0u && !dropout_keep(dseed, didx0 + k, p.drop_threshold)) pv = 0.0f;
+        v[e] = pv;
+      }
+      *reinterpret_cast<uint4*>(sP + cg * ATT_TILE + ptx::sw128_offset(q, c * 4 + u)) = pack8_bf16(v);
+    }
+  }
+  red_sum[cg * ATT_S + q] = sum;
+  ptx::fence_proxy_async_smem();
+  ptx::tc_fence_before();
+  __syncthreads();
+  sum = red_sum[q] + red_sum[ATT_S + q];
+  if (cg == 0 && q < p.S) p.lse[(static_cast<long long>(b) * p.H + h) * p.S + q] = (mx + log2f(sum)) * (1.0f / LOG2E);
+
+  if (tid == 0) {
+    ptx::tc_fence_after();
+    constexpr uint32_t idesc = ptx::make_idesc_bf16_f32(128, 64, 0, 1);
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      ptx::umma_bf16_ss(tS, ptx::make_smem_desc_sw128(ptx::smem_u32(sP) + (k >> 2) * ATT_TILE + (k & 3) * 32, 16, 1024),
+                        ptx::make_smem_desc_sw128(ptx::smem_u32(sV) + k * 2048, 8192, 1024), idesc, k > 0);
+    ptx::umma_commit(mma_bar);
+  }
+  ptx::mbar_wait(mma_bar, 1);
+  ptx::tc_fence_after();
+  float o[32];
+  ptx::tmem_ld_32x32b_x32(tS + lane_base + cg * 32, o);
+  ptx::tmem_ld_wait();
+  const float row_scale = (p.drop_threshold != 0u ? p.drop_scale : 1.0f) / sum;
+  if (q < p.S) {
+#pragma unroll
+    for (int e = 0; e < 32; ++e) o[e] *= row_scale;
+    uint4* dst = reinterpret_cast<uint4*>(p.out + (static_cast<long long>(b) * p.S + q) * p.hidden + h * ATT_D + cg * 32);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) dst[u] = pack8_bf16(o + 8 * u);
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tS, 128);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Backward: 512 threads = 4 lane quarters x 4 column groups (32 keys each); 1 CTA per SM.
 // ------------------------------------------------------------------------------------------------
 constexpr int ATT_BWD_THREADS = 512;
@@ -757,8 +894,29 @@ extern "C" int det_attention_fwd(const void* qkv, const float* mask, void* ctx, 
     DET_CHECK_CUDA(cudaFuncSetAttribute(attention_fwd_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_FWD_SMEM));
     attr_set[dev] = true;
   }
+  // DET_ATTN_FWD: "persistent" (default: two CTAs per SM walking items with the next item's tiles prefetched), "dense"
+  // (four one-item CTAs per SM), "oneshot". Dense and persistent measure the same (19.3-20.0 us at batch 48 x 12 heads,
+  // BERT step 18.6 ms either way; profiles/ncu_attention128_r2.csv): with ~4 items per SM the kernel is one item's chain
+  // of load -> QK^T -> softmax -> PV -> store, and the softmax's ~1,300 instructions per warp are issue-bound
+  // (38 % issue-active) behind a load phase every CTA enters at the same time.
+  static const int mode = [] {
+    const char* e = getenv("DET_ATTN_FWD");
+    if (e != nullptr && e[0] == 'd') return 0;
+    if (e != nullptr && e[0] == 'o') return 2;
+    return 1;
+  }();
+  if (mode == 0) {
+    static bool dense_attr[64] = {false};
+    if (dev < 64 && !dense_attr[dev]) {
+      DET_CHECK_CUDA(cudaFuncSetAttribute(attention_fwd_dense_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_FWD_DENSE_SMEM));
+      dense_attr[dev] = true;
+    }
+    attention_fwd_dense_kernel<<<B * H, ATT_FWD_THREADS, ATT_FWD_DENSE_SMEM, stream>>>(tq, p);
+    DET_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
   static const int one_shot = [] { const char* e = getenv("DET_ATTN_ONESHOT"); return e != nullptr && e[0] == '1' ? 1 : 0; }();
-  if (!one_shot && B * H > 2 * sm_count()) {
+  if (mode != 2 && !one_shot && B * H > 2 * sm_count()) {
     attention_fwd_persistent_kernel<<<2 * sm_count(), ATT_FWD_THREADS, ATT_FWD_SMEM, stream>>>(tq, p);
     DET_CHECK_CUDA(cudaGetLastError());
     return 0;
