@@ -228,6 +228,12 @@ class ActorSystem {
     if (trace_) { fputs((e.dump() + "\n").c_str(), trace_); fflush(trace_); }
   }
 
+ public:
+  // Test knob (det-selftest): a worker that has just given a cell up sleeps this long before it would look at the cell
+  // again — which it must not do. 0 in production.
+  static inline std::atomic<int> test_release_delay_us{0};
+
+ private:
   std::mutex trace_mu_;
   FILE* trace_ = nullptr;
   std::chrono::steady_clock::time_point trace_origin_;
@@ -281,11 +287,12 @@ inline void ActorSystem::worker() {
       run_queue_.pop_front();
     }
     // drain a bounded batch so one chatty actor cannot starve the rest
+    bool released = false;   // this worker gave the cell up (cleared scheduled_): from then on tell() owns its scheduling
     for (int n = 0; n < 64; ++n) {
       Message msg;
       {
         std::lock_guard<std::mutex> g(cell->mu_);
-        if (cell->mailbox_.empty()) { cell->scheduled_ = false; break; }
+        if (cell->mailbox_.empty()) { cell->scheduled_ = false; released = true; break; }
         msg = std::move(cell->mailbox_.front());
         cell->mailbox_.pop_front();
       }
@@ -320,8 +327,16 @@ inline void ActorSystem::worker() {
         break;
       }
     }
+    // Re-queue only a cell this worker still owns (batch limit reached, stop, failure). After `released` a concurrent
+    // tell() may already have set scheduled_ and queued the cell — touching it here again would put it on the run queue
+    // twice and let two workers run the same actor at once (found by ThreadSanitizer under the chaos search: two threads in
+    // one TrialActor::receive; it showed up as a rare "double free or corruption" of the master).
+    if (released) {
+      const int d = test_release_delay_us.load(std::memory_order_relaxed);    // selftest only: holds the window open
+      if (d > 0) std::this_thread::sleep_for(std::chrono::microseconds(d));
+    }
     bool again = false;
-    {
+    if (!released) {
       std::lock_guard<std::mutex> g(cell->mu_);
       if (!cell->mailbox_.empty() && !cell->stopped()) { cell->scheduled_ = true; again = true; }
       else cell->scheduled_ = false;

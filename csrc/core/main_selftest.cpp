@@ -39,6 +39,56 @@ class Counter : public Actor {
   int n_children_ = 0;
 };
 
+// An actor must never be inside receive() on two threads. Senders that let the mailbox run empty between messages hit the
+// window where a worker has just given the cell up while a tell() re-queues it (the double-scheduling bug fixed in
+// ActorSystem::worker: a cell queued twice ran on two workers at once).
+class Serial : public Actor {
+ public:
+  void receive(Context&, const Message& msg) override {
+    if (msg.type == "work") {
+      if (busy_.exchange(true)) ++overlaps_;
+      for (volatile int i = 0; i < 3000; ++i) {}      // long enough for a second worker to arrive while this one is inside
+      ++seen_;
+      busy_ = false;
+    } else if (msg.type == "report") {
+      Json r = Json::object();
+      r["overlaps"] = static_cast<long long>(overlaps_.load());
+      r["seen"] = seen_;
+      msg.respond(r);
+    }
+  }
+ private:
+  std::atomic<bool> busy_{false};
+  std::atomic<long long> overlaps_{0};
+  long long seen_ = 0;
+};
+
+static void test_actor_is_never_run_concurrently() {
+  ActorSystem::test_release_delay_us = 30;     // hold the give-up window open: a re-queue from inside it is then certain
+  ActorSystem sys(8);
+  auto a = sys.actor_of("serial", std::unique_ptr<Actor>(new Serial()));
+  const int T = 8, N = 4000;
+  std::vector<std::thread> th;
+  for (int t = 0; t < T; ++t)
+    th.emplace_back([&, t] {
+      for (int i = 0; i < N; ++i) {
+        sys.tell(a, "work");
+        for (volatile int k = 0; k < 2000 + 700 * ((i + t) % 5); ++k) {}   // let the mailbox run empty between messages
+      }
+    });
+  for (auto& t : th) t.join();
+  Json r;
+  for (int i = 0; i < 200; ++i) {
+    r = sys.ask(a, "report");
+    if (r["seen"].as_int() == static_cast<long long>(T) * N) break;
+    std::this_thread::sleep_for(std::chrono::milliseconds(5));
+  }
+  EXPECT(r["seen"].as_int() == static_cast<long long>(T) * N);
+  EXPECT(r["overlaps"].as_int() == 0);
+  sys.shutdown();
+  ActorSystem::test_release_delay_us = 0;
+}
+
 static void test_actors() {
   ActorSystem sys(8);
   auto a = sys.actor_of("counter", std::unique_ptr<Actor>(new Counter()));
@@ -126,6 +176,7 @@ static void test_store(const std::string& dir) {
 int main(int argc, char** argv) {
   const std::string dir = argc > 1 ? argv[1] : "/tmp/det-selftest-store";
   test_actors();
+  test_actor_is_never_run_concurrently();
   test_rw();
   test_store(dir);
   // a deterministic piece, to make sure the binary links the library properly
