@@ -67,7 +67,7 @@ static void test_actor_is_never_run_concurrently() {
   ActorSystem::test_release_delay_us = 30;     // hold the give-up window open: a re-queue from inside it is then certain
   ActorSystem sys(8);
   auto a = sys.actor_of("serial", std::unique_ptr<Actor>(new Serial()));
-  const int T = 8, N = 4000;
+  const int T = 8, N = 1500;
   std::vector<std::thread> th;
   for (int t = 0; t < T; ++t)
     th.emplace_back([&, t] {
