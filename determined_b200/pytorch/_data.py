@@ -120,16 +120,44 @@ class _Prefetcher:
 
         t = threading.Thread(target=work, daemon=True, name="det-prefetch")
         t.start()
+        _LIVE_PREFETCH.add((stop, t))
         try:
             while True:
-                item = q.get()
+                try:
+                    item = q.get(timeout=1.0)
+                except queue.Empty:
+                    if stop.is_set() and not t.is_alive():
+                        return                 # stopped from outside (interpreter exit): nothing more will arrive
+                    continue
                 if item is end:
                     return
                 if isinstance(item, BaseException):
                     raise item
                 yield item
         finally:
+            # the thread must be OUT of torch before the interpreter goes away: a daemon thread killed inside a C++ frame
+            # aborts the process ("terminate called without an active exception")
             stop.set()
+            t.join(timeout=5)
+            _LIVE_PREFETCH.discard((stop, t))
+
+
+_LIVE_PREFETCH: set = set()
+
+
+def stop_prefetch_threads() -> None:
+    """Stop and join every live prefetch thread (iterators that were never closed: the training loader repeats forever).
+    Registered to run at interpreter exit."""
+    for stop, t in list(_LIVE_PREFETCH):
+        stop.set()
+    for stop, t in list(_LIVE_PREFETCH):
+        t.join(timeout=5)
+        _LIVE_PREFETCH.discard((stop, t))
+
+
+import atexit as _atexit  # noqa: E402
+
+_atexit.register(stop_prefetch_threads)
 
 
 class DataLoader:
