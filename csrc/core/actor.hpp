@@ -166,6 +166,7 @@ class ActorSystem {
     std::lock_guard<std::mutex> g(trace_mu_);
     if (trace_) fclose(trace_);
     trace_ = path.empty() ? nullptr : fopen(path.c_str(), "a");
+    tracing_.store(trace_ != nullptr, std::memory_order_release);
     trace_origin_ = std::chrono::steady_clock::now();
   }
   // [{address, mailbox, children, stopped}] for /debug/actors
@@ -235,7 +236,8 @@ class ActorSystem {
 
  private:
   std::mutex trace_mu_;
-  FILE* trace_ = nullptr;
+  FILE* trace_ = nullptr;                 // guarded by trace_mu_
+  std::atomic<bool> tracing_{false};      // what the workers look at without the lock
   std::chrono::steady_clock::time_point trace_origin_;
   std::mutex mu_;
   std::condition_variable cv_;
@@ -310,7 +312,7 @@ inline void ActorSystem::worker() {
         } else if (msg.type == "__child_failed__") {
           cell->actor_->child_failed(ctx, msg.sender, msg.body.as_string());
         } else if (!cell->stopped()) {
-          if (trace_) {
+          if (tracing_.load(std::memory_order_acquire)) {
             const auto t0 = std::chrono::steady_clock::now();
             cell->actor_->receive(ctx, msg);
             trace_receive(cell->address(), msg.type, msg.sender ? msg.sender->address() : std::string(), t0);

@@ -8,6 +8,7 @@
 //             [--security-tls-master-cert-name NAME] [--config-file agent.yaml-as-json]
 // Every flag can also come from DET_AGENT_<FLAG> (upper case, dashes as underscores), flags win.
 // (reference: agent/cmd/determined-agent/run.go, agent/internal/options.go:12-103, agent.go:60-150)
+#include <atomic>
 #include <unistd.h>
 
 #include <csignal>
@@ -18,7 +19,7 @@
 #include "agent.hpp"
 #include "http.hpp"
 
-static volatile bool g_stop = false;
+static std::atomic<bool> g_stop{false};     // lock-free: safe to set from the signal handler
 static void on_signal(int) { g_stop = true; }
 
 int main(int argc, char** argv) {
