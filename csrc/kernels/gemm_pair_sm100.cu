@@ -173,6 +173,11 @@ gemm_pair_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   ptx::cluster_sync_all();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // Programmatic dependent launch: everything above (descriptor prefetch, barrier init, TMEM allocation, the cluster
+  // handshake) ran while the previous kernel of the stream was still draining; nothing below may start before its
+  // results are visible. A no-op when the kernel was launched without the attribute.
+  ptx::pdl_launch_dependents();
+  ptx::pdl_wait();
 
   PairSched sched(p, cluster_id, num_clusters);
   int tile, kb0, kb1;
@@ -426,7 +431,18 @@ static int launch_pair(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
     DET_CHECK_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, P_SMEM_BYTES));
     attr_set[dev] = true;
   }
-  kfn<<<grid, GEMM_THREADS, P_SMEM_BYTES, stream>>>(ta, tb, tc, tx, p);
+  static const bool pdl = [] { const char* e = getenv("DET_PDL"); return e != nullptr && e[0] == '1'; }();
+  if (pdl) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(GEMM_THREADS); cfg.dynamicSmemBytes = P_SMEM_BYTES; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    DET_CHECK_CUDA(cudaLaunchKernelEx(&cfg, kfn, ta, tb, tc, tx, p));
+  } else {
+    kfn<<<grid, GEMM_THREADS, P_SMEM_BYTES, stream>>>(ta, tb, tc, tx, p);
+  }
   DET_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
