@@ -1,5 +1,6 @@
 """CLI pieces that need no cluster: ``experiment create --git`` metadata checks and CSV rendering
 (reference cli/determined_cli/experiment.py:124-186, render.py)."""
+import pathlib
 import subprocess
 
 import pytest
@@ -51,3 +52,13 @@ def test_csv_rendering_of_list_output():
     assert args.git
     args = cli.build_parser().parse_args(["tunnel", "7", "--listener", "2222"])
     assert args.task_id == "7" and args.listener == 2222
+
+
+def test_cli_doc_is_generated_from_the_parser():
+    """docs/cli.md is the argparse tree, verb by verb; a new flag or verb without `python scripts/gen_cli_doc.py` fails here."""
+    import subprocess
+    import sys
+
+    root = pathlib.Path(__file__).resolve().parent.parent
+    out = subprocess.run([sys.executable, str(root / "scripts" / "gen_cli_doc.py"), "--check"], capture_output=True, text=True)
+    assert out.returncode == 0, out.stdout + out.stderr
