@@ -65,3 +65,23 @@ def test_pipelined_allgather_under_the_optimizer_keeps_replicas_identical(tmp_pa
     assert a == b, "replicas diverged with the pipelined all-gather"
     lp, lq = [m["loss"] for m in plain["training"]], [m["loss"] for m in piped["training"]]
     assert all(abs(x - y) <= 0.05 * max(abs(x), 0.05) for x, y in zip(lp, lq)), (lp, lq)
+
+
+def test_native_parallel_data_parallel_on_two_gpus():
+    """`resources.native_parallel`: ONE process drives both GPUs through nn.DataParallel — the in-tree modules (ctypes kernels
+    on the replica's current device and stream) must work as DataParallel replicas, and the loss must go down."""
+    _need_two()
+    from determined_b200.models.vision_trials import MNistTrial
+    from tests.harness_utils import TrainAndValidate, make_controller
+
+    tv = TrainAndValidate()
+    hp = {"learning_rate": 1.0, "global_batch_size": 64, "n_filters1": 32, "n_filters2": 64, "dropout1": 0.25, "dropout2": 0.5}
+    c = make_controller(MNistTrial, hp, tv.send(steps=3, scheduling_unit=10, validation_freq=3),
+                        exp_config={"resources": {"slots_per_trial": 2, "native_parallel": True},
+                                    "data": {"train_size": 1024, "validation_size": 256}})
+    assert isinstance(c.context.models[0], torch.nn.DataParallel)
+    assert c.context.get_per_slot_batch_size() == 64
+    c.run()
+    losses = [m["loss"] for m in tv.training_metrics]
+    assert len(losses) == 30 and all(l == l for l in losses)
+    assert sum(losses[-5:]) < sum(losses[:5])
