@@ -191,6 +191,14 @@ class PyTorchTrialContext(TrialContext):
             if self.aggregation_frequency != 1:
                 raise ValueError("aggregation_frequency > 1 needs the multi-process path: drop `resources.native_parallel` "
                                  "(reference _pytorch_context.py:136-142)")
+            own = sorted({type(m).__name__ for m in model.modules() if type(m).__module__.startswith("determined_b200.ops")})
+            if own:
+                # the in-tree modules write parameter gradients in place from their backward (into the flat bucket) instead
+                # of returning them through autograd; nn.DataParallel's replicas are non-leaf copies, so those writes would
+                # never reach the real parameters
+                raise ValueError("resources.native_parallel (nn.DataParallel) works with stock torch.nn modules; this model "
+                                 f"uses determined_b200.ops modules ({', '.join(own[:4])}) — drop native_parallel and use the "
+                                 "default one-process-per-GPU data parallelism")
             model = nn.DataParallel(model, device_ids=list(range(self.native_parallel_gpus())))
             log.debug("model wrapped for native parallel training")
         self._main_model.add_module(f"model_{len(self.models)}", model)
