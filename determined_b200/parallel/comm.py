@@ -171,7 +171,25 @@ class TorchDistCommunicator(Communicator):
             if self._vmm:
                 exch, mc = self._vmm
                 idx = self.device.index if self.device.index is not None else 0
-                reg = vmm.allocate(self, exch, idx, n * elem, with_multicast=mc and os.environ.get("DET_DISABLE_NVLS") != "1")
+                reg, err = None, ""
+                try:
+                    reg = vmm.allocate(self, exch, idx, n * elem, with_multicast=mc and os.environ.get("DET_DISABLE_NVLS") != "1")
+                except Exception as e:      # noqa: BLE001 - reported below, decided together
+                    err = repr(e)
+                if not self._regions:
+                    # the FIRST region decides the backend for the whole run, and all ranks decide together: one failing
+                    # rank (socket permissions, a driver that refuses the export) sends everybody to torch symmetric memory
+                    oks = self.allgather_object(reg is not None)
+                    if not all(oks):
+                        if self.rank == 0 or err:
+                            print(f"[det] native VMM arena failed on rank(s) {[r for r, ok in enumerate(oks) if not ok]} "
+                                  f"({err or 'peer failure'}); using torch symmetric memory", flush=True)
+                        exch.close()
+                        self._vmm = False
+                        reg = None
+                elif reg is None:
+                    raise RuntimeError(f"native VMM arena allocation failed after the arena was in use: {err}")
+            if self._vmm and reg is not None:
                 local = _tensor_from_ptr(reg.ptrs[self.rank], n, dtype, self.device)
                 local.zero_()
                 torch.cuda.synchronize(self.device)

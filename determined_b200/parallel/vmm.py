@@ -30,16 +30,19 @@ class FdExchange:
         self.sock = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
         self.sock.bind(self.names[self.rank])
         self.sock.listen(max(8, 4 * self.size))
+        self.sock.settimeout(60.0)     # a peer that failed before sending must not leave the others in accept() forever
         comm.barrier()      # every listener is up before anyone connects
 
     def _send(self, dst: int, fd: int) -> None:
         with socket.socket(socket.AF_UNIX, socket.SOCK_STREAM) as s:
+            s.settimeout(60.0)
             s.connect(self.names[dst])
             socket.send_fds(s, [struct.pack("i", self.rank)], [fd])
 
     def _recv(self) -> Tuple[int, int]:
         conn, _ = self.sock.accept()
         with conn:
+            conn.settimeout(60.0)
             msg, fds, _, _ = socket.recv_fds(conn, 4, 1)
         return struct.unpack("i", msg)[0], fds[0]
 
