@@ -23,6 +23,9 @@ class ResourcePoolActor : public Actor {
     if (t == "tick") {
       schedule(ctx);
       ctx.system().notify_after(ctx.self(), m_->cfg.scheduler_tick_ms, "tick");
+    } else if (t == "kick") {
+      kick_pending_ = false;
+      schedule(ctx);
     } else if (t == "add_agent") {
       if (agents_.count(msg.body["id"].as_string())) {   // heartbeat of a known agent: keep its slot assignments
         agent_info_[msg.body["id"].as_string()]["last_seen"] = msg.body["registered_time"];
@@ -38,6 +41,7 @@ class ResourcePoolActor : public Actor {
       agent_info_[a.id] = msg.body;
       m_->log("info", "agent connected: " + a.id + " with " + std::to_string(a.num_slots) + " slots");
       msg.respond(Json(true));
+      kick(ctx);
     } else if (t == "remove_agent") {
       const std::string id = msg.body["id"].as_string();
       agents_.erase(id);
@@ -80,9 +84,11 @@ class ResourcePoolActor : public Actor {
       tasks_.push_back(r);
       handlers_[r.id] = msg.sender;
       msg.respond(Json(true));
+      kick(ctx);
     } else if (t == "release") {
       release(msg.body["task_id"].as_string());
       msg.respond(Json(true));
+      kick(ctx);
     } else if (t == "summary") {
       msg.respond(summary());
     } else {
@@ -91,6 +97,16 @@ class ResourcePoolActor : public Actor {
   }
 
  private:
+  // The periodic tick (reference: 500 ms, resource_pool.go) stays as the backstop; a change that can make a waiting task
+  // schedulable — a new request, freed slots, a new agent — also asks for a pass a few milliseconds later, coalesced, so a
+  // short trial does not sit out half a tick on average before it gets its slot (a 16-trial search is dozens of hand-overs).
+  void kick(Context& ctx) {
+    if (kick_pending_) return;
+    kick_pending_ = true;
+    ctx.system().notify_after(ctx.self(), 5, "kick");
+  }
+  bool kick_pending_ = false;
+
   void release(const std::string& task_id) {
     for (auto& req : tasks_) {
       if (req.id != task_id) continue;
