@@ -71,6 +71,11 @@ def run(args) -> Dict[str, Any]:
         return {"impl": "reference", "unavailable": why}
     env = dict(os.environ)
     env["PYTHONPATH"] = SHIMS + os.pathsep + REF
+    # start-up only: the image sets PYTHONDONTWRITEBYTECODE and ships no __pycache__, so each of the 3 x N worker processes
+    # would compile torch + transformers from source again (minutes at N = 8); a shared byte-code cache changes nothing
+    # about the code that runs
+    env.pop("PYTHONDONTWRITEBYTECODE", None)
+    env.setdefault("PYTHONPYCACHEPREFIX", os.path.join(tempfile.gettempdir(), "det-ref-pycache"))
     if world == 1:
         env.pop("RANK", None), env.pop("WORLD_SIZE", None), env.pop("LOCAL_RANK", None)
     workdir = tempfile.mkdtemp(prefix="ref_arm_")  # outside the repo so `determined` resolves to baseline/_ref
