@@ -49,7 +49,7 @@ std::string md5_hex(const std::string& s) {
 MasterConfig MasterConfig::from_json(const Json& j) {
   static const std::set<std::string> known = {"host", "port", "data_dir", "scheduler", "fitting_policy", "preemption", "checkpoint_storage",
                                               "python", "repo_root", "slot_type", "visible_gpus", "artificial_slots", "auth_required",
-                                              "cluster_name", "scheduler_tick_ms", "terminate_timeout_ms", "resource_pools", "db", "telemetry", "provisioner", "resource_manager",
+                                              "cluster_name", "scheduler_tick_ms", "terminate_timeout_ms", "all_ready_timeout_ms", "resource_pools", "db", "telemetry", "provisioner", "resource_manager",
                                               "security", "task_container_defaults", "logging", "warm_workers"};
   MasterConfig c;
   for (auto& kv : j.obj())
@@ -104,6 +104,7 @@ MasterConfig MasterConfig::from_json(const Json& j) {
   }
   c.scheduler_tick_ms = static_cast<int>(j["scheduler_tick_ms"].as_int(c.scheduler_tick_ms));
   c.terminate_timeout_ms = static_cast<int>(j["terminate_timeout_ms"].as_int(c.terminate_timeout_ms));
+  c.all_ready_timeout_ms = static_cast<int>(j["all_ready_timeout_ms"].as_int(c.all_ready_timeout_ms));
   if (c.scheduler != "fair_share" && c.scheduler != "priority" && c.scheduler != "round_robin") throw ConfigError("scheduler must be fair_share, priority or round_robin");
   if (c.fitting_policy != "best" && c.fitting_policy != "worst") throw ConfigError("fitting_policy must be best or worst");
   return c;

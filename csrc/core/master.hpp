@@ -52,6 +52,7 @@ struct MasterConfig {
   Json telemetry;                        // {enabled: bool, sink: path}; events go to a local JSONL file (no network here)
   int scheduler_tick_ms = 500;
   int terminate_timeout_ms = 60000;
+  int all_ready_timeout_ms = 600000;     // reference allReadyTimeout: 10 minutes from container start to a working harness
 
   static MasterConfig from_json(const Json& j);  // strict: unknown keys are rejected
   Json to_json() const;

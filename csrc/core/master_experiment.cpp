@@ -68,6 +68,7 @@ class TrialActor : public Actor {
         msg.respond(obj({{"type", "TERMINATE"}}));
         return;
       }
+      harness_ready_ = true;      // the trial's chief is up and asking for work
       if (poll_.reply) poll_.respond(obj({{"type", "WAIT"}}));
       poll_ = msg;
       ++poll_seq_;
@@ -80,6 +81,14 @@ class TrialActor : public Actor {
       msg.respond(Json(true));
     } else if (t == "container_event") {
       on_container_event(ctx, msg.body);
+    } else if (t == "all_ready_timeout") {
+      // reference trial.go:408-418 (allReadyTimeout): containers that never produce a working harness — a gang member
+      // that hangs at rendezvous, a start-up hook that never returns — are killed; the exit takes the restart path
+      if (running_ && !harness_ready_ && msg.body.as_int() == run_id_) {
+        m_->log("warn", task_id_ + ": containers were not ready within " + std::to_string(m_->cfg.all_ready_timeout_ms / 1000) + " s; killing them");
+        exit_failure_ = "trial containers did not become ready in time";
+        for (auto& c : containers_) m_->signal_container(c, SIGKILL);
+      }
     } else if (t == "terminate_timeout") {
       if (running_ && awaiting_exit_ && msg.body.as_int() == run_id_) {
         m_->log("warn", task_id_ + ": did not exit after TERMINATE; killing");
@@ -255,8 +264,10 @@ class TrialActor : public Actor {
     running_ = true;
     awaiting_exit_ = false;
     inflight_ = false;
+    harness_ready_ = false;
     live_containers_ = static_cast<int>(containers_.size());
     exit_failure_.clear();
+    ctx.system().notify_after(ctx.self(), m_->cfg.all_ready_timeout_ms, "all_ready_timeout", Json(static_cast<long long>(run_id_)));
   }
 
   void on_workload_completed(Context& ctx, const Json& body) {
@@ -382,6 +393,7 @@ class TrialActor : public Actor {
   std::string task_id_;
   int max_restarts_ = 5, restarts_ = 0, run_id_ = 0, live_containers_ = 0;
   bool allocation_requested_ = false, allocated_ = false, running_ = false, inflight_ = false, awaiting_exit_ = false;
+  bool harness_ready_ = false;     // this run's harness has asked for a workload (the all-ready timeout watches it)
   bool close_requested_ = false, preempt_requested_ = false, killed_ = false, finished_ = false, exited_early_reported_ = false;
   Workload inflight_workload_;
   Message poll_;

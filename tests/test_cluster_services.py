@@ -564,3 +564,45 @@ def test_warm_workers_take_over_trial_starts(tmp_path):
             proc.wait(timeout=5)
         except Exception:
             proc.kill()
+
+
+def test_containers_that_never_become_ready_are_killed(tmp_path):
+    """`all_ready_timeout_ms` (reference allReadyTimeout, trial.go:408-418): a trial whose container never brings up a working
+    harness — here a start-up hook that hangs — is killed when the timeout passes and takes the restart path; with
+    max_restarts 1 the experiment ends in ERROR instead of holding its slot forever."""
+    import shutil
+
+    from determined_b200 import _build
+
+    _build.build_core()
+    model_dir = tmp_path / "model"
+    shutil.copytree(MODEL_DIR, model_dir)
+    (model_dir / "startup-hook.sh").write_text("sleep 600\n")
+    cfg_file = tmp_path / "master.json"
+    cfg_file.write_text(json.dumps({"all_ready_timeout_ms": 1500, "terminate_timeout_ms": 2000}))
+    port_file = tmp_path / "port"
+    proc = subprocess.Popen([str(LIB / "det-master"), "--config", str(cfg_file), "--port", "0", "--data-dir", str(tmp_path / "data"),
+                             "--artificial-slots", "1", "--repo-root", str(ROOT), "--python", sys.executable, "--print-port-file", str(port_file)],
+                            stdout=open(tmp_path / "master.log", "w"), stderr=subprocess.STDOUT, env=dict(os.environ, DET_CONFIG_DIR=str(tmp_path / "cfg")))
+    try:
+        for _ in range(200):
+            if port_file.exists() and port_file.read_text().strip():
+                break
+            time.sleep(0.05)
+        os.environ["DET_CONFIG_DIR"] = str(tmp_path / "cfg")
+        d = Determined(f"127.0.0.1:{int(port_file.read_text())}")
+        cfg = {"entrypoint": "model_def:XorTrial", "hyperparameters": {"global_batch_size": 8, "hidden_size": 4, "learning_rate": 0.5},
+               "searcher": {"name": "single", "metric": "validation_loss", "max_length": {"batches": 10}}, "max_restarts": 1,
+               "checkpoint_storage": {"type": "shared_fs", "host_path": str(tmp_path / "ckpts")}}
+        exp = d.create_experiment(cfg, str(model_dir))
+        t0 = time.time()
+        assert exp.wait(timeout=60) == "ERROR"
+        assert time.time() - t0 < 30
+        log = (tmp_path / "master.log").read_text()
+        assert log.count("were not ready within") == 2, log[-1500:]       # the first run and its one restart
+    finally:
+        proc.terminate()
+        try:
+            proc.wait(timeout=5)
+        except Exception:
+            proc.kill()
