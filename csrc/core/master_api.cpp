@@ -414,6 +414,90 @@ tick();setInterval(tick,2000);
     return ok(out);
   });
 
+  // ---- hyperparameter-search visualisation (reference api.proto MetricNames / MetricBatches / TrialsSnapshot / TrialsSample,
+  // served there as polling streams; here each GET answers with the current state, and the gRPC gateway streams it) ----
+  http.route("GET", "/api/v1/experiments/:id/metrics-stream/metric-names", [m](const HttpRequest& r) {
+    const long long id = atoll(r.params.at("id").c_str());
+    Json e = m->store.get("experiments", id);
+    if (e.is_null()) return not_found("experiment");
+    std::set<std::string> train, val;
+    for (auto& t : m->store.list("trials", [&](const Json& row) { return row["experiment_id"].as_int() == id; })) {
+      const std::string key = std::to_string(t["id"].as_int());
+      for (auto& s : m->store.series("steps", key)) for (auto& kv : s["metrics"]["avg_metrics"].obj()) if (kv.second.is_number()) train.insert(kv.first);
+      for (auto& s : m->store.series("validations", key)) for (auto& kv : s["metrics"]["validation_metrics"].obj()) if (kv.second.is_number()) val.insert(kv.first);
+    }
+    Json tr = Json::array(), va = Json::array();
+    for (auto& n : train) tr.push_back(n);
+    for (auto& n : val) va.push_back(n);
+    return ok(obj({{"searcher_metric", e["config"]["searcher"]["metric"]}, {"training_metrics", tr}, {"validation_metrics", va}}));
+  });
+  // one trial's series of (total batches, value) of a metric; type = training | validation
+  auto metric_series = [m](const Json& t, const std::string& name, const std::string& type) {
+    std::vector<std::pair<double, double>> pts;
+    const std::string key = std::to_string(t["id"].as_int());
+    if (type == "validation") {
+      for (auto& s : m->store.series("validations", key)) { const Json& v = s["metrics"]["validation_metrics"][name]; if (v.is_number()) pts.emplace_back(s["total_batches"].as_double(), v.as_double()); }
+    } else {
+      for (auto& s : m->store.series("steps", key)) { const Json& v = s["metrics"]["avg_metrics"][name]; if (v.is_number()) pts.emplace_back(s["total_batches"].as_double(), v.as_double()); }
+    }
+    return pts;
+  };
+  auto metric_type_of = [](const HttpRequest& r) {
+    const std::string t = r.q("metric_type", r.q("type", "validation"));
+    return (t == "training" || t == "METRIC_TYPE_TRAINING" || t == "1") ? std::string("training") : std::string("validation");
+  };
+  http.route("GET", "/api/v1/experiments/:id/metrics-stream/batches", [m, metric_series, metric_type_of](const HttpRequest& r) {
+    const long long id = atoll(r.params.at("id").c_str());
+    if (r.q("metric_name").empty()) return HttpResponse::error(400, "metric_name is required");
+    std::set<long long> at;
+    for (auto& t : m->store.list("trials", [&](const Json& row) { return row["experiment_id"].as_int() == id; }))
+      for (auto& p : metric_series(t, r.q("metric_name"), metric_type_of(r))) at.insert(static_cast<long long>(p.first));
+    Json b = Json::array();
+    for (auto v : at) b.push_back(v);
+    return ok(obj({{"batches", b}}));
+  });
+  http.route("GET", "/api/v1/experiments/:id/metrics-stream/trials-snapshot", [m, metric_series, metric_type_of](const HttpRequest& r) {
+    const long long id = atoll(r.params.at("id").c_str());
+    if (r.q("metric_name").empty()) return HttpResponse::error(400, "metric_name is required");
+    const long long at = r.qi("batches_processed", -1);
+    Json trials = Json::array();
+    for (auto& t : m->store.list("trials", [&](const Json& row) { return row["experiment_id"].as_int() == id; }))
+      for (auto& p : metric_series(t, r.q("metric_name"), metric_type_of(r)))
+        if (static_cast<long long>(p.first) == at) { trials.push_back(obj({{"trial_id", t["id"]}, {"hparams", t["hparams"]}, {"metric", p.second}})); break; }
+    return ok(obj({{"trials", trials}}));
+  });
+  http.route("GET", "/api/v1/experiments/:id/metrics-stream/trials-sample", [m, metric_series, metric_type_of](const HttpRequest& r) {
+    // the `max_trials` best trials by their latest value of the metric (order from searcher.smaller_is_better), each series
+    // cut to [start_batches, end_batches] and LTTB-downsampled to max_datapoints
+    const long long id = atoll(r.params.at("id").c_str());
+    if (r.q("metric_name").empty()) return HttpResponse::error(400, "metric_name is required");
+    Json e = m->store.get("experiments", id);
+    if (e.is_null()) return not_found("experiment");
+    const bool smaller = e["config"]["searcher"]["smaller_is_better"].as_bool(true);
+    const int max_trials = static_cast<int>(r.qi("max_trials", 25)), max_points = static_cast<int>(r.qi("max_datapoints", 1000));
+    const long long lo = r.qi("start_batches", 0), hi = r.qi("end_batches", 0) > 0 ? r.qi("end_batches", 0) : (1LL << 60);
+    struct Row { Json trial; std::vector<std::pair<double, double>> pts; double last; };
+    std::vector<Row> rows;
+    for (auto& t : m->store.list("trials", [&](const Json& row) { return row["experiment_id"].as_int() == id; })) {
+      auto pts = metric_series(t, r.q("metric_name"), metric_type_of(r));
+      if (pts.empty()) continue;
+      rows.push_back(Row{t, pts, pts.back().second});
+    }
+    std::stable_sort(rows.begin(), rows.end(), [&](const Row& a, const Row& b) { return smaller ? a.last < b.last : a.last > b.last; });
+    if (max_trials > 0 && static_cast<int>(rows.size()) > max_trials) rows.resize(static_cast<size_t>(max_trials));
+    Json trials = Json::array(), promoted = Json::array();
+    for (auto& row : rows) {
+      std::vector<std::pair<double, double>> win;
+      for (auto& p : row.pts) if (p.first >= static_cast<double>(lo) && p.first <= static_cast<double>(hi)) win.push_back(p);
+      if (max_points > 2) win = lttb_downsample(win, max_points);
+      Json data = Json::array();
+      for (auto& p : win) data.push_back(obj({{"batches", static_cast<long long>(p.first)}, {"value", p.second}}));
+      trials.push_back(obj({{"trial_id", row.trial["id"]}, {"hparams", row.trial["hparams"]}, {"data", data}}));
+      promoted.push_back(row.trial["id"]);
+    }
+    return ok(obj({{"trials", trials}, {"promoted_trials", promoted}, {"demoted_trials", Json::array()}}));
+  });
+
   // ---- trials ----
   http.route("GET", "/api/v1/trials/:id", [m](const HttpRequest& r) {
     Json t = m->store.get("trials", r.params.at("id"));

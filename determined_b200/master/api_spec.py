@@ -99,9 +99,21 @@ RPCS: List[Dict[str, Any]] = [
     _rpc("DeleteExperiment", "DELETE", "/api/v1/experiments/{id}", [ID32], None),
     _rpc("GetExperimentCheckpoints", "GET", "/api/v1/experiments/{id}/checkpoints", [ID32], ("checkpoints", "Checkpoint", "repeated")),
     _rpc("GetModelDef", "GET", "/api/v1/experiments/{id}/model_def", [ID32], ("model_def", "Struct")),
-    _rpc("MetricBatches", "GET", "/api/v1/experiments/{id}/metrics",
-         [ID32, ("metric_name", "string"), ("metric_type", "string"), ("max_points", "int32")], ("metrics", "Struct"),
+    _rpc("ExperimentMetrics", "GET", "/api/v1/experiments/{id}/metrics",
+         [ID32, ("name", "string"), ("type", "string"), ("max_points", "int32")], ("metrics", "Struct"),
          doc="Per-trial metric series of an experiment, LTTB down-sampled to max_points."),
+    _rpc("MetricNames", "GET", "/api/v1/experiments/{id}/metrics-stream/metric-names", [ID32], ("names", "Struct"),
+         doc="searcher_metric, training_metrics[], validation_metrics[] recorded so far by the experiment's trials."),
+    _rpc("MetricBatches", "GET", "/api/v1/experiments/{id}/metrics-stream/batches",
+         [ID32, ("metric_name", "string"), ("metric_type", "string")], ("result", "Struct"),
+         doc="batches[]: the milestones (batches processed) at which the metric has been recorded; metric_type training | validation."),
+    _rpc("TrialsSnapshot", "GET", "/api/v1/experiments/{id}/metrics-stream/trials-snapshot",
+         [ID32, ("batches_processed", "int32"), ("metric_name", "string"), ("metric_type", "string")], ("result", "Struct"),
+         doc="trials[]: {trial_id, hparams, metric} of every trial that has a value of the metric at that point of progress."),
+    _rpc("TrialsSample", "GET", "/api/v1/experiments/{id}/metrics-stream/trials-sample",
+         [ID32, ("metric_name", "string"), ("metric_type", "string"), ("max_trials", "int32"), ("max_datapoints", "int32"),
+          ("start_batches", "int32"), ("end_batches", "int32")], ("result", "Struct"),
+         doc="trials[]: {trial_id, hparams, data[{batches, value}]} of the best max_trials trials, down-sampled; promoted_trials / demoted_trials."),
     _rpc("PreviewHPSearch", "POST", "/api/v1/searcher/preview", [("searcher", "Struct"), ("hyperparameters", "Struct"), ("seed", "int32")],
          ("simulation", "Struct"), doc="Simulate a searcher: multiset of per-trial operation sequences."),
     # ---- trials / checkpoints ------------------------------------------------------------------------------------------------

@@ -92,6 +92,22 @@ def test_adaptive_asha_packs_trials_and_gc_runs(master):
     time.sleep(1.5)  # GC is asynchronous
     states = [c["state"] for c in d._session.get(f"/api/v1/experiments/{exp.id}/checkpoints")]
     assert "COMPLETED" in states
+    # hyperparameter-search visualisation endpoints (reference api.proto MetricNames / MetricBatches / TrialsSnapshot /
+    # TrialsSample) over the finished search
+    base = f"/api/v1/experiments/{exp.id}/metrics-stream"
+    names = d._session.get(f"{base}/metric-names")
+    assert names["searcher_metric"] == "validation_loss" and "loss" in names["training_metrics"] and "validation_loss" in names["validation_metrics"]
+    batches = d._session.get(f"{base}/batches?metric_name=validation_loss&metric_type=validation")["batches"]
+    assert batches == sorted(batches) and batches[0] == 10 and batches[-1] == 40
+    snap = d._session.get(f"{base}/trials-snapshot?metric_name=validation_loss&metric_type=validation&batches_processed=10")["trials"]
+    assert len(snap) == 6 and all(set(t) == {"trial_id", "hparams", "metric"} and "learning_rate" in t["hparams"] for t in snap)
+    top = d._session.get(f"{base}/trials-snapshot?metric_name=validation_loss&metric_type=validation&batches_processed=40")["trials"]
+    assert 1 <= len(top) < 6                                    # only promoted trials got that far
+    sample = d._session.get(f"{base}/trials-sample?metric_name=loss&metric_type=training&max_trials=3&max_datapoints=5")
+    assert len(sample["trials"]) == 3 and sample["promoted_trials"] == [t["trial_id"] for t in sample["trials"]] and sample["demoted_trials"] == []
+    assert all(1 <= len(t["data"]) <= 5 and set(t["data"][0]) == {"batches", "value"} for t in sample["trials"])
+    with pytest.raises(APIError):
+        d._session.get(f"{base}/batches")                       # metric_name is required
 
 
 def test_pause_activate_cancel_and_validation_errors(master):

@@ -104,6 +104,14 @@ def test_experiment_lifecycle_and_log_stream_over_grpc(stack):
     assert lines and any("checkpoint" in l.lower() for l in lines)
     only = [l.message for b in c.TrialLogs(id=t.id, search="checkpoint") for l in b.entries]
     assert only and all("checkpoint" in l for l in only) and len(only) < len(lines)
+    # the reference's HP-visualisation RPCs
+    names = c.MetricNames(id=exp.id).names
+    assert names["searcher_metric"] == "validation_loss" and "loss" in list(names["training_metrics"])
+    assert list(c.MetricBatches(id=exp.id, metric_name="loss", metric_type="training").result["batches"]) == [10, 20]
+    snap = c.TrialsSnapshot(id=exp.id, batches_processed=20, metric_name="validation_loss", metric_type="validation").result["trials"]
+    assert len(snap) == 1 and snap[0]["trial_id"] == t.id and snap[0]["hparams"]["hidden_size"] == 4
+    sample = c.TrialsSample(id=exp.id, metric_name="loss", metric_type="training", max_trials=5, max_datapoints=10).result
+    assert [p["batches"] for p in sample["trials"][0]["data"]] == [10, 20]
     c.ArchiveExperiment(id=exp.id)
     assert all(x.id != exp.id for x in c.GetExperiments().experiments)
     assert any(x.id == exp.id for x in c.GetExperiments(archived=True).experiments)
