@@ -248,6 +248,15 @@ tick();setInterval(tick,2000);
     for (auto& u : m->store.list("users")) a.push_back(obj({{"username", u["username"]}, {"admin", u["admin"]}, {"active", u["active"]}, {"agent_user_group", u["agent_user_group"]}}));
     return ok(a);
   });
+  http.route("GET", "/api/v1/users/:name", [m](const HttpRequest& r) {
+    Json u = m->store.get("users", r.params.at("name"));
+    if (u.is_null()) return not_found("user");
+    return ok(obj({{"username", u["username"]}, {"admin", u["admin"]}, {"active", u["active"]}, {"agent_user_group", u["agent_user_group"]}}));
+  });
+  http.route("GET", "/api/v1/master/telemetry", [m](const HttpRequest&) {
+    const bool on = m->cfg.telemetry.is_object() && m->cfg.telemetry["enabled"].as_bool(false);
+    return ok(obj({{"enabled", on}, {"segment_key", ""}, {"sink", on ? m->cfg.telemetry["sink"].str_or(m->cfg.data_dir + "/telemetry.jsonl") : std::string()}}));
+  });
   http.route("POST", "/api/v1/users", [m](const HttpRequest& r) {
     Json b = r.json();
     const std::string name = b["username"].as_string();
@@ -372,6 +381,52 @@ tick();setInterval(tick,2000);
     for (auto& t : m->store.list("trials", [&](const Json& row) { return row["experiment_id"].as_int() == id; })) m->store.del("trials", std::to_string(t["id"].as_int()));
     m->store.del("experiments", r.params.at("id"));
     return ok(Json::object());
+  });
+  http.route("GET", "/api/v1/experiment/labels", [m](const HttpRequest&) {
+    // every label in use with the number of experiments carrying it, most used first (reference GetExperimentLabels)
+    std::map<std::string, long long> n;
+    for (auto& e : m->store.list("experiments")) {
+      // labels set after creation (PATCH) live on the row; before that the config's own list applies
+      const Json& ls = e["labels"].is_array() ? e["labels"] : e["config"]["labels"];
+      for (auto& l : ls.arr()) if (l.is_string()) ++n[l.as_string()];
+    }
+    std::vector<std::pair<std::string, long long>> v(n.begin(), n.end());
+    std::stable_sort(v.begin(), v.end(), [](const auto& a, const auto& b) { return a.second > b.second; });
+    Json labels = Json::array();
+    for (auto& kv : v) labels.push_back(obj({{"label", kv.first}, {"count", kv.second}}));
+    return ok(obj({{"labels", labels}}));
+  });
+  http.route("GET", "/api/v1/experiments/:id/trials", [m](const HttpRequest& r) {
+    const long long id = atoll(r.params.at("id").c_str());
+    if (m->store.get("experiments", id).is_null()) return not_found("experiment");
+    const std::string state = r.q("state");
+    Json trials = Json::array();
+    for (auto& t : m->store.list("trials", [&](const Json& row) { return row["experiment_id"].as_int() == id && (state.empty() || row["state"].as_string() == state); }))
+      trials.push_back(trial_detail(m->store, t, r.q("metrics") == "true"));
+    return ok(trials);
+  });
+  http.route("GET", "/api/v1/experiments/:id/validation-history", [m](const HttpRequest& r) {
+    // the experiment's record progression: every validation that improved on all earlier ones, in time order
+    const long long id = atoll(r.params.at("id").c_str());
+    Json e = m->store.get("experiments", id);
+    if (e.is_null()) return not_found("experiment");
+    const std::string metric = e["config"]["searcher"]["metric"].as_string();
+    const bool smaller = e["config"]["searcher"]["smaller_is_better"].as_bool(true);
+    std::vector<Json> all;
+    for (auto& t : m->store.list("trials", [&](const Json& row) { return row["experiment_id"].as_int() == id; }))
+      for (auto& v : m->store.series("validations", std::to_string(t["id"].as_int())))
+        if (v["metrics"]["validation_metrics"][metric].is_number())
+          all.push_back(obj({{"trial_id", t["id"]}, {"end_time", v["end_time"]}, {"total_batches", v["total_batches"]},
+                             {"searcher_metric", v["metrics"]["validation_metrics"][metric]}}));
+    std::stable_sort(all.begin(), all.end(), [](const Json& a, const Json& b) { return a["end_time"].as_string() < b["end_time"].as_string(); });
+    Json hist = Json::array();
+    bool have = false;
+    double best = 0;
+    for (auto& v : all) {
+      const double x = v["searcher_metric"].as_double();
+      if (!have || (smaller ? x < best : x > best)) { best = x; have = true; hist.push_back(v); }
+    }
+    return ok(obj({{"validation_history", hist}}));
   });
   http.route("GET", "/api/v1/experiments/:id/checkpoints", [m](const HttpRequest& r) {
     const long long id = atoll(r.params.at("id").c_str());
@@ -518,6 +573,29 @@ tick();setInterval(tick,2000);
     }
     return ok(arr(out));
   });
+  http.route("GET", "/api/v1/trials/:id/logs/fields", [m](const HttpRequest& r) {
+    // the distinct values the log filters can take for this trial (reference TrialLogsFields)
+    m->system.ask(m->logger, "flush");
+    std::set<std::string> agents, containers, stdtypes, sources;
+    std::set<long long> ranks;
+    for (auto& l : m->store.read_logs(atoll(r.params.at("id").c_str()), 0, 1u << 30)) {
+      if (l["agent_id"].is_string()) agents.insert(l["agent_id"].as_string());
+      if (l["container_id"].is_string()) containers.insert(l["container_id"].as_string());
+      if (l["stdtype"].is_string()) stdtypes.insert(l["stdtype"].as_string());
+      if (l["source"].is_string()) sources.insert(l["source"].as_string());
+      if (l["rank"].is_number()) ranks.insert(l["rank"].as_int());
+    }
+    auto strs = [](const std::set<std::string>& v) { Json a = Json::array(); for (auto& x : v) a.push_back(x); return a; };
+    Json rk = Json::array();
+    for (auto x : ranks) rk.push_back(x);
+    return ok(obj({{"agent_ids", strs(agents)}, {"container_ids", strs(containers)}, {"rank_ids", rk}, {"stdtypes", strs(stdtypes)}, {"sources", strs(sources)}}));
+  });
+  http.route("GET", "/api/v1/trials/:id/checkpoints", [m](const HttpRequest& r) {
+    const long long id = atoll(r.params.at("id").c_str());
+    if (m->store.get("trials", id).is_null()) return not_found("trial");
+    const std::string state = r.q("state");
+    return ok(arr(m->store.list("checkpoints", [&](const Json& row) { return row["trial_id"].as_int() == id && (state.empty() || row["state"].as_string() == state); })));
+  });
   http.route("POST", "/api/v1/trials/:id/kill", [m](const HttpRequest& r) {
     Json t = m->store.get("trials", r.params.at("id"));
     if (t.is_null()) return not_found("trial");
@@ -577,6 +655,19 @@ tick();setInterval(tick,2000);
     Json agents = m->system.ask(m->rm, "summary")["agents"];
     for (auto& a : agents.arr()) for (auto& s : a["slots"].arr()) { Json x = s.deep_copy(); x["agent_id"] = a["id"]; out.push_back(x); }
     return ok(out);
+  });
+  http.route("GET", "/api/v1/agents/:agent", [m](const HttpRequest& r) {
+    const Json agents = m->system.ask(m->rm, "summary")["agents"];      // a named copy: a range-for over the temporary dangles
+    for (auto& a : agents.arr()) if (a["id"].as_string() == r.params.at("agent")) return ok(a);
+    return not_found("agent");
+  });
+  http.route("GET", "/api/v1/agents/:agent/slots/:slot", [m](const HttpRequest& r) {
+    const Json agents = m->system.ask(m->rm, "summary")["agents"];
+    for (auto& a : agents.arr()) {
+      if (a["id"].as_string() != r.params.at("agent")) continue;
+      for (auto& s : a["slots"].arr()) if (s["id"].dump() == r.params.at("slot") || s["id"].str_or("") == r.params.at("slot")) { Json x = s.deep_copy(); x["agent_id"] = a["id"]; return ok(x); }
+    }
+    return not_found("slot");
   });
   http.route("GET", "/api/v1/tasks", [m](const HttpRequest&) { return ok(m->system.ask(m->rm, "summary")["tasks"]); });
   http.route("POST", "/api/v1/agents/:agent/slots/:slot/:verb", [m](const HttpRequest& r) {
@@ -662,6 +753,16 @@ tick();setInterval(tick,2000);
     return ok(m->store.update("models", r.params.at("name"), upd));
   });
   http.route("GET", "/api/v1/models/:name/versions", [m](const HttpRequest& r) { return ok(arr(m->store.series("model_versions", r.params.at("name")))); });
+  http.route("GET", "/api/v1/models/:name/versions/:version", [m](const HttpRequest& r) {
+    for (auto& v : m->store.series("model_versions", r.params.at("name"))) {
+      if (v["version"].as_int(-1) != atoll(r.params.at("version").c_str())) continue;
+      Json out = v.deep_copy();
+      out["model"] = m->store.get("models", r.params.at("name"));
+      out["checkpoint_uuid"] = v["checkpoint"]["uuid"];
+      return ok(out);
+    }
+    return not_found("model version");
+  });
   http.route("POST", "/api/v1/models/:name/versions", [m](const HttpRequest& r) {
     Json model = m->store.get("models", r.params.at("name"));
     if (model.is_null()) return not_found("model");
@@ -701,6 +802,15 @@ tick();setInterval(tick,2000);
       if (c.is_null()) return not_found("task");
       c["logs"] = arr(m->store.series("command_logs", r.params.at("id")));
       return ok(c);
+    });
+    http.route("GET", std::string("/api/v1/") + kind + "/:id/logs", [m](const HttpRequest& r) {
+      if (m->store.get("commands", r.params.at("id")).is_null()) return not_found("task");
+      auto lines = m->store.series("command_logs", r.params.at("id"));
+      const size_t off = static_cast<size_t>(std::max<long long>(0, r.qi("offset", 0)));
+      const size_t lim = static_cast<size_t>(std::max<long long>(0, r.qi("limit", 5000)));
+      Json out = Json::array();
+      for (size_t i = off; i < lines.size() && out.size() < lim; ++i) out.push_back(lines[i]);
+      return ok(out);
     });
     http.route("POST", std::string("/api/v1/") + kind + "/:id/kill", [m](const HttpRequest& r) {
       auto actor = m->system.get("commands/" + r.params.at("id"));

@@ -77,6 +77,8 @@ RPCS: List[Dict[str, Any]] = [
     _rpc("Logout", "POST", "/api/v1/auth/logout", [], None),
     _rpc("CurrentUser", "GET", "/api/v1/auth/user", [], ("user", "User")),
     _rpc("GetUsers", "GET", "/api/v1/users", [], ("users", "User", "repeated")),
+    _rpc("GetUser", "GET", "/api/v1/users/{name}", [("name", "string")], ("user", "User")),
+    _rpc("GetTelemetry", "GET", "/api/v1/master/telemetry", [], ("telemetry", "Struct"), doc="enabled, segment_key (always empty: the sink is a local file)."),
     _rpc("PostUser", "POST", "/api/v1/users", [("username", "string"), ("password", "string"), ("admin", "bool")], ("user", "User")),
     _rpc("SetUserPassword", "PATCH", "/api/v1/users/{name}", [("name", "string"), ("password", "string")], ("user", "User")),
     _rpc("SetUserActive", "PATCH", "/api/v1/users/{name}", [("name", "string"), ("active", "bool")], ("user", "User")),
@@ -98,6 +100,11 @@ RPCS: List[Dict[str, Any]] = [
          ("experiment", "Experiment"), doc="Description, labels, max_slots / weight / priority, GC policy."),
     _rpc("DeleteExperiment", "DELETE", "/api/v1/experiments/{id}", [ID32], None),
     _rpc("GetExperimentCheckpoints", "GET", "/api/v1/experiments/{id}/checkpoints", [ID32], ("checkpoints", "Checkpoint", "repeated")),
+    _rpc("GetExperimentTrials", "GET", "/api/v1/experiments/{id}/trials", [ID32, ("state", "string"), ("metrics", "bool")],
+         ("trials", "Trial", "repeated")),
+    _rpc("GetExperimentLabels", "GET", "/api/v1/experiment/labels", [], ("result", "Struct"), doc="labels[]: {label, count}, most used first."),
+    _rpc("GetExperimentValidationHistory", "GET", "/api/v1/experiments/{id}/validation-history", [ID32], ("result", "Struct"),
+         doc="validation_history[]: every validation that set a new best of the searcher metric, in time order."),
     _rpc("GetModelDef", "GET", "/api/v1/experiments/{id}/model_def", [ID32], ("model_def", "Struct")),
     _rpc("ExperimentMetrics", "GET", "/api/v1/experiments/{id}/metrics",
          [ID32, ("name", "string"), ("type", "string"), ("max_points", "int32")], ("metrics", "Struct"),
@@ -122,13 +129,20 @@ RPCS: List[Dict[str, Any]] = [
     _rpc("TrialLogs", "GET", "/api/v1/trials/{id}/logs",
          [ID32, ("offset", "int64"), ("limit", "int32"), ("follow", "bool"), ("level", "string"), ("rank", "int32"), ("search", "string")],
          ("entries", "LogEntry", "repeated"), stream=True, doc="Filterable trial logs; with follow the stream stays open until the trial ends."),
+    _rpc("TrialLogsFields", "GET", "/api/v1/trials/{id}/logs/fields", [ID32], ("fields", "Struct"),
+         doc="Distinct agent_ids, container_ids, rank_ids, stdtypes, sources of a trial's log lines."),
+    _rpc("GetTrialCheckpoints", "GET", "/api/v1/trials/{id}/checkpoints", [ID32, ("state", "string")], ("checkpoints", "Checkpoint", "repeated")),
     _rpc("GetCheckpoint", "GET", "/api/v1/checkpoints/{uuid}", [("uuid", "string")], ("checkpoint", "Checkpoint")),
     _rpc("PostCheckpointMetadata", "POST", "/api/v1/checkpoints/{uuid}/metadata",
          [("uuid", "string"), ("metadata", "Struct"), ("remove", "string", "repeated")], ("checkpoint", "Checkpoint"),
          doc="Merge keys into a checkpoint's user metadata; `remove` deletes keys."),
     # ---- cluster -------------------------------------------------------------------------------------------------------------
     _rpc("GetAgents", "GET", "/api/v1/agents", [], ("agents", "Agent", "repeated")),
+    _rpc("GetAgent", "GET", "/api/v1/agents/{agent_id}", [("agent_id", "string")], ("agent", "Agent")),
+    _rpc("EnableAgent", "POST", "/api/v1/agents/{agent_id}/enable", [("agent_id", "string")], None),
+    _rpc("DisableAgent", "POST", "/api/v1/agents/{agent_id}/disable", [("agent_id", "string")], None),
     _rpc("GetSlots", "GET", "/api/v1/slots", [], ("slots", "Slot", "repeated")),
+    _rpc("GetSlot", "GET", "/api/v1/agents/{agent_id}/slots/{slot_id}", [("agent_id", "string"), ("slot_id", "string")], ("slot", "Slot")),
     _rpc("EnableSlot", "POST", "/api/v1/agents/{agent_id}/slots/{slot_id}/enable", [("agent_id", "string"), ("slot_id", "string")], None),
     _rpc("DisableSlot", "POST", "/api/v1/agents/{agent_id}/slots/{slot_id}/disable", [("agent_id", "string"), ("slot_id", "string")], None),
     _rpc("GetTasks", "GET", "/api/v1/tasks", [], ("tasks", "Task", "repeated")),
@@ -144,6 +158,8 @@ RPCS: List[Dict[str, Any]] = [
     _rpc("GetModel", "GET", "/api/v1/models/{name}", [("name", "string")], ("model", "Model")),
     _rpc("PatchModel", "PATCH", "/api/v1/models/{name}", [("name", "string"), ("description", "string"), ("metadata", "Struct")], ("model", "Model")),
     _rpc("GetModelVersions", "GET", "/api/v1/models/{name}/versions", [("name", "string")], ("versions", "ModelVersion", "repeated")),
+    _rpc("GetModelVersion", "GET", "/api/v1/models/{name}/versions/{version}", [("name", "string"), ("version", "int32")],
+         ("version_info", "Struct")),
     _rpc("PostModelVersion", "POST", "/api/v1/models/{name}/versions", [("name", "string"), ("checkpoint_uuid", "string")],
          ("version", "ModelVersion")),
 ]
@@ -157,6 +173,8 @@ for _kind, _coll in (("Command", "commands"), ("Notebook", "notebooks"), ("Shell
         _rpc(f"Get{_kind}s", "GET", f"/api/v1/{_coll}", [], ("commands", "Command", "repeated")),
         _rpc(f"Get{_kind}", "GET", f"/api/v1/{_coll}/{{id}}", [("id", "string")], ("command", "Command")),
         _rpc(f"Kill{_kind}", "POST", f"/api/v1/{_coll}/{{id}}/kill", [("id", "string")], None),
+        _rpc(f"{_kind}Logs", "GET", f"/api/v1/{_coll}/{{id}}/logs", [("id", "string"), ("offset", "int64"), ("limit", "int32")],
+             ("entries", "Struct", "repeated"), stream=True, doc="Output lines of the task."),
     ]
 
 

@@ -58,6 +58,18 @@ def test_master_cluster_templates_and_registry_over_grpc(stack):
     agents = c.GetAgents().agents
     assert agents[0].id == "agent-local" and agents[0].num_slots == 2
     assert len(c.GetSlots().slots) == 2
+    assert c.GetAgent(agent_id="agent-local").agent.num_slots == 2
+    slot = c.GetSlot(agent_id="agent-local", slot_id="0").slot
+    assert slot.agent_id == "agent-local" and slot.enabled
+    c.DisableAgent(agent_id="agent-local")
+    assert c.GetAgent(agent_id="agent-local").agent.raw["enabled"] is False
+    c.EnableAgent(agent_id="agent-local")
+    assert c.GetAgent(agent_id="agent-local").agent.raw["enabled"] is True
+    with pytest.raises(grpc.RpcError) as e:
+        c.GetAgent(agent_id="nope")
+    assert e.value.code() == grpc.StatusCode.NOT_FOUND
+    assert c.GetUser(name="determined").user.username == "determined"
+    assert c.GetTelemetry().telemetry["enabled"] is False
     c.PutTemplate(name="small", config={"scheduling_unit": 7})
     assert c.GetTemplate(name="small").template.config["scheduling_unit"] == 7
     assert [t.name for t in c.GetTemplates().templates] == ["small"]
@@ -104,6 +116,20 @@ def test_experiment_lifecycle_and_log_stream_over_grpc(stack):
     assert lines and any("checkpoint" in l.lower() for l in lines)
     only = [l.message for b in c.TrialLogs(id=t.id, search="checkpoint") for l in b.entries]
     assert only and all("checkpoint" in l for l in only) and len(only) < len(lines)
+    # per-experiment / per-trial views
+    assert [x.id for x in c.GetExperimentTrials(id=exp.id).trials] == [t.id]
+    assert [x.uuid for x in c.GetTrialCheckpoints(id=t.id).checkpoints] == [x.uuid for x in cks]
+    hist = list(c.GetExperimentValidationHistory(id=exp.id).result["validation_history"])
+    assert hist and hist[0]["trial_id"] == t.id and all(a["searcher_metric"] > b["searcher_metric"] for a, b in zip(hist, hist[1:]))
+    fields = c.TrialLogsFields(id=t.id).fields
+    assert list(fields["agent_ids"]) == ["agent-local"] and "stdout" in list(fields["stdtypes"]) and len(fields["container_ids"]) == 1
+    c.PatchExperiment(id=exp.id, labels=["grpc", "demo"])
+    labels = {x["label"]: x["count"] for x in c.GetExperimentLabels().result["labels"]}
+    assert labels.get("grpc") == 1 and labels.get("demo") == 1
+    c.PostModel(name="xor-grpc", description="", metadata={})
+    c.PostModelVersion(name="xor-grpc", checkpoint_uuid=cks[-1].uuid)
+    ver = c.GetModelVersion(name="xor-grpc", version=1).version_info
+    assert ver["checkpoint_uuid"] == cks[-1].uuid and ver["model"]["name"] == "xor-grpc"
     # the reference's HP-visualisation RPCs
     names = c.MetricNames(id=exp.id).names
     assert names["searcher_metric"] == "validation_loss" and "loss" in list(names["training_metrics"])
