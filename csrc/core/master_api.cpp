@@ -276,6 +276,15 @@ tick();setInterval(tick,2000);
     }
     for (const char* k : {"active", "admin", "agent_user_group"}) if (b.contains(k)) upd[k] = b[k];
     m->store.update("users", r.params.at("name"), upd);
+    const std::string renamed = b["username"].str_or("");
+    if (!renamed.empty() && renamed != r.params.at("name")) {      // `det user rename`: the row moves to its new key
+      if (m->store.exists("users", renamed)) return HttpResponse::error(409, "user exists");
+      Json row = m->store.get("users", r.params.at("name"));
+      row["username"] = renamed;
+      m->store.put("users", renamed, row);
+      m->store.del("users", r.params.at("name"));
+      return ok(obj({{"username", renamed}}));
+    }
     return ok(obj({{"username", r.params.at("name")}}));
   });
 

@@ -413,6 +413,55 @@ def user_change_password(a: argparse.Namespace) -> int:
     return 0
 
 
+def user_logout(a: argparse.Namespace) -> int:
+    s = Session(a.master, a.user)
+    try:
+        s.post("/api/v1/auth/logout")
+    except APIError:
+        pass                                  # an expired token is as logged out as it gets
+    s.forget_token()
+    print(f"Logged out {s.user}")
+    return 0
+
+
+def user_whoami(a: argparse.Namespace) -> int:
+    s = Session(a.master, a.user)
+    try:
+        print(f"You are logged in as user '{s.get('/api/v1/auth/user')['username']}'")
+    except APIError:
+        print(f"You are not logged in (user '{s.user}' has no valid session at {s.master})")
+        return 1
+    return 0
+
+
+def user_rename(a: argparse.Namespace) -> int:
+    Session(a.master, a.user).request("PATCH", f"/api/v1/users/{a.target_user}", {"username": a.new_username})
+    print(f"Renamed {a.target_user} to {a.new_username}")
+    return 0
+
+
+def user_link_agent(a: argparse.Namespace) -> int:
+    """Run this user's tasks under a given UID / GID on the agents (reference user.py:link_with_agent_user)."""
+    body = {"agent_user_group": {"uid": a.agent_uid, "gid": a.agent_gid, "user": a.agent_user, "group": a.agent_group}}
+    Session(a.master, a.user).request("PATCH", f"/api/v1/users/{a.det_username}", body)
+    return 0
+
+
+def show_version(a: argparse.Namespace) -> int:
+    import determined_b200
+
+    out = {"client": {"version": determined_b200.__version__}}
+    try:
+        info = Session(a.master, a.user).get("/api/v1/master")
+        out["master"] = {"version": info.get("version"), "cluster_id": info.get("cluster_id"), "master_address": Session(a.master, a.user).master}
+        if str(info.get("version")) != determined_b200.__version__:
+            print(f"warning: CLI version {determined_b200.__version__} differs from master version {info.get('version')}", file=sys.stderr)
+    except APIError as e:
+        out["master"] = {"unreachable": str(e)}
+    print(json.dumps(out, indent=2))
+    return 0
+
+
 def user_activate(active: bool):
     def run(a: argparse.Namespace) -> int:
         Session(a.master, a.user).request("PATCH", f"/api/v1/users/{a.username}", {"active": active})
@@ -510,6 +559,48 @@ def command_kill(kind: str):
     return run
 
 
+def command_logs(kind: str):
+    def run(a: argparse.Namespace) -> int:
+        s = Session(a.master, a.user)
+        seen = 0
+        while True:
+            for l in s.get(f"/api/v1/{kind}/{a.id}/logs?offset={seen}&limit=5000"):
+                print(l.get("message", ""), flush=True)
+                seen += 1
+            if not a.follow or s.get(f"/api/v1/{kind}/{a.id}")["state"] == "TERMINATED":
+                return 0
+            time.sleep(0.5)
+    return run
+
+
+def command_config(kind: str):
+    def run(a: argparse.Namespace) -> int:
+        c = Session(a.master, a.user).get(f"/api/v1/{kind}/{a.id}")
+        print(json.dumps(c.get("spec", {}).get("config") or c.get("spec", {}), indent=2))
+        return 0
+    return run
+
+
+def command_open(kind: str):
+    def run(a: argparse.Namespace) -> int:
+        s = Session(a.master, a.user)
+        c = s.get(f"/api/v1/{kind}/{a.id}")
+        if c["state"] == "TERMINATED":
+            print(f"{kind[:-1]} {a.id} has terminated", file=sys.stderr)
+            return 1
+        if kind == "shells":
+            print(f"ssh -o ProxyCommand='det -m {s.master} tunnel {a.id}' <user>@{a.id}      # or: det -m {s.master} tunnel {a.id} --listener PORT")
+            return 0
+        url = f"{s.master}/proxy/{a.id}/"
+        print(url)
+        if not a.no_browser:
+            import webbrowser
+
+            webbrowser.open(url)
+        return 0
+    return run
+
+
 # ---- parser ---------------------------------------------------------------------------------------------------------------
 def tunnel(a: argparse.Namespace) -> int:
     from . import tunnel as T
@@ -594,6 +685,11 @@ def build_parser() -> argparse.ArgumentParser:
     cmd(us, "list", user_list, aliases=["ls"])
     cmd(us, "create", user_create, A("username"), A("--admin", action="store_true"))
     cmd(us, "change-password", user_change_password, A("username"))
+    cmd(us, "logout", user_logout)
+    cmd(us, "whoami", user_whoami)
+    cmd(us, "rename", user_rename, A("target_user"), A("new_username"))
+    cmd(us, "link-with-agent-user", user_link_agent, A("det_username"), A("--agent-uid", type=int, required=True),
+        A("--agent-gid", type=int, required=True), A("--agent-user", required=True), A("--agent-group", required=True))
     cmd(us, "activate", user_activate(True), A("username"))
     cmd(us, "deactivate", user_activate(False), A("username"))
     tp = group("template", ["tpl"])
@@ -613,6 +709,12 @@ def build_parser() -> argparse.ArgumentParser:
             A("--proxy", action="store_true", help="give the task a port ({port} in the command, $DET_TASK_PORT) reachable at /proxy/<id>/ on the master"))
         cmd(g, "list", command_list(kind), aliases=["ls"])
         cmd(g, "kill", command_kill(kind), A("id"))
+        cmd(g, "logs", command_logs(kind), A("id"), A("--follow", "-f", action="store_true"))
+        cmd(g, "config", command_config(kind), A("id"))
+        if name != "cmd":
+            cmd(g, "open", command_open(kind), A("id"), A("--no-browser", action="store_true"))
+    ver = sub.add_parser("version", help="client and master versions")
+    ver.set_defaults(func=show_version)
     return p
 
 

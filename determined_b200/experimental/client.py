@@ -65,6 +65,17 @@ class Session:
         p.write_text(json.dumps(data))
         return self.token
 
+    def forget_token(self) -> None:
+        """Drop this (master, user) session from the token store."""
+        self.token = None
+        p = self._store()
+        try:
+            data = json.loads(p.read_text())
+            data.get(self.master, {}).pop(self.user, None)
+            p.write_text(json.dumps(data))
+        except Exception:
+            pass
+
     def request(self, method: str, path: str, body: Any = None, auth: bool = True, timeout: float = 60.0) -> Any:
         data = None if body is None else util.json_encode(body).encode()
         headers = {"Content-Type": "application/json"}

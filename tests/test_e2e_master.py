@@ -1,5 +1,6 @@
 """End-to-end on CPU: the C++ master daemon with artificial slots, experiments submitted through the SDK, real harness
 processes. Mirrors the reference's e2e_cpu tier (create → wait COMPLETED → verify metadata), which needs docker there."""
+import json
 import os
 import pathlib
 import subprocess
@@ -158,6 +159,33 @@ def test_cluster_endpoints_and_registry(master):
         time.sleep(0.1)
     assert c["state"] == "TERMINATED" and any("hello-from-command" in l["message"] for l in c["logs"])
     del m
+    # the same things through the `det` verbs the reference has: cmd logs / config, version, user whoami / rename / logout
+    import contextlib
+    import io
+
+    from determined_b200.cli.__main__ import main as det
+
+    def run(*argv):
+        buf = io.StringIO()
+        with contextlib.redirect_stdout(buf):
+            rc = det(["-m", master["url"], *argv])
+        return rc, buf.getvalue()
+
+    rc, out = run("cmd", "logs", str(cmd["id"]))
+    assert rc == 0 and "hello-from-command" in out
+    rc, out = run("cmd", "config", str(cmd["id"]))
+    assert rc == 0 and "echo" in out
+    rc, out = run("version")
+    assert rc == 0 and json.loads(out)["master"]["cluster_id"]
+    assert run("user", "login", "determined")[0] == 0
+    rc, out = run("user", "whoami")
+    assert rc == 0 and "determined" in out
+    assert run("user", "create", "alice")[0] == 0 and run("user", "rename", "alice", "alicia")[0] == 0
+    names = [u["username"] for u in s.get("/api/v1/users")]
+    assert "alicia" in names and "alice" not in names
+    assert run("user", "link-with-agent-user", "alicia", "--agent-uid", "1001", "--agent-gid", "1002", "--agent-user", "al", "--agent-group", "staff")[0] == 0
+    assert s.get("/api/v1/users/alicia")["agent_user_group"] == {"uid": 1001, "gid": 1002, "user": "al", "group": "staff"}
+    assert run("user", "logout")[0] == 0
 
 
 def test_adaptive_search_survives_random_failures(master):
