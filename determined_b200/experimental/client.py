@@ -157,7 +157,38 @@ class CheckpointState(enum.Enum):
     DELETED = 4
 
 
+class ModelFramework(enum.Enum):
+    PYTORCH = 1
+    TENSORFLOW = 2
+
+
 class Checkpoint:
+    @staticmethod
+    def parse_metadata(directory: str) -> Dict[str, Any]:
+        """``metadata.json`` of a downloaded checkpoint (reference ``_checkpoint.py:parse_metadata``)."""
+        with open(os.path.join(directory, "metadata.json")) as f:
+            return json.load(f)
+
+    @staticmethod
+    def get_type(metadata: Dict[str, Any]) -> ModelFramework:
+        """Which framework wrote the checkpoint: ``framework`` starts with ``torch`` / ``tensorflow``; without the key,
+        the ``format`` decides (``pickle`` / ``cloudpickle`` are PyTorch's)."""
+        fw = str(metadata.get("framework") or "")
+        if fw.startswith("torch"):
+            return ModelFramework.PYTORCH
+        if fw.startswith("tensorflow"):
+            return ModelFramework.TENSORFLOW
+        if str(metadata.get("format") or "") in ("pickle", "cloudpickle"):
+            return ModelFramework.PYTORCH
+        if str(metadata.get("format") or "") in ("saved_model", "h5"):
+            return ModelFramework.TENSORFLOW
+        raise AssertionError("unknown checkpoint format: " + json.dumps({k: metadata.get(k) for k in ("framework", "format")}))
+
+    @classmethod
+    def from_json(cls, data: Dict[str, Any], session: Optional[Session] = None) -> "Checkpoint":
+        """From the master's JSON of a checkpoint (``GET /api/v1/checkpoints/<uuid>`` or a model version's ``checkpoint``)."""
+        return cls(session or Session(), data)
+
     def __init__(self, session: Session, data: Dict[str, Any]) -> None:
         self._session = session
         self.uuid = data["uuid"]
@@ -360,9 +391,22 @@ class Model:
         self.metadata.update(metadata)
         self._session.request("PATCH", f"/api/v1/models/{self.name}", {"metadata": self.metadata})
 
+    def remove_metadata(self, keys: List[str]) -> None:
+        for k in keys:
+            self.metadata.pop(k, None)
+        self._session.request("PATCH", f"/api/v1/models/{self.name}", {"metadata": self.metadata})
+
     def set_description(self, description: str) -> None:
         self.description = description
         self._session.request("PATCH", f"/api/v1/models/{self.name}", {"description": description})
+
+    def to_json(self) -> Dict[str, Any]:
+        return {"name": self.name, "description": self.description, "metadata": self.metadata, "creation_time": self.creation_time,
+                "last_updated_time": self.last_updated_time}
+
+    @classmethod
+    def from_json(cls, data: Dict[str, Any], session: Optional[Session] = None) -> "Model":
+        return cls(session or Session(), data)
 
 
 class Determined:

@@ -62,3 +62,25 @@ def test_cli_doc_is_generated_from_the_parser():
     root = pathlib.Path(__file__).resolve().parent.parent
     out = subprocess.run([sys.executable, str(root / "scripts" / "gen_cli_doc.py"), "--check"], capture_output=True, text=True)
     assert out.returncode == 0, out.stdout + out.stderr
+
+
+def test_sdk_checkpoint_and_model_helpers(tmp_path):
+    """Static helpers of the SDK objects (reference common/determined_common/experimental/checkpoint/_checkpoint.py,
+    model.py): metadata.json parsing, framework detection, JSON round trips."""
+    import json
+
+    from determined_b200.experimental.client import Checkpoint, Model, ModelFramework, Session
+
+    (tmp_path / "metadata.json").write_text(json.dumps({"framework": "torch-2.11.0", "format": "cloudpickle", "trial_id": 3}))
+    meta = Checkpoint.parse_metadata(str(tmp_path))
+    assert meta["trial_id"] == 3 and Checkpoint.get_type(meta) is ModelFramework.PYTORCH
+    assert Checkpoint.get_type({"format": "saved_model"}) is ModelFramework.TENSORFLOW
+    assert Checkpoint.get_type({"framework": "tensorflow-1.15"}) is ModelFramework.TENSORFLOW
+    with pytest.raises(AssertionError):
+        Checkpoint.get_type({"format": "onnx"})
+    s = Session("127.0.0.1:1")
+    c = Checkpoint.from_json({"uuid": "u-1", "trial_id": 3, "experiment_id": 2, "total_batches": 40, "state": "COMPLETED",
+                              "resources": {"state_dict.pth": 10}, "framework": "torch-2.11.0", "format": "cloudpickle"}, s)
+    assert (c.uuid, c.trial_id, c.batch_number, c.state.name) == ("u-1", 3, 40, "COMPLETED")
+    m = Model.from_json({"name": "xor", "description": "d", "metadata": {"a": 1}}, s)
+    assert Model.from_json(m.to_json(), s).to_json() == m.to_json() and m.metadata == {"a": 1}

@@ -150,6 +150,9 @@ def test_cluster_endpoints_and_registry(master):
     assert s.get("/api/v1/templates/small")["config"]["scheduling_unit"] == 7
     m = d.create_model("xor", "demo")
     assert [x.name for x in d.get_models()] == ["xor"]
+    m.add_metadata({"team": "a", "stage": "dev"})
+    m.remove_metadata(["stage"])
+    assert d.get_model("xor").metadata == {"team": "a"}
     assert s.post("/api/v1/auth/login", {"username": "determined", "password": ""})["token"]
     cmd = s.post("/api/v1/commands", {"argv": ["sh", "-c", "echo hello-from-command"], "description": "echo"})
     for _ in range(50):
