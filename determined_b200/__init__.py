@@ -12,6 +12,7 @@ from . import errors
 from ._train_context import NativeContext, TrialContext
 from ._trial import Trial
 from ._trial_controller import CallbackTrialController, LoopTrialController, TrialController
+from .utils import util
 
 __version__ = "0.13.10.dev0+b200.1"
 

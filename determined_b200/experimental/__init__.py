@@ -6,7 +6,8 @@ __all__ = ["create", "create_trial_instance", "init_native", "test_one_batch", "
 
 
 def __getattr__(name):  # lazy: the SDK client pulls in HTTP machinery only when used
-    if name in ("Determined", "Checkpoint", "ExperimentReference", "TrialReference", "Model"):
+    if name in ("Determined", "Checkpoint", "ExperimentReference", "TrialReference", "Model", "ModelSortBy", "ModelOrderBy",
+                "ModelFramework", "CheckpointState"):
         from . import client
 
         return getattr(client, name)

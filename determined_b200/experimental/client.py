@@ -365,6 +365,22 @@ class ExperimentReference:
         return [Checkpoint(self._session, self._session.get(f"/api/v1/checkpoints/{c['uuid']}")) for _, c in scored[:limit]]
 
 
+class ModelSortBy(enum.Enum):
+    """Field to sort a list of models on (reference ``experimental/model.py:10-27``)."""
+    UNSPECIFIED = 0
+    NAME = 1
+    DESCRIPTION = 2
+    CREATION_TIME = 4
+    LAST_UPDATED_TIME = 5
+
+
+class ModelOrderBy(enum.Enum):
+    ASCENDING = 1
+    ASC = 1
+    DESCENDING = 2
+    DESC = 2
+
+
 class Model:
     def __init__(self, session: Session, data: Dict[str, Any]) -> None:
         self._session = session
@@ -443,5 +459,14 @@ class Determined:
     def get_model(self, name: str) -> Model:
         return Model(self._session, self._session.get(f"/api/v1/models/{name}"))
 
-    def get_models(self) -> List[Model]:
-        return [Model(self._session, m) for m in self._session.get("/api/v1/models")]
+    def get_models(self, sort_by: ModelSortBy = ModelSortBy.NAME, order_by: ModelOrderBy = ModelOrderBy.ASCENDING,
+                   name: str = "", description: str = "") -> List[Model]:
+        """Models of the registry; ``name`` / ``description`` keep the ones containing that text (case-insensitive)."""
+        models = [Model(self._session, m) for m in self._session.get("/api/v1/models")]
+        if name:
+            models = [m for m in models if name.lower() in m.name.lower()]
+        if description:
+            models = [m for m in models if description.lower() in (m.description or "").lower()]
+        key = {ModelSortBy.DESCRIPTION: lambda m: m.description or "", ModelSortBy.CREATION_TIME: lambda m: m.creation_time or "",
+               ModelSortBy.LAST_UPDATED_TIME: lambda m: m.last_updated_time or ""}.get(sort_by, lambda m: m.name)
+        return sorted(models, key=key, reverse=order_by.value == ModelOrderBy.DESCENDING.value)
