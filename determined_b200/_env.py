@@ -25,6 +25,18 @@ class ExperimentConfig(dict):
     def native_parallel_enabled(self) -> bool:
         return bool(self.get("resources", {}).get("native_parallel", False))
 
+    def native_enabled(self) -> bool:
+        """The experiment was submitted through the native API: the harness runs ``internal.native.command``."""
+        return bool((self.get("internal") or {}).get("native"))
+
+    def experiment_seed(self) -> int:
+        return int((self.get("reproducibility") or {}).get("experiment_seed", 0) or 0)
+
+    def horovod_optional_args(self) -> list:
+        """Extra launcher arguments smuggled in ``data.__det_dtrain_args`` (reference ``_experiment_config.py:8-9``); kept for
+        config compatibility — there is no horovodrun here to pass them to."""
+        return list((self.get("data") or {}).get("__det_dtrain_args", []))
+
     def slots_per_trial(self) -> int:
         return int(self.get("resources", {}).get("slots_per_trial", 1))
 

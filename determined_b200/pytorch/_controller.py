@@ -224,6 +224,11 @@ class PyTorchTrialController(LoopTrialController):
             else:
                 raise AssertionError(f"unexpected workload kind {w.kind}")
 
+    def get_epoch_idx(self, batch_id: int) -> int:
+        """Epoch a batch index falls into (reference ``_pytorch_trial.py:289-290``)."""
+        n = self.context._epoch_len
+        return batch_id // n if n else 0
+
     # ---- training -----------------------------------------------------------------------------------------------------
     def _auto_step_lr_schedulers(self, batch_idx: int) -> None:
         for sched in self.context.lr_schedulers:
