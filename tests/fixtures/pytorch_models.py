@@ -214,3 +214,20 @@ class LegacyXorTrial(dp.PyTorchTrial):
 
     def build_validation_data_loader(self):
         return dp.DataLoader(_XorData(32, 2), batch_size=self.context.get_per_slot_batch_size())
+
+
+class XorTrialNonScalarValidation(XorTrial):
+    """``evaluate_full_dataset`` that also returns a non-scalar (the per-example predictions), as the reference's
+    ``XORTrialWithNonScalarValidation`` (``tests/experiment/fixtures/pytorch_xor_model.py:193-240``)."""
+
+    evaluate_batch = None  # type: ignore[assignment]   exactly one of the two evaluation methods may be defined
+
+    def evaluate_full_dataset(self, data_loader):
+        preds, err, n = [], 0.0, 0
+        for batch in data_loader:
+            batch = self.context.to_device(batch)
+            out = self.model(batch["data"])
+            preds.append(out.detach().cpu())
+            err += float(((out > 0.5).float() != batch["label"]).float().sum())
+            n += out.shape[0]
+        return {"binary_error": err / max(n, 1), "predictions": torch.cat(preds).numpy()}

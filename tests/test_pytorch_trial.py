@@ -232,3 +232,53 @@ def test_native_parallel_off_on_cpu():
     tv = TrainAndValidate()
     c = make_controller(M.XorTrial, XOR_HP, tv.send(steps=1), exp_config={"resources": {"native_parallel": True}})
     assert c.context.native_parallel_gpus() == 0 and not isinstance(c.context.models[0], torch.nn.DataParallel)
+
+
+def test_nonscalar_validation_metrics_pass_through():
+    """A validation that returns an array next to its scalars (reference test_xor_nonscalar_validation)."""
+    tv = TrainAndValidate()
+    make_controller(M.XorTrialNonScalarValidation, XOR_HP, tv.send(steps=4, validation_freq=4)).run()
+    v = tv.validation_metrics[0]
+    assert 0.0 <= v["binary_error"] <= 1.0
+    assert np.asarray(v["predictions"]).shape == (32, 1)
+
+
+def test_restore_into_a_different_architecture_fails(tmp_path: pathlib.Path):
+    """A checkpoint of hidden_size 4 must not load into hidden_size 3 (reference test_restore_invalid_checkpoint)."""
+    ckpt = tmp_path / "ckpt"
+    make_controller(M.XorTrial, XOR_HP, TrainAndValidate().send(steps=1, validation_freq=1, checkpoint_dir=ckpt)).run()
+    with pytest.raises(RuntimeError, match="size mismatch"):
+        make_controller(M.XorTrial, dict(XOR_HP, hidden_size=3), TrainAndValidate().send(steps=1), load_path=ckpt)
+
+
+def test_workloads_of_varying_length():
+    """RUN_STEP workloads of 1, 2, ... 9 batches: each answers with exactly that many batch metrics and the batch index
+    keeps counting across them (reference test_variable_workload_size)."""
+    from determined_b200 import workload as wl
+
+    seen = []
+
+    def stream():
+        icpt = wl.WorkloadResponseInterceptor()
+        total = 0
+        for step_id in range(1, 10):
+            yield from icpt.send(wl.train_workload(step_id, num_batches=step_id, total_batches_processed=total), [])
+            bm = icpt.result()["metrics"]["batch_metrics"]
+            assert len(bm) == step_id
+            seen.extend(bm)
+            total += step_id
+        yield from icpt.send(wl.terminate_workload(10), [])
+
+    make_controller(M.XorTrial, XOR_HP, stream()).run()
+    assert len(seen) == 45 and all(np.isfinite(m["loss"]) for m in seen)
+
+
+def test_create_trial_instance_outside_training(tmp_path: pathlib.Path):
+    """`det.experimental.create_trial_instance`: a trial object with restored weights, no workloads involved."""
+    ckpt = tmp_path / "ckpt"
+    tv = TrainAndValidate()
+    c = make_controller(M.XorTrial, XOR_HP, tv.send(steps=2, validation_freq=2, checkpoint_dir=ckpt))
+    c.run()
+    trial = experimental.create_trial_instance(M.XorTrial, str(ckpt), config={"hyperparameters": XOR_HP}, hparams=XOR_HP)
+    for a, b in zip(trial.model.parameters(), c.trial.model.parameters()):
+        assert torch.equal(a.detach().cpu(), b.detach().cpu())
