@@ -22,6 +22,7 @@
 #include <functional>
 #include <map>
 #include <memory>
+#include <condition_variable>
 #include <mutex>
 #include <regex>
 #include <sstream>
@@ -334,11 +335,15 @@ class ContainerManager {
     }
     on_event_({spec.container_id, "RUNNING", 0, ""});
     const std::string cid = spec.container_id;
-    std::thread([this, cid, fd = out_pipe[0]] { pump(cid, fd, "stdout"); }).detach();
-    std::thread([this, cid, fd = err_pipe[0]] { pump(cid, fd, "stderr"); }).detach();
-    std::thread([this, cid, pid] {
+    // The exit is reported after the task's last output: the reaper waits for both pumps to reach end-of-file (bounded — a
+    // grandchild that kept the pipe open must not hold the exit back) so "TERMINATED" never overtakes the final log lines.
+    auto drain = std::make_shared<Drain>();
+    std::thread([this, cid, drain, fd = out_pipe[0]] { pump(cid, fd, "stdout"); drain->done(); }).detach();
+    std::thread([this, cid, drain, fd = err_pipe[0]] { pump(cid, fd, "stderr"); drain->done(); }).detach();
+    std::thread([this, cid, pid, drain] {
       int status = 0;
       waitpid(pid, &status, 0);
+      drain->wait_ms(2000);
       ContainerEvent ev{cid, "TERMINATED", 0, ""};
       if (WIFEXITED(status)) { ev.exit_code = WEXITSTATUS(status); if (ev.exit_code) ev.failure = "container failed with non-zero exit code: " + std::to_string(ev.exit_code); }
       else if (WIFSIGNALED(status)) { ev.exit_code = 128 + WTERMSIG(status); ev.failure = std::string("container killed by signal ") + strsignal(WTERMSIG(status)); }
@@ -369,6 +374,13 @@ class ContainerManager {
   }
 
  private:
+  struct Drain {
+    std::mutex mu;
+    std::condition_variable cv;
+    int open = 2;
+    void done() { std::lock_guard<std::mutex> g(mu); if (--open == 0) cv.notify_all(); }
+    void wait_ms(int ms) { std::unique_lock<std::mutex> g(mu); cv.wait_for(g, std::chrono::milliseconds(ms), [this] { return open == 0; }); }
+  };
   void pump(const std::string& cid, int fd, const std::string& stdtype) {
     static const std::regex rank_re("^\\[rank=(\\d+)\\] ?(.*)$");
     std::string pending;

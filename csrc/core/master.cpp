@@ -136,10 +136,10 @@ class CommandActor : public Actor {
       spec.cwd = spec_["cwd"].str_or("");
       for (auto& kv : spec_["env"].obj()) spec.env[kv.first] = kv.second.as_string();
       for (auto& d : a["devices"].arr()) spec.devices.push_back(Device{static_cast<int>(d["id"].as_int()), d["brand"].as_string(), d["uuid"].as_string(), d["type"].as_string()});
-      if (spec_["config"].is_object()) {   // commands / notebooks / shells take bind_mounts, environment and resources like trials do
+      if (spec_["config"].is_object() || spec_["has_context"].as_bool(false)) {   // commands / notebooks / shells take bind_mounts, environment and resources like trials do
         const std::string slot_type = (!spec.devices.empty() && spec.devices[0].type == "gpu" && spec.devices[0].brand != "Artificial") ? "gpu" : "cpu";
         std::string warning;
-        const std::string bad = apply_task_config(spec_["config"], slot_type, 0, false, spec.env, spec.argv, &warning);
+        const std::string bad = apply_task_config(spec_["config"], slot_type, 0, spec_["has_context"].as_bool(false), spec.env, spec.argv, &warning);
         if (!bad.empty()) m_->log("error", task_id_ + ": " + bad);
         if (!warning.empty()) m_->log("warn", task_id_ + ": " + warning);
       }
@@ -330,23 +330,29 @@ void Master::route_log(const LogLine& l) {
   else if (owner) system.tell(owner, "log", row);
 }
 
-long long Master::create_experiment(const Json& config, const Json& model_definition, long long parent_id, bool activate, const std::string& owner) {
-  const long long id = store.next_id("experiments");
-  const std::string dir = model_def_dir(id);
+// A submitted context ([{"path": "...", "content": "<text>", "mode": 0644}]; directories are implied by paths) laid out under
+// `dir`. Paths that would leave the directory are dropped.
+void Master::write_context_files(const std::string& dir, const Json& files) {
   mkdirs(dir);
-  // model_definition: [{"path": "...", "content": "<text>", "mode": 0644}]; directories are implied by paths
-  for (auto& f : model_definition.arr()) {
-    const std::string rel = f["path"].as_string();
+  if (!files.is_array()) return;
+  for (auto& f : files.arr()) {
+    const std::string rel = f["path"].str_or("");
     if (rel.empty() || rel.find("..") != std::string::npos || rel[0] == '/') continue;
     const std::string full = dir + "/" + rel;
     auto slash = full.rfind('/');
     if (slash != std::string::npos) mkdirs(full.substr(0, slash));
     if (f["type"].str_or("file") == "dir") { mkdirs(full); continue; }
     std::ofstream out(full, std::ios::binary);
-    out << f["content"].as_string();
+    out << f["content"].str_or("");
     out.close();
     if (f["mode"].is_number()) chmod(full.c_str(), static_cast<mode_t>(f["mode"].as_int()));
   }
+}
+
+long long Master::create_experiment(const Json& config, const Json& model_definition, long long parent_id, bool activate, const std::string& owner) {
+  const long long id = store.next_id("experiments");
+  const std::string dir = model_def_dir(id);
+  write_context_files(dir, model_definition);
   store.put("experiments", id, obj({{"id", id}, {"state", activate ? "ACTIVE" : "PAUSED"}, {"config", config}, {"parent_id", parent_id > 0 ? Json(parent_id) : Json()},
                                     {"start_time", now_rfc3339()}, {"end_time", Json()}, {"archived", false}, {"progress", 0.0}, {"owner", owner},
                                     {"description", config["description"]}, {"labels", config["labels"]}, {"best_validation", Json()}}));

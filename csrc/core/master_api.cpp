@@ -9,6 +9,7 @@
 
 #include "lttb.hpp"
 #include "master.hpp"
+#include "task_spec.hpp"
 
 namespace det {
 
@@ -790,10 +791,42 @@ tick();setInterval(tick,2000);
     const std::string type = std::string(kind).substr(0, strlen(kind) - 1);
     http.route("POST", std::string("/api/v1/") + kind, [m, type](const HttpRequest& r) {
       Json b = r.json();
-      if (!b["argv"].is_array() || b["argv"].size() == 0) return HttpResponse::error(400, "argv (list of strings) is required");
+      // task config: template <- submitted config (reference: command configs take a template the way experiments do);
+      // resources.slots / description / entrypoint in it stand in for the top-level fields when those are absent
+      Json config = Json::object();
+      if (b["template"].is_string()) {
+        Json tmpl = m->store.get("templates", b["template"].as_string())["config"];
+        if (tmpl.is_null()) return HttpResponse::error(404, "template " + b["template"].as_string() + " not found");
+        if (tmpl.is_object()) config = tmpl.deep_copy();
+      }
+      if (b["config"].is_object()) json_merge(config, b["config"]);
+      else if (!b["config"].is_null()) return HttpResponse::error(400, "config must be a mapping");
+      static const std::set<std::string> known = {"description", "entrypoint", "resources", "environment", "bind_mounts", "debug", "work_dir"};
+      const Json& cc = config;
+      for (auto& kv : cc.obj())
+        if (!known.count(kv.first)) return HttpResponse::error(400, "unknown field in task config: '" + kv.first + "'");
+      Json argv = b["argv"];
+      if ((!argv.is_array() || argv.size() == 0) && cc["entrypoint"].is_array()) argv = cc["entrypoint"];
+      if (!argv.is_array() || argv.size() == 0) return HttpResponse::error(400, "argv (list of strings) is required");
+      for (auto& a : argv.arr())
+        if (!a.is_string()) return HttpResponse::error(400, "argv (list of strings) is required");
+      {
+        std::string bad;
+        bind_mount_lines(cc["bind_mounts"], &bad);
+        if (!bad.empty()) return HttpResponse::error(400, bad);
+      }
+      const long long slots = b["slots"].is_number() ? b["slots"].as_int(0) : cc["resources"]["slots"].as_int(0);
+      if (slots < 0) return HttpResponse::error(400, "resources.slots must be >= 0");
       const long long id = m->store.next_id("commands");
-      Json spec = obj({{"type", type}, {"description", b["description"].str_or(type)}, {"slots", b["slots"].as_int(0)}, {"argv", b["argv"]},
-                       {"env", b["env"].is_object() ? b["env"] : Json::object()}, {"cwd", b["cwd"].str_or("")}, {"config", b["config"]}});
+      std::string cwd = b["cwd"].str_or(cc["work_dir"].str_or(""));
+      const bool has_context = b["context"].is_array() && b["context"].size() > 0;
+      if (has_context || cwd.empty()) {   // every task gets a working directory of its own (relative bind mounts land in it); uploaded
+        const std::string dir = m->command_context_dir(id);   // files are laid out there, and a startup-hook.sh among them runs first
+        m->write_context_files(dir, b["context"]);
+        if (cwd.empty()) cwd = dir;
+      }
+      Json spec = obj({{"type", type}, {"description", b["description"].str_or(cc["description"].str_or(type))}, {"slots", slots}, {"argv", argv},
+                       {"env", b["env"].is_object() ? b["env"] : Json::object()}, {"cwd", cwd}, {"config", cc.size() ? config : Json()}, {"has_context", has_context}});
       const bool service = b.contains("proxy") ? b["proxy"].as_bool(false) : (type == "notebook" || type == "tensorboard");
       if (service) {
         spec["proxy_port"] = b["port"].as_int(0) > 0 ? b["port"].as_int() : static_cast<long long>(free_tcp_port());

@@ -50,7 +50,10 @@ def _table(rows: List[List[Any]], headers: List[str]) -> str:
 
 
 def _load_config(path: str, overrides: Optional[List[str]] = None) -> Dict[str, Any]:
-    cfg = yaml.safe_load(pathlib.Path(path).read_text()) or {}
+    return _apply_overrides(yaml.safe_load(pathlib.Path(path).read_text()) or {}, overrides)
+
+
+def _apply_overrides(cfg: Dict[str, Any], overrides: Optional[List[str]] = None) -> Dict[str, Any]:
     for ov in overrides or []:  # --config key.sub=value
         key, _, val = ov.partition("=")
         cur = cfg
@@ -517,15 +520,48 @@ def model_register_version(a: argparse.Namespace) -> int:
 def command_run(kind: str):
     def run(a: argparse.Namespace) -> int:
         s = Session(a.master, a.user)
-        argv = a.command if getattr(a, "command", None) else {
+        argv = list(a.command) if getattr(a, "command", None) else {
+            "commands": [],     # the entrypoint then comes from --config-file / --template
             "notebooks": [sys.executable, "-m", "jupyter", "lab", "--ip=127.0.0.1", "--no-browser", "--port={port}", "--ServerApp.token=",
                           "--ServerApp.base_url=" + "{prefix}"],
             "shells": ["/bin/sh", "-c", "sleep infinity"],
             "tensorboards": [sys.executable, "-m", "determined_b200.exec.tensorboard"] + [str(x) for x in getattr(a, "experiment_ids", [])],
         }[kind]
-        body = {"argv": argv, "slots": getattr(a, "slots", 0), "description": " ".join(argv)[:60]}
-        if getattr(a, "proxy", False):
-            body["proxy"] = True
+        if argv and argv[0] == "--":
+            argv = argv[1:]
+        if len(argv) == 1 and any(ch.isspace() for ch in argv[0]):      # det cmd run "sleep 3; touch x": one shell line
+            argv = ["/bin/sh", "-c", argv[0]]
+        body: Dict[str, Any] = {"argv": argv} if argv else {}
+        # task config: --config-file, then --config key=value overrides, then --volume host:container[:ro] bind mounts; the
+        # master merges it over --template (reference: cli/command.py parse_config + "--template")
+        config: Dict[str, Any] = {}
+        if getattr(a, "config_file", None):
+            config = _load_config(a.config_file, a.config)
+        elif getattr(a, "config", None):
+            config = _apply_overrides({}, a.config)
+        for vol in getattr(a, "volume", None) or []:
+            parts = vol.split(":")
+            if len(parts) not in (2, 3) or (len(parts) == 3 and parts[2] not in ("ro", "rw")):
+                print(f"--volume wants HOST_PATH:CONTAINER_PATH[:ro], not {vol!r}", file=sys.stderr)
+                return 1
+            config.setdefault("bind_mounts", []).append({"host_path": os.path.abspath(parts[0]), "container_path": parts[1],
+                                                          "read_only": len(parts) == 3 and parts[2] == "ro"})
+        if config:
+            body["config"] = config
+        if getattr(a, "template", None):
+            body["template"] = a.template
+        if getattr(a, "slots", None) is not None:
+            body["slots"] = a.slots
+        if not config.get("description") and argv:
+            body["description"] = " ".join(argv)[:60]
+        if getattr(a, "context", None):
+            from ..experimental.client import read_context
+
+            try:
+                body["context"] = read_context(a.context)
+            except ValueError as e:
+                print(f"cannot package the context directory: {e}", file=sys.stderr)
+                return 1
         out = s.post(f"/api/v1/{kind}", body)
         print(f"Started {kind[:-1]} {out['id']}")
         if out["spec"].get("proxy_port"):
@@ -539,7 +575,9 @@ def command_run(kind: str):
                 print(l["message"], flush=True)
             seen = len(c["logs"])
             if c["state"] == "TERMINATED":
-                return int(c.get("exit_code") or 0)
+                rc = int(c.get("exit_code") or 0)
+                print(f"{kind[:-1]} {out['id']} exited successfully" if rc == 0 else f"finished {kind[:-1]} {out['id']}: task failed with exit code {rc}")
+                return rc
             time.sleep(0.5)
     return run
 
@@ -705,7 +743,10 @@ def build_parser() -> argparse.ArgumentParser:
     for name, kind in (("cmd", "commands"), ("notebook", "notebooks"), ("shell", "shells"), ("tensorboard", "tensorboards")):
         g = group(name)
         extra = [A("command", nargs=argparse.REMAINDER)] if name == "cmd" else ([A("experiment_ids", nargs="*", type=int)] if name == "tensorboard" else [])
-        cmd(g, "run" if name == "cmd" else "start", command_run(kind), *extra, A("--slots", type=int, default=0), A("--detach", "-d", action="store_true"),
+        cmd(g, "run" if name == "cmd" else "start", command_run(kind), *extra, A("--slots", type=int, default=None), A("--detach", "-d", action="store_true"),
+            A("--config-file"), A("--config", action="append", help="key.sub=value override of the task config"), A("--template"),
+            A("--context", "-c", help="directory to upload; becomes the task's working directory"),
+            A("--volume", "-v", action="append", help="HOST_PATH:CONTAINER_PATH[:ro] bind mount"),
             A("--proxy", action="store_true", help="give the task a port ({port} in the command, $DET_TASK_PORT) reachable at /proxy/<id>/ on the master"))
         cmd(g, "list", command_list(kind), aliases=["ls"])
         cmd(g, "kill", command_kill(kind), A("id"))

@@ -137,6 +137,8 @@ def read_context(directory: str, limit: int = constants.MAX_CONTEXT_SIZE) -> Lis
             if ignored(rel, False):
                 continue
             p = pathlib.Path(cur) / n
+            if total + p.stat().st_size > limit:       # before reading it: the file alone may not fit in memory
+                raise ValueError(f"model definition exceeds {util.sizeof_fmt(limit)}; use .detignore to exclude large files")
             try:
                 content = p.read_text()
             except UnicodeDecodeError:
