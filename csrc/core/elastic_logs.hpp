@@ -7,6 +7,7 @@
 // number the master stamps on every row, `from` / `size` pagination — the same position-based contract the file store
 // gives the REST route (`GET /api/v1/trials/:id/logs?offset=&limit=`).
 #pragma once
+#include <algorithm>
 #include <atomic>
 #include <string>
 #include <vector>
@@ -38,28 +39,35 @@ class ElasticLogs {
   }
 
   std::vector<Json> read(long long trial_id, size_t offset, size_t limit, std::string* err) {
-    Json q = Json::object();
-    q["from"] = static_cast<long long>(offset);
-    q["size"] = static_cast<long long>(limit > 10000 ? 10000 : limit);
-    Json term = Json::object();
-    term["trial_id"] = trial_id;
-    Json query = Json::object();
-    query["term"] = term;
-    q["query"] = query;
-    Json sort_field = Json::object();
-    sort_field["seq"] = "asc";
-    Json sort = Json::array();
-    sort.push_back(sort_field);
-    q["sort"] = sort;
-    std::string out;
-    const int st = http_request(host_, port_, "POST", "/" + index_ + "/_search", q.dump(), &out, 30);
     std::vector<Json> rows;
-    if (st < 200 || st >= 300) { if (err) *err = "elasticsearch _search answered " + std::to_string(st); return rows; }
-    try {
-      Json r = Json::parse(out);
-      for (auto& h : r["hits"]["hits"].arr()) rows.push_back(h["_source"]);
-    } catch (const std::exception& e) {
-      if (err) *err = std::string("elasticsearch _search: ") + e.what();
+    const size_t page = 10000;          // one _search window
+    while (rows.size() < limit) {
+      const size_t want = std::min(page, limit - rows.size());
+      Json q = Json::object();
+      q["from"] = static_cast<long long>(offset + rows.size());
+      q["size"] = static_cast<long long>(want);
+      Json term = Json::object();
+      term["trial_id"] = trial_id;
+      Json query = Json::object();
+      query["term"] = term;
+      q["query"] = query;
+      Json sort_field = Json::object();
+      sort_field["seq"] = "asc";
+      Json sort = Json::array();
+      sort.push_back(sort_field);
+      q["sort"] = sort;
+      std::string out;
+      const int st = http_request(host_, port_, "POST", "/" + index_ + "/_search", q.dump(), &out, 30);
+      if (st < 200 || st >= 300) { if (err) *err = "elasticsearch _search answered " + std::to_string(st); return rows; }
+      size_t got = 0;
+      try {
+        Json r = Json::parse(out);
+        for (auto& h : r["hits"]["hits"].arr()) { rows.push_back(h["_source"]); ++got; }
+      } catch (const std::exception& e) {
+        if (err) *err = std::string("elasticsearch _search: ") + e.what();
+        return rows;
+      }
+      if (got < want) break;
     }
     return rows;
   }

@@ -323,9 +323,19 @@ void Master::route_log(const LogLine& l) {
     auto it = container_agent_.find(l.container_id);
     if (it != container_agent_.end()) agent_id = it->second;
   }
+  // level: what the line itself says ("WARNING: ...", "[ERROR] ...", python logging's "LEVEL:name:message"), INFO otherwise
+  std::string level = "INFO";
+  {
+    size_t at = 0;
+    while (at < l.message.size() && (l.message[at] == '[' || l.message[at] == ' ')) ++at;
+    for (const char* name : {"TRACE", "DEBUG", "INFO", "WARNING", "ERROR", "CRITICAL"}) {
+      const size_t n = strlen(name);
+      if (l.message.compare(at, n, name) == 0 && at + n < l.message.size() && (l.message[at + n] == ':' || l.message[at + n] == ']')) { level = name; break; }
+    }
+  }
   Json row = obj({{"trial_id", trial_id}, {"container_id", l.container_id}, {"timestamp", now_rfc3339()}, {"stdtype", l.stdtype},
                   {"rank", l.rank >= 0 ? Json(l.rank) : Json()}, {"message", l.message}, {"source", "agent"}, {"agent_id", agent_id},
-                  {"level", l.stdtype == "stderr" ? "INFO" : "INFO"}});
+                  {"level", level}});
   if (trial_id > 0) system.tell(logger, "log", row);
   else if (owner) system.tell(owner, "log", row);
 }
@@ -424,7 +434,10 @@ bool Master::check_auth(const HttpRequest& req, std::string* user) {
   if (it != req.headers.end() && it->second.rfind("Bearer ", 0) == 0) token = it->second.substr(7);
   if (!token.empty()) {
     Json s = store.get("sessions", token);
-    if (!s.is_null()) { if (user) *user = s["username"].as_string(); return true; }
+    if (!s.is_null()) {     // a session of a deactivated (or removed) user is no session
+      const Json u = store.get("users", s["username"].as_string());
+      if (!u.is_null() && u["active"].as_bool(true)) { if (user) *user = s["username"].as_string(); return true; }
+    }
   }
   if (user) *user = "determined";
   return !cfg.auth_required;

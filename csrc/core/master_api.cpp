@@ -258,7 +258,17 @@ tick();setInterval(tick,2000);
     const bool on = m->cfg.telemetry.is_object() && m->cfg.telemetry["enabled"].as_bool(false);
     return ok(obj({{"enabled", on}, {"segment_key", ""}, {"sink", on ? m->cfg.telemetry["sink"].str_or(m->cfg.data_dir + "/telemetry.jsonl") : std::string()}}));
   });
-  http.route("POST", "/api/v1/users", [m](const HttpRequest& r) {
+  // User management follows the reference (master/internal/user/service.go): creating users and changing anyone's
+  // active / admin / agent-user fields or name is for administrators; a password may also be changed by its owner. Enforced
+  // whenever the master requires authentication (without it every caller is the default user anyway).
+  auto is_admin = [m](const HttpRequest& r, std::string* who) {
+    m->check_auth(r, who);
+    if (!m->cfg.auth_required) return true;
+    return m->store.get("users", *who)["admin"].as_bool(false);
+  };
+  http.route("POST", "/api/v1/users", [m, is_admin](const HttpRequest& r) {
+    std::string who;
+    if (!is_admin(r, &who)) return HttpResponse::error(403, "only an administrator can create users");
     Json b = r.json();
     const std::string name = b["username"].as_string();
     if (name.empty()) return HttpResponse::error(400, "username required");
@@ -266,10 +276,16 @@ tick();setInterval(tick,2000);
     m->store.put("users", name, obj({{"username", name}, {"admin", b["admin"].as_bool(false)}, {"active", true}, {"password_hash", ""}, {"salt", ""}}));
     return ok(obj({{"username", name}}));
   });
-  http.route("PATCH", "/api/v1/users/:name", [m](const HttpRequest& r) {
+  http.route("PATCH", "/api/v1/users/:name", [m, is_admin](const HttpRequest& r) {
     Json u = m->store.get("users", r.params.at("name"));
     if (u.is_null()) return not_found("user");
     Json b = r.json(), upd = Json::object();
+    std::string who;
+    if (!is_admin(r, &who)) {
+      for (const char* k : {"active", "admin", "agent_user_group", "username"})
+        if (b.contains(k)) return HttpResponse::error(403, std::string("only an administrator can change ") + k);
+      if (who != r.params.at("name")) return HttpResponse::error(403, "only an administrator can change another user's password");
+    }
     if (b.contains("password")) {
       const std::string salt = random_hex(8);
       upd["salt"] = salt;
@@ -322,14 +338,51 @@ tick();setInterval(tick,2000);
     return HttpResponse::json(obj({{"id", id}, {"config", cfg}}), 201);
   });
   http.route("GET", "/api/v1/experiments", [m](const HttpRequest& r) {
+    // reference GetExperiments: archived / states / users / labels / description filters, sort_by + order_by, offset + limit
     const bool all = r.q("all") == "true" || r.q("archived") == "true";
-    const std::string state = r.q("state");
-    Json a = Json::array();
+    auto set_of = [&](const char* a, const char* b2) {
+      std::set<std::string> out;
+      for (const char* key : {a, b2}) {
+        std::stringstream ss(r.q(key));
+        std::string item;
+        while (std::getline(ss, item, ',')) if (!item.empty()) out.insert(item);
+      }
+      return out;
+    };
+    const auto states = set_of("state", "states"), users = set_of("user", "users"), labels = set_of("label", "labels");
+    const std::string description = r.q("description");
+    std::vector<Json> rows;
     for (auto& e : m->store.list("experiments", [&](const Json& row) {
            if (!all && row["archived"].as_bool(false)) return false;
-           return state.empty() || row["state"].as_string() == state;
+           if (!states.empty() && !states.count(row["state"].str_or(""))) return false;
+           if (!users.empty() && !users.count(row["owner"].str_or("determined"))) return false;
+           if (!description.empty() && row["description"].str_or("").find(description) == std::string::npos) return false;
+           if (!labels.empty()) {
+             std::set<std::string> have;
+             if (row["labels"].is_array()) for (auto& l : row["labels"].arr()) have.insert(l.str_or(""));
+             for (auto& want : labels) if (!have.count(want)) return false;
+           }
+           return true;
          }))
-      a.push_back(experiment_summary(m->store, e));
+      rows.push_back(experiment_summary(m->store, e));
+    std::string sort_by = r.q("sort_by", "id");
+    if (sort_by.rfind("SORT_BY_", 0) == 0) sort_by = sort_by.substr(8);
+    for (auto& c : sort_by) c = static_cast<char>(tolower(c));
+    if (sort_by == "user") sort_by = "owner";
+    static const std::set<std::string> sortable = {"id", "description", "start_time", "end_time", "state", "progress", "owner", "num_trials"};
+    if (!sortable.count(sort_by)) return HttpResponse::error(400, "sort_by must be one of id, description, start_time, end_time, state, progress, user, num_trials");
+    std::string order = r.q("order_by", "asc");
+    for (auto& c : order) c = static_cast<char>(tolower(c));
+    const bool desc = order == "desc" || order == "order_by_desc";
+    std::stable_sort(rows.begin(), rows.end(), [&](const Json& x, const Json& y) {
+      const Json &a2 = desc ? y[sort_by] : x[sort_by], &b2 = desc ? x[sort_by] : y[sort_by];
+      if (a2.is_number() || b2.is_number()) return a2.as_double(0) < b2.as_double(0);
+      return a2.str_or("") < b2.str_or("");
+    });
+    const size_t offset = static_cast<size_t>(std::max<long long>(0, r.qi("offset", 0)));
+    const long long limit = r.qi("limit", 0);
+    Json a = Json::array();
+    for (size_t i = offset; i < rows.size() && (limit <= 0 || a.size() < static_cast<size_t>(limit)); ++i) a.push_back(rows[i]);
     return ok(a);
   });
   http.route("GET", "/api/v1/experiments/:id", [m](const HttpRequest& r) {
@@ -570,16 +623,62 @@ tick();setInterval(tick,2000);
     return ok(trial_detail(m->store, t, r.q("metrics") != "false"));
   });
   http.route("GET", "/api/v1/trials/:id/logs", [m](const HttpRequest& r) {
+    // Filters as in the reference's TrialLogs API (master/internal/api_trials.go): agent / container / rank / stdtype / source take
+    // comma-separated sets, level is a minimum, timestamps bound the window, search is a substring; the filters apply to the
+    // whole log from `offset`, then head / tail / limit pick lines. Every line carries its position ("id"): a follower asks
+    // for offset = last id + 1.
     m->system.ask(m->logger, "flush");
-    auto lines = m->store.read_logs(atoll(r.params.at("id").c_str()), static_cast<size_t>(r.qi("offset", 0)), static_cast<size_t>(r.qi("limit", 5000)));
-    // filters as in the reference log API: rank, stdtype, level, agent, container, search
+    const size_t offset = static_cast<size_t>(std::max<long long>(0, r.qi("offset", 0)));
+    const long long head = r.qi("head", -1), tail = r.qi("tail", -1);
+    size_t limit = static_cast<size_t>(std::max<long long>(0, r.qi("limit", 5000)));
+    if (head >= 0) limit = std::min(limit, static_cast<size_t>(head));
+    auto set_of = [&](const char* a, const char* b) {
+      std::set<std::string> out;
+      for (const char* key : {a, b}) {
+        std::stringstream ss(r.q(key));
+        std::string item;
+        while (std::getline(ss, item, ',')) if (!item.empty()) out.insert(item);
+      }
+      return out;
+    };
+    const auto ranks = set_of("rank", "rank_ids"), stdtypes = set_of("stdtype", "stdtypes"), containers = set_of("container_id", "container_ids"),
+               agents = set_of("agent_id", "agent_ids"), sources = set_of("source", "sources");
+    static const std::map<std::string, int> order = {{"TRACE", 0}, {"DEBUG", 1}, {"INFO", 2}, {"WARNING", 3}, {"ERROR", 4}, {"CRITICAL", 5}};
+    int min_level = -1;
+    if (!r.q("level").empty()) {
+      std::string lv = r.q("level");
+      for (auto& c : lv) c = static_cast<char>(toupper(c));
+      if (lv.rfind("LOG_LEVEL_", 0) == 0) lv = lv.substr(10);
+      auto it = order.find(lv);
+      if (it == order.end()) return HttpResponse::error(400, "level must be one of TRACE, DEBUG, INFO, WARNING, ERROR, CRITICAL");
+      min_level = it->second;
+    }
+    const std::string before = r.q("timestamp_before"), after = r.q("timestamp_after"), search = r.q("search");
     std::vector<Json> out;
-    for (auto& l : lines) {
-      if (!r.q("rank").empty() && l["rank"].as_int(-1) != r.qi("rank")) continue;
-      if (!r.q("stdtype").empty() && l["stdtype"].as_string() != r.q("stdtype")) continue;
-      if (!r.q("container_id").empty() && l["container_id"].as_string() != r.q("container_id")) continue;
-      if (!r.q("search").empty() && l["message"].as_string().find(r.q("search")) == std::string::npos) continue;
-      out.push_back(l);
+    size_t idx = offset;
+    for (auto& l : m->store.read_logs(atoll(r.params.at("id").c_str()), offset, 1u << 30)) {
+      Json row = l;
+      if (!row["id"].is_number()) row["id"] = static_cast<long long>(idx);
+      ++idx;
+      if (!ranks.empty() && (!l["rank"].is_number() || !ranks.count(std::to_string(l["rank"].as_int())))) continue;
+      if (!stdtypes.empty() && !stdtypes.count(l["stdtype"].str_or(""))) continue;
+      if (!containers.empty() && !containers.count(l["container_id"].str_or(""))) continue;
+      if (!agents.empty() && !agents.count(l["agent_id"].str_or(""))) continue;
+      if (!sources.empty() && !sources.count(l["source"].str_or(""))) continue;
+      if (min_level >= 0) {
+        auto it = order.find(l["level"].str_or("INFO"));
+        if ((it == order.end() ? 2 : it->second) < min_level) continue;
+      }
+      // RFC 3339 UTC timestamps of one format compare as strings
+      if (!before.empty() && !(l["timestamp"].str_or("") < before)) continue;
+      if (!after.empty() && !(l["timestamp"].str_or("") > after)) continue;
+      if (!search.empty() && l["message"].str_or("").find(search) == std::string::npos) continue;
+      out.push_back(row);
+      if (tail < 0 && out.size() >= limit) break;
+    }
+    if (tail >= 0) {
+      const size_t keep = std::min(static_cast<size_t>(tail), limit);
+      if (out.size() > keep) out.erase(out.begin(), out.end() - static_cast<long>(keep));
     }
     return ok(arr(out));
   });
@@ -832,12 +931,20 @@ tick();setInterval(tick,2000);
         spec["proxy_port"] = b["port"].as_int(0) > 0 ? b["port"].as_int() : static_cast<long long>(free_tcp_port());
         spec["ready_path"] = b["ready_path"].str_or("/");
       }
-      m->store.put("commands", id, obj({{"id", id}, {"type", type}, {"state", "PENDING"}, {"spec", spec}, {"start_time", now_rfc3339()}}));
+      std::string owner;
+      m->check_auth(r, &owner);
+      m->store.put("commands", id, obj({{"id", id}, {"type", type}, {"state", "PENDING"}, {"spec", spec}, {"start_time", now_rfc3339()}, {"owner", owner}}));
       m->system.actor_of("commands/" + std::to_string(id), make_command(m, id, spec), m->commands_root);
       return HttpResponse::json(m->store.get("commands", id), 201);
     });
-    http.route("GET", std::string("/api/v1/") + kind, [m, type](const HttpRequest&) {
-      return ok(arr(m->store.list("commands", [&](const Json& row) { return row["type"].as_string() == type; })));
+    http.route("GET", std::string("/api/v1/") + kind, [m, type](const HttpRequest& r) {
+      std::set<std::string> users;      // ?users=a,b: only these owners' tasks
+      std::stringstream ss(r.q("users"));
+      std::string item;
+      while (std::getline(ss, item, ',')) if (!item.empty()) users.insert(item);
+      return ok(arr(m->store.list("commands", [&](const Json& row) {
+        return row["type"].as_string() == type && (users.empty() || users.count(row["owner"].str_or("determined")));
+      })));
     });
     http.route("GET", std::string("/api/v1/") + kind + "/:id", [m](const HttpRequest& r) {
       Json c = m->store.get("commands", r.params.at("id"));

@@ -120,7 +120,7 @@ class Store {
     while (std::getline(f, line)) {
       if (i++ < offset) continue;
       if (out.size() >= limit) break;
-      try { out.push_back(Json::parse(line)); } catch (...) {}
+      try { Json j = Json::parse(line); j["id"] = static_cast<long long>(i - 1); out.push_back(j); } catch (...) {}   // id: position in the log
     }
     return out;
   }

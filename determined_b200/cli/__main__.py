@@ -129,13 +129,16 @@ def experiment_create(a: argparse.Namespace) -> int:
     if a.follow or a.test_mode:
         state = _follow_logs(d, exp.id)
         print(f"Experiment {exp.id} finished: {state}")
+        if a.test_mode:
+            print("Model definition test succeeded! 🎉" if state == "COMPLETED" else "Model definition test failed", flush=True)
         return 0 if state == "COMPLETED" else 1
     return 0
 
 
 def experiment_list(a: argparse.Namespace) -> int:
     d = Determined(a.master, a.user)
-    exps = d._session.get("/api/v1/experiments" + ("?all=true" if a.all else ""))
+    # like the reference: your own, unarchived experiments unless --all
+    exps = d._session.get("/api/v1/experiments" + ("?all=true" if a.all else f"?users={d._session.user}"))
     rows = [[e["id"], e.get("owner"), (e.get("description") or "")[:40], e["state"], f"{100 * (e.get('progress') or 0):.1f}%",
              e["start_time"][:19], (e.get("end_time") or "")[:19], e.get("num_trials")] for e in exps]
     print(_table(rows, ["ID", "Owner", "Description", "State", "Progress", "Start Time", "End Time", "Trials"]))
@@ -160,6 +163,13 @@ def experiment_describe(a: argparse.Namespace) -> int:
 
 def _simple_exp(verb: str):
     def run(a: argparse.Namespace) -> int:
+        if verb == "delete" and not a.yes:
+            # reference cli/experiment.py delete_experiment: irreversible, so it asks unless --yes
+            answer = input(f"Deleting experiment {a.experiment_id} removes its metadata, logs and checkpoints for good. Proceed? [y/N] ") \
+                if sys.stdin.isatty() else sys.stdin.readline()
+            if answer.strip().lower() not in ("y", "yes"):
+                print("Aborted: the experiment was not deleted", file=sys.stderr)
+                return 1
         exp = Determined(a.master, a.user).get_experiment(a.experiment_id)
         getattr(exp, verb)()
         print(f"{verb.capitalize()}d experiment {a.experiment_id}".replace("eed", "ed"))
@@ -246,17 +256,32 @@ def trial_describe(a: argparse.Namespace) -> int:
 
 
 def trial_logs(a: argparse.Namespace) -> int:
-    s = Session(a.master, a.user)
+    """Reference ``det trial logs``: --head / --tail / --follow and the agent / container / rank / level / stdtype / source /
+    timestamp filters; the filters are applied by the master, lines come back with their position so following resumes there."""
+    t = Determined(a.master, a.user).get_trial(a.trial_id)
+    ranks = list(a.rank_ids or []) + ([a.rank] if a.rank is not None else [])
+    filters: Dict[str, Any] = {"agent_ids": a.agent_ids, "container_ids": a.container_ids, "rank_ids": ranks, "stdtypes": a.stdtypes,
+                               "sources": a.sources, "level": a.level, "timestamp_before": a.timestamp_before,
+                               "timestamp_after": a.timestamp_after}
+    if a.head is not None and a.tail is not None:
+        print("--head and --tail are mutually exclusive", file=sys.stderr)
+        return 1
     off = 0
-    while True:
-        q = f"?offset={off}" + (f"&rank={a.rank}" if a.rank is not None else "")
-        lines = s.get(f"/api/v1/trials/{a.trial_id}/logs{q}")
+    if a.head is not None or a.tail is not None:
+        lines = t.logs(head=a.head, tail=a.tail, limit=max(a.head or 0, a.tail or 0), **filters)
         for l in lines:
             print(l["message"], flush=True)
-        off += len(lines)
-        if not a.follow:
+        if not a.follow or a.head is not None:
             return 0
-        if s.get(f"/api/v1/trials/{a.trial_id}")["state"] != "ACTIVE" and not lines:
+        off = lines[-1]["id"] + 1 if lines else 0
+    while True:
+        lines = t.logs(offset=off, **filters)
+        for l in lines:
+            print(l["message"], flush=True)
+        if lines:
+            off = lines[-1]["id"] + 1
+            continue        # more may be waiting behind a full page
+        if not a.follow or t.describe()["state"] != "ACTIVE":
             return 0
         time.sleep(1.0)
 
@@ -327,6 +352,9 @@ def preview_search_local(a: argparse.Namespace) -> int:
 
 def agent_list(a: argparse.Namespace) -> int:
     agents = Session(a.master, a.user).get("/api/v1/agents")
+    if a.json:
+        print(json.dumps(agents, indent=2))
+        return 0
     print(_table([[x["id"], x.get("registered_time", "")[:19], x["num_slots"], x["num_used_slots"], x.get("label"), x.get("enabled")] for x in agents],
                  ["Agent ID", "Registered Time", "Slots", "Used", "Label", "Enabled"]))
     return 0
@@ -334,6 +362,9 @@ def agent_list(a: argparse.Namespace) -> int:
 
 def slot_list(a: argparse.Namespace) -> int:
     slots = Session(a.master, a.user).get("/api/v1/slots")
+    if a.json:
+        print(json.dumps([dict(s, slot_id=s["id"]) for s in slots], indent=2))
+        return 0
     print(_table([[s["agent_id"], s["id"], s.get("enabled"), s.get("container_id") or "FREE", (s.get("device") or {}).get("type"),
                    (s.get("device") or {}).get("brand")] for s in slots], ["Agent ID", "Slot ID", "Enabled", "Task", "Type", "Device"]))
     return 0
@@ -389,11 +420,21 @@ def agent_detect(a: argparse.Namespace) -> int:
 
 
 # ---- users / templates / models / commands ----------------------------------------------------------------------------------
-def user_login(a: argparse.Namespace) -> int:
-    import getpass
+def _read_password(prompt: str) -> str:
+    """From the terminal without echo; from a pipe, one line of standard input (empty at end of input)."""
+    if sys.stdin.isatty():
+        import getpass
 
+        return getpass.getpass(prompt)
+    try:
+        return sys.stdin.readline().rstrip("\n")
+    except OSError:          # no usable standard input at all: the blank password
+        return ""
+
+
+def user_login(a: argparse.Namespace) -> int:
     s = Session(a.master, a.username)
-    s.login(getpass.getpass(f"Password for user '{a.username}': ") if sys.stdin.isatty() else "")
+    s.login(_read_password(f"Password for user '{a.username}': "))
     print(f"Logged in as {a.username}")
     return 0
 
@@ -410,9 +451,10 @@ def user_create(a: argparse.Namespace) -> int:
 
 
 def user_change_password(a: argparse.Namespace) -> int:
-    import getpass
-
-    Session(a.master, a.user).request("PATCH", f"/api/v1/users/{a.username}", {"password": getpass.getpass("New password: ")})
+    s = Session(a.master, a.user)
+    target = a.username or s.user
+    s.request("PATCH", f"/api/v1/users/{target}", {"password": _read_password(f"New password for user '{target}': ")})
+    print(f"Changed the password of {target}")
     return 0
 
 
@@ -584,8 +626,13 @@ def command_run(kind: str):
 
 def command_list(kind: str):
     def run(a: argparse.Namespace) -> int:
-        rows = Session(a.master, a.user).get(f"/api/v1/{kind}")
-        print(_table([[c["id"], c["state"], c["spec"]["description"], c["start_time"][:19]] for c in rows], ["ID", "State", "Description", "Start Time"]))
+        s = Session(a.master, a.user)
+        rows = s.get(f"/api/v1/{kind}" + ("" if a.all else f"?users={s.user}"))
+        if getattr(a, "quiet", False):
+            print("\n".join(str(c["id"]) for c in rows))
+            return 0
+        print(_table([[c["id"], c.get("owner", ""), c["state"], c["spec"]["description"], c["start_time"][:19]] for c in rows],
+                     ["ID", "Owner", "State", "Description", "Start Time"]))
         return 0
     return run
 
@@ -676,8 +723,9 @@ def build_parser() -> argparse.ArgumentParser:
     cmd(e, "list", experiment_list, A("--all", "-a", action="store_true"), aliases=["ls"])
     cmd(e, "describe", experiment_describe, A("experiment_ids"), A("--metrics", action="store_true"), A("--json", action="store_true"))
     cmd(e, "config", experiment_config, A("experiment_id", type=int))
-    for verb in ("activate", "pause", "cancel", "kill", "archive", "unarchive", "delete"):
+    for verb in ("activate", "pause", "cancel", "kill", "archive", "unarchive"):
         cmd(e, verb, _simple_exp(verb), A("experiment_id", type=int))
+    cmd(e, "delete", _simple_exp("delete"), A("experiment_id", type=int), A("--yes", action="store_true", help="do not ask for confirmation"))
     cmd(e, "wait", experiment_wait, A("experiment_id", type=int), A("--polling-interval", type=float, default=1.0))
     cmd(e, "set", experiment_set, A("what", choices=["description", "max-slots", "weight", "priority", "gc-policy"]), A("experiment_id", type=int), A("value"))
     cmd(e, "label", experiment_label, A("action", choices=["add", "remove"]), A("experiment_id", type=int), A("label"))
@@ -688,7 +736,13 @@ def build_parser() -> argparse.ArgumentParser:
     cmd(e, "download-model-def", experiment_download_model_def, A("experiment_id", type=int), A("--output-dir", "-o"))
     t = group("trial", ["t"])
     cmd(t, "describe", trial_describe, A("trial_id", type=int), A("--metrics", action="store_true"), A("--json", action="store_true"))
-    cmd(t, "logs", trial_logs, A("trial_id", type=int), A("--follow", "-f", action="store_true"), A("--rank", type=int))
+    cmd(t, "logs", trial_logs, A("trial_id", type=int), A("--follow", "-f", action="store_true"), A("--rank", type=int),
+        A("--head", type=int, help="number of lines to show, counting from the beginning"),
+        A("--tail", type=int, help="number of lines to show, counting from the end"),
+        A("--agent-id", dest="agent_ids", action="append"), A("--container-id", dest="container_ids", action="append"),
+        A("--rank-id", dest="rank_ids", type=int, action="append"), A("--timestamp-before"), A("--timestamp-after"),
+        A("--level", help="show lines of this level or higher (TRACE, DEBUG, INFO, WARNING, ERROR, CRITICAL)"),
+        A("--source", dest="sources", action="append"), A("--stdtype", dest="stdtypes", action="append"))
     cmd(t, "kill", trial_kill, A("trial_id", type=int))
     cmd(t, "download", trial_download, A("trial_id", type=int), A("--latest", action="store_true"), A("--best", action="store_true"), A("--uuid"), A("--output-dir", "-o"))
     c = group("checkpoint", ["c"])
@@ -704,12 +758,12 @@ def build_parser() -> argparse.ArgumentParser:
     ps.add_argument("config_file"), ps.add_argument("--seed", type=int, default=0), ps.add_argument("--offline", action="store_true")
     ps.set_defaults(func=lambda a: preview_search_local(a) if a.offline else preview_search(a))
     ag = group("agent", ["a"])
-    cmd(ag, "list", agent_list, aliases=["ls"])
+    cmd(ag, "list", agent_list, A("--json", action="store_true"), aliases=["ls"])
     cmd(ag, "enable", agent_toggle("enable"), A("agent_id"))
     cmd(ag, "disable", agent_toggle("disable"), A("agent_id"))
     cmd(ag, "detect", agent_detect)
     sl = group("slot", ["s"])
-    cmd(sl, "list", slot_list, aliases=["ls"])
+    cmd(sl, "list", slot_list, A("--json", action="store_true"), aliases=["ls"])
     cmd(sl, "enable", slot_toggle("enable"), A("agent_id"), A("slot_id"))
     cmd(sl, "disable", slot_toggle("disable"), A("agent_id"), A("slot_id"))
     ms = group("master")
@@ -722,7 +776,7 @@ def build_parser() -> argparse.ArgumentParser:
     cmd(us, "login", user_login, A("username"))
     cmd(us, "list", user_list, aliases=["ls"])
     cmd(us, "create", user_create, A("username"), A("--admin", action="store_true"))
-    cmd(us, "change-password", user_change_password, A("username"))
+    cmd(us, "change-password", user_change_password, A("username", nargs="?", help="default: the current user"))
     cmd(us, "logout", user_logout)
     cmd(us, "whoami", user_whoami)
     cmd(us, "rename", user_rename, A("target_user"), A("new_username"))
@@ -748,7 +802,8 @@ def build_parser() -> argparse.ArgumentParser:
             A("--context", "-c", help="directory to upload; becomes the task's working directory"),
             A("--volume", "-v", action="append", help="HOST_PATH:CONTAINER_PATH[:ro] bind mount"),
             A("--proxy", action="store_true", help="give the task a port ({port} in the command, $DET_TASK_PORT) reachable at /proxy/<id>/ on the master"))
-        cmd(g, "list", command_list(kind), aliases=["ls"])
+        cmd(g, "list", command_list(kind), A("--all", "-a", action="store_true", help="tasks of every user, not only your own"),
+            A("--quiet", "-q", action="store_true", help="only the ids"), aliases=["ls"])
         cmd(g, "kill", command_kill(kind), A("id"))
         cmd(g, "logs", command_logs(kind), A("id"), A("--follow", "-f", action="store_true"))
         cmd(g, "config", command_config(kind), A("id"))

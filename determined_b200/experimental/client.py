@@ -16,6 +16,7 @@ import shutil
 import sys
 import time
 import urllib.error
+import urllib.parse
 import urllib.request
 from typing import Any, Dict, Iterable, List, Optional
 
@@ -42,6 +43,7 @@ class Session:
         self._opener = tls.build_opener()     # https:// masters: DET_MASTER_CERT_FILE / DET_MASTER_CERT_NAME pin the certificate
         self.user = user or os.environ.get("DET_USER", "determined")
         self.token: Optional[str] = self._load_token()
+        self._tried_blank_login = False
 
     def _store(self) -> pathlib.Path:
         return pathlib.Path(os.environ.get("DET_CONFIG_DIR", pathlib.Path.home() / ".config" / "determined_b200")) / "auth.json"
@@ -92,6 +94,15 @@ class Session:
                 text = json.loads(text).get("error", text)
             except Exception:
                 pass
+            if e.code == 401 and auth and not self._tried_blank_login:
+                # accounts start with a blank password (reference common/api/authentication.py logs the default user in the
+                # same way): try that once before giving up
+                self._tried_blank_login = True
+                try:
+                    self.login("")
+                except APIError:
+                    raise APIError(e.code, text) from None
+                return self.request(method, path, body, auth, timeout)
             raise APIError(e.code, text) from None
         except urllib.error.URLError as e:
             raise APIError(0, f"cannot reach master at {self.master}: {e.reason}") from None
@@ -265,7 +276,17 @@ class TrialReference:
         return self._session.get(f"/api/v1/trials/{self.id}")
 
     def logs(self, **filters: Any) -> List[Dict[str, Any]]:
-        q = "&".join(f"{k}={v}" for k, v in filters.items())
+        """The trial's log lines. Filters: ``head`` / ``tail`` / ``offset`` / ``limit``, ``agent_ids`` / ``container_ids`` /
+        ``rank_ids`` / ``stdtypes`` / ``sources`` (a value or a list), ``level`` (minimum), ``timestamp_before`` /
+        ``timestamp_after`` (RFC 3339), ``search``. Every line carries ``id``, its position in the log."""
+        parts = []
+        for k, v in filters.items():
+            if v is None or v == []:
+                continue
+            if isinstance(v, (list, tuple, set)):
+                v = ",".join(str(x) for x in v)
+            parts.append(f"{k}={urllib.parse.quote(str(v), safe=',')}")
+        q = "&".join(parts)
         return self._session.get(f"/api/v1/trials/{self.id}/logs" + (f"?{q}" if q else ""))
 
     def kill(self) -> None:

@@ -7,7 +7,8 @@ with rollback and checkpoint bookkeeping through the real master / agent / harne
 Hyperparameters: ``metrics_progression`` (decreasing | increasing | constant), ``metrics_base`` in (0, 1),
 ``metrics_sigma``; ``chaos_probability`` (and ``_train`` / ``_validate`` / ``_checkpoint`` overrides): chance that a workload
 raises; ``fail_on_first_validation`` / ``fail_on_checkpoint_save``: message to fail with; ``request_stop``;
-``training_batch_seconds`` / ``validation_seconds`` / ``save_checkpoint_seconds``: simulated durations.
+``training_batch_seconds`` / ``validation_seconds`` / ``save_checkpoint_seconds``: simulated durations; ``write_null``: put a NUL
+byte into the trial's output (the log pipeline must carry it).
 """
 import collections
 import json
@@ -44,6 +45,8 @@ class NoOpTrialController(det.CallbackTrialController):
         self.base = float(hp.get("metrics_base", 0.9))
         self.sigma = float(hp.get("metrics_sigma", 0.0))
         self.request_stop = bool(hp.get("request_stop", False))
+        if hp.get("write_null", False):
+            print("a line with a null byte: \x00 and text after it", flush=True)
         assert self.progression in ("increasing", "decreasing", "constant") and 0 < self.base < 1 and self.sigma >= 0
         self.trained_steps: collections.Counter = collections.Counter()
         if self.load_path is not None:
