@@ -87,7 +87,11 @@ RPCS: List[Dict[str, Any]] = [
          [("config", "Struct"), ("model_definition", "Struct", "repeated"), ("template", "string"), ("activate", "bool"),
           ("validate_only", "bool"), ("parent_id", "int32")], ("experiment", "Experiment"),
          doc="Submit an experiment: config + model-definition files ({path, content (text), mode})."),
-    _rpc("GetExperiments", "GET", "/api/v1/experiments", [("state", "string"), ("archived", "bool")], ("experiments", "Experiment", "repeated")),
+    _rpc("GetExperiments", "GET", "/api/v1/experiments",
+         [("states", "string"), ("archived", "bool"), ("users", "string"), ("labels", "string"), ("description", "string"),
+          ("sort_by", "string"), ("order_by", "string"), ("offset", "int32"), ("limit", "int32")],
+         ("experiments", "Experiment", "repeated"),
+         doc="Filter (comma-separated sets; description is a substring), sort (id, description, start_time, end_time, state, progress, user, num_trials) and page."),
     _rpc("GetExperiment", "GET", "/api/v1/experiments/{id}", [ID32, ("metrics", "bool")], ("experiment", "Experiment")),
     _rpc("ActivateExperiment", "POST", "/api/v1/experiments/{id}/activate", [ID32], None),
     _rpc("PauseExperiment", "POST", "/api/v1/experiments/{id}/pause", [ID32], None),
@@ -127,8 +131,11 @@ RPCS: List[Dict[str, Any]] = [
     _rpc("GetTrial", "GET", "/api/v1/trials/{id}", [ID32, ("metrics", "bool")], ("trial", "Trial")),
     _rpc("KillTrial", "POST", "/api/v1/trials/{id}/kill", [ID32], None),
     _rpc("TrialLogs", "GET", "/api/v1/trials/{id}/logs",
-         [ID32, ("offset", "int64"), ("limit", "int32"), ("follow", "bool"), ("level", "string"), ("rank", "int32"), ("search", "string")],
-         ("entries", "LogEntry", "repeated"), stream=True, doc="Filterable trial logs; with follow the stream stays open until the trial ends."),
+         [ID32, ("offset", "int64"), ("limit", "int32"), ("head", "int32"), ("tail", "int32"), ("follow", "bool"), ("level", "string"),
+          ("agent_ids", "string"), ("container_ids", "string"), ("rank_ids", "string"), ("stdtypes", "string"), ("sources", "string"),
+          ("timestamp_before", "string"), ("timestamp_after", "string"), ("search", "string")],
+         ("entries", "LogEntry", "repeated"), stream=True,
+         doc="Filterable trial logs (sets are comma-separated, level is a minimum); every entry carries its position `id`; with follow the stream stays open until the trial ends."),
     _rpc("TrialLogsFields", "GET", "/api/v1/trials/{id}/logs/fields", [ID32], ("fields", "Struct"),
          doc="Distinct agent_ids, container_ids, rank_ids, stdtypes, sources of a trial's log lines."),
     _rpc("GetTrialCheckpoints", "GET", "/api/v1/trials/{id}/checkpoints", [ID32, ("state", "string")], ("checkpoints", "Checkpoint", "repeated")),
