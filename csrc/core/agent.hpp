@@ -10,6 +10,7 @@
 #include <sys/stat.h>
 #include <limits.h>
 #include <fcntl.h>
+#include <grp.h>
 #include <signal.h>
 #include <sys/types.h>
 #include <sys/wait.h>
@@ -17,6 +18,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <cerrno>
 #include <cstdio>
 #include <cstring>
 #include <functional>
@@ -318,6 +320,7 @@ class ContainerManager {
         auto bm = env.find("DET_BIND_MOUNTS");
         if (bm != env.end() && !apply_bind_mounts(bm->second)) _exit(125);
       }
+      if (!drop_to_task_user(env)) _exit(124);
       std::vector<char*> argv;
       for (auto& a : spec.argv) argv.push_back(const_cast<char*>(a.c_str()));
       argv.push_back(nullptr);
@@ -481,8 +484,29 @@ class ContainerManager {
   }
   // Only a single-slot harness start in a one-container trial goes to a warm worker, and only when nothing in its
   // environment has to be in place before the interpreter / CUDA start (loader paths, CUDA_*, NCCL_*, OMP_*, bind mounts).
+  // The task owner's linked agent user (`det user link-with-agent-user`; reference master/pkg/model/user.go AgentUserGroup,
+  // applied as the container's user): the forked child gives up its supplementary groups and takes the GID, then the UID, after
+  // the working directory and bind mounts are set up and right before exec. An agent that is not root cannot do this and
+  // fails the task rather than run it under the wrong identity.
+  static bool drop_to_task_user(const std::map<std::string, std::string>& env) {
+    auto u = env.find("DET_RUN_AS_UID");
+    if (u == env.end()) return true;
+    auto g = env.find("DET_RUN_AS_GID");
+    const uid_t uid = static_cast<uid_t>(strtoul(u->second.c_str(), nullptr, 10));
+    const gid_t gid = g == env.end() ? static_cast<gid_t>(uid) : static_cast<gid_t>(strtoul(g->second.c_str(), nullptr, 10));
+    if (geteuid() == uid && getegid() == gid) return true;
+    if (setgroups(0, nullptr) != 0 || setgid(gid) != 0 || setuid(uid) != 0) {
+      fprintf(stderr, "cannot run the task as uid %u gid %u: %s (the agent must run as root to use linked agent users)\n",
+              static_cast<unsigned>(uid), static_cast<unsigned>(gid), strerror(errno));
+      return false;
+    }
+    auto name = env.find("DET_RUN_AS_USER");
+    if (name != env.end() && !name->second.empty()) { setenv("USER", name->second.c_str(), 1); setenv("LOGNAME", name->second.c_str(), 1); }
+    return true;
+  }
   bool warm_eligible(const ContainerSpec& spec, const std::map<std::string, std::string>& env) {
     if (spec.devices.size() != 1) return false;
+    if (env.count("DET_RUN_AS_UID")) return false;      // a pre-started worker runs as the agent's own user
     // the harness command, bare or behind the entrypoint shell that sources startup-hook.sh (task_spec.hpp); a model
     // definition that ships such a hook needs the shell, so it starts cold
     const size_t n = spec.argv.size();

@@ -135,6 +135,7 @@ class CommandActor : public Actor {
       for (auto& v : spec_["argv"].arr()) spec.argv.push_back(v.as_string());
       spec.cwd = spec_["cwd"].str_or("");
       for (auto& kv : spec_["env"].obj()) spec.env[kv.first] = kv.second.as_string();
+      m_->apply_owner_identity(m_->store.get("commands", id_)["owner"].str_or(""), spec.env);
       for (auto& d : a["devices"].arr()) spec.devices.push_back(Device{static_cast<int>(d["id"].as_int()), d["brand"].as_string(), d["uuid"].as_string(), d["type"].as_string()});
       if (spec_["config"].is_object() || spec_["has_context"].as_bool(false)) {   // commands / notebooks / shells take bind_mounts, environment and resources like trials do
         const std::string slot_type = (!spec.devices.empty() && spec.devices[0].type == "gpu" && spec.devices[0].brand != "Artificial") ? "gpu" : "cpu";
@@ -357,6 +358,17 @@ void Master::write_context_files(const std::string& dir, const Json& files) {
     out.close();
     if (f["mode"].is_number()) chmod(full.c_str(), static_cast<mode_t>(f["mode"].as_int()));
   }
+}
+
+// Tasks of a user who is linked to an agent user run under that identity on the agents (agent.hpp: drop_to_task_user).
+void Master::apply_owner_identity(const std::string& owner, std::map<std::string, std::string>& env) {
+  if (owner.empty()) return;
+  const Json aug = store.get("users", owner)["agent_user_group"];
+  if (!aug.is_object() || !aug["uid"].is_number()) return;
+  env["DET_RUN_AS_UID"] = std::to_string(aug["uid"].as_int());
+  env["DET_RUN_AS_GID"] = std::to_string(aug["gid"].as_int(aug["uid"].as_int()));
+  if (aug["user"].is_string()) env["DET_RUN_AS_USER"] = aug["user"].as_string();
+  if (aug["group"].is_string()) env["DET_RUN_AS_GROUP"] = aug["group"].as_string();
 }
 
 long long Master::create_experiment(const Json& config, const Json& model_definition, long long parent_id, bool activate, const std::string& owner) {

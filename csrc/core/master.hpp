@@ -107,6 +107,7 @@ class Master {
   void unregister_container(const std::string& container_id);
   void spawn_checkpoint_gc(long long experiment_id);
   void write_context_files(const std::string& dir, const Json& files);
+  void apply_owner_identity(const std::string& owner, std::map<std::string, std::string>& env);
   std::string command_context_dir(long long command_id) const { return cfg.data_dir + "/commands/" + std::to_string(command_id) + "/context"; }
   std::string model_def_dir(long long experiment_id) const { return cfg.data_dir + "/experiments/" + std::to_string(experiment_id) + "/model_def"; }
   bool check_auth(const HttpRequest& req, std::string* user);

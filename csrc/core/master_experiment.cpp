@@ -257,6 +257,7 @@ class TrialActor : public Actor {
         if (!bad.empty()) m_->log("error", task_id_ + ": " + bad);
         if (!warning.empty()) m_->log("warn", task_id_ + ": " + warning);
       }
+      m_->apply_owner_identity(m_->store.get("experiments", exp_id_)["owner"].str_or(""), e);
       m_->register_container(spec.container_id, ctx.self(), trial_id_);
       containers_.push_back(spec.container_id);
       m_->start_container(a["agent"].as_string(), spec);

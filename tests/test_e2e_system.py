@@ -293,3 +293,24 @@ def test_users_passwords_deactivation_and_per_user_listings(auth_master):
     assert det(m, "user", "login", "alice", stdin="reset\n").returncode == 0
     listed = det(m, "user", "list", user="admin").stdout
     assert "alice" in listed and "bob" in listed
+
+
+@pytest.mark.skipif(os.geteuid() != 0, reason="switching users needs an agent that runs as root")
+def test_tasks_run_as_the_linked_agent_user(master):
+    """`det user link-with-agent-user`: the owner's tasks run under that UID / GID on the agents (reference
+    e2e_tests/tests/test_users.py test_link_with_agent_user / test_non_root_shell)."""
+    s = Session(master["url"])
+    r = det(master, "cmd", "run", "id")
+    assert r.returncode == 0 and "uid=0" in r.stdout
+    r = det(master, "user", "link-with-agent-user", "determined", "--agent-uid", "65534", "--agent-gid", "65534", "--agent-user", "nobody",
+            "--agent-group", "nogroup")
+    assert r.returncode == 0, r.stdout + r.stderr
+    try:
+        assert s.get("/api/v1/users/determined")["agent_user_group"]["uid"] == 65534
+        r = det(master, "cmd", "run", "sh", "-c", "id; echo user=$USER")
+        assert r.returncode == 0 and "uid=65534" in r.stdout and "gid=65534" in r.stdout and "user=nobody" in r.stdout, r.stdout + r.stderr
+        assert "groups=65534" in r.stdout and "0(root)" not in r.stdout           # root's supplementary groups are gone too
+    finally:
+        s.request("PATCH", "/api/v1/users/determined", {"agent_user_group": None})
+    r = det(master, "cmd", "run", "id")
+    assert r.returncode == 0 and "uid=0" in r.stdout
