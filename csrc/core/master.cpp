@@ -135,6 +135,10 @@ class CommandActor : public Actor {
       for (auto& v : spec_["argv"].arr()) spec.argv.push_back(v.as_string());
       spec.cwd = spec_["cwd"].str_or("");
       for (auto& kv : spec_["env"].obj()) spec.env[kv.first] = kv.second.as_string();
+      if (!spec.env.count("PYTHONPATH") && !m_->cfg.repo_root.empty()) {   // the package is importable in every task, as in the reference's images
+        const char* pp = getenv("PYTHONPATH");
+        spec.env["PYTHONPATH"] = m_->cfg.repo_root + (pp && *pp ? std::string(":") + pp : "");
+      }
       m_->apply_owner_identity(m_->store.get("commands", id_)["owner"].str_or(""), spec.env);
       for (auto& d : a["devices"].arr()) spec.devices.push_back(Device{static_cast<int>(d["id"].as_int()), d["brand"].as_string(), d["uuid"].as_string(), d["type"].as_string()});
       if (spec_["config"].is_object() || spec_["has_context"].as_bool(false)) {   // commands / notebooks / shells take bind_mounts, environment and resources like trials do
@@ -171,7 +175,9 @@ class CommandActor : public Actor {
     } else if (msg.type == "check_ready") {
       if (container_.empty() || ready_) return;
       std::string body;
-      const int st = http_request(host_, port_, "GET", spec_["ready_path"].str_or("/"), "", &body, 2);
+      std::string ready_path = spec_["ready_path"].str_or("/");
+      if (spec_["keep_prefix"].as_bool(false)) ready_path = "/proxy/" + std::to_string(id_) + ready_path;
+      const int st = http_request(host_, port_, "GET", ready_path, "", &body, 2);
       if (st > 0 && st < 500) {
         ready_ = true;
         m_->store.update("commands", id_, obj({{"is_ready", true}, {"ready_time", now_rfc3339()}}));

@@ -144,6 +144,7 @@ void Master::register_routes() {
       std::string path = "/";
       auto it = r.params.find("*");
       if (it != r.params.end()) path += it->second;
+      if (c["spec"]["keep_prefix"].as_bool(false)) path = "/proxy/" + r.params.at("id") + path;
       if (!r.query_string.empty()) path += "?" + r.query_string;
       const std::string host = c["proxy_host"].str_or("127.0.0.1");
       const int port = static_cast<int>(c["proxy_port"].as_int());
@@ -930,6 +931,34 @@ tick();setInterval(tick,2000);
       if (service) {
         spec["proxy_port"] = b["port"].as_int(0) > 0 ? b["port"].as_int() : static_cast<long long>(free_tcp_port());
         spec["ready_path"] = b["ready_path"].str_or("/");
+        // Jupyter and TensorBoard are told their URL prefix (base_url / --path_prefix) and expect to see it on every request,
+        // as behind the reference's proxy; other services get the path below /proxy/<id>/
+        spec["keep_prefix"] = b.contains("keep_prefix") ? b["keep_prefix"].as_bool(false) : (type == "notebook" || type == "tensorboard");
+      }
+      if (type == "tensorboard" && (b["experiment_ids"].is_array() || b["trial_ids"].is_array())) {
+        // where the event files of the requested experiments / trials live: their storage section and key prefix
+        // (reference master/internal/command/tensorboard_manager.go builds the same list from the experiment configs)
+        Json sources = Json::array();
+        auto add = [&](long long exp_id, long long trial_id) {
+          const Json e = m->store.get("experiments", exp_id);
+          if (e.is_null()) return false;
+          const Json& ec = e["config"];
+          std::string prefix = m->cluster_id + "/tensorboard/experiment/" + std::to_string(exp_id);
+          if (trial_id > 0) prefix += "/trial/" + std::to_string(trial_id);
+          sources.push_back(obj({{"experiment_id", exp_id}, {"trial_id", trial_id > 0 ? Json(trial_id) : Json()}, {"prefix", prefix},
+                                 {"storage", ec["tensorboard_storage"].is_object() ? ec["tensorboard_storage"] : ec["checkpoint_storage"]}}));
+          return true;
+        };
+        if (b["experiment_ids"].is_array())
+          for (auto& x : b["experiment_ids"].arr())
+            if (!add(x.as_int(0), 0)) return HttpResponse::error(404, "experiment " + std::to_string(x.as_int(0)) + " not found");
+        if (b["trial_ids"].is_array())
+          for (auto& x : b["trial_ids"].arr()) {
+            const Json t = m->store.get("trials", x.as_int(0));
+            if (t.is_null() || !add(t["experiment_id"].as_int(0), x.as_int(0))) return HttpResponse::error(404, "trial " + std::to_string(x.as_int(0)) + " not found");
+          }
+        if (sources.size() == 0) return HttpResponse::error(400, "a TensorBoard needs at least one experiment or trial");
+        spec["env"]["DET_TENSORBOARD_SOURCES"] = sources.dump();
       }
       std::string owner;
       m->check_auth(r, &owner);

@@ -590,6 +590,11 @@ def command_run(kind: str):
                                                           "read_only": len(parts) == 3 and parts[2] == "ro"})
         if config:
             body["config"] = config
+        if kind == "tensorboards":
+            if not a.experiment_ids and not a.trial_ids:
+                print("a TensorBoard needs at least one experiment id or --trial-ids", file=sys.stderr)
+                return 1
+            body["experiment_ids"], body["trial_ids"] = list(a.experiment_ids), list(a.trial_ids or [])
         if getattr(a, "template", None):
             body["template"] = a.template
         if getattr(a, "slots", None) is not None:
@@ -796,7 +801,7 @@ def build_parser() -> argparse.ArgumentParser:
     cmd(mo, "register-version", model_register_version, A("name"), A("uuid"))
     for name, kind in (("cmd", "commands"), ("notebook", "notebooks"), ("shell", "shells"), ("tensorboard", "tensorboards")):
         g = group(name)
-        extra = [A("command", nargs=argparse.REMAINDER)] if name == "cmd" else ([A("experiment_ids", nargs="*", type=int)] if name == "tensorboard" else [])
+        extra = [A("command", nargs=argparse.REMAINDER)] if name == "cmd" else ([A("experiment_ids", nargs="*", type=int), A("--trial-ids", "-t", nargs="+", type=int, help="serve these trials only")] if name == "tensorboard" else [])
         cmd(g, "run" if name == "cmd" else "start", command_run(kind), *extra, A("--slots", type=int, default=None), A("--detach", "-d", action="store_true"),
             A("--config-file"), A("--config", action="append", help="key.sub=value override of the task config"), A("--template"),
             A("--context", "-c", help="directory to upload; becomes the task's working directory"),

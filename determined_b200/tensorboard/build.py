@@ -1,9 +1,9 @@
 """``TensorboardManager`` tracks the tfevent files a trial writes under a local base path and mirrors new / grown
-files to ``<storage>/<cluster_id>/tensorboard/experiment/<e>/trial/<t>/``; ``BatchMetricWriter`` writes
+files to ``<storage>/<cluster_id>/tensorboard/experiment/<e>/trial/<t>/`` (a shared file system, or S3 / GCS objects); ``BatchMetricWriter`` writes
 ``Determined/<metric>`` scalars per batch and validation. TensorBoard tasks read the synced directory.
 Parity: reference ``harness/determined/tensorboard/base.py:6-55``, ``build.py:10-96``,
-``metric_writers/callback.py:10-55``, ``metric_writers/pytorch.py:9-42``. Shared-fs sync is a file copy; the object-store
-back-ends upload through the same storage-manager classes as checkpoints when their SDKs are present."""
+``metric_writers/callback.py:10-55``, ``metric_writers/pytorch.py:9-42``. Shared-fs sync is a file copy; S3 / GCS sync uploads
+through the clients the checkpoint storage managers use (``utils/objstore.py``)."""
 from __future__ import annotations
 
 import os
@@ -24,8 +24,13 @@ def get_sync_path(cluster_id: str, experiment_id: str, trial_id: str) -> pathlib
 
 
 class TensorboardManager:
-    def __init__(self, base_path: pathlib.Path, sync_path: pathlib.Path, storage_root: Optional[pathlib.Path]) -> None:
+    """``storage_root`` (shared_fs) or ``object_store`` (an S3 / GCS client plus key prefix, see :func:`object_store_for`)
+    names where the event files are mirrored; with neither, ``sync`` is a no-op."""
+
+    def __init__(self, base_path: pathlib.Path, sync_path: pathlib.Path, storage_root: Optional[pathlib.Path],
+                 object_store: Optional[Any] = None, object_prefix: str = "") -> None:
         self.base_path, self.sync_path, self.storage_root = pathlib.Path(base_path), pathlib.Path(sync_path), storage_root
+        self.object_store, self.object_prefix = object_store, object_prefix
         self._sizes: Dict[pathlib.Path, int] = {}
         self.base_path.mkdir(parents=True, exist_ok=True)
 
@@ -42,12 +47,27 @@ class TensorboardManager:
         return out
 
     def sync(self) -> None:
-        if self.storage_root is None:
+        if self.storage_root is None and self.object_store is None:
             return
         for p in self.to_sync():
-            dst = self.storage_root / self.sync_path / p.relative_to(self.base_path)
+            rel = self.sync_path / p.relative_to(self.base_path)
+            if self.object_store is not None:
+                self.object_store.put_file(self.object_prefix + rel.as_posix(), str(p))
+                continue
+            dst = self.storage_root / rel
             dst.parent.mkdir(parents=True, exist_ok=True)
             shutil.copy2(str(p), str(dst))
+
+
+def object_store_for(cfg: Dict[str, Any]) -> Any:
+    """(client, key prefix) for an ``s3`` / ``gcs`` storage section, else ``(None, "")`` — the same clients the checkpoint
+    storage managers use (reference ``tensorboard/s3.py``, ``gcs.py``)."""
+    if cfg.get("type") not in ("s3", "gcs"):
+        return None, ""
+    from .. import storage
+
+    mgr = storage.build(cfg)
+    return mgr.client, getattr(mgr, "prefix", "")
 
 
 class BatchMetricWriter:
@@ -82,7 +102,8 @@ def build_tensorboard_manager(env: EnvContext) -> TensorboardManager:
         storage_root = pathlib.Path(cfg.get("container_path") or cfg["host_path"])
         if cfg.get("storage_path"):
             storage_root = storage_root / cfg["storage_path"]
-    return TensorboardManager(base, get_sync_path(env.det_cluster_id, env.det_experiment_id, env.det_trial_id), storage_root)
+    client, prefix = object_store_for(cfg)
+    return TensorboardManager(base, get_sync_path(env.det_cluster_id, env.det_experiment_id, env.det_trial_id), storage_root, client, prefix)
 
 
 def build_metric_writer(manager: TensorboardManager) -> BatchMetricWriter:

@@ -160,3 +160,54 @@ def test_killed_pending_command_terminates(master):
     assert s.get(f"/api/v1/commands/{task_id}")["state"] == "TERMINATED"
     # and the queue is clean: a command that fits still runs
     assert det(master, "cmd", "run", "true").returncode == 0
+
+
+def test_tensorboard_for_a_shared_fs_experiment(master):
+    """`det tensorboard start <experiment>` serves the experiment's synced event files behind /proxy/<id>/ (reference
+    e2e_tests/tests/command/test_tensorboard.py): the master resolves where the files live from the experiment's storage
+    section, TensorBoard is told its URL prefix, and the scalars of the trial are there."""
+    import urllib.request
+
+    from determined_b200.experimental.client import Determined
+
+    pytest.importorskip("tensorboard")
+    d = Determined(master["url"])
+    cfg = {"entrypoint": "model_def:XorTrial", "hyperparameters": {"global_batch_size": 8, "hidden_size": 4, "learning_rate": 0.5},
+           "searcher": {"name": "single", "metric": "validation_loss", "max_length": {"batches": 20}}, "scheduling_unit": 10,
+           "checkpoint_storage": {"type": "shared_fs", "host_path": str(master["tmp"] / "ckpts")}, "max_restarts": 0}
+    exp = d.create_experiment(cfg, str(ROOT / "tests" / "fixtures" / "xor_model_def"))
+    assert exp.wait(timeout=180) == "COMPLETED"
+    trial_id = exp.describe()["trials"][0]["id"]
+    assert det(master, "tensorboard", "start", "--detach").returncode != 0                 # nothing to serve
+    assert det(master, "tensorboard", "start", "--detach", "424242").returncode != 0       # no such experiment
+    r = det(master, "tensorboard", "start", "--detach", str(exp.id))
+    assert r.returncode == 0, r.stdout + r.stderr
+    task_id = int(r.stdout.split()[2])
+    s = Session(master["url"])
+    try:
+        sources = __import__("json").loads(s.get(f"/api/v1/tensorboards/{task_id}")["spec"]["env"]["DET_TENSORBOARD_SOURCES"])
+        assert sources[0]["experiment_id"] == exp.id and sources[0]["prefix"].endswith(f"/tensorboard/experiment/{exp.id}")
+        deadline = time.time() + 120
+        while time.time() < deadline and not s.get(f"/api/v1/tensorboards/{task_id}").get("is_ready"):
+            assert s.get(f"/api/v1/tensorboards/{task_id}")["state"] != "TERMINATED", s.get(f"/api/v1/tensorboards/{task_id}")["logs"][-5:]
+            time.sleep(0.5)
+        assert s.get(f"/api/v1/tensorboards/{task_id}")["is_ready"]
+        base = f"http://{master['url']}/proxy/{task_id}"
+        tags = {}
+        while time.time() < deadline and not tags:                    # TensorBoard loads runs in the background
+            with urllib.request.urlopen(base + "/data/plugin/scalars/tags", timeout=10) as resp:
+                tags = __import__("json").loads(resp.read())
+            time.sleep(0.5)
+        run = [k for k in tags if k.startswith(f"experiment-{exp.id}") and k.endswith(f"trial/{trial_id}")]
+        assert run and "Determined/loss" in tags[run[0]], tags
+        with urllib.request.urlopen(base + "/", timeout=10) as resp:
+            assert b"TensorBoard" in resp.read()
+    finally:
+        det(master, "tensorboard", "kill", str(task_id))
+    # one trial only
+    r = det(master, "tensorboard", "start", "--detach", "--trial-ids", str(trial_id))
+    assert r.returncode == 0, r.stdout + r.stderr
+    tid2 = int(r.stdout.split()[2])
+    src = __import__("json").loads(s.get(f"/api/v1/tensorboards/{tid2}")["spec"]["env"]["DET_TENSORBOARD_SOURCES"])
+    assert src[0]["trial_id"] == trial_id and src[0]["prefix"].endswith(f"/trial/{trial_id}")
+    det(master, "tensorboard", "kill", str(tid2))

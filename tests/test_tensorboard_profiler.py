@@ -58,3 +58,51 @@ def test_profiler_samples_and_serializes(tmp_path):
     p.start()                                                     # one profiler object serves every workload in turn
     p.stop()
     assert len(p.samples) <= 2
+
+
+def test_event_files_sync_to_s3_and_are_fetched_by_the_tensorboard_task(tmp_path, monkeypatch):
+    """Object-store path (reference tensorboard/s3.py + fetchers/s3.py): the trial's manager uploads new / grown event files,
+    the TensorBoard task mirrors them into a local directory and picks up growth on the next poll."""
+    from tests.fake_objstore import make_s3
+
+    from determined_b200.exec.tensorboard import resolve_sources
+    from determined_b200.tensorboard.build import object_store_for
+
+    srv, url, objects, stats = make_s3()
+    try:
+        cfg = {"type": "s3", "bucket": "tb", "access_key": "AKIDEXAMPLE", "secret_key": "s3cr3t", "endpoint_url": url, "prefix": "runs"}
+        client, prefix = object_store_for(cfg)
+        assert prefix == "runs/" and object_store_for({"type": "shared_fs", "host_path": "/tmp"}) == (None, "")
+        mgr = TensorboardManager(tmp_path / "local", get_sync_path("cid", "3", "7"), None, client, prefix)
+        w = BatchMetricWriter(mgr.base_path)
+        w.on_train_step_end(1, 2, [{"loss": 1.0}, {"loss": 0.5}])
+        mgr.sync()
+        name = mgr.list_tfevents()[0].name
+        key = f"runs/cid/tensorboard/experiment/3/trial/7/{name}"
+        assert key in objects and stats["bad_signature"] == 0
+        first_size = len(objects[key])
+        # the TensorBoard task's side
+        sources = [{"experiment_id": 3, "trial_id": None, "storage": cfg, "prefix": "cid/tensorboard/experiment/3"}]
+        runs, fetchers = resolve_sources(sources, tmp_path / "scratch")
+        assert [n for n, _ in runs] == ["experiment-3"] and len(fetchers) == 1
+        assert fetchers[0].fetch_new() == 1
+        local = pathlib.Path(runs[0][1]) / "trial" / "7" / name
+        assert local.stat().st_size == first_size
+        assert fetchers[0].fetch_new() == 0                         # unchanged: nothing is downloaded again
+        w.on_validation_step_end(1, 2, {"validation_loss": 0.4})
+        mgr.sync()
+        assert len(objects[key]) > first_size
+        assert fetchers[0].fetch_new() == 1 and local.stat().st_size == len(objects[key])
+        from tensorboard.backend.event_processing.event_accumulator import EventAccumulator
+
+        acc = EventAccumulator(str(local.parent))
+        acc.Reload()
+        assert {"Determined/loss", "Determined/validation_loss"} <= set(acc.Tags()["scalars"])
+        # shared_fs sources are served in place, unknown back-ends are skipped
+        runs, fetchers = resolve_sources([{"experiment_id": 4, "trial_id": 9, "prefix": "cid/tensorboard/experiment/4/trial/9",
+                                           "storage": {"type": "shared_fs", "host_path": str(tmp_path), "storage_path": "sp"}},
+                                          {"experiment_id": 5, "prefix": "x", "storage": {"type": "hdfs", "hdfs_url": "http://h", "hdfs_path": "/"}}],
+                                         tmp_path / "scratch2")
+        assert runs == [("experiment-4-trial-9", str(tmp_path / "sp" / "cid/tensorboard/experiment/4/trial/9"))] and fetchers == []
+    finally:
+        srv.shutdown()
