@@ -2,7 +2,7 @@
 this box, with pid / log files under a state directory.
 
 Role of the reference's ``deploy/determined_deploy/local`` (docker-compose: Postgres + master + agent containers,
-``cluster-up / cluster-down / master-up / agent-up / logs``). There is no database or container runtime to start here:
+``cluster-up / cluster-down / master-up / master-down / agent-up / agent-down / logs``, ``--master-config-path``). There is no database or container runtime to start here:
 the master keeps its own journal and launches harness processes directly.
 """
 from __future__ import annotations
@@ -44,7 +44,23 @@ def _read_pid(f: pathlib.Path) -> Optional[int]:
         return None
 
 
-def master_up(name: str, port: int, slots: int = 0, scheduler: str = "fair_share", extra: Optional[List[str]] = None) -> int:
+def _master_config_flag(d: pathlib.Path, config_path: Optional[str]) -> List[str]:
+    """``--master-config-path``: a master.yaml (or JSON) in the keys of docs/cluster-config.md, handed to det-master as JSON
+    (reference ``det-deploy local --master-config-path`` mounts the file as /etc/determined/master.yaml)."""
+    if not config_path:
+        return []
+    import yaml
+
+    cfg = yaml.safe_load(pathlib.Path(config_path).read_text()) or {}
+    if not isinstance(cfg, dict):
+        raise SystemExit(f"{config_path}: a master configuration is a mapping")
+    out = d / "master-config.json"
+    out.write_text(json.dumps(cfg))
+    return ["--config", str(out)]
+
+
+def master_up(name: str, port: int, slots: int = 0, scheduler: str = "fair_share", extra: Optional[List[str]] = None,
+              config_path: Optional[str] = None) -> int:
     from determined_b200 import _build
 
     _build.build_core()
@@ -53,8 +69,16 @@ def master_up(name: str, port: int, slots: int = 0, scheduler: str = "fair_share
         raise SystemExit(f"cluster {name!r} already has a running master (pid {_read_pid(d / 'master.pid')})")
     port_file = d / "master.port"
     port_file.unlink(missing_ok=True)
-    cmd = [str(LIB / "det-master"), "--port", str(port), "--data-dir", str(d / "data"), "--repo-root", str(ROOT), "--python", sys.executable,
-           "--scheduler", scheduler, "--print-port-file", str(port_file)]
+    # flags win over the file inside det-master, so only what the caller chose (or the file leaves open) is passed as a flag
+    file_flag = _master_config_flag(d, config_path)
+    in_file = json.loads((d / "master-config.json").read_text()) if file_flag else {}
+    cmd = [str(LIB / "det-master"), *file_flag, "--repo-root", str(ROOT), "--python", sys.executable, "--print-port-file", str(port_file)]
+    if "port" not in in_file or port != 8080:
+        cmd += ["--port", str(port)]
+    if "data_dir" not in in_file:
+        cmd += ["--data-dir", str(d / "data")]
+    if "scheduler" not in in_file or scheduler != "fair_share":
+        cmd += ["--scheduler", scheduler]
     if slots:
         cmd += ["--artificial-slots", str(slots)]
     cmd += extra or []
@@ -76,12 +100,19 @@ def master_up(name: str, port: int, slots: int = 0, scheduler: str = "fair_share
     return bound
 
 
-def agent_up(name: str, master_port: int, agent_id: str, slots: int = 0) -> int:
+def agent_up(name: str, master_port: int, agent_id: str, slots: int = 0, master_host: str = "127.0.0.1", label: str = "") -> int:
+    from determined_b200 import _build
+
+    _build.build_core()
     d = _state_dir(name)
-    cmd = [str(LIB / "det-agent"), "--master-host", "127.0.0.1", "--master-port", str(master_port), "--agent-id", agent_id,
+    if _read_pid(d / f"agent-{agent_id}.pid"):
+        raise SystemExit(f"agent {agent_id!r} of cluster {name!r} is already running (pid {_read_pid(d / f'agent-{agent_id}.pid')})")
+    cmd = [str(LIB / "det-agent"), "--master-host", master_host, "--master-port", str(master_port), "--agent-id", agent_id,
            "--repo-root", str(ROOT), "--python", sys.executable]
     if slots:
         cmd += ["--artificial-slots", str(slots)]
+    if label:
+        cmd += ["--label", label]
     proc = subprocess.Popen(cmd, stdout=open(d / f"agent-{agent_id}.log", "a"), stderr=subprocess.STDOUT, start_new_session=True)
     (d / f"agent-{agent_id}.pid").write_text(str(proc.pid))
     return proc.pid
@@ -105,10 +136,12 @@ def grpc_up(name: str, master_port: int, grpc_port: int) -> int:
     return grpc_port
 
 
-def cluster_down(name: str) -> List[int]:
+def cluster_down(name: str, pattern: str = "*.pid") -> List[int]:
+    """Stop the processes whose pid files match ``pattern`` (everything by default; ``master.pid`` / ``agent-<id>.pid`` for
+    master-down / agent-down)."""
     d = _state_dir(name)
     stopped = []
-    for f in sorted(d.glob("*.pid"), key=lambda p: p.name.startswith("master")):   # agents first, master last
+    for f in sorted(d.glob(pattern), key=lambda p: p.name.startswith("master")):   # agents first, master last
         pid = _read_pid(f)
         if pid:
             try:
@@ -151,8 +184,28 @@ def main(argv: Optional[List[str]] = None) -> None:
     up.add_argument("--artificial-slots", type=int, default=0, help="CPU slots instead of detected GPUs (testing)")
     up.add_argument("--scheduler", default="fair_share", choices=["fair_share", "priority", "round_robin"])
     up.add_argument("--grpc-port", type=int, default=-1, help="also start the gRPC gateway on this port (0 = any free port)")
+    up.add_argument("--master-config-path", default=None, help="master configuration file (YAML or JSON, keys of docs/cluster-config.md)")
     down = lsub.add_parser("cluster-down")
     down.add_argument("--cluster-name", default="determined")
+    mu = lsub.add_parser("master-up", help="only the master (with its in-process agent unless the configuration says otherwise)")
+    mu.add_argument("--cluster-name", default="determined")
+    mu.add_argument("--master-port", type=int, default=8080)
+    mu.add_argument("--master-config-path", default=None)
+    mu.add_argument("--artificial-slots", type=int, default=0)
+    mu.add_argument("--scheduler", default="fair_share", choices=["fair_share", "priority", "round_robin"])
+    md = lsub.add_parser("master-down")
+    md.add_argument("--cluster-name", default="determined")
+    au = lsub.add_parser("agent-up", help="one det-agent that registers with a master, here or elsewhere")
+    au.add_argument("master_host")
+    au.add_argument("--master-port", type=int, default=8080)
+    au.add_argument("--agent-name", default="det-agent")
+    au.add_argument("--agent-label", default="")
+    au.add_argument("--artificial-slots", type=int, default=0)
+    au.add_argument("--cluster-name", default="determined")
+    ad = lsub.add_parser("agent-down")
+    ad.add_argument("--agent-name", default="det-agent")
+    ad.add_argument("--all", action="store_true", help="every agent of the cluster")
+    ad.add_argument("--cluster-name", default="determined")
     st = lsub.add_parser("status")
     st.add_argument("--cluster-name", default="determined")
     lg = lsub.add_parser("logs")
@@ -165,13 +218,24 @@ def main(argv: Optional[List[str]] = None) -> None:
         print(json.dumps(cloud.run(args), indent=1))
         return
     if args.verb == "cluster-up":
-        port = master_up(args.cluster_name, args.master_port, args.artificial_slots, args.scheduler)
+        port = master_up(args.cluster_name, args.master_port, args.artificial_slots, args.scheduler, config_path=args.master_config_path)
         for i in range(args.agents):
             agent_up(args.cluster_name, port, f"agent-{i + 1}", args.artificial_slots)
         extra = {"grpc": f"127.0.0.1:{grpc_up(args.cluster_name, port, args.grpc_port)}"} if args.grpc_port >= 0 else {}
         print(json.dumps({"master": f"127.0.0.1:{port}", "ui": f"http://127.0.0.1:{port}/ui", **extra, **status(args.cluster_name)}))
     elif args.verb == "cluster-down":
         print(json.dumps({"stopped": cluster_down(args.cluster_name)}))
+    elif args.verb == "master-up":
+        port = master_up(args.cluster_name, args.master_port, args.artificial_slots, args.scheduler, config_path=args.master_config_path)
+        print(json.dumps({"master": f"127.0.0.1:{port}", "ui": f"http://127.0.0.1:{port}/ui", **status(args.cluster_name)}))
+    elif args.verb == "master-down":
+        print(json.dumps({"stopped": cluster_down(args.cluster_name, "master.pid")}))
+    elif args.verb == "agent-up":
+        pid = agent_up(args.cluster_name, args.master_port, args.agent_name, args.artificial_slots, args.master_host, args.agent_label)
+        print(json.dumps({"agent": args.agent_name, "pid": pid}))
+    elif args.verb == "agent-down":
+        gone = cluster_down(args.cluster_name, "agent-*.pid" if args.all else f"agent-{args.agent_name}.pid")
+        print(json.dumps({"stopped": gone}))
     elif args.verb == "status":
         print(json.dumps(status(args.cluster_name)))
     elif args.verb == "logs":

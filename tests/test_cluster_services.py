@@ -154,6 +154,45 @@ def test_det_deploy_local_up_down(tmp_path):
     assert down.returncode == 0 and len(json.loads(down.stdout)["stopped"]) == 2
 
 
+def test_det_deploy_local_master_and_agents_separately(tmp_path):
+    """master-up with a configuration file, agent-up / agent-down against it, master-down (reference deploy/test_local.py:
+    test_custom_etc, test_master_up_down, test_agent_up_down)."""
+    env = dict(os.environ, DET_DEPLOY_DIR=str(tmp_path), DET_CONFIG_DIR=str(tmp_path / "cfg"))
+    run = lambda *a: subprocess.run([sys.executable, str(ROOT / "det-deploy"), "local", *a, "--cluster-name", "sep"], capture_output=True,  # noqa: E731
+                                    text=True, env=env, timeout=120)
+    etc = tmp_path / "master.yaml"
+    etc.write_text("port: 0\ncluster_name: from-the-file\nscheduler: priority\nartificial_slots: 1\n")
+    up = run("master-up", "--master-config-path", str(etc), "--master-port", "0")
+    assert up.returncode == 0, up.stderr
+    info = json.loads(up.stdout.strip().splitlines()[-1])
+    host, port = info["master"].split(":")
+    try:
+        c = MasterClient(host, int(port))
+        assert c.request("GET", "/info")["cluster_name"] == "from-the-file" and c.request("GET", "/info")["scheduler"] == "priority"
+        assert run("master-up", "--master-port", "0").returncode != 0          # one master per cluster name
+        for name in ("a1", "a2"):
+            assert run("agent-up", "127.0.0.1", "--master-port", port, "--agent-name", name, "--artificial-slots", "1",
+                       "--agent-label", "pool-x").returncode == 0
+        for _ in range(100):
+            agents = {a["id"]: a for a in c.request("GET", "/api/v1/agents")}
+            if {"a1", "a2"} <= set(agents):
+                break
+            time.sleep(0.1)
+        assert {"agent-local", "a1", "a2"} == set(agents) and agents["a1"]["label"] == "pool-x"
+        assert run("agent-up", "127.0.0.1", "--master-port", port, "--agent-name", "a1").returncode != 0     # already running
+        assert len(json.loads(run("agent-down", "--agent-name", "a1").stdout)["stopped"]) == 1
+        for _ in range(100):
+            if "a1" not in {a["id"] for a in c.request("GET", "/api/v1/agents")}:
+                break
+            time.sleep(0.1)
+        assert {a["id"] for a in c.request("GET", "/api/v1/agents")} == {"agent-local", "a2"}
+        assert len(json.loads(run("agent-down", "--all").stdout)["stopped"]) == 1
+    finally:
+        down = run("master-down")
+        run("cluster-down")
+    assert down.returncode == 0 and len(json.loads(down.stdout)["stopped"]) == 1
+
+
 def test_data_layer_builds_once_and_serves_cached_copy(tmp_path):
     calls = []
     dl = data_layer.DataLayer({"type": "lfs", "container_storage_path": str(tmp_path)})
