@@ -81,6 +81,7 @@ class HttpServer {
     return tls_ctx_ != nullptr;
   }
   bool tls_enabled() const { return tls_ctx_ != nullptr; }
+  void set_cors(bool on) { cors_ = on; }
 
   // Binds and listens; returns the bound port (useful with port 0) or -1.
   int listen(const std::string& host, int port) {
@@ -231,8 +232,15 @@ class HttpServer {
       auto rit = reason.find(resp.status);
       std::ostringstream os;
       os << "HTTP/1.1 " << resp.status << " " << (rit == reason.end() ? "Status" : rit->second) << "\r\n"
-         << "Content-Type: " << resp.content_type << "\r\nContent-Length: " << resp.body.size()
-         << "\r\nAccess-Control-Allow-Origin: *\r\nConnection: close\r\n\r\n" << resp.body;
+         << "Content-Type: " << resp.content_type << "\r\nContent-Length: " << resp.body.size();
+      if (cors_) {   // enable_cors: other origins (a WebUI served elsewhere) may call the API with a bearer token
+        auto origin = req.headers.find("origin");
+        os << "\r\nAccess-Control-Allow-Origin: " << (origin == req.headers.end() ? std::string("*") : origin->second)
+           << "\r\nAccess-Control-Allow-Methods: GET, POST, PUT, PATCH, DELETE, OPTIONS"
+           << "\r\nAccess-Control-Allow-Headers: Authorization, Content-Type, X-Requested-With"
+           << "\r\nAccess-Control-Allow-Credentials: true\r\nVary: Origin";
+      }
+      os << "\r\nConnection: close\r\n\r\n" << resp.body;
       const std::string out = os.str();
       c.write_all(out.data(), out.size());
     }
@@ -268,6 +276,7 @@ class HttpServer {
   std::function<bool(const HttpRequest&, HttpResponse&)> middleware_;
   int fd_ = -1, port_ = 0;
   SSL_CTX* tls_ctx_ = nullptr;
+  bool cors_ = false;
   std::atomic<bool> stop_{false};
   std::thread thread_;
 };

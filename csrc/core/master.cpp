@@ -50,7 +50,10 @@ MasterConfig MasterConfig::from_json(const Json& j) {
   static const std::set<std::string> known = {"host", "port", "data_dir", "scheduler", "fitting_policy", "preemption", "checkpoint_storage",
                                               "python", "repo_root", "slot_type", "visible_gpus", "artificial_slots", "auth_required",
                                               "cluster_name", "scheduler_tick_ms", "terminate_timeout_ms", "all_ready_timeout_ms", "resource_pools", "db", "telemetry", "provisioner", "resource_manager",
-                                              "security", "task_container_defaults", "logging", "warm_workers"};
+                                              "security", "task_container_defaults", "logging", "warm_workers",
+                                              // reference master.yaml keys: honoured (log, tensorboard_timeout, enable_cors) or accepted because they name
+                                              // things this master does not have (a database, a static root, a harness wheel)
+                                              "log", "tensorboard_timeout", "enable_cors", "config_file", "root", "harness_path"};
   MasterConfig c;
   for (auto& kv : j.obj())
     if (!known.count(kv.first)) throw ConfigError("unknown field in master config: '" + kv.first + "'");
@@ -88,6 +91,35 @@ MasterConfig MasterConfig::from_json(const Json& j) {
       if (c.tls_cert.empty() != c.tls_key.empty()) throw ConfigError("security.tls needs both cert and key");
     }
   }
+  c.default_task = j["security"]["default_task"];
+  if (c.default_task.is_object() && !c.default_task["uid"].is_number()) throw ConfigError("security.default_task needs uid (and gid, user, group)");
+  c.task_container_defaults = j["task_container_defaults"];
+  if (c.task_container_defaults.is_object()) {
+    static const std::set<std::string> tcd_known = {"dtrain_network_interface", "nccl_port_range", "gloo_port_range", "shm_size_bytes", "network_mode",
+                                                    "cpu_pod_spec", "gpu_pod_spec", "image", "registry_auth", "force_pull_image"};
+    for (auto& kv : c.task_container_defaults.obj())
+      if (!tcd_known.count(kv.first)) throw ConfigError("unknown field in master config: 'task_container_defaults." + kv.first + "'");
+    if (c.task_container_defaults.contains("shm_size_bytes") && c.task_container_defaults["shm_size_bytes"].as_int(0) <= 0)
+      throw ConfigError("task_container_defaults.shm_size_bytes must be > 0");
+    for (const char* key : {"nccl_port_range", "gloo_port_range"}) {
+      const std::string r = c.task_container_defaults[key].str_or("");
+      if (r.empty()) continue;
+      unsigned lo = 0, hi = 0;
+      char tail = 0;
+      if (sscanf(r.c_str(), "%u:%u%c", &lo, &hi, &tail) != 2 || lo > 65535 || hi > 65535)
+        throw ConfigError(std::string("task_container_defaults.") + key + ": expected a port range of the form MIN:MAX, got '" + r + "'");
+      if (lo > hi) throw ConfigError(std::string("task_container_defaults.") + key + ": the minimum exceeds the maximum");
+    }
+  }
+  c.tensorboard_timeout_s = static_cast<int>(j["tensorboard_timeout"].as_int(c.tensorboard_timeout_s));
+  if (c.tensorboard_timeout_s < 0) throw ConfigError("tensorboard_timeout must be >= 0");
+  c.enable_cors = j["enable_cors"].as_bool(false);
+  if (j["log"].is_object()) {
+    c.log_level = j["log"]["level"].str_or(c.log_level);
+    if (c.log_level == "warning") c.log_level = "warn";
+    static const std::set<std::string> levels = {"trace", "debug", "info", "warn", "error", "fatal"};
+    if (!levels.count(c.log_level)) throw ConfigError("log.level must be one of trace, debug, info, warn, error, fatal");
+  }
   c.cluster_name = j["cluster_name"].str_or(c.cluster_name);
   c.provisioner = j["provisioner"];
   c.telemetry = j["telemetry"];
@@ -113,7 +145,9 @@ Json MasterConfig::to_json() const {
   return obj({{"host", host}, {"port", port}, {"data_dir", data_dir}, {"scheduler", scheduler}, {"fitting_policy", fitting_policy},
               {"preemption", preemption}, {"checkpoint_storage", checkpoint_storage}, {"python", python}, {"repo_root", repo_root},
               {"slot_type", slot_type}, {"artificial_slots", artificial_slots}, {"auth_required", auth_required},
-              {"cluster_name", cluster_name}, {"scheduler_tick_ms", scheduler_tick_ms}, {"resource_manager", resource_manager}});
+              {"cluster_name", cluster_name}, {"scheduler_tick_ms", scheduler_tick_ms}, {"resource_manager", resource_manager},
+              {"task_container_defaults", task_container_defaults}, {"tensorboard_timeout", tensorboard_timeout_s}, {"enable_cors", enable_cors},
+              {"log", obj({{"level", log_level}})}});
 }
 
 // ---- command tasks (generic commands, notebooks, shells, tensorboards) ---------------------------------------------
@@ -172,6 +206,11 @@ class CommandActor : public Actor {
       m_->register_container(container_, ctx.self(), -id_);
       set_state("RUNNING");
       m_->start_container(a["agent"].as_string(), spec);
+      if (spec_["type"].str_or("") == "tensorboard" && m_->cfg.tensorboard_timeout_s > 0) {
+        // reference tensorboard_manager.go: a TensorBoard nobody has asked anything of for tensorboard_timeout seconds is stopped
+        m_->store.update("commands", id_, obj({{"last_request_s", static_cast<long long>(std::time(nullptr))}}));
+        ctx.system().notify_after(ctx.self(), 1000 * std::max(1, std::min(m_->cfg.tensorboard_timeout_s, 30)), "idle_check");
+      }
     } else if (msg.type == "check_ready") {
       if (container_.empty() || ready_) return;
       std::string body;
@@ -184,6 +223,15 @@ class CommandActor : public Actor {
         m_->log("info", task_id_ + " is ready at /proxy/" + std::to_string(id_) + "/");
       } else {
         ctx.system().notify_after(ctx.self(), 500, "check_ready");
+      }
+    } else if (msg.type == "idle_check") {
+      if (container_.empty()) return;
+      const long long idle = static_cast<long long>(std::time(nullptr)) - m_->store.get("commands", id_)["last_request_s"].as_int(0);
+      if (idle >= m_->cfg.tensorboard_timeout_s) {
+        m_->log("info", task_id_ + ": idle for " + std::to_string(idle) + " s; stopping it (tensorboard_timeout)");
+        m_->signal_container(container_, SIGKILL);
+      } else {
+        ctx.system().notify_after(ctx.self(), 1000 * std::max(1, std::min(m_->cfg.tensorboard_timeout_s, 30)), "idle_check");
       }
     } else if (msg.type == "container_event") {
       if (msg.body["state"].as_string() == "TERMINATED") {
@@ -232,6 +280,9 @@ void Master::report_telemetry(const std::string& event, const Json& properties) 
   if (f) f << e.dump() << "\n";
 }
 void Master::log(const std::string& level, const std::string& msg) {
+  static const std::map<std::string, int> rank = {{"trace", 0}, {"debug", 1}, {"info", 2}, {"warn", 3}, {"error", 4}, {"fatal", 5}};
+  auto at = rank.find(level), min = rank.find(cfg.log_level);
+  if (at != rank.end() && min != rank.end() && at->second < min->second) return;      // below log.level
   Json e = obj({{"time", now_rfc3339()}, {"level", level}, {"message", msg}});
   {
     std::lock_guard<std::mutex> g(log_mu_);
@@ -368,8 +419,8 @@ void Master::write_context_files(const std::string& dir, const Json& files) {
 
 // Tasks of a user who is linked to an agent user run under that identity on the agents (agent.hpp: drop_to_task_user).
 void Master::apply_owner_identity(const std::string& owner, std::map<std::string, std::string>& env) {
-  if (owner.empty()) return;
-  const Json aug = store.get("users", owner)["agent_user_group"];
+  Json aug = owner.empty() ? Json() : store.get("users", owner)["agent_user_group"];
+  if (!aug.is_object() || !aug["uid"].is_number()) aug = cfg.default_task;      // security.default_task: everyone who is not linked
   if (!aug.is_object() || !aug["uid"].is_number()) return;
   env["DET_RUN_AS_UID"] = std::to_string(aug["uid"].as_int());
   env["DET_RUN_AS_GID"] = std::to_string(aug["gid"].as_int(aug["uid"].as_int()));
@@ -486,7 +537,13 @@ int Master::start() {
   const bool k8s = cfg.resource_manager.is_object() && cfg.resource_manager["type"].str_or("agent") == "kubernetes";
   if (k8s) {
     // Pods replace agents: every schedulable node with allocatable slot resources joins the pool as "k8s-<node>".
-    const KubeConfig kc = KubeConfig::from_json(cfg.resource_manager);
+    KubeConfig kc = KubeConfig::from_json(cfg.resource_manager);
+    if (!kc.pod_spec_overrides.is_object()) {
+      // task_container_defaults.gpu_pod_spec / cpu_pod_spec (a Pod manifest; its .spec is what is merged into task pods)
+      const bool gpu_pool = cfg.slot_type != "cpu";
+      const Json& pod = cfg.task_container_defaults[gpu_pool ? "gpu_pod_spec" : "cpu_pod_spec"];
+      if (pod.is_object()) kc.pod_spec_overrides = pod["spec"].is_object() ? pod["spec"] : pod;
+    }
     kube.reset(new KubernetesPods(
         kc, cluster_id, [this](const ContainerEvent& ev) { route_container_event(ev); }, [this](const LogLine& l) { route_log(l); },
         [this, kc](const std::string& node, int slots, bool present) {
@@ -529,6 +586,7 @@ int Master::start() {
     std::string err;
     if (!http.enable_tls(cfg.tls_cert, cfg.tls_key, &err)) throw std::runtime_error("security.tls: " + err);
   }
+  http.set_cors(cfg.enable_cors);
   const int port = http.listen(cfg.host, cfg.port);
   if (port >= 0 && cfg.provisioner.is_object()) provisioner = system.actor_of("provisioner", make_provisioner(this, cfg.provisioner));
   if (port < 0) throw std::runtime_error("cannot bind " + cfg.host + ":" + std::to_string(cfg.port));

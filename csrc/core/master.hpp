@@ -53,6 +53,11 @@ struct MasterConfig {
   int scheduler_tick_ms = 500;
   int terminate_timeout_ms = 60000;
   int all_ready_timeout_ms = 600000;     // reference allReadyTimeout: 10 minutes from container start to a working harness
+  Json task_container_defaults;          // {shm_size_bytes, dtrain_network_interface, nccl_port_range, gloo_port_range, ...}
+  Json default_task;                     // security.default_task: {uid, gid, user, group} of tasks whose owner has no linked agent user
+  int tensorboard_timeout_s = 300;       // idle TensorBoards are stopped after this long without a request (reference tensorboard_timeout)
+  bool enable_cors = false;              // Access-Control-Allow-* on every response, OPTIONS pre-flights answered
+  std::string log_level = "info";        // log.level: trace | debug | info | warn | error | fatal
 
   static MasterConfig from_json(const Json& j);  // strict: unknown keys are rejected
   Json to_json() const;

@@ -141,6 +141,10 @@ void Master::register_routes() {
       if (c.is_null()) return not_found("task");
       if (c["proxy_port"].as_int(0) <= 0) return HttpResponse::error(404, "task exposes no service");
       if (c["state"].str_or("") != "RUNNING") return HttpResponse::error(502, "task is " + c["state"].str_or("not running"));
+      if (c["type"].str_or("") == "tensorboard") {    // keeps an idle TensorBoard from being reaped (tensorboard_timeout)
+        const long long now_s = static_cast<long long>(std::time(nullptr));
+        if (c["last_request_s"].as_int(0) != now_s) m->store.update("commands", r.params.at("id"), obj({{"last_request_s", now_s}}));
+      }
       std::string path = "/";
       auto it = r.params.find("*");
       if (it != r.params.end()) path += it->second;

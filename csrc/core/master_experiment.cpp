@@ -235,6 +235,21 @@ class TrialActor : public Actor {
       e["DET_WORKLOAD_MANAGER_TYPE"] = "TRIAL_WORKLOAD_MANAGER";
       e["DET_RENDEZVOUS_PORTS"] = std::to_string(1734 + (trial_id_ % 16)) + "," + std::to_string(1750 + (trial_id_ % 16));
       e["DET_TRIAL_RUNNER_NETWORK_INTERFACE"] = "lo";
+      {
+        // master-wide task_container_defaults (reference master/pkg/tasks/task.go TrialEnvVars): the interface and port ranges
+        // the collectives' bootstrap may use — handed to NCCL and gloo in their own variables as well — and the shared-memory
+        // size a trial gets unless its resources.shm_size says otherwise
+        const Json& tcd = m_->cfg.task_container_defaults;
+        const std::string nic = tcd["dtrain_network_interface"].str_or("");
+        if (!nic.empty()) {
+          e["DET_TRIAL_RUNNER_NETWORK_INTERFACE"] = nic;
+          e["NCCL_SOCKET_IFNAME"] = nic;
+          e["GLOO_SOCKET_IFNAME"] = nic;
+        }
+        if (!tcd["nccl_port_range"].str_or("").empty()) e["NCCL_PORT_RANGE"] = tcd["nccl_port_range"].as_string();
+        if (!tcd["gloo_port_range"].str_or("").empty()) e["GLOO_PORT_RANGE"] = tcd["gloo_port_range"].as_string();
+        if (tcd["shm_size_bytes"].as_int(0) > 0) e["DET_SHM_SIZE"] = std::to_string(tcd["shm_size_bytes"].as_int());
+      }
       e["DET_CLUSTER_ID"] = m_->cluster_id;
       e["DET_AGENT_ID"] = a["agent"].as_string();
       e["DET_CONTAINER_RANK"] = std::to_string(a["rank"].as_int());

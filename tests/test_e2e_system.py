@@ -215,12 +215,14 @@ def test_delete_archive_labels_and_listing_filters(master):
     # filters, sorting, paging
     assert [e["id"] for e in s.get("/api/v1/experiments?description=listing-target")] == [paused.id]
     assert all(e["state"] == "COMPLETED" for e in s.get("/api/v1/experiments?states=COMPLETED"))
+    other = d.create_experiment(noop_config(master["tmp"], batches=10), NOOP_DIR, activate=False)       # a second row to sort and page over
     ids = [e["id"] for e in s.get("/api/v1/experiments?sort_by=id&order_by=desc")]
     assert ids == sorted(ids, reverse=True) and len(ids) >= 2
     assert [e["id"] for e in s.get("/api/v1/experiments?sort_by=id&order_by=desc&limit=1&offset=1")] == ids[1:2]
     assert s.get("/api/v1/experiments?users=nobody") == []
     with pytest.raises(APIError):
         s.get("/api/v1/experiments?sort_by=colour")
+    other.cancel()
     # delete: gone from the API, and the CLI says so
     assert det(master, "experiment", "delete", str(paused.id), "--yes").returncode == 0
     assert det(master, "experiment", "describe", str(paused.id)).returncode != 0
@@ -314,3 +316,123 @@ def test_tasks_run_as_the_linked_agent_user(master):
         s.request("PATCH", "/api/v1/users/determined", {"agent_user_group": None})
     r = det(master, "cmd", "run", "id")
     assert r.returncode == 0 and "uid=0" in r.stdout
+
+
+# ---- master configuration file ------------------------------------------------------------------------------------------
+def run_master_with_config(tmp, cfg):
+    """Start det-master from a configuration file; returns (process, url) or (None, error text) when it refuses the file."""
+    from determined_b200 import _build
+
+    _build.build_core()
+    tmp.mkdir(parents=True, exist_ok=True)
+    path, port_file = tmp / "master.json", tmp / "port"
+    path.write_text(json.dumps(dict({"port": 0, "data_dir": str(tmp / "data"), "artificial_slots": 1, "repo_root": str(ROOT), "python": sys.executable}, **cfg)))
+    log = tmp / "master.log"
+    proc = subprocess.Popen([str(MASTER), "--config", str(path), "--print-port-file", str(port_file)], stdout=open(log, "w"), stderr=subprocess.STDOUT,
+                            env=dict(os.environ, DET_CONFIG_DIR=str(tmp / "cfg")))
+    for _ in range(100):
+        if port_file.exists() and port_file.read_text().strip():
+            return proc, f"127.0.0.1:{int(port_file.read_text())}"
+        if proc.poll() is not None:
+            return None, log.read_text()
+        time.sleep(0.05)
+    proc.kill()
+    return None, "the master did not start: " + log.read_text()
+
+
+@pytest.mark.parametrize("bad,why", [
+    ({"task_container_defaults": {"nccl_port_range": "12-15"}}, "MIN:MAX"),
+    ({"task_container_defaults": {"gloo_port_range": "200:100"}}, "minimum exceeds"),
+    ({"task_container_defaults": {"shm_size_bytes": 0}}, "shm_size_bytes"),
+    ({"task_container_defaults": {"colour": "red"}}, "task_container_defaults.colour"),
+    ({"log": {"level": "chatty"}}, "log.level"),
+    ({"tensorboard_timeout": -1}, "tensorboard_timeout"),
+    ({"security": {"default_task": {"user": "nobody"}}}, "default_task"),
+])
+def test_master_refuses_bad_configuration(tmp_path, bad, why):
+    proc, text = run_master_with_config(tmp_path / "m", bad)
+    if proc is not None:
+        stop_master(proc)
+    assert proc is None and why in text, text
+
+
+def test_master_configuration_keys_of_the_reference_are_honoured(tmp_path):
+    """A master.yaml in the reference's shape: log level, CORS, task container defaults reaching the trial's environment,
+    a short tensorboard_timeout reaping an idle TensorBoard;
+    db / root / harness_path name things this master does not have and are accepted."""
+    import urllib.request
+
+    cfg = {"log": {"level": "error", "color": False}, "enable_cors": True, "tensorboard_timeout": 2, "cluster_name": "cfg-test",
+           "db": {"user": "postgres", "host": "db", "port": "5432"}, "root": "/usr/share/determined/master", "harness_path": "/opt/determined",
+           "scheduler": {"type": "priority", "fit": "worst"},
+           "task_container_defaults": {"dtrain_network_interface": "lo", "nccl_port_range": "12000:12100", "gloo_port_range": "13000:13100",
+                                       "shm_size_bytes": 134217728}}
+    proc, url = run_master_with_config(tmp_path / "m", cfg)
+    assert proc is not None, url
+    try:
+        os.environ["DET_CONFIG_DIR"] = str(tmp_path / "m" / "cfg")
+        s = Session(url)
+        info = s.get("/info")
+        assert info["cluster_name"] == "cfg-test" and info["scheduler"] == "priority"
+        shown = s.get("/api/v1/master/config")
+        assert shown["fitting_policy"] == "worst" and shown["tensorboard_timeout"] == 2 and shown["log"]["level"] == "error"
+        # log.level error: the usual start-up chatter is not in the master's log
+        assert "master listening" not in (tmp_path / "m" / "master.log").read_text()
+        # CORS: the caller's origin is allowed, pre-flights are answered
+        req = urllib.request.Request(f"http://{url}/info", headers={"Origin": "http://ui.example"})
+        with urllib.request.urlopen(req, timeout=5) as resp:
+            assert resp.headers["Access-Control-Allow-Origin"] == "http://ui.example" and "Authorization" in resp.headers["Access-Control-Allow-Headers"]
+        req = urllib.request.Request(f"http://{url}/api/v1/experiments", method="OPTIONS", headers={"Origin": "http://ui.example"})
+        with urllib.request.urlopen(req, timeout=5) as resp:
+            assert resp.status == 204 and "PATCH" in resp.headers["Access-Control-Allow-Methods"]
+        # the defaults reach a trial's environment (a command prints what a trial of the same master would get is not enough:
+        # run a trial whose model definition checks them)
+        model = tmp_path / "model"
+        model.mkdir()
+        (model / "model_def.py").write_text((pathlib.Path(NOOP_DIR) / "model_def.py").read_text() + '''
+
+import os as _os
+
+assert _os.environ["DET_TRIAL_RUNNER_NETWORK_INTERFACE"] == "lo" and _os.environ["NCCL_SOCKET_IFNAME"] == "lo" and _os.environ["GLOO_SOCKET_IFNAME"] == "lo"
+assert _os.environ["NCCL_PORT_RANGE"] == "12000:12100" and _os.environ["GLOO_PORT_RANGE"] == "13000:13100"
+assert int(_os.environ["DET_SHM_SIZE"]) == 134217728
+''')
+        d = Determined(url)
+        exp = d.create_experiment(noop_config(tmp_path, batches=1), str(model))
+        assert exp.wait(timeout=120) == "COMPLETED", trial_messages(d, exp)[-10:]
+        # an idle TensorBoard is reaped after tensorboard_timeout seconds
+        done = exp
+        tb = s.post("/api/v1/tensorboards", {"argv": ["sleep", "600"], "experiment_ids": [done.id], "proxy": False})
+        t0 = time.time()
+        while time.time() - t0 < 20 and s.get(f"/api/v1/tensorboards/{tb['id']}")["state"] != "TERMINATED":
+            time.sleep(0.25)
+        assert s.get(f"/api/v1/tensorboards/{tb['id']}")["state"] == "TERMINATED" and time.time() - t0 >= 1.5
+    finally:
+        stop_master(proc)
+
+
+@pytest.mark.skipif(os.geteuid() != 0, reason="switching users needs an agent that runs as root")
+def test_security_default_task_is_the_identity_of_unlinked_users_tasks(tmp_path):
+    proc, url = run_master_with_config(tmp_path / "m", {"security": {"default_task": {"uid": 65534, "gid": 65534, "user": "nobody", "group": "nogroup"}}})
+    assert proc is not None, url
+    try:
+        os.environ["DET_CONFIG_DIR"] = str(tmp_path / "m" / "cfg")
+        s = Session(url)
+        cmd = s.post("/api/v1/commands", {"argv": ["id", "-u"]})
+        for _ in range(100):
+            cur = s.get(f"/api/v1/commands/{cmd['id']}")
+            if cur["state"] == "TERMINATED":
+                break
+            time.sleep(0.1)
+        assert [l["message"] for l in cur["logs"]] == ["65534"]
+        # a linked user keeps their own identity
+        s.request("PATCH", "/api/v1/users/determined", {"agent_user_group": {"uid": 0, "gid": 0, "user": "root", "group": "root"}})
+        cmd = s.post("/api/v1/commands", {"argv": ["id", "-u"]})
+        for _ in range(100):
+            cur = s.get(f"/api/v1/commands/{cmd['id']}")
+            if cur["state"] == "TERMINATED":
+                break
+            time.sleep(0.1)
+        assert [l["message"] for l in cur["logs"]] == ["0"]
+    finally:
+        stop_master(proc)
