@@ -180,6 +180,12 @@ class ContainerManager {
     std::lock_guard<std::mutex> g(mu_);
     pycache_dir_ = dir;
   }
+  // Environment every task on this node starts with unless its own spec sets the variable (the agent's http_proxy /
+  // https_proxy / ftp_proxy / no_proxy options, reference agent/internal/options.go).
+  void set_task_env(const std::map<std::string, std::string>& env) {
+    std::lock_guard<std::mutex> g(mu_);
+    task_env_ = env;
+  }
   void prewarm(const std::string& key) {
     {
       std::lock_guard<std::mutex> g(mu_);
@@ -238,6 +244,10 @@ class ContainerManager {
     on_event_({spec.container_id, "PULLING", 0, ""});   // no image to pull: state kept for protocol parity
     on_event_({spec.container_id, "STARTING", 0, ""});
     std::map<std::string, std::string> env = spec.env;
+    {
+      std::lock_guard<std::mutex> g(mu_);
+      for (auto& kv : task_env_) env.emplace(kv.first, kv.second);      // the spec's own value wins
+    }
     env["DET_CONTAINER_ID"] = spec.container_id;
     std::string slot_ids = "[", gpu_mask;
     bool use_gpu = false;
@@ -539,6 +549,7 @@ class ContainerManager {
   }
   EventFn on_event_;
   LogFn on_log_;
+  std::map<std::string, std::string> task_env_;
   std::mutex mu_;
   std::map<std::string, pid_t> pids_;
   std::map<std::string, std::shared_ptr<WarmWorker>> warm_;   // idle workers by slot key

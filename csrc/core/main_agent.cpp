@@ -12,7 +12,10 @@
 #include <unistd.h>
 
 #include <csignal>
+#include <fstream>
 #include <iostream>
+#include <set>
+#include <sstream>
 #include <mutex>
 #include <thread>
 
@@ -28,6 +31,52 @@ int main(int argc, char** argv) {
   int port = 8080, artificial = 0;
   bool detect_only = false;
   TlsClientOptions tls;
+  std::map<std::string, std::string> task_env;
+  // --config-file F (or DET_AGENT_CONFIG_FILE): the agent.yaml of the reference as JSON — master_host, master_port, agent_id,
+  // label / resource_pool, slot_type, visible_gpus, artificial_slots, container_master_host, security.tls.{enabled, skip_verify,
+  // master_cert, master_cert_name}, http_proxy / https_proxy / ftp_proxy / no_proxy. Environment variables and flags override it.
+  std::string config_file = getenv("DET_AGENT_CONFIG_FILE") ? getenv("DET_AGENT_CONFIG_FILE") : "";
+  for (int i = 1; i + 1 < argc; ++i) if (std::string(argv[i]) == "--config-file") config_file = argv[i + 1];
+  std::string file_id;
+  if (!config_file.empty()) {
+    std::ifstream f(config_file);
+    if (!f) { std::cerr << "det-agent: cannot read " << config_file << "\n"; return 2; }
+    std::stringstream ss;
+    ss << f.rdbuf();
+    Json j;
+    try { j = Json::parse(ss.str()); } catch (const std::exception& e) { std::cerr << "det-agent: " << config_file << ": " << e.what() << "\n"; return 2; }
+    if (!j.is_object()) { std::cerr << "det-agent: " << config_file << ": a configuration is a mapping\n"; return 2; }
+    static const std::set<std::string> known = {"master_host", "master_port", "agent_id", "label", "resource_pool", "slot_type", "visible_gpus",
+                                                "artificial_slots", "container_master_host", "container_master_port", "security", "http_proxy",
+                                                "https_proxy", "ftp_proxy", "no_proxy", "warm_workers", "config_file", "fluent", "api_enabled",
+                                                "bind_ip", "bind_port"};
+    for (auto& kv : j.obj())
+      if (!known.count(kv.first)) { std::cerr << "det-agent: unknown field in agent config: '" << kv.first << "'\n"; return 2; }
+    const Json& c = j;
+    host = c["master_host"].str_or(host);
+    port = static_cast<int>(c["master_port"].as_int(port));
+    file_id = c["agent_id"].str_or("");
+    label = c["label"].str_or(c["resource_pool"].str_or(label));
+    slot_type = c["slot_type"].str_or(slot_type);
+    visible = c["visible_gpus"].str_or(visible);
+    artificial = static_cast<int>(c["artificial_slots"].as_int(artificial));
+    container_master_host = c["container_master_host"].str_or(container_master_host);
+    warm_mode = c["warm_workers"].str_or(warm_mode);
+    const Json& t = c["security"]["tls"];
+    if (t.is_object()) {
+      tls.enabled = t["enabled"].as_bool(tls.enabled);
+      tls.skip_verify = t["skip_verify"].as_bool(tls.skip_verify);
+      tls.ca_file = t["master_cert"].str_or(tls.ca_file);
+      tls.cert_name = t["master_cert_name"].str_or(tls.cert_name);
+    }
+    for (const char* k : {"http_proxy", "https_proxy", "ftp_proxy", "no_proxy"})
+      if (!c[k].str_or("").empty()) {
+        std::string upper = k;
+        for (auto& ch : upper) ch = static_cast<char>(toupper(ch));
+        task_env[k] = c[k].as_string();
+        task_env[upper] = c[k].as_string();
+      }
+  }
   auto envs = [](const char* k, std::string& dst) { if (const char* v = getenv(k)) dst = v; };
   auto envb = [](const char* k, bool& dst) { if (const char* v = getenv(k)) dst = std::string(v) == "1" || std::string(v) == "true"; };
   envs("DET_AGENT_MASTER_HOST", host); envs("DET_AGENT_LABEL", label); envs("DET_AGENT_SLOT_TYPE", slot_type);
@@ -37,11 +86,12 @@ int main(int argc, char** argv) {
   if (const char* v = getenv("DET_AGENT_MASTER_PORT")) port = atoi(v);
   char hostname[256] = "agent";
   gethostname(hostname, sizeof hostname);
-  id = std::string("agent-") + hostname;
+  id = file_id.empty() ? std::string("agent-") + hostname : file_id;
   for (int i = 1; i < argc; ++i) {
     const std::string a = argv[i];
     auto next = [&]() -> std::string { return i + 1 < argc ? argv[++i] : ""; };
-    if (a == "--master-host") host = next();
+    if (a == "--config-file") next();
+    else if (a == "--master-host") host = next();
     else if (a == "--master-port") port = atoi(next().c_str());
     else if (a == "--agent-id") id = next();
     else if (a == "--label") label = next();
@@ -100,6 +150,7 @@ int main(int argc, char** argv) {
         pending_logs.push_back(e);
       });
   cm.set_pycache_dir(pycache_dir);
+  cm.set_task_env(task_env);
   cm.set_slot_count(static_cast<int>(devices.size()));
   cm.enable_warm(warm_mode, warm_python, warm_root);
   if (warm_mode == "eager" && !warm_python.empty())

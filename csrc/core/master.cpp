@@ -158,7 +158,8 @@ class CommandActor : public Actor {
   void pre_start(Context& ctx) override {
     set_state("PENDING");
     m_->system.tell(m_->rm, "allocate", obj({{"task_id", task_id_}, {"name", spec_["description"].str_or(task_id_)}, {"group", task_id_},
-                                             {"slots_needed", spec_["slots"].as_int(0)}, {"non_preemptible", true}, {"single_agent", true}}), ctx.self());
+                                             {"slots_needed", spec_["slots"].as_int(0)}, {"non_preemptible", true}, {"single_agent", true},
+                                             {"label", spec_["config"]["resources"]["agent_label"].str_or("")}}), ctx.self());
   }
   void receive(Context& ctx, const Message& msg) override {
     if (msg.type == "resources_allocated") {

@@ -69,6 +69,40 @@ def test_trial_runs_on_remote_agent(slotless_master):
     assert logs, "the remote agent's log lines reached the master"
 
 
+def test_agent_configuration_file_and_proxy_environment(slotless_master, tmp_path):
+    """det-agent --config-file: the reference's agent.yaml keys (as JSON); flags override the file; the proxy settings reach
+    the tasks the agent runs (reference agent/internal/options.go); unknown keys are refused."""
+    cfg = tmp_path / "agent.json"
+    cfg.write_text(json.dumps({"master_host": "127.0.0.1", "master_port": slotless_master["port"], "agent_id": "from-file", "label": "file-label",
+                               "artificial_slots": 1, "http_proxy": "http://proxy.example:3128", "no_proxy": "localhost,127.0.0.1",
+                               "security": {"tls": {"enabled": False}}, "fluent": {"image": "ignored"}}))
+    agent = subprocess.Popen([str(LIB / "det-agent"), "--config-file", str(cfg), "--label", "flag-label"], stdout=open(tmp_path / "agent.log", "w"),
+                             stderr=subprocess.STDOUT)
+    try:
+        c = MasterClient("127.0.0.1", slotless_master["port"])
+        for _ in range(100):
+            agents = {a["id"]: a for a in c.request("GET", "/api/v1/agents")}
+            if "from-file" in agents:
+                break
+            time.sleep(0.1)
+        assert agents["from-file"]["num_slots"] == 1 and agents["from-file"]["label"] == "flag-label"
+        # a task that asks for that label lands on this agent and sees the proxy settings
+        cmd = c.request("POST", "/api/v1/commands", {"argv": ["sh", "-c", "echo $http_proxy $HTTP_PROXY $no_proxy"], "slots": 1,
+                                                     "config": {"resources": {"agent_label": "flag-label"}}})
+        for _ in range(150):
+            cur = c.request("GET", f"/api/v1/commands/{cmd['id']}")
+            if cur["state"] == "TERMINATED":
+                break
+            time.sleep(0.1)
+        assert [l["message"] for l in cur["logs"]] == ["http://proxy.example:3128 http://proxy.example:3128 localhost,127.0.0.1"], cur
+    finally:
+        agent.terminate()
+        agent.wait(timeout=10)
+    cfg.write_text(json.dumps({"master_host": "127.0.0.1", "colour": "red"}))
+    bad = subprocess.run([str(LIB / "det-agent"), "--config-file", str(cfg)], capture_output=True, text=True, timeout=10)
+    assert bad.returncode == 2 and "unknown field in agent config: 'colour'" in bad.stderr
+
+
 def test_rw_coordinator_leases(slotless_master):
     c = MasterClient("127.0.0.1", slotless_master["port"])
     r1 = c.request("POST", "/api/v1/rw_coordinator/ds1/read_lock", {"wait_ms": 1000})
