@@ -297,7 +297,7 @@ class TrialActor : public Actor {
     if (w.kind == Workload::RunStep) {
       units = units_from_batches(w.num_batches, seq_.unit_context());
       m_->store.append("steps", tkey, obj({{"trial_id", trial_id_}, {"step_id", w.step_id}, {"num_batches", w.num_batches},
-                                            {"total_batches", w.total_batches_processed + w.num_batches}, {"state", msg.has_exited_reason ? "ERROR" : "COMPLETED"},
+                                            {"total_batches", w.total_batches_processed + w.num_batches}, {"state", msg.has_exited_reason && msg.exited_reason == ExitedReason::Errored ? "ERROR" : "COMPLETED"},
                                             {"start_time", body["start_time"]}, {"end_time", body["end_time"]}, {"metrics", body["metrics"]}}));
     } else if (w.kind == Workload::ComputeValidationMetrics) {
       m_->store.append("validations", tkey, obj({{"trial_id", trial_id_}, {"step_id", w.step_id}, {"total_batches", w.total_batches_processed},

@@ -64,8 +64,14 @@ def test_one_batch(controller_cls: Optional[Type] = None, native_context_cls: Op
             ckpt = pathlib.Path(checkpoint_dir) if checkpoint_dir else pathlib.Path(tmp) / "checkpoint"
             controller = build(_make_test_workloads(ckpt, cfg, results))
             controller.run()
-            if trial_class is not None and not (ckpt / "state_dict.pth").exists():
-                raise AssertionError("checkpoint workload did not write state_dict.pth")
+            if trial_class is not None:
+                # a PyTorchTrial checkpoint has state_dict.pth; other trial interfaces choose their own files, but write some
+                from ..pytorch import PyTorchTrial
+
+                if issubclass(trial_class, PyTorchTrial) and not (ckpt / "state_dict.pth").exists():
+                    raise AssertionError("checkpoint workload did not write state_dict.pth")
+                if not ckpt.exists() or not any(ckpt.iterdir()):
+                    raise AssertionError("checkpoint workload wrote nothing")
             results["checkpoint_files"] = sorted(p.name for p in ckpt.iterdir()) if ckpt.exists() else []
         log.info("The test experiment passed")
 

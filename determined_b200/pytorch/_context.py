@@ -57,14 +57,32 @@ class _LossScaler:
 
 
 class _Experimental:
-    """``context.experimental`` — B200-specific opt-ins that have no counterpart in the reference."""
+    """``context.experimental`` — B200-specific opt-ins, plus the data-layer decorators the reference hangs here
+    (``harness/determined/_experimental_context.py``: ``cache_train_dataset`` / ``cache_validation_dataset``)."""
 
     def __init__(self, parent: "PyTorchTrialContext") -> None:
         self._parent = parent
+        self._data_layer: Any = None
         self.cuda_graphs = False
         self.graph_warmup_batches = 3
         self._step_dev: Optional[torch.Tensor] = None
         self._step_host: Optional[torch.Tensor] = None
+
+    def _layer(self) -> Any:
+        if self._data_layer is None:
+            from .. import data_layer
+
+            self._data_layer = data_layer.from_context(self._parent)
+        return self._data_layer
+
+    def cache_train_dataset(self, dataset_id: str, dataset_version: str, shuffle: bool = False,
+                            skip_shuffle_at_epoch_end: bool = False) -> Any:
+        """Decorator: build the training data set once per (id, version) and serve the cached copy afterwards — to this trial
+        positioned at its resume offset / shard (``determined_b200/data_layer.py``)."""
+        return self._layer().cache_train_dataset(dataset_id, dataset_version, shuffle, skip_shuffle_at_epoch_end)
+
+    def cache_validation_dataset(self, dataset_id: str, dataset_version: str, shuffle: bool = False) -> Any:
+        return self._layer().cache_validation_dataset(dataset_id, dataset_version, shuffle)
 
     def step_info(self) -> torch.Tensor:
         """Device tensor ``[epoch_idx, batch_idx]`` (fp32) of the batch being trained, refreshed by the controller BEFORE

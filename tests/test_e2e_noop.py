@@ -166,3 +166,26 @@ def test_a_training_step_longer_than_the_long_poll(master):
     exp = d.create_experiment(cfg, NOOP_DIR)
     assert exp.wait(timeout=180) == "COMPLETED"
     assert only_trial(exp)["total_batches_processed"] == 1
+
+
+def test_boosted_trees_trial_runs_under_the_master(master):
+    """A trial that is not a neural network (a CallbackTrialController over boosting rounds) goes through the same master /
+    harness path: scheduling units of boosting rounds, validations, a checkpoint, the searcher metric."""
+    import yaml
+
+    d = Determined(master["url"])
+    ex = ROOT / "examples" / "decision_trees" / "gbt_titanic_pytorch"
+    cfg = yaml.safe_load((ex / "const.yaml").read_text())
+    cfg["hyperparameters"]["n_trees"] = 20
+    cfg["searcher"]["max_length"] = {"batches": 20}
+    cfg["scheduling_unit"] = 5
+    cfg["min_validation_period"] = {"batches": 10}
+    cfg["checkpoint_storage"] = {"type": "shared_fs", "host_path": str(master["tmp"] / "ckpts")}
+    exp = d.create_experiment(cfg, str(ex))
+    assert exp.wait(timeout=180) == "COMPLETED"
+    t = only_trial(exp)
+    assert t["total_batches_processed"] == 20 and len(t["validations"]) >= 2
+    last = sorted(t["validations"], key=lambda v: v["total_batches"])[-1]["metrics"]["validation_metrics"]
+    assert last["n_trees"] == 20 and last["accuracy"] > 0.7
+    ck = d.get_trial(t["id"]).select_checkpoint(latest=True)
+    assert "boosted_trees.pt" in ck.resources

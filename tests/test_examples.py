@@ -14,7 +14,8 @@ CONFIGS = sorted((ROOT / "examples").glob("*/*/*.yaml"))
 def test_examples_present():
     names = {p.parent.name for p in CONFIGS}
     assert {"mnist_pytorch", "cifar10_pytorch", "resnet50_imagenet_pytorch", "bert_glue_pytorch", "gan_mnist_pytorch",
-            "dcgan_pytorch"} <= names
+            "dcgan_pytorch", "fashion_mnist_pytorch", "iris_pytorch", "unets_pytorch", "data_layer_mnist_pytorch",
+            "gbt_titanic_pytorch"} <= names
 
 
 @pytest.mark.parametrize("path", CONFIGS, ids=lambda p: f"{p.parent.name}/{p.name}")
