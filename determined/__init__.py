@@ -8,7 +8,7 @@ from determined_b200 import *  # noqa: F401,F403
 from determined_b200 import __version__  # noqa: F401
 
 for _name in ("pytorch", "experimental", "workload", "storage", "load", "constants", "utils", "ops", "models",
-              "parallel"):
+              "parallel", "keras"):
     try:
         _mod = importlib.import_module(f"determined_b200.{_name}")
     except Exception:  # pragma: no cover - optional pieces

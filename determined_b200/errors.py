@@ -13,6 +13,10 @@ class InvalidConfigurationException(InvalidExperimentException):
     pass
 
 
+class InvalidDataTypeException(InvalidExperimentException):
+    """The trial handed the harness input data of a kind it cannot iterate."""
+
+
 class InternalException(Exception):
     """A bug in the harness itself."""
 
