@@ -287,14 +287,20 @@ void Master::log(const std::string& level, const std::string& msg) {
   Json e = obj({{"time", now_rfc3339()}, {"level", level}, {"message", msg}});
   {
     std::lock_guard<std::mutex> g(log_mu_);
+    e["id"] = log_seq_++;
     log_ring_.push_back(e);
     if (log_ring_.size() > 25000) log_ring_.pop_front();
   }
   fprintf(stderr, "[%s] %s: %s\n", e["time"].as_string().c_str(), level.c_str(), msg.c_str());
 }
-std::vector<Json> Master::recent_logs(size_t limit) {
+std::vector<Json> Master::recent_logs(size_t limit, long long after_id) {
   std::lock_guard<std::mutex> g(log_mu_);
   std::vector<Json> out;
+  if (after_id >= 0) {      // a follower: everything newer than what it has seen, oldest first
+    for (auto& e : log_ring_)
+      if (e["id"].as_int(0) > after_id && out.size() < limit) out.push_back(e);
+    return out;
+  }
   size_t start = log_ring_.size() > limit ? log_ring_.size() - limit : 0;
   for (size_t i = start; i < log_ring_.size(); ++i) out.push_back(log_ring_[i]);
   return out;

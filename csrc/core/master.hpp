@@ -95,7 +95,7 @@ class Master {
   void log(const std::string& level, const std::string& msg);
   // usage telemetry (reference: master/internal/telemetry — Segment track calls): one JSON line per event, opt-in
   void report_telemetry(const std::string& event, const Json& properties);
-  std::vector<Json> recent_logs(size_t limit);
+  std::vector<Json> recent_logs(size_t limit, long long after_id = -1);   // entries carry a running "id"; after_id: only newer ones
 
   // services used by actors
   long long create_experiment(const Json& resolved_config, const Json& model_definition, long long parent_id, bool activate,
@@ -122,6 +122,7 @@ class Master {
   void restore_experiments();
   std::mutex log_mu_;
   std::deque<Json> log_ring_;
+  long long log_seq_ = 0;
   std::mutex container_mu_;
   std::map<std::string, std::pair<ActorRef, long long>> container_owner_;
 };

@@ -229,7 +229,10 @@ tick();setInterval(tick,2000);
   http.route("GET", "/api/v1/master", info);
   http.route("GET", "/api/v1/master/config", [m](const HttpRequest&) { return ok(m->cfg.to_json()); });
   http.route("GET", "/logs", [m](const HttpRequest& r) { return ok(arr(m->recent_logs(static_cast<size_t>(r.qi("limit", 1000))))); });
-  http.route("GET", "/api/v1/master/logs", [m](const HttpRequest& r) { return ok(arr(m->recent_logs(static_cast<size_t>(r.qi("limit", 1000))))); });
+  // the last `limit` lines of the master's log, or — for followers — the lines after the one with id `after`
+  http.route("GET", "/api/v1/master/logs", [m](const HttpRequest& r) {
+    return ok(arr(m->recent_logs(static_cast<size_t>(std::max<long long>(0, r.qi("limit", 1000))), r.q("after").empty() ? -1 : r.qi("after", -1))));
+  });
 
   // ---- auth / users ----
   http.route("POST", "/api/v1/auth/login", [m](const HttpRequest& r) {

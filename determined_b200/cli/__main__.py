@@ -380,7 +380,13 @@ def slot_toggle(verb: str):
 
 def agent_toggle(verb: str):
     def run(a: argparse.Namespace) -> int:
-        Session(a.master, a.user).post(f"/api/v1/agents/{a.agent_id}/{verb}")
+        s = Session(a.master, a.user)
+        if bool(a.agent_id) == bool(a.all):
+            print("give an agent id or --all", file=sys.stderr)
+            return 1
+        for agent_id in ([a.agent_id] if a.agent_id else sorted(x["id"] for x in s.get("/api/v1/agents"))):
+            s.post(f"/api/v1/agents/{agent_id}/{verb}")
+            print(f"{verb.capitalize()}d agent {agent_id}")
         return 0
     return run
 
@@ -396,9 +402,18 @@ def master_config(a: argparse.Namespace) -> int:
 
 
 def master_logs(a: argparse.Namespace) -> int:
-    for l in Session(a.master, a.user).get(f"/api/v1/master/logs?limit={a.tail or 1000}"):
-        print(l["time"], l["level"].upper(), l["message"])
-    return 0
+    s = Session(a.master, a.user)
+    lines = s.get(f"/api/v1/master/logs?limit={a.tail or 25000}")
+    last = -1
+    while True:
+        for l in lines:
+            print(l["time"], l["level"].upper(), l["message"], flush=True)
+        if lines:
+            last = lines[-1]["id"]
+        if not a.follow:
+            return 0
+        time.sleep(1.0)
+        lines = s.get(f"/api/v1/master/logs?after={last}&limit=5000")
 
 
 def master_up(a: argparse.Namespace) -> int:
@@ -764,8 +779,8 @@ def build_parser() -> argparse.ArgumentParser:
     ps.set_defaults(func=lambda a: preview_search_local(a) if a.offline else preview_search(a))
     ag = group("agent", ["a"])
     cmd(ag, "list", agent_list, A("--json", action="store_true"), aliases=["ls"])
-    cmd(ag, "enable", agent_toggle("enable"), A("agent_id"))
-    cmd(ag, "disable", agent_toggle("disable"), A("agent_id"))
+    cmd(ag, "enable", agent_toggle("enable"), A("agent_id", nargs="?"), A("--all", action="store_true", help="every agent"))
+    cmd(ag, "disable", agent_toggle("disable"), A("agent_id", nargs="?"), A("--all", action="store_true", help="every agent"))
     cmd(ag, "detect", agent_detect)
     sl = group("slot", ["s"])
     cmd(sl, "list", slot_list, A("--json", action="store_true"), aliases=["ls"])
@@ -774,7 +789,7 @@ def build_parser() -> argparse.ArgumentParser:
     ms = group("master")
     cmd(ms, "info", master_info)
     cmd(ms, "config", master_config)
-    cmd(ms, "logs", master_logs, A("--tail", type=int))
+    cmd(ms, "logs", master_logs, A("--tail", type=int), A("--follow", "-f", action="store_true"))
     cmd(ms, "up", master_up, A("--port", type=int, default=8080), A("--data-dir", default="/tmp/determined-master"),
         A("--scheduler", default="fair_share"), A("--artificial-slots", type=int, default=0))
     us = group("user", ["u"])

@@ -436,3 +436,35 @@ def test_security_default_task_is_the_identity_of_unlinked_users_tasks(tmp_path)
         assert [l["message"] for l in cur["logs"]] == ["0"]
     finally:
         stop_master(proc)
+
+
+def test_master_logs_follow_and_agent_toggles(master):
+    s = Session(master["url"])
+    lines = s.get("/api/v1/master/logs?limit=5")
+    assert lines and [l["id"] for l in lines] == sorted(l["id"] for l in lines)
+    newest = lines[-1]["id"]
+    assert s.get(f"/api/v1/master/logs?after={newest}") == []
+    d = Determined(master["url"])
+    d.create_experiment(noop_config(master["tmp"], batches=1), NOOP_DIR).wait(timeout=120)        # makes the master log something
+    newer = s.get(f"/api/v1/master/logs?after={newest}")
+    assert newer and all(l["id"] > newest for l in newer) and any("created experiment" in l["message"] for l in newer)
+    r = det(master, "master", "logs", "--tail", "3")
+    assert r.returncode == 0 and len(r.stdout.splitlines()) == 3
+    # --follow keeps printing until it is stopped
+    p = subprocess.Popen([sys.executable, "-m", "determined_b200.cli", "-m", master["url"], "master", "logs", "--tail", "1", "-f"], stdout=subprocess.PIPE,
+                         text=True, env=master["env"], cwd=str(ROOT))
+    try:
+        time.sleep(3.0)
+        d.create_experiment(noop_config(master["tmp"], batches=1), NOOP_DIR, activate=False).cancel()
+        time.sleep(3.0)
+    finally:
+        p.terminate()
+    out = p.communicate(timeout=10)[0]
+    assert len(out.splitlines()) >= 2 and "created experiment" in out
+    # agent enable / disable: one agent or --all
+    assert det(master, "agent", "disable").returncode != 0
+    r = det(master, "agent", "disable", "--all")
+    assert r.returncode == 0 and "Disabled agent agent-local" in r.stdout
+    assert all(not a["enabled"] for a in json.loads(det(master, "agent", "list", "--json").stdout))
+    r = det(master, "agent", "enable", "agent-local")
+    assert r.returncode == 0 and all(a["enabled"] for a in json.loads(det(master, "agent", "list", "--json").stdout))
